@@ -1,0 +1,165 @@
+/* qb200.h - C ABI of libqb200.so: the B200 (sm_100a) fake-quantization hot path.
+ *
+ * The reference (amishacorns/quantized.pytorch) is pure Python on ATen and has NO FFI of its own;
+ * each entry point below names the reference code (models/modules/quantize.py:LINE) it replaces.
+ * INTEGRATION.md shows the ctypes binding a maintainer of the reference would add.
+ *
+ * Conventions
+ *  - plain pointers and sizes only; every pointer is DEVICE memory unless it says "host";
+ *  - the caller owns every buffer; the library keeps no reference past the stream work it enqueues;
+ *  - every call takes the CUDA stream explicitly (void* = cudaStream_t) and never synchronises;
+ *  - returns 0 on success, a negative qb_status otherwise; qb_last_error() gives the message of the
+ *    last failure on the calling thread.  There is no CPU fallback: no device => QB_ERR_CUDA.
+ *  - "range" is float[2] = {min,max} in device memory, so no value ever visits the host on the step path
+ *    (the reference does float(tensor) twice per quantizer, quantize.py:126,132,249,486,493).
+ */
+#ifndef QB200_H
+#define QB200_H
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef enum {
+    QB_OK = 0,
+    QB_ERR_ARG = -1,         /* null pointer, non-positive size, unsupported bit width ...   */
+    QB_ERR_UNSUPPORTED = -2, /* a shape/option this build has no kernel for                  */
+    QB_ERR_CUDA = -3,        /* a CUDA runtime/driver call failed (message has the cudaError) */
+    QB_ERR_WORKSPACE = -4    /* workspace too small (see the *_ws_bytes helpers)             */
+} qb_status;
+
+/* How the scale is derived from {min,max} - both exist in the reference (quantize.py:71-75):     */
+#define QB_SCALE_DOUBLE 0 /* Python-float range: s = max((double)(max-min)/(2^b-1), 1e-8) -> fp32  */
+#define QB_SCALE_FLOAT 1  /* tensor range:       s = clamp_min((max-min)/(float)(2^b-1), 1e-8f)    */
+
+const char* qb_last_error(void);
+int qb_version(void);
+/* device properties the host side sizes launches with; fails with QB_ERR_CUDA if no sm_100 device */
+int qb_device_info(int device, int* sm_count, int* cc_major, int* cc_minor, size_t* l2_bytes);
+
+/* ---------------------------------------------------------------------------------------------------
+ * QuantMeasure statistics - quantize.py:226-235 (per-sample min/max averaged over the batch, global
+ * mean and unbiased std; four ATen reductions + 2 host syncs there, one pass here).
+ *   x        [B, inner] fp32 contiguous
+ *   stats    double[8] out: {sum_b min_b, sum_b max_b, sum x, sum x^2, global min, global max, n, B}
+ *   ws       workspace, qb_measure_ws_bytes(B) bytes, zero-filled ONCE by the caller before first use
+ *            (the kernel leaves it clean); one workspace per concurrently running call.
+ * Sums are fp64 and combined in a fixed order: results are run-to-run deterministic.            */
+size_t qb_measure_ws_bytes(int64_t B);
+int qb_measure_stats(const float* x, int64_t B, int64_t inner, double* stats, void* ws, size_t ws_bytes,
+                     void* stream);
+
+/* QuantMeasure buffer update + range selection - quantize.py:216-219,228-246,256-268.
+ *   stats      double[8] from qb_measure_stats (possibly all-reduced over ranks: entries 0-3 SUM,
+ *              4 MIN, 5 MAX, 6-7 SUM); ignored when training == 0
+ *   running    float[5] views, in the order running_min, running_max, num_measurements, running_var,
+ *              running_mean (each the reference's [1] buffer); updated in place when training
+ *   momentum   < 0 => cumulative average n/(n+1) (momentum=None in the reference)
+ *   method     0 'avg', 1 'aciq' (Laplace clipping, alpha table quantize.py:214; needs 2<=bits<=8)
+ *   range_out  float[2] the {min,max} this call quantizes with                                     */
+int qb_measure_finalize(const double* stats, float* running_min, float* running_max, float* num_measurements,
+                        float* running_var, float* running_mean, double momentum, int training, int method,
+                        int bits, float* range_out, void* stream);
+
+/* ---------------------------------------------------------------------------------------------------
+ * UniformQuantize.forward, min-anchored deterministic branch - quantize.py:66-75,90,95,100
+ * (what every quantize() call reaches, because of the argument shuffle at :159-160).
+ *   y = rne(clamp((x - min) / s, 0, 2^bits-1)) * s + min, true fp32 division, unfused mul/add.
+ *   range_dev  float[2] device {min,max}; if NULL the host doubles lo,hi are used instead
+ *   codes      optional uint8 (bits<=8) integer codes, same indexing as x; may be NULL
+ *   y          may alias x (in place) or be NULL when only codes are wanted                      */
+int qb_fakequant_affine(const float* x, float* y, uint8_t* codes, int64_t n, int bits, const float* range_dev,
+                        double lo, double hi, int scale_mode, void* stream);
+
+/* Per-row variant for weights - quantize.py:318-323,332-334: row_min/row_max over flatten(1) are
+ * computed here (and written out, they are the module's weight_min/weight_max buffers), then each
+ * row is quantized with its own QB_SCALE_FLOAT scale.  If compute_range == 0 the given row_min/max
+ * are used as is (frozen ranges / overwrite_params, quantize.py:301-312).                          */
+int qb_fakequant_rows(const float* w, float* wq, uint8_t* codes, int64_t rows, int64_t cols, int bits,
+                      float* row_min, float* row_max, int compute_range, void* stream);
+
+/* Global min/max of a tensor -> range_out float[2].  UniformQuantizeGrad.backward's
+ * float(g.min()), float(g.max()) (quantize.py:126,132) and the range-from-data case (:45-55).
+ *   ws: qb_minmax_ws_bytes() bytes, zero-filled once by the caller.                               */
+size_t qb_minmax_ws_bytes(void);
+int qb_minmax(const float* x, int64_t n, float* range_out, void* ws, size_t ws_bytes, void* stream);
+
+/* UniformQuantize.forward, zero-point + stochastic branch - quantize.py:77-88,92-98 (reached only
+ * from UniformQuantizeGrad.backward :137-138):
+ *   zp = trunc(clamp(-min/s, 0, 2^b-1)) in double;  q = rne(clamp(g/s + zp + u, 0, 2^b-1));  out = (q-zp)*s
+ *   noise   optional fp32 tensor of u in [-0.5,0.5) to inject (parity tests replay the reference's
+ *           uniform_ draws); if NULL u comes from Philox4x32-10 keyed by (seed, element index + offset);
+ *           stochastic == 0 => u = 0
+ *   step_dev optional device uint64 mixed into the Philox key (seed + step*golden) so that a captured
+ *           CUDA graph draws fresh noise on every replay; may be NULL
+ *   codes   optional uint8 codes q (bits<=8)                                                     */
+int qb_fakequant_grad(const float* g, float* out, uint8_t* codes, int64_t n, int bits, const float* range_dev,
+                      double lo, double hi, const float* noise, int stochastic, uint64_t seed, uint64_t offset,
+                      const uint64_t* step_dev, void* stream);
+
+/* Fused single-launch "range from the same tensor, then quantize" (cooperative grid sync):
+ * replaces qb_minmax + qb_fakequant_grad for the gradient path (12 B/elem: two reads, one write).
+ *   range_out float[2] receives the {min,max} used.  ws as for qb_minmax.                          */
+int qb_fakequant_grad_fused(const float* g, float* out, uint8_t* codes, int64_t n, int bits, float* range_out,
+                            const float* noise, int stochastic, uint64_t seed, uint64_t offset,
+                            const uint64_t* step_dev, void* ws, size_t ws_bytes, void* stream);
+
+/* ---------------------------------------------------------------------------------------------------
+ * RangeBN - quantize.py:461-505.  x is the ALREADY fake-quantized NCHW input [B,C,HW] (2-D inputs:
+ * HW = 1).  Chunking follows :468-469: channel c's elements in (b,h,w) order cut into num_chunks
+ * runs of L = B*HW/num_chunks (B*HW % num_chunks must be 0, as in the reference).
+ *
+ * qb_rangebn_stats: per (c,k) max / min and the flat (b*HW+p) index of their FIRST occurrence
+ * (ATen's tie-break, SURVEY.md KAT 8), and the per-channel reduction
+ *   red double[3*C] = {sum_k max_ck | sum_k min_ck | sum x_c}   (three planes of C)
+ * which is what crosses ranks under batch sharding (all-reduce SUM; each rank owns whole chunks).
+ *   amax,amin  int32[C*num_chunks] out (may be NULL in eval/no-grad)
+ *   ws         float[2*C*num_chunks] + double[C*num_chunks] scratch for the per-chunk values:
+ *              qb_rangebn_ws_bytes(C, num_chunks)                                                  */
+size_t qb_rangebn_ws_bytes(int64_t C, int num_chunks);
+int qb_rangebn_stats(const float* x, int64_t B, int64_t C, int64_t HW, int num_chunks, int32_t* amax,
+                     int32_t* amin, double* red, void* ws, size_t ws_bytes, void* stream);
+
+/* Per-channel finalize (:470-498): mean, scale = 1/((mean_max-mean_min)*scale_fix+eps), running
+ * buffer update (running <- running*momentum + new*(1-momentum)), then the three 8-bit vector
+ * quantizers: scale and gamma with QB_SCALE_DOUBLE over their own min/max, beta with
+ * QB_SCALE_FLOAT over its data range.  training == 0: mean/scale come from running_mean/var.
+ *   red       double[3*C] from qb_rangebn_stats (summed over ranks); num_chunks is the GLOBAL chunk count
+ *   count     global element count per channel (B*HW summed over ranks)
+ *   chunk_len L used in scale_fix (global)
+ *   outputs   mean[C], scale_raw[C] (unquantized 1/range, needed by backward), qscale[C], qgamma[C], qbeta[C]
+ *   gamma/beta may be NULL (affine=False): qgamma/qbeta are then not written.
+ * Single CTA; C up to 65536.                                                                      */
+int qb_rangebn_finalize(const double* red, int64_t C, int num_chunks,
+                        double count, double chunk_len, float eps, double momentum, int training, int bits,
+                        const float* gamma, const float* beta, float* running_mean, float* running_var,
+                        float* mean, float* scale_raw, float* qscale, float* qgamma, float* qbeta, void* stream);
+
+/* out = ((x - mean_c) * qscale_c) * qgamma_c + qbeta_c, four separately rounded fp32 ops (:488-499).
+ * qgamma / qbeta may be NULL.  out may alias x.                                                   */
+int qb_rangebn_apply(const float* x, float* out, int64_t B, int64_t C, int64_t HW, const float* mean,
+                     const float* qscale, const float* qgamma, const float* qbeta, void* stream);
+
+/* Backward of RangeBN given the (already quantized) output gradient gq - autograd of :467-499:
+ *   reduce: sg[c] = sum gq, sgx[c] = sum gq * x   (fp64)
+ *   apply : dx = gq*(qgamma_c*qscale_c) + a_c  and  dx[first argmax of chunk] += e_c, dx[first argmin] -= e_c
+ * with a_c, e_c produced by qb_rangebn_bwd_coeffs from the reduced sums:
+ *   dbeta = sg, dgamma = qscale*(sgx - mean*sg), dscale = qgamma*(sgx - mean*sg),
+ *   e = -scale_fix*scale_raw^2*dscale/num_chunks, a = -(qscale*qgamma*sg)/count.                    */
+size_t qb_rangebn_bwd_ws_bytes(int64_t C);
+int qb_rangebn_bwd_reduce(const float* gq, const float* x, int64_t B, int64_t C, int64_t HW, double* sg,
+                          double* sgx, void* ws, size_t ws_bytes, void* stream);
+int qb_rangebn_bwd_coeffs(const double* sg, const double* sgx, int64_t C, int num_chunks, double count,
+                          double chunk_len, int training, const float* mean, const float* scale_raw,
+                          const float* qscale, const float* qgamma, float* dgamma, float* dbeta, float* coef_a,
+                          float* coef_e, void* stream);
+int qb_rangebn_bwd_apply(const float* gq, float* dx, int64_t B, int64_t C, int64_t HW, int num_chunks,
+                         const float* qscale, const float* qgamma, const float* coef_a, const float* coef_e,
+                         const int32_t* amax, const int32_t* amin, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* QB200_H */

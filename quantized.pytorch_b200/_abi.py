@@ -1,0 +1,276 @@
+"""ctypes binding of libqb200.so (C ABI: include/qb200.h) + thin tensor-level wrappers.
+
+PyTorch is plumbing here: it owns device memory and streams; every compute call goes through
+the C ABI with raw pointers and the *current* CUDA stream of the calling thread (the autograd
+engine runs backward on its own thread, so the stream is looked up per call).
+There is NO fallback: if the library or a CUDA device is missing the call raises.
+"""
+import ctypes as C
+import os
+
+import torch
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libqb200.so")
+
+QB_SCALE_DOUBLE, QB_SCALE_FLOAT = 0, 1
+
+_p = C.c_void_p
+_i64, _i32, _u64, _dbl, _flt, _sz = C.c_int64, C.c_int, C.c_uint64, C.c_double, C.c_float, C.c_size_t
+
+# name -> (restype, argtypes); must list every function declared in include/qb200.h (tests check it)
+PROTOTYPES = {
+    "qb_last_error": (C.c_char_p, []),
+    "qb_version": (_i32, []),
+    "qb_device_info": (_i32, [_i32, C.POINTER(_i32), C.POINTER(_i32), C.POINTER(_i32), C.POINTER(_sz)]),
+    "qb_measure_ws_bytes": (_sz, [_i64]),
+    "qb_measure_stats": (_i32, [_p, _i64, _i64, _p, _p, _sz, _p]),
+    "qb_measure_finalize": (_i32, [_p, _p, _p, _p, _p, _p, _dbl, _i32, _i32, _i32, _p, _p]),
+    "qb_fakequant_affine": (_i32, [_p, _p, _p, _i64, _i32, _p, _dbl, _dbl, _i32, _p]),
+    "qb_fakequant_rows": (_i32, [_p, _p, _p, _i64, _i64, _i32, _p, _p, _i32, _p]),
+    "qb_minmax_ws_bytes": (_sz, []),
+    "qb_minmax": (_i32, [_p, _i64, _p, _p, _sz, _p]),
+    "qb_fakequant_grad": (_i32, [_p, _p, _p, _i64, _i32, _p, _dbl, _dbl, _p, _i32, _u64, _u64, _p, _p]),
+    "qb_fakequant_grad_fused": (_i32, [_p, _p, _p, _i64, _i32, _p, _p, _i32, _u64, _u64, _p, _p, _sz, _p]),
+    "qb_rangebn_ws_bytes": (_sz, [_i64, _i32]),
+    "qb_rangebn_stats": (_i32, [_p, _i64, _i64, _i64, _i32, _p, _p, _p, _p, _sz, _p]),
+    "qb_rangebn_finalize": (_i32, [_p, _i64, _i32, _dbl, _dbl, _flt, _dbl, _i32, _i32, _p, _p, _p, _p, _p, _p, _p, _p,
+                                   _p, _p]),
+    "qb_rangebn_apply": (_i32, [_p, _p, _i64, _i64, _i64, _p, _p, _p, _p, _p]),
+    "qb_rangebn_bwd_ws_bytes": (_sz, [_i64]),
+    "qb_rangebn_bwd_reduce": (_i32, [_p, _p, _i64, _i64, _i64, _p, _p, _p, _sz, _p]),
+    "qb_rangebn_bwd_coeffs": (_i32, [_p, _p, _i64, _i32, _dbl, _dbl, _i32, _p, _p, _p, _p, _p, _p, _p, _p, _p]),
+    "qb_rangebn_bwd_apply": (_i32, [_p, _p, _i64, _i64, _i64, _i32, _p, _p, _p, _p, _p, _p, _p]),
+}
+
+_lib = None
+
+
+class QB200Error(RuntimeError):
+    pass
+
+
+def load():
+    """Load libqb200.so (built by ``__graft_entry__.build()`` / ``make -C csrc``).  Raises if absent."""
+    global _lib
+    if _lib is None:
+        if not os.path.isfile(LIB_PATH):
+            raise QB200Error("libqb200.so not built: run `python -c 'import __graft_entry__ as g; g.build()'` "
+                             "(expected at %s); there is no CPU fallback" % LIB_PATH)
+        lib = C.CDLL(LIB_PATH)
+        for name, (res, args) in PROTOTYPES.items():
+            fn = getattr(lib, name)
+            fn.restype, fn.argtypes = res, args
+        _lib = lib
+    return _lib
+
+
+def last_error():
+    return load().qb_last_error().decode("utf-8", "replace")
+
+
+def _check(rc, what):
+    if rc != 0:
+        raise QB200Error("%s failed (%d): %s" % (what, rc, last_error()))
+
+
+def device_info(device=0):
+    sm, maj, mnr, l2 = _i32(), _i32(), _i32(), _sz()
+    _check(load().qb_device_info(device, C.byref(sm), C.byref(maj), C.byref(mnr), C.byref(l2)), "qb_device_info")
+    return dict(sm_count=sm.value, cc=(maj.value, mnr.value), l2_bytes=l2.value)
+
+
+# ----------------------------------------------------------------------------------------------
+# tensor-level helpers
+# ----------------------------------------------------------------------------------------------
+def _stream():
+    return torch.cuda.current_stream().cuda_stream
+
+
+def _ptr(t):
+    return None if t is None else t.data_ptr()
+
+
+def _f32c(t, name):
+    if not (t.is_cuda and t.dtype == torch.float32):
+        raise QB200Error("%s must be a CUDA float32 tensor (got %s on %s); there is no CPU fallback"
+                         % (name, t.dtype, t.device))
+    return t if t.is_contiguous() else t.contiguous()
+
+
+_ws_cache = {}
+
+
+def workspace(kind, nbytes, device):
+    """Zero-initialised scratch, one per (kind, device, stream, thread-of-use).  The kernels leave their
+    workspace clean, so it is zeroed only at creation."""
+    key = (kind, device.index, torch.cuda.current_stream(device).cuda_stream)
+    ws = _ws_cache.get(key)
+    if ws is None or ws.numel() < nbytes:
+        ws = torch.zeros(max(nbytes, 1), dtype=torch.uint8, device=device)
+        _ws_cache[key] = ws
+    return ws
+
+
+def measure_stats(x, stats=None):
+    """x [B, ...] -> double[8] stats tensor (see qb_measure_stats)."""
+    lib = load()
+    x = _f32c(x, "x")
+    B = x.size(0)
+    inner = x.numel() // max(B, 1)
+    if stats is None:
+        stats = torch.empty(8, dtype=torch.float64, device=x.device)
+    nb = lib.qb_measure_ws_bytes(B)
+    ws = workspace("measure", nb, x.device)
+    _check(lib.qb_measure_stats(_ptr(x), B, inner, _ptr(stats), _ptr(ws), ws.numel(), _stream()), "qb_measure_stats")
+    return stats
+
+
+def measure_finalize(stats, running, momentum, training, method, bits, range_out=None):
+    """running: tuple of the five [1] buffers (min, max, num_measurements, var, mean)."""
+    lib = load()
+    rmin, rmax, nmeas, rvar, rmean = running
+    if range_out is None:
+        range_out = torch.empty(2, dtype=torch.float32, device=rmin.device)
+    _check(lib.qb_measure_finalize(_ptr(stats), _ptr(rmin), _ptr(rmax), _ptr(nmeas), _ptr(rvar), _ptr(rmean),
+                                   -1.0 if momentum is None else float(momentum), int(training), int(method), int(bits),
+                                   _ptr(range_out), _stream()), "qb_measure_finalize")
+    return range_out
+
+
+def fakequant_affine(x, bits, range_dev=None, lo=0.0, hi=0.0, scale_mode=QB_SCALE_DOUBLE, out=None, codes=None,
+                     want_y=True):
+    lib = load()
+    x = _f32c(x, "x")
+    if want_y and out is None:
+        out = torch.empty_like(x)
+    _check(lib.qb_fakequant_affine(_ptr(x), _ptr(out) if want_y else None, _ptr(codes), x.numel(), int(bits),
+                                   _ptr(range_dev), float(lo), float(hi), int(scale_mode), _stream()),
+           "qb_fakequant_affine")
+    return out
+
+
+def fakequant_rows(w, bits, row_min=None, row_max=None, compute_range=True, out=None, codes=None, want_y=True):
+    lib = load()
+    w = _f32c(w, "w")
+    rows = w.size(0)
+    cols = w.numel() // max(rows, 1)
+    if row_min is None:
+        row_min = torch.empty(rows, dtype=torch.float32, device=w.device)
+        row_max = torch.empty(rows, dtype=torch.float32, device=w.device)
+    if want_y and out is None:
+        out = torch.empty_like(w)
+    _check(lib.qb_fakequant_rows(_ptr(w), _ptr(out) if want_y else None, _ptr(codes), rows, cols, int(bits),
+                                 _ptr(row_min), _ptr(row_max), int(compute_range), _stream()), "qb_fakequant_rows")
+    return out, row_min, row_max
+
+
+def minmax(x, range_out=None):
+    lib = load()
+    x = _f32c(x, "x")
+    if range_out is None:
+        range_out = torch.empty(2, dtype=torch.float32, device=x.device)
+    ws = workspace("minmax", lib.qb_minmax_ws_bytes(), x.device)
+    _check(lib.qb_minmax(_ptr(x), x.numel(), _ptr(range_out), _ptr(ws), ws.numel(), _stream()), "qb_minmax")
+    return range_out
+
+
+def fakequant_grad(g, bits, range_dev=None, lo=0.0, hi=0.0, noise=None, stochastic=True, seed=0, offset=0,
+                   step_dev=None, out=None, codes=None, want_y=True):
+    lib = load()
+    g = _f32c(g, "g")
+    if noise is not None:
+        noise = _f32c(noise, "noise")
+        if noise.numel() != g.numel():
+            raise QB200Error("noise has %d elements, gradient %d" % (noise.numel(), g.numel()))
+    if want_y and out is None:
+        out = torch.empty_like(g)
+    _check(lib.qb_fakequant_grad(_ptr(g), _ptr(out) if want_y else None, _ptr(codes), g.numel(), int(bits),
+                                 _ptr(range_dev), float(lo), float(hi), _ptr(noise), int(stochastic),
+                                 int(seed) & (2 ** 64 - 1), int(offset), _ptr(step_dev), _stream()), "qb_fakequant_grad")
+    return out
+
+
+def fakequant_grad_fused(g, bits, noise=None, stochastic=True, seed=0, offset=0, step_dev=None, out=None, codes=None,
+                         range_out=None, want_y=True):
+    """UniformQuantizeGrad.backward in one cooperative launch.  Returns (out, range_out)."""
+    lib = load()
+    g = _f32c(g, "g")
+    if noise is not None:
+        noise = _f32c(noise, "noise")
+        if noise.numel() != g.numel():
+            raise QB200Error("noise has %d elements, gradient %d" % (noise.numel(), g.numel()))
+    if want_y and out is None:
+        out = torch.empty_like(g)
+    if range_out is None:
+        range_out = torch.empty(2, dtype=torch.float32, device=g.device)
+    ws = workspace("minmax", lib.qb_minmax_ws_bytes(), g.device)
+    _check(lib.qb_fakequant_grad_fused(_ptr(g), _ptr(out) if want_y else None, _ptr(codes), g.numel(), int(bits),
+                                       _ptr(range_out), _ptr(noise), int(stochastic), int(seed) & (2 ** 64 - 1),
+                                       int(offset), _ptr(step_dev), _ptr(ws), ws.numel(), _stream()),
+           "qb_fakequant_grad_fused")
+    return out, range_out
+
+
+# ----------------------------------------------------------------------------------------------
+# RangeBN
+# ----------------------------------------------------------------------------------------------
+def rangebn_stats(x, B, Cn, HW, num_chunks, want_arg=True):
+    """x: quantized NCHW input.  Returns (red double[3*C], amax int32[C*K] | None, amin | None)."""
+    lib = load()
+    dev = x.device
+    red = torch.empty(3 * Cn, dtype=torch.float64, device=dev)
+    amax = torch.empty(Cn * num_chunks, dtype=torch.int32, device=dev) if want_arg else None
+    amin = torch.empty(Cn * num_chunks, dtype=torch.int32, device=dev) if want_arg else None
+    ws = workspace("rangebn", lib.qb_rangebn_ws_bytes(Cn, num_chunks), dev)
+    _check(lib.qb_rangebn_stats(_ptr(x), B, Cn, HW, num_chunks, _ptr(amax), _ptr(amin), _ptr(red), _ptr(ws), ws.numel(),
+                                _stream()), "qb_rangebn_stats")
+    return red, amax, amin
+
+
+def rangebn_finalize(red, Cn, num_chunks, count, chunk_len, eps, momentum, training, bits, gamma, beta, running_mean,
+                     running_var):
+    """Returns vec float[5, C]: rows mean, scale_raw, qscale, qgamma, qbeta."""
+    lib = load()
+    vec = torch.empty(5, Cn, dtype=torch.float32, device=running_mean.device)
+    _check(lib.qb_rangebn_finalize(_ptr(red), Cn, int(num_chunks), float(count), float(chunk_len), float(eps),
+                                   float(momentum), int(training), int(bits), _ptr(gamma), _ptr(beta),
+                                   _ptr(running_mean), _ptr(running_var), _ptr(vec[0]), _ptr(vec[1]), _ptr(vec[2]),
+                                   _ptr(vec[3]) if gamma is not None else None,
+                                   _ptr(vec[4]) if beta is not None else None, _stream()), "qb_rangebn_finalize")
+    return vec
+
+
+def rangebn_apply(x, B, Cn, HW, vec, has_gamma, has_beta, out=None):
+    lib = load()
+    if out is None:
+        out = torch.empty_like(x)
+    _check(lib.qb_rangebn_apply(_ptr(x), _ptr(out), B, Cn, HW, _ptr(vec[0]), _ptr(vec[2]),
+                                _ptr(vec[3]) if has_gamma else None, _ptr(vec[4]) if has_beta else None, _stream()),
+           "qb_rangebn_apply")
+    return out
+
+
+def rangebn_backward(gq, xq, B, Cn, HW, num_chunks, count, chunk_len, training, vec, has_gamma, amax, amin,
+                     reduce_hook=None):
+    """Returns (dx, dgamma, dbeta).  ``reduce_hook(sums)`` may all-reduce the double[2*C] sums in place
+    (batch-sharded training)."""
+    lib = load()
+    dev = gq.device
+    sums = torch.empty(2 * Cn, dtype=torch.float64, device=dev)
+    ws = workspace("rangebn_bwd", lib.qb_rangebn_bwd_ws_bytes(Cn), dev)
+    _check(lib.qb_rangebn_bwd_reduce(_ptr(gq), _ptr(xq), B, Cn, HW, _ptr(sums[:Cn]), _ptr(sums[Cn:]), _ptr(ws),
+                                     ws.numel(), _stream()), "qb_rangebn_bwd_reduce")
+    if reduce_hook is not None:
+        reduce_hook(sums)
+    coef = torch.empty(4, Cn, dtype=torch.float32, device=dev)     # dgamma, dbeta, a, e
+    _check(lib.qb_rangebn_bwd_coeffs(_ptr(sums[:Cn]), _ptr(sums[Cn:]), Cn, int(num_chunks), float(count),
+                                     float(chunk_len), int(training), _ptr(vec[0]), _ptr(vec[1]), _ptr(vec[2]),
+                                     _ptr(vec[3]) if has_gamma else None, _ptr(coef[0]), _ptr(coef[1]), _ptr(coef[2]),
+                                     _ptr(coef[3]), _stream()), "qb_rangebn_bwd_coeffs")
+    dx = torch.empty_like(gq)
+    _check(lib.qb_rangebn_bwd_apply(_ptr(gq), _ptr(dx), B, Cn, HW, int(num_chunks) if training else 0, _ptr(vec[2]),
+                                    _ptr(vec[3]) if has_gamma else None, _ptr(coef[2]),
+                                    _ptr(coef[3]) if training else None, _ptr(amax) if training else None,
+                                    _ptr(amin) if training else None, _stream()), "qb_rangebn_bwd_apply")
+    return dx, coef[0], coef[1]

@@ -1,0 +1,187 @@
+// fakequant.cu - elementwise fake-quantization kernels (HBM-bound: 8 B/elem given range, 12 B/elem fused).
+//
+// Replaces the clone + 8 in-place ATen passes of UniformQuantize.forward
+// (models/modules/quantize.py:66-100) by one read + one write with 128-bit coalesced accesses,
+// and UniformQuantizeGrad.backward's two reductions + host syncs + uniform_ + 8 passes (:124-139) by a
+// single cooperative launch (min/max -> grid sync -> quantize with in-register Philox noise).
+#include <cooperative_groups.h>
+
+#include "common.cuh"
+
+namespace cg = cooperative_groups;
+
+constexpr int FQ_THREADS = 256;
+constexpr int FQ_UNROLL = 4;  // independent 128-bit loads in flight per thread
+
+struct RangeArg {
+    const float* dev;  // device {min,max} or nullptr
+    double lo, hi;     // host range when dev == nullptr
+};
+
+__device__ __forceinline__ QParams load_qparams(const RangeArg& r, int bits, int mode) {
+    double lo = r.lo, hi = r.hi;
+    if (r.dev) {
+        lo = (double)__ldg(r.dev);
+        hi = (double)__ldg(r.dev + 1);
+    }
+    return make_qparams(lo, hi, bits, mode);
+}
+
+__device__ __forceinline__ uchar4 pack_codes(float4 q) {
+    return make_uchar4((unsigned char)q.x, (unsigned char)q.y, (unsigned char)q.z, (unsigned char)q.w);
+}
+
+// ------------------------------------------------------------------------------------------------
+// min-anchored affine (A1)
+// ------------------------------------------------------------------------------------------------
+template <bool WRITE_Y, bool WRITE_C>
+__device__ __forceinline__ void affine_quad(const float4 v, float* y, uint8_t* codes, int64_t quad, const QParams& p) {
+    float4 q = make_float4(q_affine_code(v.x, p), q_affine_code(v.y, p), q_affine_code(v.z, p), q_affine_code(v.w, p));
+    if (WRITE_Y)
+        st_stream4(y + 4 * quad, make_float4(q_affine_deq(q.x, p), q_affine_deq(q.y, p), q_affine_deq(q.z, p),
+                                             q_affine_deq(q.w, p)));
+    if (WRITE_C) reinterpret_cast<uchar4*>(codes)[quad] = pack_codes(q);
+}
+
+template <bool WRITE_Y, bool WRITE_C>
+__global__ void __launch_bounds__(FQ_THREADS)
+k_fq_affine_v4(const float* __restrict__ x, float* y, uint8_t* codes, int64_t n, int bits, RangeArg r, int mode) {
+    const QParams p = load_qparams(r, bits, mode);
+    const int64_t nquads = n >> 2;
+    const int64_t stride = (int64_t)gridDim.x * FQ_THREADS;
+    int64_t i = (int64_t)blockIdx.x * FQ_THREADS + threadIdx.x;
+    for (; i + (FQ_UNROLL - 1) * stride < nquads; i += FQ_UNROLL * stride) {
+        float4 v[FQ_UNROLL];
+#pragma unroll
+        for (int u = 0; u < FQ_UNROLL; ++u) v[u] = ld_stream4(x + 4 * (i + u * stride));
+#pragma unroll
+        for (int u = 0; u < FQ_UNROLL; ++u) affine_quad<WRITE_Y, WRITE_C>(v[u], y, codes, i + u * stride, p);
+    }
+    for (; i < nquads; i += stride) affine_quad<WRITE_Y, WRITE_C>(ld_stream4(x + 4 * i), y, codes, i, p);
+    // n % 4 tail
+    if (blockIdx.x == 0 && threadIdx.x < (n & 3)) {
+        int64_t e = (nquads << 2) + threadIdx.x;
+        float q = q_affine_code(x[e], p);
+        if (WRITE_Y) y[e] = q_affine_deq(q, p);
+        if (WRITE_C) codes[e] = (uint8_t)q;
+    }
+}
+
+// scalar path for pointers that are not 16-byte aligned (views into larger tensors)
+__global__ void __launch_bounds__(FQ_THREADS)
+k_fq_affine_scalar(const float* __restrict__ x, float* y, uint8_t* codes, int64_t n, int bits, RangeArg r, int mode) {
+    const QParams p = load_qparams(r, bits, mode);
+    for (int64_t e = (int64_t)blockIdx.x * FQ_THREADS + threadIdx.x; e < n; e += (int64_t)gridDim.x * FQ_THREADS) {
+        float q = q_affine_code(x[e], p);
+        if (y) y[e] = q_affine_deq(q, p);
+        if (codes) codes[e] = (uint8_t)q;
+    }
+}
+
+static int fq_grid(int64_t work_items, int per_sm) {
+    int sms = qb_sm_count();
+    if (sms <= 0) sms = 148;
+    int64_t want = (work_items + FQ_THREADS - 1) / FQ_THREADS;
+    int64_t cap = (int64_t)sms * per_sm;
+    if (want < 1) want = 1;
+    return (int)(want < cap ? want : cap);
+}
+
+static bool aligned(const void* p, size_t a) { return (reinterpret_cast<uintptr_t>(p) & (a - 1)) == 0; }
+
+extern "C" int qb_fakequant_affine(const float* x, float* y, uint8_t* codes, int64_t n, int bits,
+                                   const float* range_dev, double lo, double hi, int scale_mode, void* stream) {
+    QB_CHECK_ARG(n >= 0, "qb_fakequant_affine: n=%lld", (long long)n);
+    if (n == 0) return QB_OK;
+    QB_CHECK_ARG(x && (y || codes), "qb_fakequant_affine: null x or no output");
+    QB_CHECK_ARG(bits >= 1 && bits <= 24, "qb_fakequant_affine: bits=%d outside 1..24", bits);
+    QB_CHECK_ARG(!codes || bits <= 8, "qb_fakequant_affine: uint8 codes need bits<=8 (bits=%d)", bits);
+    QB_CHECK_ARG(scale_mode == QB_SCALE_DOUBLE || scale_mode == QB_SCALE_FLOAT, "qb_fakequant_affine: scale_mode=%d",
+                 scale_mode);
+    RangeArg r{range_dev, lo, hi};
+    cudaStream_t st = qb_stream(stream);
+    const bool vec = aligned(x, 16) && (!y || aligned(y, 16)) && (!codes || aligned(codes, 4));
+    if (vec) {
+        int grid = fq_grid(n >> 2, 8);
+        if (y && codes)
+            k_fq_affine_v4<true, true><<<grid, FQ_THREADS, 0, st>>>(x, y, codes, n, bits, r, scale_mode);
+        else if (y)
+            k_fq_affine_v4<true, false><<<grid, FQ_THREADS, 0, st>>>(x, y, codes, n, bits, r, scale_mode);
+        else
+            k_fq_affine_v4<false, true><<<grid, FQ_THREADS, 0, st>>>(x, y, codes, n, bits, r, scale_mode);
+    } else {
+        k_fq_affine_scalar<<<fq_grid(n, 8), FQ_THREADS, 0, st>>>(x, y, codes, n, bits, r, scale_mode);
+    }
+    QB_LAUNCH_CHECK();
+    return QB_OK;
+}
+
+// ------------------------------------------------------------------------------------------------
+// per-row (per-output-channel) weights: one CTA per row, row staged in registers/shared memory
+// quantize.py:318-323 (row min/max over flatten(1)) + :332-334 (tensor-range quantize)
+// ------------------------------------------------------------------------------------------------
+__device__ __forceinline__ float2 block_minmax(float mn, float mx, float* sm /* 2*32 floats */) {
+    mn = warp_min(mn);
+    mx = warp_max(mx);
+    const int w = threadIdx.x >> 5, l = threadIdx.x & 31, nw = (blockDim.x + 31) >> 5;
+    __syncthreads();  // protect sm reuse
+    if (l == 0) {
+        sm[w] = mn;
+        sm[32 + w] = mx;
+    }
+    __syncthreads();
+    mn = l < nw ? sm[l] : QB_INF;
+    mx = l < nw ? sm[32 + l] : -QB_INF;
+    mn = warp_min(mn);
+    mx = warp_max(mx);
+    return make_float2(mn, mx);
+}
+
+constexpr int ROW_THREADS = 256;
+
+__global__ void __launch_bounds__(ROW_THREADS)
+k_fq_rows(const float* __restrict__ w, float* wq, uint8_t* codes, int64_t cols, int bits, float* row_min,
+          float* row_max, int compute_range) {
+    __shared__ float sm[64];
+    const int64_t row = blockIdx.x;
+    const float* src = w + row * cols;
+    float lo, hi;
+    if (compute_range) {
+        float mn = QB_INF, mx = -QB_INF;
+        for (int64_t j = threadIdx.x; j < cols; j += ROW_THREADS) {
+            float v = src[j];
+            mn = fminf(mn, v);
+            mx = fmaxf(mx, v);
+        }
+        float2 r = block_minmax(mn, mx, sm);
+        lo = r.x;
+        hi = r.y;
+        if (threadIdx.x == 0) {
+            row_min[row] = lo;
+            row_max[row] = hi;
+        }
+    } else {
+        lo = row_min[row];
+        hi = row_max[row];
+    }
+    const QParams p = make_qparams_f(lo, hi, bits);
+    for (int64_t j = threadIdx.x; j < cols; j += ROW_THREADS) {   // second read hits L1/L2 (rows <= 18 KB)
+        float q = q_affine_code(src[j], p);
+        if (wq) wq[row * cols + j] = q_affine_deq(q, p);
+        if (codes) codes[row * cols + j] = (uint8_t)q;
+    }
+}
+
+extern "C" int qb_fakequant_rows(const float* w, float* wq, uint8_t* codes, int64_t rows, int64_t cols, int bits,
+                                 float* row_min, float* row_max, int compute_range, void* stream) {
+    QB_CHECK_ARG(rows >= 0 && cols >= 0, "qb_fakequant_rows: rows=%lld cols=%lld", (long long)rows, (long long)cols);
+    if (rows == 0 || cols == 0) return QB_OK;
+    QB_CHECK_ARG(w && (wq || codes) && row_min && row_max, "qb_fakequant_rows: null pointer");
+    QB_CHECK_ARG(bits >= 1 && bits <= 24, "qb_fakequant_rows: bits=%d outside 1..24", bits);
+    QB_CHECK_ARG(!codes || bits <= 8, "qb_fakequant_rows: uint8 codes need bits<=8");
+    QB_CHECK_ARG(rows <= 2147483647LL, "qb_fakequant_rows: too many rows");
+    k_fq_rows<<<(unsigned)rows, ROW_THREADS, 0, qb_stream(stream)>>>(w, wq, codes, cols, bits, row_min, row_max,
+                                                                    compute_range);
+    QB_LAUNCH_CHECK();
+    return QB_OK;
+}

@@ -1,0 +1,249 @@
+// measure.cu - QuantMeasure statistics in one pass (4 B/elem) and the device-side buffer update.
+//
+// Reference: models/modules/quantize.py:221-246.  There: min over each sample, mean over the batch;
+// the same for max; global mean; global unbiased std - four full reads of the tensor, then
+// float(min), float(max) host syncs.  Here: one read, per-sample extrema combined through order-
+// independent integer atomics, sums in fp64 with a fixed combination order, result left on the device.
+#include "common.cuh"
+
+constexpr int MS_THREADS = 256;
+constexpr int MS_VEC_PER_THREAD = 8;                               // float4 loads per thread per tile
+constexpr int64_t MS_TILE = MS_THREADS * 4 * MS_VEC_PER_THREAD;    // 8192 elements
+constexpr int MS_MAX_BLOCKS = 2048;
+
+// workspace: [uint32 row_max_enc[B]] [uint32 row_min_enc[B]] [double psum[MS_MAX_BLOCKS]] [double psq[...]] [counter]
+// encodings are 0 when empty, so a zero-filled workspace is a valid initial state.
+static size_t ms_off_sum(int64_t B) { return ((size_t)B * 8 + 15) & ~(size_t)15; }
+extern "C" size_t qb_measure_ws_bytes(int64_t B) {
+    if (B < 0) return 0;
+    return ms_off_sum(B) + (size_t)MS_MAX_BLOCKS * 16 + 64;
+}
+
+// monotone float -> uint32 map (larger float => larger uint); never yields 0 for a non-NaN float
+__device__ __forceinline__ unsigned int enc_ord(float f) {
+    unsigned int b = __float_as_uint(f);
+    return (b & 0x80000000u) ? ~b : (b | 0x80000000u);
+}
+__device__ __forceinline__ float dec_ord(unsigned int u) {
+    return __uint_as_float((u & 0x80000000u) ? (u & 0x7fffffffu) : ~u);
+}
+
+__device__ __forceinline__ void acc4(float4 v, float& mn, float& mx, float& s, float& q) {
+    mn = fminf(fminf(mn, fminf(v.x, v.y)), fminf(v.z, v.w));
+    mx = fmaxf(fmaxf(mx, fmaxf(v.x, v.y)), fmaxf(v.z, v.w));
+    s += (v.x + v.y) + (v.z + v.w);
+    q += (v.x * v.x + v.y * v.y) + (v.z * v.z + v.w * v.w);
+}
+
+__global__ void __launch_bounds__(MS_THREADS)
+k_measure_stats(const float* __restrict__ x, int64_t B, int64_t inner, int vec, double* stats, unsigned int* row_max,
+                unsigned int* row_min, double* psum, double* psq, unsigned int* counter) {
+    __shared__ float smn[8], smx[8];
+    __shared__ double sd[2][8];
+    __shared__ bool last;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int64_t tiles_per_row = (inner + MS_TILE - 1) / MS_TILE;
+    const int64_t T = B * tiles_per_row;
+    double dsum = 0.0, dsq = 0.0;
+    for (int64_t t = blockIdx.x; t < T; t += gridDim.x) {
+        const int64_t b = t / tiles_per_row, s = t - b * tiles_per_row;
+        const int64_t off = s * MS_TILE;
+        const int64_t len = (inner - off < MS_TILE) ? inner - off : MS_TILE;
+        const float* src = x + b * inner + off;
+        float mn = QB_INF, mx = -QB_INF, fs = 0.f, fq = 0.f;
+        if (vec) {
+            const int64_t nq = len >> 2;
+            float4 v[MS_VEC_PER_THREAD];
+#pragma unroll
+            for (int u = 0; u < MS_VEC_PER_THREAD; ++u) {
+                int64_t qi = threadIdx.x + (int64_t)u * MS_THREADS;
+                if (qi < nq) v[u] = __ldcs(reinterpret_cast<const float4*>(src) + qi);
+            }
+#pragma unroll
+            for (int u = 0; u < MS_VEC_PER_THREAD; ++u) {
+                int64_t qi = threadIdx.x + (int64_t)u * MS_THREADS;
+                if (qi < nq) acc4(v[u], mn, mx, fs, fq);
+            }
+            if ((int64_t)threadIdx.x < (len & 3)) {     // only the last tile of a row can have a tail (inner%4==0 => none)
+                float e = src[(nq << 2) + threadIdx.x];
+                mn = fminf(mn, e); mx = fmaxf(mx, e); fs += e; fq += e * e;
+            }
+        } else {
+            for (int64_t j = threadIdx.x; j < len; j += MS_THREADS) {
+                float e = src[j];
+                mn = fminf(mn, e); mx = fmaxf(mx, e); fs += e; fq += e * e;
+            }
+        }
+        dsum += (double)fs;
+        dsq += (double)fq;
+        mn = warp_min(mn);
+        mx = warp_max(mx);
+        __syncthreads();
+        if (lane == 0) { smn[warp] = mn; smx[warp] = mx; }
+        __syncthreads();
+        if (threadIdx.x == 0) {
+#pragma unroll
+            for (int w = 1; w < MS_THREADS / 32; ++w) { mn = fminf(mn, smn[w]); mx = fmaxf(mx, smx[w]); }
+            atomicMax(&row_max[b], enc_ord(mx));
+            atomicMax(&row_min[b], ~enc_ord(mn));    // max of complemented code == min
+        }
+    }
+    // per-CTA partial sums, fixed slot per CTA
+    dsum = warp_sum(dsum);
+    dsq = warp_sum(dsq);
+    if (lane == 0) { sd[0][warp] = dsum; sd[1][warp] = dsq; }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        double a = 0.0, c = 0.0;
+        for (int w = 0; w < MS_THREADS / 32; ++w) { a += sd[0][w]; c += sd[1][w]; }
+        psum[blockIdx.x] = a;
+        psq[blockIdx.x] = c;
+        __threadfence();
+        last = (atomicAdd(counter, 1u) == gridDim.x - 1);
+    }
+    __syncthreads();
+    if (!last) return;
+    __threadfence();
+    // ---- last CTA: combine in a fixed order, clean the workspace ----
+    double smin = 0.0, smax = 0.0, tsum = 0.0, tsq = 0.0;
+    float gmn = QB_INF, gmx = -QB_INF;
+    for (int64_t b = threadIdx.x; b < B; b += MS_THREADS) {
+        float rmx = dec_ord(__ldcg(&row_max[b]));
+        float rmn = dec_ord(~__ldcg(&row_min[b]));
+        row_max[b] = 0u;
+        row_min[b] = 0u;
+        smax += (double)rmx;
+        smin += (double)rmn;
+        gmn = fminf(gmn, rmn);
+        gmx = fmaxf(gmx, rmx);
+    }
+    for (int i = threadIdx.x; i < (int)gridDim.x; i += MS_THREADS) {
+        tsum += __ldcg(&psum[i]);
+        tsq += __ldcg(&psq[i]);
+    }
+    smin = warp_sum(smin); smax = warp_sum(smax); tsum = warp_sum(tsum); tsq = warp_sum(tsq);
+    gmn = warp_min(gmn); gmx = warp_max(gmx);
+    __shared__ double fin[4][8];
+    __shared__ float fmm[2][8];
+    if (lane == 0) {
+        fin[0][warp] = smin; fin[1][warp] = smax; fin[2][warp] = tsum; fin[3][warp] = tsq;
+        fmm[0][warp] = gmn; fmm[1][warp] = gmx;
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        double r[4] = {0, 0, 0, 0};
+        for (int w = 0; w < MS_THREADS / 32; ++w) {
+            for (int k = 0; k < 4; ++k) r[k] += fin[k][w];
+            gmn = fminf(gmn, fmm[0][w]);
+            gmx = fmaxf(gmx, fmm[1][w]);
+        }
+        stats[0] = r[0]; stats[1] = r[1]; stats[2] = r[2]; stats[3] = r[3];
+        stats[4] = (double)gmn; stats[5] = (double)gmx;
+        stats[6] = (double)B * (double)inner; stats[7] = (double)B;
+        *counter = 0u;
+    }
+}
+
+extern "C" int qb_measure_stats(const float* x, int64_t B, int64_t inner, double* stats, void* ws, size_t ws_bytes,
+                                void* stream) {
+    QB_CHECK_ARG(x && stats && ws, "qb_measure_stats: null pointer");
+    QB_CHECK_ARG(B > 0 && inner > 0, "qb_measure_stats: B=%lld inner=%lld (empty input has no range)", (long long)B,
+                 (long long)inner);
+    if (ws_bytes < qb_measure_ws_bytes(B)) {
+        qb_set_error("qb_measure_stats: workspace %zu < %zu bytes", ws_bytes, qb_measure_ws_bytes(B));
+        return QB_ERR_WORKSPACE;
+    }
+    char* base = static_cast<char*>(ws);
+    unsigned int* row_max = reinterpret_cast<unsigned int*>(base);
+    unsigned int* row_min = row_max + B;
+    double* psum = reinterpret_cast<double*>(base + ms_off_sum(B));
+    double* psq = psum + MS_MAX_BLOCKS;
+    unsigned int* counter = reinterpret_cast<unsigned int*>(psq + MS_MAX_BLOCKS);
+    const int vec = ((reinterpret_cast<uintptr_t>(x) & 15) == 0) && (inner % 4 == 0);
+    const int64_t T = B * ((inner + MS_TILE - 1) / MS_TILE);
+    int sms = qb_sm_count();
+    if (sms <= 0) sms = 148;
+    int64_t cap = (int64_t)sms * 8;
+    if (cap > MS_MAX_BLOCKS) cap = MS_MAX_BLOCKS;
+    int grid = (int)(T < cap ? T : cap);
+    k_measure_stats<<<grid, MS_THREADS, 0, qb_stream(stream)>>>(x, B, inner, vec, stats, row_max, row_min, psum, psq,
+                                                                counter);
+    QB_LAUNCH_CHECK();
+    return QB_OK;
+}
+
+// ---------------------------------------------------------------------------------------------------
+// QuantMeasure buffer update + range selection (quantize.py:216-219, 228-246, 256-268), one thread.
+// ---------------------------------------------------------------------------------------------------
+__device__ __forceinline__ void blend(float* running, float value, bool cumulative, float m_cum, float m_f, float om_f) {
+    // running.mul_(momentum).add_(new_value * (1 - momentum))
+    if (cumulative) {
+        float om = __fsub_rn(1.0f, m_cum);
+        *running = __fadd_rn(__fmul_rn(*running, m_cum), __fmul_rn(value, om));
+    } else {
+        *running = __fadd_rn(__fmul_rn(*running, m_f), __fmul_rn(value, om_f));
+    }
+}
+
+__device__ __forceinline__ void aciq_range(float& std_ref, float mean, float tmin, float tmax, float alpha, float& lo,
+                                           float& hi) {
+    std_ref = __fadd_rn(std_ref, 1e-8f);                      // std += 1e-8 (in place in the reference)
+    float clip = __fmul_rn(std_ref, alpha);
+    float half_range = __fdiv_rn(__fsub_rn(tmax, tmin), 2.0f);
+    clip = half_range < clip ? half_range : clip;            // Python min(max_range/2, clip_val)
+    float a = __fsub_rn(mean, clip), b = __fadd_rn(mean, clip);
+    lo = a > tmin ? a : tmin;                                // Python max(tmin, mean-clip): first arg wins ties
+    hi = b < tmax ? b : tmax;
+}
+
+__global__ void k_measure_finalize(const double* stats, float* rmin, float* rmax, float* nmeas, float* rvar, float* rmean,
+                                   double momentum, int training, int method, float alpha, float* range_out) {
+    if (threadIdx.x != 0 || blockIdx.x != 0) return;
+    float lo, hi;
+    if (training) {
+        const double B = stats[7], n = stats[6];
+        lo = (float)(stats[0] / B);
+        hi = (float)(stats[1] / B);
+        const double mean_d = stats[2] / n;
+        double var_d = (stats[3] - stats[2] * mean_d) / (n - 1.0);       // unbiased; n==1 -> nan like torch
+        if (var_d < 0.0) var_d = 0.0;
+        const float mean = (float)mean_d;
+        float stdv = (float)sqrt(var_d);
+        const bool cumulative = momentum < 0.0;
+        const float cnt = *nmeas;
+        const float m_cum = __fdiv_rn(cnt, __fadd_rn(cnt, 1.0f));
+        const float m_f = (float)momentum, om_f = (float)(1.0 - momentum);
+        blend(rmin, lo, cumulative, m_cum, m_f, om_f);
+        blend(rmax, hi, cumulative, m_cum, m_f, om_f);
+        blend(rmean, mean, cumulative, m_cum, m_f, om_f);
+        blend(rvar, stdv, cumulative, m_cum, m_f, om_f);
+        *nmeas = __fadd_rn(cnt, 1.0f);
+        if (method == 1) aciq_range(stdv, mean, lo, hi, alpha, lo, hi);
+    } else if (method == 1) {
+        aciq_range(*rvar, *rmean, *rmin, *rmax, alpha, lo, hi);          // NB: mutates running_var like the reference
+    } else {
+        lo = *rmin;
+        hi = *rmax;
+    }
+    range_out[0] = lo;
+    range_out[1] = hi;
+}
+
+extern "C" int qb_measure_finalize(const double* stats, float* running_min, float* running_max, float* num_measurements,
+                                   float* running_var, float* running_mean, double momentum, int training, int method,
+                                   int bits, float* range_out, void* stream) {
+    QB_CHECK_ARG(running_min && running_max && num_measurements && running_var && running_mean && range_out,
+                 "qb_measure_finalize: null pointer");
+    QB_CHECK_ARG(!training || stats, "qb_measure_finalize: training needs stats");
+    QB_CHECK_ARG(method == 0 || method == 1, "qb_measure_finalize: method=%d", method);
+    static const float alpha_tab[9] = {0.f, 0.f, 2.83f, 3.89f, 5.03f, 6.2f, 7.41f, 8.64f, 9.89f};   // quantize.py:214
+    float alpha = 0.f;
+    if (method == 1) {
+        QB_CHECK_ARG(bits >= 2 && bits <= 8, "qb_measure_finalize: aciq not supported for %d bits", bits);
+        alpha = alpha_tab[bits];
+    }
+    k_measure_finalize<<<1, 32, 0, qb_stream(stream)>>>(stats, running_min, running_max, num_measurements, running_var,
+                                                        running_mean, momentum, training, method, alpha, range_out);
+    QB_LAUNCH_CHECK();
+    return QB_OK;
+}
