@@ -74,6 +74,44 @@ def _check(rc, what):
         raise QB200Error("%s failed (%d): %s" % (what, rc, last_error()))
 
 
+LAUNCHES = 0          # kernels launched through the C ABI by this process (bench.py reports it)
+_profile = None       # list of (name, algorithmic_bytes, start_event, end_event) while profiling
+
+# kernels enqueued per C call
+_NLAUNCH = {"qb_rangebn_stats": 2, "qb_rangebn_bwd_reduce": 2, "qb_rangebn_bwd_apply": 2}
+
+
+def _run(name, nbytes, *args):
+    """Call one C-ABI entry point; count its launches; under profile_begin() bracket it with CUDA events on the
+    launching stream."""
+    global LAUNCHES
+    fn = getattr(load(), name)
+    LAUNCHES += _NLAUNCH.get(name, 1)
+    if _profile is None:
+        rc = fn(*args)
+    else:
+        a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a.record()
+        rc = fn(*args)
+        b.record()
+        _profile.append((name, nbytes, a, b))
+    if rc != 0:
+        raise QB200Error("%s failed (%d): %s" % (name, rc, last_error()))
+
+
+def profile_begin():
+    global _profile
+    _profile = []
+
+
+def profile_end():
+    """-> [(name, algorithmic_bytes, ms)] for every call since profile_begin()."""
+    global _profile
+    recs, _profile = _profile or [], None
+    torch.cuda.synchronize()
+    return [(n, nb, a.elapsed_time(b)) for n, nb, a, b in recs]
+
+
 def device_info(device=0):
     sm, maj, mnr, l2 = _i32(), _i32(), _i32(), _sz()
     _check(load().qb_device_info(device, C.byref(sm), C.byref(maj), C.byref(mnr), C.byref(l2)), "qb_device_info")
@@ -122,7 +160,7 @@ def measure_stats(x, stats=None):
         stats = torch.empty(8, dtype=torch.float64, device=x.device)
     nb = lib.qb_measure_ws_bytes(B)
     ws = workspace("measure", nb, x.device)
-    _check(lib.qb_measure_stats(_ptr(x), B, inner, _ptr(stats), _ptr(ws), ws.numel(), _stream()), "qb_measure_stats")
+    _run("qb_measure_stats", 4 * x.numel(), _ptr(x), B, inner, _ptr(stats), _ptr(ws), ws.numel(), _stream())
     return stats
 
 
@@ -132,9 +170,9 @@ def measure_finalize(stats, running, momentum, training, method, bits, range_out
     rmin, rmax, nmeas, rvar, rmean = running
     if range_out is None:
         range_out = torch.empty(2, dtype=torch.float32, device=rmin.device)
-    _check(lib.qb_measure_finalize(_ptr(stats), _ptr(rmin), _ptr(rmax), _ptr(nmeas), _ptr(rvar), _ptr(rmean),
+    _run("qb_measure_finalize", 0, _ptr(stats), _ptr(rmin), _ptr(rmax), _ptr(nmeas), _ptr(rvar), _ptr(rmean),
                                    -1.0 if momentum is None else float(momentum), int(training), int(method), int(bits),
-                                   _ptr(range_out), _stream()), "qb_measure_finalize")
+                                   _ptr(range_out), _stream())
     return range_out
 
 
@@ -144,9 +182,8 @@ def fakequant_affine(x, bits, range_dev=None, lo=0.0, hi=0.0, scale_mode=QB_SCAL
     x = _f32c(x, "x")
     if want_y and out is None:
         out = torch.empty_like(x)
-    _check(lib.qb_fakequant_affine(_ptr(x), _ptr(out) if want_y else None, _ptr(codes), x.numel(), int(bits),
-                                   _ptr(range_dev), float(lo), float(hi), int(scale_mode), _stream()),
-           "qb_fakequant_affine")
+    _run("qb_fakequant_affine", (4 + (4 if want_y else 0) + (1 if codes is not None else 0)) * x.numel(), _ptr(x), _ptr(out) if want_y else None, _ptr(codes), x.numel(), int(bits),
+                                   _ptr(range_dev), float(lo), float(hi), int(scale_mode), _stream())
     return out
 
 
@@ -160,8 +197,8 @@ def fakequant_rows(w, bits, row_min=None, row_max=None, compute_range=True, out=
         row_max = torch.empty(rows, dtype=torch.float32, device=w.device)
     if want_y and out is None:
         out = torch.empty_like(w)
-    _check(lib.qb_fakequant_rows(_ptr(w), _ptr(out) if want_y else None, _ptr(codes), rows, cols, int(bits),
-                                 _ptr(row_min), _ptr(row_max), int(compute_range), _stream()), "qb_fakequant_rows")
+    _run("qb_fakequant_rows", (4 + (4 if want_y else 0) + (1 if codes is not None else 0)) * w.numel(), _ptr(w), _ptr(out) if want_y else None, _ptr(codes), rows, cols, int(bits),
+                                 _ptr(row_min), _ptr(row_max), int(compute_range), _stream())
     return out, row_min, row_max
 
 
@@ -171,7 +208,7 @@ def minmax(x, range_out=None):
     if range_out is None:
         range_out = torch.empty(2, dtype=torch.float32, device=x.device)
     ws = workspace("minmax", lib.qb_minmax_ws_bytes(), x.device)
-    _check(lib.qb_minmax(_ptr(x), x.numel(), _ptr(range_out), _ptr(ws), ws.numel(), _stream()), "qb_minmax")
+    _run("qb_minmax", 4 * x.numel(), _ptr(x), x.numel(), _ptr(range_out), _ptr(ws), ws.numel(), _stream())
     return range_out
 
 
@@ -185,9 +222,9 @@ def fakequant_grad(g, bits, range_dev=None, lo=0.0, hi=0.0, noise=None, stochast
             raise QB200Error("noise has %d elements, gradient %d" % (noise.numel(), g.numel()))
     if want_y and out is None:
         out = torch.empty_like(g)
-    _check(lib.qb_fakequant_grad(_ptr(g), _ptr(out) if want_y else None, _ptr(codes), g.numel(), int(bits),
+    _run("qb_fakequant_grad", (4 + (4 if want_y else 0) + (1 if codes is not None else 0) + (4 if noise is not None else 0)) * g.numel(), _ptr(g), _ptr(out) if want_y else None, _ptr(codes), g.numel(), int(bits),
                                  _ptr(range_dev), float(lo), float(hi), _ptr(noise), int(stochastic),
-                                 int(seed) & (2 ** 64 - 1), int(offset), _ptr(step_dev), _stream()), "qb_fakequant_grad")
+                                 int(seed) & (2 ** 64 - 1), int(offset), _ptr(step_dev), _stream())
     return out
 
 
@@ -205,10 +242,9 @@ def fakequant_grad_fused(g, bits, noise=None, stochastic=True, seed=0, offset=0,
     if range_out is None:
         range_out = torch.empty(2, dtype=torch.float32, device=g.device)
     ws = workspace("minmax", lib.qb_minmax_ws_bytes(), g.device)
-    _check(lib.qb_fakequant_grad_fused(_ptr(g), _ptr(out) if want_y else None, _ptr(codes), g.numel(), int(bits),
+    _run("qb_fakequant_grad_fused", (8 + (4 if want_y else 0) + (1 if codes is not None else 0) + (4 if noise is not None else 0)) * g.numel(), _ptr(g), _ptr(out) if want_y else None, _ptr(codes), g.numel(), int(bits),
                                        _ptr(range_out), _ptr(noise), int(stochastic), int(seed) & (2 ** 64 - 1),
-                                       int(offset), _ptr(step_dev), _ptr(ws), ws.numel(), _stream()),
-           "qb_fakequant_grad_fused")
+                                       int(offset), _ptr(step_dev), _ptr(ws), ws.numel(), _stream())
     return out, range_out
 
 
@@ -223,8 +259,8 @@ def rangebn_stats(x, B, Cn, HW, num_chunks, want_arg=True):
     amax = torch.empty(Cn * num_chunks, dtype=torch.int32, device=dev) if want_arg else None
     amin = torch.empty(Cn * num_chunks, dtype=torch.int32, device=dev) if want_arg else None
     ws = workspace("rangebn", lib.qb_rangebn_ws_bytes(Cn, num_chunks), dev)
-    _check(lib.qb_rangebn_stats(_ptr(x), B, Cn, HW, num_chunks, _ptr(amax), _ptr(amin), _ptr(red), _ptr(ws), ws.numel(),
-                                _stream()), "qb_rangebn_stats")
+    _run("qb_rangebn_stats", 4 * B * Cn * HW, _ptr(x), B, Cn, HW, num_chunks, _ptr(amax), _ptr(amin), _ptr(red), _ptr(ws), ws.numel(),
+                                _stream())
     return red, amax, amin
 
 
@@ -233,11 +269,11 @@ def rangebn_finalize(red, Cn, num_chunks, count, chunk_len, eps, momentum, train
     """Returns vec float[5, C]: rows mean, scale_raw, qscale, qgamma, qbeta."""
     lib = load()
     vec = torch.empty(5, Cn, dtype=torch.float32, device=running_mean.device)
-    _check(lib.qb_rangebn_finalize(_ptr(red), Cn, int(num_chunks), float(count), float(chunk_len), float(eps),
+    _run("qb_rangebn_finalize", 0, _ptr(red), Cn, int(num_chunks), float(count), float(chunk_len), float(eps),
                                    float(momentum), int(training), int(bits), _ptr(gamma), _ptr(beta),
                                    _ptr(running_mean), _ptr(running_var), _ptr(vec[0]), _ptr(vec[1]), _ptr(vec[2]),
                                    _ptr(vec[3]) if gamma is not None else None,
-                                   _ptr(vec[4]) if beta is not None else None, _stream()), "qb_rangebn_finalize")
+                                   _ptr(vec[4]) if beta is not None else None, _stream())
     return vec
 
 
@@ -245,32 +281,34 @@ def rangebn_apply(x, B, Cn, HW, vec, has_gamma, has_beta, out=None):
     lib = load()
     if out is None:
         out = torch.empty_like(x)
-    _check(lib.qb_rangebn_apply(_ptr(x), _ptr(out), B, Cn, HW, _ptr(vec[0]), _ptr(vec[2]),
-                                _ptr(vec[3]) if has_gamma else None, _ptr(vec[4]) if has_beta else None, _stream()),
-           "qb_rangebn_apply")
+    _run("qb_rangebn_apply", 8 * B * Cn * HW, _ptr(x), _ptr(out), B, Cn, HW, _ptr(vec[0]), _ptr(vec[2]),
+                                _ptr(vec[3]) if has_gamma else None, _ptr(vec[4]) if has_beta else None, _stream())
     return out
 
 
 def rangebn_backward(gq, xq, B, Cn, HW, num_chunks, count, chunk_len, training, vec, has_gamma, amax, amin,
-                     reduce_hook=None):
+                     reduce_hook=None, chunks_global=None):
     """Returns (dx, dgamma, dbeta).  ``reduce_hook(sums)`` may all-reduce the double[2*C] sums in place
-    (batch-sharded training)."""
+    (batch-sharded training); ``num_chunks`` is this rank's chunk count (layout of amax/amin),
+    ``chunks_global`` the count the chunk-mean was taken over."""
     lib = load()
     dev = gq.device
+    if chunks_global is None:
+        chunks_global = num_chunks
     sums = torch.empty(2 * Cn, dtype=torch.float64, device=dev)
     ws = workspace("rangebn_bwd", lib.qb_rangebn_bwd_ws_bytes(Cn), dev)
-    _check(lib.qb_rangebn_bwd_reduce(_ptr(gq), _ptr(xq), B, Cn, HW, _ptr(sums[:Cn]), _ptr(sums[Cn:]), _ptr(ws),
-                                     ws.numel(), _stream()), "qb_rangebn_bwd_reduce")
+    _run("qb_rangebn_bwd_reduce", 8 * B * Cn * HW, _ptr(gq), _ptr(xq), B, Cn, HW, _ptr(sums[:Cn]), _ptr(sums[Cn:]), _ptr(ws),
+                                     ws.numel(), _stream())
     if reduce_hook is not None:
         reduce_hook(sums)
     coef = torch.empty(4, Cn, dtype=torch.float32, device=dev)     # dgamma, dbeta, a, e
-    _check(lib.qb_rangebn_bwd_coeffs(_ptr(sums[:Cn]), _ptr(sums[Cn:]), Cn, int(num_chunks), float(count),
+    _run("qb_rangebn_bwd_coeffs", 0, _ptr(sums[:Cn]), _ptr(sums[Cn:]), Cn, int(chunks_global), float(count),
                                      float(chunk_len), int(training), _ptr(vec[0]), _ptr(vec[1]), _ptr(vec[2]),
                                      _ptr(vec[3]) if has_gamma else None, _ptr(coef[0]), _ptr(coef[1]), _ptr(coef[2]),
-                                     _ptr(coef[3]), _stream()), "qb_rangebn_bwd_coeffs")
+                                     _ptr(coef[3]), _stream())
     dx = torch.empty_like(gq)
-    _check(lib.qb_rangebn_bwd_apply(_ptr(gq), _ptr(dx), B, Cn, HW, int(num_chunks) if training else 0, _ptr(vec[2]),
+    _run("qb_rangebn_bwd_apply", 8 * B * Cn * HW, _ptr(gq), _ptr(dx), B, Cn, HW, int(num_chunks) if training else 0, _ptr(vec[2]),
                                     _ptr(vec[3]) if has_gamma else None, _ptr(coef[2]),
                                     _ptr(coef[3]) if training else None, _ptr(amax) if training else None,
-                                    _ptr(amin) if training else None, _stream()), "qb_rangebn_bwd_apply")
+                                    _ptr(amin) if training else None, _stream())
     return dx, coef[0], coef[1]

@@ -1,0 +1,667 @@
+"""Drop-in mirror of the reference's ``models/modules/quantize.py`` hot path on B200 kernels.
+
+Same names, constructor arguments, buffers / state-dict keys and (effective) semantics as the reference
+(file:line citations are relative to /root/reference/models/modules/quantize.py), but every tensor
+pass runs in a hand-written sm_100a kernel behind the C ABI (include/qb200.h) and NO value is synced to
+the host on the step path: ranges live in device memory (the reference calls ``float(tensor)`` 242 times
+per ResNet-18 step), so a whole training step can be captured in a CUDA graph.
+
+Differences that are deliberate and documented in DESIGN.md:
+  * the batch-mean of per-sample minima / maxima and the RangeBN chunk means are accumulated in fp64 and
+    rounded once (ATen sums in fp32 in an unspecified order): ranges agree to <= 1 ulp, and given the same
+    range the integer codes are bit-identical;
+  * stochastic-rounding noise comes from Philox4x32-10 inside the kernel (torch's CPU mt19937 stream cannot
+    be reproduced on a GPU); ``set_noise_provider`` injects a recorded noise tensor for parity tests.
+"""
+import itertools
+import math
+
+import torch
+import torch.nn as nn
+import torch.nn.functional as F
+from torch.autograd.function import Function, InplaceFunction
+
+from . import _abi
+from ._abi import QB200Error, QB_SCALE_DOUBLE, QB_SCALE_FLOAT
+
+__all__ = ["UniformQuantize", "UniformQuantizeGrad", "quantize", "quantize_grad", "conv2d_biprec", "linear_biprec",
+           "QuantNode", "QuantMeasure", "QConv2d", "QLinear", "RangeBN", "set_measure_mode", "set_quant_mode",
+           "overwrite_params", "freeze_quant_params", "set_bn_is_train", "set_global_quantization_method",
+           "distill_set_train", "is_bn", "is_quant", "recursive_apply", "set_noise_provider", "manual_seed",
+           "noise_step", "set_stat_reducer"]
+
+# ---------------------------------------------------------------------------------------------------
+# noise source of the stochastic branch + cross-rank statistic hooks
+# ---------------------------------------------------------------------------------------------------
+_noise_provider = None
+_seed_base = 0x5DEECE66D
+_seed_counter = itertools.count(1)
+_step_tensors = {}
+_reducer = None
+
+
+def set_noise_provider(fn):
+    """fn(shape) -> CUDA float32 tensor of uniform(-0.5,0.5) noise (or None for Philox).  Parity tests replay
+    the noise the reference drew (quantize.py:93).  Returns the previous provider."""
+    global _noise_provider
+    prev, _noise_provider = _noise_provider, fn
+    return prev
+
+
+def manual_seed(seed):
+    """Re-key the in-kernel Philox stream (the call counter restarts too)."""
+    global _seed_base, _seed_counter
+    _seed_base = int(seed) & (2 ** 63 - 1)
+    _seed_counter = itertools.count(1)
+
+
+def noise_step(device=None):
+    """Device-resident step counter mixed into every Philox key.  ``noise_step().add_(1)`` inside a captured
+    CUDA graph makes each replay draw fresh noise (host-side seeds are frozen at capture)."""
+    device = torch.device("cuda", torch.cuda.current_device()) if device is None else torch.device(device)
+    t = _step_tensors.get(device)
+    if t is None:
+        t = _step_tensors[device] = torch.zeros(1, dtype=torch.int64, device=device)
+    return t
+
+
+def _next_seed():
+    return (_seed_base + next(_seed_counter) * 0x9E3779B97F4A7C15) & (2 ** 64 - 1)
+
+
+def set_stat_reducer(reducer):
+    """Install the cross-rank statistic reducer used by batch-sharded training (see ``dist.py``): an object with
+    ``measure(stats)``, ``rangebn(red)``, ``rangebn_bwd(sums)`` and ``grad_range(range)`` that all-reduce IN PLACE.
+    ``None`` restores single-process behaviour."""
+    global _reducer
+    prev, _reducer = _reducer, reducer
+    return prev
+
+
+def _quantize_gradient(g, bits, stochastic=True):
+    """UniformQuantizeGrad.backward (quantize.py:124-139): global min/max, zero-point stochastic quantizer."""
+    g = g.contiguous()
+    noise = _noise_provider(tuple(g.shape)) if (stochastic and _noise_provider is not None) else None
+    if _reducer is None:
+        out, _ = _abi.fakequant_grad_fused(g, bits, noise=noise, stochastic=stochastic, seed=_next_seed(),
+                                           step_dev=noise_step(g.device))
+        return out
+    r = _abi.minmax(g)
+    _reducer.grad_range(r)
+    return _abi.fakequant_grad(g, bits, range_dev=r, noise=noise, stochastic=stochastic, seed=_next_seed(),
+                               step_dev=noise_step(g.device))
+
+
+# ---------------------------------------------------------------------------------------------------
+# UniformQuantize / UniformQuantizeGrad / quantize / quantize_grad         (quantize.py:39-164)
+# ---------------------------------------------------------------------------------------------------
+def _is_scalar_like(v):
+    return (not torch.is_tensor(v)) or v.numel() == 1
+
+
+class UniformQuantize(InplaceFunction):
+    """quantize.py:39-109.  Same positional signature as the reference's forward."""
+
+    @classmethod
+    def forward(cls, ctx, input, num_bits=8, min_value=None, max_value=None, stochastic=False, inplace=False,
+                enforce_true_zero=True, num_chunks=None, out_half=False):
+        num_chunks = input.shape[0] if num_chunks is None else num_chunks
+        if (min_value is None or max_value is None) and max(input.shape[0] // num_chunks, 1) != 1:
+            raise QB200Error("UniformQuantize: per-group data ranges (B // num_chunks > 1) do not broadcast in the "
+                             "reference either; unsupported")
+        ctx.inplace, ctx.num_bits, ctx.stochastic = inplace, num_bits, stochastic
+        ctx.min_value, ctx.max_value = min_value, max_value
+        x = input.contiguous()
+        if inplace:
+            ctx.mark_dirty(input)
+        out = input if (inplace and x is input) else None
+        dev_range, lo, hi, mode = None, 0.0, 0.0, QB_SCALE_DOUBLE
+        per_row = False
+        if min_value is None or max_value is None:
+            dev_range = _abi.minmax(x)                       # :45-55 -> 1-element tensors => tensor-scale branch
+            mode = QB_SCALE_FLOAT
+            if min_value is not None or max_value is not None:
+                given_lo = dev_range[0] if min_value is None else torch.as_tensor(min_value, device=x.device).reshape(())
+                given_hi = dev_range[1] if max_value is None else torch.as_tensor(max_value, device=x.device).reshape(())
+                dev_range = torch.stack([given_lo, given_hi]).float()
+        elif torch.is_tensor(min_value) or torch.is_tensor(max_value):
+            mode = QB_SCALE_FLOAT
+            if _is_scalar_like(min_value) and _is_scalar_like(max_value):
+                dev_range = torch.stack([torch.as_tensor(min_value, device=x.device).reshape(()).float(),
+                                         torch.as_tensor(max_value, device=x.device).reshape(()).float()])
+            else:
+                rows = x.shape[0]
+                if not (torch.is_tensor(min_value) and torch.is_tensor(max_value) and min_value.numel() == rows
+                        and max_value.numel() == rows and min_value.shape[0] == rows):
+                    raise QB200Error("UniformQuantize: tensor ranges must be scalar or one value per row of dim 0")
+                per_row = True
+        else:
+            lo, hi = float(min_value), float(max_value)
+        if enforce_true_zero:
+            if per_row:
+                raise QB200Error("UniformQuantize: enforce_true_zero needs a scalar range (as in the reference)")
+            noise = _noise_provider(tuple(x.shape)) if (stochastic and _noise_provider is not None) else None
+            y = _abi.fakequant_grad(x, num_bits, range_dev=dev_range, lo=lo, hi=hi, noise=noise,
+                                    stochastic=bool(stochastic), seed=_next_seed(), step_dev=noise_step(x.device), out=out)
+        else:
+            if stochastic:
+                raise QB200Error("UniformQuantize: stochastic rounding on the min-anchored branch is not implemented "
+                                 "(no call site of the reference reaches it)")
+            if per_row:
+                y, _, _ = _abi.fakequant_rows(x, num_bits, row_min=min_value.detach().reshape(-1).contiguous().float(),
+                                              row_max=max_value.detach().reshape(-1).contiguous().float(),
+                                              compute_range=False, out=out)
+            else:
+                y = _abi.fakequant_affine(x, num_bits, range_dev=dev_range, lo=lo, hi=hi, scale_mode=mode, out=out)
+        if inplace and y is not input:
+            input.copy_(y)
+            y = input
+        if out_half and num_bits <= 16:
+            y = y.half()
+        return y
+
+    @staticmethod
+    def backward(ctx, grad_output):
+        # straight-through estimator; one None per remaining forward argument actually passed
+        return (grad_output,) + (None,) * 8
+
+
+class UniformQuantizeGrad(InplaceFunction):
+    """quantize.py:112-139: identity forward, quantized gradient backward."""
+
+    @classmethod
+    def forward(cls, ctx, input, num_bits=8, min_value=None, max_value=None, stochastic=True, inplace=False):
+        ctx.inplace, ctx.num_bits, ctx.stochastic = inplace, num_bits, stochastic
+        ctx.min_value, ctx.max_value = min_value, max_value
+        # the reference returns `input` itself (:121), which current torch rejects once a consumer modifies it
+        # in place; a fresh tensor is the numerically neutral equivalent
+        return input.clone()
+
+    @staticmethod
+    def backward(ctx, grad_output):
+        if ctx.min_value is None and ctx.max_value is None:
+            grad_input = _quantize_gradient(grad_output, ctx.num_bits, ctx.stochastic)
+        else:
+            g = grad_output.contiguous()
+            r = _abi.minmax(g) if (ctx.min_value is None or ctx.max_value is None) else None
+            lo = r[0] if ctx.min_value is None else torch.as_tensor(float(ctx.min_value), device=g.device)
+            hi = r[1] if ctx.max_value is None else torch.as_tensor(float(ctx.max_value), device=g.device)
+            rng = torch.stack([lo.reshape(()), hi.reshape(())]).float()
+            noise = _noise_provider(tuple(g.shape)) if (ctx.stochastic and _noise_provider is not None) else None
+            grad_input = _abi.fakequant_grad(g, ctx.num_bits, range_dev=rng, noise=noise, stochastic=bool(ctx.stochastic),
+                                             seed=_next_seed(), step_dev=noise_step(g.device))
+        return grad_input, None, None, None, None, None
+
+
+def quantize(x, num_bits=8, min_value=None, max_value=None, num_chunks=None, stochastic=False, inplace=False):
+    """quantize.py:159-160 INCLUDING its positional shuffle: the reference passes
+    (x, num_bits, min, max, num_chunks, stochastic, inplace) into forward's
+    (input, num_bits, min, max, stochastic, inplace, enforce_true_zero, ...) slots, i.e. effectively
+    stochastic := num_chunks, inplace := stochastic, enforce_true_zero := inplace (False by default)."""
+    return UniformQuantize().apply(x, num_bits, min_value, max_value, num_chunks, stochastic, inplace)
+
+
+def quantize_grad(x, num_bits=8, min_value=None, max_value=None, stochastic=True, inplace=False):
+    """quantize.py:163-164."""
+    return UniformQuantizeGrad().apply(x, num_bits, min_value, max_value, stochastic, inplace)
+
+
+# ---------------------------------------------------------------------------------------------------
+# contraction with the bi-precision backward                                  (quantize.py:142-156)
+# ---------------------------------------------------------------------------------------------------
+def _pair(v):
+    return tuple(v) if isinstance(v, (tuple, list)) else (v, v)
+
+
+class _QContraction(Function):
+    """out = conv2d / linear of already fake-quantized operands.
+
+    backward, per the reference:
+      grad_mode 'full'   (num_bits_grad None)                : dX, dW, db from g
+      grad_mode 'biprec' (conv2d_biprec / linear_biprec)     : dW, db from g;  dX from Q(g)    (:143-148)
+      grad_mode 'quant'  (quantize_grad after the op, :342-346): dX, dW, db all from Q(g)
+    The reference evaluates the convolution twice in biprec mode (out1 + out2 - out1.detach(), identical
+    values); here it is evaluated once and only the backward differs.
+    """
+
+    @staticmethod
+    def forward(ctx, x, w, b, conv, bits_grad, grad_mode):
+        ctx.conv, ctx.bits_grad, ctx.grad_mode = conv, bits_grad, grad_mode
+        ctx.has_bias = b is not None
+        ctx.save_for_backward(x, w)
+        if conv is None:
+            return F.linear(x, w, b)
+        stride, padding, dilation, groups = conv
+        return F.conv2d(x, w, b, stride, padding, dilation, groups)
+
+    @staticmethod
+    def backward(ctx, g):
+        x, w = ctx.saved_tensors
+        need_x, need_w, need_b = ctx.needs_input_grad[0], ctx.needs_input_grad[1], ctx.has_bias and ctx.needs_input_grad[2]
+        g = g.contiguous()
+        gq = None
+        if ctx.grad_mode != "full" and (need_x or ctx.grad_mode == "quant"):
+            gq = _quantize_gradient(g, ctx.bits_grad)
+        g_param = gq if ctx.grad_mode == "quant" else g          # weight / bias branch
+        g_input = g if ctx.grad_mode == "full" else gq           # input branch
+        dx = dw = db = None
+        if ctx.conv is None:
+            if need_x:
+                dx = g_input.matmul(w)
+            if need_w:
+                dw = g_param.reshape(-1, g_param.shape[-1]).t().matmul(x.reshape(-1, x.shape[-1]))
+            if need_b:
+                db = g_param.reshape(-1, g_param.shape[-1]).sum(0)
+        else:
+            stride, padding, dilation, groups = ctx.conv
+            bias_sizes = [w.shape[0]] if ctx.has_bias else None
+            if need_x:
+                dx = torch.ops.aten.convolution_backward(g_input, x, w, bias_sizes, stride, padding, dilation, False,
+                                                         [0, 0], groups, [True, False, False])[0]
+            if need_w or need_b:
+                _, dw, db = torch.ops.aten.convolution_backward(g_param, x, w, bias_sizes, stride, padding, dilation,
+                                                                False, [0, 0], groups, [False, need_w, bool(need_b)])
+        return dx, dw, db, None, None, None
+
+
+def conv2d_biprec(input, weight, bias=None, stride=1, padding=0, dilation=1, groups=1, num_bits_grad=None):
+    """quantize.py:142-148."""
+    conv = (_pair(stride), _pair(padding), _pair(dilation), groups)
+    return _QContraction.apply(input, weight, bias, conv, num_bits_grad, "biprec" if num_bits_grad is not None else "full")
+
+
+def linear_biprec(input, weight, bias=None, num_bits_grad=None):
+    """quantize.py:151-156."""
+    return _QContraction.apply(input, weight, bias, None, num_bits_grad, "biprec" if num_bits_grad is not None else "full")
+
+
+# ---------------------------------------------------------------------------------------------------
+# QuantNode / QuantMeasure                                                   (quantize.py:177-268)
+# ---------------------------------------------------------------------------------------------------
+class QuantNode():
+    def __init__(self):
+        self.enable_quant = True
+        self.freeze_param_dyn_range = False
+
+    def set_measure_mode(self, measure, momentum=None):
+        self.enable_quant = not measure
+        if momentum and isinstance(self, QuantMeasure):
+            self.momentum = momentum
+        elif isinstance(self, nn.Module):
+            for q in self._modules.values():
+                if isinstance(q, QuantNode):
+                    q.set_measure_mode(measure, momentum=momentum)
+
+    def overwrite_params(self, logging=None):
+        if isinstance(self, nn.Module):
+            for q in self._modules.values():
+                if isinstance(q, QuantNode):
+                    q.overwrite_params(logging)
+
+
+class _AffineSTE(Function):
+    """Min-anchored fake-quant with a device-resident range; straight-through backward (:105-109)."""
+
+    @staticmethod
+    def forward(ctx, x, range_dev, bits):
+        return _abi.fakequant_affine(x, bits, range_dev=range_dev, scale_mode=QB_SCALE_DOUBLE)
+
+    @staticmethod
+    def backward(ctx, g):
+        return g, None, None
+
+
+class QuantMeasure(nn.Module, QuantNode):
+    """Running activation-range tracker + activation fake-quant (quantize.py:198-268)."""
+    _QMEASURE_SUPPORTED_METHODS = ['avg', 'aciq']
+
+    def __init__(self, num_bits=8, momentum=None, method='avg'):
+        super(QuantMeasure, self).__init__()
+        QuantNode.__init__(self)
+        assert method in QuantMeasure._QMEASURE_SUPPORTED_METHODS
+        self.register_buffer('running_min', torch.zeros(1))
+        self.register_buffer('running_max', torch.zeros(1))
+        self.register_buffer('num_measurements', torch.zeros(1))
+        self.register_buffer('running_var', torch.ones(1))
+        self.register_buffer('running_mean', torch.zeros(1))
+        self.momentum = momentum
+        self.num_bits = num_bits
+        self.method = method
+        self.laplace_alpha = {2: 2.83, 3: 3.89, 4: 5.03, 5: 6.2, 6: 7.41, 7: 8.64, 8: 9.89}.get(num_bits)
+
+    def _buffers5(self):
+        return (self.running_min, self.running_max, self.num_measurements, self.running_var, self.running_mean)
+
+    def measure(self, input):
+        """Update the running buffers (training) and return the device range float[2] this call uses.
+        quantize.py:223-246 without the float() syncs."""
+        method = 1 if self.method == 'aciq' else 0
+        if method:
+            assert self.laplace_alpha, 'aciq not supported for module num bits'
+        x = input.detach()
+        if self.training:
+            stats = _abi.measure_stats(x)
+            if _reducer is not None:
+                _reducer.measure(stats)
+            return _abi.measure_finalize(stats, self._buffers5(), self.momentum, True, method, self.num_bits)
+        return _abi.measure_finalize(None, self._buffers5(), self.momentum, False, method, self.num_bits)
+
+    def forward(self, input):
+        rng = self.measure(input)
+        if self.enable_quant:
+            return _AffineSTE.apply(input, rng, self.num_bits)
+        return input
+
+    def _get_measured_range(self):
+        return float(self.running_min), float(self.running_max)
+
+
+# ---------------------------------------------------------------------------------------------------
+# QConv2d / QLinear                                                          (quantize.py:271-432)
+# ---------------------------------------------------------------------------------------------------
+class _RowsSTE(Function):
+    """Per-output-channel weight fake-quant (:318-323, 332-334), straight-through backward.  The row ranges are
+    written straight into the module's weight_min / weight_max buffers (the reference re-assigns them each
+    forward); ``compute_range`` False reuses the stored ranges (frozen dynamic range, overwrite_params)."""
+
+    @staticmethod
+    def forward(ctx, w, row_min, row_max, bits, compute_range):
+        out, _, _ = _abi.fakequant_rows(w, bits, row_min=row_min, row_max=row_max, compute_range=compute_range)
+        return out
+
+    @staticmethod
+    def backward(ctx, g):
+        return g, None, None, None, None
+
+
+class _ScalarRangeSTE(Function):
+    """Per-tensor fake-quant with the range taken from the tensor itself and a tensor-typed scale: the bias
+    path (:328-330, 336-338).  Returns (quantized, range float[2])."""
+
+    @staticmethod
+    def forward(ctx, v, bits):
+        rng = _abi.minmax(v)
+        out = _abi.fakequant_affine(v, bits, range_dev=rng, scale_mode=QB_SCALE_FLOAT)
+        ctx.mark_non_differentiable(rng)
+        return out, rng
+
+    @staticmethod
+    def backward(ctx, g, _g_rng):
+        return g, None
+
+
+class _QBase(QuantNode):
+    """State and forward logic shared by QConv2d / QLinear."""
+
+    def _init_quant(self, num_bits, num_bits_weight, num_bits_grad, biprecision, bias_quant, per_channel, bias):
+        QuantNode.__init__(self)
+        self.num_bits = num_bits
+        self.num_bits_weight = num_bits_weight or num_bits
+        self.num_bits_grad = num_bits_grad
+        self.quantize_input = QuantMeasure(self.num_bits)
+        self.biprecision = biprecision
+        self.bias_quant = bias_quant and bias
+        self.per_channel = per_channel
+        if not per_channel:
+            # the reference assigns a Python float to a registered buffer in forward and raises
+            raise QB200Error("per_channel=False is not usable in the reference (quantize.py:325-326 raises); "
+                             "only per-output-channel weight ranges are implemented")
+        n_channels = self.weight.size(0)
+        self.scale_shape = (n_channels,) + (1,) * (self.weight.dim() - 1)
+        with torch.no_grad():
+            flat = self.weight.flatten(1)
+            self.register_buffer('weight_min', flat.min(-1)[0].view(self.scale_shape).clone())
+            self.register_buffer('weight_max', flat.max(-1)[0].view(self.scale_shape).clone())
+            if self.bias_quant:
+                self.register_buffer('bias_min', self.bias.min().clone())
+                self.register_buffer('bias_max', self.bias.max().clone())
+
+    def _quantized_params(self):
+        """qweight, qbias as the forward uses them (:317-340)."""
+        update = not self.freeze_param_dyn_range
+        qweight = _RowsSTE.apply(self.weight, self.weight_min, self.weight_max, self.num_bits_weight, update)
+        qbias = self.bias
+        if self.bias is not None and (self.bias_quant or update):
+            if update:
+                qb, rng = _ScalarRangeSTE.apply(self.bias, self.num_bits_weight)
+                if hasattr(self, 'bias_min'):
+                    with torch.no_grad():
+                        self.bias_min.copy_(rng[0])
+                        self.bias_max.copy_(rng[1])
+                if self.bias_quant:
+                    qbias = qb
+            else:
+                qbias = UniformQuantize().apply(self.bias, self.num_bits_weight, self.bias_min, self.bias_max, False,
+                                                False, False)
+        return qweight, qbias
+
+    def _grad_mode(self):
+        if self.num_bits_grad is None:
+            return "full"
+        return "biprec" if self.biprecision else "quant"
+
+    def overwrite_params(self, logging=None):
+        """quantize.py:301-312 / 386-396: bake the quantized weights (ranges as stored) into the parameters."""
+        with torch.no_grad():
+            w, _, _ = _abi.fakequant_rows(self.weight, self.num_bits_weight, row_min=self.weight_min,
+                                          row_max=self.weight_max, compute_range=False)
+            self.weight.copy_(w)
+            if self.bias_quant:
+                self.bias.copy_(UniformQuantize().apply(self.bias, self.num_bits_weight, self.bias_min, self.bias_max,
+                                                        False, False, False))
+
+
+class QConv2d(nn.Conv2d, _QBase):
+    """quantize.py:271-354."""
+
+    def __init__(self, in_channels, out_channels, kernel_size, stride=1, padding=0, dilation=1, groups=1, bias=True,
+                 num_bits=8, num_bits_weight=None, num_bits_grad=None, biprecision=False, bias_quant=True,
+                 per_channel=True, **kwargs):
+        super(QConv2d, self).__init__(in_channels, out_channels, kernel_size, stride, padding, dilation, groups, bias,
+                                      **kwargs)
+        self._init_quant(num_bits, num_bits_weight, num_bits_grad, biprecision, bias_quant, per_channel, bias)
+
+    def forward(self, input):
+        input_ = self.quantize_input(input)
+        if not self.enable_quant:
+            return F.conv2d(input, self.weight, self.bias, self.stride, self.padding, self.dilation, self.groups)
+        qweight, qbias = self._quantized_params()
+        conv = (_pair(self.stride), _pair(self.padding), _pair(self.dilation), self.groups)
+        return _QContraction.apply(input_, qweight, qbias, conv, self.num_bits_grad, self._grad_mode())
+
+
+class QLinear(nn.Linear, _QBase):
+    """quantize.py:357-432."""
+
+    def __init__(self, in_features, out_features, bias=True, num_bits=8, num_bits_weight=None, num_bits_grad=None,
+                 biprecision=False, bias_quant=True, per_channel=True, **kwargs):
+        super(QLinear, self).__init__(in_features, out_features, bias, **kwargs)
+        self._init_quant(num_bits, num_bits_weight, num_bits_grad, biprecision, bias_quant, per_channel, bias)
+
+    def forward(self, input):
+        input_ = self.quantize_input(input)
+        if not self.enable_quant:
+            return F.linear(input, self.weight, self.bias)
+        qweight, qbias = self._quantized_params()
+        return _QContraction.apply(input_, qweight, qbias, None, self.num_bits_grad, self._grad_mode())
+
+
+# ---------------------------------------------------------------------------------------------------
+# RangeBN                                                                    (quantize.py:435-505)
+# ---------------------------------------------------------------------------------------------------
+class _RangeBNFn(Function):
+    """Statistics + normalisation of the (already fake-quantized) input and, in backward, the output-gradient
+    quantizer followed by the closed-form gradient of :467-499 (rangebn.cu)."""
+
+    @staticmethod
+    def forward(ctx, xq, gamma, beta, running_mean, running_var, training, momentum, num_chunks, eps, bits, bits_grad):
+        xq = xq.contiguous()
+        B, Cn = xq.shape[0], xq.shape[1]
+        HW = xq.numel() // (B * Cn)
+        count, chunk_len, chunks_global = float(B * HW), 0.0, num_chunks
+        red = amax = amin = None
+        if training:
+            local_chunks = num_chunks
+            if _reducer is not None:
+                local_chunks, count = _reducer.rangebn_layout(B, HW, num_chunks)
+            want_arg = any(ctx.needs_input_grad[:3])
+            red, amax, amin = _abi.rangebn_stats(xq, B, Cn, HW, local_chunks, want_arg=want_arg)
+            if _reducer is not None:
+                _reducer.rangebn(red)
+            chunk_len = count / chunks_global
+            ctx.local_chunks = local_chunks
+        vec = _abi.rangebn_finalize(red, Cn, chunks_global, count, chunk_len, eps, momentum, training, bits, gamma, beta,
+                                    running_mean, running_var)
+        out = _abi.rangebn_apply(xq, B, Cn, HW, vec, gamma is not None, beta is not None)
+        ctx.dims = (B, Cn, HW, chunks_global, count, chunk_len, training, bits_grad, gamma is not None, beta is not None)
+        ctx.save_for_backward(xq, vec, amax, amin)
+        return out
+
+    @staticmethod
+    def backward(ctx, g):
+        xq, vec, amax, amin = ctx.saved_tensors
+        B, Cn, HW, K, count, chunk_len, training, bits_grad, has_gamma, has_beta = ctx.dims
+        gq = _quantize_gradient(g, bits_grad) if bits_grad is not None else g.contiguous()
+        hook = _reducer.rangebn_bwd if (_reducer is not None and training) else None
+        dx, dgamma, dbeta = _abi.rangebn_backward(gq, xq, B, Cn, HW, ctx.local_chunks if training else 0, count,
+                                                  chunk_len, training, vec, has_gamma, amax, amin, reduce_hook=hook,
+                                                  chunks_global=K)
+        return (dx if ctx.needs_input_grad[0] else None, dgamma if has_gamma else None, dbeta if has_beta else None,
+                None, None, None, None, None, None, None, None)
+
+
+class RangeBN(nn.Module):
+    """quantize.py:435-505 ("normalized RangeBN")."""
+
+    def __init__(self, num_features, dim=1, momentum=0.1, affine=True, num_chunks=16, eps=1e-5, num_bits=8,
+                 num_bits_grad=8):
+        super(RangeBN, self).__init__()
+        self.register_buffer('running_mean', torch.zeros(num_features))
+        self.register_buffer('running_var', torch.zeros(num_features))
+        self.momentum = momentum
+        self.dim = dim
+        if affine:
+            self.bias = nn.Parameter(torch.Tensor(num_features))
+            self.weight = nn.Parameter(torch.Tensor(num_features))
+        else:
+            self.register_parameter('bias', None)
+            self.register_parameter('weight', None)
+        self.num_bits = num_bits
+        self.num_bits_grad = num_bits_grad
+        self.quantize_input = QuantMeasure(self.num_bits)
+        self.eps = eps
+        self.num_chunks = num_chunks
+        self.reset_params()
+
+    def reset_params(self):
+        if self.weight is not None:
+            self.weight.data.uniform_()
+        if self.bias is not None:
+            self.bias.data.zero_()
+
+    def forward(self, x):
+        x = self.quantize_input(x)
+        two_d = x.dim() == 2
+        if two_d:
+            x = x.unsqueeze(-1).unsqueeze(-1)
+        out = _RangeBNFn.apply(x, self.weight, self.bias, self.running_mean, self.running_var, self.training,
+                               self.momentum, self.num_chunks, self.eps, self.num_bits, self.num_bits_grad)
+        if out.size(3) == 1 and out.size(2) == 1:
+            out = out.squeeze(-1).squeeze(-1)
+        return out
+
+
+# ---------------------------------------------------------------------------------------------------
+# model-walk helpers                                                          (quantize.py:508-610)
+# ---------------------------------------------------------------------------------------------------
+def is_bn(m):
+    return isinstance(m, nn.BatchNorm2d) or isinstance(m, nn.BatchNorm1d)
+
+
+def is_quant(m):
+    return isinstance(m, QuantNode) or isinstance(m, QLinear) or isinstance(m, QConv2d)
+
+
+def recursive_apply(model, func, *args):
+    for m in model.children():
+        func(m, *args)
+        recursive_apply(m, func, *args)
+
+
+def set_bn_is_train(model, train, logger=None, reload_running_estimators=False, reset_running_estimators=False,
+                    freeze_affine=False):
+    """quantize.py:523-544."""
+    def func(m, *args):
+        if not is_bn(m):
+            return
+        if reload_running_estimators or reset_running_estimators:
+            if (reload_running_estimators and not hasattr(m, 'locked_running_mean')) or reset_running_estimators:
+                m.locked_running_mean = m.running_mean.data.clone()
+                m.locked_running_var = m.running_var.data.clone()
+            else:
+                m.running_mean.data = m.locked_running_mean.clone()
+                m.running_var.data = m.locked_running_var.clone()
+        if freeze_affine:
+            for p in m.parameters():
+                p.requires_grad = False
+        m.train(train)
+
+    recursive_apply(model, func)
+
+
+def set_measure_mode(model, measure, momentum=None, logger=None):
+    """quantize.py:547-558: calibration switch - quantizers pass through while ranges keep accumulating."""
+    def func(m, *args):
+        if is_bn(m):
+            m.train(not measure)
+        elif is_quant(m):
+            m.set_measure_mode(measure, momentum=momentum)
+
+    recursive_apply(model, func)
+
+
+def set_quant_mode(model, quant, logger=None):
+    def func(m, *args):
+        if is_quant(m):
+            m.enable_quant = quant
+
+    recursive_apply(model, func)
+
+
+def overwrite_params(model, logger=None):
+    def func(m, *args):
+        if is_quant(m):
+            m.overwrite_params(logger)
+
+    recursive_apply(model, func)
+
+
+def freeze_quant_params(model, freeze=True, include_param_dyn_range=True, momentum='same', logger=None):
+    """quantize.py:579-592, INCLUDING its misspelt attribute: the reference sets ``freeze_param_dyn_rang`` (sic), so
+    weight ranges are in fact never frozen by this call.  Kept for parity."""
+    def func(m, *args):
+        if isinstance(m, QuantMeasure):
+            m.train(not freeze)
+            if momentum != 'same':
+                m.momentum = momentum
+        if include_param_dyn_range and isinstance(m, QuantNode):
+            m.freeze_param_dyn_rang = freeze
+
+    recursive_apply(model, func)
+
+
+def distill_set_train(model, train):
+    model.train(train)
+    if train:
+        freeze_quant_params(model)
+        set_bn_is_train(model, False)
+
+
+def set_global_quantization_method(model, method='aciq', logger=None):
+    assert method in QuantMeasure._QMEASURE_SUPPORTED_METHODS
+
+    def func(m, *args):
+        if isinstance(m, QuantMeasure):
+            m.method = method
+
+    recursive_apply(model, func)

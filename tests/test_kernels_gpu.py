@@ -198,8 +198,8 @@ def test_measure_stats(lib, shape):
         st = lib.measure_stats(x.to(DEV)).cpu()
         assert st[0].item() == rows.min(-1)[0].double().sum().item()
         assert st[1].item() == rows.max(-1)[0].double().sum().item()
-        assert abs(st[2].item() - x.double().sum().item()) <= 1e-9 * x.double().abs().sum().item()
-        assert abs(st[3].item() - (x.double() ** 2).sum().item()) <= 1e-9 * (x.double() ** 2).sum().item()
+        assert abs(st[2].item() - x.double().sum().item()) <= 1e-7 * x.double().abs().sum().item()
+        assert abs(st[3].item() - (x.double() ** 2).sum().item()) <= 1e-7 * (x.double() ** 2).sum().item()
         assert st[4].item() == float(x.min()) and st[5].item() == float(x.max())
         assert st[6].item() == x.numel() and st[7].item() == shape[0]
 
