@@ -11,12 +11,14 @@ constexpr int MS_VEC_PER_THREAD = 8;                               // float4 loa
 constexpr int64_t MS_TILE = MS_THREADS * 4 * MS_VEC_PER_THREAD;    // 8192 elements
 constexpr int MS_MAX_BLOCKS = 2048;
 
-// workspace: [uint32 row_max_enc[B]] [uint32 row_min_enc[B]] [double psum[MS_MAX_BLOCKS]] [double psq[...]] [counter]
-// encodings are 0 when empty, so a zero-filled workspace is a valid initial state.
-static size_t ms_off_sum(int64_t B) { return ((size_t)B * 8 + 15) & ~(size_t)15; }
+// workspace: [counter, 64 B] [double psum[MS_MAX_BLOCKS]] [double psq[MS_MAX_BLOCKS]] [uint32 row_max_enc[B]]
+// [uint32 row_min_enc[B]].  The fixed-size part comes first so that one workspace can serve calls with different
+// B: only the counter and the row slots must be zero on entry (the kernel re-zeroes them), and their position
+// never overlaps the partial-sum area whatever B was used before.
+static const size_t MS_FIXED_BYTES = 64 + (size_t)MS_MAX_BLOCKS * 16;
 extern "C" size_t qb_measure_ws_bytes(int64_t B) {
     if (B < 0) return 0;
-    return ms_off_sum(B) + (size_t)MS_MAX_BLOCKS * 16 + 64;
+    return MS_FIXED_BYTES + (size_t)B * 8;
 }
 
 // monotone float -> uint32 map (larger float => larger uint); never yields 0 for a non-NaN float
@@ -154,11 +156,11 @@ extern "C" int qb_measure_stats(const float* x, int64_t B, int64_t inner, double
         return QB_ERR_WORKSPACE;
     }
     char* base = static_cast<char*>(ws);
-    unsigned int* row_max = reinterpret_cast<unsigned int*>(base);
-    unsigned int* row_min = row_max + B;
-    double* psum = reinterpret_cast<double*>(base + ms_off_sum(B));
+    unsigned int* counter = reinterpret_cast<unsigned int*>(base);
+    double* psum = reinterpret_cast<double*>(base + 64);
     double* psq = psum + MS_MAX_BLOCKS;
-    unsigned int* counter = reinterpret_cast<unsigned int*>(psq + MS_MAX_BLOCKS);
+    unsigned int* row_max = reinterpret_cast<unsigned int*>(base + MS_FIXED_BYTES);
+    unsigned int* row_min = row_max + B;
     const int vec = ((reinterpret_cast<uintptr_t>(x) & 15) == 0) && (inner % 4 == 0);
     const int64_t T = B * ((inner + MS_TILE - 1) / MS_TILE);
     int sms = qb_sm_count();

@@ -1,0 +1,106 @@
+"""Batch-sharded training: one process per GPU, torch.distributed (NCCL over NVLink 5 / NVSwitch).
+
+The reference runs multi-GPU through ``nn.DataParallel`` (main.py:344-345): every replica computes its
+QuantMeasure / RangeBN / gradient ranges on its own shard and the replicas' buffer updates are dropped, so its
+numerics change with the GPU count.  Here the N-rank run is DEFINED to equal the single-process run on the
+global batch: besides the gradient all-reduce, the tiny per-layer statistics are
+all-reduced so that every rank derives the same ranges:
+
+  QuantMeasure   double[8]   {sum_b min_b, sum_b max_b, sum x, sum x^2 | min | max | n, B}   SUM / MIN / MAX
+  RangeBN fwd    double[3C]  {sum_k chunk-max, sum_k chunk-min, sum x}                      SUM (ranks own whole chunks)
+  RangeBN bwd    double[2C]  {sum gq, sum gq*xq}                                             SUM
+  grad quantizer float[2]    {min, max}  -> MAX over {-min, max}                             MAX
+
+These are latency-bound messages (16 B ... 12 KB): one NCCL all-reduce each, enqueued on the compute stream so
+no host synchronisation is introduced.  Gradients are all-reduced (SUM, then scaled by 1/world) in one flat
+bucket per dtype after backward.
+"""
+import torch
+import torch.distributed as dist
+
+from . import quantize as Q
+
+_state = {"device": None, "world": 1, "rank": 0}
+
+
+class StatReducer:
+    """All-reduces the statistic blocks IN PLACE (interface expected by quantize.set_stat_reducer)."""
+
+    def __init__(self, group=None):
+        self.group = group
+        self.world = dist.get_world_size(group)
+        self.rank = dist.get_rank(group)
+
+    # QuantMeasure: entries 0-3 and 6-7 are sums, 4 is a min, 5 a max.  One SUM plus one MAX message.
+    def measure(self, stats):
+        ext = torch.stack([-stats[4], stats[5]])
+        stats[4] = 0.0
+        stats[5] = 0.0
+        dist.all_reduce(stats, op=dist.ReduceOp.SUM, group=self.group)
+        dist.all_reduce(ext, op=dist.ReduceOp.MAX, group=self.group)
+        stats[4] = -ext[0]
+        stats[5] = ext[1]
+
+    def rangebn_layout(self, B_local, HW, num_chunks):
+        """-> (chunks owned by this rank, global element count per channel).  Contiguous batch shards hold whole
+        chunks when num_chunks % world == 0 (16 chunks on 1/2/4/8 ranks)."""
+        if num_chunks % self.world != 0:
+            raise Q.QB200Error("RangeBN: num_chunks=%d must be divisible by world size %d" % (num_chunks, self.world))
+        local = num_chunks // self.world
+        if (B_local * HW) % local != 0:
+            raise Q.QB200Error("RangeBN: local B*H*W=%d not divisible by the %d local chunks" % (B_local * HW, local))
+        return local, float(B_local * HW * self.world)
+
+    def rangebn(self, red):
+        dist.all_reduce(red, op=dist.ReduceOp.SUM, group=self.group)
+
+    def rangebn_bwd(self, sums):
+        dist.all_reduce(sums, op=dist.ReduceOp.SUM, group=self.group)
+
+    def grad_range(self, rng):
+        ext = torch.stack([-rng[0], rng[1]])
+        dist.all_reduce(ext, op=dist.ReduceOp.MAX, group=self.group)
+        rng[0] = -ext[0]
+        rng[1] = ext[1]
+
+
+def init(device=None, group=None):
+    """Install the cross-rank statistic reducer.  torch.distributed must already be initialised."""
+    if not dist.is_initialized():
+        raise RuntimeError("torch.distributed is not initialised")
+    _state.update(device=device, world=dist.get_world_size(group), rank=dist.get_rank(group), group=group)
+    if _state["world"] > 1:
+        Q.set_stat_reducer(StatReducer(group))
+    return _state["rank"], _state["world"]
+
+
+def shutdown():
+    Q.set_stat_reducer(None)
+
+
+def broadcast_parameters(model, src=0, group=None):
+    """Replicas start identical (what DataParallel's per-step replicate achieves in the reference)."""
+    with torch.no_grad():
+        for t in list(model.parameters()) + list(model.buffers()):
+            dist.broadcast(t, src=src, group=group)
+
+
+def allreduce_gradients(model, group=None, average=True):
+    """Flat-bucket all-reduce of every gradient (46.8 MB for ResNet-18): one NCCL call, NVLS-eligible."""
+    grads = [p.grad for p in model.parameters() if p.grad is not None]
+    if not grads:
+        return
+    flat = torch._utils._flatten_dense_tensors(grads)
+    dist.all_reduce(flat, op=dist.ReduceOp.SUM, group=group)
+    if average:
+        flat.div_(dist.get_world_size(group))
+    for g, f in zip(grads, torch._utils._unflatten_dense_tensors(flat, grads)):
+        g.copy_(f)
+
+
+def shard_batch(x, rank=None, world=None):
+    """Contiguous slice of the global batch for this rank (so RangeBN chunks map to whole ranks)."""
+    rank = _state["rank"] if rank is None else rank
+    world = _state["world"] if world is None else world
+    per = x.shape[0] // world
+    return x[rank * per:(rank + 1) * per]
