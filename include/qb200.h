@@ -159,6 +159,23 @@ int qb_rangebn_bwd_apply(const float* gq, float* dx, int64_t B, int64_t C, int64
                          const float* qscale, const float* qgamma, const float* coef_a, const float* coef_e,
                          const int32_t* amax, const int32_t* amin, void* stream);
 
+/* ---------------------------------------------------------------------------------------------------
+ * Channels-last (NHWC) variants of the RangeBN kernels: x is [B, H*W, C] in memory (torch.channels_last),
+ * the native activation layout of this library (the int8 implicit GEMM reads and writes it).  Same
+ * semantics, outputs and index conventions (amax/amin hold the flat b*HW+p index) as the NCHW entry
+ * points above; finalize / bwd_coeffs are layout independent.                                        */
+size_t qb_rangebn_nhwc_ws_bytes(int64_t C, int num_chunks);
+int qb_rangebn_stats_nhwc(const float* x, int64_t B, int64_t C, int64_t HW, int num_chunks, int32_t* amax,
+                          int32_t* amin, double* red, void* ws, size_t ws_bytes, void* stream);
+int qb_rangebn_apply_nhwc(const float* x, float* out, int64_t B, int64_t C, int64_t HW, const float* mean,
+                          const float* qscale, const float* qgamma, const float* qbeta, void* stream);
+size_t qb_rangebn_bwd_nhwc_ws_bytes(int64_t C);
+int qb_rangebn_bwd_reduce_nhwc(const float* gq, const float* x, int64_t B, int64_t C, int64_t HW, double* sg,
+                               double* sgx, void* ws, size_t ws_bytes, void* stream);
+int qb_rangebn_bwd_apply_nhwc(const float* gq, float* dx, int64_t B, int64_t C, int64_t HW, int num_chunks,
+                              const float* qscale, const float* qgamma, const float* coef_a, const float* coef_e,
+                              const int32_t* amax, const int32_t* amin, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

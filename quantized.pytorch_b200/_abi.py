@@ -41,6 +41,12 @@ PROTOTYPES = {
     "qb_rangebn_bwd_reduce": (_i32, [_p, _p, _i64, _i64, _i64, _p, _p, _p, _sz, _p]),
     "qb_rangebn_bwd_coeffs": (_i32, [_p, _p, _i64, _i32, _dbl, _dbl, _i32, _p, _p, _p, _p, _p, _p, _p, _p, _p]),
     "qb_rangebn_bwd_apply": (_i32, [_p, _p, _i64, _i64, _i64, _i32, _p, _p, _p, _p, _p, _p, _p]),
+    "qb_rangebn_nhwc_ws_bytes": (_sz, [_i64, _i32]),
+    "qb_rangebn_stats_nhwc": (_i32, [_p, _i64, _i64, _i64, _i32, _p, _p, _p, _p, _sz, _p]),
+    "qb_rangebn_apply_nhwc": (_i32, [_p, _p, _i64, _i64, _i64, _p, _p, _p, _p, _p]),
+    "qb_rangebn_bwd_nhwc_ws_bytes": (_sz, [_i64]),
+    "qb_rangebn_bwd_reduce_nhwc": (_i32, [_p, _p, _i64, _i64, _i64, _p, _p, _p, _sz, _p]),
+    "qb_rangebn_bwd_apply_nhwc": (_i32, [_p, _p, _i64, _i64, _i64, _i32, _p, _p, _p, _p, _p, _p, _p]),
 }
 
 _lib = None
@@ -78,7 +84,8 @@ LAUNCHES = 0          # kernels launched through the C ABI by this process (benc
 _profile = None       # list of (name, algorithmic_bytes, start_event, end_event) while profiling
 
 # kernels enqueued per C call
-_NLAUNCH = {"qb_rangebn_stats": 2, "qb_rangebn_bwd_reduce": 2, "qb_rangebn_bwd_apply": 2}
+_NLAUNCH = {"qb_rangebn_stats": 2, "qb_rangebn_bwd_reduce": 2, "qb_rangebn_bwd_apply": 2,
+            "qb_rangebn_stats_nhwc": 2, "qb_rangebn_bwd_reduce_nhwc": 2, "qb_rangebn_bwd_apply_nhwc": 2}
 
 
 def _run(name, nbytes, *args):
@@ -133,7 +140,14 @@ def _f32c(t, name):
     if not (t.is_cuda and t.dtype == torch.float32):
         raise QB200Error("%s must be a CUDA float32 tensor (got %s on %s); there is no CPU fallback"
                          % (name, t.dtype, t.device))
-    return t if t.is_contiguous() else t.contiguous()
+    if t.is_contiguous() or (t.dim() == 4 and t.is_contiguous(memory_format=torch.channels_last)):
+        return t            # dense in either memory format: elementwise kernels work on the raw storage order
+    return t.contiguous()
+
+
+def is_nhwc(t):
+    """True if a 4-D tensor is laid out channels-last (and not equally describable as NCHW-contiguous)."""
+    return t.dim() == 4 and t.is_contiguous(memory_format=torch.channels_last) and not t.is_contiguous()
 
 
 _ws_cache = {}
@@ -251,15 +265,16 @@ def fakequant_grad_fused(g, bits, noise=None, stochastic=True, seed=0, offset=0,
 # ----------------------------------------------------------------------------------------------
 # RangeBN
 # ----------------------------------------------------------------------------------------------
-def rangebn_stats(x, B, Cn, HW, num_chunks, want_arg=True):
+def rangebn_stats(x, B, Cn, HW, num_chunks, want_arg=True, nhwc=False):
     """x: quantized NCHW input.  Returns (red double[3*C], amax int32[C*K] | None, amin | None)."""
     lib = load()
     dev = x.device
     red = torch.empty(3 * Cn, dtype=torch.float64, device=dev)
     amax = torch.empty(Cn * num_chunks, dtype=torch.int32, device=dev) if want_arg else None
     amin = torch.empty(Cn * num_chunks, dtype=torch.int32, device=dev) if want_arg else None
-    ws = workspace("rangebn", lib.qb_rangebn_ws_bytes(Cn, num_chunks), dev)
-    _run("qb_rangebn_stats", 4 * B * Cn * HW, _ptr(x), B, Cn, HW, num_chunks, _ptr(amax), _ptr(amin), _ptr(red), _ptr(ws), ws.numel(),
+    sfx = "_nhwc" if nhwc else ""
+    ws = workspace("rangebn" + sfx, (lib.qb_rangebn_nhwc_ws_bytes if nhwc else lib.qb_rangebn_ws_bytes)(Cn, num_chunks), dev)
+    _run("qb_rangebn_stats" + sfx, 4 * B * Cn * HW, _ptr(x), B, Cn, HW, num_chunks, _ptr(amax), _ptr(amin), _ptr(red), _ptr(ws), ws.numel(),
                                 _stream())
     return red, amax, amin
 
@@ -277,17 +292,17 @@ def rangebn_finalize(red, Cn, num_chunks, count, chunk_len, eps, momentum, train
     return vec
 
 
-def rangebn_apply(x, B, Cn, HW, vec, has_gamma, has_beta, out=None):
+def rangebn_apply(x, B, Cn, HW, vec, has_gamma, has_beta, out=None, nhwc=False):
     lib = load()
     if out is None:
         out = torch.empty_like(x)
-    _run("qb_rangebn_apply", 8 * B * Cn * HW, _ptr(x), _ptr(out), B, Cn, HW, _ptr(vec[0]), _ptr(vec[2]),
+    _run("qb_rangebn_apply" + ("_nhwc" if nhwc else ""), 8 * B * Cn * HW, _ptr(x), _ptr(out), B, Cn, HW, _ptr(vec[0]), _ptr(vec[2]),
                                 _ptr(vec[3]) if has_gamma else None, _ptr(vec[4]) if has_beta else None, _stream())
     return out
 
 
 def rangebn_backward(gq, xq, B, Cn, HW, num_chunks, count, chunk_len, training, vec, has_gamma, amax, amin,
-                     reduce_hook=None, chunks_global=None):
+                     reduce_hook=None, chunks_global=None, nhwc=False):
     """Returns (dx, dgamma, dbeta).  ``reduce_hook(sums)`` may all-reduce the double[2*C] sums in place
     (batch-sharded training); ``num_chunks`` is this rank's chunk count (layout of amax/amin),
     ``chunks_global`` the count the chunk-mean was taken over."""
@@ -296,8 +311,9 @@ def rangebn_backward(gq, xq, B, Cn, HW, num_chunks, count, chunk_len, training, 
     if chunks_global is None:
         chunks_global = num_chunks
     sums = torch.empty(2 * Cn, dtype=torch.float64, device=dev)
-    ws = workspace("rangebn_bwd", lib.qb_rangebn_bwd_ws_bytes(Cn), dev)
-    _run("qb_rangebn_bwd_reduce", 8 * B * Cn * HW, _ptr(gq), _ptr(xq), B, Cn, HW, _ptr(sums[:Cn]), _ptr(sums[Cn:]), _ptr(ws),
+    sfx = "_nhwc" if nhwc else ""
+    ws = workspace("rangebn_bwd" + sfx, (lib.qb_rangebn_bwd_nhwc_ws_bytes if nhwc else lib.qb_rangebn_bwd_ws_bytes)(Cn), dev)
+    _run("qb_rangebn_bwd_reduce" + sfx, 8 * B * Cn * HW, _ptr(gq), _ptr(xq), B, Cn, HW, _ptr(sums[:Cn]), _ptr(sums[Cn:]), _ptr(ws),
                                      ws.numel(), _stream())
     if reduce_hook is not None:
         reduce_hook(sums)
@@ -307,7 +323,7 @@ def rangebn_backward(gq, xq, B, Cn, HW, num_chunks, count, chunk_len, training, 
                                      _ptr(vec[3]) if has_gamma else None, _ptr(coef[0]), _ptr(coef[1]), _ptr(coef[2]),
                                      _ptr(coef[3]), _stream())
     dx = torch.empty_like(gq)
-    _run("qb_rangebn_bwd_apply", 8 * B * Cn * HW, _ptr(gq), _ptr(dx), B, Cn, HW, int(num_chunks) if training else 0, _ptr(vec[2]),
+    _run("qb_rangebn_bwd_apply" + sfx, 8 * B * Cn * HW, _ptr(gq), _ptr(dx), B, Cn, HW, int(num_chunks) if training else 0, _ptr(vec[2]),
                                     _ptr(vec[3]) if has_gamma else None, _ptr(coef[2]),
                                     _ptr(coef[3]) if training else None, _ptr(amax) if training else None,
                                     _ptr(amin) if training else None, _stream())

@@ -10,27 +10,6 @@
 constexpr int RB_THREADS = 256;
 
 // ---------------------------------------------------------------------------------------------------
-// exact unsigned 32-bit division by an invariant (Granlund-Montgomery round-up method)
-// ---------------------------------------------------------------------------------------------------
-struct FastDiv {
-    uint32_t d, m, s;  // q = (umulhi(m,n) + ((n - umulhi(m,n)) >> 1)) >> s    (d >= 2);  d == 1: q = n
-};
-static FastDiv make_fastdiv(uint32_t d) {
-    FastDiv f{d, 0u, 0u};
-    if (d <= 1) return f;
-    uint32_t l = 0;
-    while ((1ull << l) < d) ++l;   // ceil(log2 d)
-    f.m = (uint32_t)((((1ull << l) - d) << 32) / d + 1);
-    f.s = l - 1;
-    return f;
-}
-__device__ __forceinline__ uint32_t fdiv(uint32_t n, const FastDiv& f) {
-    if (f.d == 1) return n;
-    uint32_t t = __umulhi(f.m, n);
-    return (t + ((n - t) >> 1)) >> f.s;
-}
-
-// ---------------------------------------------------------------------------------------------------
 // walk the elements of task (c, k): flat (b,p) indices e in [e0, e1) of channel c, run by run
 // ---------------------------------------------------------------------------------------------------
 template <int G, class F4, class F1>

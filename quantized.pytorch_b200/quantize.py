@@ -33,6 +33,10 @@ __all__ = ["UniformQuantize", "UniformQuantizeGrad", "quantize", "quantize_grad"
 # ---------------------------------------------------------------------------------------------------
 # noise source of the stochastic branch + cross-rank statistic hooks
 # ---------------------------------------------------------------------------------------------------
+# Activations flow channels-last (NHWC) through the network: QConv2d converts a 4-D NCHW-contiguous input once and
+# every kernel preserves the layout.  Logical shapes, indexing and results are unchanged (torch.channels_last).
+CHANNELS_LAST = True
+
 _noise_provider = None
 _seed_base = 0x5DEECE66D
 _seed_counter = itertools.count(1)
@@ -80,8 +84,10 @@ def set_stat_reducer(reducer):
 
 def _quantize_gradient(g, bits, stochastic=True):
     """UniformQuantizeGrad.backward (quantize.py:124-139): global min/max, zero-point stochastic quantizer."""
-    g = g.contiguous()
+    g = _abi._f32c(g, "grad")
     noise = _noise_provider(tuple(g.shape)) if (stochastic and _noise_provider is not None) else None
+    if noise is not None and _abi.is_nhwc(g):
+        noise = noise.reshape(g.shape).contiguous(memory_format=torch.channels_last)   # same logical element <-> same noise
     if _reducer is None:
         out, _ = _abi.fakequant_grad_fused(g, bits, noise=noise, stochastic=stochastic, seed=_next_seed(),
                                            step_dev=noise_step(g.device))
@@ -238,7 +244,7 @@ class _QContraction(Function):
     def backward(ctx, g):
         x, w = ctx.saved_tensors
         need_x, need_w, need_b = ctx.needs_input_grad[0], ctx.needs_input_grad[1], ctx.has_bias and ctx.needs_input_grad[2]
-        g = g.contiguous()
+        g = _abi._f32c(g, "grad")
         gq = None
         if ctx.grad_mode != "full" and (need_x or ctx.grad_mode == "quant"):
             gq = _quantize_gradient(g, ctx.bits_grad)
@@ -462,6 +468,8 @@ class QConv2d(nn.Conv2d, _QBase):
         self._init_quant(num_bits, num_bits_weight, num_bits_grad, biprecision, bias_quant, per_channel, bias)
 
     def forward(self, input):
+        if CHANNELS_LAST and input.dim() == 4 and not input.is_contiguous(memory_format=torch.channels_last):
+            input = input.contiguous(memory_format=torch.channels_last)      # library-native activation layout
         input_ = self.quantize_input(input)
         if not self.enable_quant:
             return F.conv2d(input, self.weight, self.bias, self.stride, self.padding, self.dilation, self.groups)
@@ -495,7 +503,8 @@ class _RangeBNFn(Function):
 
     @staticmethod
     def forward(ctx, xq, gamma, beta, running_mean, running_var, training, momentum, num_chunks, eps, bits, bits_grad):
-        xq = xq.contiguous()
+        xq = _abi._f32c(xq, "x")
+        nhwc = _abi.is_nhwc(xq)
         B, Cn = xq.shape[0], xq.shape[1]
         HW = xq.numel() // (B * Cn)
         count, chunk_len, chunks_global = float(B * HW), 0.0, num_chunks
@@ -505,15 +514,16 @@ class _RangeBNFn(Function):
             if _reducer is not None:
                 local_chunks, count = _reducer.rangebn_layout(B, HW, num_chunks)
             want_arg = any(ctx.needs_input_grad[:3])
-            red, amax, amin = _abi.rangebn_stats(xq, B, Cn, HW, local_chunks, want_arg=want_arg)
+            red, amax, amin = _abi.rangebn_stats(xq, B, Cn, HW, local_chunks, want_arg=want_arg, nhwc=nhwc)
             if _reducer is not None:
                 _reducer.rangebn(red)
             chunk_len = count / chunks_global
             ctx.local_chunks = local_chunks
         vec = _abi.rangebn_finalize(red, Cn, chunks_global, count, chunk_len, eps, momentum, training, bits, gamma, beta,
                                     running_mean, running_var)
-        out = _abi.rangebn_apply(xq, B, Cn, HW, vec, gamma is not None, beta is not None)
+        out = _abi.rangebn_apply(xq, B, Cn, HW, vec, gamma is not None, beta is not None, nhwc=nhwc)
         ctx.dims = (B, Cn, HW, chunks_global, count, chunk_len, training, bits_grad, gamma is not None, beta is not None)
+        ctx.nhwc = nhwc
         ctx.save_for_backward(xq, vec, amax, amin)
         return out
 
@@ -521,11 +531,12 @@ class _RangeBNFn(Function):
     def backward(ctx, g):
         xq, vec, amax, amin = ctx.saved_tensors
         B, Cn, HW, K, count, chunk_len, training, bits_grad, has_gamma, has_beta = ctx.dims
-        gq = _quantize_gradient(g, bits_grad) if bits_grad is not None else g.contiguous()
+        g = g.contiguous(memory_format=torch.channels_last) if ctx.nhwc else g.contiguous()
+        gq = _quantize_gradient(g, bits_grad) if bits_grad is not None else g
         hook = _reducer.rangebn_bwd if (_reducer is not None and training) else None
         dx, dgamma, dbeta = _abi.rangebn_backward(gq, xq, B, Cn, HW, ctx.local_chunks if training else 0, count,
                                                   chunk_len, training, vec, has_gamma, amax, amin, reduce_hook=hook,
-                                                  chunks_global=K)
+                                                  chunks_global=K, nhwc=ctx.nhwc)
         return (dx if ctx.needs_input_grad[0] else None, dgamma if has_gamma else None, dbeta if has_beta else None,
                 None, None, None, None, None, None, None, None)
 

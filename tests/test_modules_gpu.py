@@ -73,8 +73,10 @@ def test_rangebn_golden(tag):
         assert rel_l2(bn(x.detach()), g[tag + "_out_eval"]) < 1e-5
 
 
-@pytest.mark.parametrize("shape", [(16, 64, 8, 8), (32, 16, 7, 7), (64, 512), (16, 3, 5, 6), (256, 8, 14, 14)])
-def test_rangebn_vs_oracle(shape):
+@pytest.mark.parametrize("nhwc", [False, True])
+@pytest.mark.parametrize("shape", [(16, 64, 8, 8), (32, 16, 7, 7), (64, 512), (16, 3, 5, 6), (256, 8, 14, 14),
+                                   (32, 6, 3, 5), (16, 1040, 2, 2)])
+def test_rangebn_vs_oracle(shape, nhwc):
     """Random shapes incl. HW%4!=0, 2-D, chunk boundaries inside a sample; first-index arg tie-break on
     heavily tied (quantized) data is exercised because the input is an 8-bit grid."""
     Q = q()
@@ -101,11 +103,18 @@ def test_rangebn_vs_oracle(shape):
         outr.backward(go)
     finally:
         qref.set_noise_provider(prev)
-    xd = x.to(DEV).requires_grad_()
+    xd = x.to(DEV)
+    god = go.to(DEV)
+    if nhwc and len(shape) == 4:
+        xd = xd.contiguous(memory_format=torch.channels_last)
+        god = god.contiguous(memory_format=torch.channels_last)
+    xd.requires_grad_()
     prev = Q.set_noise_provider(CudaReplay([noise]))
     try:
         out = bn(xd)
-        out.backward(go.to(DEV))
+        if nhwc and len(shape) == 4 and shape[2] * shape[3] > 1:
+            assert out.is_contiguous(memory_format=torch.channels_last)
+        out.backward(god)
     finally:
         Q.set_noise_provider(prev)
     assert rel_l2(out, outr) < 1e-5
@@ -126,6 +135,9 @@ def test_rangebn_apply_bit_exact_given_vectors(lib):
         ref = ((x - vec[0].view(1, C, 1, 1)) * vec[2].view(1, C, 1, 1)) * vec[3].view(1, C, 1, 1) + vec[4].view(1, C, 1, 1)
         out = lib.rangebn_apply(x.to(DEV), B, C, H * W, vec.to(DEV), True, True)
         assert torch.equal(out.cpu(), ref)
+        xl = x.to(DEV).contiguous(memory_format=torch.channels_last)
+        out = lib.rangebn_apply(xl, B, C, H * W, vec.to(DEV), True, True, nhwc=True)
+        assert torch.equal(out.cpu(), ref)
 
 
 def test_rangebn_arg_first_occurrence(lib):
@@ -138,7 +150,13 @@ def test_rangebn_arg_first_occurrence(lib):
         L = y.shape[-1]
         imax = y.max(-1)[1] + torch.arange(K).view(1, K) * L
         imin = y.min(-1)[1] + torch.arange(K).view(1, K) * L
-        red, amax, amin = lib.rangebn_stats(x.to(DEV), B, C, H * W, K)
+        for nhwc in (False, True):
+            xd = x.to(DEV)
+            if nhwc:
+                xd = xd.contiguous(memory_format=torch.channels_last)
+            red, amax, amin = lib.rangebn_stats(xd, B, C, H * W, K, nhwc=nhwc)
+            assert torch.equal(amax.cpu().view(C, K).long(), imax), (shape, nhwc)
+            assert torch.equal(amin.cpu().view(C, K).long(), imin), (shape, nhwc)
         assert torch.equal(amax.cpu().view(C, K).long(), imax)
         assert torch.equal(amin.cpu().view(C, K).long(), imin)
         red = red.cpu().view(3, C)
