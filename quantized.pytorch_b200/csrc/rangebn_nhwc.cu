@@ -12,7 +12,7 @@
 
 constexpr int NH_THREADS = 256;
 constexpr int NH_UNROLL = 4;
-constexpr int NH_MAX_SEG = 64;      // row segments per chunk (partials per (chunk, channel))
+constexpr int NH_MAX_SEG = 32;      // row segments per chunk (partials per (chunk, channel))
 
 struct NhwcGeom {
     int64_t R, C;         // rows, channels
@@ -26,7 +26,7 @@ struct NhwcGeom {
 };
 
 template <int VEC>
-static NhwcGeom make_geom(int64_t R, int64_t C, int K) {
+static NhwcGeom make_geom(int64_t R, int64_t C, int K, int max_seg = NH_MAX_SEG) {
     NhwcGeom g;
     g.R = R; g.C = C; g.K = K; g.L = R / K;
     g.tileC = (int)(C < (int64_t)NH_THREADS * VEC ? C : (int64_t)NH_THREADS * VEC);
@@ -34,10 +34,10 @@ static NhwcGeom make_geom(int64_t R, int64_t C, int K) {
     g.RL = NH_THREADS / g.CT;
     int ctiles = (int)((C + g.tileC - 1) / g.tileC);
     // enough CTAs to fill 148 SMs a few times over, each segment at least RL*NH_UNROLL rows
-    int64_t want = (148 * 6 + (int64_t)K * ctiles - 1) / ((int64_t)K * ctiles);
+    int64_t want = (148 * 4 + (int64_t)K * ctiles - 1) / ((int64_t)K * ctiles);
     int64_t max_by_rows = g.L / ((int64_t)g.RL * NH_UNROLL);
     if (want > max_by_rows) want = max_by_rows;
-    if (want > NH_MAX_SEG) want = NH_MAX_SEG;
+    if (want > max_seg) want = max_seg;
     if (want < 1) want = 1;
     g.S = (int)want;
     g.seg_rows = (g.L + g.S - 1) / g.S;
@@ -139,25 +139,38 @@ k_rbn_stats_nhwc(const float* __restrict__ x, NhwcGeom g, float* pmax, float* pm
     }
 }
 
-// merge segments -> per (c,k) extrema + arg, and red[3][C] (fixed order)
-__global__ void k_rbn_stats_nhwc_pack(const float* pmax, const float* pmin, const int32_t* imax, const int32_t* imin,
-                                      const double* psum, int64_t C, int K, int S, int32_t* amax, int32_t* amin,
+// merge the S segment partials of every (chunk k, channel c): one thread each, c fastest (coalesced)
+__global__ void k_rbn_stats_nhwc_merge(const float* pmax, const float* pmin, const int32_t* imax, const int32_t* imin,
+                                       const double* psum, int64_t C, int K, int S, int32_t* amax, int32_t* amin,
+                                       float* cmax, float* cmin, double* csum) {
+    const int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= C * K) return;
+    const int64_t k = t / C, c = t - k * C;
+    ArgV mx{-QB_INF, 0x7fffffff}, mn{QB_INF, 0x7fffffff};
+    double ssum = 0.0;
+    for (int s = 0; s < S; ++s) {
+        const int64_t o = (k * S + s) * C + c;
+        amax_merge(mx, pmax[o], imax[o]);
+        amin_merge(mn, pmin[o], imin[o]);
+        ssum += psum[o];
+    }
+    cmax[t] = mx.v;
+    cmin[t] = mn.v;
+    csum[t] = ssum;
+    if (amax) amax[c * K + k] = mx.i;
+    if (amin) amin[c * K + k] = mn.i;
+}
+
+// red[3][C]: sum over the K chunks in a fixed order
+__global__ void k_rbn_stats_nhwc_pack(const float* cmax, const float* cmin, const double* csum, int64_t C, int K,
                                       double* red) {
     const int64_t c = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (c >= C) return;
     double smax = 0.0, smin = 0.0, ssum = 0.0;
     for (int k = 0; k < K; ++k) {
-        ArgV mx{-QB_INF, 0x7fffffff}, mn{QB_INF, 0x7fffffff};
-        for (int s = 0; s < S; ++s) {
-            const int64_t o = ((int64_t)k * S + s) * C + c;
-            amax_merge(mx, pmax[o], imax[o]);
-            amin_merge(mn, pmin[o], imin[o]);
-            ssum += psum[o];
-        }
-        smax += (double)mx.v;
-        smin += (double)mn.v;
-        if (amax) amax[c * K + k] = mx.i;
-        if (amin) amin[c * K + k] = mn.i;
+        smax += (double)cmax[(int64_t)k * C + c];
+        smin += (double)cmin[(int64_t)k * C + c];
+        ssum += csum[(int64_t)k * C + c];
     }
     red[c] = smax;
     red[C + c] = smin;
@@ -166,7 +179,7 @@ __global__ void k_rbn_stats_nhwc_pack(const float* pmax, const float* pmin, cons
 
 extern "C" size_t qb_rangebn_nhwc_ws_bytes(int64_t C, int num_chunks) {
     if (C < 0 || num_chunks < 0) return 0;
-    return (size_t)C * num_chunks * NH_MAX_SEG * 24;
+    return (size_t)C * num_chunks * (NH_MAX_SEG * 24 + 16);
 }
 
 static size_t nhwc_smem(const NhwcGeom& g, int vec, int per_elem) { return (size_t)g.RL * g.CT * vec * per_elem; }
@@ -192,6 +205,10 @@ extern "C" int qb_rangebn_stats_nhwc(const float* x, int64_t B, int64_t C, int64
     float* pmin = pmax + n;
     int32_t* imax = reinterpret_cast<int32_t*>(pmin + n);
     int32_t* imin = imax + n;
+    const size_t nk = (size_t)num_chunks * C;
+    double* csum = reinterpret_cast<double*>(static_cast<char*>(ws) + (size_t)C * num_chunks * NH_MAX_SEG * 24);
+    float* cmax = reinterpret_cast<float*>(csum + nk);
+    float* cmin = cmax + nk;
     dim3 grid((unsigned)(num_chunks * g.S), (unsigned)((C + g.tileC - 1) / g.tileC));
     cudaStream_t st = qb_stream(stream);
     if (vec4)
@@ -199,8 +216,10 @@ extern "C" int qb_rangebn_stats_nhwc(const float* x, int64_t B, int64_t C, int64
     else
         k_rbn_stats_nhwc<1><<<grid, NH_THREADS, nhwc_smem(g, 1, 24), st>>>(x, g, pmax, pmin, imax, imin, psum);
     QB_LAUNCH_CHECK();
-    k_rbn_stats_nhwc_pack<<<(unsigned)((C + 127) / 128), 128, 0, st>>>(pmax, pmin, imax, imin, psum, C, num_chunks, g.S,
-                                                                      amax, amin, red);
+    k_rbn_stats_nhwc_merge<<<(unsigned)((nk + 127) / 128), 128, 0, st>>>(pmax, pmin, imax, imin, psum, C, num_chunks, g.S,
+                                                                        amax, amin, cmax, cmin, csum);
+    QB_LAUNCH_CHECK();
+    k_rbn_stats_nhwc_pack<<<(unsigned)((C + 127) / 128), 128, 0, st>>>(cmax, cmin, csum, C, num_chunks, red);
     QB_LAUNCH_CHECK();
     return QB_OK;
 }
@@ -237,9 +256,24 @@ k_rbn_apply_nhwc(const float* __restrict__ x, float* out, uint32_t n, FastDiv dC
         const uint32_t e = 4u * i;
         uint32_t c = e - fdiv(e, dC) * dC.d;
         float4 r;
-        if (C4) {            // C % 4 == 0: the quad holds channels c..c+3
-            r.x = nhwc_one<MODE>(v.x, c, p); r.y = nhwc_one<MODE>(v.y, c + 1, p);
-            r.z = nhwc_one<MODE>(v.z, c + 2, p); r.w = nhwc_one<MODE>(v.w, c + 3, p);
+        if (C4) {            // C % 4 == 0: the quad holds channels c..c+3 -> 128-bit parameter loads (L1 resident)
+            const float4 a0 = p.p0 ? __ldg(reinterpret_cast<const float4*>(p.p0 + c)) : make_float4(1.f, 1.f, 1.f, 1.f);
+            const float4 a1 = __ldg(reinterpret_cast<const float4*>(p.p1 + c));
+            const float4 a2 = p.p2 ? __ldg(reinterpret_cast<const float4*>(p.p2 + c)) : make_float4(1.f, 1.f, 1.f, 1.f);
+            if (MODE == 0) {
+                r.x = __fmul_rn(__fsub_rn(v.x, a0.x), a1.x); r.y = __fmul_rn(__fsub_rn(v.y, a0.y), a1.y);
+                r.z = __fmul_rn(__fsub_rn(v.z, a0.z), a1.z); r.w = __fmul_rn(__fsub_rn(v.w, a0.w), a1.w);
+                if (p.p2) { r.x = __fmul_rn(r.x, a2.x); r.y = __fmul_rn(r.y, a2.y); r.z = __fmul_rn(r.z, a2.z); r.w = __fmul_rn(r.w, a2.w); }
+                if (p.p3) {
+                    const float4 a3 = __ldg(reinterpret_cast<const float4*>(p.p3 + c));
+                    r.x = __fadd_rn(r.x, a3.x); r.y = __fadd_rn(r.y, a3.y); r.z = __fadd_rn(r.z, a3.z); r.w = __fadd_rn(r.w, a3.w);
+                }
+            } else {
+                r = v;
+                if (p.p0) { r.x = __fmul_rn(r.x, a0.x); r.y = __fmul_rn(r.y, a0.y); r.z = __fmul_rn(r.z, a0.z); r.w = __fmul_rn(r.w, a0.w); }
+                r.x = __fadd_rn(__fmul_rn(r.x, a1.x), a2.x); r.y = __fadd_rn(__fmul_rn(r.y, a1.y), a2.y);
+                r.z = __fadd_rn(__fmul_rn(r.z, a1.z), a2.z); r.w = __fadd_rn(__fmul_rn(r.w, a1.w), a2.w);
+            }
         } else {
             r.x = nhwc_one<MODE>(v.x, c, p); c = (c + 1 == dC.d) ? 0 : c + 1;
             r.y = nhwc_one<MODE>(v.y, c, p); c = (c + 1 == dC.d) ? 0 : c + 1;
@@ -361,16 +395,20 @@ k_rbn_bwd_reduce_nhwc(const float* __restrict__ gq, const float* __restrict__ x,
     }
 }
 
+// one warp per channel: lanes stride over the segments, fixed-order shuffle tree => deterministic
 __global__ void k_rbn_bwd_pack_nhwc(const double* part, int64_t C, int S, double* sg, double* sgx) {
-    const int64_t c = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    const int64_t c = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+    const int lane = threadIdx.x & 31;
     if (c >= C) return;
     double a = 0.0, b = 0.0;
-    for (int s = 0; s < S; ++s) { a += part[(int64_t)s * C + c]; b += part[((int64_t)S + s) * C + c]; }
-    sg[c] = a;
-    sgx[c] = b;
+    for (int s = lane; s < S; s += 32) { a += part[(int64_t)s * C + c]; b += part[((int64_t)S + s) * C + c]; }
+    a = warp_sum(a);
+    b = warp_sum(b);
+    if (lane == 0) { sg[c] = a; sgx[c] = b; }
 }
 
-extern "C" size_t qb_rangebn_bwd_nhwc_ws_bytes(int64_t C) { return C < 0 ? 0 : (size_t)C * NH_MAX_SEG * 16; }
+constexpr int NH_MAX_SEG_BWD = 1024;
+extern "C" size_t qb_rangebn_bwd_nhwc_ws_bytes(int64_t C) { return C < 0 ? 0 : (size_t)C * NH_MAX_SEG_BWD * 16; }
 
 extern "C" int qb_rangebn_bwd_reduce_nhwc(const float* gq, const float* x, int64_t B, int64_t C, int64_t HW, double* sg,
                                           double* sgx, void* ws, size_t ws_bytes, void* stream) {
@@ -382,7 +420,7 @@ extern "C" int qb_rangebn_bwd_reduce_nhwc(const float* gq, const float* x, int64
     }
     const int64_t R = B * HW;
     const bool vec4 = (C % 4 == 0) && (((reinterpret_cast<uintptr_t>(x) | reinterpret_cast<uintptr_t>(gq)) & 15) == 0);
-    NhwcGeom g = vec4 ? make_geom<4>(R, C, 1) : make_geom<1>(R, C, 1);
+    NhwcGeom g = vec4 ? make_geom<4>(R, C, 1, NH_MAX_SEG_BWD) : make_geom<1>(R, C, 1, NH_MAX_SEG_BWD);
     double* part = static_cast<double*>(ws);
     dim3 grid((unsigned)g.S, (unsigned)((C + g.tileC - 1) / g.tileC));
     cudaStream_t st = qb_stream(stream);
@@ -391,7 +429,7 @@ extern "C" int qb_rangebn_bwd_reduce_nhwc(const float* gq, const float* x, int64
     else
         k_rbn_bwd_reduce_nhwc<1><<<grid, NH_THREADS, nhwc_smem(g, 1, 16), st>>>(gq, x, g, part);
     QB_LAUNCH_CHECK();
-    k_rbn_bwd_pack_nhwc<<<(unsigned)((C + 127) / 128), 128, 0, st>>>(part, C, g.S, sg, sgx);
+    k_rbn_bwd_pack_nhwc<<<(unsigned)((C * 32 + 127) / 128), 128, 0, st>>>(part, C, g.S, sg, sgx);
     QB_LAUNCH_CHECK();
     return QB_OK;
 }
