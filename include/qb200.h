@@ -176,6 +176,20 @@ int qb_rangebn_bwd_apply_nhwc(const float* gq, float* dx, int64_t B, int64_t C, 
                               const float* qscale, const float* qgamma, const float* coef_a, const float* coef_e,
                               const int32_t* amax, const int32_t* amin, void* stream);
 
+/* ---------------------------------------------------------------------------------------------------
+ * Contraction - F.linear / F.conv2d on the dequantised tensors (quantize.py:143-156, 343, 424) as an int8
+ * tcgen05 GEMM on the integer codes with the asymmetric dequantisation folded into the epilogue:
+ *   C[m,n] = sa*sw[n]*SUM_k A[m,k]B[n,k] + sa*lw[n]*a_rowsum[m] + la*sw[n]*b_rowsum[n] + K*la*lw[n] + bias[n]
+ *   A uint8 [M,K] codes of the activation quantizer with device range a_range {la, max} (QB_SCALE_DOUBLE)
+ *   B uint8 [N,K] codes of the per-row weight quantizer with ranges b_row_min/max[N] (QB_SCALE_FLOAT)
+ *   a_rowsum int32[M], b_rowsum int32[N]: row sums of the codes (qb_rowsum_u8)
+ *   bias: fp32 [N] (already fake-quantized) or NULL;  C fp32 [M, ldc]
+ * K must be a multiple of 16 and A, B 16-byte aligned (TMA).                                          */
+int qb_rowsum_u8(const uint8_t* codes, int64_t rows, int64_t cols, int32_t* out, void* stream);
+int qb_gemm_i8(const uint8_t* A, const uint8_t* B, float* C, int64_t M, int64_t N, int64_t K, int64_t ldc,
+               const float* a_range, int a_bits, const float* b_row_min, const float* b_row_max, int b_bits,
+               const int32_t* a_rowsum, const int32_t* b_rowsum, const float* bias, void* stream);
+
 #ifdef __cplusplus
 }
 #endif
