@@ -190,6 +190,23 @@ int qb_gemm_i8(const uint8_t* A, const uint8_t* B, float* C, int64_t M, int64_t 
                const float* a_range, int a_bits, const float* b_row_min, const float* b_row_max, int b_bits,
                const int32_t* a_rowsum, const int32_t* b_rowsum, const float* bias, void* stream);
 
+/* Weight preparation for the implicit GEMM: per-output-channel range + fake-quant of a [Cout, Cin, kh*kw] fp32 weight
+ * (quantize.py:318-334) with, besides the fp32 result wq (same layout; may be NULL), the uint8 codes re-ordered to
+ * [Cout][kh*kw][Cin] (K-major, channel innermost like the NHWC activations) and tapsum[Cout][kh*kw] = SUM_c codes.     */
+int qb_fakequant_rows_conv(const float* w, float* wq, uint8_t* codes_khwc, int32_t* tapsum, int64_t Cout, int64_t Cin,
+                           int taps, int bits, float* row_min, float* row_max, int compute_range, void* stream);
+
+/* QConv2d forward contraction (quantize.py:143-148, 343): int8 tcgen05 implicit GEMM over channels-last codes.
+ *   x_codes uint8 [B,H,W,Cin] (NHWC), a_range device {min,max} of its quantizer; pixsum int32[B*H*W] = SUM_c codes
+ *   w_codes_khwc uint8 [Cout][kh*kw][Cin], per-row ranges, tapsum (from qb_fakequant_rows_conv); bias fp32[Cout] or NULL
+ *   out fp32 [B,Ho,Wo,Cout] (NHWC).  Zero padding is exact for any input range (border-aware epilogue).
+ * Supported: Cin % 32 == 0, Cout % 16 == 0, kh*kw <= 9, stride 1 or 2, dilation 1, groups 1; anything else returns
+ * QB_ERR_UNSUPPORTED (the caller must then use another contraction; nothing is computed).                            */
+int qb_conv_i8_fwd(const uint8_t* x_codes, const uint8_t* w_codes_khwc, float* out, int64_t B, int64_t H, int64_t W,
+                   int64_t Cin, int64_t Cout, int kh, int kw, int stride, int pad, const float* a_range, int a_bits,
+                   const float* w_row_min, const float* w_row_max, int w_bits, const int32_t* pixsum,
+                   const int32_t* tapsum, const float* bias, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

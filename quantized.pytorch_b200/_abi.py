@@ -49,6 +49,9 @@ PROTOTYPES = {
     "qb_rangebn_bwd_apply_nhwc": (_i32, [_p, _p, _i64, _i64, _i64, _i32, _p, _p, _p, _p, _p, _p, _p]),
     "qb_rowsum_u8": (_i32, [_p, _i64, _i64, _p, _p]),
     "qb_gemm_i8": (_i32, [_p, _p, _p, _i64, _i64, _i64, _i64, _p, _i32, _p, _p, _i32, _p, _p, _p, _p]),
+    "qb_fakequant_rows_conv": (_i32, [_p, _p, _p, _p, _i64, _i64, _i32, _i32, _p, _p, _i32, _p]),
+    "qb_conv_i8_fwd": (_i32, [_p, _p, _p, _i64, _i64, _i64, _i64, _i64, _i32, _i32, _i32, _i32, _p, _i32, _p, _p, _i32,
+                              _p, _p, _p, _p]),
 }
 
 _lib = None
@@ -350,4 +353,28 @@ def gemm_i8(a_codes, b_codes, M, N, K, a_range, a_bits, b_row_min, b_row_max, b_
     _run("qb_gemm_i8", M * K + N * K + 4 * M * N, _ptr(a_codes), _ptr(b_codes), _ptr(out), M, N, K, out.stride(0),
          _ptr(a_range), int(a_bits), _ptr(b_row_min), _ptr(b_row_max), int(b_bits), _ptr(a_rowsum), _ptr(b_rowsum),
          _ptr(bias), _stream())
+    return out
+
+
+def fakequant_rows_conv(w, bits, row_min, row_max, compute_range=True, want_y=True):
+    """w [Cout, Cin, kh, kw] contiguous -> (wq | None, codes [Cout, kh*kw, Cin] uint8, tapsum [Cout, kh*kw] int32)."""
+    w = w if w.is_contiguous() else w.contiguous()
+    Cout, Cin = w.shape[0], w.shape[1]
+    taps = w.numel() // (Cout * Cin)
+    wq = torch.empty_like(w) if want_y else None
+    codes = torch.empty(Cout, taps, Cin, dtype=torch.uint8, device=w.device)
+    tapsum = torch.empty(Cout, taps, dtype=torch.int32, device=w.device)
+    _run("qb_fakequant_rows_conv", (4 + (4 if want_y else 0) + 1) * w.numel(), _ptr(w), _ptr(wq), _ptr(codes), _ptr(tapsum),
+         Cout, Cin, taps, int(bits), _ptr(row_min), _ptr(row_max), int(compute_range), _stream())
+    return wq, codes, tapsum
+
+
+def conv_i8_fwd(x_codes, w_codes, B, H, W, Cin, Cout, kh, kw, stride, pad, a_range, a_bits, row_min, row_max, w_bits, pixsum,
+                tapsum, bias=None):
+    """-> fp32 output, logical shape [B, Cout, Ho, Wo] stored channels-last."""
+    Ho, Wo = (H + 2 * pad - kh) // stride + 1, (W + 2 * pad - kw) // stride + 1
+    out = torch.empty((B, Cout, Ho, Wo), dtype=torch.float32, device=x_codes.device, memory_format=torch.channels_last)
+    _run("qb_conv_i8_fwd", B * H * W * Cin + Cout * kh * kw * Cin + 4 * B * Ho * Wo * Cout, _ptr(x_codes), _ptr(w_codes),
+         _ptr(out), B, H, W, Cin, Cout, kh, kw, stride, pad, _ptr(a_range), int(a_bits), _ptr(row_min), _ptr(row_max),
+         int(w_bits), _ptr(pixsum), _ptr(tapsum), _ptr(bias), _stream())
     return out

@@ -158,5 +158,6 @@ qb_encode_tiled_fn qb_get_encode_tiled();   // nullptr (and error set) when the 
 
 // rank-`rank` tiled map over a tensor of `elem_bytes`-sized elements; dims/strides innermost first, strides in bytes
 // for dims 1..rank-1; 128-byte swizzle, zero OOB fill.
+// swizzle_bytes: 128, 64 or 32 (must equal box[0] * element size for the UMMA descriptors used here)
 int qb_make_tmap(CUtensorMap* out, CUtensorMapDataType dt, int rank, const void* base, const uint64_t* dims,
-                 const uint64_t* strides_bytes, const uint32_t* box, const uint32_t* elem_strides);
+                 const uint64_t* strides_bytes, const uint32_t* box, const uint32_t* elem_strides, int swizzle_bytes = 128);

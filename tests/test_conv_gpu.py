@@ -1,0 +1,69 @@
+"""int8 tcgen05 implicit-GEMM convolution (qb_conv_i8_fwd) against fp64 / the reference's fp32 F.conv2d on the same
+fake-quantized tensors: shapes of every ResNet-18 / MobileNet dense conv class, both signs of input range (the
+border-aware zero-padding terms only matter when min != 0)."""
+import numpy as np
+import pytest
+import torch
+import torch.nn.functional as F
+
+pytestmark = pytest.mark.gpu
+DEV = "cuda"
+
+CASES = [  # B, Cin, H, W, Cout, k, stride, pad
+    (2, 64, 56, 56, 64, 3, 1, 1),
+    (3, 64, 56, 56, 128, 3, 2, 1),
+    (2, 64, 56, 56, 128, 1, 2, 0),
+    (4, 128, 28, 28, 128, 3, 1, 1),
+    (4, 128, 28, 28, 256, 3, 2, 1),
+    (5, 256, 14, 14, 256, 3, 1, 1),
+    (5, 256, 14, 14, 512, 1, 2, 0),
+    (7, 512, 7, 7, 512, 3, 1, 1),
+    (2, 32, 112, 112, 64, 1, 1, 0),
+    (2, 32, 20, 150, 48, 3, 1, 1),
+    (1, 96, 9, 11, 80, 3, 2, 1),
+    (3, 64, 8, 8, 64, 3, 1, 1),
+]
+
+
+@pytest.mark.parametrize("case", CASES)
+@pytest.mark.parametrize("relu", [True, False])
+@pytest.mark.parametrize("use_bias", [False, True])
+def test_conv_i8_fwd(lib, case, relu, use_bias):
+    B, Cin, H, W, Cout, k, stride, pad = case
+    gen = torch.Generator().manual_seed(sum(case))
+    x = torch.randn(B, Cin, H, W, generator=gen)
+    if relu:
+        x = x.clamp_min(0)
+    else:
+        x = x + 0.7                                        # min far from zero: padding correction terms are large
+    w = torch.randn(Cout, Cin, k, k, generator=gen) * 0.05
+    bias = torch.randn(Cout, generator=gen) * 0.1 if use_bias else None
+    xd = x.to(DEV).contiguous(memory_format=torch.channels_last)
+    rng = torch.tensor([float(x.min()), float(x.max())], device=DEV)
+    codes = torch.empty((B, Cin, H, W), dtype=torch.uint8, device=DEV).contiguous(memory_format=torch.channels_last)
+    xq = lib.fakequant_affine(xd, 8, range_dev=rng, codes=codes)
+    pixsum = lib.rowsum_u8(codes, B * H * W, Cin)
+    rmin, rmax = torch.empty(Cout, device=DEV), torch.empty(Cout, device=DEV)
+    wq, wcodes, tapsum = lib.fakequant_rows_conv(w.to(DEV), 8, rmin, rmax)
+    # weight prep agrees with the plain row kernel
+    wq2, rmin2, rmax2 = lib.fakequant_rows(w.to(DEV), 8)
+    assert torch.equal(wq, wq2) and torch.equal(rmin, rmin2) and torch.equal(rmax, rmax2)
+    bd = bias.to(DEV) if use_bias else None
+    out = lib.conv_i8_fwd(codes, wcodes, B, H, W, Cin, Cout, k, k, stride, pad, rng, 8, rmin, rmax, 8, pixsum, tapsum, bias=bd)
+    torch.cuda.synchronize()
+    assert out.is_contiguous(memory_format=torch.channels_last)
+    ref64 = F.conv2d(xq.double().cpu(), wq.double().cpu(), bias.double() if use_bias else None, stride, pad)
+    assert out.shape == ref64.shape
+    rel = float((out.cpu().double() - ref64).norm() / ref64.norm())
+    assert rel < 5e-6, rel
+    ref32 = F.conv2d(xq.cpu(), wq.cpu(), bias, stride, pad)       # what the reference computes (fp32, CPU)
+    rel32 = float((out.cpu() - ref32).norm() / ref32.norm())
+    assert rel32 < 1e-4, rel32
+
+
+def test_conv_i8_unsupported_is_an_error(lib):
+    x = torch.zeros((1, 3, 8, 8), dtype=torch.uint8, device=DEV)
+    z = torch.zeros(64, device=DEV)
+    zi = torch.zeros(64, dtype=torch.int32, device=DEV)
+    with pytest.raises(lib.QB200Error):
+        lib.conv_i8_fwd(x, x, 1, 8, 8, 3, 64, 3, 3, 1, 1, z, 8, z, z, 8, zi, zi)
