@@ -184,15 +184,18 @@ int qb_rangebn_bwd_apply_nhwc(const float* gq, float* dx, int64_t B, int64_t C, 
  *   B uint8 [N,K] codes of the per-row weight quantizer with ranges b_row_min/max[N] (QB_SCALE_FLOAT)
  *   a_rowsum int32[M], b_rowsum int32[N]: row sums of the codes (qb_rowsum_u8)
  *   bias: fp32 [N] (already fake-quantized) or NULL;  C fp32 [M, ldc]
+ *   b_offset: 0 if B holds the raw unsigned codes; 2^(b_bits-1) if B holds the CENTRED signed codes q - 2^(b_bits-1)
+ *             that qb_fakequant_rows_conv emits (b_rowsum then sums the centred codes) - better conditioned
  * K must be a multiple of 16 and A, B 16-byte aligned (TMA).                                          */
 int qb_rowsum_u8(const uint8_t* codes, int64_t rows, int64_t cols, int32_t* out, void* stream);
 int qb_gemm_i8(const uint8_t* A, const uint8_t* B, float* C, int64_t M, int64_t N, int64_t K, int64_t ldc,
                const float* a_range, int a_bits, const float* b_row_min, const float* b_row_max, int b_bits,
-               const int32_t* a_rowsum, const int32_t* b_rowsum, const float* bias, void* stream);
+               const int32_t* a_rowsum, const int32_t* b_rowsum, const float* bias, int b_offset, void* stream);
 
 /* Weight preparation for the implicit GEMM: per-output-channel range + fake-quant of a [Cout, Cin, kh*kw] fp32 weight
  * (quantize.py:318-334) with, besides the fp32 result wq (same layout; may be NULL), the uint8 codes re-ordered to
- * [Cout][kh*kw][Cin] (K-major, channel innermost like the NHWC activations) and tapsum[Cout][kh*kw] = SUM_c codes.     */
+ * [Cout][kh*kw][Cin] (K-major, channel innermost like the NHWC activations), CENTRED: int8 q - 2^(bits-1), and
+ * tapsum[Cout][kh*kw] = SUM_c of the centred codes.  With kh*kw == 1 this is the [N,K] operand of qb_gemm_i8.          */
 int qb_fakequant_rows_conv(const float* w, float* wq, uint8_t* codes_khwc, int32_t* tapsum, int64_t Cout, int64_t Cin,
                            int taps, int bits, float* row_min, float* row_max, int compute_range, void* stream);
 

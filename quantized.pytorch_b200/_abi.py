@@ -48,7 +48,7 @@ PROTOTYPES = {
     "qb_rangebn_bwd_reduce_nhwc": (_i32, [_p, _p, _i64, _i64, _i64, _p, _p, _p, _sz, _p]),
     "qb_rangebn_bwd_apply_nhwc": (_i32, [_p, _p, _i64, _i64, _i64, _i32, _p, _p, _p, _p, _p, _p, _p]),
     "qb_rowsum_u8": (_i32, [_p, _i64, _i64, _p, _p]),
-    "qb_gemm_i8": (_i32, [_p, _p, _p, _i64, _i64, _i64, _i64, _p, _i32, _p, _p, _i32, _p, _p, _p, _p]),
+    "qb_gemm_i8": (_i32, [_p, _p, _p, _i64, _i64, _i64, _i64, _p, _i32, _p, _p, _i32, _p, _p, _p, _i32, _p]),
     "qb_fakequant_rows_conv": (_i32, [_p, _p, _p, _p, _i64, _i64, _i32, _i32, _p, _p, _i32, _p]),
     "qb_conv_i8_fwd": (_i32, [_p, _p, _p, _i64, _i64, _i64, _i64, _i64, _i32, _i32, _i32, _i32, _p, _i32, _p, _p, _i32,
                               _p, _p, _p, _p]),
@@ -346,13 +346,13 @@ def rowsum_u8(codes, rows, cols, out=None):
 
 
 def gemm_i8(a_codes, b_codes, M, N, K, a_range, a_bits, b_row_min, b_row_max, b_bits, a_rowsum, b_rowsum, bias=None,
-            out=None):
+            out=None, b_offset=0):
     """out[M,N] fp32 = dequantised (A_hat @ B_hat^T + bias) from uint8 codes (see qb_gemm_i8)."""
     if out is None:
         out = torch.empty(M, N, dtype=torch.float32, device=a_codes.device)
     _run("qb_gemm_i8", M * K + N * K + 4 * M * N, _ptr(a_codes), _ptr(b_codes), _ptr(out), M, N, K, out.stride(0),
          _ptr(a_range), int(a_bits), _ptr(b_row_min), _ptr(b_row_max), int(b_bits), _ptr(a_rowsum), _ptr(b_rowsum),
-         _ptr(bias), _stream())
+         _ptr(bias), int(b_offset), _stream())
     return out
 
 

@@ -113,7 +113,7 @@ k_conv_i8(const __grid_constant__ CUtensorMap tmap_x, const __grid_constant__ CU
             }
         }
     } else if (warp == 1) {
-        constexpr uint32_t idesc = umma_idesc(/*S32*/ 2, /*u8*/ 0, /*u8*/ 0, 128, BN);
+        constexpr uint32_t idesc = umma_idesc(/*S32*/ 2, /*A u8*/ 0, /*B s8*/ 1, 128, BN);
         const int mmas = g.BK / 32;
         for (int kb = 0; kb < num_kb; ++kb) {
             const int s = kb % g.stages;
@@ -141,7 +141,7 @@ k_conv_i8(const __grid_constant__ CUtensorMap tmap_x, const __grid_constant__ CU
             float c1 = 0.f, c2 = 0.f, c3 = 0.f, c4 = 0.f, bs = 0.f;
             if (n < g.Cout) {
                 const QParams pw = make_qparams_f(__ldg(ep.w_row_min + n), __ldg(ep.w_row_max + n), ep.w_bits);
-                const double sw = (double)pw.scale, lw = (double)pw.lo;
+                const double sw = (double)pw.scale, lw = (double)pw.lo + (double)(1 << (ep.w_bits - 1)) * (double)pw.scale;
                 c1 = (float)(sa * sw); c2 = (float)(sa * lw); c3 = (float)(la * sw); c4 = (float)(la * lw);
                 bs = ep.bias ? __ldg(ep.bias + n) : 0.f;
                 for (int tp = 0; tp < taps; ++tp) s_tap[j * taps + tp] = __ldg(ep.tapsum + (int64_t)n * taps + tp);
@@ -216,7 +216,10 @@ k_conv_i8(const __grid_constant__ CUtensorMap tmap_x, const __grid_constant__ CU
 
 // ------------------------------------------------------------------------------------------------
 // weight preparation: per-output-channel range + fake-quant (quantize.py:318-334) and, for the tensor cores, the codes
-// re-ordered to [Cout][kh*kw][Cin] (K-major, channel innermost like the NHWC activations) plus T[n][tap]
+// re-ordered to [Cout][kh*kw][Cin] (K-major, channel innermost like the NHWC activations) plus T[n][tap].
+// The codes are CENTRED: qc = q - 2^(bits-1) as signed int8, w_hat = qc*sw + (lw + 2^(bits-1)*sw).  Weights are nearly
+// symmetric, so the centred offset lw' is ~20x smaller than lw and SUM qa*qc is itself small: the fp32 epilogue then
+// has no large cancelling terms (with raw codes the K=4608 layers lost two digits).
 // ------------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(256)
 k_fq_rows_conv(const float* __restrict__ w, float* wq, uint8_t* codes_khwc, int32_t* tapsum, int Cin, int taps, int bits,
@@ -254,8 +257,9 @@ k_fq_rows_conv(const float* __restrict__ w, float* wq, uint8_t* codes_khwc, int3
         const float q = q_affine_code(src[j], p);
         if (wq) wq[n * cols + j] = q_affine_deq(q, p);
         const int c = j / taps, tp = j - c * taps;
-        if (codes_khwc) codes_khwc[n * cols + (int64_t)tp * Cin + c] = (uint8_t)q;
-        if (tapsum) atomicAdd(&s_tap[tp], (int)q);          // integer: order independent
+        const int qc = (int)q - (1 << (bits - 1));           // centred code in [-2^(b-1), 2^(b-1)): signed int8 operand
+        if (codes_khwc) codes_khwc[n * cols + (int64_t)tp * Cin + c] = (uint8_t)(int8_t)qc;
+        if (tapsum) atomicAdd(&s_tap[tp], qc);               // integer: order independent
     }
     __syncthreads();
     if (tapsum && threadIdx.x < taps) tapsum[n * taps + threadIdx.x] = s_tap[threadIdx.x];

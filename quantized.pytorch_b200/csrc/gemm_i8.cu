@@ -71,6 +71,7 @@ struct GemmEpilogue {
     const int32_t* a_rowsum;   // SUM_k qa[m,k]
     const int32_t* b_rowsum;   // SUM_k qw[n,k]
     const float* bias;         // already fake-quantized bias or nullptr
+    int b_offset;              // 0: B holds raw unsigned codes; 2^(bits-1): B holds centred signed codes (q - offset)
 };
 
 __global__ void __launch_bounds__(G_THREADS, 1)
@@ -119,7 +120,7 @@ k_gemm_i8(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CU
         }
     } else if (warp == 1) {
         // ===== MMA issuer =====
-        constexpr uint32_t idesc = umma_idesc(/*S32*/ 2, /*u8*/ 0, /*u8*/ 0, G_BM, G_BN);
+        const uint32_t idesc = umma_idesc(/*S32*/ 2, /*A u8*/ 0, /*B*/ ep.b_offset ? 1u : 0u, G_BM, G_BN);
         for (int kb = 0; kb < num_kb; ++kb) {
             const int s = kb % G_STAGES;
             const uint32_t ph = (kb / G_STAGES) & 1;
@@ -160,7 +161,7 @@ k_gemm_i8(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CU
                     const int n = n0 + c + j;
                     if (n < N) {
                         const QParams pb = make_qparams_f(__ldg(ep.b_row_min + n), __ldg(ep.b_row_max + n), ep.b_bits);
-                        const double sw = (double)pb.scale, lw = (double)pb.lo;
+                        const double sw = (double)pb.scale, lw = (double)pb.lo + (double)ep.b_offset * (double)pb.scale;
                         double v = sa * sw * (double)(int32_t)r[j] + sa * lw * rs_a + la * sw * (double)__ldg(ep.b_rowsum + n) +
                                    (double)K * la * lw;
                         if (ep.bias) v += (double)__ldg(ep.bias + n);
@@ -207,7 +208,7 @@ extern "C" int qb_rowsum_u8(const uint8_t* codes, int64_t rows, int64_t cols, in
 
 extern "C" int qb_gemm_i8(const uint8_t* A, const uint8_t* B, float* C, int64_t M, int64_t N, int64_t K, int64_t ldc,
                           const float* a_range, int a_bits, const float* b_row_min, const float* b_row_max, int b_bits,
-                          const int32_t* a_rowsum, const int32_t* b_rowsum, const float* bias, void* stream) {
+                          const int32_t* a_rowsum, const int32_t* b_rowsum, const float* bias, int b_offset, void* stream) {
     QB_CHECK_ARG(A && B && C && a_range && b_row_min && b_row_max && a_rowsum && b_rowsum, "qb_gemm_i8: null pointer");
     QB_CHECK_ARG(M > 0 && N > 0 && K > 0 && ldc >= N, "qb_gemm_i8: bad shape M=%lld N=%lld K=%lld ldc=%lld", (long long)M,
                  (long long)N, (long long)K, (long long)ldc);
@@ -229,7 +230,8 @@ extern "C" int qb_gemm_i8(const uint8_t* A, const uint8_t* B, float* C, int64_t 
         QB_CUDA(cudaFuncSetAttribute(k_gemm_i8, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)G_SMEM_BYTES));
         attr_set = true;
     }
-    GemmEpilogue ep{a_range, a_bits, b_row_min, b_row_max, b_bits, a_rowsum, b_rowsum, bias};
+    QB_CHECK_ARG(b_offset == 0 || b_offset == (1 << (b_bits - 1)), "qb_gemm_i8: b_offset must be 0 or 2^(b_bits-1)");
+    GemmEpilogue ep{a_range, a_bits, b_row_min, b_row_max, b_bits, a_rowsum, b_rowsum, bias, b_offset};
     dim3 grid((unsigned)((N + G_BN - 1) / G_BN), (unsigned)((M + G_BM - 1) / G_BM));
     k_gemm_i8<<<grid, G_THREADS, G_SMEM_BYTES, qb_stream(stream)>>>(ta, tb, C, (int)M, (int)N, (int)K, ldc, ep);
     QB_LAUNCH_CHECK();

