@@ -243,31 +243,36 @@ class _QContraction(Function):
     @staticmethod
     def backward(ctx, g):
         x, w = ctx.saved_tensors
-        need_x, need_w, need_b = ctx.needs_input_grad[0], ctx.needs_input_grad[1], ctx.has_bias and ctx.needs_input_grad[2]
-        g = _abi._f32c(g, "grad")
-        gq = None
-        if ctx.grad_mode != "full" and (need_x or ctx.grad_mode == "quant"):
-            gq = _quantize_gradient(g, ctx.bits_grad)
-        g_param = gq if ctx.grad_mode == "quant" else g          # weight / bias branch
-        g_input = g if ctx.grad_mode == "full" else gq           # input branch
-        dx = dw = db = None
-        if ctx.conv is None:
-            if need_x:
-                dx = g_input.matmul(w)
-            if need_w:
-                dw = g_param.reshape(-1, g_param.shape[-1]).t().matmul(x.reshape(-1, x.shape[-1]))
-            if need_b:
-                db = g_param.reshape(-1, g_param.shape[-1]).sum(0)
-        else:
-            stride, padding, dilation, groups = ctx.conv
-            bias_sizes = [w.shape[0]] if ctx.has_bias else None
-            if need_x:
-                dx = torch.ops.aten.convolution_backward(g_input, x, w, bias_sizes, stride, padding, dilation, False,
-                                                         [0, 0], groups, [True, False, False])[0]
-            if need_w or need_b:
-                _, dw, db = torch.ops.aten.convolution_backward(g_param, x, w, bias_sizes, stride, padding, dilation,
-                                                                False, [0, 0], groups, [False, need_w, bool(need_b)])
-        return dx, dw, db, None, None, None
+        return _contraction_backward(ctx, g, x, w) + (None, None, None)
+
+
+def _contraction_backward(ctx, g, x, w):
+    """Gradients of out = op(x, w, b) w.r.t. (x, w, b) under ctx.grad_mode (see _QContraction)."""
+    need_x, need_w, need_b = ctx.needs_input_grad[0], ctx.needs_input_grad[1], ctx.has_bias and ctx.needs_input_grad[2]
+    g = _abi._f32c(g, "grad")
+    gq = None
+    if ctx.grad_mode != "full" and (need_x or ctx.grad_mode == "quant"):
+        gq = _quantize_gradient(g, ctx.bits_grad)
+    g_param = gq if ctx.grad_mode == "quant" else g          # weight / bias branch
+    g_input = g if ctx.grad_mode == "full" else gq           # input branch
+    dx = dw = db = None
+    if ctx.conv is None:
+        if need_x:
+            dx = g_input.matmul(w)
+        if need_w:
+            dw = g_param.reshape(-1, g_param.shape[-1]).t().matmul(x.reshape(-1, x.shape[-1]))
+        if need_b:
+            db = g_param.reshape(-1, g_param.shape[-1]).sum(0)
+    else:
+        stride, padding, dilation, groups = ctx.conv
+        bias_sizes = [w.shape[0]] if ctx.has_bias else None
+        if need_x:
+            dx = torch.ops.aten.convolution_backward(g_input, x, w, bias_sizes, stride, padding, dilation, False,
+                                                     [0, 0], groups, [True, False, False])[0]
+        if need_w or need_b:
+            _, dw, db = torch.ops.aten.convolution_backward(g_param, x, w, bias_sizes, stride, padding, dilation,
+                                                            False, [0, 0], groups, [False, need_w, bool(need_b)])
+    return dx, dw, db
 
 
 def conv2d_biprec(input, weight, bias=None, stride=1, padding=0, dilation=1, groups=1, num_bits_grad=None):
@@ -426,6 +431,10 @@ class _QBase(QuantNode):
         """qweight, qbias as the forward uses them (:317-340)."""
         update = not self.freeze_param_dyn_range
         qweight = _RowsSTE.apply(self.weight, self.weight_min, self.weight_max, self.num_bits_weight, update)
+        return qweight, self._quantized_bias()
+
+    def _quantized_bias(self):
+        update = not self.freeze_param_dyn_range
         qbias = self.bias
         if self.bias is not None and (self.bias_quant or update):
             if update:
@@ -439,7 +448,7 @@ class _QBase(QuantNode):
             else:
                 qbias = UniformQuantize().apply(self.bias, self.num_bits_weight, self.bias_min, self.bias_max, False,
                                                 False, False)
-        return qweight, qbias
+        return qbias
 
     def _grad_mode(self):
         if self.num_bits_grad is None:
@@ -457,6 +466,71 @@ class _QBase(QuantNode):
                                                         False, False, False))
 
 
+# Route QConv2d / QLinear through the int8 tcgen05 kernels whenever the geometry is supported (conv_i8.cu,
+# gemm_i8.cu); otherwise the contraction of the already fake-quantized tensors goes to cuDNN / cuBLAS.
+USE_INT8_TENSOR_CORES = True
+
+
+def _conv_i8_supported(mod, x):
+    if not (USE_INT8_TENSOR_CORES and x.dim() == 4 and mod.groups == 1 and mod.padding_mode == 'zeros'):
+        return False
+    kh, kw = mod.kernel_size
+    st, pd, dl = _pair(mod.stride), _pair(mod.padding), _pair(mod.dilation)
+    return (dl == (1, 1) and st[0] == st[1] and st[0] in (1, 2) and pd[0] == pd[1] and not isinstance(pd[0], str)
+            and kh * kw <= 9 and mod.in_channels % 32 == 0 and mod.out_channels % 16 == 0
+            and mod.num_bits <= 8 and mod.num_bits_weight <= 8
+            and (x.shape[2] + 2 * pd[0] - kh) // st[0] + 1 >= 1 and (x.shape[3] + 2 * pd[1] - kw) // st[1] + 1 >= 1)
+
+
+def _linear_i8_supported(mod, x):
+    return (USE_INT8_TENSOR_CORES and x.dim() == 2 and mod.in_features % 16 == 0 and mod.num_bits <= 8
+            and mod.num_bits_weight <= 8)
+
+
+class _QTensorCoreFn(Function):
+    """QConv2d / QLinear forward on the integer codes: activation fake-quant (codes + fp32 copy for the backward),
+    per-channel weight fake-quant (centred codes), int8 tcgen05 implicit GEMM with the dequantising epilogue.
+    Backward is the same as _QContraction's (straight-through for both quantizers, quantize.py:105-109)."""
+
+    @staticmethod
+    def forward(ctx, input, weight, qbias, mod, rng):
+        conv = isinstance(mod, nn.Conv2d)
+        need_bwd = any(ctx.needs_input_grad[:3])
+        x = _abi._f32c(input, "input")
+        bits_a, bits_w = mod.num_bits, mod.num_bits_weight
+        update = not mod.freeze_param_dyn_range
+        codes = torch.empty_like(x, dtype=torch.uint8)                      # same memory format as x
+        xq = _abi.fakequant_affine(x, bits_a, range_dev=rng, codes=codes, want_y=need_bwd)
+        w4 = weight if conv else weight.view(weight.shape[0], weight.shape[1], 1, 1)
+        wq, wcodes, tapsum = _abi.fakequant_rows_conv(w4, bits_w, mod.weight_min, mod.weight_max, compute_range=update,
+                                                      want_y=need_bwd)
+        if conv:
+            B, Cin, H, W = x.shape
+            kh, kw = mod.kernel_size
+            pixsum = _abi.rowsum_u8(codes, B * H * W, Cin)
+            out = _abi.conv_i8_fwd(codes, wcodes, B, H, W, Cin, mod.out_channels, kh, kw, _pair(mod.stride)[0],
+                                   _pair(mod.padding)[0], rng, bits_a, mod.weight_min, mod.weight_max, bits_w, pixsum, tapsum,
+                                   bias=qbias)
+            ctx.conv = (_pair(mod.stride), _pair(mod.padding), _pair(mod.dilation), mod.groups)
+        else:
+            M, K = x.shape
+            N = mod.out_features
+            rowsum = _abi.rowsum_u8(codes, M, K)
+            out = _abi.gemm_i8(codes, wcodes, M, N, K, rng, bits_a, mod.weight_min, mod.weight_max, bits_w, rowsum,
+                               tapsum, bias=qbias, b_offset=1 << (bits_w - 1))
+            wq = wq.view(N, K) if wq is not None else None
+            ctx.conv = None
+        ctx.bits_grad, ctx.grad_mode, ctx.has_bias = mod.num_bits_grad, mod._grad_mode(), qbias is not None
+        if need_bwd:
+            ctx.save_for_backward(xq, wq)
+        return out
+
+    @staticmethod
+    def backward(ctx, g):
+        x, w = ctx.saved_tensors
+        return _contraction_backward(ctx, g, x, w) + (None, None)
+
+
 class QConv2d(nn.Conv2d, _QBase):
     """quantize.py:271-354."""
 
@@ -470,6 +544,9 @@ class QConv2d(nn.Conv2d, _QBase):
     def forward(self, input):
         if CHANNELS_LAST and input.dim() == 4 and not input.is_contiguous(memory_format=torch.channels_last):
             input = input.contiguous(memory_format=torch.channels_last)      # library-native activation layout
+        if self.enable_quant and _conv_i8_supported(self, input):
+            rng = self.quantize_input.measure(input)
+            return _QTensorCoreFn.apply(input, self.weight, self._quantized_bias(), self, rng)
         input_ = self.quantize_input(input)
         if not self.enable_quant:
             return F.conv2d(input, self.weight, self.bias, self.stride, self.padding, self.dilation, self.groups)
@@ -487,6 +564,9 @@ class QLinear(nn.Linear, _QBase):
         self._init_quant(num_bits, num_bits_weight, num_bits_grad, biprecision, bias_quant, per_channel, bias)
 
     def forward(self, input):
+        if self.enable_quant and _linear_i8_supported(self, input):
+            rng = self.quantize_input.measure(input)
+            return _QTensorCoreFn.apply(input, self.weight, self._quantized_bias(), self, rng)
         input_ = self.quantize_input(input)
         if not self.enable_quant:
             return F.linear(input, self.weight, self.bias)

@@ -253,3 +253,66 @@ def test_resnet20_loss_curve_vs_oracle():
     sd, sr = mod.state_dict(), ref.state_dict()
     for k in ("bn1.quantize_input.running_min", "bn1.quantize_input.running_max", "fc.quantize_input.running_max"):
         np.testing.assert_allclose(sd[k].cpu().numpy(), sr[k].numpy(), rtol=2e-2, atol=1e-3)
+
+
+@pytest.mark.parametrize("kind,cfg,shape", [
+    ("conv", dict(cin=64, cout=64, k=3, stride=1, pad=1, bias=False), (4, 64, 14, 14)),
+    ("conv", dict(cin=64, cout=128, k=3, stride=2, pad=1, bias=True), (4, 64, 14, 14)),
+    ("conv", dict(cin=32, cout=48, k=1, stride=1, pad=0, bias=False), (3, 32, 9, 9)),
+    ("conv", dict(cin=128, cout=256, k=1, stride=2, pad=0, bias=False), (2, 128, 8, 8)),
+    ("lin", dict(cin=512, cout=1000, bias=True), (32, 512)),
+    ("lin", dict(cin=64, cout=10, bias=True), (16, 64)),
+])
+@pytest.mark.parametrize("relu_input", [True, False])
+def test_tensorcore_modules_vs_oracle(kind, cfg, shape, relu_input):
+    """QConv2d / QLinear on the int8 tcgen05 path (geometry supported) against the CPU oracle modules: forward within
+    1e-4 relative L2 of the fp32 reference, bi-precision backward (dW from g, dX from the quantized g) with the same
+    injected noise."""
+    Q = q()
+    gen = torch.Generator().manual_seed(sum(shape) + cfg["cout"])
+
+    def build(ns):
+        if kind == "conv":
+            return ns.QConv2d(cfg["cin"], cfg["cout"], cfg["k"], stride=cfg["stride"], padding=cfg["pad"], bias=cfg["bias"],
+                              num_bits=8, num_bits_weight=8, num_bits_grad=8, biprecision=True)
+        return ns.QLinear(cfg["cin"], cfg["cout"], bias=cfg["bias"], num_bits=8, num_bits_weight=8, num_bits_grad=8,
+                          biprecision=True)
+
+    ref, mod = build(qref_modules).train(), build(Q)
+    with torch.no_grad():
+        ref.weight.copy_(torch.randn(ref.weight.shape, generator=gen) * 0.05)
+        if ref.bias is not None:
+            ref.bias.copy_(torch.randn(ref.bias.shape, generator=gen) * 0.1)
+    mod.load_state_dict(ref.state_dict())
+    mod = mod.to(DEV).train()
+    x = torch.randn(shape, generator=gen)
+    x = x.clamp_min(0) if relu_input else x + 0.5
+    flat = x.view(shape[0], -1)
+    flat[:, 0], flat[:, 1] = float(x.min()), float(x.max())       # identical per-sample extrema: exact batch mean
+    xr = x.clone().requires_grad_()
+    outr = ref(xr)
+    go = torch.randn(outr.shape, generator=gen) * 1e-2
+    noise = torch.rand(outr.shape, generator=gen) - 0.5
+    prev = qref.set_noise_provider(Replay([noise]))
+    try:
+        outr.backward(go)
+    finally:
+        qref.set_noise_provider(prev)
+    xd = x.to(DEV).requires_grad_()
+    from qtorch_b200 import _abi
+    n0 = _abi.LAUNCHES
+    _abi.profile_begin()
+    out = mod(xd)
+    names = [r[0] for r in _abi.profile_end()]
+    assert ("qb_conv_i8_fwd" if kind == "conv" else "qb_gemm_i8") in names, names    # really on the tensor-core path
+    prev = Q.set_noise_provider(CudaReplay([noise]))
+    try:
+        out.backward(go.to(DEV))
+    finally:
+        Q.set_noise_provider(prev)
+    assert rel_l2(out, outr) < 1e-4
+    assert rel_l2(xd.grad, xr.grad) < 1e-4
+    assert rel_l2(mod.weight.grad, ref.weight.grad) < 1e-4
+    if cfg["bias"]:
+        assert rel_l2(mod.bias.grad, ref.bias.grad) < 1e-4
+    assert torch.equal(mod.weight_min.cpu().flatten(), ref.weight_min.detach().flatten())
