@@ -50,6 +50,11 @@ __device__ __forceinline__ uint64_t umma_smem_desc(uint32_t smem_addr, int bk) {
     return d;
 }
 
+// Persistent kernel: gridDim.x CTAs (one per SM) walk the tile list t = blockIdx.x, += gridDim.x; tiles are ordered with
+// the output-channel tile slowest so a CTA's per-channel coefficients rarely change.  Three asynchronous roles:
+//   warp 0   TMA producer: keeps the shared-memory ring full ACROSS tile boundaries
+//   warp 1   MMA issuer  : accumulates tile j into TMEM buffer j&1 (2 x BN columns allocated)
+//   warps 2-5 epilogue   : drain buffer j&1 (tcgen05.ld), dequantise, store - overlapped with the MMAs of tile j+1
 template <int BN>
 __global__ void __launch_bounds__(CV_THREADS, 1)
 k_conv_i8(const __grid_constant__ CUtensorMap tmap_x, const __grid_constant__ CUtensorMap tmap_w, float* __restrict__ out,
@@ -60,12 +65,13 @@ k_conv_i8(const __grid_constant__ CUtensorMap tmap_x, const __grid_constant__ CU
     uint8_t* tail = smem + (size_t)g.stages * stage_bytes;
     uint64_t* full_bar = reinterpret_cast<uint64_t*>(tail);
     uint64_t* empty_bar = full_bar + 8;
-    uint64_t* accum_bar = empty_bar + 8;
-    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(accum_bar + 1);
+    uint64_t* tfull_bar = empty_bar + 8;                       // [2] accumulator buffer ready
+    uint64_t* tempty_bar = tfull_bar + 2;                      // [2] accumulator buffer drained
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty_bar + 2);
     float* s_c1 = reinterpret_cast<float*>(tail + 256);       // sa*sw[n]
-    float* s_c2 = s_c1 + BN;                                   // sa*lw[n]
+    float* s_c2 = s_c1 + BN;                                   // sa*lw'[n]
     float* s_c3 = s_c2 + BN;                                   // la*sw[n]
-    float* s_c4 = s_c3 + BN;                                   // la*lw[n]
+    float* s_c4 = s_c3 + BN;                                   // la*lw'[n]
     float* s_bias = s_c4 + BN;
     int32_t* s_tap = reinterpret_cast<int32_t*>(s_bias + BN);  // [BN][taps]
 
@@ -73,12 +79,10 @@ k_conv_i8(const __grid_constant__ CUtensorMap tmap_x, const __grid_constant__ CU
     const int taps = g.kh * g.kw;
     const int cblocks = g.Cin / g.BK;
     const int num_kb = taps * cblocks;
-    // tile coordinates
-    int t = blockIdx.x;
-    const int tw_i = t % g.tiles_w; t /= g.tiles_w;
-    const int th_i = t % g.tiles_h; t /= g.tiles_h;
-    const int b0 = t * g.TN, ho0 = th_i * g.TH, wo0 = tw_i * g.TW;
-    const int n0 = blockIdx.y * BN;
+    const int tiles_m = g.tiles_w * g.tiles_h * g.tiles_b;
+    const int tiles_n = (g.Cout + BN - 1) / BN;
+    const int total_tiles = tiles_m * tiles_n;
+    constexpr uint32_t TMEM_COLS = 2 * BN;
 
     if (warp == 0 && lane == 0) {
         tma_prefetch_desc(&tmap_x);
@@ -87,131 +91,172 @@ k_conv_i8(const __grid_constant__ CUtensorMap tmap_x, const __grid_constant__ CU
             mbar_init(&full_bar[s], 1);
             mbar_init(&empty_bar[s], 1);
         }
-        mbar_init(accum_bar, 1);
+        for (int i = 0; i < 2; ++i) {
+            mbar_init(&tfull_bar[i], 1);
+            mbar_init(&tempty_bar[i], 4);                      // one arrival per epilogue warp
+        }
         fence_barrier_init();
     }
-    if (warp == 1) tmem_alloc<(uint32_t)BN>(tmem_slot);
+    if (warp == 1) tmem_alloc<TMEM_COLS>(tmem_slot);
     tc_fence_before_sync();
     __syncthreads();
     tc_fence_after_sync();
     const uint32_t tmem_base = *tmem_slot;
 
     if (warp == 0) {
+        // ===== TMA producer =====
         if (elect_one()) {
-            int kb = 0;
-            for (int tap = 0; tap < taps; ++tap) {
-                const int r = tap / g.kw, s_ = tap - r * g.kw;
-                for (int cb = 0; cb < cblocks; ++cb, ++kb) {
-                    const int s = kb % g.stages;
-                    const uint32_t ph = (kb / g.stages) & 1;
-                    mbar_wait(&empty_bar[s], ph ^ 1);
-                    mbar_arrive_expect_tx(&full_bar[s], (uint32_t)(g.TN * g.TH * g.TW * g.BK) + b_bytes);
-                    uint8_t* sa = smem + (size_t)s * stage_bytes;
-                    tma_load_4d(sa, &tmap_x, &full_bar[s], cb * g.BK, wo0 * g.stride - g.pad + s_, ho0 * g.stride - g.pad + r, b0);
-                    tma_load_2d(sa + a_bytes, &tmap_w, &full_bar[s], tap * g.Cin + cb * g.BK, n0);
+            uint32_t it = 0;
+            for (int t = blockIdx.x; t < total_tiles; t += gridDim.x) {
+                const int tn = t / tiles_m;
+                int tm = t - tn * tiles_m;
+                const int tw_i = tm % g.tiles_w; tm /= g.tiles_w;
+                const int th_i = tm % g.tiles_h; tm /= g.tiles_h;
+                const int b0 = tm * g.TN, ho0 = th_i * g.TH, wo0 = tw_i * g.TW, n0 = tn * BN;
+                for (int tap = 0; tap < taps; ++tap) {
+                    const int r = tap / g.kw, s_ = tap - r * g.kw;
+                    for (int cb = 0; cb < cblocks; ++cb, ++it) {
+                        const int s = it % g.stages;
+                        const uint32_t ph = (it / g.stages) & 1;
+                        mbar_wait(&empty_bar[s], ph ^ 1);
+                        mbar_arrive_expect_tx(&full_bar[s], (uint32_t)(g.TN * g.TH * g.TW * g.BK) + b_bytes);
+                        uint8_t* sa = smem + (size_t)s * stage_bytes;
+                        tma_load_4d(sa, &tmap_x, &full_bar[s], cb * g.BK, wo0 * g.stride - g.pad + s_,
+                                    ho0 * g.stride - g.pad + r, b0);
+                        tma_load_2d(sa + a_bytes, &tmap_w, &full_bar[s], tap * g.Cin + cb * g.BK, n0);
+                    }
                 }
             }
         }
     } else if (warp == 1) {
+        // ===== MMA issuer =====
         constexpr uint32_t idesc = umma_idesc(/*S32*/ 2, /*A u8*/ 0, /*B s8*/ 1, 128, BN);
         const int mmas = g.BK / 32;
-        for (int kb = 0; kb < num_kb; ++kb) {
-            const int s = kb % g.stages;
-            const uint32_t ph = (kb / g.stages) & 1;
-            mbar_wait(&full_bar[s], ph);
+        uint32_t it = 0;
+        int j = 0;
+        for (int t = blockIdx.x; t < total_tiles; t += gridDim.x, ++j) {
+            const int buf = j & 1;
+            mbar_wait(&tempty_bar[buf], ((j >> 1) & 1) ^ 1);       // epilogue has drained this buffer (first use passes)
             tc_fence_after_sync();
-            if (elect_one()) {
-                const uint32_t a_addr = smem_u32(smem + (size_t)s * stage_bytes);
-                const uint32_t b_addr = a_addr + a_bytes;
-                for (int k = 0; k < mmas; ++k)
-                    umma_i8(tmem_base, umma_smem_desc(a_addr + k * 32, g.BK), umma_smem_desc(b_addr + k * 32, g.BK), idesc,
-                            (kb | k) != 0);
-                umma_commit(&empty_bar[s]);
-                if (kb == num_kb - 1) umma_commit(accum_bar);
+            const uint32_t d_tmem = tmem_base + (uint32_t)(buf * BN);
+            for (int kb = 0; kb < num_kb; ++kb, ++it) {
+                const int s = it % g.stages;
+                const uint32_t ph = (it / g.stages) & 1;
+                mbar_wait(&full_bar[s], ph);
+                tc_fence_after_sync();
+                if (elect_one()) {
+                    const uint32_t a_addr = smem_u32(smem + (size_t)s * stage_bytes);
+                    const uint32_t b_addr = a_addr + a_bytes;
+                    for (int k = 0; k < mmas; ++k)
+                        umma_i8(d_tmem, umma_smem_desc(a_addr + k * 32, g.BK), umma_smem_desc(b_addr + k * 32, g.BK), idesc,
+                                (kb | k) != 0);
+                    umma_commit(&empty_bar[s]);
+                    if (kb == num_kb - 1) umma_commit(&tfull_bar[buf]);
+                }
+                __syncwarp();
             }
-            __syncwarp();
         }
     } else {
-        // ===== epilogue warps (128 threads): per-channel coefficients into smem while the main loop runs =====
+        // ===== epilogue warps (128 threads) =====
         const int et = threadIdx.x - 64;
+        const int sub = warp & 3;                                   // TMEM lane quarter this warp may access
         const QParams pa = make_qparams_d((double)__ldg(ep.a_range), (double)__ldg(ep.a_range + 1), ep.a_bits);
         const double sa = (double)pa.scale, la = (double)pa.lo;
-        for (int j = et; j < BN; j += 128) {
-            const int n = n0 + j;
-            float c1 = 0.f, c2 = 0.f, c3 = 0.f, c4 = 0.f, bs = 0.f;
-            if (n < g.Cout) {
-                const QParams pw = make_qparams_f(__ldg(ep.w_row_min + n), __ldg(ep.w_row_max + n), ep.w_bits);
-                const double sw = (double)pw.scale, lw = (double)pw.lo + (double)(1 << (ep.w_bits - 1)) * (double)pw.scale;
-                c1 = (float)(sa * sw); c2 = (float)(sa * lw); c3 = (float)(la * sw); c4 = (float)(la * lw);
-                bs = ep.bias ? __ldg(ep.bias + n) : 0.f;
-                for (int tp = 0; tp < taps; ++tp) s_tap[j * taps + tp] = __ldg(ep.tapsum + (int64_t)n * taps + tp);
-            }
-            s_c1[j] = c1; s_c2[j] = c2; s_c3[j] = c3; s_c4[j] = c4; s_bias[j] = bs;
-        }
-        asm volatile("bar.sync 1, 128;" ::: "memory");          // epilogue warps only
-        // this thread's output pixel
-        const int sub = warp & 3;
-        const int i = sub * 32 + lane;
+        const bool need_la = pa.lo != 0.0f;
         const int per_img = g.TH * g.TW;
+        const int i = sub * 32 + lane;
         const int nl = i / per_img, rem = i - nl * per_img;
         const int th = rem / g.TW, tw = rem - th * g.TW;
-        const int b = b0 + nl, ho = ho0 + th, wo = wo0 + tw;
-        const bool valid = (nl < g.TN) && (b < g.B) && (ho < g.Ho) && (wo < g.Wo);
-        float rs_a = 0.f, kvalid = 0.f;
-        uint32_t mask = 0;
-        if (valid) {
-            int cnt = 0, acc = 0;
-            for (int tp = 0; tp < taps; ++tp) {
-                const int r = tp / g.kw, s_ = tp - r * g.kw;
-                const int hi = ho * g.stride - g.pad + r, wi = wo * g.stride - g.pad + s_;
-                if (hi >= 0 && hi < g.H && wi >= 0 && wi < g.W) {
-                    mask |= 1u << tp;
-                    ++cnt;
-                    acc += __ldg(ep.pixsum + ((int64_t)b * g.H + hi) * g.W + wi);
-                }
-            }
-            rs_a = (float)acc;
-            kvalid = (float)(cnt * g.Cin);
-        }
-        const bool need_la = pa.lo != 0.0f;
-        const bool interior = mask == ((1u << taps) - 1u);
-        mbar_wait(accum_bar, 0);
-        tc_fence_after_sync();
-        float* dst = out + (((int64_t)b * g.Ho + ho) * g.Wo + wo) * g.Cout + n0;
-#pragma unroll 1
-        for (int c = 0; c < BN; c += 32) {
-            uint32_t r[32];
-            tmem_ld_32x32(tmem_base + ((uint32_t)(sub * 32) << 16) + (uint32_t)c, r);
-            tmem_ld_wait();
-            if (valid) {
-#pragma unroll
-                for (int j = 0; j < 32; ++j) {
-                    const int jn = c + j;
-                    float v = fmaf(s_c1[jn], (float)(int32_t)r[j], fmaf(s_c2[jn], rs_a, s_bias[jn]));
-                    if (need_la) {
-                        int tsum = 0;
-                        for (int tp = 0; tp < taps; ++tp)
-                            if (interior || ((mask >> tp) & 1u)) tsum += s_tap[jn * taps + tp];
-                        v += fmaf(s_c3[jn], (float)tsum, s_c4[jn] * kvalid);
+        int cur_tn = -1, j = 0;
+        for (int t = blockIdx.x; t < total_tiles; t += gridDim.x, ++j) {
+            const int tn = t / tiles_m;
+            int tm = t - tn * tiles_m;
+            const int tw_i = tm % g.tiles_w; tm /= g.tiles_w;
+            const int th_i = tm % g.tiles_h; tm /= g.tiles_h;
+            const int b0 = tm * g.TN, ho0 = th_i * g.TH, wo0 = tw_i * g.TW, n0 = tn * BN;
+            if (tn != cur_tn) {                                      // per-channel coefficients of this channel tile
+                asm volatile("bar.sync 1, 128;" ::: "memory");      // everyone is done with the previous ones
+                for (int jn = et; jn < BN; jn += 128) {
+                    const int n = n0 + jn;
+                    float c1 = 0.f, c2 = 0.f, c3 = 0.f, c4 = 0.f, bs = 0.f;
+                    if (n < g.Cout) {
+                        const QParams pw = make_qparams_f(__ldg(ep.w_row_min + n), __ldg(ep.w_row_max + n), ep.w_bits);
+                        const double sw = (double)pw.scale,
+                                     lw = (double)pw.lo + (double)(1 << (ep.w_bits - 1)) * (double)pw.scale;
+                        c1 = (float)(sa * sw); c2 = (float)(sa * lw); c3 = (float)(la * sw); c4 = (float)(la * lw);
+                        bs = ep.bias ? __ldg(ep.bias + n) : 0.f;
+                        for (int tp = 0; tp < taps; ++tp) s_tap[jn * taps + tp] = __ldg(ep.tapsum + (int64_t)n * taps + tp);
                     }
-                    r[j] = __float_as_uint(v);
+                    s_c1[jn] = c1; s_c2[jn] = c2; s_c3[jn] = c3; s_c4[jn] = c4; s_bias[jn] = bs;
                 }
-                if (n0 + c + 32 <= g.Cout && (g.Cout & 3) == 0) {
+                asm volatile("bar.sync 1, 128;" ::: "memory");
+                cur_tn = tn;
+            }
+            // this thread's output pixel of the tile
+            const int b = b0 + nl, ho = ho0 + th, wo = wo0 + tw;
+            const bool valid = (nl < g.TN) && (b < g.B) && (ho < g.Ho) && (wo < g.Wo);
+            float rs_a = 0.f, kvalid = 0.f;
+            uint32_t mask = 0;
+            if (valid) {
+                int cnt = 0, acc = 0;
+                for (int tp = 0; tp < taps; ++tp) {
+                    const int r = tp / g.kw, s_ = tp - r * g.kw;
+                    const int hi = ho * g.stride - g.pad + r, wi = wo * g.stride - g.pad + s_;
+                    if (hi >= 0 && hi < g.H && wi >= 0 && wi < g.W) {
+                        mask |= 1u << tp;
+                        ++cnt;
+                        acc += __ldg(ep.pixsum + ((int64_t)b * g.H + hi) * g.W + wi);
+                    }
+                }
+                rs_a = (float)acc;
+                kvalid = (float)(cnt * g.Cin);
+            }
+            const bool interior = mask == ((1u << taps) - 1u);
+            float* dst = out + (((int64_t)b * g.Ho + ho) * g.Wo + wo) * g.Cout + n0;
+            const int buf = j & 1;
+            mbar_wait(&tfull_bar[buf], (j >> 1) & 1);
+            tc_fence_after_sync();
+            const uint32_t t_addr = tmem_base + (uint32_t)(buf * BN) + ((uint32_t)(sub * 32) << 16);
+#pragma unroll 1
+            for (int c = 0; c < BN; c += 32) {
+                uint32_t r[32];
+                tmem_ld_32x32(t_addr + (uint32_t)c, r);
+                tmem_ld_wait();
+                if (c + 32 >= BN) {                                  // last read of this buffer: hand it back to the MMA warp
+                    tc_fence_before_sync();
+                    __syncwarp();
+                    if (lane == 0) mbar_arrive(&tempty_bar[buf]);
+                }
+                if (valid) {
 #pragma unroll
-                    for (int j = 0; j < 32; j += 4)
-                        __stcs(reinterpret_cast<float4*>(dst + c + j),
-                               make_float4(__uint_as_float(r[j]), __uint_as_float(r[j + 1]), __uint_as_float(r[j + 2]),
-                                           __uint_as_float(r[j + 3])));
-                } else {
-                    for (int j = 0; j < 32; ++j)
-                        if (n0 + c + j < g.Cout) dst[c + j] = __uint_as_float(r[j]);
+                    for (int q = 0; q < 32; ++q) {
+                        const int jn = c + q;
+                        float v = fmaf(s_c1[jn], (float)(int32_t)r[q], fmaf(s_c2[jn], rs_a, s_bias[jn]));
+                        if (need_la) {
+                            int tsum = 0;
+                            for (int tp = 0; tp < taps; ++tp)
+                                if (interior || ((mask >> tp) & 1u)) tsum += s_tap[jn * taps + tp];
+                            v += fmaf(s_c3[jn], (float)tsum, s_c4[jn] * kvalid);
+                        }
+                        r[q] = __float_as_uint(v);
+                    }
+                    if (n0 + c + 32 <= g.Cout && (g.Cout & 3) == 0) {
+#pragma unroll
+                        for (int q = 0; q < 32; q += 4)
+                            __stcs(reinterpret_cast<float4*>(dst + c + q),
+                                   make_float4(__uint_as_float(r[q]), __uint_as_float(r[q + 1]), __uint_as_float(r[q + 2]),
+                                               __uint_as_float(r[q + 3])));
+                    } else {
+                        for (int q = 0; q < 32; ++q)
+                            if (n0 + c + q < g.Cout) dst[c + q] = __uint_as_float(r[q]);
+                    }
                 }
             }
         }
     }
     tc_fence_before_sync();
     __syncthreads();
-    if (warp == 1) tmem_dealloc<(uint32_t)BN>(tmem_base);
+    if (warp == 1) tmem_dealloc<TMEM_COLS>(tmem_base);
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -291,7 +336,10 @@ static int launch_conv(const CUtensorMap& tx, const CUtensorMap& tw, float* out,
         QB_CUDA(cudaFuncSetAttribute(k_conv_i8<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
         configured = smem;
     }
-    dim3 grid((unsigned)(g.tiles_w * g.tiles_h * g.tiles_b), (unsigned)((g.Cout + BN - 1) / BN));
+    const int64_t total = (int64_t)g.tiles_w * g.tiles_h * g.tiles_b * ((g.Cout + BN - 1) / BN);
+    int sms = qb_sm_count();
+    if (sms <= 0) sms = 148;
+    const unsigned grid = (unsigned)(total < sms ? total : sms);       // persistent: one CTA per SM
     k_conv_i8<BN><<<grid, CV_THREADS, smem, st>>>(tx, tw, out, g, ep);
     QB_LAUNCH_CHECK();
     return QB_OK;

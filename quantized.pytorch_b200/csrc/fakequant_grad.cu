@@ -191,18 +191,20 @@ __device__ __forceinline__ void sweep_grad(const float* __restrict__ g, float* o
     const int64_t stride = (int64_t)gridDim.x * GQ_THREADS;
     const int64_t tid = (int64_t)blockIdx.x * GQ_THREADS + threadIdx.x;
     if (vec) {
+        // Philox keeps ~40 live registers per quad in flight: 2 quads keep the kernel at 3 CTAs/SM, 4 would halve occupancy
+        constexpr int U = (NOISE == NOISE_PHILOX) ? 2 : GQ_UNROLL;
         const int64_t nquads = n >> 2;
         int64_t i = tid;
-        for (; i + (GQ_UNROLL - 1) * stride < nquads; i += GQ_UNROLL * stride) {
-            float4 v[GQ_UNROLL];
-            int64_t qd[GQ_UNROLL];
+        for (; i + (U - 1) * stride < nquads; i += U * stride) {
+            float4 v[U];
+            int64_t qd[U];
 #pragma unroll
-            for (int u = 0; u < GQ_UNROLL; ++u) {
+            for (int u = 0; u < U; ++u) {
                 qd[u] = REVERSE ? nquads - 1 - (i + u * stride) : i + u * stride;
                 v[u] = __ldcs(reinterpret_cast<const float4*>(g) + qd[u]);
             }
 #pragma unroll
-            for (int u = 0; u < GQ_UNROLL; ++u)
+            for (int u = 0; u < U; ++u)
                 grad_quad<NOISE, WRITE_Y, WRITE_C>(v[u], noise_quad<NOISE>(na, seed, qd[u]), out, codes, qd[u], p);
         }
         for (; i < nquads; i += stride) {
@@ -226,7 +228,7 @@ __device__ __forceinline__ void sweep_grad(const float* __restrict__ g, float* o
 }
 
 template <int NOISE, bool WRITE_Y, bool WRITE_C>
-__global__ void __launch_bounds__(GQ_THREADS)
+__global__ void __launch_bounds__(GQ_THREADS, 3)
 k_fq_grad(const float* __restrict__ g, float* out, uint8_t* codes, int64_t n, int vec, int bits, const float* range_dev,
           double lo, double hi, NoiseArg na) {
     if (range_dev) {
@@ -239,7 +241,7 @@ k_fq_grad(const float* __restrict__ g, float* out, uint8_t* codes, int64_t n, in
 
 // fused: phase 1 min/max, grid sync, phase 2 quantize (cooperative launch: grid <= co-resident CTAs)
 template <int NOISE, bool WRITE_Y, bool WRITE_C>
-__global__ void __launch_bounds__(GQ_THREADS)
+__global__ void __launch_bounds__(GQ_THREADS, 3)
 k_fq_grad_fused(const float* __restrict__ g, float* out, uint8_t* codes, int64_t n, int vec, int bits, float* range_out,
                 NoiseArg na, MinMaxWs* ws) {
     __shared__ float sm[64];

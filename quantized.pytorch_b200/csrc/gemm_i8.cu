@@ -176,7 +176,24 @@ k_gemm_i8(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CU
     if (warp == 1) tmem_dealloc<G_TMEM_COLS>(tmem_base);
 }
 
-// SUM over each row of uint8 codes (the epilogue's correction terms); one warp per row
+// SUM over each row of uint8 codes (the epilogue's correction terms).  Short rows (a pixel's channels): one thread per
+// row - consecutive threads read consecutive rows, so a warp still covers one contiguous span; long rows: one warp per row.
+__device__ __forceinline__ uint32_t sum16(const uint4 v, uint32_t acc) {
+    acc = __dp4a(v.x, 0x01010101u, acc);
+    acc = __dp4a(v.y, 0x01010101u, acc);
+    acc = __dp4a(v.z, 0x01010101u, acc);
+    return __dp4a(v.w, 0x01010101u, acc);
+}
+
+__global__ void __launch_bounds__(256) k_rowsum_u8_thread(const uint8_t* __restrict__ codes, int64_t rows, int cols16, int32_t* out) {
+    const int64_t row = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (row >= rows) return;
+    const uint4* p = reinterpret_cast<const uint4*>(codes + row * (int64_t)cols16 * 16);
+    uint32_t acc = 0;
+    for (int j = 0; j < cols16; ++j) acc = sum16(__ldcs(p + j), acc);
+    out[row] = (int32_t)acc;
+}
+
 __global__ void k_rowsum_u8(const uint8_t* __restrict__ codes, int64_t rows, int64_t cols, int32_t* out) {
     const int64_t row = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     const int lane = threadIdx.x & 31;
@@ -184,13 +201,7 @@ __global__ void k_rowsum_u8(const uint8_t* __restrict__ codes, int64_t rows, int
     const uint8_t* p = codes + row * cols;
     uint32_t acc = 0;
     if ((cols & 15) == 0 && (reinterpret_cast<uintptr_t>(p) & 15) == 0) {
-        for (int64_t j = lane; j < (cols >> 4); j += 32) {
-            const uint4 v = __ldg(reinterpret_cast<const uint4*>(p) + j);
-            acc = __dp4a(v.x, 0x01010101u, acc);
-            acc = __dp4a(v.y, 0x01010101u, acc);
-            acc = __dp4a(v.z, 0x01010101u, acc);
-            acc = __dp4a(v.w, 0x01010101u, acc);
-        }
+        for (int64_t j = lane; j < (cols >> 4); j += 32) acc = sum16(__ldg(reinterpret_cast<const uint4*>(p) + j), acc);
     } else {
         for (int64_t j = lane; j < cols; j += 32) acc += p[j];
     }
@@ -201,7 +212,10 @@ __global__ void k_rowsum_u8(const uint8_t* __restrict__ codes, int64_t rows, int
 
 extern "C" int qb_rowsum_u8(const uint8_t* codes, int64_t rows, int64_t cols, int32_t* out, void* stream) {
     QB_CHECK_ARG(codes && out && rows > 0 && cols > 0, "qb_rowsum_u8: bad arguments");
-    k_rowsum_u8<<<(unsigned)((rows * 32 + 255) / 256), 256, 0, qb_stream(stream)>>>(codes, rows, cols, out);
+    if ((cols & 15) == 0 && cols <= 512 && (reinterpret_cast<uintptr_t>(codes) & 15) == 0)
+        k_rowsum_u8_thread<<<(unsigned)((rows + 255) / 256), 256, 0, qb_stream(stream)>>>(codes, rows, (int)(cols >> 4), out);
+    else
+        k_rowsum_u8<<<(unsigned)((rows * 32 + 255) / 256), 256, 0, qb_stream(stream)>>>(codes, rows, cols, out);
     QB_LAUNCH_CHECK();
     return QB_OK;
 }
