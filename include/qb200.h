@@ -73,6 +73,11 @@ int qb_measure_finalize(const double* stats, float* running_min, float* running_
 int qb_fakequant_affine(const float* x, float* y, uint8_t* codes, int64_t n, int bits, const float* range_dev,
                         double lo, double hi, int scale_mode, void* stream);
 
+/* Self-test hook (no reference counterpart): the quantizers divide by the scale with an FMA sequence that must equal
+ * IEEE division (ATen's div_, quantize.py:90,92); this evaluates that sequence and __fdiv_rn on the same operands
+ * so a test can compare them bit for bit.  a, out_fast, out_ieee: fp32[n].                                          */
+int qb_selftest_div(const float* a, float b, float* out_fast, float* out_ieee, int64_t n, void* stream);
+
 /* Per-row variant for weights - quantize.py:318-323,332-334: row_min/row_max over flatten(1) are
  * computed here (and written out, they are the module's weight_min/weight_max buffers), then each
  * row is quantized with its own QB_SCALE_FLOAT scale.  If compute_range == 0 the given row_min/max

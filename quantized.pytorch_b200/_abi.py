@@ -27,6 +27,7 @@ PROTOTYPES = {
     "qb_measure_stats": (_i32, [_p, _i64, _i64, _p, _p, _sz, _p]),
     "qb_measure_finalize": (_i32, [_p, _p, _p, _p, _p, _p, _dbl, _i32, _i32, _i32, _p, _p]),
     "qb_fakequant_affine": (_i32, [_p, _p, _p, _i64, _i32, _p, _dbl, _dbl, _i32, _p]),
+    "qb_selftest_div": (_i32, [_p, _flt, _p, _p, _i64, _p]),
     "qb_fakequant_rows": (_i32, [_p, _p, _p, _i64, _i64, _i32, _p, _p, _i32, _p]),
     "qb_minmax_ws_bytes": (_sz, []),
     "qb_minmax": (_i32, [_p, _i64, _p, _p, _sz, _p]),
@@ -229,6 +230,14 @@ def minmax(x, range_out=None):
     ws = workspace("minmax", lib.qb_minmax_ws_bytes(), x.device)
     _run("qb_minmax", 4 * x.numel(), _ptr(x), x.numel(), _ptr(range_out), _ptr(ws), ws.numel(), _stream())
     return range_out
+
+
+def selftest_div(a, b):
+    """-> (qb_div(a, b), __fdiv_rn(a, b)) elementwise; see include/qb200.h."""
+    a = _f32c(a, "a")
+    fast, ieee = torch.empty_like(a), torch.empty_like(a)
+    _run("qb_selftest_div", 0, _ptr(a), float(b), _ptr(fast), _ptr(ieee), a.numel(), _stream())
+    return fast, ieee
 
 
 def fakequant_grad(g, bits, range_dev=None, lo=0.0, hi=0.0, noise=None, stochastic=True, seed=0, offset=0,

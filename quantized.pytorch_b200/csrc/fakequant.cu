@@ -11,7 +11,7 @@
 namespace cg = cooperative_groups;
 
 constexpr int FQ_THREADS = 256;
-constexpr int FQ_UNROLL = 4;  // independent 128-bit loads in flight per thread
+constexpr int FQ_U = 2;      // independent 256-bit loads in flight per thread
 
 struct RangeArg {
     const float* dev;  // device {min,max} or nullptr
@@ -27,47 +27,87 @@ __device__ __forceinline__ QParams load_qparams(const RangeArg& r, int bits, int
     return make_qparams(lo, hi, bits, mode);
 }
 
-__device__ __forceinline__ uchar4 pack_codes(float4 q) {
-    return make_uchar4((unsigned char)q.x, (unsigned char)q.y, (unsigned char)q.z, (unsigned char)q.w);
+// ------------------------------------------------------------------------------------------------
+// min-anchored affine (A1): thread = one 32-byte octet per step, FQ_U octets in flight
+// ------------------------------------------------------------------------------------------------
+template <bool WRITE_Y, bool WRITE_C, bool SMALL>
+__device__ __forceinline__ void affine_octet(const F8& v, float* y, uint8_t* codes, int64_t oct, const QParams& p,
+                                             const Divisor& d) {
+    float a[8];
+    bool ok = d.fast;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+        a[j] = __fsub_rn(v.v[j], p.lo);
+        ok = ok && qb_div_ok(a[j]);
+    }
+    float t[8];
+    if (ok) {
+#pragma unroll
+        for (int j = 0; j < 8; ++j) t[j] = qb_div_fast(a[j], d);
+    } else {
+#pragma unroll
+        for (int j = 0; j < 8; ++j) t[j] = __fdiv_rn(a[j], d.b);
+    }
+    F8 o;
+    uint32_t c[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+        const float s = fminf(fmaxf(t[j], 0.0f), p.qmax);
+        float q;
+        if (SMALL) {
+            const float m = __fadd_rn(s, QB_MAGIC);
+            c[j] = __float_as_uint(m);
+            q = __fsub_rn(m, QB_MAGIC);
+        } else {
+            q = rintf(s);
+            c[j] = (uint32_t)q;
+        }
+        o.v[j] = q_affine_deq(q, p);
+    }
+    if (WRITE_Y) st256_stream(y + 8 * oct, o);
+    if (WRITE_C) {
+        uint2 pk;
+        pk.x = __byte_perm(__byte_perm(c[0], c[1], 0x0040), __byte_perm(c[2], c[3], 0x0040), 0x5410);
+        pk.y = __byte_perm(__byte_perm(c[4], c[5], 0x0040), __byte_perm(c[6], c[7], 0x0040), 0x5410);
+        reinterpret_cast<uint2*>(codes)[oct] = pk;
+    }
 }
 
-// ------------------------------------------------------------------------------------------------
-// min-anchored affine (A1)
-// ------------------------------------------------------------------------------------------------
-template <bool WRITE_Y, bool WRITE_C>
-__device__ __forceinline__ void affine_quad(const float4 v, float* y, uint8_t* codes, int64_t quad, const QParams& p) {
-    float4 q = make_float4(q_affine_code(v.x, p), q_affine_code(v.y, p), q_affine_code(v.z, p), q_affine_code(v.w, p));
-    if (WRITE_Y)
-        st_stream4(y + 4 * quad, make_float4(q_affine_deq(q.x, p), q_affine_deq(q.y, p), q_affine_deq(q.z, p),
-                                             q_affine_deq(q.w, p)));
-    if (WRITE_C) reinterpret_cast<uchar4*>(codes)[quad] = pack_codes(q);
-}
-
-template <bool WRITE_Y, bool WRITE_C>
-__global__ void __launch_bounds__(FQ_THREADS)
-k_fq_affine_v4(const float* __restrict__ x, float* y, uint8_t* codes, int64_t n, int bits, RangeArg r, int mode) {
-    const QParams p = load_qparams(r, bits, mode);
-    const int64_t nquads = n >> 2;
+template <bool WRITE_Y, bool WRITE_C, bool SMALL>
+__device__ __forceinline__ void affine_sweep(const float* __restrict__ x, float* y, uint8_t* codes, int64_t n,
+                                             const QParams& p, const Divisor& d) {
+    const int64_t noct = n >> 3;
     const int64_t stride = (int64_t)gridDim.x * FQ_THREADS;
     int64_t i = (int64_t)blockIdx.x * FQ_THREADS + threadIdx.x;
-    for (; i + (FQ_UNROLL - 1) * stride < nquads; i += FQ_UNROLL * stride) {
-        float4 v[FQ_UNROLL];
+    for (; i + (FQ_U - 1) * stride < noct; i += FQ_U * stride) {
+        F8 v[FQ_U];
 #pragma unroll
-        for (int u = 0; u < FQ_UNROLL; ++u) v[u] = ld_stream4(x + 4 * (i + u * stride));
+        for (int u = 0; u < FQ_U; ++u) v[u] = ld256_stream(x + 8 * (i + u * stride));
 #pragma unroll
-        for (int u = 0; u < FQ_UNROLL; ++u) affine_quad<WRITE_Y, WRITE_C>(v[u], y, codes, i + u * stride, p);
+        for (int u = 0; u < FQ_U; ++u) affine_octet<WRITE_Y, WRITE_C, SMALL>(v[u], y, codes, i + u * stride, p, d);
     }
-    for (; i < nquads; i += stride) affine_quad<WRITE_Y, WRITE_C>(ld_stream4(x + 4 * i), y, codes, i, p);
-    // n % 4 tail
-    if (blockIdx.x == 0 && threadIdx.x < (n & 3)) {
-        int64_t e = (nquads << 2) + threadIdx.x;
-        float q = q_affine_code(x[e], p);
+    for (; i < noct; i += stride) affine_octet<WRITE_Y, WRITE_C, SMALL>(ld256_stream(x + 8 * i), y, codes, i, p, d);
+    // n % 8 tail
+    if (blockIdx.x == 0 && threadIdx.x < (n & 7)) {
+        const int64_t e = (noct << 3) + threadIdx.x;
+        const float q = q_affine_code(x[e], p, d);
         if (WRITE_Y) y[e] = q_affine_deq(q, p);
         if (WRITE_C) codes[e] = (uint8_t)q;
     }
 }
 
-// scalar path for pointers that are not 16-byte aligned (views into larger tensors)
+template <bool WRITE_Y, bool WRITE_C>
+__global__ void __launch_bounds__(FQ_THREADS, 4)
+k_fq_affine_v8(const float* __restrict__ x, float* y, uint8_t* codes, int64_t n, int bits, RangeArg r, int mode) {
+    const QParams p = load_qparams(r, bits, mode);
+    const Divisor d = make_divisor(p.scale);
+    if (p.qmax < 4194304.0f)
+        affine_sweep<WRITE_Y, WRITE_C, true>(x, y, codes, n, p, d);
+    else
+        affine_sweep<WRITE_Y, WRITE_C, false>(x, y, codes, n, p, d);
+}
+
+// scalar path for pointers that are not 32-byte aligned (views into larger tensors)
 __global__ void __launch_bounds__(FQ_THREADS)
 k_fq_affine_scalar(const float* __restrict__ x, float* y, uint8_t* codes, int64_t n, int bits, RangeArg r, int mode) {
     const QParams p = load_qparams(r, bits, mode);
@@ -100,15 +140,15 @@ extern "C" int qb_fakequant_affine(const float* x, float* y, uint8_t* codes, int
                  scale_mode);
     RangeArg r{range_dev, lo, hi};
     cudaStream_t st = qb_stream(stream);
-    const bool vec = aligned(x, 16) && (!y || aligned(y, 16)) && (!codes || aligned(codes, 4));
+    const bool vec = aligned(x, 32) && (!y || aligned(y, 32)) && (!codes || aligned(codes, 8));
     if (vec) {
-        int grid = fq_grid(n >> 2, 8);
+        int grid = fq_grid(n >> 3, 4);
         if (y && codes)
-            k_fq_affine_v4<true, true><<<grid, FQ_THREADS, 0, st>>>(x, y, codes, n, bits, r, scale_mode);
+            k_fq_affine_v8<true, true><<<grid, FQ_THREADS, 0, st>>>(x, y, codes, n, bits, r, scale_mode);
         else if (y)
-            k_fq_affine_v4<true, false><<<grid, FQ_THREADS, 0, st>>>(x, y, codes, n, bits, r, scale_mode);
+            k_fq_affine_v8<true, false><<<grid, FQ_THREADS, 0, st>>>(x, y, codes, n, bits, r, scale_mode);
         else
-            k_fq_affine_v4<false, true><<<grid, FQ_THREADS, 0, st>>>(x, y, codes, n, bits, r, scale_mode);
+            k_fq_affine_v8<false, true><<<grid, FQ_THREADS, 0, st>>>(x, y, codes, n, bits, r, scale_mode);
     } else {
         k_fq_affine_scalar<<<fq_grid(n, 8), FQ_THREADS, 0, st>>>(x, y, codes, n, bits, r, scale_mode);
     }
@@ -182,6 +222,24 @@ extern "C" int qb_fakequant_rows(const float* w, float* wq, uint8_t* codes, int6
     QB_CHECK_ARG(rows <= 2147483647LL, "qb_fakequant_rows: too many rows");
     k_fq_rows<<<(unsigned)rows, ROW_THREADS, 0, qb_stream(stream)>>>(w, wq, codes, cols, bits, row_min, row_max,
                                                                     compute_range);
+    QB_LAUNCH_CHECK();
+    return QB_OK;
+}
+
+// ------------------------------------------------------------------------------------------------
+// self-test hook: qb_div (the FMA sequence every quantizer uses) next to __fdiv_rn on the same operands
+// ------------------------------------------------------------------------------------------------
+__global__ void k_selftest_div(const float* __restrict__ a, float b, float* out_fast, float* out_ieee, int64_t n) {
+    const Divisor d = make_divisor(b);
+    for (int64_t e = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; e < n; e += (int64_t)gridDim.x * blockDim.x) {
+        out_fast[e] = qb_div(a[e], d);
+        out_ieee[e] = __fdiv_rn(a[e], b);
+    }
+}
+
+extern "C" int qb_selftest_div(const float* a, float b, float* out_fast, float* out_ieee, int64_t n, void* stream) {
+    QB_CHECK_ARG(a && out_fast && out_ieee && n > 0, "qb_selftest_div: null pointer or n<=0");
+    k_selftest_div<<<fq_grid(n, 8), FQ_THREADS, 0, qb_stream(stream)>>>(a, b, out_fast, out_ieee, n);
     QB_LAUNCH_CHECK();
     return QB_OK;
 }

@@ -11,7 +11,8 @@
 namespace cg = cooperative_groups;
 
 constexpr int GQ_THREADS = 256;
-constexpr int GQ_UNROLL = 4;
+constexpr int GQ_U = 2;              // 32-byte octets in flight per thread in the quantizing sweep
+constexpr int MM_U = 4;              // ... in the min/max sweep (no stores, few registers)
 constexpr int MM_MAX_BLOCKS = 4096;  // partial slots in the workspace
 
 // workspace layout: float partial_min[MM_MAX_BLOCKS], float partial_max[MM_MAX_BLOCKS], uint32 counter
@@ -28,7 +29,7 @@ enum { NOISE_NONE = 0, NOISE_INJECT = 1, NOISE_PHILOX = 2 };
 
 struct NoiseArg {
     const float* inject;       // NOISE_INJECT
-    uint64_t seed, offset;     // NOISE_PHILOX: element e uses lane (e+offset)&3 of philox(seed', (e+offset)>>2)
+    uint64_t seed, offset;     // NOISE_PHILOX: element e uses lane (e+offset)&7 of philox(seed', (e+offset)>>3)
     const uint64_t* step_dev;  // optional device step counter mixed into the seed (CUDA-graph replays)
 };
 
@@ -53,40 +54,37 @@ __device__ __forceinline__ void block_reduce_minmax(float& mn, float& mx, float*
     mx = warp_max(l < nw ? sm[32 + l] : -QB_INF);
 }
 
-// per-thread min/max over a grid-strided sweep of n floats (vector body when aligned, scalar tail)
-template <bool STREAM>
+__device__ __forceinline__ void octet_minmax(const F8& v, float& mn, float& mx) {
+    const float a = fminf(fminf(v.v[0], v.v[1]), fminf(v.v[2], v.v[3])), b = fminf(fminf(v.v[4], v.v[5]), fminf(v.v[6], v.v[7]));
+    const float c = fmaxf(fmaxf(v.v[0], v.v[1]), fmaxf(v.v[2], v.v[3])), d = fmaxf(fmaxf(v.v[4], v.v[5]), fmaxf(v.v[6], v.v[7]));
+    mn = fminf(mn, fminf(a, b));
+    mx = fmaxf(mx, fmaxf(c, d));
+}
+
+// per-thread min/max over a grid-strided sweep of n floats (256-bit body when 32-byte aligned, scalar tail).
+// Default cache policy on purpose: the fused kernel wants these lines to stay in L2 for its second pass.
 __device__ __forceinline__ void sweep_minmax(const float* __restrict__ x, int64_t n, bool vec, float& mn, float& mx) {
     const int64_t stride = (int64_t)gridDim.x * GQ_THREADS;
     const int64_t tid = (int64_t)blockIdx.x * GQ_THREADS + threadIdx.x;
     if (vec) {
-        const int64_t nquads = n >> 2;
+        const int64_t noct = n >> 3;
         int64_t i = tid;
-        for (; i + (GQ_UNROLL - 1) * stride < nquads; i += GQ_UNROLL * stride) {
-            float4 v[GQ_UNROLL];
+        for (; i + (MM_U - 1) * stride < noct; i += MM_U * stride) {
+            F8 v[MM_U];
 #pragma unroll
-            for (int u = 0; u < GQ_UNROLL; ++u) {
-                const float4* p = reinterpret_cast<const float4*>(x) + (i + u * stride);
-                v[u] = STREAM ? __ldcs(p) : __ldg(p);
-            }
+            for (int u = 0; u < MM_U; ++u) v[u] = ld256_keep(x + 8 * (i + u * stride));
 #pragma unroll
-            for (int u = 0; u < GQ_UNROLL; ++u) {
-                mn = fminf(fminf(mn, fminf(v[u].x, v[u].y)), fminf(v[u].z, v[u].w));
-                mx = fmaxf(fmaxf(mx, fmaxf(v[u].x, v[u].y)), fmaxf(v[u].z, v[u].w));
-            }
+            for (int u = 0; u < MM_U; ++u) octet_minmax(v[u], mn, mx);
         }
-        for (; i < nquads; i += stride) {
-            float4 v = __ldg(reinterpret_cast<const float4*>(x) + i);
-            mn = fminf(fminf(mn, fminf(v.x, v.y)), fminf(v.z, v.w));
-            mx = fmaxf(fmaxf(mx, fmaxf(v.x, v.y)), fmaxf(v.z, v.w));
-        }
-        if (tid < (n & 3)) {
-            float v = x[(nquads << 2) + tid];
+        for (; i < noct; i += stride) octet_minmax(ld256_keep(x + 8 * i), mn, mx);
+        if (tid < (n & 7)) {
+            const float v = x[(noct << 3) + tid];
             mn = fminf(mn, v);
             mx = fmaxf(mx, v);
         }
     } else {
         for (int64_t e = tid; e < n; e += stride) {
-            float v = x[e];
+            const float v = x[e];
             mn = fminf(mn, v);
             mx = fmaxf(mx, v);
         }
@@ -99,7 +97,7 @@ k_minmax(const float* __restrict__ x, int64_t n, int vec, float* range_out, MinM
     __shared__ float sm[64];
     __shared__ bool last;
     float mn = QB_INF, mx = -QB_INF;
-    sweep_minmax<false>(x, n, vec != 0, mn, mx);
+    sweep_minmax(x, n, vec != 0, mn, mx);
     block_reduce_minmax(mn, mx, sm);
     if (threadIdx.x == 0) {
         ws->pmin[blockIdx.x] = mn;
@@ -125,7 +123,7 @@ k_minmax(const float* __restrict__ x, int64_t n, int vec, float* range_out, MinM
     }
 }
 
-static bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; }
+static bool aligned32(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 31) == 0; }
 
 static int gq_grid(int64_t items, int per_sm) {
     int sms = qb_sm_count();
@@ -144,8 +142,8 @@ extern "C" int qb_minmax(const float* x, int64_t n, float* range_out, void* ws, 
         qb_set_error("qb_minmax: workspace %zu < %zu bytes", ws_bytes, sizeof(MinMaxWs));
         return QB_ERR_WORKSPACE;
     }
-    const int vec = aligned16(x);
-    int grid = gq_grid(vec ? (n >> 2) / GQ_UNROLL : n / GQ_UNROLL, 8);
+    const int vec = aligned32(x);
+    int grid = gq_grid(vec ? (n >> 3) / MM_U : n / MM_U, 8);
     k_minmax<<<grid, GQ_THREADS, 0, qb_stream(stream)>>>(x, n, vec, range_out, static_cast<MinMaxWs*>(ws));
     QB_LAUNCH_CHECK();
     return QB_OK;
@@ -154,99 +152,145 @@ extern "C" int qb_minmax(const float* x, int64_t n, float* range_out, void* ws, 
 // ------------------------------------------------------------------------------------------------
 // zero-point stochastic quantizer (A2), range given
 // ------------------------------------------------------------------------------------------------
-template <int NOISE>
-__device__ __forceinline__ float4 noise_quad(const NoiseArg& a, uint64_t seed, int64_t quad) {
-    if (NOISE == NOISE_INJECT) return __ldcs(reinterpret_cast<const float4*>(a.inject) + quad);
-    if (NOISE == NOISE_PHILOX) return philox_noise4(seed, (uint64_t)quad + (a.offset >> 2));
-    return make_float4(0.f, 0.f, 0.f, 0.f);
+struct GradQ {          // grid-uniform quantizer state
+    QParams p;
+    Divisor d;
+};
+__device__ __forceinline__ GradQ make_gradq(double lo, double hi, int bits) {
+    GradQ q;
+    q.p = make_qparams_d(lo, hi, bits);
+    q.d = make_divisor(q.p.scale);
+    return q;
 }
+
 template <int NOISE>
 __device__ __forceinline__ float noise_elem(const NoiseArg& a, uint64_t seed, int64_t e) {
     if (NOISE == NOISE_INJECT) return a.inject[e];
-    if (NOISE == NOISE_PHILOX) {
-        uint64_t ge = (uint64_t)e + a.offset;
-        float4 r = philox_noise4(seed, ge >> 2);
-        int l = (int)(ge & 3);
-        return l == 0 ? r.x : l == 1 ? r.y : l == 2 ? r.z : r.w;
-    }
+    if (NOISE == NOISE_PHILOX) return philox_noise1(seed, (uint64_t)e + a.offset);
     return 0.f;
 }
 
 template <int NOISE, bool WRITE_Y, bool WRITE_C>
-__device__ __forceinline__ void grad_quad(float4 v, float4 u, float* out, uint8_t* codes, int64_t quad, const QParams& p) {
-    float4 q = make_float4(q_zp_code(v.x, u.x, p), q_zp_code(v.y, u.y, p), q_zp_code(v.z, u.z, p), q_zp_code(v.w, u.w, p));
-    if (WRITE_Y)
-        st_stream4(out + 4 * quad, make_float4(q_zp_deq(q.x, p), q_zp_deq(q.y, p), q_zp_deq(q.z, p), q_zp_deq(q.w, p)));
-    if (WRITE_C)
-        reinterpret_cast<uchar4*>(codes)[quad] =
-            make_uchar4((unsigned char)q.x, (unsigned char)q.y, (unsigned char)q.z, (unsigned char)q.w);
+__device__ __forceinline__ void grad_elem(const float* g, float* out, uint8_t* codes, int64_t e, const GradQ& Q,
+                                          const NoiseArg& na, uint64_t seed) {
+    float t = __fadd_rn(qb_div(g[e], Q.d), Q.p.zp);
+    if (NOISE != NOISE_NONE) t = __fadd_rn(t, noise_elem<NOISE>(na, seed, e));
+    const float q = qb_rne(fminf(fmaxf(t, 0.0f), Q.p.qmax), Q.p);
+    if (WRITE_Y) out[e] = q_zp_deq(q, Q.p);
+    if (WRITE_C) codes[e] = (uint8_t)q;
+}
+
+// one 32-byte octet: 8 quotients, zero point, noise, clamp, round, dequantize.  SMALL (qmax < 2^22): rounding and the
+// integer code both come out of one magic-number add (no FRND / F2I on the conversion pipe).
+template <int NOISE, bool WRITE_Y, bool WRITE_C, bool SMALL>
+__device__ __forceinline__ void grad_octet(const F8& v, float* out, uint8_t* codes, int64_t oct, const GradQ& Q,
+                                           const NoiseArg& na, uint64_t seed) {
+    float u[8];
+    if (NOISE == NOISE_INJECT) {
+        const F8 w = ld256_stream(na.inject + 8 * oct);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) u[j] = w.v[j];
+    } else if (NOISE == NOISE_PHILOX) {
+        philox_noise8(seed, (uint64_t)oct + (na.offset >> 3), u);
+    }
+    bool ok = Q.d.fast;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) ok = ok && qb_div_ok(v.v[j]);
+    float t[8];
+    if (ok) {
+#pragma unroll
+        for (int j = 0; j < 8; ++j) t[j] = qb_div_fast(v.v[j], Q.d);
+    } else {
+#pragma unroll
+        for (int j = 0; j < 8; ++j) t[j] = __fdiv_rn(v.v[j], Q.d.b);
+    }
+    F8 y;
+    uint32_t c[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+        float s = __fadd_rn(t[j], Q.p.zp);
+        if (NOISE != NOISE_NONE) s = __fadd_rn(s, u[j]);
+        s = fminf(fmaxf(s, 0.0f), Q.p.qmax);
+        float q;
+        if (SMALL) {
+            const float m = __fadd_rn(s, QB_MAGIC);
+            c[j] = __float_as_uint(m);                       // low byte = the code (bits <= 8 whenever codes are written)
+            q = __fsub_rn(m, QB_MAGIC);
+        } else {
+            q = rintf(s);
+            c[j] = (uint32_t)q;
+        }
+        y.v[j] = q_zp_deq(q, Q.p);
+    }
+    if (WRITE_Y) st256_stream(out + 8 * oct, y);
+    if (WRITE_C) {
+        uint2 pk;
+        pk.x = __byte_perm(__byte_perm(c[0], c[1], 0x0040), __byte_perm(c[2], c[3], 0x0040), 0x5410);
+        pk.y = __byte_perm(__byte_perm(c[4], c[5], 0x0040), __byte_perm(c[6], c[7], 0x0040), 0x5410);
+        reinterpret_cast<uint2*>(codes)[oct] = pk;
+    }
 }
 
 // Body shared by the given-range kernel and phase 2 of the fused kernel.  REVERSE sweeps the tensor from
 // its end so that the fused kernel's second read starts with the lines its first read left in L2.
-template <int NOISE, bool WRITE_Y, bool WRITE_C, bool REVERSE>
-__device__ __forceinline__ void sweep_grad(const float* __restrict__ g, float* out, uint8_t* codes, int64_t n, bool vec,
-                                           const QParams& p, const NoiseArg& na) {
+template <int NOISE, bool WRITE_Y, bool WRITE_C, bool REVERSE, bool SMALL>
+__device__ __forceinline__ void sweep_grad_impl(const float* __restrict__ g, float* out, uint8_t* codes, int64_t n, bool vec,
+                                                const GradQ& Q, const NoiseArg& na) {
     const uint64_t seed = effective_seed(na);
     const int64_t stride = (int64_t)gridDim.x * GQ_THREADS;
     const int64_t tid = (int64_t)blockIdx.x * GQ_THREADS + threadIdx.x;
     if (vec) {
-        // Philox keeps ~40 live registers per quad in flight: 2 quads keep the kernel at 3 CTAs/SM, 4 would halve occupancy
-        constexpr int U = (NOISE == NOISE_PHILOX) ? 2 : GQ_UNROLL;
-        const int64_t nquads = n >> 2;
+        const int64_t noct = n >> 3;
         int64_t i = tid;
-        for (; i + (U - 1) * stride < nquads; i += U * stride) {
-            float4 v[U];
-            int64_t qd[U];
+        for (; i + (GQ_U - 1) * stride < noct; i += GQ_U * stride) {
+            F8 v[GQ_U];
+            int64_t od[GQ_U];
 #pragma unroll
-            for (int u = 0; u < U; ++u) {
-                qd[u] = REVERSE ? nquads - 1 - (i + u * stride) : i + u * stride;
-                v[u] = __ldcs(reinterpret_cast<const float4*>(g) + qd[u]);
+            for (int u = 0; u < GQ_U; ++u) {
+                od[u] = REVERSE ? noct - 1 - (i + u * stride) : i + u * stride;
+                v[u] = ld256_stream(g + 8 * od[u]);
             }
 #pragma unroll
-            for (int u = 0; u < U; ++u)
-                grad_quad<NOISE, WRITE_Y, WRITE_C>(v[u], noise_quad<NOISE>(na, seed, qd[u]), out, codes, qd[u], p);
+            for (int u = 0; u < GQ_U; ++u) grad_octet<NOISE, WRITE_Y, WRITE_C, SMALL>(v[u], out, codes, od[u], Q, na, seed);
         }
-        for (; i < nquads; i += stride) {
-            int64_t qd = REVERSE ? nquads - 1 - i : i;
-            grad_quad<NOISE, WRITE_Y, WRITE_C>(__ldcs(reinterpret_cast<const float4*>(g) + qd),
-                                               noise_quad<NOISE>(na, seed, qd), out, codes, qd, p);
+        for (; i < noct; i += stride) {
+            const int64_t od = REVERSE ? noct - 1 - i : i;
+            grad_octet<NOISE, WRITE_Y, WRITE_C, SMALL>(ld256_stream(g + 8 * od), out, codes, od, Q, na, seed);
         }
-        if (tid < (n & 3)) {
-            int64_t e = (nquads << 2) + tid;
-            float q = q_zp_code(g[e], noise_elem<NOISE>(na, seed, e), p);
-            if (WRITE_Y) out[e] = q_zp_deq(q, p);
-            if (WRITE_C) codes[e] = (uint8_t)q;
-        }
+        if (tid < (n & 7)) grad_elem<NOISE, WRITE_Y, WRITE_C>(g, out, codes, (noct << 3) + tid, Q, na, seed);
     } else {
-        for (int64_t e = tid; e < n; e += stride) {
-            float q = q_zp_code(g[e], noise_elem<NOISE>(na, seed, e), p);
-            if (WRITE_Y) out[e] = q_zp_deq(q, p);
-            if (WRITE_C) codes[e] = (uint8_t)q;
-        }
+        for (int64_t e = tid; e < n; e += stride) grad_elem<NOISE, WRITE_Y, WRITE_C>(g, out, codes, e, Q, na, seed);
     }
+}
+template <int NOISE, bool WRITE_Y, bool WRITE_C, bool REVERSE>
+__device__ __forceinline__ void sweep_grad(const float* __restrict__ g, float* out, uint8_t* codes, int64_t n, bool vec,
+                                           const GradQ& Q, const NoiseArg& na) {
+    if (Q.p.qmax < 4194304.0f)
+        sweep_grad_impl<NOISE, WRITE_Y, WRITE_C, REVERSE, true>(g, out, codes, n, vec, Q, na);
+    else
+        sweep_grad_impl<NOISE, WRITE_Y, WRITE_C, REVERSE, false>(g, out, codes, n, vec, Q, na);
 }
 
 template <int NOISE, bool WRITE_Y, bool WRITE_C>
-__global__ void __launch_bounds__(GQ_THREADS, 3)
+__global__ void __launch_bounds__(GQ_THREADS, 4)
 k_fq_grad(const float* __restrict__ g, float* out, uint8_t* codes, int64_t n, int vec, int bits, const float* range_dev,
           double lo, double hi, NoiseArg na) {
     if (range_dev) {
         lo = (double)__ldg(range_dev);
         hi = (double)__ldg(range_dev + 1);
     }
-    const QParams p = make_qparams_d(lo, hi, bits);
-    sweep_grad<NOISE, WRITE_Y, WRITE_C, false>(g, out, codes, n, vec != 0, p, na);
+    const GradQ Q = make_gradq(lo, hi, bits);
+    sweep_grad<NOISE, WRITE_Y, WRITE_C, false>(g, out, codes, n, vec != 0, Q, na);
 }
 
 // fused: phase 1 min/max, grid sync, phase 2 quantize (cooperative launch: grid <= co-resident CTAs)
 template <int NOISE, bool WRITE_Y, bool WRITE_C>
-__global__ void __launch_bounds__(GQ_THREADS, 3)
+__global__ void __launch_bounds__(GQ_THREADS, 4)
 k_fq_grad_fused(const float* __restrict__ g, float* out, uint8_t* codes, int64_t n, int vec, int bits, float* range_out,
                 NoiseArg na, MinMaxWs* ws) {
     __shared__ float sm[64];
     float mn = QB_INF, mx = -QB_INF;
-    sweep_minmax<false>(g, n, vec != 0, mn, mx);
+    sweep_minmax(g, n, vec != 0, mn, mx);
     block_reduce_minmax(mn, mx, sm);
     if (threadIdx.x == 0) {
         ws->pmin[blockIdx.x] = mn;
@@ -264,8 +308,8 @@ k_fq_grad_fused(const float* __restrict__ g, float* out, uint8_t* codes, int64_t
         range_out[0] = mn;
         range_out[1] = mx;
     }
-    const QParams p = make_qparams_d((double)mn, (double)mx, bits);
-    sweep_grad<NOISE, WRITE_Y, WRITE_C, true>(g, out, codes, n, vec != 0, p, na);
+    const GradQ Q = make_gradq((double)mn, (double)mx, bits);
+    sweep_grad<NOISE, WRITE_Y, WRITE_C, true>(g, out, codes, n, vec != 0, Q, na);
 }
 
 template <typename F>
@@ -292,8 +336,8 @@ static int check_grad_args(const char* who, const float* g, float* out, uint8_t*
 }
 
 static bool grad_vec_ok(const float* g, const float* out, const uint8_t* codes, const float* noise, uint64_t offset) {
-    return aligned16(g) && (!out || aligned16(out)) && (!noise || aligned16(noise)) &&
-           (!codes || (reinterpret_cast<uintptr_t>(codes) & 3) == 0) && (offset & 3) == 0;
+    return aligned32(g) && (!out || aligned32(out)) && (!noise || aligned32(noise)) &&
+           (!codes || (reinterpret_cast<uintptr_t>(codes) & 7) == 0) && (offset & 7) == 0;
 }
 
 extern "C" int qb_fakequant_grad(const float* g, float* out, uint8_t* codes, int64_t n, int bits, const float* range_dev,
@@ -305,7 +349,7 @@ extern "C" int qb_fakequant_grad(const float* g, float* out, uint8_t* codes, int
     const int nm = !stochastic ? NOISE_NONE : (noise ? NOISE_INJECT : NOISE_PHILOX);
     NoiseArg na{noise, seed, offset, step_dev};
     const int vec = grad_vec_ok(g, out, codes, noise, offset);
-    const int grid = gq_grid(vec ? (n >> 2) : n, 8);
+    const int grid = gq_grid(vec ? (n >> 3) : n, 8);
     cudaStream_t st = qb_stream(stream);
     rc = dispatch_grad(nm, out != nullptr, codes != nullptr, [&](auto NM, auto WY, auto WC) {
         k_fq_grad<decltype(NM)::value, decltype(WY)::value, decltype(WC)::value>
@@ -341,7 +385,7 @@ extern "C" int qb_fakequant_grad_fused(const float* g, float* out, uint8_t* code
             qb_set_error("qb_fakequant_grad_fused: kernel does not fit on an SM");
             return QB_ERR_CUDA;
         }
-        int grid = gq_grid(vec ? (n >> 2) : n, per_sm < 8 ? per_sm : 8);
+        int grid = gq_grid(vec ? (n >> 3) : n, per_sm < 8 ? per_sm : 8);
         void* args[] = {(void*)&g, (void*)&out, (void*)&codes, (void*)&n, (void*)&vec, (void*)&bits,
                         (void*)&range_out, (void*)&na, (void*)&w};
         QB_CUDA(cudaLaunchCooperativeKernel((const void*)kern, dim3(grid), dim3(GQ_THREADS), args, 0, st));

@@ -177,6 +177,50 @@ def test_grad_philox_statistics_and_replay(lib):
     assert not torch.equal(a, e)
 
 
+def test_fast_division_is_ieee(lib):
+    """The FMA division every quantizer uses (common.cuh qb_div) against __fdiv_rn, bit for bit: dense random
+    numerators over the magnitudes gradients/activations take, exact zeros (post-ReLU tensors; they must not change
+    the answer), values around code boundaries, and the fallback window (huge / inf)."""
+    gen = torch.Generator().manual_seed(77)
+    n = 1 << 22
+    for b in [1e-8, 3.1e-7, 1.7e-4, 0.0123, 0.9999, 1.0, 3.0, 255.0, 1e5]:
+        mag = torch.exp2(torch.randint(-40, 20, (n,), generator=gen).float())
+        a = torch.randn(n, generator=gen) * mag
+        a[::7] = 0.0
+        a[1::1013] = -0.0
+        k = torch.randint(0, 256, (n // 4,), generator=gen).float()
+        a[: n // 4] = (k + 0.5) * b                                   # quotients next to rounding ties
+        a[n // 4: n // 2] = torch.nextafter(a[: n // 4], torch.zeros(()))
+        a[-4:] = torch.tensor([3e38, -3e38, float("inf"), 1e30])
+        fast, ieee = lib.selftest_div(a.to(DEV), b)
+        bits_equal(fast, ieee, "b=%g" % b)
+        ref = a / torch.tensor(b, dtype=torch.float32)               # ATen CPU true division
+        sel = a.abs() >= 2.0 ** -100                                 # CPU may flush nothing; compare where normal
+        assert torch.equal(ieee.cpu()[sel].view(torch.int32), ref[sel].view(torch.int32))
+
+
+def test_philox_noise_lattice_and_moments(lib):
+    """Recover the in-kernel noise u through the quantizer itself: with g = 0, range [-128, 127] (scale 1, zp 128)
+    the code is rne(128 + u) - which only reveals the sign - so use 16 bits: scale 1/257.. simpler and exact:
+    quantize g = k + 0.5 (k integer) with scale 1: the code is k + [u >= 0 rounding], giving P(u > 0); and the
+    mean/variance of the rounding error of a constant tensor give E[u], Var[u]."""
+    n = 1 << 22
+    # scale exactly 1: lo = -128, hi = 127 -> s = 255/255 = 1, zp = 128
+    frac = 0.25
+    g = torch.full((n,), 3.0 + frac, device=DEV)
+    g[0], g[1] = -128.0, 127.0                                     # pin the range
+    out, r = lib.fakequant_grad_fused(g, 8, seed=99)
+    assert r.cpu().tolist() == [-128.0, 127.0]
+    up = (out[2:] == 4.0).double().mean().item()                   # P(round up) must equal the fraction
+    assert abs(up - frac) < 4 * np.sqrt(frac * (1 - frac) / n)
+    assert bool(((out[2:] == 3.0) | (out[2:] == 4.0)).all())
+    # different octets / lanes are uncorrelated: lag-1 and lag-8 autocorrelation of the up/down pattern
+    z = (out[2:] == 4.0).double() - up
+    for lag in (1, 2, 8, 256):
+        c = float((z[:-lag] * z[lag:]).mean() / (z * z).mean())
+        assert abs(c) < 5 / np.sqrt(n), (lag, c)
+
+
 def test_minmax(lib):
     for n in [1, 2, 1000, 1 << 22]:
         x = torch.randn(n)

@@ -40,7 +40,11 @@ def main():
         y = torch.empty_like(x)
         codes = torch.empty(n, dtype=torch.uint8, device=dev)
         r = _abi.minmax(x)
+        xr = torch.relu(x)                      # half exact zeros with min == 0: what every post-ReLU QConv2d input is
+        rr = _abi.minmax(xr)
         cases = {
+            "affine_relu_in+codes(9B)": (9, lambda: _abi.fakequant_affine(xr, 8, range_dev=rr, out=y, codes=codes)),
+            "grad_fused_relu_masked(12B)": (12, lambda: _abi.fakequant_grad_fused(xr, 8, out=y, seed=1)),
             "affine_given(8B/elem)": (8, lambda: _abi.fakequant_affine(x, 8, range_dev=r, out=y)),
             "affine_given+codes(9B)": (9, lambda: _abi.fakequant_affine(x, 8, range_dev=r, out=y, codes=codes)),
             "affine_4bit(8B)": (8, lambda: _abi.fakequant_affine(x, 4, range_dev=r, out=y)),
@@ -56,7 +60,7 @@ def main():
             gbs = bpe * n / ms / 1e6
             rows.append(dict(kernel=name, log2n=e, ms=round(ms, 4), gbs=round(gbs, 1), frac=round(gbs / peak, 3)))
             print("%-28s n=2^%d  %8.4f ms  %8.1f GB/s  %.3f of measured %.0f" % (name, e, ms, gbs, gbs / peak, peak), flush=True)
-        del x, y, codes
+        del x, y, codes, xr
     for rows_, cols in [(64, 1 << 16), (512, 4608), (1000, 512)]:
         w = torch.randn(rows_, cols, device=dev)
         ms = timeit(lambda: _abi.fakequant_rows(w, 8))
