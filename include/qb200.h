@@ -170,13 +170,34 @@ int qb_rangebn_bwd_apply(const float* gq, float* dx, int64_t B, int64_t C, int64
  * semantics, outputs and index conventions (amax/amin hold the flat b*HW+p index) as the NCHW entry
  * points above; finalize / bwd_coeffs are layout independent.                                        */
 size_t qb_rangebn_nhwc_ws_bytes(int64_t C, int num_chunks);
+/* Fusion hooks of the channels-last path (all optional, NULL = plain behaviour):
+ *   q_range/q_bits   x is the RAW RangeBN input and the QuantMeasure fake-quant of quantize.py:463 (range float[2] on
+ *                    the device, QB_SCALE_DOUBLE) is applied on the fly - x_hat is never materialised;
+ *   amax_kc/amin_kc  additional [chunk][channel] copies of the arg tables for the fused backward;
+ *   g_range/g_bits/noise/stochastic/seed/offset/step_dev   gq is the RAW output gradient and UniformQuantizeGrad's
+ *                    backward (quantize.py:124-139, arguments as qb_fakequant_grad) is applied on the fly; the noise of
+ *                    an element is a function of (seed, element index) so both backward passes see the same draw.
+ *                    Needs C % 8 == 0 and 32-byte aligned tensors. */
 int qb_rangebn_stats_nhwc(const float* x, int64_t B, int64_t C, int64_t HW, int num_chunks, int32_t* amax,
-                          int32_t* amin, double* red, void* ws, size_t ws_bytes, void* stream);
+                          int32_t* amin, int32_t* amax_kc, int32_t* amin_kc, double* red, const float* q_range,
+                          int q_bits, void* ws, size_t ws_bytes, void* stream);
 int qb_rangebn_apply_nhwc(const float* x, float* out, int64_t B, int64_t C, int64_t HW, const float* mean,
-                          const float* qscale, const float* qgamma, const float* qbeta, void* stream);
+                          const float* qscale, const float* qgamma, const float* qbeta, const float* q_range,
+                          int q_bits, void* stream);
 size_t qb_rangebn_bwd_nhwc_ws_bytes(int64_t C);
 int qb_rangebn_bwd_reduce_nhwc(const float* gq, const float* x, int64_t B, int64_t C, int64_t HW, double* sg,
-                               double* sgx, void* ws, size_t ws_bytes, void* stream);
+                               double* sgx, const float* q_range, int q_bits, const float* g_range, int g_bits,
+                               const float* noise, int stochastic, uint64_t seed, uint64_t offset,
+                               const uint64_t* step_dev, void* ws, size_t ws_bytes, void* stream);
+/* dx = (Q(g)*qgamma)*qscale + a, +-e at the chunk arg-max/arg-min rows, in ONE pass, plus min/max of the final dx
+ * (dx_range_out float[2], optional; mm_ws = qb_minmax_ws_bytes() bytes zero-filled once): the range the gradient
+ * quantizer of the preceding QConv2d needs (quantize.py:126,132) without another read of dx. */
+int qb_rangebn_bwd_apply_fused_nhwc(const float* g, float* dx, int64_t B, int64_t C, int64_t HW, int num_chunks,
+                                    const float* qscale, const float* qgamma, const float* coef_a,
+                                    const float* coef_e, const int32_t* amax_kc, const int32_t* amin_kc,
+                                    const float* g_range, int g_bits, const float* noise, int stochastic,
+                                    uint64_t seed, uint64_t offset, const uint64_t* step_dev,
+                                    float* dx_range_out, void* mm_ws, size_t mm_ws_bytes, void* stream);
 int qb_rangebn_bwd_apply_nhwc(const float* gq, float* dx, int64_t B, int64_t C, int64_t HW, int num_chunks,
                               const float* qscale, const float* qgamma, const float* coef_a, const float* coef_e,
                               const int32_t* amax, const int32_t* amin, void* stream);

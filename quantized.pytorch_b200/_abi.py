@@ -43,10 +43,13 @@ PROTOTYPES = {
     "qb_rangebn_bwd_coeffs": (_i32, [_p, _p, _i64, _i32, _dbl, _dbl, _i32, _p, _p, _p, _p, _p, _p, _p, _p, _p]),
     "qb_rangebn_bwd_apply": (_i32, [_p, _p, _i64, _i64, _i64, _i32, _p, _p, _p, _p, _p, _p, _p]),
     "qb_rangebn_nhwc_ws_bytes": (_sz, [_i64, _i32]),
-    "qb_rangebn_stats_nhwc": (_i32, [_p, _i64, _i64, _i64, _i32, _p, _p, _p, _p, _sz, _p]),
-    "qb_rangebn_apply_nhwc": (_i32, [_p, _p, _i64, _i64, _i64, _p, _p, _p, _p, _p]),
+    "qb_rangebn_stats_nhwc": (_i32, [_p, _i64, _i64, _i64, _i32, _p, _p, _p, _p, _p, _p, _i32, _p, _sz, _p]),
+    "qb_rangebn_apply_nhwc": (_i32, [_p, _p, _i64, _i64, _i64, _p, _p, _p, _p, _p, _i32, _p]),
     "qb_rangebn_bwd_nhwc_ws_bytes": (_sz, [_i64]),
-    "qb_rangebn_bwd_reduce_nhwc": (_i32, [_p, _p, _i64, _i64, _i64, _p, _p, _p, _sz, _p]),
+    "qb_rangebn_bwd_reduce_nhwc": (_i32, [_p, _p, _i64, _i64, _i64, _p, _p, _p, _i32, _p, _i32, _p, _i32, _u64, _u64, _p,
+                                          _p, _sz, _p]),
+    "qb_rangebn_bwd_apply_fused_nhwc": (_i32, [_p, _p, _i64, _i64, _i64, _i32, _p, _p, _p, _p, _p, _p, _p, _i32, _p, _i32,
+                                               _u64, _u64, _p, _p, _p, _sz, _p]),
     "qb_rangebn_bwd_apply_nhwc": (_i32, [_p, _p, _i64, _i64, _i64, _i32, _p, _p, _p, _p, _p, _p, _p]),
     "qb_rowsum_u8": (_i32, [_p, _i64, _i64, _p, _p]),
     "qb_gemm_i8": (_i32, [_p, _p, _p, _i64, _i64, _i64, _i64, _p, _i32, _p, _p, _i32, _p, _p, _p, _i32, _p]),
@@ -91,7 +94,7 @@ _profile = None       # list of (name, algorithmic_bytes, start_event, end_event
 
 # kernels enqueued per C call
 _NLAUNCH = {"qb_rangebn_stats": 2, "qb_rangebn_bwd_reduce": 2, "qb_rangebn_bwd_apply": 2,
-            "qb_rangebn_stats_nhwc": 2, "qb_rangebn_bwd_reduce_nhwc": 2, "qb_rangebn_bwd_apply_nhwc": 2}
+            "qb_rangebn_stats_nhwc": 3, "qb_rangebn_bwd_reduce_nhwc": 2, "qb_rangebn_bwd_apply_nhwc": 2}
 
 
 def _run(name, nbytes, *args):
@@ -279,17 +282,29 @@ def fakequant_grad_fused(g, bits, noise=None, stochastic=True, seed=0, offset=0,
 # ----------------------------------------------------------------------------------------------
 # RangeBN
 # ----------------------------------------------------------------------------------------------
-def rangebn_stats(x, B, Cn, HW, num_chunks, want_arg=True, nhwc=False):
-    """x: quantized NCHW input.  Returns (red double[3*C], amax int32[C*K] | None, amin | None)."""
+def rangebn_stats(x, B, Cn, HW, num_chunks, want_arg=True, nhwc=False, q_range=None, q_bits=8):
+    """x: RangeBN input (already fake-quantized, or RAW with ``q_range``: channels-last only, the quantizer then runs
+    inside the kernel).  Returns (red double[3*C], amax int32 | None, amin | None).  For channels-last, amax / amin
+    are [2, C*K]: row 0 in the reference's [c][k] order, row 1 transposed to [k][c] for the fused backward."""
     lib = load()
     dev = x.device
     red = torch.empty(3 * Cn, dtype=torch.float64, device=dev)
-    amax = torch.empty(Cn * num_chunks, dtype=torch.int32, device=dev) if want_arg else None
-    amin = torch.empty(Cn * num_chunks, dtype=torch.int32, device=dev) if want_arg else None
     sfx = "_nhwc" if nhwc else ""
     ws = workspace("rangebn" + sfx, (lib.qb_rangebn_nhwc_ws_bytes if nhwc else lib.qb_rangebn_ws_bytes)(Cn, num_chunks), dev)
-    _run("qb_rangebn_stats" + sfx, 4 * B * Cn * HW, _ptr(x), B, Cn, HW, num_chunks, _ptr(amax), _ptr(amin), _ptr(red), _ptr(ws), ws.numel(),
-                                _stream())
+    if nhwc:
+        amax = torch.empty(2, Cn * num_chunks, dtype=torch.int32, device=dev) if want_arg else None
+        amin = torch.empty(2, Cn * num_chunks, dtype=torch.int32, device=dev) if want_arg else None
+        _run("qb_rangebn_stats_nhwc", 4 * B * Cn * HW, _ptr(x), B, Cn, HW, num_chunks,
+             _ptr(amax[0]) if want_arg else None, _ptr(amin[0]) if want_arg else None,
+             _ptr(amax[1]) if want_arg else None, _ptr(amin[1]) if want_arg else None, _ptr(red),
+             _ptr(q_range), int(q_bits), _ptr(ws), ws.numel(), _stream())
+        return red, amax, amin
+    if q_range is not None:
+        raise QB200Error("rangebn_stats: on-the-fly input quantization is a channels-last feature")
+    amax = torch.empty(Cn * num_chunks, dtype=torch.int32, device=dev) if want_arg else None
+    amin = torch.empty(Cn * num_chunks, dtype=torch.int32, device=dev) if want_arg else None
+    _run("qb_rangebn_stats", 4 * B * Cn * HW, _ptr(x), B, Cn, HW, num_chunks, _ptr(amax), _ptr(amin), _ptr(red), _ptr(ws),
+         ws.numel(), _stream())
     return red, amax, amin
 
 
@@ -306,20 +321,30 @@ def rangebn_finalize(red, Cn, num_chunks, count, chunk_len, eps, momentum, train
     return vec
 
 
-def rangebn_apply(x, B, Cn, HW, vec, has_gamma, has_beta, out=None, nhwc=False):
+def rangebn_apply(x, B, Cn, HW, vec, has_gamma, has_beta, out=None, nhwc=False, q_range=None, q_bits=8):
     lib = load()
     if out is None:
         out = torch.empty_like(x)
-    _run("qb_rangebn_apply" + ("_nhwc" if nhwc else ""), 8 * B * Cn * HW, _ptr(x), _ptr(out), B, Cn, HW, _ptr(vec[0]), _ptr(vec[2]),
-                                _ptr(vec[3]) if has_gamma else None, _ptr(vec[4]) if has_beta else None, _stream())
+    args = [_ptr(x), _ptr(out), B, Cn, HW, _ptr(vec[0]), _ptr(vec[2]), _ptr(vec[3]) if has_gamma else None,
+            _ptr(vec[4]) if has_beta else None]
+    if nhwc:
+        args += [_ptr(q_range), int(q_bits)]
+    elif q_range is not None:
+        raise QB200Error("rangebn_apply: on-the-fly input quantization is a channels-last feature")
+    _run("qb_rangebn_apply" + ("_nhwc" if nhwc else ""), 8 * B * Cn * HW, *args, _stream())
     return out
 
 
 def rangebn_backward(gq, xq, B, Cn, HW, num_chunks, count, chunk_len, training, vec, has_gamma, amax, amin,
-                     reduce_hook=None, chunks_global=None, nhwc=False):
-    """Returns (dx, dgamma, dbeta).  ``reduce_hook(sums)`` may all-reduce the double[2*C] sums in place
+                     reduce_hook=None, chunks_global=None, nhwc=False, q_range=None, q_bits=8, grad_quant=None,
+                     want_dx_range=False):
+    """Returns (dx, dgamma, dbeta[, dx_range]).  ``reduce_hook(sums)`` may all-reduce the double[2*C] sums in place
     (batch-sharded training); ``num_chunks`` is this rank's chunk count (layout of amax/amin),
-    ``chunks_global`` the count the chunk-mean was taken over."""
+    ``chunks_global`` the count the chunk-mean was taken over.
+
+    Channels-last fusion: ``q_range`` - xq is the RAW RangeBN input, quantized on the fly; ``grad_quant`` =
+    dict(range=float[2] device tensor, bits, noise, stochastic, seed, step_dev) - gq is the RAW output gradient,
+    quantized on the fly in both passes; ``want_dx_range`` - also return min/max of dx (float[2])."""
     lib = load()
     dev = gq.device
     if chunks_global is None:
@@ -327,8 +352,22 @@ def rangebn_backward(gq, xq, B, Cn, HW, num_chunks, count, chunk_len, training, 
     sums = torch.empty(2 * Cn, dtype=torch.float64, device=dev)
     sfx = "_nhwc" if nhwc else ""
     ws = workspace("rangebn_bwd" + sfx, (lib.qb_rangebn_bwd_nhwc_ws_bytes if nhwc else lib.qb_rangebn_bwd_ws_bytes)(Cn), dev)
-    _run("qb_rangebn_bwd_reduce" + sfx, 8 * B * Cn * HW, _ptr(gq), _ptr(xq), B, Cn, HW, _ptr(sums[:Cn]), _ptr(sums[Cn:]), _ptr(ws),
-                                     ws.numel(), _stream())
+    fused = nhwc and Cn % 8 == 0 and gq.numel() < 2 ** 32
+    if (grad_quant is not None or want_dx_range) and not fused:
+        raise QB200Error("rangebn_backward: gradient-quantizer / dx-range fusion needs channels-last with C % 8 == 0")
+    gqa = [None, 0, None, 0, 0, 0, None]
+    if grad_quant is not None:
+        gqa = [_ptr(grad_quant["range"]), int(grad_quant["bits"]), _ptr(grad_quant.get("noise")),
+               int(bool(grad_quant.get("stochastic", True))), int(grad_quant.get("seed", 0)) & (2 ** 64 - 1), 0,
+               _ptr(grad_quant.get("step_dev"))]
+    if nhwc:
+        _run("qb_rangebn_bwd_reduce_nhwc", 8 * B * Cn * HW, _ptr(gq), _ptr(xq), B, Cn, HW, _ptr(sums[:Cn]), _ptr(sums[Cn:]),
+             _ptr(q_range), int(q_bits), *gqa, _ptr(ws), ws.numel(), _stream())
+    else:
+        if q_range is not None:
+            raise QB200Error("rangebn_backward: on-the-fly input quantization is a channels-last feature")
+        _run("qb_rangebn_bwd_reduce", 8 * B * Cn * HW, _ptr(gq), _ptr(xq), B, Cn, HW, _ptr(sums[:Cn]), _ptr(sums[Cn:]),
+             _ptr(ws), ws.numel(), _stream())
     if reduce_hook is not None:
         reduce_hook(sums)
     coef = torch.empty(4, Cn, dtype=torch.float32, device=dev)     # dgamma, dbeta, a, e
@@ -337,16 +376,27 @@ def rangebn_backward(gq, xq, B, Cn, HW, num_chunks, count, chunk_len, training, 
                                      _ptr(vec[3]) if has_gamma else None, _ptr(coef[0]), _ptr(coef[1]), _ptr(coef[2]),
                                      _ptr(coef[3]), _stream())
     dx = torch.empty_like(gq)
-    _run("qb_rangebn_bwd_apply" + sfx, 8 * B * Cn * HW, _ptr(gq), _ptr(dx), B, Cn, HW, int(num_chunks) if training else 0, _ptr(vec[2]),
-                                    _ptr(vec[3]) if has_gamma else None, _ptr(coef[2]),
-                                    _ptr(coef[3]) if training else None, _ptr(amax) if training else None,
-                                    _ptr(amin) if training else None, _stream())
+    dx_range = None
+    if fused:
+        mm = None
+        if want_dx_range:
+            dx_range = torch.empty(2, dtype=torch.float32, device=dev)
+            mm = workspace("minmax", lib.qb_minmax_ws_bytes(), dev)
+        _run("qb_rangebn_bwd_apply_fused_nhwc", 8 * B * Cn * HW, _ptr(gq), _ptr(dx), B, Cn, HW,
+             int(num_chunks) if training else 0, _ptr(vec[2]), _ptr(vec[3]) if has_gamma else None, _ptr(coef[2]),
+             _ptr(coef[3]) if training else None, _ptr(amax[1]) if training else None,
+             _ptr(amin[1]) if training else None, *gqa, _ptr(dx_range), _ptr(mm), mm.numel() if mm is not None else 0,
+             _stream())
+    else:
+        a0 = amax[0] if (nhwc and amax is not None) else amax
+        i0 = amin[0] if (nhwc and amin is not None) else amin
+        _run("qb_rangebn_bwd_apply" + sfx, 8 * B * Cn * HW, _ptr(gq), _ptr(dx), B, Cn, HW, int(num_chunks) if training else 0,
+             _ptr(vec[2]), _ptr(vec[3]) if has_gamma else None, _ptr(coef[2]), _ptr(coef[3]) if training else None,
+             _ptr(a0) if training else None, _ptr(i0) if training else None, _stream())
+    if want_dx_range:
+        return dx, coef[0], coef[1], dx_range
     return dx, coef[0], coef[1]
 
-
-# ----------------------------------------------------------------------------------------------
-# int8 tensor-core contraction
-# ----------------------------------------------------------------------------------------------
 def rowsum_u8(codes, rows, cols, out=None):
     if out is None:
         out = torch.empty(rows, dtype=torch.int32, device=codes.device)

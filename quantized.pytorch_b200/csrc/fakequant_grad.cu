@@ -25,20 +25,6 @@ struct MinMaxWs {
 
 extern "C" size_t qb_minmax_ws_bytes(void) { return sizeof(MinMaxWs); }
 
-enum { NOISE_NONE = 0, NOISE_INJECT = 1, NOISE_PHILOX = 2 };
-
-struct NoiseArg {
-    const float* inject;       // NOISE_INJECT
-    uint64_t seed, offset;     // NOISE_PHILOX: element e uses lane (e+offset)&7 of philox(seed', (e+offset)>>3)
-    const uint64_t* step_dev;  // optional device step counter mixed into the seed (CUDA-graph replays)
-};
-
-__device__ __forceinline__ uint64_t effective_seed(const NoiseArg& a) {
-    uint64_t s = a.seed;
-    if (a.step_dev) s += __ldg(a.step_dev) * 0x9E3779B97F4A7C15ull;
-    return s;
-}
-
 __device__ __forceinline__ void block_reduce_minmax(float& mn, float& mx, float* sm) {
     mn = warp_min(mn);
     mx = warp_max(mx);
@@ -152,24 +138,6 @@ extern "C" int qb_minmax(const float* x, int64_t n, float* range_out, void* ws, 
 // ------------------------------------------------------------------------------------------------
 // zero-point stochastic quantizer (A2), range given
 // ------------------------------------------------------------------------------------------------
-struct GradQ {          // grid-uniform quantizer state
-    QParams p;
-    Divisor d;
-};
-__device__ __forceinline__ GradQ make_gradq(double lo, double hi, int bits) {
-    GradQ q;
-    q.p = make_qparams_d(lo, hi, bits);
-    q.d = make_divisor(q.p.scale);
-    return q;
-}
-
-template <int NOISE>
-__device__ __forceinline__ float noise_elem(const NoiseArg& a, uint64_t seed, int64_t e) {
-    if (NOISE == NOISE_INJECT) return a.inject[e];
-    if (NOISE == NOISE_PHILOX) return philox_noise1(seed, (uint64_t)e + a.offset);
-    return 0.f;
-}
-
 template <int NOISE, bool WRITE_Y, bool WRITE_C>
 __device__ __forceinline__ void grad_elem(const float* g, float* out, uint8_t* codes, int64_t e, const GradQ& Q,
                                           const NoiseArg& na, uint64_t seed) {

@@ -13,6 +13,7 @@
 constexpr int NH_THREADS = 256;
 constexpr int NH_UNROLL = 4;
 constexpr int NH_MAX_SEG = 32;      // row segments per chunk (partials per (chunk, channel))
+constexpr int NH_MAX_SEG_BWD = 1024;
 
 struct NhwcGeom {
     int64_t R, C;         // rows, channels
@@ -53,17 +54,26 @@ __device__ __forceinline__ void amin_merge(ArgV& a, float v, int32_t i) { if (v 
 template <int VEC> struct VecT;
 template <> struct VecT<4> { using T = float4; };
 template <> struct VecT<1> { using T = float; };
+template <> struct VecT<8> { using T = F8; };
+__device__ __forceinline__ void unpack(const F8& v, float (&a)[8]) {
+#pragma unroll
+    for (int j = 0; j < 8; ++j) a[j] = v.v[j];
+}
+template <typename V> __device__ __forceinline__ V ld_vec_stream(const float* p) { return __ldcs(reinterpret_cast<const V*>(p)); }
+template <> __device__ __forceinline__ F8 ld_vec_stream<F8>(const float* p) { return ld256_stream(p); }
 __device__ __forceinline__ void unpack(const float4& v, float (&a)[4]) { a[0] = v.x; a[1] = v.y; a[2] = v.z; a[3] = v.w; }
 __device__ __forceinline__ void unpack(const float& v, float (&a)[1]) { a[0] = v; }
 
 // ---------------------------------------------------------------------------------------------------
 // forward statistics: partials per (chunk k, segment s, channel c)
 // ---------------------------------------------------------------------------------------------------
-template <int VEC>
+template <int VEC, bool QUANT>
 __global__ void __launch_bounds__(NH_THREADS)
 k_rbn_stats_nhwc(const float* __restrict__ x, NhwcGeom g, float* pmax, float* pmin, int32_t* imax, int32_t* imin,
-                 double* psum) {
+                 double* psum, const float* q_range, int q_bits) {
     using V = typename VecT<VEC>::T;
+    AffineQ aq;
+    if (QUANT) aq = load_affineq(q_range, q_bits);
     extern __shared__ unsigned char smem_raw[];
     const int ct = threadIdx.x % g.CT, rl = threadIdx.x / g.CT;
     const int64_t c0 = (int64_t)blockIdx.y * g.tileC + (int64_t)ct * VEC;
@@ -90,6 +100,7 @@ k_rbn_stats_nhwc(const float* __restrict__ x, NhwcGeom g, float* pmax, float* pm
                 float a[VEC];
                 unpack(v[u], a);
                 const int32_t idx = (int32_t)(r + u * step);
+                if (QUANT) affine_fq_vec<VEC>(a, aq);
 #pragma unroll
                 for (int j = 0; j < VEC; ++j) { amax_upd(mx[j], a[j], idx); amin_upd(mn[j], a[j], idx); fs[j] += a[j]; }
             }
@@ -102,6 +113,7 @@ k_rbn_stats_nhwc(const float* __restrict__ x, NhwcGeom g, float* pmax, float* pm
         for (; r < r_end; r += step) {
             float a[VEC];
             unpack(__ldcs(reinterpret_cast<const V*>(x + r * g.C + c0)), a);
+            if (QUANT) affine_fq_vec<VEC>(a, aq);
 #pragma unroll
             for (int j = 0; j < VEC; ++j) { amax_upd(mx[j], a[j], (int32_t)r); amin_upd(mn[j], a[j], (int32_t)r); fs[j] += a[j]; }
         }
@@ -142,7 +154,7 @@ k_rbn_stats_nhwc(const float* __restrict__ x, NhwcGeom g, float* pmax, float* pm
 // merge the S segment partials of every (chunk k, channel c): one thread each, c fastest (coalesced)
 __global__ void k_rbn_stats_nhwc_merge(const float* pmax, const float* pmin, const int32_t* imax, const int32_t* imin,
                                        const double* psum, int64_t C, int K, int S, int32_t* amax, int32_t* amin,
-                                       float* cmax, float* cmin, double* csum) {
+                                       int32_t* amax_kc, int32_t* amin_kc, float* cmax, float* cmin, double* csum) {
     const int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (t >= C * K) return;
     const int64_t k = t / C, c = t - k * C;
@@ -159,6 +171,8 @@ __global__ void k_rbn_stats_nhwc_merge(const float* pmax, const float* pmin, con
     csum[t] = ssum;
     if (amax) amax[c * K + k] = mx.i;
     if (amin) amin[c * K + k] = mn.i;
+    if (amax_kc) amax_kc[t] = mx.i;          // [k][c]: what the fused backward reads with one vector load per octet
+    if (amin_kc) amin_kc[t] = mn.i;
 }
 
 // red[3][C]: sum over the K chunks in a fixed order
@@ -185,7 +199,9 @@ extern "C" size_t qb_rangebn_nhwc_ws_bytes(int64_t C, int num_chunks) {
 static size_t nhwc_smem(const NhwcGeom& g, int vec, int per_elem) { return (size_t)g.RL * g.CT * vec * per_elem; }
 
 extern "C" int qb_rangebn_stats_nhwc(const float* x, int64_t B, int64_t C, int64_t HW, int num_chunks, int32_t* amax,
-                                     int32_t* amin, double* red, void* ws, size_t ws_bytes, void* stream) {
+                                     int32_t* amin, int32_t* amax_kc, int32_t* amin_kc, double* red, const float* q_range,
+                                     int q_bits, void* ws, size_t ws_bytes, void* stream) {
+    QB_CHECK_ARG(!q_range || (q_bits >= 1 && q_bits <= 24), "qb_rangebn_stats_nhwc: q_bits=%d", q_bits);
     QB_CHECK_ARG(x && red && ws, "qb_rangebn_stats_nhwc: null pointer");
     QB_CHECK_ARG(B > 0 && C > 0 && HW > 0 && num_chunks > 0, "qb_rangebn_stats_nhwc: bad shape");
     const int64_t R = B * HW;
@@ -211,13 +227,17 @@ extern "C" int qb_rangebn_stats_nhwc(const float* x, int64_t B, int64_t C, int64
     float* cmin = cmax + nk;
     dim3 grid((unsigned)(num_chunks * g.S), (unsigned)((C + g.tileC - 1) / g.tileC));
     cudaStream_t st = qb_stream(stream);
-    if (vec4)
-        k_rbn_stats_nhwc<4><<<grid, NH_THREADS, nhwc_smem(g, 4, 24), st>>>(x, g, pmax, pmin, imax, imin, psum);
+    if (vec4 && q_range)
+        k_rbn_stats_nhwc<4, true><<<grid, NH_THREADS, nhwc_smem(g, 4, 24), st>>>(x, g, pmax, pmin, imax, imin, psum, q_range, q_bits);
+    else if (vec4)
+        k_rbn_stats_nhwc<4, false><<<grid, NH_THREADS, nhwc_smem(g, 4, 24), st>>>(x, g, pmax, pmin, imax, imin, psum, nullptr, 0);
+    else if (q_range)
+        k_rbn_stats_nhwc<1, true><<<grid, NH_THREADS, nhwc_smem(g, 1, 24), st>>>(x, g, pmax, pmin, imax, imin, psum, q_range, q_bits);
     else
-        k_rbn_stats_nhwc<1><<<grid, NH_THREADS, nhwc_smem(g, 1, 24), st>>>(x, g, pmax, pmin, imax, imin, psum);
+        k_rbn_stats_nhwc<1, false><<<grid, NH_THREADS, nhwc_smem(g, 1, 24), st>>>(x, g, pmax, pmin, imax, imin, psum, nullptr, 0);
     QB_LAUNCH_CHECK();
     k_rbn_stats_nhwc_merge<<<(unsigned)((nk + 127) / 128), 128, 0, st>>>(pmax, pmin, imax, imin, psum, C, num_chunks, g.S,
-                                                                        amax, amin, cmax, cmin, csum);
+                                                                        amax, amin, amax_kc, amin_kc, cmax, cmin, csum);
     QB_LAUNCH_CHECK();
     k_rbn_stats_nhwc_pack<<<(unsigned)((C + 127) / 128), 128, 0, st>>>(cmax, cmin, csum, C, num_chunks, red);
     QB_LAUNCH_CHECK();
@@ -231,6 +251,8 @@ extern "C" int qb_rangebn_stats_nhwc(const float* x, int64_t B, int64_t C, int64
 // ---------------------------------------------------------------------------------------------------
 struct NhwcVecs {
     const float *p0, *p1, *p2, *p3;   // fwd: mean, qscale, qgamma|null, qbeta|null ; bwd: qgamma|null, qscale, coef_a, unused
+    const float* q_range;             // fwd only: quantize x on the fly with this device range (or null)
+    int q_bits;
 };
 
 template <int MODE>
@@ -246,13 +268,20 @@ __device__ __forceinline__ float nhwc_one(float v, uint32_t c, const NhwcVecs& p
     }
 }
 
-template <int MODE, bool C4>
+template <int MODE, bool C4, bool QUANT>
 __global__ void __launch_bounds__(NH_THREADS)
 k_rbn_apply_nhwc(const float* __restrict__ x, float* out, uint32_t n, FastDiv dC, NhwcVecs p) {
     const uint32_t nquads = n >> 2;
     const uint32_t stride = gridDim.x * NH_THREADS;
+    AffineQ aq;
+    if (QUANT) aq = load_affineq(p.q_range, p.q_bits);
     for (uint32_t i = blockIdx.x * NH_THREADS + threadIdx.x; i < nquads; i += stride) {
-        const float4 v = ld_stream4(x + 4ull * i);
+        float4 v = ld_stream4(x + 4ull * i);
+        if (QUANT) {
+            float a[4] = {v.x, v.y, v.z, v.w};
+            affine_fq_vec<4>(a, aq);
+            v = make_float4(a[0], a[1], a[2], a[3]);
+        }
         const uint32_t e = 4u * i;
         uint32_t c = e - fdiv(e, dC) * dC.d;
         float4 r;
@@ -284,7 +313,7 @@ k_rbn_apply_nhwc(const float* __restrict__ x, float* out, uint32_t n, FastDiv dC
     }
     if (blockIdx.x == 0 && threadIdx.x < (n & 3)) {
         const uint32_t e = (nquads << 2) + threadIdx.x;
-        out[e] = nhwc_one<MODE>(x[e], e - fdiv(e, dC) * dC.d, p);
+        out[e] = nhwc_one<MODE>(QUANT ? affine_fq(x[e], aq) : x[e], e - fdiv(e, dC) * dC.d, p);
     }
 }
 
@@ -307,91 +336,123 @@ static int launch_apply_nhwc(const char* who, const float* x, float* out, int64_
                  "%s: tensors must be 16-byte aligned", who);
     FastDiv dC = make_fastdiv((uint32_t)C);
     const int grid = nh_grid(n >> 2);
-    if (C % 4 == 0)
-        k_rbn_apply_nhwc<MODE, true><<<grid, NH_THREADS, 0, st>>>(x, out, (uint32_t)n, dC, p);
+    const bool quant = MODE == 0 && p.q_range != nullptr;
+    if (C % 4 == 0 && quant)
+        k_rbn_apply_nhwc<MODE, true, MODE == 0><<<grid, NH_THREADS, 0, st>>>(x, out, (uint32_t)n, dC, p);
+    else if (C % 4 == 0)
+        k_rbn_apply_nhwc<MODE, true, false><<<grid, NH_THREADS, 0, st>>>(x, out, (uint32_t)n, dC, p);
+    else if (quant)
+        k_rbn_apply_nhwc<MODE, false, MODE == 0><<<grid, NH_THREADS, 0, st>>>(x, out, (uint32_t)n, dC, p);
     else
-        k_rbn_apply_nhwc<MODE, false><<<grid, NH_THREADS, 0, st>>>(x, out, (uint32_t)n, dC, p);
+        k_rbn_apply_nhwc<MODE, false, false><<<grid, NH_THREADS, 0, st>>>(x, out, (uint32_t)n, dC, p);
     QB_LAUNCH_CHECK();
     return QB_OK;
 }
 
 extern "C" int qb_rangebn_apply_nhwc(const float* x, float* out, int64_t B, int64_t C, int64_t HW, const float* mean,
-                                     const float* qscale, const float* qgamma, const float* qbeta, void* stream) {
+                                     const float* qscale, const float* qgamma, const float* qbeta, const float* q_range,
+                                     int q_bits, void* stream) {
     QB_CHECK_ARG(x && out && mean && qscale, "qb_rangebn_apply_nhwc: null pointer");
     QB_CHECK_ARG(B > 0 && C > 0 && HW > 0, "qb_rangebn_apply_nhwc: bad shape");
-    return launch_apply_nhwc<0>("qb_rangebn_apply_nhwc", x, out, B * HW, C, NhwcVecs{mean, qscale, qgamma, qbeta},
-                                qb_stream(stream));
+    QB_CHECK_ARG(!q_range || (q_bits >= 1 && q_bits <= 24), "qb_rangebn_apply_nhwc: q_bits=%d", q_bits);
+    return launch_apply_nhwc<0>("qb_rangebn_apply_nhwc", x, out, B * HW, C,
+                                NhwcVecs{mean, qscale, qgamma, qbeta, q_range, q_bits}, qb_stream(stream));
 }
 
 // ---------------------------------------------------------------------------------------------------
-// backward reduce: sg[c] = sum_r gq[r][c], sgx[c] = sum_r gq[r][c] * x[r][c]   (column sums, fp64)
+// backward reduce: sg[c] = sum_r gq[r][c], sgx[c] = sum_r gq[r][c] * x_hat[r][c]   (column sums, fp64)
+// Fused form: g is the RAW output gradient and x the RAW RangeBN input; gq = Q_grad(g) (zero-point stochastic
+// quantizer, noise regenerated from the element index) and x_hat = Q_act(x) are recomputed in registers, so neither
+// quantized tensor is ever written to or read back from HBM.
 // ---------------------------------------------------------------------------------------------------
-template <int VEC>
-__global__ void __launch_bounds__(NH_THREADS)
-k_rbn_bwd_reduce_nhwc(const float* __restrict__ gq, const float* __restrict__ x, NhwcGeom g, double* part /*[2][S][C]*/) {
+struct GradQuantArg {
+    const float* range;   // device {min,max} of g, or nullptr: g is already quantized
+    int bits;
+    int noise_mode;
+    NoiseArg noise;
+};
+
+template <int VEC, bool QUANT, int NOISE>   // NOISE < 0: g already quantized
+__global__ void __launch_bounds__(NH_THREADS, 3)
+k_rbn_bwd_reduce_nhwc(const float* __restrict__ gq, const float* __restrict__ x, NhwcGeom g, double* part /*[2][S][C]*/,
+                      const float* q_range, int q_bits, GradQuantArg ga) {
     using V = typename VecT<VEC>::T;
+    constexpr int UN = VEC == 8 ? 2 : NH_UNROLL;
     extern __shared__ unsigned char smem_raw[];
+    AffineQ aq;
+    if (QUANT) aq = load_affineq(q_range, q_bits);
+    GradQ GQ;
+    uint64_t seed = 0;
+    if (NOISE >= 0) {
+        GQ = make_gradq((double)__ldg(ga.range), (double)__ldg(ga.range + 1), ga.bits);
+        seed = effective_seed(ga.noise);
+    }
     const int ct = threadIdx.x % g.CT, rl = threadIdx.x / g.CT;
     const int64_t c0 = (int64_t)blockIdx.y * g.tileC + (int64_t)ct * VEC;
     const int s = blockIdx.x;
     const int64_t r_begin = (int64_t)s * g.seg_rows;
     const int64_t r_end = (r_begin + g.seg_rows < g.R) ? r_begin + g.seg_rows : g.R;
     const bool active = rl < g.RL && c0 < g.C;
-    double dg[VEC], dgx[VEC];
+    // thread-local partials stay in fp32: the geometry gives a thread at most ~100 rows (S up to 1024 segments), the
+    // cross-thread / cross-segment combination below is fp64 in a fixed order
     float fg[VEC], fgx[VEC];
 #pragma unroll
-    for (int j = 0; j < VEC; ++j) { dg[j] = 0.0; dgx[j] = 0.0; fg[j] = 0.f; fgx[j] = 0.f; }
+    for (int j = 0; j < VEC; ++j) { fg[j] = 0.f; fgx[j] = 0.f; }
+    auto one_row = [&](const V& av_, const V& bv_, int64_t r) {
+        float av[VEC], bv[VEC];
+        unpack(av_, av);
+        unpack(bv_, bv);
+        if (NOISE >= 0) {
+            float u[8];
+            const int64_t e = r * g.C + c0;                       // VEC == 8 on this path: e is a multiple of 8
+            if (NOISE == NOISE_INJECT) {
+                const F8 w = ld256_stream(ga.noise.inject + e);
+#pragma unroll
+                for (int j = 0; j < 8; ++j) u[j] = w.v[j];
+            } else if (NOISE == NOISE_PHILOX) {
+                philox_noise8(seed, (uint64_t)(e >> 3) + (ga.noise.offset >> 3), u);
+            }
+            if (VEC == 8) grad_fq_vec<(NOISE < 0 ? 0 : NOISE), 8>(reinterpret_cast<float(&)[8]>(av), u, GQ);
+        }
+        if (QUANT) affine_fq_vec<VEC>(bv, aq);
+#pragma unroll
+        for (int j = 0; j < VEC; ++j) {
+            fg[j] += av[j];
+            fgx[j] += av[j] * bv[j];
+        }
+    };
     if (active) {
         int64_t r = r_begin + rl;
         const int64_t step = g.RL;
-        int cnt = 0;
-        for (; r + (NH_UNROLL - 1) * step < r_end; r += NH_UNROLL * step) {
-            V a[NH_UNROLL], b[NH_UNROLL];
+        for (; r + (UN - 1) * step < r_end; r += UN * step) {
+            V a[UN], b[UN];
 #pragma unroll
-            for (int u = 0; u < NH_UNROLL; ++u) {
-                a[u] = __ldcs(reinterpret_cast<const V*>(gq + (r + u * step) * g.C + c0));
-                b[u] = __ldcs(reinterpret_cast<const V*>(x + (r + u * step) * g.C + c0));
+            for (int u = 0; u < UN; ++u) {
+                a[u] = ld_vec_stream<V>(gq + (r + u * step) * g.C + c0);
+                b[u] = ld_vec_stream<V>(x + (r + u * step) * g.C + c0);
             }
 #pragma unroll
-            for (int u = 0; u < NH_UNROLL; ++u) {
-                float av[VEC], bv[VEC];
-                unpack(a[u], av);
-                unpack(b[u], bv);
-#pragma unroll
-                for (int j = 0; j < VEC; ++j) { fg[j] += av[j]; fgx[j] += av[j] * bv[j]; }
-            }
-            if (++cnt == 8) {
-#pragma unroll
-                for (int j = 0; j < VEC; ++j) { dg[j] += (double)fg[j]; dgx[j] += (double)fgx[j]; fg[j] = 0.f; fgx[j] = 0.f; }
-                cnt = 0;
-            }
+            for (int u = 0; u < UN; ++u) one_row(a[u], b[u], r + u * step);
         }
-        for (; r < r_end; r += step) {
-            float av[VEC], bv[VEC];
-            unpack(__ldcs(reinterpret_cast<const V*>(gq + r * g.C + c0)), av);
-            unpack(__ldcs(reinterpret_cast<const V*>(x + r * g.C + c0)), bv);
-#pragma unroll
-            for (int j = 0; j < VEC; ++j) { fg[j] += av[j]; fgx[j] += av[j] * bv[j]; }
-        }
-#pragma unroll
-        for (int j = 0; j < VEC; ++j) { dg[j] += (double)fg[j]; dgx[j] += (double)fgx[j]; }
+        for (; r < r_end; r += step)
+            one_row(ld_vec_stream<V>(gq + r * g.C + c0), ld_vec_stream<V>(x + r * g.C + c0), r);
     }
     const int W = g.CT * VEC;
     double* s_g = reinterpret_cast<double*>(smem_raw);
     double* s_gx = s_g + (size_t)g.RL * W;
     if (rl < g.RL) {
 #pragma unroll
-        for (int j = 0; j < VEC; ++j) { s_g[rl * W + ct * VEC + j] = dg[j]; s_gx[rl * W + ct * VEC + j] = dgx[j]; }
+        for (int j = 0; j < VEC; ++j) { s_g[rl * W + ct * VEC + j] = (double)fg[j]; s_gx[rl * W + ct * VEC + j] = (double)fgx[j]; }
     }
     __syncthreads();
-    if (rl == 0 && c0 < g.C) {
-#pragma unroll
-        for (int j = 0; j < VEC; ++j) {
-            if (c0 + j >= g.C) break;
-            for (int q = 1; q < g.RL; ++q) { dg[j] += s_g[q * W + ct * VEC + j]; dgx[j] += s_gx[q * W + ct * VEC + j]; }
-            part[(int64_t)s * g.C + c0 + j] = dg[j];
-            part[((int64_t)g.S + s) * g.C + c0 + j] = dgx[j];
-        }
+    // column c of the tile is finished by thread c: coalesced shared reads, RL terms in a fixed order
+    for (int col = threadIdx.x; col < W; col += NH_THREADS) {
+        const int64_t c = (int64_t)blockIdx.y * g.tileC + col;
+        if (c >= g.C) break;
+        double a = 0.0, b2 = 0.0;
+        for (int q = 0; q < g.RL; ++q) { a += s_g[q * W + col]; b2 += s_gx[q * W + col]; }
+        part[(int64_t)s * g.C + c] = a;
+        part[((int64_t)g.S + s) * g.C + c] = b2;
     }
 }
 
@@ -407,27 +468,65 @@ __global__ void k_rbn_bwd_pack_nhwc(const double* part, int64_t C, int S, double
     if (lane == 0) { sg[c] = a; sgx[c] = b; }
 }
 
-constexpr int NH_MAX_SEG_BWD = 1024;
 extern "C" size_t qb_rangebn_bwd_nhwc_ws_bytes(int64_t C) { return C < 0 ? 0 : (size_t)C * NH_MAX_SEG_BWD * 16; }
 
+template <int VEC, bool QUANT, int NOISE>
+static void launch_bwd_reduce(dim3 grid, size_t smem, cudaStream_t st, const float* gq, const float* x, const NhwcGeom& g,
+                              double* part, const float* q_range, int q_bits, const GradQuantArg& ga) {
+    k_rbn_bwd_reduce_nhwc<VEC, QUANT, NOISE><<<grid, NH_THREADS, smem, st>>>(gq, x, g, part, q_range, q_bits, ga);
+}
+
+static int grad_noise_mode(const float* g_range, const float* noise, int stochastic) {
+    if (!g_range) return -1;
+    return !stochastic ? NOISE_NONE : (noise ? NOISE_INJECT : NOISE_PHILOX);
+}
+
+/* g_range != NULL: g is the raw gradient, quantized on the fly to g_bits with this device range (needs C % 8 == 0 and
+ * 32-byte aligned tensors); noise/stochastic/seed/offset/step_dev as in qb_fakequant_grad. */
 extern "C" int qb_rangebn_bwd_reduce_nhwc(const float* gq, const float* x, int64_t B, int64_t C, int64_t HW, double* sg,
-                                          double* sgx, void* ws, size_t ws_bytes, void* stream) {
+                                          double* sgx, const float* q_range, int q_bits, const float* g_range, int g_bits,
+                                          const float* noise, int stochastic, uint64_t seed, uint64_t offset,
+                                          const uint64_t* step_dev, void* ws, size_t ws_bytes, void* stream) {
     QB_CHECK_ARG(gq && x && sg && sgx && ws, "qb_rangebn_bwd_reduce_nhwc: null pointer");
     QB_CHECK_ARG(B > 0 && C > 0 && HW > 0, "qb_rangebn_bwd_reduce_nhwc: bad shape");
+    QB_CHECK_ARG(!q_range || (q_bits >= 1 && q_bits <= 24), "qb_rangebn_bwd_reduce_nhwc: q_bits=%d", q_bits);
+    QB_CHECK_ARG(!g_range || (g_bits >= 1 && g_bits <= 24), "qb_rangebn_bwd_reduce_nhwc: g_bits=%d", g_bits);
     if (ws_bytes < qb_rangebn_bwd_nhwc_ws_bytes(C)) {
         qb_set_error("qb_rangebn_bwd_reduce_nhwc: workspace %zu < %zu bytes", ws_bytes, qb_rangebn_bwd_nhwc_ws_bytes(C));
         return QB_ERR_WORKSPACE;
     }
     const int64_t R = B * HW;
-    const bool vec4 = (C % 4 == 0) && (((reinterpret_cast<uintptr_t>(x) | reinterpret_cast<uintptr_t>(gq)) & 15) == 0);
-    NhwcGeom g = vec4 ? make_geom<4>(R, C, 1, NH_MAX_SEG_BWD) : make_geom<1>(R, C, 1, NH_MAX_SEG_BWD);
+    const uintptr_t al = reinterpret_cast<uintptr_t>(x) | reinterpret_cast<uintptr_t>(gq) | reinterpret_cast<uintptr_t>(noise);
+    const bool vec8 = (C % 8 == 0) && ((al & 31) == 0) && (offset % 8 == 0);
+    const bool vec4 = (C % 4 == 0) && ((al & 15) == 0);
+    const int nm = grad_noise_mode(g_range, noise, stochastic);
+    if (nm >= 0 && !vec8) {
+        qb_set_error("qb_rangebn_bwd_reduce_nhwc: on-the-fly gradient quantization needs C %% 8 == 0 and 32-byte alignment");
+        return QB_ERR_UNSUPPORTED;
+    }
+    NhwcGeom g = vec8 ? make_geom<8>(R, C, 1, NH_MAX_SEG_BWD) : vec4 ? make_geom<4>(R, C, 1, NH_MAX_SEG_BWD)
+                                                                      : make_geom<1>(R, C, 1, NH_MAX_SEG_BWD);
     double* part = static_cast<double*>(ws);
     dim3 grid((unsigned)g.S, (unsigned)((C + g.tileC - 1) / g.tileC));
     cudaStream_t st = qb_stream(stream);
-    if (vec4)
-        k_rbn_bwd_reduce_nhwc<4><<<grid, NH_THREADS, nhwc_smem(g, 4, 16), st>>>(gq, x, g, part);
-    else
-        k_rbn_bwd_reduce_nhwc<1><<<grid, NH_THREADS, nhwc_smem(g, 1, 16), st>>>(gq, x, g, part);
+    GradQuantArg ga{g_range, g_bits, nm, NoiseArg{noise, seed, offset, step_dev}};
+    const bool qx = q_range != nullptr;
+    if (vec8) {
+        const size_t sm = nhwc_smem(g, 8, 16);
+#define QB_RED8(NM) (qx ? launch_bwd_reduce<8, true, NM>(grid, sm, st, gq, x, g, part, q_range, q_bits, ga) \
+                        : launch_bwd_reduce<8, false, NM>(grid, sm, st, gq, x, g, part, q_range, q_bits, ga))
+        if (nm < 0) QB_RED8(-1);
+        else if (nm == NOISE_NONE) QB_RED8(NOISE_NONE);
+        else if (nm == NOISE_INJECT) QB_RED8(NOISE_INJECT);
+        else QB_RED8(NOISE_PHILOX);
+#undef QB_RED8
+    } else if (vec4) {
+        if (qx) launch_bwd_reduce<4, true, -1>(grid, nhwc_smem(g, 4, 16), st, gq, x, g, part, q_range, q_bits, ga);
+        else launch_bwd_reduce<4, false, -1>(grid, nhwc_smem(g, 4, 16), st, gq, x, g, part, q_range, q_bits, ga);
+    } else {
+        if (qx) launch_bwd_reduce<1, true, -1>(grid, nhwc_smem(g, 1, 16), st, gq, x, g, part, q_range, q_bits, ga);
+        else launch_bwd_reduce<1, false, -1>(grid, nhwc_smem(g, 1, 16), st, gq, x, g, part, q_range, q_bits, ga);
+    }
     QB_LAUNCH_CHECK();
     k_rbn_bwd_pack_nhwc<<<(unsigned)((C * 32 + 127) / 128), 128, 0, st>>>(part, C, g.S, sg, sgx);
     QB_LAUNCH_CHECK();
@@ -447,13 +546,197 @@ __global__ void k_rbn_bwd_scatter_nhwc(float* dx, int64_t C, int K, const float*
     *q = __fsub_rn(*q, e);
 }
 
+// ---------------------------------------------------------------------------------------------------
+// Fused backward apply (C % 8 == 0): one 32-byte octet = 8 adjacent channels of one row.
+//   gq = Q_grad(g) recomputed in registers (same noise as the reduce pass: it is a function of the element index),
+//   dx = (gq * qgamma_c) * qscale_c + a_c, then +e_c / -e_c where this row is the chunk's first arg-max / arg-min
+//   (amax_kc / amin_kc are [chunk][channel] tables, one vector load each), and the global min / max of the FINAL dx
+//   (the range UniformQuantizeGrad.backward of the preceding QConv2d needs, quantize.py:126,132) as a by-product.
+// ---------------------------------------------------------------------------------------------------
+struct BwdApplyArgs {
+    const float *qgamma, *qscale, *coef_a, *coef_e;
+    const int32_t *amax_kc, *amin_kc;
+    uint32_t C;
+    FastDiv dC, dL;          // row = e / C ; chunk = row / L
+    float* range_out;        // float[2] or nullptr
+    float* pmin; float* pmax; unsigned int* counter;   // MinMaxWs-style partials (see fakequant_grad.cu)
+};
+
+template <int NOISE, bool RANGE>
+__global__ void __launch_bounds__(NH_THREADS)
+k_rbn_bwd_apply_fused(const float* __restrict__ g, float* __restrict__ dx, uint32_t noct, BwdApplyArgs A, GradQuantArg ga) {
+    __shared__ float sm[64];
+    __shared__ bool last;
+    GradQ GQ;
+    uint64_t seed = 0;
+    if (NOISE >= 0) {
+        GQ = make_gradq((double)__ldg(ga.range), (double)__ldg(ga.range + 1), ga.bits);
+        seed = effective_seed(ga.noise);
+    }
+    float mn = QB_INF, mx = -QB_INF;
+    const uint32_t stride = gridDim.x * NH_THREADS;
+    for (uint32_t i = blockIdx.x * NH_THREADS + threadIdx.x; i < noct; i += stride) {
+        const F8 v = ld256_stream(g + 8ull * i);
+        const uint32_t e = 8u * i;                       // < 2^32 checked by the launcher
+        const uint32_t row = fdiv(e, A.dC), c = e - row * A.C;
+        float gq[8];
+        if (NOISE >= 0) {
+            float u[8];
+            if (NOISE == NOISE_INJECT) {
+                const F8 w = ld256_stream(ga.noise.inject + 8ull * i);
+#pragma unroll
+                for (int j = 0; j < 8; ++j) u[j] = w.v[j];
+            } else if (NOISE == NOISE_PHILOX) {
+                philox_noise8(seed, (uint64_t)i + (ga.noise.offset >> 3), u);
+            }
+#pragma unroll
+            for (int j = 0; j < 8; ++j) gq[j] = v.v[j];
+            grad_fq_vec<(NOISE < 0 ? 0 : NOISE), 8>(gq, u, GQ);
+        } else {
+#pragma unroll
+            for (int j = 0; j < 8; ++j) gq[j] = v.v[j];
+        }
+        float ga_[8], sc[8], ca[8];
+        {
+            const float4 s0 = __ldg(reinterpret_cast<const float4*>(A.qscale + c)), s1 = __ldg(reinterpret_cast<const float4*>(A.qscale + c + 4));
+            const float4 a0 = __ldg(reinterpret_cast<const float4*>(A.coef_a + c)), a1 = __ldg(reinterpret_cast<const float4*>(A.coef_a + c + 4));
+            sc[0] = s0.x; sc[1] = s0.y; sc[2] = s0.z; sc[3] = s0.w; sc[4] = s1.x; sc[5] = s1.y; sc[6] = s1.z; sc[7] = s1.w;
+            ca[0] = a0.x; ca[1] = a0.y; ca[2] = a0.z; ca[3] = a0.w; ca[4] = a1.x; ca[5] = a1.y; ca[6] = a1.z; ca[7] = a1.w;
+            if (A.qgamma) {
+                const float4 g0 = __ldg(reinterpret_cast<const float4*>(A.qgamma + c)), g1 = __ldg(reinterpret_cast<const float4*>(A.qgamma + c + 4));
+                ga_[0] = g0.x; ga_[1] = g0.y; ga_[2] = g0.z; ga_[3] = g0.w; ga_[4] = g1.x; ga_[5] = g1.y; ga_[6] = g1.z; ga_[7] = g1.w;
+            }
+        }
+        F8 o;
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+            const float t = A.qgamma ? __fmul_rn(gq[j], ga_[j]) : gq[j];
+            o.v[j] = __fadd_rn(__fmul_rn(t, sc[j]), ca[j]);
+        }
+        if (A.amax_kc) {
+            const uint32_t k = fdiv(row, A.dL);
+            const int32_t* pa = A.amax_kc + (size_t)k * A.C + c;
+            const int32_t* pi = A.amin_kc + (size_t)k * A.C + c;
+            const int4 x0 = __ldg(reinterpret_cast<const int4*>(pa)), x1 = __ldg(reinterpret_cast<const int4*>(pa + 4));
+            const int4 n0 = __ldg(reinterpret_cast<const int4*>(pi)), n1 = __ldg(reinterpret_cast<const int4*>(pi + 4));
+            const int32_t am[8] = {x0.x, x0.y, x0.z, x0.w, x1.x, x1.y, x1.z, x1.w};
+            const int32_t an[8] = {n0.x, n0.y, n0.z, n0.w, n1.x, n1.y, n1.z, n1.w};
+            bool any = false;
+#pragma unroll
+            for (int j = 0; j < 8; ++j) any = any || am[j] == (int32_t)row || an[j] == (int32_t)row;
+            if (any) {                                    // 2*K rows out of B*H*W per channel: rare
+                const float4 e0 = __ldg(reinterpret_cast<const float4*>(A.coef_e + c)), e1 = __ldg(reinterpret_cast<const float4*>(A.coef_e + c + 4));
+                const float ce[8] = {e0.x, e0.y, e0.z, e0.w, e1.x, e1.y, e1.z, e1.w};
+#pragma unroll
+                for (int j = 0; j < 8; ++j) {
+                    if (am[j] == (int32_t)row) o.v[j] = __fadd_rn(o.v[j], ce[j]);
+                    if (an[j] == (int32_t)row) o.v[j] = __fsub_rn(o.v[j], ce[j]);
+                }
+            }
+        }
+        st256(dx + 8ull * i, o);                           // default policy: the next kernel re-reads dx (L2)
+        if (RANGE) {
+#pragma unroll
+            for (int j = 0; j < 8; ++j) { mn = fminf(mn, o.v[j]); mx = fmaxf(mx, o.v[j]); }
+        }
+    }
+    if (!RANGE) return;
+    mn = warp_min(mn);
+    mx = warp_max(mx);
+    const int w = threadIdx.x >> 5, l = threadIdx.x & 31;
+    if (l == 0) { sm[w] = mn; sm[32 + w] = mx; }
+    __syncthreads();
+    if (w == 0) {
+        mn = warp_min(l < NH_THREADS / 32 ? sm[l] : QB_INF);
+        mx = warp_max(l < NH_THREADS / 32 ? sm[32 + l] : -QB_INF);
+        if (l == 0) {
+            A.pmin[blockIdx.x] = mn;
+            A.pmax[blockIdx.x] = mx;
+            __threadfence();
+            last = (atomicAdd(A.counter, 1u) == gridDim.x - 1);
+        }
+    }
+    __syncthreads();
+    if (!last) return;
+    __threadfence();
+    mn = QB_INF;
+    mx = -QB_INF;
+    for (int i = threadIdx.x; i < (int)gridDim.x; i += NH_THREADS) {
+        mn = fminf(mn, __ldcg(&A.pmin[i]));
+        mx = fmaxf(mx, __ldcg(&A.pmax[i]));
+    }
+    mn = warp_min(mn);
+    mx = warp_max(mx);
+    __syncthreads();
+    if (l == 0) { sm[w] = mn; sm[32 + w] = mx; }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        for (int q = 1; q < NH_THREADS / 32; ++q) { mn = fminf(mn, sm[q]); mx = fmaxf(mx, sm[32 + q]); }
+        A.range_out[0] = mn;
+        A.range_out[1] = mx;
+        *A.counter = 0u;
+    }
+}
+
+template <int NOISE>
+static void launch_bwd_apply_fused(int grid, cudaStream_t st, const float* g, float* dx, uint32_t noct, const BwdApplyArgs& A,
+                                   const GradQuantArg& ga) {
+    if (A.range_out) k_rbn_bwd_apply_fused<NOISE, true><<<grid, NH_THREADS, 0, st>>>(g, dx, noct, A, ga);
+    else k_rbn_bwd_apply_fused<NOISE, false><<<grid, NH_THREADS, 0, st>>>(g, dx, noct, A, ga);
+}
+
+/* Fused variant used when C % 8 == 0: g_range != NULL quantizes g on the fly (as in qb_rangebn_bwd_reduce_nhwc);
+ * amax_kc / amin_kc are the [chunk][channel] arg tables of qb_rangebn_stats_nhwc; dx_range_out (float[2], optional)
+ * receives min/max of dx; mm_ws: qb_minmax_ws_bytes() bytes, zero-filled once. */
+extern "C" int qb_rangebn_bwd_apply_fused_nhwc(const float* g, float* dx, int64_t B, int64_t C, int64_t HW, int num_chunks,
+                                               const float* qscale, const float* qgamma, const float* coef_a,
+                                               const float* coef_e, const int32_t* amax_kc, const int32_t* amin_kc,
+                                               const float* g_range, int g_bits, const float* noise, int stochastic,
+                                               uint64_t seed, uint64_t offset, const uint64_t* step_dev,
+                                               float* dx_range_out, void* mm_ws, size_t mm_ws_bytes, void* stream) {
+    QB_CHECK_ARG(g && dx && qscale && coef_a, "qb_rangebn_bwd_apply_fused_nhwc: null pointer");
+    QB_CHECK_ARG(B > 0 && C > 0 && HW > 0, "qb_rangebn_bwd_apply_fused_nhwc: bad shape");
+    QB_CHECK_ARG(!g_range || (g_bits >= 1 && g_bits <= 24), "qb_rangebn_bwd_apply_fused_nhwc: g_bits=%d", g_bits);
+    const int64_t R = B * HW, n = R * C;
+    const uintptr_t al = reinterpret_cast<uintptr_t>(g) | reinterpret_cast<uintptr_t>(dx) | reinterpret_cast<uintptr_t>(noise);
+    if (C % 8 != 0 || (al & 31) != 0 || (offset & 7) != 0 || n >= 4294967296LL) {
+        qb_set_error("qb_rangebn_bwd_apply_fused_nhwc: needs C %% 8 == 0, 32-byte aligned tensors, < 2^32 elements");
+        return QB_ERR_UNSUPPORTED;
+    }
+    const bool scatter = coef_e && amax_kc && amin_kc && num_chunks > 0;
+    QB_CHECK_ARG(!scatter || R % num_chunks == 0, "qb_rangebn_bwd_apply_fused_nhwc: rows not divisible by chunks");
+    QB_CHECK_ARG(!dx_range_out || (mm_ws && mm_ws_bytes >= (size_t)(2 * 4096 + 16) * 4),
+                 "qb_rangebn_bwd_apply_fused_nhwc: range output needs the min/max workspace");
+    BwdApplyArgs A;
+    A.qgamma = qgamma; A.qscale = qscale; A.coef_a = coef_a; A.coef_e = coef_e;
+    A.amax_kc = scatter ? amax_kc : nullptr; A.amin_kc = scatter ? amin_kc : nullptr;
+    A.C = (uint32_t)C;
+    A.dC = make_fastdiv((uint32_t)C);
+    A.dL = make_fastdiv((uint32_t)(scatter ? R / num_chunks : 1));
+    A.range_out = dx_range_out;
+    float* wsf = static_cast<float*>(mm_ws);
+    A.pmin = wsf; A.pmax = wsf ? wsf + 4096 : nullptr;
+    A.counter = wsf ? reinterpret_cast<unsigned int*>(wsf + 8192) : nullptr;
+    const int nm = grad_noise_mode(g_range, noise, stochastic);
+    GradQuantArg ga{g_range, g_bits, nm, NoiseArg{noise, seed, offset, step_dev}};
+    int grid = nh_grid(n >> 3);
+    if (grid > 4096) grid = 4096;
+    cudaStream_t st = qb_stream(stream);
+    if (nm < 0) launch_bwd_apply_fused<-1>(grid, st, g, dx, (uint32_t)(n >> 3), A, ga);
+    else if (nm == NOISE_NONE) launch_bwd_apply_fused<NOISE_NONE>(grid, st, g, dx, (uint32_t)(n >> 3), A, ga);
+    else if (nm == NOISE_INJECT) launch_bwd_apply_fused<NOISE_INJECT>(grid, st, g, dx, (uint32_t)(n >> 3), A, ga);
+    else launch_bwd_apply_fused<NOISE_PHILOX>(grid, st, g, dx, (uint32_t)(n >> 3), A, ga);
+    QB_LAUNCH_CHECK();
+    return QB_OK;
+}
+
 extern "C" int qb_rangebn_bwd_apply_nhwc(const float* gq, float* dx, int64_t B, int64_t C, int64_t HW, int num_chunks,
                                          const float* qscale, const float* qgamma, const float* coef_a,
                                          const float* coef_e, const int32_t* amax, const int32_t* amin, void* stream) {
     QB_CHECK_ARG(gq && dx && qscale && coef_a, "qb_rangebn_bwd_apply_nhwc: null pointer");
     QB_CHECK_ARG(B > 0 && C > 0 && HW > 0, "qb_rangebn_bwd_apply_nhwc: bad shape");
     cudaStream_t st = qb_stream(stream);
-    int rc = launch_apply_nhwc<1>("qb_rangebn_bwd_apply_nhwc", gq, dx, B * HW, C, NhwcVecs{qgamma, qscale, coef_a, nullptr}, st);
+    int rc = launch_apply_nhwc<1>("qb_rangebn_bwd_apply_nhwc", gq, dx, B * HW, C, NhwcVecs{qgamma, qscale, coef_a, nullptr, nullptr, 0}, st);
     if (rc) return rc;
     if (coef_e && amax && amin && num_chunks > 0) {
         const int64_t t = C * num_chunks;

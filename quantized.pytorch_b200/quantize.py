@@ -82,18 +82,49 @@ def set_stat_reducer(reducer):
     return prev
 
 
-def _quantize_gradient(g, bits, stochastic=True):
-    """UniformQuantizeGrad.backward (quantize.py:124-139): global min/max, zero-point stochastic quantizer."""
-    g = _abi._f32c(g, "grad")
+# Producer-supplied gradient ranges.  RangeBN's backward kernel computes min/max of the dx it writes; the QConv2d in
+# front of it needs exactly that range for its own gradient quantizer (quantize.py:126,132).  The producer stashes
+# (dx, range) here; the consumer takes it if - and only if - the gradient it receives is that very tensor (same
+# storage, shape, strides and version; the strong reference keeps the storage from being recycled meanwhile).
+_grad_ranges = {}
+
+
+def _stash_grad_range(t, rng):
+    if len(_grad_ranges) >= 4:
+        _grad_ranges.clear()
+    _grad_ranges[t.data_ptr()] = (t, t._version, rng)
+
+
+def _take_grad_range(g):
+    ent = _grad_ranges.pop(g.data_ptr(), None)
+    if ent is None:
+        return None
+    t, ver, rng = ent
+    if t.shape == g.shape and t.stride() == g.stride() and t.dtype == g.dtype and g._version == ver:
+        return rng
+    return None
+
+
+def _grad_noise(g, stochastic):
     noise = _noise_provider(tuple(g.shape)) if (stochastic and _noise_provider is not None) else None
     if noise is not None and _abi.is_nhwc(g):
         noise = noise.reshape(g.shape).contiguous(memory_format=torch.channels_last)   # same logical element <-> same noise
-    if _reducer is None:
+    return noise
+
+
+def _quantize_gradient(g, bits, stochastic=True):
+    """UniformQuantizeGrad.backward (quantize.py:124-139): global min/max, zero-point stochastic quantizer."""
+    g = _abi._f32c(g, "grad")
+    noise = _grad_noise(g, stochastic)
+    r = _take_grad_range(g)
+    if _reducer is None and r is None:
         out, _ = _abi.fakequant_grad_fused(g, bits, noise=noise, stochastic=stochastic, seed=_next_seed(),
                                            step_dev=noise_step(g.device))
         return out
-    r = _abi.minmax(g)
-    _reducer.grad_range(r)
+    if r is None:
+        r = _abi.minmax(g)
+    if _reducer is not None:
+        _reducer.grad_range(r)
     return _abi.fakequant_grad(g, bits, range_dev=r, noise=noise, stochastic=stochastic, seed=_next_seed(),
                                step_dev=noise_step(g.device))
 
@@ -578,47 +609,70 @@ class QLinear(nn.Linear, _QBase):
 # RangeBN                                                                    (quantize.py:435-505)
 # ---------------------------------------------------------------------------------------------------
 class _RangeBNFn(Function):
-    """Statistics + normalisation of the (already fake-quantized) input and, in backward, the output-gradient
-    quantizer followed by the closed-form gradient of :467-499 (rangebn.cu)."""
+    """Statistics + normalisation of the fake-quantized input and, in backward, the output-gradient quantizer
+    followed by the closed-form gradient of :467-499 (rangebn.cu / rangebn_nhwc.cu).
+
+    Channels-last fusion (``q_range`` given): ``x`` is the RAW input and QuantMeasure's fake-quant (:463) runs inside
+    the statistics / apply / backward-reduce kernels, so x_hat never exists in HBM; with C % 8 == 0 the gradient
+    quantizer runs inside the two backward passes as well and the dx range is handed to the preceding QConv2d."""
 
     @staticmethod
-    def forward(ctx, xq, gamma, beta, running_mean, running_var, training, momentum, num_chunks, eps, bits, bits_grad):
+    def forward(ctx, xq, gamma, beta, running_mean, running_var, training, momentum, num_chunks, eps, bits, bits_grad,
+                q_range, q_bits):
         xq = _abi._f32c(xq, "x")
         nhwc = _abi.is_nhwc(xq)
         B, Cn = xq.shape[0], xq.shape[1]
         HW = xq.numel() // (B * Cn)
         count, chunk_len, chunks_global = float(B * HW), 0.0, num_chunks
         red = amax = amin = None
+        ctx.local_chunks = num_chunks
         if training:
             local_chunks = num_chunks
             if _reducer is not None:
                 local_chunks, count = _reducer.rangebn_layout(B, HW, num_chunks)
             want_arg = any(ctx.needs_input_grad[:3])
-            red, amax, amin = _abi.rangebn_stats(xq, B, Cn, HW, local_chunks, want_arg=want_arg, nhwc=nhwc)
+            red, amax, amin = _abi.rangebn_stats(xq, B, Cn, HW, local_chunks, want_arg=want_arg, nhwc=nhwc,
+                                                 q_range=q_range, q_bits=q_bits)
             if _reducer is not None:
                 _reducer.rangebn(red)
             chunk_len = count / chunks_global
             ctx.local_chunks = local_chunks
         vec = _abi.rangebn_finalize(red, Cn, chunks_global, count, chunk_len, eps, momentum, training, bits, gamma, beta,
                                     running_mean, running_var)
-        out = _abi.rangebn_apply(xq, B, Cn, HW, vec, gamma is not None, beta is not None, nhwc=nhwc)
+        out = _abi.rangebn_apply(xq, B, Cn, HW, vec, gamma is not None, beta is not None, nhwc=nhwc, q_range=q_range,
+                                 q_bits=q_bits)
         ctx.dims = (B, Cn, HW, chunks_global, count, chunk_len, training, bits_grad, gamma is not None, beta is not None)
-        ctx.nhwc = nhwc
-        ctx.save_for_backward(xq, vec, amax, amin)
+        ctx.nhwc, ctx.q_bits = nhwc, q_bits
+        ctx.save_for_backward(xq, vec, amax, amin, q_range)
         return out
 
     @staticmethod
     def backward(ctx, g):
-        xq, vec, amax, amin = ctx.saved_tensors
+        xq, vec, amax, amin, q_range = ctx.saved_tensors
         B, Cn, HW, K, count, chunk_len, training, bits_grad, has_gamma, has_beta = ctx.dims
         g = g.contiguous(memory_format=torch.channels_last) if ctx.nhwc else g.contiguous()
-        gq = _quantize_gradient(g, bits_grad) if bits_grad is not None else g
         hook = _reducer.rangebn_bwd if (_reducer is not None and training) else None
-        dx, dgamma, dbeta = _abi.rangebn_backward(gq, xq, B, Cn, HW, ctx.local_chunks if training else 0, count,
-                                                  chunk_len, training, vec, has_gamma, amax, amin, reduce_hook=hook,
-                                                  chunks_global=K, nhwc=ctx.nhwc)
+        common = dict(reduce_hook=hook, chunks_global=K, nhwc=ctx.nhwc, q_range=q_range, q_bits=ctx.q_bits)
+        lc = ctx.local_chunks if training else 0
+        if ctx.nhwc and Cn % 8 == 0 and g.numel() < 2 ** 32 and g.data_ptr() % 32 == 0 and xq.data_ptr() % 32 == 0:
+            gquant = None
+            if bits_grad is not None:
+                g = _abi._f32c(g, "grad")
+                r = _abi.minmax(g)
+                if _reducer is not None:
+                    _reducer.grad_range(r)
+                gquant = dict(range=r, bits=bits_grad, noise=_grad_noise(g, True), stochastic=True, seed=_next_seed(),
+                              step_dev=noise_step(g.device))
+            dx, dgamma, dbeta, dx_range = _abi.rangebn_backward(g, xq, B, Cn, HW, lc, count, chunk_len, training, vec,
+                                                                has_gamma, amax, amin, grad_quant=gquant,
+                                                                want_dx_range=True, **common)
+            _stash_grad_range(dx, dx_range)
+        else:
+            gq = _quantize_gradient(g, bits_grad) if bits_grad is not None else g
+            dx, dgamma, dbeta = _abi.rangebn_backward(gq, xq, B, Cn, HW, lc, count, chunk_len, training, vec, has_gamma,
+                                                      amax, amin, **common)
         return (dx if ctx.needs_input_grad[0] else None, dgamma if has_gamma else None, dbeta if has_beta else None,
-                None, None, None, None, None, None, None, None)
+                None, None, None, None, None, None, None, None, None, None)
 
 
 class RangeBN(nn.Module):
@@ -651,13 +705,18 @@ class RangeBN(nn.Module):
             self.bias.data.zero_()
 
     def forward(self, x):
-        x = self.quantize_input(x)
         two_d = x.dim() == 2
         if two_d:
             x = x.unsqueeze(-1).unsqueeze(-1)
+        qi = self.quantize_input
+        q_range, q_bits = None, 0
+        if x.dim() == 4 and x.is_cuda and x.dtype == torch.float32 and _abi.is_nhwc(x) and qi.enable_quant:
+            q_range, q_bits = qi.measure(x), qi.num_bits     # the fake-quant itself runs inside the RangeBN kernels
+        else:
+            x = qi(x)
         out = _RangeBNFn.apply(x, self.weight, self.bias, self.running_mean, self.running_var, self.training,
-                               self.momentum, self.num_chunks, self.eps, self.num_bits, self.num_bits_grad)
-        if out.size(3) == 1 and out.size(2) == 1:
+                               self.momentum, self.num_chunks, self.eps, self.num_bits, self.num_bits_grad, q_range, q_bits)
+        if two_d:
             out = out.squeeze(-1).squeeze(-1)
         return out
 
