@@ -55,7 +55,7 @@ PROTOTYPES = {
     "qb_gemm_i8": (_i32, [_p, _p, _p, _i64, _i64, _i64, _i64, _p, _i32, _p, _p, _i32, _p, _p, _p, _i32, _p]),
     "qb_fakequant_rows_conv": (_i32, [_p, _p, _p, _p, _i64, _i64, _i32, _i32, _p, _p, _i32, _p]),
     "qb_conv_i8_fwd": (_i32, [_p, _p, _p, _i64, _i64, _i64, _i64, _i64, _i32, _i32, _i32, _i32, _p, _i32, _p, _p, _i32,
-                              _p, _p, _p, _p]),
+                              _p, _p, _p, _p, _p]),
 }
 
 _lib = None
@@ -94,7 +94,7 @@ _profile = None       # list of (name, algorithmic_bytes, start_event, end_event
 
 # kernels enqueued per C call
 _NLAUNCH = {"qb_rangebn_stats": 2, "qb_rangebn_bwd_reduce": 2, "qb_rangebn_bwd_apply": 2,
-            "qb_rangebn_stats_nhwc": 3, "qb_rangebn_bwd_reduce_nhwc": 2, "qb_rangebn_bwd_apply_nhwc": 2}
+            "qb_conv_i8_fwd": 2, "qb_rangebn_stats_nhwc": 3, "qb_rangebn_bwd_reduce_nhwc": 2, "qb_rangebn_bwd_apply_nhwc": 2}
 
 
 def _run(name, nbytes, *args):
@@ -433,7 +433,8 @@ def conv_i8_fwd(x_codes, w_codes, B, H, W, Cin, Cout, kh, kw, stride, pad, a_ran
     """-> fp32 output, logical shape [B, Cout, Ho, Wo] stored channels-last."""
     Ho, Wo = (H + 2 * pad - kh) // stride + 1, (W + 2 * pad - kw) // stride + 1
     out = torch.empty((B, Cout, Ho, Wo), dtype=torch.float32, device=x_codes.device, memory_format=torch.channels_last)
+    boxsum = torch.empty(B * Ho * Wo, dtype=torch.int32, device=x_codes.device)
     _run("qb_conv_i8_fwd", B * H * W * Cin + Cout * kh * kw * Cin + 4 * B * Ho * Wo * Cout, _ptr(x_codes), _ptr(w_codes),
          _ptr(out), B, H, W, Cin, Cout, kh, kw, stride, pad, _ptr(a_range), int(a_bits), _ptr(row_min), _ptr(row_max),
-         int(w_bits), _ptr(pixsum), _ptr(tapsum), _ptr(bias), _stream())
+         int(w_bits), _ptr(pixsum), _ptr(boxsum), _ptr(tapsum), _ptr(bias), _stream())
     return out

@@ -33,7 +33,7 @@ struct ConvEpilogue {
     const float* w_row_min;     // per output channel (QB_SCALE_FLOAT)
     const float* w_row_max;
     int w_bits;
-    const int32_t* pixsum;      // P[B*H*W]
+    const int32_t* boxsum;      // S[B*Ho*Wo] = SUM over the in-bounds taps of the per-pixel code sums (k_conv_boxsum)
     const int32_t* tapsum;      // T[Cout][kh*kw]
     const float* bias;          // fake-quantized bias or nullptr
 };
@@ -50,30 +50,35 @@ __device__ __forceinline__ uint64_t umma_smem_desc(uint32_t smem_addr, int bk) {
     return d;
 }
 
+constexpr int CV_STAGING_BYTES = 2 * 128 * 128;     // two [128 rows][32 fp32] output staging buffers (128-byte swizzle)
+
+__device__ __forceinline__ void epi_bar() { asm volatile("bar.sync 1, 128;" ::: "memory"); }
+
 // Persistent kernel: gridDim.x CTAs (one per SM) walk the tile list t = blockIdx.x, += gridDim.x; tiles are ordered with
 // the output-channel tile slowest so a CTA's per-channel coefficients rarely change.  Three asynchronous roles:
 //   warp 0   TMA producer: keeps the shared-memory ring full ACROSS tile boundaries
 //   warp 1   MMA issuer  : accumulates tile j into TMEM buffer j&1 (2 x BN columns allocated)
-//   warps 2-5 epilogue   : drain buffer j&1 (tcgen05.ld), dequantise, store - overlapped with the MMAs of tile j+1
+//   warps 2-5 epilogue   : drain buffer j&1 (tcgen05.ld) 32 columns at a time, dequantise, park the [rows][32] slab in
+//                          a swizzled shared-memory staging buffer and hand it to a TMA store (coalesced 128-byte rows,
+//                          ragged tile edges clipped by the hardware) - overlapped with the MMAs of tile j+1
 template <int BN>
 __global__ void __launch_bounds__(CV_THREADS, 1)
-k_conv_i8(const __grid_constant__ CUtensorMap tmap_x, const __grid_constant__ CUtensorMap tmap_w, float* __restrict__ out,
-          ConvGeom g, ConvEpilogue ep) {
+k_conv_i8(const __grid_constant__ CUtensorMap tmap_x, const __grid_constant__ CUtensorMap tmap_w,
+          const __grid_constant__ CUtensorMap tmap_o, ConvGeom g, ConvEpilogue ep) {
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
     const uint32_t a_bytes = 128u * g.BK, b_bytes = (uint32_t)BN * g.BK, stage_bytes = a_bytes + b_bytes;
-    uint8_t* tail = smem + (size_t)g.stages * stage_bytes;
+    float* staging = reinterpret_cast<float*>(smem + (size_t)g.stages * stage_bytes);          // 1024-byte aligned
+    uint8_t* tail = reinterpret_cast<uint8_t*>(staging) + CV_STAGING_BYTES;
     uint64_t* full_bar = reinterpret_cast<uint64_t*>(tail);
     uint64_t* empty_bar = full_bar + 8;
     uint64_t* tfull_bar = empty_bar + 8;                       // [2] accumulator buffer ready
     uint64_t* tempty_bar = tfull_bar + 2;                      // [2] accumulator buffer drained
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty_bar + 2);
-    float* s_c1 = reinterpret_cast<float*>(tail + 256);       // sa*sw[n]
-    float* s_c2 = s_c1 + BN;                                   // sa*lw'[n]
-    float* s_c3 = s_c2 + BN;                                   // la*sw[n]
+    float4* s_coef = reinterpret_cast<float4*>(tail + 256);   // {sa*sw[n], sa*lw'[n], bias[n], la*(sw*Tall + lw'*K)}
+    float* s_c3 = reinterpret_cast<float*>(s_coef + BN);      // la*sw[n]      (border pixels of inputs with min != 0)
     float* s_c4 = s_c3 + BN;                                   // la*lw'[n]
-    float* s_bias = s_c4 + BN;
-    int32_t* s_tap = reinterpret_cast<int32_t*>(s_bias + BN);  // [BN][taps]
+    int32_t* s_tap = reinterpret_cast<int32_t*>(s_c4 + BN);   // [BN][taps]
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int taps = g.kh * g.kw;
@@ -87,6 +92,7 @@ k_conv_i8(const __grid_constant__ CUtensorMap tmap_x, const __grid_constant__ CU
     if (warp == 0 && lane == 0) {
         tma_prefetch_desc(&tmap_x);
         tma_prefetch_desc(&tmap_w);
+        tma_prefetch_desc(&tmap_o);
         for (int s = 0; s < g.stages; ++s) {
             mbar_init(&full_bar[s], 1);
             mbar_init(&empty_bar[s], 1);
@@ -113,17 +119,19 @@ k_conv_i8(const __grid_constant__ CUtensorMap tmap_x, const __grid_constant__ CU
                 const int tw_i = tm % g.tiles_w; tm /= g.tiles_w;
                 const int th_i = tm % g.tiles_h; tm /= g.tiles_h;
                 const int b0 = tm * g.TN, ho0 = th_i * g.TH, wo0 = tw_i * g.TW, n0 = tn * BN;
-                for (int tap = 0; tap < taps; ++tap) {
-                    const int r = tap / g.kw, s_ = tap - r * g.kw;
-                    for (int cb = 0; cb < cblocks; ++cb, ++it) {
-                        const int s = it % g.stages;
-                        const uint32_t ph = (it / g.stages) & 1;
-                        mbar_wait(&empty_bar[s], ph ^ 1);
-                        mbar_arrive_expect_tx(&full_bar[s], (uint32_t)(g.TN * g.TH * g.TW * g.BK) + b_bytes);
-                        uint8_t* sa = smem + (size_t)s * stage_bytes;
-                        tma_load_4d(sa, &tmap_x, &full_bar[s], cb * g.BK, wo0 * g.stride - g.pad + s_,
-                                    ho0 * g.stride - g.pad + r, b0);
-                        tma_load_2d(sa + a_bytes, &tmap_w, &full_bar[s], tap * g.Cin + cb * g.BK, n0);
+                for (int r = 0; r < g.kh; ++r) {
+                    for (int s_ = 0; s_ < g.kw; ++s_) {
+                        const int tap = r * g.kw + s_;
+                        for (int cb = 0; cb < cblocks; ++cb, ++it) {
+                            const int s = it % g.stages;
+                            const uint32_t ph = (it / g.stages) & 1;
+                            mbar_wait(&empty_bar[s], ph ^ 1);
+                            mbar_arrive_expect_tx(&full_bar[s], (uint32_t)(g.TN * g.TH * g.TW * g.BK) + b_bytes);
+                            uint8_t* sa = smem + (size_t)s * stage_bytes;
+                            tma_load_4d(sa, &tmap_x, &full_bar[s], cb * g.BK, wo0 * g.stride - g.pad + s_,
+                                        ho0 * g.stride - g.pad + r, b0);
+                            tma_load_2d(sa + a_bytes, &tmap_w, &full_bar[s], tap * g.Cin + cb * g.BK, n0);
+                        }
                     }
                 }
             }
@@ -164,10 +172,15 @@ k_conv_i8(const __grid_constant__ CUtensorMap tmap_x, const __grid_constant__ CU
         const double sa = (double)pa.scale, la = (double)pa.lo;
         const bool need_la = pa.lo != 0.0f;
         const int per_img = g.TH * g.TW;
-        const int i = sub * 32 + lane;
+        const int i = sub * 32 + lane;                              // row of the tile = TMEM lane = staging row
         const int nl = i / per_img, rem = i - nl * per_img;
         const int th = rem / g.TW, tw = rem - th * g.TW;
+        const bool in_box = nl < g.TN;
+        const uint32_t stage_u32 = smem_u32(staging);
+        const uint32_t row_off = (uint32_t)i * 128u, sw = (uint32_t)(i & 7);
+        const float kfull = (float)(taps * g.Cin);
         int cur_tn = -1, j = 0;
+        uint32_t slab = 0;                                          // running count of staged slabs (buffer = slab & 1)
         for (int t = blockIdx.x; t < total_tiles; t += gridDim.x, ++j) {
             const int tn = t / tiles_m;
             int tm = t - tn * tiles_m;
@@ -175,88 +188,130 @@ k_conv_i8(const __grid_constant__ CUtensorMap tmap_x, const __grid_constant__ CU
             const int th_i = tm % g.tiles_h; tm /= g.tiles_h;
             const int b0 = tm * g.TN, ho0 = th_i * g.TH, wo0 = tw_i * g.TW, n0 = tn * BN;
             if (tn != cur_tn) {                                      // per-channel coefficients of this channel tile
-                asm volatile("bar.sync 1, 128;" ::: "memory");      // everyone is done with the previous ones
+                epi_bar();                                           // everyone is done with the previous ones
                 for (int jn = et; jn < BN; jn += 128) {
                     const int n = n0 + jn;
-                    float c1 = 0.f, c2 = 0.f, c3 = 0.f, c4 = 0.f, bs = 0.f;
+                    float4 cf = make_float4(0.f, 0.f, 0.f, 0.f);
+                    float c3 = 0.f, c4 = 0.f;
                     if (n < g.Cout) {
                         const QParams pw = make_qparams_f(__ldg(ep.w_row_min + n), __ldg(ep.w_row_max + n), ep.w_bits);
-                        const double sw = (double)pw.scale,
+                        const double swd = (double)pw.scale,
                                      lw = (double)pw.lo + (double)(1 << (ep.w_bits - 1)) * (double)pw.scale;
-                        c1 = (float)(sa * sw); c2 = (float)(sa * lw); c3 = (float)(la * sw); c4 = (float)(la * lw);
-                        bs = ep.bias ? __ldg(ep.bias + n) : 0.f;
-                        for (int tp = 0; tp < taps; ++tp) s_tap[jn * taps + tp] = __ldg(ep.tapsum + (int64_t)n * taps + tp);
+                        int tall = 0;
+                        for (int tp = 0; tp < taps; ++tp) {
+                            const int v = __ldg(ep.tapsum + (int64_t)n * taps + tp);
+                            s_tap[jn * taps + tp] = v;
+                            tall += v;
+                        }
+                        cf.x = (float)(sa * swd);
+                        cf.y = (float)(sa * lw);
+                        cf.z = ep.bias ? __ldg(ep.bias + n) : 0.f;
+                        c3 = (float)(la * swd);
+                        c4 = (float)(la * lw);
+                        cf.w = fmaf(c3, (float)tall, c4 * kfull);
                     }
-                    s_c1[jn] = c1; s_c2[jn] = c2; s_c3[jn] = c3; s_c4[jn] = c4; s_bias[jn] = bs;
+                    s_coef[jn] = cf; s_c3[jn] = c3; s_c4[jn] = c4;
                 }
-                asm volatile("bar.sync 1, 128;" ::: "memory");
+                epi_bar();
                 cur_tn = tn;
             }
             // this thread's output pixel of the tile
             const int b = b0 + nl, ho = ho0 + th, wo = wo0 + tw;
-            const bool valid = (nl < g.TN) && (b < g.B) && (ho < g.Ho) && (wo < g.Wo);
-            float rs_a = 0.f, kvalid = 0.f;
+            const bool valid = in_box && (b < g.B) && (ho < g.Ho) && (wo < g.Wo);
+            float rs_a = 0.f, kvalid = kfull;
             uint32_t mask = 0;
+            bool interior = true;
             if (valid) {
-                int cnt = 0, acc = 0;
-                for (int tp = 0; tp < taps; ++tp) {
-                    const int r = tp / g.kw, s_ = tp - r * g.kw;
-                    const int hi = ho * g.stride - g.pad + r, wi = wo * g.stride - g.pad + s_;
-                    if (hi >= 0 && hi < g.H && wi >= 0 && wi < g.W) {
-                        mask |= 1u << tp;
-                        ++cnt;
-                        acc += __ldg(ep.pixsum + ((int64_t)b * g.H + hi) * g.W + wi);
-                    }
+                rs_a = (float)__ldg(ep.boxsum + ((int64_t)b * g.Ho + ho) * g.Wo + wo);
+                if (need_la) {
+                    int cnt = 0;
+                    for (int r = 0; r < g.kh; ++r)
+                        for (int s_ = 0; s_ < g.kw; ++s_) {
+                            const int hi = ho * g.stride - g.pad + r, wi = wo * g.stride - g.pad + s_;
+                            if (hi >= 0 && hi < g.H && wi >= 0 && wi < g.W) { mask |= 1u << (r * g.kw + s_); ++cnt; }
+                        }
+                    interior = cnt == taps;
+                    kvalid = (float)(cnt * g.Cin);
                 }
-                rs_a = (float)acc;
-                kvalid = (float)(cnt * g.Cin);
             }
-            const bool interior = mask == ((1u << taps) - 1u);
-            float* dst = out + (((int64_t)b * g.Ho + ho) * g.Wo + wo) * g.Cout + n0;
+            const int ncols = (g.Cout - n0 < BN) ? g.Cout - n0 : BN;
+            const int nslabs = (ncols + 31) >> 5;
             const int buf = j & 1;
             mbar_wait(&tfull_bar[buf], (j >> 1) & 1);
             tc_fence_after_sync();
             const uint32_t t_addr = tmem_base + (uint32_t)(buf * BN) + ((uint32_t)(sub * 32) << 16);
 #pragma unroll 1
-            for (int c = 0; c < BN; c += 32) {
+            for (int cs = 0; cs < nslabs; ++cs, ++slab) {
+                const int c = cs * 32;
                 uint32_t r[32];
                 tmem_ld_32x32(t_addr + (uint32_t)c, r);
+                if (et == 0) tma_store_wait_read<1>();               // the store that used this staging buffer is done reading
+                epi_bar();
                 tmem_ld_wait();
-                if (c + 32 >= BN) {                                  // last read of this buffer: hand it back to the MMA warp
+                if (cs == nslabs - 1) {                              // last read of this accumulator: hand it back to the MMA warp
                     tc_fence_before_sync();
                     __syncwarp();
                     if (lane == 0) mbar_arrive(&tempty_bar[buf]);
                 }
+                const uint32_t dst = stage_u32 + (slab & 1u) * (128u * 128u) + row_off;
                 if (valid) {
+                    const float base2 = rs_a;
 #pragma unroll
                     for (int q = 0; q < 32; ++q) {
-                        const int jn = c + q;
-                        float v = fmaf(s_c1[jn], (float)(int32_t)r[q], fmaf(s_c2[jn], rs_a, s_bias[jn]));
-                        if (need_la) {
-                            int tsum = 0;
-                            for (int tp = 0; tp < taps; ++tp)
-                                if (interior || ((mask >> tp) & 1u)) tsum += s_tap[jn * taps + tp];
-                            v += fmaf(s_c3[jn], (float)tsum, s_c4[jn] * kvalid);
-                        }
-                        r[q] = __float_as_uint(v);
+                        const float4 cf = s_coef[c + q];
+                        r[q] = __float_as_uint(fmaf(cf.x, (float)(int32_t)r[q], fmaf(cf.y, base2, cf.z)));
                     }
-                    if (n0 + c + 32 <= g.Cout && (g.Cout & 3) == 0) {
+                    if (need_la) {
 #pragma unroll
-                        for (int q = 0; q < 32; q += 4)
-                            __stcs(reinterpret_cast<float4*>(dst + c + q),
-                                   make_float4(__uint_as_float(r[q]), __uint_as_float(r[q + 1]), __uint_as_float(r[q + 2]),
-                                               __uint_as_float(r[q + 3])));
-                    } else {
-                        for (int q = 0; q < 32; ++q)
-                            if (n0 + c + q < g.Cout) dst[c + q] = __uint_as_float(r[q]);
+                        for (int q = 0; q < 32; ++q) {
+                            float add = s_coef[c + q].w;
+                            if (!interior) {
+                                int tsum = 0;
+#pragma unroll 1
+                                for (int tp = 0; tp < taps; ++tp)
+                                    if ((mask >> tp) & 1u) tsum += s_tap[(c + q) * taps + tp];
+                                add = fmaf(s_c3[c + q], (float)tsum, s_c4[c + q] * kvalid);
+                            }
+                            r[q] = __float_as_uint(__uint_as_float(r[q]) + add);
+                        }
                     }
+#pragma unroll
+                    for (int q = 0; q < 8; ++q)
+                        asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(dst + (((uint32_t)q ^ sw) << 4)),
+                                     "r"(r[4 * q]), "r"(r[4 * q + 1]), "r"(r[4 * q + 2]), "r"(r[4 * q + 3]) : "memory");
+                }
+                fence_proxy_async();
+                epi_bar();
+                if (et == 0) {
+                    tma_store_4d(&tmap_o, reinterpret_cast<uint8_t*>(staging) + (slab & 1u) * (128u * 128u), n0 + c, wo0, ho0, b0);
+                    tma_store_commit();
                 }
             }
         }
+        if (et == 0) tma_store_wait<0>();
     }
     tc_fence_before_sync();
     __syncthreads();
     if (warp == 1) tmem_dealloc<TMEM_COLS>(tmem_base);
+}
+
+// S[b,ho,wo] = SUM over the in-bounds filter taps of P[b,hi,wi] (P = per-pixel sums of the input codes): the row sums
+// of the implicit im2col matrix, zero padding excluded.  One thread per output pixel; P is L2 resident.
+__global__ void k_conv_boxsum(const int32_t* __restrict__ P, int32_t* __restrict__ S, int B, int H, int W, int Ho, int Wo,
+                              int kh, int kw, int stride, int pad) {
+    const int64_t m = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (m >= (int64_t)B * Ho * Wo) return;
+    const int wo = (int)(m % Wo), ho = (int)((m / Wo) % Ho), b = (int)(m / ((int64_t)Wo * Ho));
+    int acc = 0;
+    for (int r = 0; r < kh; ++r) {
+        const int hi = ho * stride - pad + r;
+        if (hi < 0 || hi >= H) continue;
+        for (int s = 0; s < kw; ++s) {
+            const int wi = wo * stride - pad + s;
+            if (wi >= 0 && wi < W) acc += __ldg(P + ((int64_t)b * H + hi) * W + wi);
+        }
+    }
+    S[m] = acc;
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -325,12 +380,13 @@ extern "C" int qb_fakequant_rows_conv(const float* w, float* wq, uint8_t* codes_
 // ------------------------------------------------------------------------------------------------
 // host launcher
 // ------------------------------------------------------------------------------------------------
+static size_t conv_tail_bytes(int BN, int taps) { return 256 + (size_t)BN * 24 + (size_t)BN * taps * 4; }
+
 template <int BN>
-static int launch_conv(const CUtensorMap& tx, const CUtensorMap& tw, float* out, const ConvGeom& g, const ConvEpilogue& ep,
-                       cudaStream_t st) {
+static int launch_conv(const CUtensorMap& tx, const CUtensorMap& tw, const CUtensorMap& to, const ConvGeom& g,
+                       const ConvEpilogue& ep, cudaStream_t st) {
     const size_t stage = (size_t)(128 + BN) * g.BK;
-    const size_t tail = 256 + (size_t)BN * 20 + (size_t)BN * g.kh * g.kw * 4;
-    const size_t smem = (size_t)g.stages * stage + 1024 + tail;
+    const size_t smem = (size_t)g.stages * stage + CV_STAGING_BYTES + 1024 + conv_tail_bytes(BN, g.kh * g.kw);
     static size_t configured = 0;
     if (smem > configured) {
         QB_CUDA(cudaFuncSetAttribute(k_conv_i8<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
@@ -340,7 +396,7 @@ static int launch_conv(const CUtensorMap& tx, const CUtensorMap& tw, float* out,
     int sms = qb_sm_count();
     if (sms <= 0) sms = 148;
     const unsigned grid = (unsigned)(total < sms ? total : sms);       // persistent: one CTA per SM
-    k_conv_i8<BN><<<grid, CV_THREADS, smem, st>>>(tx, tw, out, g, ep);
+    k_conv_i8<BN><<<grid, CV_THREADS, smem, st>>>(tx, tw, to, g, ep);
     QB_LAUNCH_CHECK();
     return QB_OK;
 }
@@ -348,18 +404,20 @@ static int launch_conv(const CUtensorMap& tx, const CUtensorMap& tw, float* out,
 extern "C" int qb_conv_i8_fwd(const uint8_t* x_codes, const uint8_t* w_codes_khwc, float* out, int64_t B, int64_t H,
                               int64_t W, int64_t Cin, int64_t Cout, int kh, int kw, int stride, int pad,
                               const float* a_range, int a_bits, const float* w_row_min, const float* w_row_max, int w_bits,
-                              const int32_t* pixsum, const int32_t* tapsum, const float* bias, void* stream) {
-    QB_CHECK_ARG(x_codes && w_codes_khwc && out && a_range && w_row_min && w_row_max && pixsum && tapsum,
+                              const int32_t* pixsum, int32_t* boxsum_ws, const int32_t* tapsum, const float* bias,
+                              void* stream) {
+    QB_CHECK_ARG(x_codes && w_codes_khwc && out && a_range && w_row_min && w_row_max && pixsum && boxsum_ws && tapsum,
                  "qb_conv_i8_fwd: null pointer");
     QB_CHECK_ARG(B > 0 && H > 0 && W > 0 && Cin > 0 && Cout > 0 && kh > 0 && kw > 0 && stride > 0 && pad >= 0,
                  "qb_conv_i8_fwd: bad shape");
     const int64_t Ho = (H + 2 * pad - kh) / stride + 1, Wo = (W + 2 * pad - kw) / stride + 1;
     if (Cin % 32 != 0 || kh * kw > CV_MAX_TAPS || stride > 2 || Ho < 1 || Wo < 1 || Cout % 16 != 0 ||
-        ((reinterpret_cast<uintptr_t>(x_codes) | reinterpret_cast<uintptr_t>(w_codes_khwc)) & 15) != 0) {
+        ((reinterpret_cast<uintptr_t>(x_codes) | reinterpret_cast<uintptr_t>(w_codes_khwc) | reinterpret_cast<uintptr_t>(out)) & 15) != 0) {
         qb_set_error("qb_conv_i8_fwd: unsupported geometry (need Cin%%32==0, Cout%%16==0, kh*kw<=9, stride<=2, 16-byte "
-                     "aligned codes): Cin=%lld Cout=%lld k=%dx%d stride=%d", (long long)Cin, (long long)Cout, kh, kw, stride);
+                     "aligned tensors): Cin=%lld Cout=%lld k=%dx%d stride=%d", (long long)Cin, (long long)Cout, kh, kw, stride);
         return QB_ERR_UNSUPPORTED;
     }
+    QB_CHECK_ARG(B * Ho * Wo < 2147483647LL && B * H * W < 2147483647LL, "qb_conv_i8_fwd: pixel count exceeds int32");
     ConvGeom g;
     g.B = (int)B; g.H = (int)H; g.W = (int)W; g.Cin = (int)Cin; g.Ho = (int)Ho; g.Wo = (int)Wo; g.Cout = (int)Cout;
     g.kh = kh; g.kw = kw; g.stride = stride; g.pad = pad;
@@ -375,11 +433,18 @@ extern "C" int qb_conv_i8_fwd(const uint8_t* x_codes, const uint8_t* w_codes_khw
     const int BN = Cout >= 256 ? 256 : (Cout >= 128 ? 128 : 64);
     {
         const size_t stage = (size_t)(128 + BN) * g.BK;
-        const size_t tail = 256 + (size_t)BN * 20 + (size_t)BN * kh * kw * 4 + 1024;
-        int s = (int)((220 * 1024 - tail) / stage);
+        const size_t fixed = CV_STAGING_BYTES + 1024 + conv_tail_bytes(BN, kh * kw);
+        int s = (int)((225 * 1024 - fixed) / stage);
         g.stages = s > 8 ? 8 : (s < 2 ? 2 : s);
     }
-    CUtensorMap tx, tw;
+    cudaStream_t st = qb_stream(stream);
+    {
+        const int64_t M = B * Ho * Wo;
+        k_conv_boxsum<<<(unsigned)((M + 255) / 256), 256, 0, st>>>(pixsum, boxsum_ws, (int)B, (int)H, (int)W, (int)Ho, (int)Wo,
+                                                                  kh, kw, stride, pad);
+        QB_LAUNCH_CHECK();
+    }
+    CUtensorMap tx, tw, to;
     {   // activations: dims innermost-first {Cin, W, H, B}
         const uint64_t dims[4] = {(uint64_t)Cin, (uint64_t)W, (uint64_t)H, (uint64_t)B};
         const uint64_t str[3] = {(uint64_t)Cin, (uint64_t)W * Cin, (uint64_t)H * W * Cin};
@@ -395,9 +460,15 @@ extern "C" int qb_conv_i8_fwd(const uint8_t* x_codes, const uint8_t* w_codes_khw
         int rc = qb_make_tmap(&tw, CU_TENSOR_MAP_DATA_TYPE_UINT8, 2, w_codes_khwc, dims, str, box, nullptr, g.BK);
         if (rc) return rc;
     }
-    ConvEpilogue ep{a_range, a_bits, w_row_min, w_row_max, w_bits, pixsum, tapsum, bias};
-    cudaStream_t st = qb_stream(stream);
-    if (BN == 256) return launch_conv<256>(tx, tw, out, g, ep, st);
-    if (BN == 128) return launch_conv<128>(tx, tw, out, g, ep, st);
-    return launch_conv<64>(tx, tw, out, g, ep, st);
+    {   // output fp32 NHWC: dims {Cout, Wo, Ho, B}; one staged slab = 32 channels x the tile's pixels
+        const uint64_t dims[4] = {(uint64_t)Cout, (uint64_t)Wo, (uint64_t)Ho, (uint64_t)B};
+        const uint64_t str[3] = {(uint64_t)Cout * 4, (uint64_t)Wo * Cout * 4, (uint64_t)Ho * Wo * Cout * 4};
+        const uint32_t box[4] = {32u, (uint32_t)g.TW, (uint32_t)g.TH, (uint32_t)g.TN};
+        int rc = qb_make_tmap(&to, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, out, dims, str, box, nullptr, 128);
+        if (rc) return rc;
+    }
+    ConvEpilogue ep{a_range, a_bits, w_row_min, w_row_max, w_bits, boxsum_ws, tapsum, bias};
+    if (BN == 256) return launch_conv<256>(tx, tw, to, g, ep, st);
+    if (BN == 128) return launch_conv<128>(tx, tw, to, g, ep, st);
+    return launch_conv<64>(tx, tw, to, g, ep, st);
 }
