@@ -15,7 +15,8 @@
 // ho0*stride-pad+r, b0) with element strides (1, stride, stride, 1): no im2col buffer exists anywhere.
 #include "tc_common.cuh"
 
-constexpr int CV_THREADS = 192;
+constexpr int CV_THREADS = 320;      // TMA warp, MMA warp, 2 x 4 epilogue warps
+constexpr int CV_MAX_STAGES = 16;
 constexpr int CV_MAX_TAPS = 9;
 
 struct ConvGeom {
@@ -50,17 +51,25 @@ __device__ __forceinline__ uint64_t umma_smem_desc(uint32_t smem_addr, int bk) {
     return d;
 }
 
-constexpr int CV_STAGING_BYTES = 2 * 128 * 128;     // two [128 rows][32 fp32] output staging buffers (128-byte swizzle)
+constexpr int CV_SLAB_BYTES = 128 * 128;             // one [128 rows][32 fp32] output slab (128-byte swizzle)
+constexpr int CV_STAGING_BYTES = 4 * CV_SLAB_BYTES;  // two slabs per epilogue group
 
-__device__ __forceinline__ void epi_bar() { asm volatile("bar.sync 1, 128;" ::: "memory"); }
+__device__ __forceinline__ void epi_bar(int id) { asm volatile("bar.sync %0, 128;" ::"r"(id) : "memory"); }
+__device__ __forceinline__ void epi_bar_all() { asm volatile("bar.sync 3, 256;" ::: "memory"); }
+__device__ __forceinline__ float4 lds128(uint32_t addr) {
+    float4 v;
+    asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "r"(addr));
+    return v;
+}
 
 // Persistent kernel: gridDim.x CTAs (one per SM) walk the tile list t = blockIdx.x, += gridDim.x; tiles are ordered with
 // the output-channel tile slowest so a CTA's per-channel coefficients rarely change.  Three asynchronous roles:
 //   warp 0   TMA producer: keeps the shared-memory ring full ACROSS tile boundaries
 //   warp 1   MMA issuer  : accumulates tile j into TMEM buffer j&1 (2 x BN columns allocated)
-//   warps 2-5 epilogue   : drain buffer j&1 (tcgen05.ld) 32 columns at a time, dequantise, park the [rows][32] slab in
-//                          a swizzled shared-memory staging buffer and hand it to a TMA store (coalesced 128-byte rows,
-//                          ragged tile edges clipped by the hardware) - overlapped with the MMAs of tile j+1
+//   warps 2-9 epilogue   : two groups of four warps (one warp per TMEM lane quarter) take alternate 32-column slabs of
+//                          buffer j&1: tcgen05.ld, dequantise, park the [rows][32] slab in a swizzled shared-memory
+//                          staging buffer and hand it to a TMA store (coalesced 128-byte rows, ragged tile edges clipped
+//                          by the hardware) - overlapped with the MMAs of tile j+1
 template <int BN>
 __global__ void __launch_bounds__(CV_THREADS, 1)
 k_conv_i8(const __grid_constant__ CUtensorMap tmap_x, const __grid_constant__ CUtensorMap tmap_w,
@@ -71,11 +80,11 @@ k_conv_i8(const __grid_constant__ CUtensorMap tmap_x, const __grid_constant__ CU
     float* staging = reinterpret_cast<float*>(smem + (size_t)g.stages * stage_bytes);          // 1024-byte aligned
     uint8_t* tail = reinterpret_cast<uint8_t*>(staging) + CV_STAGING_BYTES;
     uint64_t* full_bar = reinterpret_cast<uint64_t*>(tail);
-    uint64_t* empty_bar = full_bar + 8;
-    uint64_t* tfull_bar = empty_bar + 8;                       // [2] accumulator buffer ready
+    uint64_t* empty_bar = full_bar + CV_MAX_STAGES;
+    uint64_t* tfull_bar = empty_bar + CV_MAX_STAGES;           // [2] accumulator buffer ready
     uint64_t* tempty_bar = tfull_bar + 2;                      // [2] accumulator buffer drained
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty_bar + 2);
-    float4* s_coef = reinterpret_cast<float4*>(tail + 256);   // {sa*sw[n], sa*lw'[n], bias[n], la*(sw*Tall + lw'*K)}
+    float4* s_coef = reinterpret_cast<float4*>(tail + 320);   // {sa*sw[n], sa*lw'[n], bias[n], la*(sw*Tall + lw'*K)}
     float* s_c3 = reinterpret_cast<float*>(s_coef + BN);      // la*sw[n]      (border pixels of inputs with min != 0)
     float* s_c4 = s_c3 + BN;                                   // la*lw'[n]
     int32_t* s_tap = reinterpret_cast<int32_t*>(s_c4 + BN);   // [BN][taps]
@@ -99,7 +108,7 @@ k_conv_i8(const __grid_constant__ CUtensorMap tmap_x, const __grid_constant__ CU
         }
         for (int i = 0; i < 2; ++i) {
             mbar_init(&tfull_bar[i], 1);
-            mbar_init(&tempty_bar[i], 4);                      // one arrival per epilogue warp
+            mbar_init(&tempty_bar[i], 8);                      // one arrival per epilogue warp
         }
         fence_barrier_init();
     }
@@ -165,8 +174,9 @@ k_conv_i8(const __grid_constant__ CUtensorMap tmap_x, const __grid_constant__ CU
             }
         }
     } else {
-        // ===== epilogue warps (128 threads) =====
-        const int et = threadIdx.x - 64;
+        // ===== epilogue: 2 groups x 4 warps; group `grp` owns the slabs cs with cs % 2 == grp =====
+        const int e_all = threadIdx.x - 64;                         // 0..255
+        const int grp = e_all >> 7, et = e_all & 127;
         const int sub = warp & 3;                                   // TMEM lane quarter this warp may access
         const QParams pa = make_qparams_d((double)__ldg(ep.a_range), (double)__ldg(ep.a_range + 1), ep.a_bits);
         const double sa = (double)pa.scale, la = (double)pa.lo;
@@ -176,11 +186,27 @@ k_conv_i8(const __grid_constant__ CUtensorMap tmap_x, const __grid_constant__ CU
         const int nl = i / per_img, rem = i - nl * per_img;
         const int th = rem / g.TW, tw = rem - th * g.TW;
         const bool in_box = nl < g.TN;
-        const uint32_t stage_u32 = smem_u32(staging);
+        uint8_t* my_staging = reinterpret_cast<uint8_t*>(staging) + grp * 2 * CV_SLAB_BYTES;
+        const uint32_t stage_u32 = smem_u32(my_staging);
+        const uint32_t coef_u32 = smem_u32(s_coef);
         const uint32_t row_off = (uint32_t)i * 128u, sw = (uint32_t)(i & 7);
         const float kfull = (float)(taps * g.Cin);
+        const int bar_id = 1 + grp;
         int cur_tn = -1, j = 0;
-        uint32_t slab = 0;                                          // running count of staged slabs (buffer = slab & 1)
+        uint32_t slab = 0;                                          // slabs staged by this group so far (buffer = slab & 1)
+        // boxsum of this thread's pixel, fetched one tile ahead so its latency hides behind the current tile
+        auto fetch_box = [&](int t, bool& valid_out) -> int {
+            if (t >= total_tiles) { valid_out = false; return 0; }
+            const int tn = t / tiles_m;
+            int tm = t - tn * tiles_m;
+            const int tw_i = tm % g.tiles_w; tm /= g.tiles_w;
+            const int th_i = tm % g.tiles_h; tm /= g.tiles_h;
+            const int b = tm * g.TN + nl, ho = th_i * g.TH + th, wo = tw_i * g.TW + tw;
+            valid_out = in_box && (b < g.B) && (ho < g.Ho) && (wo < g.Wo);
+            return valid_out ? __ldg(ep.boxsum + ((int64_t)b * g.Ho + ho) * g.Wo + wo) : 0;
+        };
+        bool valid_next;
+        int box_next = fetch_box(blockIdx.x, valid_next);
         for (int t = blockIdx.x; t < total_tiles; t += gridDim.x, ++j) {
             const int tn = t / tiles_m;
             int tm = t - tn * tiles_m;
@@ -188,8 +214,8 @@ k_conv_i8(const __grid_constant__ CUtensorMap tmap_x, const __grid_constant__ CU
             const int th_i = tm % g.tiles_h; tm /= g.tiles_h;
             const int b0 = tm * g.TN, ho0 = th_i * g.TH, wo0 = tw_i * g.TW, n0 = tn * BN;
             if (tn != cur_tn) {                                      // per-channel coefficients of this channel tile
-                epi_bar();                                           // everyone is done with the previous ones
-                for (int jn = et; jn < BN; jn += 128) {
+                epi_bar_all();                                       // everyone is done with the previous ones
+                for (int jn = e_all; jn < BN; jn += 256) {
                     const int n = n0 + jn;
                     float4 cf = make_float4(0.f, 0.f, 0.f, 0.f);
                     float c3 = 0.f, c4 = 0.f;
@@ -212,78 +238,84 @@ k_conv_i8(const __grid_constant__ CUtensorMap tmap_x, const __grid_constant__ CU
                     }
                     s_coef[jn] = cf; s_c3[jn] = c3; s_c4[jn] = c4;
                 }
-                epi_bar();
+                epi_bar_all();
                 cur_tn = tn;
             }
-            // this thread's output pixel of the tile
-            const int b = b0 + nl, ho = ho0 + th, wo = wo0 + tw;
-            const bool valid = in_box && (b < g.B) && (ho < g.Ho) && (wo < g.Wo);
-            float rs_a = 0.f, kvalid = kfull;
+            const bool valid = valid_next;
+            const float rs_a = (float)box_next;
+            box_next = fetch_box(t + (int)gridDim.x, valid_next);
+            float kvalid = kfull;
             uint32_t mask = 0;
             bool interior = true;
-            if (valid) {
-                rs_a = (float)__ldg(ep.boxsum + ((int64_t)b * g.Ho + ho) * g.Wo + wo);
-                if (need_la) {
-                    int cnt = 0;
-                    for (int r = 0; r < g.kh; ++r)
-                        for (int s_ = 0; s_ < g.kw; ++s_) {
-                            const int hi = ho * g.stride - g.pad + r, wi = wo * g.stride - g.pad + s_;
-                            if (hi >= 0 && hi < g.H && wi >= 0 && wi < g.W) { mask |= 1u << (r * g.kw + s_); ++cnt; }
-                        }
-                    interior = cnt == taps;
-                    kvalid = (float)(cnt * g.Cin);
-                }
+            if (need_la && valid) {
+                const int ho = ho0 + th, wo = wo0 + tw;
+                int cnt = 0;
+                for (int r = 0; r < g.kh; ++r)
+                    for (int s_ = 0; s_ < g.kw; ++s_) {
+                        const int hi = ho * g.stride - g.pad + r, wi = wo * g.stride - g.pad + s_;
+                        if (hi >= 0 && hi < g.H && wi >= 0 && wi < g.W) { mask |= 1u << (r * g.kw + s_); ++cnt; }
+                    }
+                interior = cnt == taps;
+                kvalid = (float)(cnt * g.Cin);
             }
             const int ncols = (g.Cout - n0 < BN) ? g.Cout - n0 : BN;
             const int nslabs = (ncols + 31) >> 5;
+            const int last_cs = ((nslabs - 1 - grp) & ~1) + grp;    // last slab of this group (< grp: the group has none)
             const int buf = j & 1;
             mbar_wait(&tfull_bar[buf], (j >> 1) & 1);
             tc_fence_after_sync();
             const uint32_t t_addr = tmem_base + (uint32_t)(buf * BN) + ((uint32_t)(sub * 32) << 16);
+            if (nslabs <= grp) {                                     // nothing to drain for this group: release right away
+                tc_fence_before_sync();
+                __syncwarp();
+                if (lane == 0) mbar_arrive(&tempty_bar[buf]);
+            }
 #pragma unroll 1
-            for (int cs = 0; cs < nslabs; ++cs, ++slab) {
+            for (int cs = grp; cs < nslabs; cs += 2, ++slab) {
                 const int c = cs * 32;
                 uint32_t r[32];
                 tmem_ld_32x32(t_addr + (uint32_t)c, r);
-                if (et == 0) tma_store_wait_read<1>();               // the store that used this staging buffer is done reading
-                epi_bar();
                 tmem_ld_wait();
-                if (cs == nslabs - 1) {                              // last read of this accumulator: hand it back to the MMA warp
+                if (cs == last_cs) {                                 // last read of this accumulator by this warp
                     tc_fence_before_sync();
                     __syncwarp();
                     if (lane == 0) mbar_arrive(&tempty_bar[buf]);
                 }
-                const uint32_t dst = stage_u32 + (slab & 1u) * (128u * 128u) + row_off;
+                const uint32_t dst = stage_u32 + (slab & 1u) * (uint32_t)CV_SLAB_BYTES + row_off;
                 if (valid) {
-                    const float base2 = rs_a;
+                    const uint32_t cf_addr = coef_u32 + (uint32_t)c * 16u;
 #pragma unroll
                     for (int q = 0; q < 32; ++q) {
-                        const float4 cf = s_coef[c + q];
-                        r[q] = __float_as_uint(fmaf(cf.x, (float)(int32_t)r[q], fmaf(cf.y, base2, cf.z)));
-                    }
-                    if (need_la) {
-#pragma unroll
-                        for (int q = 0; q < 32; ++q) {
-                            float add = s_coef[c + q].w;
-                            if (!interior) {
-                                int tsum = 0;
-#pragma unroll 1
-                                for (int tp = 0; tp < taps; ++tp)
-                                    if ((mask >> tp) & 1u) tsum += s_tap[(c + q) * taps + tp];
-                                add = fmaf(s_c3[c + q], (float)tsum, s_c4[c + q] * kvalid);
-                            }
-                            r[q] = __float_as_uint(__uint_as_float(r[q]) + add);
-                        }
+                        const float4 cf = lds128(cf_addr + q * 16);
+                        r[q] = __float_as_uint(fmaf(cf.x, (float)(int32_t)r[q], fmaf(cf.y, rs_a, cf.z)));
                     }
 #pragma unroll
                     for (int q = 0; q < 8; ++q)
                         asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(dst + (((uint32_t)q ^ sw) << 4)),
                                      "r"(r[4 * q]), "r"(r[4 * q + 1]), "r"(r[4 * q + 2]), "r"(r[4 * q + 3]) : "memory");
+                    if (need_la) {                                   // inputs whose range does not start at 0 (rare): fix up
+#pragma unroll 1                                                     // this thread's own row in place, column by column
+                        for (int q = 0; q < 32; ++q) {
+                            float add = s_coef[c + q].w;
+                            if (!interior) {
+                                int tsum = 0;
+                                for (int tp = 0; tp < taps; ++tp)
+                                    if ((mask >> tp) & 1u) tsum += s_tap[(c + q) * taps + tp];
+                                add = fmaf(s_c3[c + q], (float)tsum, s_c4[c + q] * kvalid);
+                            }
+                            const uint32_t a = dst + ((((uint32_t)q >> 2) ^ sw) << 4) + ((uint32_t)q & 3u) * 4u;
+                            float v;
+                            asm volatile("ld.shared.f32 %0, [%1];" : "=f"(v) : "r"(a));
+                            v += add;
+                            asm volatile("st.shared.f32 [%0], %1;" ::"r"(a), "f"(v) : "memory");
+                        }
+                    }
                 }
                 fence_proxy_async();
-                epi_bar();
+                if (et == 0) tma_store_wait_read<0>();               // every earlier store of this group has left its slab
+                epi_bar(bar_id);
                 if (et == 0) {
-                    tma_store_4d(&tmap_o, reinterpret_cast<uint8_t*>(staging) + (slab & 1u) * (128u * 128u), n0 + c, wo0, ho0, b0);
+                    tma_store_4d(&tmap_o, my_staging + (slab & 1u) * CV_SLAB_BYTES, n0 + c, wo0, ho0, b0);
                     tma_store_commit();
                 }
             }
@@ -380,7 +412,7 @@ extern "C" int qb_fakequant_rows_conv(const float* w, float* wq, uint8_t* codes_
 // ------------------------------------------------------------------------------------------------
 // host launcher
 // ------------------------------------------------------------------------------------------------
-static size_t conv_tail_bytes(int BN, int taps) { return 256 + (size_t)BN * 24 + (size_t)BN * taps * 4; }
+static size_t conv_tail_bytes(int BN, int taps) { return 320 + (size_t)BN * 24 + (size_t)BN * taps * 4; }
 
 template <int BN>
 static int launch_conv(const CUtensorMap& tx, const CUtensorMap& tw, const CUtensorMap& to, const ConvGeom& g,
@@ -435,7 +467,7 @@ extern "C" int qb_conv_i8_fwd(const uint8_t* x_codes, const uint8_t* w_codes_khw
         const size_t stage = (size_t)(128 + BN) * g.BK;
         const size_t fixed = CV_STAGING_BYTES + 1024 + conv_tail_bytes(BN, kh * kw);
         int s = (int)((225 * 1024 - fixed) / stage);
-        g.stages = s > 8 ? 8 : (s < 2 ? 2 : s);
+        g.stages = s > CV_MAX_STAGES ? CV_MAX_STAGES : (s < 2 ? 2 : s);
     }
     cudaStream_t st = qb_stream(stream);
     {
