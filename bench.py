@@ -234,8 +234,8 @@ def main_ours(args, rank, world, local_rank):
     # ---- roofline of our dominant kernel: one extra, instrumented eager step (events around every C-ABI call) ----
     roof = None
     cpu_base = None
+    roof = roofline_pass(step_body, _abi)          # on EVERY rank: the step contains collectives
     if rank == 0:
-        roof = roofline_pass(step_body, _abi)
         if not args.no_cpu_baseline and world == 1:
             ips, _ = cpu_reference_run(args.model, args.cpu_sample_batch, 2, 1)
             cpu_base = {"value": round(ips, 3), "unit": UNIT, "cores": torch.get_num_threads(), "kind": "port",

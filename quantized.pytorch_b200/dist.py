@@ -34,12 +34,11 @@ class StatReducer:
     # QuantMeasure: entries 0-3 and 6-7 are sums, 4 is a min, 5 a max.  One SUM plus one MAX message.
     def measure(self, stats):
         ext = torch.stack([-stats[4], stats[5]])
-        stats[4] = 0.0
-        stats[5] = 0.0
+        stats[4:6].zero_()                      # (a Python-scalar setitem is a host->device copy: illegal under capture)
         dist.all_reduce(stats, op=dist.ReduceOp.SUM, group=self.group)
         dist.all_reduce(ext, op=dist.ReduceOp.MAX, group=self.group)
-        stats[4] = -ext[0]
-        stats[5] = ext[1]
+        stats[4:5].copy_(-ext[0:1])
+        stats[5:6].copy_(ext[1:2])
 
     def rangebn_layout(self, B_local, HW, num_chunks):
         """-> (chunks owned by this rank, global element count per channel).  Contiguous batch shards hold whole
@@ -60,8 +59,8 @@ class StatReducer:
     def grad_range(self, rng):
         ext = torch.stack([-rng[0], rng[1]])
         dist.all_reduce(ext, op=dist.ReduceOp.MAX, group=self.group)
-        rng[0] = -ext[0]
-        rng[1] = ext[1]
+        rng[0:1].copy_(-ext[0:1])
+        rng[1:2].copy_(ext[1:2])
 
 
 def init(device=None, group=None):
@@ -86,16 +85,30 @@ def broadcast_parameters(model, src=0, group=None):
 
 
 def allreduce_gradients(model, group=None, average=True):
-    """Flat-bucket all-reduce of every gradient (46.8 MB for ResNet-18): one NCCL call, NVLS-eligible."""
-    grads = [p.grad for p in model.parameters() if p.grad is not None]
-    if not grads:
-        return
-    flat = torch._utils._flatten_dense_tensors(grads)
-    dist.all_reduce(flat, op=dist.ReduceOp.SUM, group=group)
+    """Flat-bucket all-reduce of the batch-sharded gradients (46.8 MB for ResNet-18): one NCCL call, NVLS-eligible.
+
+    ``average=True``  - every rank's loss is the MEAN over its own shard: gradients are summed and divided by world.
+    ``average=False`` - every rank's loss is (sum over its shard) / GLOBAL batch: gradients are summed only.
+    RangeBN's gamma / beta gradients are different: they are computed from the all-reduced backward sums
+    (StatReducer.rangebn_bwd), i.e. they are already the GLOBAL gradient on every rank and must not be summed again;
+    with a local-mean loss they come out world x too large (the upstream gradients are), so they are divided instead."""
+    world = dist.get_world_size(group)
+    replicated = set()
+    for m in model.modules():
+        if isinstance(m, Q.RangeBN):
+            replicated.update(id(p) for p in (m.weight, m.bias) if p is not None)
+    grads = [p.grad for p in model.parameters() if p.grad is not None and id(p) not in replicated]
+    if grads:
+        flat = torch._utils._flatten_dense_tensors(grads)
+        dist.all_reduce(flat, op=dist.ReduceOp.SUM, group=group)
+        if average:
+            flat.div_(world)
+        for g, f in zip(grads, torch._utils._unflatten_dense_tensors(flat, grads)):
+            g.copy_(f)
     if average:
-        flat.div_(dist.get_world_size(group))
-    for g, f in zip(grads, torch._utils._unflatten_dense_tensors(flat, grads)):
-        g.copy_(f)
+        for p in model.parameters():
+            if p.grad is not None and id(p) in replicated:
+                p.grad.div_(world)
 
 
 def shard_batch(x, rank=None, world=None):
