@@ -238,6 +238,27 @@ int qb_conv_i8_fwd(const uint8_t* x_codes, const uint8_t* w_codes_khwc, float* o
                    const float* w_row_min, const float* w_row_max, int w_bits, const int32_t* pixsum,
                    int32_t* boxsum_ws, const int32_t* tapsum, const float* bias, void* stream);
 
+/* ---------------------------------------------------------------------------------------------------
+ * quantize2.py flavour: QParams (range, zero_point) are device tensors, one per tensor or one per
+ * row of dim 0; no 1e-8 floor on the scale; optional signed codes, optional raw-code output, stochastic rounding on
+ * the same branch.  models/modules/quantize2.py:41-76 (UniformQuantize.forward).
+ *   x, y       fp32 [rows, cols] (y may alias x); zero_point, range: fp32[per_row ? rows : 1] on the device
+ *   dequantize 0 -> y holds the integer codes as fp32 (quantize2.py:72 skipped)
+ *   noise / stochastic / seed / offset / step_dev as in qb_fakequant_grad                                           */
+int qb_fakequant2(const float* x, float* y, int64_t rows, int64_t cols, const float* zero_point, const float* range,
+                  int per_row, int bits, int is_signed, int dequantize, const float* noise, int stochastic,
+                  uint64_t seed, uint64_t offset, const uint64_t* step_dev, void* stream);
+/* calculate_qparams with flatten_dims=(1,-1) (quantize2.py:19-28): min / max of every row of x [rows, cols].         */
+int qb_row_minmax(const float* x, int64_t rows, int64_t cols, float* row_min, float* row_max, void* stream);
+/* quantize2.RangeBN (quantize2.py:275-349): red = double[3C] from qb_rangebn_stats[_nhwc]; scale is neither inverted
+ * nor quantized, running_var tracks the scale, the normalisation divides by den = scale + eps.  rinv = 1/den feeds the
+ * backward kernels (qb_rangebn_bwd_*: pass rinv as scale_raw and qscale, gamma as qgamma).                            */
+int qb_rangebn2_finalize(const double* red, int64_t C, int num_chunks, double count, double chunk_len, float eps,
+                         double momentum, int training, float* running_mean, float* running_var, float* mean,
+                         float* scale, float* den, float* rinv, void* stream);
+int qb_rangebn2_apply(const float* x, float* out, int64_t B, int64_t C, int64_t HW, int nhwc, const float* mean,
+                      const float* den, const float* gamma, const float* beta, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

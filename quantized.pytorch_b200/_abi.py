@@ -52,6 +52,10 @@ PROTOTYPES = {
                                                _u64, _u64, _p, _p, _p, _sz, _p]),
     "qb_rangebn_bwd_apply_nhwc": (_i32, [_p, _p, _i64, _i64, _i64, _i32, _p, _p, _p, _p, _p, _p, _p]),
     "qb_rowsum_u8": (_i32, [_p, _i64, _i64, _p, _p]),
+    "qb_fakequant2": (_i32, [_p, _p, _i64, _i64, _p, _p, _i32, _i32, _i32, _i32, _p, _i32, _u64, _u64, _p, _p]),
+    "qb_row_minmax": (_i32, [_p, _i64, _i64, _p, _p, _p]),
+    "qb_rangebn2_finalize": (_i32, [_p, _i64, _i32, _dbl, _dbl, _flt, _dbl, _i32, _p, _p, _p, _p, _p, _p, _p]),
+    "qb_rangebn2_apply": (_i32, [_p, _p, _i64, _i64, _i64, _i32, _p, _p, _p, _p, _p]),
     "qb_gemm_i8": (_i32, [_p, _p, _p, _i64, _i64, _i64, _i64, _p, _i32, _p, _p, _i32, _p, _p, _p, _i32, _p]),
     "qb_fakequant_rows_conv": (_i32, [_p, _p, _p, _p, _i64, _i64, _i32, _i32, _p, _p, _i32, _p]),
     "qb_conv_i8_fwd": (_i32, [_p, _p, _p, _i64, _i64, _i64, _i64, _i64, _i32, _i32, _i32, _i32, _p, _i32, _p, _p, _i32,
@@ -437,4 +441,52 @@ def conv_i8_fwd(x_codes, w_codes, B, H, W, Cin, Cout, kh, kw, stride, pad, a_ran
     _run("qb_conv_i8_fwd", B * H * W * Cin + Cout * kh * kw * Cin + 4 * B * Ho * Wo * Cout, _ptr(x_codes), _ptr(w_codes),
          _ptr(out), B, H, W, Cin, Cout, kh, kw, stride, pad, _ptr(a_range), int(a_bits), _ptr(row_min), _ptr(row_max),
          int(w_bits), _ptr(pixsum), _ptr(boxsum), _ptr(tapsum), _ptr(bias), _stream())
+    return out
+
+
+# ----------------------------------------------------------------------------------------------
+# quantize2.py flavour (row A9)
+# ----------------------------------------------------------------------------------------------
+def fakequant2(x, zero_point, rng, bits, per_row=False, signed=False, dequantize=True, noise=None, stochastic=False, seed=0,
+               step_dev=None, out=None):
+    """x viewed as [rows, cols] (rows = x.shape[0] when per_row else 1); zero_point / rng: device fp32 tensors with
+    rows (or 1) elements.  See qb_fakequant2."""
+    x = _f32c(x, "x")
+    rows = x.shape[0] if per_row else 1
+    cols = x.numel() // max(rows, 1)
+    if out is None:
+        out = torch.empty_like(x)
+    zp = zero_point.detach().reshape(-1).contiguous().float()
+    rg = rng.detach().reshape(-1).contiguous().float()
+    if zp.numel() != (rows if per_row else 1) or rg.numel() != zp.numel():
+        raise QB200Error("fakequant2: qparams must hold one value per tensor or one per row of dim 0")
+    _run("qb_fakequant2", 8 * x.numel(), _ptr(x), _ptr(out), rows, cols, _ptr(zp), _ptr(rg), int(per_row), int(bits),
+         int(bool(signed)), int(bool(dequantize)), _ptr(noise), int(bool(stochastic)), int(seed) & (2 ** 64 - 1), 0,
+         _ptr(step_dev), _stream())
+    return out
+
+
+def row_minmax(x):
+    """-> (row_min, row_max) fp32[x.shape[0]] over everything but dim 0."""
+    x = _f32c(x, "x")
+    x = x if x.is_contiguous() else x.contiguous()
+    rows = x.shape[0]
+    mn = torch.empty(rows, dtype=torch.float32, device=x.device)
+    mx = torch.empty(rows, dtype=torch.float32, device=x.device)
+    _run("qb_row_minmax", 4 * x.numel(), _ptr(x), rows, x.numel() // rows, _ptr(mn), _ptr(mx), _stream())
+    return mn, mx
+
+
+def rangebn2_finalize(red, Cn, num_chunks, count, chunk_len, eps, momentum, training, running_mean, running_var):
+    """-> vec float[4, C]: rows mean, scale, den = scale + eps, rinv = 1 / den."""
+    vec = torch.empty(4, Cn, dtype=torch.float32, device=running_mean.device)
+    _run("qb_rangebn2_finalize", 0, _ptr(red), Cn, int(num_chunks), float(count), float(chunk_len), float(eps), float(momentum),
+         int(training), _ptr(running_mean), _ptr(running_var), _ptr(vec[0]), _ptr(vec[1]), _ptr(vec[2]), _ptr(vec[3]), _stream())
+    return vec
+
+
+def rangebn2_apply(x, B, Cn, HW, vec, gamma, beta, nhwc=False):
+    out = torch.empty_like(x)
+    _run("qb_rangebn2_apply", 8 * x.numel(), _ptr(x), _ptr(out), B, Cn, HW, int(nhwc), _ptr(vec[0]), _ptr(vec[2]), _ptr(gamma),
+         _ptr(beta), _stream())
     return out

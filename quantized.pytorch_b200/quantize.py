@@ -262,8 +262,9 @@ class _QContraction(Function):
     """
 
     @staticmethod
-    def forward(ctx, x, w, b, conv, bits_grad, grad_mode):
+    def forward(ctx, x, w, b, conv, bits_grad, grad_mode, grad_quantizer=None):
         ctx.conv, ctx.bits_grad, ctx.grad_mode = conv, bits_grad, grad_mode
+        ctx.grad_quantizer = grad_quantizer          # quantize2 flavour: callable(g) -> Q(g); None = quantize.py's
         ctx.has_bias = b is not None
         ctx.save_for_backward(x, w)
         if conv is None:
@@ -274,7 +275,7 @@ class _QContraction(Function):
     @staticmethod
     def backward(ctx, g):
         x, w = ctx.saved_tensors
-        return _contraction_backward(ctx, g, x, w) + (None, None, None)
+        return _contraction_backward(ctx, g, x, w) + (None, None, None, None)
 
 
 def _contraction_backward(ctx, g, x, w):
@@ -283,7 +284,8 @@ def _contraction_backward(ctx, g, x, w):
     g = _abi._f32c(g, "grad")
     gq = None
     if ctx.grad_mode != "full" and (need_x or ctx.grad_mode == "quant"):
-        gq = _quantize_gradient(g, ctx.bits_grad)
+        custom = getattr(ctx, "grad_quantizer", None)
+        gq = custom(g) if custom is not None else _quantize_gradient(g, ctx.bits_grad)
     g_param = gq if ctx.grad_mode == "quant" else g          # weight / bias branch
     g_input = g if ctx.grad_mode == "full" else gq           # input branch
     dx = dw = db = None
