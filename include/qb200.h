@@ -229,6 +229,9 @@ int qb_fakequant_rows_conv(const float* w, float* wq, uint8_t* codes_khwc, int32
  *   x_codes uint8 [B,H,W,Cin] (NHWC), a_range device {min,max} of its quantizer; pixsum int32[B*H*W] = SUM_c codes
  *   w_codes_khwc uint8 [Cout][kh*kw][Cin], per-row ranges, tapsum (from qb_fakequant_rows_conv); bias fp32[Cout] or NULL
  *   boxsum_ws int32[B*Ho*Wo] scratch: receives the per-output-pixel sums of pixsum over the in-bounds taps
+ *   out_stats (optional) double[8]: the QuantMeasure statistics block of the OUTPUT (same layout as qb_measure_stats,
+ *   stats_ws = qb_measure_ws_bytes(B) bytes zero-filled once): the range reduction of the layer that follows
+ *   (quantize.py:223-235) fused into the epilogue, so the output is not read again for it
  *   out fp32 [B,Ho,Wo,Cout] (NHWC), written by TMA stores.  Zero padding is exact for any input range (border-aware
  *   epilogue).
  * Supported: Cin % 32 == 0, Cout % 16 == 0, kh*kw <= 9, stride 1 or 2, dilation 1, groups 1; anything else returns
@@ -236,7 +239,8 @@ int qb_fakequant_rows_conv(const float* w, float* wq, uint8_t* codes_khwc, int32
 int qb_conv_i8_fwd(const uint8_t* x_codes, const uint8_t* w_codes_khwc, float* out, int64_t B, int64_t H, int64_t W,
                    int64_t Cin, int64_t Cout, int kh, int kw, int stride, int pad, const float* a_range, int a_bits,
                    const float* w_row_min, const float* w_row_max, int w_bits, const int32_t* pixsum,
-                   int32_t* boxsum_ws, const int32_t* tapsum, const float* bias, void* stream);
+                   int32_t* boxsum_ws, const int32_t* tapsum, const float* bias, double* out_stats, void* stats_ws,
+                   size_t stats_ws_bytes, void* stream);
 
 /* ---------------------------------------------------------------------------------------------------
  * quantize2.py flavour: QParams (range, zero_point) are device tensors, one per tensor or one per

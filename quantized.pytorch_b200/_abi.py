@@ -59,7 +59,7 @@ PROTOTYPES = {
     "qb_gemm_i8": (_i32, [_p, _p, _p, _i64, _i64, _i64, _i64, _p, _i32, _p, _p, _i32, _p, _p, _p, _i32, _p]),
     "qb_fakequant_rows_conv": (_i32, [_p, _p, _p, _p, _i64, _i64, _i32, _i32, _p, _p, _i32, _p]),
     "qb_conv_i8_fwd": (_i32, [_p, _p, _p, _i64, _i64, _i64, _i64, _i64, _i32, _i32, _i32, _i32, _p, _i32, _p, _p, _i32,
-                              _p, _p, _p, _p, _p]),
+                              _p, _p, _p, _p, _p, _p, _sz, _p]),
 }
 
 _lib = None
@@ -433,14 +433,17 @@ def fakequant_rows_conv(w, bits, row_min, row_max, compute_range=True, want_y=Tr
 
 
 def conv_i8_fwd(x_codes, w_codes, B, H, W, Cin, Cout, kh, kw, stride, pad, a_range, a_bits, row_min, row_max, w_bits, pixsum,
-                tapsum, bias=None):
-    """-> fp32 output, logical shape [B, Cout, Ho, Wo] stored channels-last."""
+                tapsum, bias=None, out_stats=None):
+    """-> fp32 output, logical shape [B, Cout, Ho, Wo] stored channels-last.  ``out_stats``: double[8] tensor that
+    receives the QuantMeasure statistics of the output (fused range reduction for the next layer)."""
     Ho, Wo = (H + 2 * pad - kh) // stride + 1, (W + 2 * pad - kw) // stride + 1
     out = torch.empty((B, Cout, Ho, Wo), dtype=torch.float32, device=x_codes.device, memory_format=torch.channels_last)
     boxsum = torch.empty(B * Ho * Wo, dtype=torch.int32, device=x_codes.device)
+    ws = workspace("measure", load().qb_measure_ws_bytes(B), x_codes.device) if out_stats is not None else None
     _run("qb_conv_i8_fwd", B * H * W * Cin + Cout * kh * kw * Cin + 4 * B * Ho * Wo * Cout, _ptr(x_codes), _ptr(w_codes),
          _ptr(out), B, H, W, Cin, Cout, kh, kw, stride, pad, _ptr(a_range), int(a_bits), _ptr(row_min), _ptr(row_max),
-         int(w_bits), _ptr(pixsum), _ptr(boxsum), _ptr(tapsum), _ptr(bias), _stream())
+         int(w_bits), _ptr(pixsum), _ptr(boxsum), _ptr(tapsum), _ptr(bias), _ptr(out_stats), _ptr(ws),
+         ws.numel() if ws is not None else 0, _stream())
     return out
 
 

@@ -37,6 +37,14 @@ struct ConvEpilogue {
     const int32_t* boxsum;      // S[B*Ho*Wo] = SUM over the in-bounds taps of the per-pixel code sums (k_conv_boxsum)
     const int32_t* tapsum;      // T[Cout][kh*kw]
     const float* bias;          // fake-quantized bias or nullptr
+    // optional: QuantMeasure statistics of the OUTPUT (what the following RangeBN's quantize_input needs,
+    // quantize.py:223-235), produced while the tile is in registers; same block / workspace layout as qb_measure_stats
+    double* stats;              // double[8] or nullptr
+    unsigned int* st_counter;
+    double* st_psum;
+    double* st_psq;
+    unsigned int* st_row_max;
+    unsigned int* st_row_min;
 };
 
 __device__ __forceinline__ uint64_t umma_smem_desc(uint32_t smem_addr, int bk) {
@@ -205,6 +213,8 @@ k_conv_i8(const __grid_constant__ CUtensorMap tmap_x, const __grid_constant__ CU
             valid_out = in_box && (b < g.B) && (ho < g.Ho) && (wo < g.Wo);
             return valid_out ? __ldg(ep.boxsum + ((int64_t)b * g.Ho + ho) * g.Wo + wo) : 0;
         };
+        const bool want_stats = ep.stats != nullptr;
+        double st_sum = 0.0, st_sq = 0.0;                            // this thread's share of SUM x, SUM x^2 (all its tiles)
         bool valid_next;
         int box_next = fetch_box(blockIdx.x, valid_next);
         for (int t = blockIdx.x; t < total_tiles; t += gridDim.x, ++j) {
@@ -258,6 +268,7 @@ k_conv_i8(const __grid_constant__ CUtensorMap tmap_x, const __grid_constant__ CU
                 interior = cnt == taps;
                 kvalid = (float)(cnt * g.Cin);
             }
+            float t_mn = QB_INF, t_mx = -QB_INF, t_sum = 0.f, t_sq = 0.f;   // statistics of this thread's row of the tile
             const int ncols = (g.Cout - n0 < BN) ? g.Cout - n0 : BN;
             const int nslabs = (ncols + 31) >> 5;
             const int last_cs = ((nslabs - 1 - grp) & ~1) + grp;    // last slab of this group (< grp: the group has none)
@@ -287,7 +298,11 @@ k_conv_i8(const __grid_constant__ CUtensorMap tmap_x, const __grid_constant__ CU
 #pragma unroll
                     for (int q = 0; q < 32; ++q) {
                         const float4 cf = lds128(cf_addr + q * 16);
-                        r[q] = __float_as_uint(fmaf(cf.x, (float)(int32_t)r[q], fmaf(cf.y, rs_a, cf.z)));
+                        const float v = fmaf(cf.x, (float)(int32_t)r[q], fmaf(cf.y, rs_a, cf.z));
+                        r[q] = __float_as_uint(v);
+                        if (want_stats && !need_la && c + q < ncols) {
+                            t_mn = fminf(t_mn, v); t_mx = fmaxf(t_mx, v); t_sum += v; t_sq = fmaf(v, v, t_sq);
+                        }
                     }
 #pragma unroll
                     for (int q = 0; q < 8; ++q)
@@ -308,6 +323,9 @@ k_conv_i8(const __grid_constant__ CUtensorMap tmap_x, const __grid_constant__ CU
                             asm volatile("ld.shared.f32 %0, [%1];" : "=f"(v) : "r"(a));
                             v += add;
                             asm volatile("st.shared.f32 [%0], %1;" ::"r"(a), "f"(v) : "memory");
+                            if (want_stats && c + q < ncols) {
+                                t_mn = fminf(t_mn, v); t_mx = fmaxf(t_mx, v); t_sum += v; t_sq = fmaf(v, v, t_sq);
+                            }
                         }
                     }
                 }
@@ -319,8 +337,85 @@ k_conv_i8(const __grid_constant__ CUtensorMap tmap_x, const __grid_constant__ CU
                     tma_store_commit();
                 }
             }
+            if (want_stats) {
+                st_sum += (double)t_sum;
+                st_sq += (double)t_sq;
+                // per-sample extrema: order-independent integer atomics on monotone codes (exact, like measure.cu);
+                // one atomic per warp when all its valid rows belong to one sample
+                const int bb = valid ? b0 + nl : -1;
+                const unsigned int act = __ballot_sync(0xffffffffu, valid && t_mn <= t_mx);
+                if (act) {
+                    const int lead = __ffs(act) - 1;
+                    const int b_lead = __shfl_sync(0xffffffffu, bb, lead);
+                    const bool uniform = __all_sync(0xffffffffu, !(valid && t_mn <= t_mx) || bb == b_lead);
+                    if (uniform) {
+                        const float wmn = warp_min(t_mn), wmx = warp_max(t_mx);
+                        if (lane == lead) {
+                            atomicMax(ep.st_row_max + b_lead, enc_ord(wmx));
+                            atomicMax(ep.st_row_min + b_lead, ~enc_ord(wmn));
+                        }
+                    } else if (valid && t_mn <= t_mx) {
+                        atomicMax(ep.st_row_max + bb, enc_ord(t_mx));
+                        atomicMax(ep.st_row_min + bb, ~enc_ord(t_mn));
+                    }
+                }
+            }
         }
         if (et == 0) tma_store_wait<0>();
+        if (want_stats) {
+            // CTA partial in a fixed order (warp shuffle tree, then warps 0..7), slot blockIdx.x; the last CTA to arrive
+            // combines every slot and the per-sample extrema in a fixed order and leaves the workspace clean
+            epi_bar_all();                                                   // both groups' stores have drained: staging is scratch now
+            st_sum = warp_sum(st_sum);
+            st_sq = warp_sum(st_sq);
+            double* s_all = reinterpret_cast<double*>(staging);
+            if (lane == 0) { s_all[(warp - 2) * 2] = st_sum; s_all[(warp - 2) * 2 + 1] = st_sq; }
+            epi_bar_all();
+            __shared__ bool s_last;
+            if (e_all == 0) {
+                double a = 0.0, c2 = 0.0;
+                for (int w = 0; w < 8; ++w) { a += s_all[2 * w]; c2 += s_all[2 * w + 1]; }
+                ep.st_psum[blockIdx.x] = a;
+                ep.st_psq[blockIdx.x] = c2;
+                __threadfence();
+                s_last = (atomicAdd(ep.st_counter, 1u) == gridDim.x - 1);
+            }
+            epi_bar_all();
+            if (s_last) {
+                __threadfence();
+                double smin = 0.0, smax = 0.0, tsum = 0.0, tsq = 0.0;
+                float gmn = QB_INF, gmx = -QB_INF;
+                for (int b = e_all; b < g.B; b += 256) {
+                    const float rmx = dec_ord(__ldcg(ep.st_row_max + b)), rmn = dec_ord(~__ldcg(ep.st_row_min + b));
+                    ep.st_row_max[b] = 0u;
+                    ep.st_row_min[b] = 0u;
+                    smax += (double)rmx; smin += (double)rmn;
+                    gmn = fminf(gmn, rmn); gmx = fmaxf(gmx, rmx);
+                }
+                for (int k = e_all; k < (int)gridDim.x; k += 256) { tsum += __ldcg(ep.st_psum + k); tsq += __ldcg(ep.st_psq + k); }
+                smin = warp_sum(smin); smax = warp_sum(smax); tsum = warp_sum(tsum); tsq = warp_sum(tsq);
+                gmn = warp_min(gmn); gmx = warp_max(gmx);
+                epi_bar_all();
+                if (lane == 0) {
+                    double* o = s_all + (warp - 2) * 6;
+                    o[0] = smin; o[1] = smax; o[2] = tsum; o[3] = tsq; o[4] = (double)gmn; o[5] = (double)gmx;
+                }
+                epi_bar_all();
+                if (e_all == 0) {
+                    double rr[4] = {0, 0, 0, 0};
+                    for (int w = 0; w < 8; ++w) {
+                        for (int k = 0; k < 4; ++k) rr[k] += s_all[w * 6 + k];
+                        gmn = fminf(gmn, (float)s_all[w * 6 + 4]);
+                        gmx = fmaxf(gmx, (float)s_all[w * 6 + 5]);
+                    }
+                    ep.stats[0] = rr[0]; ep.stats[1] = rr[1]; ep.stats[2] = rr[2]; ep.stats[3] = rr[3];
+                    ep.stats[4] = (double)gmn; ep.stats[5] = (double)gmx;
+                    ep.stats[6] = (double)g.B * (double)g.Ho * (double)g.Wo * (double)g.Cout;
+                    ep.stats[7] = (double)g.B;
+                    *ep.st_counter = 0u;
+                }
+            }
+        }
     }
     tc_fence_before_sync();
     __syncthreads();
@@ -437,7 +532,7 @@ extern "C" int qb_conv_i8_fwd(const uint8_t* x_codes, const uint8_t* w_codes_khw
                               int64_t W, int64_t Cin, int64_t Cout, int kh, int kw, int stride, int pad,
                               const float* a_range, int a_bits, const float* w_row_min, const float* w_row_max, int w_bits,
                               const int32_t* pixsum, int32_t* boxsum_ws, const int32_t* tapsum, const float* bias,
-                              void* stream) {
+                              double* out_stats, void* stats_ws, size_t stats_ws_bytes, void* stream) {
     QB_CHECK_ARG(x_codes && w_codes_khwc && out && a_range && w_row_min && w_row_max && pixsum && boxsum_ws && tapsum,
                  "qb_conv_i8_fwd: null pointer");
     QB_CHECK_ARG(B > 0 && H > 0 && W > 0 && Cin > 0 && Cout > 0 && kh > 0 && kw > 0 && stride > 0 && pad >= 0,
@@ -499,7 +594,21 @@ extern "C" int qb_conv_i8_fwd(const uint8_t* x_codes, const uint8_t* w_codes_khw
         int rc = qb_make_tmap(&to, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, out, dims, str, box, nullptr, 128);
         if (rc) return rc;
     }
-    ConvEpilogue ep{a_range, a_bits, w_row_min, w_row_max, w_bits, boxsum_ws, tapsum, bias};
+    ConvEpilogue ep{a_range, a_bits, w_row_min, w_row_max, w_bits, boxsum_ws, tapsum, bias,
+                    nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
+    if (out_stats) {
+        if (!stats_ws || stats_ws_bytes < qb_measure_ws_bytes(B)) {
+            qb_set_error("qb_conv_i8_fwd: statistics workspace %zu < %zu bytes", stats_ws_bytes, qb_measure_ws_bytes(B));
+            return QB_ERR_WORKSPACE;
+        }
+        char* base = static_cast<char*>(stats_ws);
+        ep.stats = out_stats;
+        ep.st_counter = reinterpret_cast<unsigned int*>(base);
+        ep.st_psum = reinterpret_cast<double*>(base + 64);
+        ep.st_psq = ep.st_psum + QB_MS_MAX_BLOCKS;
+        ep.st_row_max = reinterpret_cast<unsigned int*>(base + QB_MS_FIXED_BYTES);
+        ep.st_row_min = ep.st_row_max + B;
+    }
     if (BN == 256) return launch_conv<256>(tx, tw, to, g, ep, st);
     if (BN == 128) return launch_conv<128>(tx, tw, to, g, ep, st);
     return launch_conv<64>(tx, tw, to, g, ep, st);

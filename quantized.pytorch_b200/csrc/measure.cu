@@ -9,25 +9,16 @@
 constexpr int MS_THREADS = 256;
 constexpr int MS_VEC_PER_THREAD = 8;                               // float4 loads per thread per tile
 constexpr int64_t MS_TILE = MS_THREADS * 4 * MS_VEC_PER_THREAD;    // 8192 elements
-constexpr int MS_MAX_BLOCKS = 2048;
+constexpr int MS_MAX_BLOCKS = QB_MS_MAX_BLOCKS;
 
 // workspace: [counter, 64 B] [double psum[MS_MAX_BLOCKS]] [double psq[MS_MAX_BLOCKS]] [uint32 row_max_enc[B]]
 // [uint32 row_min_enc[B]].  The fixed-size part comes first so that one workspace can serve calls with different
 // B: only the counter and the row slots must be zero on entry (the kernel re-zeroes them), and their position
 // never overlaps the partial-sum area whatever B was used before.
-static const size_t MS_FIXED_BYTES = 64 + (size_t)MS_MAX_BLOCKS * 16;
+static const size_t MS_FIXED_BYTES = QB_MS_FIXED_BYTES;
 extern "C" size_t qb_measure_ws_bytes(int64_t B) {
     if (B < 0) return 0;
     return MS_FIXED_BYTES + (size_t)B * 8;
-}
-
-// monotone float -> uint32 map (larger float => larger uint); never yields 0 for a non-NaN float
-__device__ __forceinline__ unsigned int enc_ord(float f) {
-    unsigned int b = __float_as_uint(f);
-    return (b & 0x80000000u) ? ~b : (b | 0x80000000u);
-}
-__device__ __forceinline__ float dec_ord(unsigned int u) {
-    return __uint_as_float((u & 0x80000000u) ? (u & 0x7fffffffu) : ~u);
 }
 
 __device__ __forceinline__ void acc4(float4 v, float& mn, float& mx, float& s, float& q) {

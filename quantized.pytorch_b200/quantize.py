@@ -105,6 +105,27 @@ def _take_grad_range(g):
     return None
 
 
+# Producer-supplied forward statistics, same protocol: the int8 convolution epilogue emits the QuantMeasure statistics
+# block of its output; the quantize_input of the RangeBN that follows takes it instead of reading the tensor again.
+_fwd_stats = {}
+
+
+def _stash_fwd_stats(t, stats):
+    if len(_fwd_stats) >= 4:
+        _fwd_stats.clear()
+    _fwd_stats[t.data_ptr()] = (t, t._version, stats)
+
+
+def _take_fwd_stats(x):
+    ent = _fwd_stats.pop(x.data_ptr(), None)
+    if ent is None:
+        return None
+    t, ver, stats = ent
+    if t.shape == x.shape and t.stride() == x.stride() and t.dtype == x.dtype and x._version == ver:
+        return stats
+    return None
+
+
 def _grad_noise(g, stochastic):
     noise = _noise_provider(tuple(g.shape)) if (stochastic and _noise_provider is not None) else None
     if noise is not None and _abi.is_nhwc(g):
@@ -384,7 +405,9 @@ class QuantMeasure(nn.Module, QuantNode):
             assert self.laplace_alpha, 'aciq not supported for module num bits'
         x = input.detach()
         if self.training:
-            stats = _abi.measure_stats(x)
+            stats = _take_fwd_stats(x)
+            if stats is None:
+                stats = _abi.measure_stats(x)
             if _reducer is not None:
                 _reducer.measure(stats)
             return _abi.measure_finalize(stats, self._buffers5(), self.momentum, True, method, self.num_bits)
@@ -541,9 +564,12 @@ class _QTensorCoreFn(Function):
             B, Cin, H, W = x.shape
             kh, kw = mod.kernel_size
             pixsum = _abi.rowsum_u8(codes, B * H * W, Cin)
+            stats = torch.empty(8, dtype=torch.float64, device=x.device) if mod.training else None
             out = _abi.conv_i8_fwd(codes, wcodes, B, H, W, Cin, mod.out_channels, kh, kw, _pair(mod.stride)[0],
                                    _pair(mod.padding)[0], rng, bits_a, mod.weight_min, mod.weight_max, bits_w, pixsum, tapsum,
-                                   bias=qbias)
+                                   bias=qbias, out_stats=stats)
+            if stats is not None:
+                _stash_fwd_stats(out, stats)
             ctx.conv = (_pair(mod.stride), _pair(mod.padding), _pair(mod.dilation), mod.groups)
         else:
             M, K = x.shape

@@ -49,8 +49,18 @@ def test_conv_i8_fwd(lib, case, relu, use_bias):
     wq2, rmin2, rmax2 = lib.fakequant_rows(w.to(DEV), 8)
     assert torch.equal(wq, wq2) and torch.equal(rmin, rmin2) and torch.equal(rmax, rmax2)
     bd = bias.to(DEV) if use_bias else None
-    out = lib.conv_i8_fwd(codes, wcodes, B, H, W, Cin, Cout, k, k, stride, pad, rng, 8, rmin, rmax, 8, pixsum, tapsum, bias=bd)
+    stats = torch.empty(8, dtype=torch.float64, device=DEV)
+    out = lib.conv_i8_fwd(codes, wcodes, B, H, W, Cin, Cout, k, k, stride, pad, rng, 8, rmin, rmax, 8, pixsum, tapsum, bias=bd,
+                          out_stats=stats)
     torch.cuda.synchronize()
+    # fused output statistics (the next layer's QuantMeasure block): extrema exact, sums to fp64 accumulation accuracy
+    ref_stats = lib.measure_stats(out)
+    assert torch.equal(stats[[0, 1, 4, 5, 6, 7]], ref_stats[[0, 1, 4, 5, 6, 7]]), (stats, ref_stats)
+    assert torch.allclose(stats[2:4], ref_stats[2:4], rtol=1e-6, atol=1e-6 * float(ref_stats[3].sqrt())), (stats, ref_stats)
+    stats2 = torch.empty(8, dtype=torch.float64, device=DEV)
+    lib.conv_i8_fwd(codes, wcodes, B, H, W, Cin, Cout, k, k, stride, pad, rng, 8, rmin, rmax, 8, pixsum, tapsum, bias=bd,
+                    out_stats=stats2)
+    assert torch.equal(stats, stats2)                      # deterministic, workspace left clean
     assert out.is_contiguous(memory_format=torch.channels_last)
     ref64 = F.conv2d(xq.double().cpu(), wq.double().cpu(), bias.double() if use_bias else None, stride, pad)
     assert out.shape == ref64.shape
