@@ -188,15 +188,17 @@ size_t qb_rangebn_bwd_nhwc_ws_bytes(int64_t C);
 int qb_rangebn_bwd_reduce_nhwc(const float* gq, const float* x, int64_t B, int64_t C, int64_t HW, double* sg,
                                double* sgx, const float* q_range, int q_bits, const float* g_range, int g_bits,
                                const float* noise, int stochastic, uint64_t seed, uint64_t offset,
-                               const uint64_t* step_dev, void* ws, size_t ws_bytes, void* stream);
+                               const uint64_t* step_dev, uint8_t* gq_codes_out, void* ws, size_t ws_bytes, void* stream);
 /* dx = (Q(g)*qgamma)*qscale + a, +-e at the chunk arg-max/arg-min rows, in ONE pass, plus min/max of the final dx
- * (dx_range_out float[2], optional; mm_ws = qb_minmax_ws_bytes() bytes zero-filled once): the range the gradient
+ * (gq_codes: optional uint8 codes of Q(g) written by qb_rangebn_bwd_reduce_nhwc's gq_codes_out - the pass then reads
+ * 1 B/elem and only dequantizes instead of reading g and regenerating the noise;
+ * dx_range_out float[2], optional; mm_ws = qb_minmax_ws_bytes() bytes zero-filled once): the range the gradient
  * quantizer of the preceding QConv2d needs (quantize.py:126,132) without another read of dx. */
 int qb_rangebn_bwd_apply_fused_nhwc(const float* g, float* dx, int64_t B, int64_t C, int64_t HW, int num_chunks,
                                     const float* qscale, const float* qgamma, const float* coef_a,
                                     const float* coef_e, const int32_t* amax_kc, const int32_t* amin_kc,
                                     const float* g_range, int g_bits, const float* noise, int stochastic,
-                                    uint64_t seed, uint64_t offset, const uint64_t* step_dev,
+                                    uint64_t seed, uint64_t offset, const uint64_t* step_dev, const uint8_t* gq_codes,
                                     float* dx_range_out, void* mm_ws, size_t mm_ws_bytes, void* stream);
 int qb_rangebn_bwd_apply_nhwc(const float* gq, float* dx, int64_t B, int64_t C, int64_t HW, int num_chunks,
                               const float* qscale, const float* qgamma, const float* coef_a, const float* coef_e,

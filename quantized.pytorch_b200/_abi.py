@@ -47,9 +47,9 @@ PROTOTYPES = {
     "qb_rangebn_apply_nhwc": (_i32, [_p, _p, _i64, _i64, _i64, _p, _p, _p, _p, _p, _i32, _p]),
     "qb_rangebn_bwd_nhwc_ws_bytes": (_sz, [_i64]),
     "qb_rangebn_bwd_reduce_nhwc": (_i32, [_p, _p, _i64, _i64, _i64, _p, _p, _p, _i32, _p, _i32, _p, _i32, _u64, _u64, _p,
-                                          _p, _sz, _p]),
+                                          _p, _p, _sz, _p]),
     "qb_rangebn_bwd_apply_fused_nhwc": (_i32, [_p, _p, _i64, _i64, _i64, _i32, _p, _p, _p, _p, _p, _p, _p, _i32, _p, _i32,
-                                               _u64, _u64, _p, _p, _p, _sz, _p]),
+                                               _u64, _u64, _p, _p, _p, _p, _sz, _p]),
     "qb_rangebn_bwd_apply_nhwc": (_i32, [_p, _p, _i64, _i64, _i64, _i32, _p, _p, _p, _p, _p, _p, _p]),
     "qb_rowsum_u8": (_i32, [_p, _i64, _i64, _p, _p]),
     "qb_fakequant2": (_i32, [_p, _p, _i64, _i64, _p, _p, _i32, _i32, _i32, _i32, _p, _i32, _u64, _u64, _p, _p]),
@@ -364,9 +364,12 @@ def rangebn_backward(gq, xq, B, Cn, HW, num_chunks, count, chunk_len, training, 
         gqa = [_ptr(grad_quant["range"]), int(grad_quant["bits"]), _ptr(grad_quant.get("noise")),
                int(bool(grad_quant.get("stochastic", True))), int(grad_quant.get("seed", 0)) & (2 ** 64 - 1), 0,
                _ptr(grad_quant.get("step_dev"))]
+    codes = None
+    if fused and grad_quant is not None and int(grad_quant["bits"]) <= 8:
+        codes = torch.empty(gq.numel(), dtype=torch.uint8, device=dev)   # Q(g) handed from the reduce to the apply pass
     if nhwc:
         _run("qb_rangebn_bwd_reduce_nhwc", 8 * B * Cn * HW, _ptr(gq), _ptr(xq), B, Cn, HW, _ptr(sums[:Cn]), _ptr(sums[Cn:]),
-             _ptr(q_range), int(q_bits), *gqa, _ptr(ws), ws.numel(), _stream())
+             _ptr(q_range), int(q_bits), *gqa, _ptr(codes), _ptr(ws), ws.numel(), _stream())
     else:
         if q_range is not None:
             raise QB200Error("rangebn_backward: on-the-fly input quantization is a channels-last feature")
@@ -389,8 +392,8 @@ def rangebn_backward(gq, xq, B, Cn, HW, num_chunks, count, chunk_len, training, 
         _run("qb_rangebn_bwd_apply_fused_nhwc", 8 * B * Cn * HW, _ptr(gq), _ptr(dx), B, Cn, HW,
              int(num_chunks) if training else 0, _ptr(vec[2]), _ptr(vec[3]) if has_gamma else None, _ptr(coef[2]),
              _ptr(coef[3]) if training else None, _ptr(amax[1]) if training else None,
-             _ptr(amin[1]) if training else None, *gqa, _ptr(dx_range), _ptr(mm), mm.numel() if mm is not None else 0,
-             _stream())
+             _ptr(amin[1]) if training else None, *gqa, _ptr(codes), _ptr(dx_range), _ptr(mm),
+             mm.numel() if mm is not None else 0, _stream())
     else:
         a0 = amax[0] if (nhwc and amax is not None) else amax
         i0 = amin[0] if (nhwc and amin is not None) else amin

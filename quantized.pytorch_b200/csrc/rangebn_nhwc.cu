@@ -370,6 +370,8 @@ struct GradQuantArg {
     int bits;
     int noise_mode;
     NoiseArg noise;
+    uint8_t* codes;       // reduce pass: optional uint8 copy of the integer codes of Q(g) (bits <= 8), same indexing as g;
+                          // apply pass (NOISE == -2): the codes to dequantize INSTEAD of reading and re-quantizing g
 };
 
 template <int VEC, bool QUANT, int NOISE>   // NOISE < 0: g already quantized
@@ -412,7 +414,16 @@ k_rbn_bwd_reduce_nhwc(const float* __restrict__ gq, const float* __restrict__ x,
             } else if (NOISE == NOISE_PHILOX) {
                 philox_noise8(seed, (uint64_t)(e >> 3) + (ga.noise.offset >> 3), u);
             }
-            if (VEC == 8) grad_fq_vec<(NOISE < 0 ? 0 : NOISE), 8>(reinterpret_cast<float(&)[8]>(av), u, GQ);
+            if (VEC == 8) {
+                uint32_t cd[8];
+                grad_fq_vec<(NOISE < 0 ? 0 : NOISE), 8>(reinterpret_cast<float(&)[8]>(av), u, GQ, ga.codes ? cd : nullptr);
+                if (ga.codes) {
+                    uint2 pk;
+                    pk.x = cd[0] | (cd[1] << 8) | (cd[2] << 16) | (cd[3] << 24);
+                    pk.y = cd[4] | (cd[5] << 8) | (cd[6] << 16) | (cd[7] << 24);
+                    *reinterpret_cast<uint2*>(ga.codes + e) = pk;
+                }
+            }
         }
         if (QUANT) affine_fq_vec<VEC>(bv, aq);
 #pragma unroll
@@ -486,8 +497,11 @@ static int grad_noise_mode(const float* g_range, const float* noise, int stochas
 extern "C" int qb_rangebn_bwd_reduce_nhwc(const float* gq, const float* x, int64_t B, int64_t C, int64_t HW, double* sg,
                                           double* sgx, const float* q_range, int q_bits, const float* g_range, int g_bits,
                                           const float* noise, int stochastic, uint64_t seed, uint64_t offset,
-                                          const uint64_t* step_dev, void* ws, size_t ws_bytes, void* stream) {
+                                          const uint64_t* step_dev, uint8_t* gq_codes_out, void* ws, size_t ws_bytes,
+                                          void* stream) {
     QB_CHECK_ARG(gq && x && sg && sgx && ws, "qb_rangebn_bwd_reduce_nhwc: null pointer");
+    QB_CHECK_ARG(!gq_codes_out || (g_range && g_bits <= 8 && (reinterpret_cast<uintptr_t>(gq_codes_out) & 7) == 0),
+                 "qb_rangebn_bwd_reduce_nhwc: codes output needs the fused gradient quantizer, bits <= 8, 8-byte alignment");
     QB_CHECK_ARG(B > 0 && C > 0 && HW > 0, "qb_rangebn_bwd_reduce_nhwc: bad shape");
     QB_CHECK_ARG(!q_range || (q_bits >= 1 && q_bits <= 24), "qb_rangebn_bwd_reduce_nhwc: q_bits=%d", q_bits);
     QB_CHECK_ARG(!g_range || (g_bits >= 1 && g_bits <= 24), "qb_rangebn_bwd_reduce_nhwc: g_bits=%d", g_bits);
@@ -509,7 +523,7 @@ extern "C" int qb_rangebn_bwd_reduce_nhwc(const float* gq, const float* x, int64
     double* part = static_cast<double*>(ws);
     dim3 grid((unsigned)g.S, (unsigned)((C + g.tileC - 1) / g.tileC));
     cudaStream_t st = qb_stream(stream);
-    GradQuantArg ga{g_range, g_bits, nm, NoiseArg{noise, seed, offset, step_dev}};
+    GradQuantArg ga{g_range, g_bits, nm, NoiseArg{noise, seed, offset, step_dev}, gq_codes_out};
     const bool qx = q_range != nullptr;
     if (vec8) {
         const size_t sm = nhwc_smem(g, 8, 16);
@@ -564,82 +578,98 @@ struct BwdApplyArgs {
 
 template <int NOISE, bool RANGE>
 __global__ void __launch_bounds__(NH_THREADS)
-k_rbn_bwd_apply_fused(const float* __restrict__ g, float* __restrict__ dx, uint32_t noct, BwdApplyArgs A, GradQuantArg ga) {
+k_rbn_bwd_apply_fused(const float* __restrict__ g, float* __restrict__ dx, NhwcGeom geo, BwdApplyArgs A, GradQuantArg ga) {
+    // Column-persistent mapping (same geometry as the statistics kernel): a thread owns 8 adjacent channels for the whole
+    // CTA lifetime, so the per-channel coefficients and the chunk's arg rows live in registers - the row loop touches
+    // memory only for the data itself (the first version re-loaded 10 parameter vectors per octet and was L1-bound).
     __shared__ float sm[64];
     __shared__ bool last;
     GradQ GQ;
     uint64_t seed = 0;
-    if (NOISE >= 0) {
+    if (NOISE >= 0 || NOISE == -2) {
         GQ = make_gradq((double)__ldg(ga.range), (double)__ldg(ga.range + 1), ga.bits);
         seed = effective_seed(ga.noise);
     }
     float mn = QB_INF, mx = -QB_INF;
-    const uint32_t stride = gridDim.x * NH_THREADS;
-    for (uint32_t i = blockIdx.x * NH_THREADS + threadIdx.x; i < noct; i += stride) {
-        const F8 v = ld256_stream(g + 8ull * i);
-        const uint32_t e = 8u * i;                       // < 2^32 checked by the launcher
-        const uint32_t row = fdiv(e, A.dC), c = e - row * A.C;
-        float gq[8];
-        if (NOISE >= 0) {
-            float u[8];
-            if (NOISE == NOISE_INJECT) {
-                const F8 w = ld256_stream(ga.noise.inject + 8ull * i);
-#pragma unroll
-                for (int j = 0; j < 8; ++j) u[j] = w.v[j];
-            } else if (NOISE == NOISE_PHILOX) {
-                philox_noise8(seed, (uint64_t)i + (ga.noise.offset >> 3), u);
-            }
-#pragma unroll
-            for (int j = 0; j < 8; ++j) gq[j] = v.v[j];
-            grad_fq_vec<(NOISE < 0 ? 0 : NOISE), 8>(gq, u, GQ);
-        } else {
-#pragma unroll
-            for (int j = 0; j < 8; ++j) gq[j] = v.v[j];
-        }
-        float ga_[8], sc[8], ca[8];
-        {
-            const float4 s0 = __ldg(reinterpret_cast<const float4*>(A.qscale + c)), s1 = __ldg(reinterpret_cast<const float4*>(A.qscale + c + 4));
-            const float4 a0 = __ldg(reinterpret_cast<const float4*>(A.coef_a + c)), a1 = __ldg(reinterpret_cast<const float4*>(A.coef_a + c + 4));
-            sc[0] = s0.x; sc[1] = s0.y; sc[2] = s0.z; sc[3] = s0.w; sc[4] = s1.x; sc[5] = s1.y; sc[6] = s1.z; sc[7] = s1.w;
-            ca[0] = a0.x; ca[1] = a0.y; ca[2] = a0.z; ca[3] = a0.w; ca[4] = a1.x; ca[5] = a1.y; ca[6] = a1.z; ca[7] = a1.w;
-            if (A.qgamma) {
-                const float4 g0 = __ldg(reinterpret_cast<const float4*>(A.qgamma + c)), g1 = __ldg(reinterpret_cast<const float4*>(A.qgamma + c + 4));
-                ga_[0] = g0.x; ga_[1] = g0.y; ga_[2] = g0.z; ga_[3] = g0.w; ga_[4] = g1.x; ga_[5] = g1.y; ga_[6] = g1.z; ga_[7] = g1.w;
-            }
-        }
-        F8 o;
+    const int ct = threadIdx.x % geo.CT, rl = threadIdx.x / geo.CT;
+    const int64_t c0 = (int64_t)blockIdx.y * geo.tileC + (int64_t)ct * 8;
+    const int k = blockIdx.x / geo.S, sgm = blockIdx.x % geo.S;
+    const int64_t r_begin = (int64_t)k * geo.L + (int64_t)sgm * geo.seg_rows;
+    int64_t r_end = r_begin + geo.seg_rows;
+    if (r_end > (int64_t)(k + 1) * geo.L) r_end = (int64_t)(k + 1) * geo.L;
+    if (rl < geo.RL && c0 < geo.C) {
+        float sc[8], ca[8], gm[8], ce[8];
+        int32_t am[8], an[8];
 #pragma unroll
         for (int j = 0; j < 8; ++j) {
-            const float t = A.qgamma ? __fmul_rn(gq[j], ga_[j]) : gq[j];
-            o.v[j] = __fadd_rn(__fmul_rn(t, sc[j]), ca[j]);
+            sc[j] = __ldg(A.qscale + c0 + j);
+            ca[j] = __ldg(A.coef_a + c0 + j);
+            gm[j] = A.qgamma ? __ldg(A.qgamma + c0 + j) : 1.0f;
+            ce[j] = A.amax_kc ? __ldg(A.coef_e + c0 + j) : 0.0f;
+            am[j] = A.amax_kc ? __ldg(A.amax_kc + (size_t)k * A.C + c0 + j) : -1;
+            an[j] = A.amax_kc ? __ldg(A.amin_kc + (size_t)k * A.C + c0 + j) : -1;
         }
-        if (A.amax_kc) {
-            const uint32_t k = fdiv(row, A.dL);
-            const int32_t* pa = A.amax_kc + (size_t)k * A.C + c;
-            const int32_t* pi = A.amin_kc + (size_t)k * A.C + c;
-            const int4 x0 = __ldg(reinterpret_cast<const int4*>(pa)), x1 = __ldg(reinterpret_cast<const int4*>(pa + 4));
-            const int4 n0 = __ldg(reinterpret_cast<const int4*>(pi)), n1 = __ldg(reinterpret_cast<const int4*>(pi + 4));
-            const int32_t am[8] = {x0.x, x0.y, x0.z, x0.w, x1.x, x1.y, x1.z, x1.w};
-            const int32_t an[8] = {n0.x, n0.y, n0.z, n0.w, n1.x, n1.y, n1.z, n1.w};
-            bool any = false;
+        auto one_row = [&](const F8& raw, const uint2& pk, int64_t r) {
+            const int64_t e = r * geo.C + c0;
+            float gq[8];
+            if (NOISE == -2) {                            // 8 codes instead of 8 floats: dequantize only
 #pragma unroll
-            for (int j = 0; j < 8; ++j) any = any || am[j] == (int32_t)row || an[j] == (int32_t)row;
-            if (any) {                                    // 2*K rows out of B*H*W per channel: rare
-                const float4 e0 = __ldg(reinterpret_cast<const float4*>(A.coef_e + c)), e1 = __ldg(reinterpret_cast<const float4*>(A.coef_e + c + 4));
-                const float ce[8] = {e0.x, e0.y, e0.z, e0.w, e1.x, e1.y, e1.z, e1.w};
+                for (int j = 0; j < 4; ++j) {
+                    gq[j] = q_zp_deq((float)((pk.x >> (8 * j)) & 0xffu), GQ.p);
+                    gq[4 + j] = q_zp_deq((float)((pk.y >> (8 * j)) & 0xffu), GQ.p);
+                }
+            } else {
 #pragma unroll
-                for (int j = 0; j < 8; ++j) {
-                    if (am[j] == (int32_t)row) o.v[j] = __fadd_rn(o.v[j], ce[j]);
-                    if (an[j] == (int32_t)row) o.v[j] = __fsub_rn(o.v[j], ce[j]);
+                for (int j = 0; j < 8; ++j) gq[j] = raw.v[j];
+                if (NOISE >= 0) {
+                    float u[8];
+                    if (NOISE == NOISE_INJECT) {
+                        const F8 w = ld256_stream(ga.noise.inject + e);
+#pragma unroll
+                        for (int j = 0; j < 8; ++j) u[j] = w.v[j];
+                    } else if (NOISE == NOISE_PHILOX) {
+                        philox_noise8(seed, (uint64_t)(e >> 3) + (ga.noise.offset >> 3), u);
+                    }
+                    grad_fq_vec<(NOISE < 0 ? 0 : NOISE), 8>(gq, u, GQ);
                 }
             }
-        }
-        st256(dx + 8ull * i, o);                           // default policy: the next kernel re-reads dx (L2)
-        if (RANGE) {
+            F8 o;
+            const int32_t row = (int32_t)r;
 #pragma unroll
-            for (int j = 0; j < 8; ++j) { mn = fminf(mn, o.v[j]); mx = fmaxf(mx, o.v[j]); }
+            for (int j = 0; j < 8; ++j) {
+                const float t = A.qgamma ? __fmul_rn(gq[j], gm[j]) : gq[j];
+                float v = __fadd_rn(__fmul_rn(t, sc[j]), ca[j]);
+                if (am[j] == row) v = __fadd_rn(v, ce[j]);
+                if (an[j] == row) v = __fsub_rn(v, ce[j]);
+                o.v[j] = v;
+                if (RANGE) { mn = fminf(mn, v); mx = fmaxf(mx, v); }
+            }
+            st256(dx + e, o);                              // default policy: the next kernel re-reads dx (L2)
+        };
+        int64_t r = r_begin + rl;
+        const int64_t step = geo.RL;
+        for (; r + step < r_end; r += 2 * step) {
+            F8 v0, v1;
+            uint2 p0 = make_uint2(0, 0), p1 = make_uint2(0, 0);
+            if (NOISE == -2) {
+                p0 = __ldcs(reinterpret_cast<const uint2*>(ga.codes + r * geo.C + c0));
+                p1 = __ldcs(reinterpret_cast<const uint2*>(ga.codes + (r + step) * geo.C + c0));
+            } else {
+                v0 = ld256_stream(g + r * geo.C + c0);
+                v1 = ld256_stream(g + (r + step) * geo.C + c0);
+            }
+            one_row(v0, p0, r);
+            one_row(v1, p1, r + step);
+        }
+        for (; r < r_end; r += step) {
+            F8 v0;
+            uint2 p0 = make_uint2(0, 0);
+            if (NOISE == -2) p0 = __ldcs(reinterpret_cast<const uint2*>(ga.codes + r * geo.C + c0));
+            else v0 = ld256_stream(g + r * geo.C + c0);
+            one_row(v0, p0, r);
         }
     }
+    const unsigned int nblocks = gridDim.x * gridDim.y, bid = blockIdx.y * gridDim.x + blockIdx.x;
     if (!RANGE) return;
     mn = warp_min(mn);
     mx = warp_max(mx);
@@ -650,10 +680,10 @@ k_rbn_bwd_apply_fused(const float* __restrict__ g, float* __restrict__ dx, uint3
         mn = warp_min(l < NH_THREADS / 32 ? sm[l] : QB_INF);
         mx = warp_max(l < NH_THREADS / 32 ? sm[32 + l] : -QB_INF);
         if (l == 0) {
-            A.pmin[blockIdx.x] = mn;
-            A.pmax[blockIdx.x] = mx;
+            A.pmin[bid] = mn;
+            A.pmax[bid] = mx;
             __threadfence();
-            last = (atomicAdd(A.counter, 1u) == gridDim.x - 1);
+            last = (atomicAdd(A.counter, 1u) == nblocks - 1);
         }
     }
     __syncthreads();
@@ -661,7 +691,7 @@ k_rbn_bwd_apply_fused(const float* __restrict__ g, float* __restrict__ dx, uint3
     __threadfence();
     mn = QB_INF;
     mx = -QB_INF;
-    for (int i = threadIdx.x; i < (int)gridDim.x; i += NH_THREADS) {
+    for (int i = threadIdx.x; i < (int)nblocks; i += NH_THREADS) {
         mn = fminf(mn, __ldcg(&A.pmin[i]));
         mx = fmaxf(mx, __ldcg(&A.pmax[i]));
     }
@@ -679,10 +709,10 @@ k_rbn_bwd_apply_fused(const float* __restrict__ g, float* __restrict__ dx, uint3
 }
 
 template <int NOISE>
-static void launch_bwd_apply_fused(int grid, cudaStream_t st, const float* g, float* dx, uint32_t noct, const BwdApplyArgs& A,
-                                   const GradQuantArg& ga) {
-    if (A.range_out) k_rbn_bwd_apply_fused<NOISE, true><<<grid, NH_THREADS, 0, st>>>(g, dx, noct, A, ga);
-    else k_rbn_bwd_apply_fused<NOISE, false><<<grid, NH_THREADS, 0, st>>>(g, dx, noct, A, ga);
+static void launch_bwd_apply_fused(dim3 grid, cudaStream_t st, const float* g, float* dx, const NhwcGeom& geo,
+                                   const BwdApplyArgs& A, const GradQuantArg& ga) {
+    if (A.range_out) k_rbn_bwd_apply_fused<NOISE, true><<<grid, NH_THREADS, 0, st>>>(g, dx, geo, A, ga);
+    else k_rbn_bwd_apply_fused<NOISE, false><<<grid, NH_THREADS, 0, st>>>(g, dx, geo, A, ga);
 }
 
 /* Fused variant used when C % 8 == 0: g_range != NULL quantizes g on the fly (as in qb_rangebn_bwd_reduce_nhwc);
@@ -693,8 +723,11 @@ extern "C" int qb_rangebn_bwd_apply_fused_nhwc(const float* g, float* dx, int64_
                                                const float* coef_e, const int32_t* amax_kc, const int32_t* amin_kc,
                                                const float* g_range, int g_bits, const float* noise, int stochastic,
                                                uint64_t seed, uint64_t offset, const uint64_t* step_dev,
-                                               float* dx_range_out, void* mm_ws, size_t mm_ws_bytes, void* stream) {
-    QB_CHECK_ARG(g && dx && qscale && coef_a, "qb_rangebn_bwd_apply_fused_nhwc: null pointer");
+                                               const uint8_t* gq_codes, float* dx_range_out, void* mm_ws,
+                                               size_t mm_ws_bytes, void* stream) {
+    QB_CHECK_ARG((g || gq_codes) && dx && qscale && coef_a, "qb_rangebn_bwd_apply_fused_nhwc: null pointer");
+    QB_CHECK_ARG(!gq_codes || (g_range && g_bits <= 8 && (reinterpret_cast<uintptr_t>(gq_codes) & 7) == 0),
+                 "qb_rangebn_bwd_apply_fused_nhwc: codes input needs g_range, bits <= 8, 8-byte alignment");
     QB_CHECK_ARG(B > 0 && C > 0 && HW > 0, "qb_rangebn_bwd_apply_fused_nhwc: bad shape");
     QB_CHECK_ARG(!g_range || (g_bits >= 1 && g_bits <= 24), "qb_rangebn_bwd_apply_fused_nhwc: g_bits=%d", g_bits);
     const int64_t R = B * HW, n = R * C;
@@ -717,15 +750,29 @@ extern "C" int qb_rangebn_bwd_apply_fused_nhwc(const float* g, float* dx, int64_
     float* wsf = static_cast<float*>(mm_ws);
     A.pmin = wsf; A.pmax = wsf ? wsf + 4096 : nullptr;
     A.counter = wsf ? reinterpret_cast<unsigned int*>(wsf + 8192) : nullptr;
-    const int nm = grad_noise_mode(g_range, noise, stochastic);
-    GradQuantArg ga{g_range, g_bits, nm, NoiseArg{noise, seed, offset, step_dev}};
-    int grid = nh_grid(n >> 3);
-    if (grid > 4096) grid = 4096;
+    const int nm = gq_codes ? -2 : grad_noise_mode(g_range, noise, stochastic);
+    GradQuantArg ga{g_range, g_bits, nm, NoiseArg{noise, seed, offset, step_dev}, const_cast<uint8_t*>(gq_codes)};
+    // chunk-aligned row segments (a CTA never straddles two chunks, so its arg rows are loop invariant); enough CTAs
+    // to fill the machine several times, at most 4096 partial slots for the range reduction
+    const int Kc = scatter ? num_chunks : 1;
+    NhwcGeom geo = make_geom<8>(R, C, Kc, 256);
+    {
+        const int ctiles = (int)((C + geo.tileC - 1) / geo.tileC);
+        int64_t want = (148 * 8 + (int64_t)Kc * ctiles - 1) / ((int64_t)Kc * ctiles);
+        const int64_t max_by_rows = geo.L / ((int64_t)geo.RL * 2) > 0 ? geo.L / ((int64_t)geo.RL * 2) : 1;
+        if (want > max_by_rows) want = max_by_rows;
+        while ((int64_t)Kc * want * ctiles > 4096 && want > 1) --want;
+        geo.S = (int)(want < 1 ? 1 : want);
+        geo.seg_rows = (geo.L + geo.S - 1) / geo.S;
+        QB_CHECK_ARG((int64_t)Kc * geo.S * ctiles <= 4096, "qb_rangebn_bwd_apply_fused_nhwc: too many chunk x channel tiles");
+    }
+    dim3 grid((unsigned)(Kc * geo.S), (unsigned)((C + geo.tileC - 1) / geo.tileC));
     cudaStream_t st = qb_stream(stream);
-    if (nm < 0) launch_bwd_apply_fused<-1>(grid, st, g, dx, (uint32_t)(n >> 3), A, ga);
-    else if (nm == NOISE_NONE) launch_bwd_apply_fused<NOISE_NONE>(grid, st, g, dx, (uint32_t)(n >> 3), A, ga);
-    else if (nm == NOISE_INJECT) launch_bwd_apply_fused<NOISE_INJECT>(grid, st, g, dx, (uint32_t)(n >> 3), A, ga);
-    else launch_bwd_apply_fused<NOISE_PHILOX>(grid, st, g, dx, (uint32_t)(n >> 3), A, ga);
+    if (nm == -2) launch_bwd_apply_fused<-2>(grid, st, g, dx, geo, A, ga);
+    else if (nm < 0) launch_bwd_apply_fused<-1>(grid, st, g, dx, geo, A, ga);
+    else if (nm == NOISE_NONE) launch_bwd_apply_fused<NOISE_NONE>(grid, st, g, dx, geo, A, ga);
+    else if (nm == NOISE_INJECT) launch_bwd_apply_fused<NOISE_INJECT>(grid, st, g, dx, geo, A, ga);
+    else launch_bwd_apply_fused<NOISE_PHILOX>(grid, st, g, dx, geo, A, ga);
     QB_LAUNCH_CHECK();
     return QB_OK;
 }

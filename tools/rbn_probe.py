@@ -1,0 +1,51 @@
+"""RangeBN fused kernels at one ResNet-18 shape (default layer1: 256x64x56x56), for timing / ncu."""
+import os, sys
+import torch
+sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+import qtorch_b200  # noqa
+from qtorch_b200 import _abi
+
+B, C, H = [int(a) for a in (sys.argv[1:4] if len(sys.argv) > 3 else (256, 64, 56))]
+dev = torch.device("cuda")
+HW = H * H
+x = (torch.randn(B, C, H, H, device=dev) * 2).contiguous(memory_format=torch.channels_last)
+g = (torch.randn(B, C, H, H, device=dev) * 1e-3).contiguous(memory_format=torch.channels_last)
+g = g * (torch.rand_like(g) > 0.5)
+gamma, beta = torch.rand(C, device=dev) + 0.5, torch.randn(C, device=dev)
+rm, rv = torch.zeros(C, device=dev), torch.zeros(C, device=dev)
+qr = _abi.minmax(x)
+
+
+def fwd():
+    red, amax, amin = _abi.rangebn_stats(x, B, C, HW, 16, nhwc=True, q_range=qr, q_bits=8)
+    vec = _abi.rangebn_finalize(red, C, 16, B * HW, B * HW / 16, 1e-5, 0.1, True, 8, gamma, beta, rm, rv)
+    out = _abi.rangebn_apply(x, B, C, HW, vec, True, True, nhwc=True, q_range=qr, q_bits=8)
+    return vec, amax, amin, out
+
+
+def bwd(vec, amax, amin):
+    r = _abi.minmax(g)
+    gq = dict(range=r, bits=8, noise=None, stochastic=True, seed=7, step_dev=None)
+    return _abi.rangebn_backward(g, x, B, C, HW, 16, B * HW, B * HW / 16, True, vec, True, amax, amin, nhwc=True, q_range=qr,
+                                 q_bits=8, grad_quant=gq, want_dx_range=True)
+
+
+vec, amax, amin, out = fwd()
+for _ in range(3):
+    fwd()
+    bwd(vec, amax, amin)
+torch.cuda.synchronize()
+_abi.profile_begin()
+for _ in range(5):
+    fwd()
+    bwd(vec, amax, amin)
+torch.cuda.synchronize()
+recs = _abi.profile_end()
+agg = {}
+for name, nbytes, ms in recs:
+    a = agg.setdefault(name, [0.0, 0])
+    a[0] += ms
+    a[1] += 1
+n = x.numel()
+for k, (ms, c) in agg.items():
+    print("%-36s %.4f ms/call   %.2f B/elem-equivalent at 6551 GB/s" % (k, ms / c, ms / c * 6551e6 / n))
