@@ -8,6 +8,8 @@
 //   warp 0   : TMA producer (cp.async.bulk.tensor, 128-byte swizzle) into a multi-stage shared-memory ring
 //   warp 1   : TMEM allocation + single-thread tcgen05.mma.kind::i8 issue, accumulator in TMEM (128 lanes x 128 cols)
 //   warps 2-5: epilogue - tcgen05.ld the accumulator, apply the formula in fp64, store fp32
+#include <stdlib.h>
+
 #include "tc_common.cuh"
 
 // ------------------------------------------------------------------------------------------------
@@ -220,6 +222,20 @@ extern "C" int qb_rowsum_u8(const uint8_t* codes, int64_t rows, int64_t cols, in
     return QB_OK;
 }
 
+int qb_gemm_i8_pair_launch(const uint8_t* A, const uint8_t* B, float* C, int64_t M, int64_t N, int64_t K, int64_t ldc,
+                           const float* a_range, int a_bits, const float* b_row_min, const float* b_row_max, int b_bits,
+                           const int32_t* a_rowsum, const int32_t* b_rowsum, const float* bias, int b_offset, cudaStream_t st);
+
+// QB_GEMM_KERNEL=single|pair pins the kernel choice (tests, sweeps); default: CTA pairs once there are >= 8 pair tiles
+static int gemm_kernel_override() {
+    static int v = -1;
+    if (v < 0) {
+        const char* e = getenv("QB_GEMM_KERNEL");
+        v = !e ? 0 : (e[0] == 's' ? 1 : (e[0] == 'p' ? 2 : 0));
+    }
+    return v;
+}
+
 extern "C" int qb_gemm_i8(const uint8_t* A, const uint8_t* B, float* C, int64_t M, int64_t N, int64_t K, int64_t ldc,
                           const float* a_range, int a_bits, const float* b_row_min, const float* b_row_max, int b_bits,
                           const int32_t* a_rowsum, const int32_t* b_rowsum, const float* bias, int b_offset, void* stream) {
@@ -232,6 +248,15 @@ extern "C" int qb_gemm_i8(const uint8_t* A, const uint8_t* B, float* C, int64_t 
         return QB_ERR_UNSUPPORTED;
     }
     QB_CHECK_ARG(M < 2147483647LL && N < 2147483647LL && K < 2147483647LL, "qb_gemm_i8: dimension exceeds int32");
+    QB_CHECK_ARG(b_offset == 0 || b_offset == (1 << (b_bits - 1)), "qb_gemm_i8: b_offset must be 0 or 2^(b_bits-1)");
+    {
+        const bool pair_ok = (ldc & 3) == 0 && (reinterpret_cast<uintptr_t>(C) & 15) == 0;
+        const int64_t pair_tiles = ((M + 255) / 256) * ((N + 255) / 256);
+        const int ov = gemm_kernel_override();
+        if (pair_ok && (ov == 2 || (ov == 0 && pair_tiles >= 8)))
+            return qb_gemm_i8_pair_launch(A, B, C, M, N, K, ldc, a_range, a_bits, b_row_min, b_row_max, b_bits, a_rowsum,
+                                          b_rowsum, bias, b_offset, qb_stream(stream));
+    }
     CUtensorMap ta, tb;
     const uint64_t da[2] = {(uint64_t)K, (uint64_t)M}, db[2] = {(uint64_t)K, (uint64_t)N}, st[1] = {(uint64_t)K};
     const uint32_t box[2] = {(uint32_t)G_BK, (uint32_t)G_BM};
@@ -244,7 +269,6 @@ extern "C" int qb_gemm_i8(const uint8_t* A, const uint8_t* B, float* C, int64_t 
         QB_CUDA(cudaFuncSetAttribute(k_gemm_i8, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)G_SMEM_BYTES));
         attr_set = true;
     }
-    QB_CHECK_ARG(b_offset == 0 || b_offset == (1 << (b_bits - 1)), "qb_gemm_i8: b_offset must be 0 or 2^(b_bits-1)");
     GemmEpilogue ep{a_range, a_bits, b_row_min, b_row_max, b_bits, a_rowsum, b_rowsum, bias, b_offset};
     dim3 grid((unsigned)((N + G_BN - 1) / G_BN), (unsigned)((M + G_BM - 1) / G_BM));
     k_gemm_i8<<<grid, G_THREADS, G_SMEM_BYTES, qb_stream(stream)>>>(ta, tb, C, (int)M, (int)N, (int)K, ldc, ep);

@@ -27,7 +27,8 @@ def make_case(lib, M, N, K, seed, relu=True):
 
 
 @pytest.mark.parametrize("M,N,K", [(128, 128, 128), (128, 128, 1024), (256, 1000, 512), (100, 72, 80), (8, 10, 32),
-                                   (1000, 300, 2000), (2048, 1024, 1024), (129, 257, 144)])
+                                   (1000, 300, 2000), (2048, 1024, 1024), (129, 257, 144),
+                                   (2048, 2048, 2048), (1100, 1300, 1040), (4096, 512, 256), (777, 2052, 4112)])
 @pytest.mark.parametrize("relu", [True, False])
 def test_gemm_i8(lib, M, N, K, relu):
     c = make_case(lib, M, N, K, seed=M + N + K, relu=relu)
@@ -40,7 +41,7 @@ def test_gemm_i8(lib, M, N, K, relu):
     torch.cuda.synchronize()
     ref64 = c["xq"].double().cpu() @ c["wq"].double().cpu().t() + c["b"].double()
     rel = float((out.cpu().double() - ref64).norm() / ref64.norm())
-    assert rel < 2e-6, rel
+    assert rel < 5e-6, rel          # fp32 epilogue on centred integer sums (pair kernel) or fp64 epilogue (single)
     # the reference computes this product in fp32 on the CPU (quantize.py:424)
     lo, hi = qref.weight_row_range(c["w"])
     ref32 = torch.nn.functional.linear(qref.fq_affine(c["x"], 8, float(c["x"].min()), float(c["x"].max())),
@@ -54,7 +55,7 @@ def test_gemm_i8(lib, M, N, K, relu):
     assert torch.equal(wc.view(N, K).view(torch.int8).cpu().long() + 128, c["b_codes"].cpu().long())
     out2 = lib.gemm_i8(c["a_codes"], wc, M, N, K, c["rng"], 8, rmin2, rmax2, 8, ars, tapsum.view(N), bias=bias, b_offset=128)
     rel2 = float((out2.cpu().double() - ref64).norm() / ref64.norm())
-    assert rel2 < 2e-6, rel2
+    assert rel2 < 5e-6, rel2
 
 
 def test_gemm_i8_rejects_unaligned_k(lib):
