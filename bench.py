@@ -20,8 +20,12 @@ sys.path.insert(0, ROOT)
 
 import torch  # noqa: E402
 
-METRIC = "ResNet-18 8-bit train images/sec"
+METRICS = {"resnet18": "ResNet-18 8-bit train images/sec", "mobilenet": "MobileNet 8-bit train images/sec",
+           "resnet20_cifar": "ResNet-20 (CIFAR) 8-bit train images/sec"}
 UNIT = "images/s"
+INT8_PEAK_TOPS = 4500.0        # B200 datasheet, dense int8 (the bound of the QConv2d/QLinear contractions)
+DTYPE = ("u8 codes (activations) x s8 codes (weights) -> s32 on tcgen05 for the forward contractions; fp32 carrier for "
+         "fake-quantized tensors and statistics; backward contractions fp32/TF32 (cuDNN)")
 
 
 def parse():
@@ -82,7 +86,7 @@ def main_reference(args, rank):
     sample = "%s train step at batch %d (bounded sample of the batch-%d workload), torch-CPU oracle port" % (
         args.model, args.cpu_sample_batch, args.batch)
     print(json.dumps({
-        "impl": "reference", "metric": METRIC, "value": round(ips, 3), "unit": UNIT, "n_gpus": args.gpus,
+        "impl": "reference", "metric": METRICS[args.model], "value": round(ips, 3), "unit": UNIT, "n_gpus": args.gpus,
         "steps": args.steps, "warmup": args.warmup, "ms_per_step": round(spstep * 1e3, 2), "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "config": {"workload": workload_name(args), "per_gpu_batch": args.batch, "cpu_sample_batch": args.cpu_sample_batch},
@@ -248,9 +252,9 @@ def main_ours(args, rank, world, local_rank):
     imgs = B * world * args.steps
     h2d = host_x[0].numel() * 4 + host_y[0].numel() * 8
     line = {
-        "metric": METRIC, "value": round(imgs / (ms_dev / 1e3), 2), "unit": UNIT, "n_gpus": world, "steps": args.steps,
+        "metric": METRICS[args.model], "value": round(imgs / (ms_dev / 1e3), 2), "unit": UNIT, "n_gpus": world, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": round(ms_dev / args.steps, 3), "higher_is_better": True, "scaling": "weak",
-        "vs_baseline": None, "dtype": "u8 codes on an fp32 carrier (fake-quant); contraction fp32/tf32 cuDNN (round 1)",
+        "vs_baseline": None, "dtype": DTYPE,
         "data": "synthetic",
         "config": {"workload": workload_name(args), "per_gpu_batch": B, "global_batch": B * world,
                    "parallelism": "dp%d" % world, "cuda_graph": graph is not None,
@@ -288,12 +292,25 @@ def roofline_pass(step_body, _abi):
     top = max(fam.items(), key=lambda kv: kv[1][1])
     name, (nbytes, ms, calls) = top
     achieved = nbytes / ms / 1e6
+    fams = {}
+    for k, v in sorted(fam.items(), key=lambda kv: -kv[1][1]):
+        fams[k] = {"GBps": round(v[0] / v[1] / 1e6, 1), "ms": round(v[1], 3), "calls": v[2]}
+        ops = _abi.PROFILE_OPS.get(k)
+        if ops:                                    # tensor-core families: also against the int8 dense peak
+            fams[k]["TOPs"] = round(ops / v[1] / 1e9, 1)
+            fams[k]["frac_int8_peak"] = round(ops / v[1] / 1e9 / INT8_PEAK_TOPS, 4)
     return {"bound": "hbm", "kernel": name, "achieved": round(achieved, 1), "peak": peak, "peak_source": src,
-            "unit": "GB/s", "frac": round(achieved / peak, 4), "traffic": None, "launches_per_step": calls,
+            "unit": "GB/s", "frac": round(achieved / peak, 4), "traffic": TRAFFIC.get(name), "launches_per_step": calls,
             "algorithmic_bytes_per_step": nbytes, "ms_per_step": round(ms, 4),
-            "how": "CUDA events around each launch of one extra eager step after the timed region",
-            "families": {k: {"GBps": round(v[0] / v[1] / 1e6, 1), "ms": round(v[1], 3), "calls": v[2]}
-                         for k, v in sorted(fam.items(), key=lambda kv: -kv[1][1])}}
+            "how": "CUDA events around each launch of one extra eager step after the timed region; traffic = ncu "
+                   "dram__bytes_read.sum + dram__bytes_write.sum per launch, averaged over the step's launches of this "
+                   "kernel (profiles/, see DESIGN.md section 6), null when no capture of this kernel is committed",
+            "families": fams}
+
+
+# per-launch DRAM traffic of the dominant kernel families from the committed ncu --set full captures (bytes per launch,
+# mean over the launches of one ResNet-18 b256 step); filled from profiles/ncu_*_summary.txt
+TRAFFIC = {}
 
 
 def main():

@@ -101,10 +101,17 @@ _NLAUNCH = {"qb_rangebn_stats": 2, "qb_rangebn_bwd_reduce": 2, "qb_rangebn_bwd_a
             "qb_conv_i8_fwd": 2, "qb_rangebn_stats_nhwc": 3, "qb_rangebn_bwd_reduce_nhwc": 2, "qb_rangebn_bwd_apply_nhwc": 2}
 
 
+_next_ops = 0          # integer operations (2*M*N*K) of the next tensor-core call, set by the conv / GEMM wrappers
+PROFILE_OPS = {}       # name -> operations recorded between profile_begin() and profile_end()
+
+
 def _run(name, nbytes, *args):
     """Call one C-ABI entry point; count its launches; under profile_begin() bracket it with CUDA events on the
     launching stream."""
-    global LAUNCHES
+    global LAUNCHES, _next_ops
+    if _profile is not None and _next_ops:
+        PROFILE_OPS[name] = PROFILE_OPS.get(name, 0) + _next_ops
+    _next_ops = 0
     fn = getattr(load(), name)
     LAUNCHES += _NLAUNCH.get(name, 1)
     if _profile is None:
@@ -122,6 +129,7 @@ def _run(name, nbytes, *args):
 def profile_begin():
     global _profile
     _profile = []
+    PROFILE_OPS.clear()
 
 
 def profile_end():
@@ -414,8 +422,10 @@ def rowsum_u8(codes, rows, cols, out=None):
 def gemm_i8(a_codes, b_codes, M, N, K, a_range, a_bits, b_row_min, b_row_max, b_bits, a_rowsum, b_rowsum, bias=None,
             out=None, b_offset=0):
     """out[M,N] fp32 = dequantised (A_hat @ B_hat^T + bias) from uint8 codes (see qb_gemm_i8)."""
+    global _next_ops
     if out is None:
         out = torch.empty(M, N, dtype=torch.float32, device=a_codes.device)
+    _next_ops = 2 * M * N * K
     _run("qb_gemm_i8", M * K + N * K + 4 * M * N, _ptr(a_codes), _ptr(b_codes), _ptr(out), M, N, K, out.stride(0),
          _ptr(a_range), int(a_bits), _ptr(b_row_min), _ptr(b_row_max), int(b_bits), _ptr(a_rowsum), _ptr(b_rowsum),
          _ptr(bias), int(b_offset), _stream())
@@ -443,6 +453,8 @@ def conv_i8_fwd(x_codes, w_codes, B, H, W, Cin, Cout, kh, kw, stride, pad, a_ran
     out = torch.empty((B, Cout, Ho, Wo), dtype=torch.float32, device=x_codes.device, memory_format=torch.channels_last)
     boxsum = torch.empty(B * Ho * Wo, dtype=torch.int32, device=x_codes.device)
     ws = workspace("measure", load().qb_measure_ws_bytes(B), x_codes.device) if out_stats is not None else None
+    global _next_ops
+    _next_ops = 2 * B * Ho * Wo * Cout * kh * kw * Cin
     _run("qb_conv_i8_fwd", B * H * W * Cin + Cout * kh * kw * Cin + 4 * B * Ho * Wo * Cout, _ptr(x_codes), _ptr(w_codes),
          _ptr(out), B, H, W, Cin, Cout, kh, kw, stride, pad, _ptr(a_range), int(a_bits), _ptr(row_min), _ptr(row_max),
          int(w_bits), _ptr(pixsum), _ptr(boxsum), _ptr(tapsum), _ptr(bias), _ptr(out_stats), _ptr(ws),
