@@ -177,16 +177,19 @@ size_t qb_rangebn_nhwc_ws_bytes(int64_t C, int num_chunks);
  *   g_range/g_bits/noise/stochastic/seed/offset/step_dev   gq is the RAW output gradient and UniformQuantizeGrad's
  *                    backward (quantize.py:124-139, arguments as qb_fakequant_grad) is applied on the fly; the noise of
  *                    an element is a function of (seed, element index) so both backward passes see the same draw.
- *                    Needs C % 8 == 0 and 32-byte aligned tensors. */
+ *                    Needs C % 8 == 0 and 32-byte aligned tensors.
+ *   x_codes_out / x_codes   (q_bits <= 8, C % 8 == 0) the statistics pass also WRITES x_hat as uint8 codes [B, H*W, C];
+ *                    apply and the backward reduce then read those codes (1 B/elem) instead of re-reading and
+ *                    re-quantizing the fp32 input (x may be NULL there): the raw input need not be kept for backward. */
 int qb_rangebn_stats_nhwc(const float* x, int64_t B, int64_t C, int64_t HW, int num_chunks, int32_t* amax,
                           int32_t* amin, int32_t* amax_kc, int32_t* amin_kc, double* red, const float* q_range,
-                          int q_bits, void* ws, size_t ws_bytes, void* stream);
-int qb_rangebn_apply_nhwc(const float* x, float* out, int64_t B, int64_t C, int64_t HW, const float* mean,
-                          const float* qscale, const float* qgamma, const float* qbeta, const float* q_range,
-                          int q_bits, void* stream);
+                          int q_bits, uint8_t* x_codes_out, void* ws, size_t ws_bytes, void* stream);
+int qb_rangebn_apply_nhwc(const float* x, const uint8_t* x_codes, float* out, int64_t B, int64_t C, int64_t HW,
+                          const float* mean, const float* qscale, const float* qgamma, const float* qbeta,
+                          const float* q_range, int q_bits, void* stream);
 size_t qb_rangebn_bwd_nhwc_ws_bytes(int64_t C);
-int qb_rangebn_bwd_reduce_nhwc(const float* gq, const float* x, int64_t B, int64_t C, int64_t HW, double* sg,
-                               double* sgx, const float* q_range, int q_bits, const float* g_range, int g_bits,
+int qb_rangebn_bwd_reduce_nhwc(const float* gq, const float* x, const uint8_t* x_codes, int64_t B, int64_t C, int64_t HW,
+                               double* sg, double* sgx, const float* q_range, int q_bits, const float* g_range, int g_bits,
                                const float* noise, int stochastic, uint64_t seed, uint64_t offset,
                                const uint64_t* step_dev, uint8_t* gq_codes_out, void* ws, size_t ws_bytes, void* stream);
 /* dx = (Q(g)*qgamma)*qscale + a, +-e at the chunk arg-max/arg-min rows, in ONE pass, plus min/max of the final dx

@@ -43,10 +43,10 @@ PROTOTYPES = {
     "qb_rangebn_bwd_coeffs": (_i32, [_p, _p, _i64, _i32, _dbl, _dbl, _i32, _p, _p, _p, _p, _p, _p, _p, _p, _p]),
     "qb_rangebn_bwd_apply": (_i32, [_p, _p, _i64, _i64, _i64, _i32, _p, _p, _p, _p, _p, _p, _p]),
     "qb_rangebn_nhwc_ws_bytes": (_sz, [_i64, _i32]),
-    "qb_rangebn_stats_nhwc": (_i32, [_p, _i64, _i64, _i64, _i32, _p, _p, _p, _p, _p, _p, _i32, _p, _sz, _p]),
-    "qb_rangebn_apply_nhwc": (_i32, [_p, _p, _i64, _i64, _i64, _p, _p, _p, _p, _p, _i32, _p]),
+    "qb_rangebn_stats_nhwc": (_i32, [_p, _i64, _i64, _i64, _i32, _p, _p, _p, _p, _p, _p, _i32, _p, _p, _sz, _p]),
+    "qb_rangebn_apply_nhwc": (_i32, [_p, _p, _p, _i64, _i64, _i64, _p, _p, _p, _p, _p, _i32, _p]),
     "qb_rangebn_bwd_nhwc_ws_bytes": (_sz, [_i64]),
-    "qb_rangebn_bwd_reduce_nhwc": (_i32, [_p, _p, _i64, _i64, _i64, _p, _p, _p, _i32, _p, _i32, _p, _i32, _u64, _u64, _p,
+    "qb_rangebn_bwd_reduce_nhwc": (_i32, [_p, _p, _p, _i64, _i64, _i64, _p, _p, _p, _i32, _p, _i32, _p, _i32, _u64, _u64, _p,
                                           _p, _p, _sz, _p]),
     "qb_rangebn_bwd_apply_fused_nhwc": (_i32, [_p, _p, _i64, _i64, _i64, _i32, _p, _p, _p, _p, _p, _p, _p, _i32, _p, _i32,
                                                _u64, _u64, _p, _p, _p, _p, _sz, _p]),
@@ -294,10 +294,11 @@ def fakequant_grad_fused(g, bits, noise=None, stochastic=True, seed=0, offset=0,
 # ----------------------------------------------------------------------------------------------
 # RangeBN
 # ----------------------------------------------------------------------------------------------
-def rangebn_stats(x, B, Cn, HW, num_chunks, want_arg=True, nhwc=False, q_range=None, q_bits=8):
+def rangebn_stats(x, B, Cn, HW, num_chunks, want_arg=True, nhwc=False, q_range=None, q_bits=8, x_codes_out=None):
     """x: RangeBN input (already fake-quantized, or RAW with ``q_range``: channels-last only, the quantizer then runs
     inside the kernel).  Returns (red double[3*C], amax int32 | None, amin | None).  For channels-last, amax / amin
-    are [2, C*K]: row 0 in the reference's [c][k] order, row 1 transposed to [k][c] for the fused backward."""
+    are [2, C*K]: row 0 in the reference's [c][k] order, row 1 transposed to [k][c] for the fused backward.
+    ``x_codes_out`` (uint8, x.numel() elements): also receives x_hat as integer codes (see qb200.h)."""
     lib = load()
     dev = x.device
     red = torch.empty(3 * Cn, dtype=torch.float64, device=dev)
@@ -306,11 +307,13 @@ def rangebn_stats(x, B, Cn, HW, num_chunks, want_arg=True, nhwc=False, q_range=N
     if nhwc:
         amax = torch.empty(2, Cn * num_chunks, dtype=torch.int32, device=dev) if want_arg else None
         amin = torch.empty(2, Cn * num_chunks, dtype=torch.int32, device=dev) if want_arg else None
-        _run("qb_rangebn_stats_nhwc", 4 * B * Cn * HW, _ptr(x), B, Cn, HW, num_chunks,
+        _run("qb_rangebn_stats_nhwc", (4 + (1 if x_codes_out is not None else 0)) * B * Cn * HW, _ptr(x), B, Cn, HW, num_chunks,
              _ptr(amax[0]) if want_arg else None, _ptr(amin[0]) if want_arg else None,
              _ptr(amax[1]) if want_arg else None, _ptr(amin[1]) if want_arg else None, _ptr(red),
-             _ptr(q_range), int(q_bits), _ptr(ws), ws.numel(), _stream())
+             _ptr(q_range), int(q_bits), _ptr(x_codes_out), _ptr(ws), ws.numel(), _stream())
         return red, amax, amin
+    if x_codes_out is not None:
+        raise QB200Error("rangebn_stats: x_codes_out is a channels-last feature")
     if q_range is not None:
         raise QB200Error("rangebn_stats: on-the-fly input quantization is a channels-last feature")
     amax = torch.empty(Cn * num_chunks, dtype=torch.int32, device=dev) if want_arg else None
@@ -333,30 +336,33 @@ def rangebn_finalize(red, Cn, num_chunks, count, chunk_len, eps, momentum, train
     return vec
 
 
-def rangebn_apply(x, B, Cn, HW, vec, has_gamma, has_beta, out=None, nhwc=False, q_range=None, q_bits=8):
+def rangebn_apply(x, B, Cn, HW, vec, has_gamma, has_beta, out=None, nhwc=False, q_range=None, q_bits=8, x_codes=None):
+    """``x_codes`` (channels-last): x_hat as the uint8 codes rangebn_stats wrote; x is then used for its shape only."""
     lib = load()
     if out is None:
         out = torch.empty_like(x)
-    args = [_ptr(x), _ptr(out), B, Cn, HW, _ptr(vec[0]), _ptr(vec[2]), _ptr(vec[3]) if has_gamma else None,
-            _ptr(vec[4]) if has_beta else None]
+    args = [_ptr(x)] + ([_ptr(x_codes)] if nhwc else []) + [
+        _ptr(out), B, Cn, HW, _ptr(vec[0]), _ptr(vec[2]), _ptr(vec[3]) if has_gamma else None,
+        _ptr(vec[4]) if has_beta else None]
     if nhwc:
         args += [_ptr(q_range), int(q_bits)]
-    elif q_range is not None:
-        raise QB200Error("rangebn_apply: on-the-fly input quantization is a channels-last feature")
-    _run("qb_rangebn_apply" + ("_nhwc" if nhwc else ""), 8 * B * Cn * HW, *args, _stream())
+    elif q_range is not None or x_codes is not None:
+        raise QB200Error("rangebn_apply: on-the-fly input quantization / x_codes are channels-last features")
+    _run("qb_rangebn_apply" + ("_nhwc" if nhwc else ""), (5 if x_codes is not None else 8) * B * Cn * HW, *args, _stream())
     return out
 
 
 def rangebn_backward(gq, xq, B, Cn, HW, num_chunks, count, chunk_len, training, vec, has_gamma, amax, amin,
                      reduce_hook=None, chunks_global=None, nhwc=False, q_range=None, q_bits=8, grad_quant=None,
-                     want_dx_range=False):
+                     want_dx_range=False, x_codes=None):
     """Returns (dx, dgamma, dbeta[, dx_range]).  ``reduce_hook(sums)`` may all-reduce the double[2*C] sums in place
     (batch-sharded training); ``num_chunks`` is this rank's chunk count (layout of amax/amin),
     ``chunks_global`` the count the chunk-mean was taken over.
 
     Channels-last fusion: ``q_range`` - xq is the RAW RangeBN input, quantized on the fly; ``grad_quant`` =
     dict(range=float[2] device tensor, bits, noise, stochastic, seed, step_dev) - gq is the RAW output gradient,
-    quantized on the fly in both passes; ``want_dx_range`` - also return min/max of dx (float[2])."""
+    quantized on the fly in both passes; ``want_dx_range`` - also return min/max of dx (float[2]); ``x_codes`` - x_hat
+    as the uint8 codes the forward statistics pass wrote (xq may then be None)."""
     lib = load()
     dev = gq.device
     if chunks_global is None:
@@ -376,11 +382,12 @@ def rangebn_backward(gq, xq, B, Cn, HW, num_chunks, count, chunk_len, training, 
     if fused and grad_quant is not None and int(grad_quant["bits"]) <= 8:
         codes = torch.empty(gq.numel(), dtype=torch.uint8, device=dev)   # Q(g) handed from the reduce to the apply pass
     if nhwc:
-        _run("qb_rangebn_bwd_reduce_nhwc", 8 * B * Cn * HW, _ptr(gq), _ptr(xq), B, Cn, HW, _ptr(sums[:Cn]), _ptr(sums[Cn:]),
-             _ptr(q_range), int(q_bits), *gqa, _ptr(codes), _ptr(ws), ws.numel(), _stream())
+        nb = 4 + (1 if x_codes is not None else 4) + (1 if codes is not None else 0)
+        _run("qb_rangebn_bwd_reduce_nhwc", nb * B * Cn * HW, _ptr(gq), _ptr(xq), _ptr(x_codes), B, Cn, HW, _ptr(sums[:Cn]),
+             _ptr(sums[Cn:]), _ptr(q_range), int(q_bits), *gqa, _ptr(codes), _ptr(ws), ws.numel(), _stream())
     else:
-        if q_range is not None:
-            raise QB200Error("rangebn_backward: on-the-fly input quantization is a channels-last feature")
+        if q_range is not None or x_codes is not None:
+            raise QB200Error("rangebn_backward: on-the-fly input quantization / x_codes are channels-last features")
         _run("qb_rangebn_bwd_reduce", 8 * B * Cn * HW, _ptr(gq), _ptr(xq), B, Cn, HW, _ptr(sums[:Cn]), _ptr(sums[Cn:]),
              _ptr(ws), ws.numel(), _stream())
     if reduce_hook is not None:
@@ -397,7 +404,7 @@ def rangebn_backward(gq, xq, B, Cn, HW, num_chunks, count, chunk_len, training, 
         if want_dx_range:
             dx_range = torch.empty(2, dtype=torch.float32, device=dev)
             mm = workspace("minmax", lib.qb_minmax_ws_bytes(), dev)
-        _run("qb_rangebn_bwd_apply_fused_nhwc", 8 * B * Cn * HW, _ptr(gq), _ptr(dx), B, Cn, HW,
+        _run("qb_rangebn_bwd_apply_fused_nhwc", (5 if codes is not None else 8) * B * Cn * HW, _ptr(gq), _ptr(dx), B, Cn, HW,
              int(num_chunks) if training else 0, _ptr(vec[2]), _ptr(vec[3]) if has_gamma else None, _ptr(coef[2]),
              _ptr(coef[3]) if training else None, _ptr(amax[1]) if training else None,
              _ptr(amin[1]) if training else None, *gqa, _ptr(codes), _ptr(dx_range), _ptr(mm),

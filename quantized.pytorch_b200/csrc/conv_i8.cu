@@ -13,6 +13,8 @@
 // of the UMMA M=128 tile; unused rows are never stored) x BN output channels.  For filter tap (r,s) and channel block cb
 // the A operand is ONE 4-D TMA box {BK channels, TW, TH, TN} of the NHWC code tensor at (cb*BK, wo0*stride-pad+s,
 // ho0*stride-pad+r, b0) with element strides (1, stride, stride, 1): no im2col buffer exists anywhere.
+#include <stdlib.h>
+
 #include "tc_common.cuh"
 
 constexpr int CV_THREADS = 320;      // TMA warp, MMA warp, 2 x 4 epilogue warps
@@ -26,6 +28,7 @@ struct ConvGeom {
     int tiles_w, tiles_h, tiles_b;
     int BK;                     // bytes (= channels) of K per pipeline stage: 32, 64 or 128
     int stages;
+    int halo;                   // 1: 3x3 / stride 1 / Cin == BK, Cout == BN: column-shifted halo boxes + resident weights
 };
 
 struct ConvEpilogue {
@@ -84,14 +87,21 @@ k_conv_i8(const __grid_constant__ CUtensorMap tmap_x, const __grid_constant__ CU
           const __grid_constant__ CUtensorMap tmap_o, ConvGeom g, ConvEpilogue ep) {
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
-    const uint32_t a_bytes = 128u * g.BK, b_bytes = (uint32_t)BN * g.BK, stage_bytes = a_bytes + b_bytes;
-    float* staging = reinterpret_cast<float*>(smem + (size_t)g.stages * stage_bytes);          // 1024-byte aligned
+    // halo mode: a stage holds the kw column-shifted boxes {BK, TW, TH+kh-1} of ONE tile (tap (r,s) = box s advanced by
+    // r*TW rows = whole 8-row swizzle atoms since TW % 8 == 0); all kh*kw weight slabs stay resident behind the ring
+    const uint32_t hbox_bytes = (uint32_t)(g.BK * g.TW * (g.TH + g.kh - 1));
+    const uint32_t a_bytes = 128u * g.BK, b_bytes = (uint32_t)BN * g.BK;
+    const uint32_t stage_bytes = g.halo ? (uint32_t)g.kw * hbox_bytes : a_bytes + b_bytes;
+    uint8_t* wres = smem + (size_t)g.stages * stage_bytes;
+    const uint32_t wres_bytes = g.halo ? (uint32_t)(g.kh * g.kw) * b_bytes : 0u;
+    float* staging = reinterpret_cast<float*>(wres + wres_bytes);                               // 1024-byte aligned
     uint8_t* tail = reinterpret_cast<uint8_t*>(staging) + CV_STAGING_BYTES;
     uint64_t* full_bar = reinterpret_cast<uint64_t*>(tail);
     uint64_t* empty_bar = full_bar + CV_MAX_STAGES;
     uint64_t* tfull_bar = empty_bar + CV_MAX_STAGES;           // [2] accumulator buffer ready
     uint64_t* tempty_bar = tfull_bar + 2;                      // [2] accumulator buffer drained
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty_bar + 2);
+    uint64_t* wfull_bar = reinterpret_cast<uint64_t*>(tail + 296);   // halo mode: resident weights have landed
     float4* s_coef = reinterpret_cast<float4*>(tail + 320);   // {sa*sw[n], sa*lw'[n], bias[n], la*(sw*Tall + lw'*K)}
     float* s_c3 = reinterpret_cast<float*>(s_coef + BN);      // la*sw[n]      (border pixels of inputs with min != 0)
     float* s_c4 = s_c3 + BN;                                   // la*lw'[n]
@@ -118,6 +128,7 @@ k_conv_i8(const __grid_constant__ CUtensorMap tmap_x, const __grid_constant__ CU
             mbar_init(&tfull_bar[i], 1);
             mbar_init(&tempty_bar[i], 8);                      // one arrival per epilogue warp
         }
+        mbar_init(wfull_bar, 1);
         fence_barrier_init();
     }
     if (warp == 1) tmem_alloc<TMEM_COLS>(tmem_slot);
@@ -128,7 +139,25 @@ k_conv_i8(const __grid_constant__ CUtensorMap tmap_x, const __grid_constant__ CU
 
     if (warp == 0) {
         // ===== TMA producer =====
-        if (elect_one()) {
+        const bool lead = elect_one();
+        if (lead && g.halo) {
+            mbar_arrive_expect_tx(wfull_bar, wres_bytes);
+            for (int tap = 0; tap < taps; ++tap) tma_load_2d(wres + (size_t)tap * b_bytes, &tmap_w, wfull_bar, tap * g.Cin, 0);
+            uint32_t it = 0;
+            for (int t = blockIdx.x; t < total_tiles; t += gridDim.x, ++it) {
+                int tm = t;                                     // tiles_n == 1 in halo mode
+                const int tw_i = tm % g.tiles_w; tm /= g.tiles_w;
+                const int th_i = tm % g.tiles_h; tm /= g.tiles_h;
+                const int b0 = tm * g.TN, ho0 = th_i * g.TH, wo0 = tw_i * g.TW;
+                const int s = it % g.stages;
+                const uint32_t ph = (it / g.stages) & 1;
+                mbar_wait(&empty_bar[s], ph ^ 1);
+                mbar_arrive_expect_tx(&full_bar[s], stage_bytes);
+                uint8_t* sa = smem + (size_t)s * stage_bytes;
+                for (int s_ = 0; s_ < g.kw; ++s_)
+                    tma_load_4d(sa + (size_t)s_ * hbox_bytes, &tmap_x, &full_bar[s], 0, wo0 - g.pad + s_, ho0 - g.pad, b0);
+            }
+        } else if (lead) {
             uint32_t it = 0;
             for (int t = blockIdx.x; t < total_tiles; t += gridDim.x) {
                 const int tn = t / tiles_m;
@@ -164,6 +193,29 @@ k_conv_i8(const __grid_constant__ CUtensorMap tmap_x, const __grid_constant__ CU
             mbar_wait(&tempty_bar[buf], ((j >> 1) & 1) ^ 1);       // epilogue has drained this buffer (first use passes)
             tc_fence_after_sync();
             const uint32_t d_tmem = tmem_base + (uint32_t)(buf * BN);
+            if (g.halo) {
+                if (j == 0) mbar_wait(wfull_bar, 0);
+                const int s = it % g.stages;
+                const uint32_t ph = (it / g.stages) & 1;
+                mbar_wait(&full_bar[s], ph);
+                tc_fence_after_sync();
+                if (elect_one()) {
+                    const uint32_t st_addr = smem_u32(smem + (size_t)s * stage_bytes), w_addr = smem_u32(wres);
+                    for (int r = 0; r < g.kh; ++r)
+                        for (int s_ = 0; s_ < g.kw; ++s_) {
+                            const uint32_t a_addr = st_addr + (uint32_t)s_ * hbox_bytes + (uint32_t)(r * g.TW * g.BK);
+                            const uint32_t b_addr = w_addr + (uint32_t)(r * g.kw + s_) * b_bytes;
+                            for (int k = 0; k < mmas; ++k)
+                                umma_i8(d_tmem, umma_smem_desc(a_addr + k * 32, g.BK), umma_smem_desc(b_addr + k * 32, g.BK),
+                                        idesc, (r | s_ | k) != 0);
+                        }
+                    umma_commit(&empty_bar[s]);
+                    umma_commit(&tfull_bar[buf]);
+                }
+                __syncwarp();
+                ++it;
+                continue;
+            }
             for (int kb = 0; kb < num_kb; ++kb, ++it) {
                 const int s = it % g.stages;
                 const uint32_t ph = (it / g.stages) & 1;
@@ -512,8 +564,9 @@ static size_t conv_tail_bytes(int BN, int taps) { return 320 + (size_t)BN * 24 +
 template <int BN>
 static int launch_conv(const CUtensorMap& tx, const CUtensorMap& tw, const CUtensorMap& to, const ConvGeom& g,
                        const ConvEpilogue& ep, cudaStream_t st) {
-    const size_t stage = (size_t)(128 + BN) * g.BK;
-    const size_t smem = (size_t)g.stages * stage + CV_STAGING_BYTES + 1024 + conv_tail_bytes(BN, g.kh * g.kw);
+    const size_t stage = g.halo ? (size_t)g.kw * g.BK * g.TW * (g.TH + g.kh - 1) : (size_t)(128 + BN) * g.BK;
+    const size_t smem = (size_t)g.stages * stage + CV_STAGING_BYTES + 1024 + conv_tail_bytes(BN, g.kh * g.kw) +
+                        (g.halo ? (size_t)g.kh * g.kw * BN * g.BK : 0);
     static size_t configured = 0;
     if (smem > configured) {
         QB_CUDA(cudaFuncSetAttribute(k_conv_i8<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
@@ -558,9 +611,20 @@ extern "C" int qb_conv_i8_fwd(const uint8_t* x_codes, const uint8_t* w_codes_khw
     g.tiles_h = (int)((Ho + g.TH - 1) / g.TH);
     g.tiles_b = (int)((B + g.TN - 1) / g.TN);
     const int BN = Cout >= 256 ? 256 : (Cout >= 128 ? 128 : 64);
+    // halo mode (see the kernel): 3x3, stride 1, pad 1, all input channels in one K block, all output channels in one
+    // N tile, and an 8 x 16 pixel tile so that a filter-row shift is a whole number of swizzle atoms
+    static const bool halo_off = getenv("QB_CONV_HALO") && getenv("QB_CONV_HALO")[0] == '0';
+    g.halo = (!halo_off && kh == 3 && kw == 3 && stride == 1 && pad == 1 && Cin == g.BK && Cout == BN && BN == 64 && Wo >= 8 &&
+              Ho >= 16) ? 1 : 0;
+    if (g.halo) {
+        g.TW = 8; g.TH = 16; g.TN = 1;
+        g.tiles_w = (int)((Wo + g.TW - 1) / g.TW);
+        g.tiles_h = (int)((Ho + g.TH - 1) / g.TH);
+        g.tiles_b = (int)B;
+    }
     {
-        const size_t stage = (size_t)(128 + BN) * g.BK;
-        const size_t fixed = CV_STAGING_BYTES + 1024 + conv_tail_bytes(BN, kh * kw);
+        const size_t stage = g.halo ? (size_t)kw * g.BK * g.TW * (g.TH + kh - 1) : (size_t)(128 + BN) * g.BK;
+        const size_t fixed = CV_STAGING_BYTES + 1024 + conv_tail_bytes(BN, kh * kw) + (g.halo ? (size_t)kh * kw * BN * g.BK : 0);
         int s = (int)((225 * 1024 - fixed) / stage);
         g.stages = s > CV_MAX_STAGES ? CV_MAX_STAGES : (s < 2 ? 2 : s);
     }
@@ -575,7 +639,8 @@ extern "C" int qb_conv_i8_fwd(const uint8_t* x_codes, const uint8_t* w_codes_khw
     {   // activations: dims innermost-first {Cin, W, H, B}
         const uint64_t dims[4] = {(uint64_t)Cin, (uint64_t)W, (uint64_t)H, (uint64_t)B};
         const uint64_t str[3] = {(uint64_t)Cin, (uint64_t)W * Cin, (uint64_t)H * W * Cin};
-        const uint32_t box[4] = {(uint32_t)g.BK, (uint32_t)(g.TW * stride), (uint32_t)(g.TH * stride), (uint32_t)g.TN};
+        const uint32_t box[4] = {(uint32_t)g.BK, (uint32_t)(g.TW * stride), (uint32_t)((g.TH + (g.halo ? kh - 1 : 0)) * stride),
+                                 (uint32_t)g.TN};
         const uint32_t es[4] = {1, (uint32_t)stride, (uint32_t)stride, 1};
         int rc = qb_make_tmap(&tx, CU_TENSOR_MAP_DATA_TYPE_UINT8, 4, x_codes, dims, str, box, es, g.BK);
         if (rc) return rc;

@@ -64,13 +64,25 @@ template <> __device__ __forceinline__ F8 ld_vec_stream<F8>(const float* p) { re
 __device__ __forceinline__ void unpack(const float4& v, float (&a)[4]) { a[0] = v.x; a[1] = v.y; a[2] = v.z; a[3] = v.w; }
 __device__ __forceinline__ void unpack(const float& v, float (&a)[1]) { a[0] = v; }
 
+template <int VEC>
+__device__ __forceinline__ void store_codes(uint8_t* dst, const uint32_t (&cd)[VEC]) {
+    if (VEC == 1) {
+        *dst = (uint8_t)cd[0];
+    } else {
+#pragma unroll
+        for (int j = 0; j < VEC; j += 4)
+            *reinterpret_cast<uint32_t*>(dst + j) = cd[j] | (cd[j + 1 < VEC ? j + 1 : 0] << 8) | (cd[j + 2 < VEC ? j + 2 : 0] << 16) |
+                                                    (cd[j + 3 < VEC ? j + 3 : 0] << 24);
+    }
+}
+
 // ---------------------------------------------------------------------------------------------------
 // forward statistics: partials per (chunk k, segment s, channel c)
 // ---------------------------------------------------------------------------------------------------
 template <int VEC, bool QUANT>
 __global__ void __launch_bounds__(NH_THREADS)
 k_rbn_stats_nhwc(const float* __restrict__ x, NhwcGeom g, float* pmax, float* pmin, int32_t* imax, int32_t* imin,
-                 double* psum, const float* q_range, int q_bits) {
+                 double* psum, const float* q_range, int q_bits, uint8_t* __restrict__ codes_out) {
     using V = typename VecT<VEC>::T;
     AffineQ aq;
     if (QUANT) aq = load_affineq(q_range, q_bits);
@@ -100,7 +112,15 @@ k_rbn_stats_nhwc(const float* __restrict__ x, NhwcGeom g, float* pmax, float* pm
                 float a[VEC];
                 unpack(v[u], a);
                 const int32_t idx = (int32_t)(r + u * step);
-                if (QUANT) affine_fq_vec<VEC>(a, aq);
+                if (QUANT) {
+                    if (codes_out) {          // x_hat leaves as uint8 codes: the later passes read 1 B/elem instead of 4
+                        uint32_t cd[VEC];
+                        affine_fq_vec<VEC>(a, aq, cd);
+                        store_codes<VEC>(codes_out + (r + u * step) * g.C + c0, cd);
+                    } else {
+                        affine_fq_vec<VEC>(a, aq);
+                    }
+                }
 #pragma unroll
                 for (int j = 0; j < VEC; ++j) { amax_upd(mx[j], a[j], idx); amin_upd(mn[j], a[j], idx); fs[j] += a[j]; }
             }
@@ -113,7 +133,15 @@ k_rbn_stats_nhwc(const float* __restrict__ x, NhwcGeom g, float* pmax, float* pm
         for (; r < r_end; r += step) {
             float a[VEC];
             unpack(__ldcs(reinterpret_cast<const V*>(x + r * g.C + c0)), a);
-            if (QUANT) affine_fq_vec<VEC>(a, aq);
+            if (QUANT) {
+                if (codes_out) {
+                    uint32_t cd[VEC];
+                    affine_fq_vec<VEC>(a, aq, cd);
+                    store_codes<VEC>(codes_out + r * g.C + c0, cd);
+                } else {
+                    affine_fq_vec<VEC>(a, aq);
+                }
+            }
 #pragma unroll
             for (int j = 0; j < VEC; ++j) { amax_upd(mx[j], a[j], (int32_t)r); amin_upd(mn[j], a[j], (int32_t)r); fs[j] += a[j]; }
         }
@@ -160,6 +188,7 @@ __global__ void k_rbn_stats_nhwc_merge(const float* pmax, const float* pmin, con
     const int64_t k = t / C, c = t - k * C;
     ArgV mx{-QB_INF, 0x7fffffff}, mn{QB_INF, 0x7fffffff};
     double ssum = 0.0;
+#pragma unroll 8
     for (int s = 0; s < S; ++s) {
         const int64_t o = (k * S + s) * C + c;
         amax_merge(mx, pmax[o], imax[o]);
@@ -200,7 +229,8 @@ static size_t nhwc_smem(const NhwcGeom& g, int vec, int per_elem) { return (size
 
 extern "C" int qb_rangebn_stats_nhwc(const float* x, int64_t B, int64_t C, int64_t HW, int num_chunks, int32_t* amax,
                                      int32_t* amin, int32_t* amax_kc, int32_t* amin_kc, double* red, const float* q_range,
-                                     int q_bits, void* ws, size_t ws_bytes, void* stream) {
+                                     int q_bits, uint8_t* x_codes_out, void* ws, size_t ws_bytes, void* stream) {
+    QB_CHECK_ARG(!x_codes_out || (q_range && q_bits <= 8), "qb_rangebn_stats_nhwc: x_codes_out needs q_range and q_bits <= 8");
     QB_CHECK_ARG(!q_range || (q_bits >= 1 && q_bits <= 24), "qb_rangebn_stats_nhwc: q_bits=%d", q_bits);
     QB_CHECK_ARG(x && red && ws, "qb_rangebn_stats_nhwc: null pointer");
     QB_CHECK_ARG(B > 0 && C > 0 && HW > 0 && num_chunks > 0, "qb_rangebn_stats_nhwc: bad shape");
@@ -228,13 +258,13 @@ extern "C" int qb_rangebn_stats_nhwc(const float* x, int64_t B, int64_t C, int64
     dim3 grid((unsigned)(num_chunks * g.S), (unsigned)((C + g.tileC - 1) / g.tileC));
     cudaStream_t st = qb_stream(stream);
     if (vec4 && q_range)
-        k_rbn_stats_nhwc<4, true><<<grid, NH_THREADS, nhwc_smem(g, 4, 24), st>>>(x, g, pmax, pmin, imax, imin, psum, q_range, q_bits);
+        k_rbn_stats_nhwc<4, true><<<grid, NH_THREADS, nhwc_smem(g, 4, 24), st>>>(x, g, pmax, pmin, imax, imin, psum, q_range, q_bits, x_codes_out);
     else if (vec4)
-        k_rbn_stats_nhwc<4, false><<<grid, NH_THREADS, nhwc_smem(g, 4, 24), st>>>(x, g, pmax, pmin, imax, imin, psum, nullptr, 0);
+        k_rbn_stats_nhwc<4, false><<<grid, NH_THREADS, nhwc_smem(g, 4, 24), st>>>(x, g, pmax, pmin, imax, imin, psum, nullptr, 0, nullptr);
     else if (q_range)
-        k_rbn_stats_nhwc<1, true><<<grid, NH_THREADS, nhwc_smem(g, 1, 24), st>>>(x, g, pmax, pmin, imax, imin, psum, q_range, q_bits);
+        k_rbn_stats_nhwc<1, true><<<grid, NH_THREADS, nhwc_smem(g, 1, 24), st>>>(x, g, pmax, pmin, imax, imin, psum, q_range, q_bits, x_codes_out);
     else
-        k_rbn_stats_nhwc<1, false><<<grid, NH_THREADS, nhwc_smem(g, 1, 24), st>>>(x, g, pmax, pmin, imax, imin, psum, nullptr, 0);
+        k_rbn_stats_nhwc<1, false><<<grid, NH_THREADS, nhwc_smem(g, 1, 24), st>>>(x, g, pmax, pmin, imax, imin, psum, nullptr, 0, nullptr);
     QB_LAUNCH_CHECK();
     k_rbn_stats_nhwc_merge<<<(unsigned)((nk + 127) / 128), 128, 0, st>>>(pmax, pmin, imax, imin, psum, C, num_chunks, g.S,
                                                                         amax, amin, amax_kc, amin_kc, cmax, cmin, csum);
@@ -317,6 +347,48 @@ k_rbn_apply_nhwc(const float* __restrict__ x, float* out, uint32_t n, FastDiv dC
     }
 }
 
+// Forward normalisation from the uint8 codes the statistics pass wrote (C % 8 == 0): 1 + 4 B/elem.  Column-persistent:
+// a thread keeps mean / qscale / qgamma / qbeta of its 8 channels in registers and strides over rows.
+__global__ void __launch_bounds__(NH_THREADS)
+k_rbn_apply_codes_nhwc(const uint8_t* __restrict__ codes, float* __restrict__ out, NhwcGeom geo, NhwcVecs p) {
+    const AffineQ aq = load_affineq(p.q_range, p.q_bits);
+    const int ct = threadIdx.x % geo.CT, rl = threadIdx.x / geo.CT;
+    const int64_t c0 = (int64_t)blockIdx.y * geo.tileC + (int64_t)ct * 8;
+    const int64_t r_begin = (int64_t)blockIdx.x * geo.seg_rows;
+    const int64_t r_end = (r_begin + geo.seg_rows < geo.R) ? r_begin + geo.seg_rows : geo.R;
+    if (rl >= geo.RL || c0 >= geo.C) return;
+    float mu[8], sc[8], gm[8], be[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+        mu[j] = __ldg(p.p0 + c0 + j);
+        sc[j] = __ldg(p.p1 + c0 + j);
+        gm[j] = p.p2 ? __ldg(p.p2 + c0 + j) : 1.0f;
+        be[j] = p.p3 ? __ldg(p.p3 + c0 + j) : 0.0f;
+    }
+    auto one_row = [&](const uint2& pk, int64_t r) {
+        F8 o;
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+            const float xh = q_affine_deq((float)(((j < 4 ? pk.x : pk.y) >> (8 * (j & 3))) & 0xffu), aq.p);
+            float t = __fmul_rn(__fsub_rn(xh, mu[j]), sc[j]);
+            if (p.p2) t = __fmul_rn(t, gm[j]);
+            if (p.p3) t = __fadd_rn(t, be[j]);
+            o.v[j] = t;
+        }
+        st256(out + r * geo.C + c0, o);
+    };
+    const int64_t step = geo.RL;
+    int64_t r = r_begin + rl;
+    for (; r + 3 * step < r_end; r += 4 * step) {
+        uint2 pk[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u) pk[u] = __ldcs(reinterpret_cast<const uint2*>(codes + (r + u * step) * geo.C + c0));
+#pragma unroll
+        for (int u = 0; u < 4; ++u) one_row(pk[u], r + u * step);
+    }
+    for (; r < r_end; r += step) one_row(__ldcs(reinterpret_cast<const uint2*>(codes + r * geo.C + c0)), r);
+}
+
 static int nh_grid(int64_t items) {
     int sms = qb_sm_count();
     if (sms <= 0) sms = 148;
@@ -349,12 +421,30 @@ static int launch_apply_nhwc(const char* who, const float* x, float* out, int64_
     return QB_OK;
 }
 
-extern "C" int qb_rangebn_apply_nhwc(const float* x, float* out, int64_t B, int64_t C, int64_t HW, const float* mean,
-                                     const float* qscale, const float* qgamma, const float* qbeta, const float* q_range,
-                                     int q_bits, void* stream) {
-    QB_CHECK_ARG(x && out && mean && qscale, "qb_rangebn_apply_nhwc: null pointer");
+extern "C" int qb_rangebn_apply_nhwc(const float* x, const uint8_t* x_codes, float* out, int64_t B, int64_t C, int64_t HW,
+                                     const float* mean, const float* qscale, const float* qgamma, const float* qbeta,
+                                     const float* q_range, int q_bits, void* stream) {
+    QB_CHECK_ARG((x || x_codes) && out && mean && qscale, "qb_rangebn_apply_nhwc: null pointer");
     QB_CHECK_ARG(B > 0 && C > 0 && HW > 0, "qb_rangebn_apply_nhwc: bad shape");
     QB_CHECK_ARG(!q_range || (q_bits >= 1 && q_bits <= 24), "qb_rangebn_apply_nhwc: q_bits=%d", q_bits);
+    if (x_codes) {
+        QB_CHECK_ARG(q_range && q_bits <= 8 && C % 8 == 0 && (reinterpret_cast<uintptr_t>(x_codes) & 7) == 0 &&
+                         (reinterpret_cast<uintptr_t>(out) & 31) == 0,
+                     "qb_rangebn_apply_nhwc: x_codes needs q_range, q_bits <= 8, C %% 8 == 0, aligned tensors");
+        const int64_t R = B * HW;
+        NhwcGeom geo = make_geom<8>(R, C, 1, 1 << 20);
+        const int ctiles = (int)((C + geo.tileC - 1) / geo.tileC);
+        int64_t want = (148 * 8 + ctiles - 1) / ctiles;                      // ~8 CTAs per SM
+        const int64_t max_by_rows = R / ((int64_t)geo.RL * 4) > 0 ? R / ((int64_t)geo.RL * 4) : 1;
+        if (want > max_by_rows) want = max_by_rows;
+        geo.S = (int)want;
+        geo.seg_rows = (R + geo.S - 1) / geo.S;
+        dim3 grid((unsigned)geo.S, (unsigned)ctiles);
+        k_rbn_apply_codes_nhwc<<<grid, NH_THREADS, 0, qb_stream(stream)>>>(x_codes, out, geo,
+                                                                           NhwcVecs{mean, qscale, qgamma, qbeta, q_range, q_bits});
+        QB_LAUNCH_CHECK();
+        return QB_OK;
+    }
     return launch_apply_nhwc<0>("qb_rangebn_apply_nhwc", x, out, B * HW, C,
                                 NhwcVecs{mean, qscale, qgamma, qbeta, q_range, q_bits}, qb_stream(stream));
 }
@@ -374,10 +464,12 @@ struct GradQuantArg {
                           // apply pass (NOISE == -2): the codes to dequantize INSTEAD of reading and re-quantizing g
 };
 
-template <int VEC, bool QUANT, int NOISE>   // NOISE < 0: g already quantized
+// QUANT: 0 = x is x_hat already, 1 = x is the raw input, quantized on the fly with q_range, 2 = x_hat comes as the uint8
+// codes the forward statistics pass wrote (x_codes; VEC == 8 only): 1 B/elem instead of 4 and no re-quantization
+template <int VEC, int QUANT, int NOISE>   // NOISE < 0: g already quantized
 __global__ void __launch_bounds__(NH_THREADS, 3)
-k_rbn_bwd_reduce_nhwc(const float* __restrict__ gq, const float* __restrict__ x, NhwcGeom g, double* part /*[2][S][C]*/,
-                      const float* q_range, int q_bits, GradQuantArg ga) {
+k_rbn_bwd_reduce_nhwc(const float* __restrict__ gq, const float* __restrict__ x, const uint8_t* __restrict__ x_codes, NhwcGeom g,
+                      double* part /*[2][S][C]*/, const float* q_range, int q_bits, GradQuantArg ga) {
     using V = typename VecT<VEC>::T;
     constexpr int UN = VEC == 8 ? 2 : NH_UNROLL;
     extern __shared__ unsigned char smem_raw[];
@@ -400,10 +492,16 @@ k_rbn_bwd_reduce_nhwc(const float* __restrict__ gq, const float* __restrict__ x,
     float fg[VEC], fgx[VEC];
 #pragma unroll
     for (int j = 0; j < VEC; ++j) { fg[j] = 0.f; fgx[j] = 0.f; }
-    auto one_row = [&](const V& av_, const V& bv_, int64_t r) {
+    auto one_row = [&](const V& av_, const V& bv_, const uint2& pk, int64_t r) {
         float av[VEC], bv[VEC];
         unpack(av_, av);
-        unpack(bv_, bv);
+        if (QUANT == 2) {
+#pragma unroll
+            for (int j = 0; j < VEC; ++j)
+                bv[j] = q_affine_deq((float)(((j < 4 ? pk.x : pk.y) >> (8 * (j & 3))) & 0xffu), aq.p);
+        } else {
+            unpack(bv_, bv);
+        }
         if (NOISE >= 0) {
             float u[8];
             const int64_t e = r * g.C + c0;                       // VEC == 8 on this path: e is a multiple of 8
@@ -425,7 +523,7 @@ k_rbn_bwd_reduce_nhwc(const float* __restrict__ gq, const float* __restrict__ x,
                 }
             }
         }
-        if (QUANT) affine_fq_vec<VEC>(bv, aq);
+        if (QUANT == 1) affine_fq_vec<VEC>(bv, aq);
 #pragma unroll
         for (int j = 0; j < VEC; ++j) {
             fg[j] += av[j];
@@ -437,16 +535,23 @@ k_rbn_bwd_reduce_nhwc(const float* __restrict__ gq, const float* __restrict__ x,
         const int64_t step = g.RL;
         for (; r + (UN - 1) * step < r_end; r += UN * step) {
             V a[UN], b[UN];
+            uint2 pk[UN];
 #pragma unroll
             for (int u = 0; u < UN; ++u) {
                 a[u] = ld_vec_stream<V>(gq + (r + u * step) * g.C + c0);
-                b[u] = ld_vec_stream<V>(x + (r + u * step) * g.C + c0);
+                if (QUANT == 2) pk[u] = __ldcs(reinterpret_cast<const uint2*>(x_codes + (r + u * step) * g.C + c0));
+                else b[u] = ld_vec_stream<V>(x + (r + u * step) * g.C + c0);
             }
 #pragma unroll
-            for (int u = 0; u < UN; ++u) one_row(a[u], b[u], r + u * step);
+            for (int u = 0; u < UN; ++u) one_row(a[u], b[u], pk[u], r + u * step);
         }
-        for (; r < r_end; r += step)
-            one_row(ld_vec_stream<V>(gq + r * g.C + c0), ld_vec_stream<V>(x + r * g.C + c0), r);
+        for (; r < r_end; r += step) {
+            V b1;
+            uint2 pk1 = make_uint2(0u, 0u);
+            if (QUANT == 2) pk1 = __ldcs(reinterpret_cast<const uint2*>(x_codes + r * g.C + c0));
+            else b1 = ld_vec_stream<V>(x + r * g.C + c0);
+            one_row(ld_vec_stream<V>(gq + r * g.C + c0), b1, pk1, r);
+        }
     }
     const int W = g.CT * VEC;
     double* s_g = reinterpret_cast<double*>(smem_raw);
@@ -473,6 +578,7 @@ __global__ void k_rbn_bwd_pack_nhwc(const double* part, int64_t C, int S, double
     const int lane = threadIdx.x & 31;
     if (c >= C) return;
     double a = 0.0, b = 0.0;
+#pragma unroll 8                                                          // independent loads in flight; fixed order
     for (int s = lane; s < S; s += 32) { a += part[(int64_t)s * C + c]; b += part[((int64_t)S + s) * C + c]; }
     a = warp_sum(a);
     b = warp_sum(b);
@@ -481,10 +587,10 @@ __global__ void k_rbn_bwd_pack_nhwc(const double* part, int64_t C, int S, double
 
 extern "C" size_t qb_rangebn_bwd_nhwc_ws_bytes(int64_t C) { return C < 0 ? 0 : (size_t)C * NH_MAX_SEG_BWD * 16; }
 
-template <int VEC, bool QUANT, int NOISE>
-static void launch_bwd_reduce(dim3 grid, size_t smem, cudaStream_t st, const float* gq, const float* x, const NhwcGeom& g,
-                              double* part, const float* q_range, int q_bits, const GradQuantArg& ga) {
-    k_rbn_bwd_reduce_nhwc<VEC, QUANT, NOISE><<<grid, NH_THREADS, smem, st>>>(gq, x, g, part, q_range, q_bits, ga);
+template <int VEC, int QUANT, int NOISE>
+static void launch_bwd_reduce(dim3 grid, size_t smem, cudaStream_t st, const float* gq, const float* x, const uint8_t* x_codes,
+                              const NhwcGeom& g, double* part, const float* q_range, int q_bits, const GradQuantArg& ga) {
+    k_rbn_bwd_reduce_nhwc<VEC, QUANT, NOISE><<<grid, NH_THREADS, smem, st>>>(gq, x, x_codes, g, part, q_range, q_bits, ga);
 }
 
 static int grad_noise_mode(const float* g_range, const float* noise, int stochastic) {
@@ -494,12 +600,15 @@ static int grad_noise_mode(const float* g_range, const float* noise, int stochas
 
 /* g_range != NULL: g is the raw gradient, quantized on the fly to g_bits with this device range (needs C % 8 == 0 and
  * 32-byte aligned tensors); noise/stochastic/seed/offset/step_dev as in qb_fakequant_grad. */
-extern "C" int qb_rangebn_bwd_reduce_nhwc(const float* gq, const float* x, int64_t B, int64_t C, int64_t HW, double* sg,
-                                          double* sgx, const float* q_range, int q_bits, const float* g_range, int g_bits,
+extern "C" int qb_rangebn_bwd_reduce_nhwc(const float* gq, const float* x, const uint8_t* x_codes, int64_t B, int64_t C,
+                                          int64_t HW, double* sg, double* sgx, const float* q_range, int q_bits,
+                                          const float* g_range, int g_bits,
                                           const float* noise, int stochastic, uint64_t seed, uint64_t offset,
                                           const uint64_t* step_dev, uint8_t* gq_codes_out, void* ws, size_t ws_bytes,
                                           void* stream) {
-    QB_CHECK_ARG(gq && x && sg && sgx && ws, "qb_rangebn_bwd_reduce_nhwc: null pointer");
+    QB_CHECK_ARG(gq && (x || x_codes) && sg && sgx && ws, "qb_rangebn_bwd_reduce_nhwc: null pointer");
+    QB_CHECK_ARG(!x_codes || (q_range && q_bits <= 8 && C % 8 == 0 && (reinterpret_cast<uintptr_t>(x_codes) & 7) == 0),
+                 "qb_rangebn_bwd_reduce_nhwc: x_codes needs q_range, q_bits <= 8, C %% 8 == 0 and 8-byte alignment");
     QB_CHECK_ARG(!gq_codes_out || (g_range && g_bits <= 8 && (reinterpret_cast<uintptr_t>(gq_codes_out) & 7) == 0),
                  "qb_rangebn_bwd_reduce_nhwc: codes output needs the fused gradient quantizer, bits <= 8, 8-byte alignment");
     QB_CHECK_ARG(B > 0 && C > 0 && HW > 0, "qb_rangebn_bwd_reduce_nhwc: bad shape");
@@ -510,12 +619,13 @@ extern "C" int qb_rangebn_bwd_reduce_nhwc(const float* gq, const float* x, int64
         return QB_ERR_WORKSPACE;
     }
     const int64_t R = B * HW;
-    const uintptr_t al = reinterpret_cast<uintptr_t>(x) | reinterpret_cast<uintptr_t>(gq) | reinterpret_cast<uintptr_t>(noise);
+    const uintptr_t al = (x_codes ? 0 : reinterpret_cast<uintptr_t>(x)) | reinterpret_cast<uintptr_t>(gq) |
+                         reinterpret_cast<uintptr_t>(noise);
     const bool vec8 = (C % 8 == 0) && ((al & 31) == 0) && (offset % 8 == 0);
     const bool vec4 = (C % 4 == 0) && ((al & 15) == 0);
     const int nm = grad_noise_mode(g_range, noise, stochastic);
-    if (nm >= 0 && !vec8) {
-        qb_set_error("qb_rangebn_bwd_reduce_nhwc: on-the-fly gradient quantization needs C %% 8 == 0 and 32-byte alignment");
+    if ((nm >= 0 || x_codes) && !vec8) {
+        qb_set_error("qb_rangebn_bwd_reduce_nhwc: on-the-fly gradient quantization / x_codes need C %% 8 == 0 and 32-byte alignment");
         return QB_ERR_UNSUPPORTED;
     }
     NhwcGeom g = vec8 ? make_geom<8>(R, C, 1, NH_MAX_SEG_BWD) : vec4 ? make_geom<4>(R, C, 1, NH_MAX_SEG_BWD)
@@ -527,19 +637,20 @@ extern "C" int qb_rangebn_bwd_reduce_nhwc(const float* gq, const float* x, int64
     const bool qx = q_range != nullptr;
     if (vec8) {
         const size_t sm = nhwc_smem(g, 8, 16);
-#define QB_RED8(NM) (qx ? launch_bwd_reduce<8, true, NM>(grid, sm, st, gq, x, g, part, q_range, q_bits, ga) \
-                        : launch_bwd_reduce<8, false, NM>(grid, sm, st, gq, x, g, part, q_range, q_bits, ga))
+#define QB_RED8(NM) (x_codes ? launch_bwd_reduce<8, 2, NM>(grid, sm, st, gq, x, x_codes, g, part, q_range, q_bits, ga) \
+                     : qx ? launch_bwd_reduce<8, 1, NM>(grid, sm, st, gq, x, x_codes, g, part, q_range, q_bits, ga)    \
+                          : launch_bwd_reduce<8, 0, NM>(grid, sm, st, gq, x, x_codes, g, part, q_range, q_bits, ga))
         if (nm < 0) QB_RED8(-1);
         else if (nm == NOISE_NONE) QB_RED8(NOISE_NONE);
         else if (nm == NOISE_INJECT) QB_RED8(NOISE_INJECT);
         else QB_RED8(NOISE_PHILOX);
 #undef QB_RED8
     } else if (vec4) {
-        if (qx) launch_bwd_reduce<4, true, -1>(grid, nhwc_smem(g, 4, 16), st, gq, x, g, part, q_range, q_bits, ga);
-        else launch_bwd_reduce<4, false, -1>(grid, nhwc_smem(g, 4, 16), st, gq, x, g, part, q_range, q_bits, ga);
+        if (qx) launch_bwd_reduce<4, 1, -1>(grid, nhwc_smem(g, 4, 16), st, gq, x, nullptr, g, part, q_range, q_bits, ga);
+        else launch_bwd_reduce<4, 0, -1>(grid, nhwc_smem(g, 4, 16), st, gq, x, nullptr, g, part, q_range, q_bits, ga);
     } else {
-        if (qx) launch_bwd_reduce<1, true, -1>(grid, nhwc_smem(g, 1, 16), st, gq, x, g, part, q_range, q_bits, ga);
-        else launch_bwd_reduce<1, false, -1>(grid, nhwc_smem(g, 1, 16), st, gq, x, g, part, q_range, q_bits, ga);
+        if (qx) launch_bwd_reduce<1, 1, -1>(grid, nhwc_smem(g, 1, 16), st, gq, x, nullptr, g, part, q_range, q_bits, ga);
+        else launch_bwd_reduce<1, 0, -1>(grid, nhwc_smem(g, 1, 16), st, gq, x, nullptr, g, part, q_range, q_bits, ga);
     }
     QB_LAUNCH_CHECK();
     k_rbn_bwd_pack_nhwc<<<(unsigned)((C * 32 + 127) / 128), 128, 0, st>>>(part, C, g.S, sg, sgx);

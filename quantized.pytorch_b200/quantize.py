@@ -652,15 +652,20 @@ class _RangeBNFn(Function):
         B, Cn = xq.shape[0], xq.shape[1]
         HW = xq.numel() // (B * Cn)
         count, chunk_len, chunks_global = float(B * HW), 0.0, num_chunks
-        red = amax = amin = None
+        red = amax = amin = xc = None
         ctx.local_chunks = num_chunks
         if training:
             local_chunks = num_chunks
             if _reducer is not None:
                 local_chunks, count = _reducer.rangebn_layout(B, HW, num_chunks)
             want_arg = any(ctx.needs_input_grad[:3])
+            if (nhwc and q_range is not None and q_bits <= 8 and Cn % 8 == 0 and xq.numel() < 2 ** 32
+                    and xq.data_ptr() % 32 == 0):
+                # x_hat leaves the statistics pass as uint8 codes: apply and backward read 1 B/elem, the raw conv output
+                # is not kept for backward
+                xc = torch.empty(xq.numel(), dtype=torch.uint8, device=xq.device)
             red, amax, amin = _abi.rangebn_stats(xq, B, Cn, HW, local_chunks, want_arg=want_arg, nhwc=nhwc,
-                                                 q_range=q_range, q_bits=q_bits)
+                                                 q_range=q_range, q_bits=q_bits, x_codes_out=xc)
             if _reducer is not None:
                 _reducer.rangebn(red)
             chunk_len = count / chunks_global
@@ -668,21 +673,22 @@ class _RangeBNFn(Function):
         vec = _abi.rangebn_finalize(red, Cn, chunks_global, count, chunk_len, eps, momentum, training, bits, gamma, beta,
                                     running_mean, running_var)
         out = _abi.rangebn_apply(xq, B, Cn, HW, vec, gamma is not None, beta is not None, nhwc=nhwc, q_range=q_range,
-                                 q_bits=q_bits)
+                                 q_bits=q_bits, x_codes=xc)
         ctx.dims = (B, Cn, HW, chunks_global, count, chunk_len, training, bits_grad, gamma is not None, beta is not None)
         ctx.nhwc, ctx.q_bits = nhwc, q_bits
-        ctx.save_for_backward(xq, vec, amax, amin, q_range)
+        ctx.save_for_backward(None if xc is not None else xq, vec, amax, amin, q_range, xc)
         return out
 
     @staticmethod
     def backward(ctx, g):
-        xq, vec, amax, amin, q_range = ctx.saved_tensors
+        xq, vec, amax, amin, q_range, xc = ctx.saved_tensors
         B, Cn, HW, K, count, chunk_len, training, bits_grad, has_gamma, has_beta = ctx.dims
         g = g.contiguous(memory_format=torch.channels_last) if ctx.nhwc else g.contiguous()
         hook = _reducer.rangebn_bwd if (_reducer is not None and training) else None
-        common = dict(reduce_hook=hook, chunks_global=K, nhwc=ctx.nhwc, q_range=q_range, q_bits=ctx.q_bits)
+        common = dict(reduce_hook=hook, chunks_global=K, nhwc=ctx.nhwc, q_range=q_range, q_bits=ctx.q_bits, x_codes=xc)
         lc = ctx.local_chunks if training else 0
-        if ctx.nhwc and Cn % 8 == 0 and g.numel() < 2 ** 32 and g.data_ptr() % 32 == 0 and xq.data_ptr() % 32 == 0:
+        if (ctx.nhwc and Cn % 8 == 0 and g.numel() < 2 ** 32 and g.data_ptr() % 32 == 0
+                and (xc is not None or xq.data_ptr() % 32 == 0)):
             gquant = None
             if bits_grad is not None:
                 g = _abi._f32c(g, "grad")

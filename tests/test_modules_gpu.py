@@ -321,3 +321,35 @@ def test_tensorcore_modules_vs_oracle(kind, cfg, shape, relu_input):
     if cfg["bias"]:
         assert rel_l2(mod.bias.grad, ref.bias.grad) < 1e-4
     assert torch.equal(mod.weight_min.cpu().flatten(), ref.weight_min.detach().flatten())
+
+
+@pytest.mark.parametrize("shape", [(16, 64, 8, 8), (32, 16, 7, 7), (8, 128, 12, 12)])
+def test_rangebn_code_handoff_bit_exact(lib, shape):
+    """x_hat handed between the RangeBN passes as uint8 codes (stats writes them, apply / backward reduce read them)
+    is bit-identical to re-quantizing the raw fp32 input in every pass, and the codes equal the stand-alone quantizer's."""
+    B, C, H, W = shape
+    HW, K = H * W, 16
+    gen = torch.Generator().manual_seed(77)
+    x = (torch.randn(shape, generator=gen) * 2 + 0.3).to(DEV).contiguous(memory_format=torch.channels_last)
+    g = (torch.randn(shape, generator=gen) * 1e-3).to(DEV).contiguous(memory_format=torch.channels_last)
+    noise = (torch.rand(shape, generator=gen) - 0.5).to(DEV).contiguous(memory_format=torch.channels_last)
+    gamma, beta = (torch.rand(C, generator=gen) + 0.5).to(DEV), torch.randn(C, generator=gen).to(DEV)
+    qr = torch.tensor([float(x.min()) * 0.9, float(x.max()) * 0.8], device=DEV)       # clamps on both sides
+    res = []
+    for use_codes in (False, True):
+        xc = torch.empty(x.numel(), dtype=torch.uint8, device=DEV) if use_codes else None
+        rm, rv = torch.zeros(C, device=DEV), torch.zeros(C, device=DEV)
+        red, amax, amin = lib.rangebn_stats(x, B, C, HW, K, nhwc=True, q_range=qr, q_bits=8, x_codes_out=xc)
+        vec = lib.rangebn_finalize(red, C, K, B * HW, B * HW / K, 1e-5, 0.1, True, 8, gamma, beta, rm, rv)
+        out = lib.rangebn_apply(x, B, C, HW, vec, True, True, nhwc=True, q_range=qr, q_bits=8, x_codes=xc)
+        gq = dict(range=lib.minmax(g), bits=8, noise=noise, stochastic=True, seed=0, step_dev=None)
+        dx, dgamma, dbeta, dxr = lib.rangebn_backward(g, None if use_codes else x, B, C, HW, K, B * HW, B * HW / K, True, vec,
+                                                      True, amax, amin, nhwc=True, q_range=qr, q_bits=8, grad_quant=gq,
+                                                      want_dx_range=True, x_codes=xc)
+        res.append((red, amax, amin, out, dx, dgamma, dbeta, dxr, xc))
+    a, b = res
+    for i, name in enumerate(["red", "amax", "amin", "out", "dx", "dgamma", "dbeta", "dx_range"]):
+        assert torch.equal(a[i], b[i]), name
+    want = torch.empty(x.numel(), dtype=torch.uint8, device=DEV)
+    lib.fakequant_affine(x, 8, range_dev=qr, codes=want, want_y=False)
+    assert torch.equal(b[8], want)

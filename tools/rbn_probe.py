@@ -6,6 +6,7 @@ import qtorch_b200  # noqa
 from qtorch_b200 import _abi
 
 B, C, H = [int(a) for a in (sys.argv[1:4] if len(sys.argv) > 3 else (256, 64, 56))]
+CODES = os.environ.get("RBN_CODES", "1") != "0"      # x_hat handed between the passes as uint8 codes
 dev = torch.device("cuda")
 HW = H * H
 x = (torch.randn(B, C, H, H, device=dev) * 2).contiguous(memory_format=torch.channels_last)
@@ -14,12 +15,13 @@ g = g * (torch.rand_like(g) > 0.5)
 gamma, beta = torch.rand(C, device=dev) + 0.5, torch.randn(C, device=dev)
 rm, rv = torch.zeros(C, device=dev), torch.zeros(C, device=dev)
 qr = _abi.minmax(x)
+xc = torch.empty(x.numel(), dtype=torch.uint8, device=dev) if CODES else None
 
 
 def fwd():
-    red, amax, amin = _abi.rangebn_stats(x, B, C, HW, 16, nhwc=True, q_range=qr, q_bits=8)
+    red, amax, amin = _abi.rangebn_stats(x, B, C, HW, 16, nhwc=True, q_range=qr, q_bits=8, x_codes_out=xc)
     vec = _abi.rangebn_finalize(red, C, 16, B * HW, B * HW / 16, 1e-5, 0.1, True, 8, gamma, beta, rm, rv)
-    out = _abi.rangebn_apply(x, B, C, HW, vec, True, True, nhwc=True, q_range=qr, q_bits=8)
+    out = _abi.rangebn_apply(x, B, C, HW, vec, True, True, nhwc=True, q_range=qr, q_bits=8, x_codes=xc)
     return vec, amax, amin, out
 
 
@@ -27,7 +29,7 @@ def bwd(vec, amax, amin):
     r = _abi.minmax(g)
     gq = dict(range=r, bits=8, noise=None, stochastic=True, seed=7, step_dev=None)
     return _abi.rangebn_backward(g, x, B, C, HW, 16, B * HW, B * HW / 16, True, vec, True, amax, amin, nhwc=True, q_range=qr,
-                                 q_bits=8, grad_quant=gq, want_dx_range=True)
+                                 q_bits=8, grad_quant=gq, want_dx_range=True, x_codes=xc)
 
 
 vec, amax, amin, out = fwd()
