@@ -29,7 +29,20 @@ struct ConvGeom {
     int BK;                     // bytes (= channels) of K per pipeline stage: 32, 64 or 128
     int stages;
     int halo;                   // 1: 3x3 / stride 1 / Cin == BK, Cout == BN: column-shifted halo boxes + resident weights
+    FastDiv d_tiles_m, d_tiles_w, d_tiles_h;   // tile-index decoding without integer division
 };
+
+// tile t -> (channel tile tn, first image b0, first output row ho0, first output column wo0)
+__device__ __forceinline__ void conv_decode_tile(int t, const ConvGeom& g, int tiles_m, int& tn, int& b0, int& ho0, int& wo0) {
+    tn = (int)fdiv((uint32_t)t, g.d_tiles_m);
+    uint32_t tm = (uint32_t)(t - tn * tiles_m);
+    uint32_t q = fdiv(tm, g.d_tiles_w);
+    wo0 = (int)(tm - q * (uint32_t)g.tiles_w) * g.TW;
+    tm = q;
+    q = fdiv(tm, g.d_tiles_h);
+    ho0 = (int)(tm - q * (uint32_t)g.tiles_h) * g.TH;
+    b0 = (int)q * g.TN;
+}
 
 struct ConvEpilogue {
     const float* a_range;       // device {min,max} of the input quantizer (QB_SCALE_DOUBLE)
@@ -73,6 +86,42 @@ __device__ __forceinline__ float4 lds128(uint32_t addr) {
     return v;
 }
 
+// packed fp32x2 arithmetic (FFMA2 / FADD2: two independent IEEE operations per instruction) and 3-input min / max
+__device__ __forceinline__ uint64_t pack2(float lo, float hi) {
+    uint64_t r;
+    asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(lo), "f"(hi));
+    return r;
+}
+__device__ __forceinline__ void unpack2(uint64_t v, float& lo, float& hi) { asm("mov.b64 {%0, %1}, %2;" : "=f"(lo), "=f"(hi) : "l"(v)); }
+__device__ __forceinline__ uint64_t fma2(uint64_t a, uint64_t b, uint64_t c) {
+    uint64_t d;
+    asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(d) : "l"(a), "l"(b), "l"(c));
+    return d;
+}
+__device__ __forceinline__ uint64_t add2(uint64_t a, uint64_t b) {
+    uint64_t d;
+    asm("add.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b));
+    return d;
+}
+__device__ __forceinline__ float min3(float a, float b, float c) {
+    float d;
+    asm("min.f32 %0, %1, %2, %3;" : "=f"(d) : "f"(a), "f"(b), "f"(c));
+    return d;
+}
+__device__ __forceinline__ float max3(float a, float b, float c) {
+    float d;
+    asm("max.f32 %0, %1, %2, %3;" : "=f"(d) : "f"(a), "f"(b), "f"(c));
+    return d;
+}
+__device__ __forceinline__ void lds_2x64(uint32_t addr, uint64_t& a, uint64_t& b) {
+    asm volatile("ld.shared.v2.b64 {%0, %1}, [%2];" : "=l"(a), "=l"(b) : "r"(addr));
+}
+__device__ __forceinline__ uint64_t lds_64(uint32_t addr) {
+    uint64_t a;
+    asm volatile("ld.shared.b64 %0, [%1];" : "=l"(a) : "r"(addr));
+    return a;
+}
+
 // Persistent kernel: gridDim.x CTAs (one per SM) walk the tile list t = blockIdx.x, += gridDim.x; tiles are ordered with
 // the output-channel tile slowest so a CTA's per-channel coefficients rarely change.  Three asynchronous roles:
 //   warp 0   TMA producer: keeps the shared-memory ring full ACROSS tile boundaries
@@ -102,8 +151,12 @@ k_conv_i8(const __grid_constant__ CUtensorMap tmap_x, const __grid_constant__ CU
     uint64_t* tempty_bar = tfull_bar + 2;                      // [2] accumulator buffer drained
     uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty_bar + 2);
     uint64_t* wfull_bar = reinterpret_cast<uint64_t*>(tail + 296);   // halo mode: resident weights have landed
-    float4* s_coef = reinterpret_cast<float4*>(tail + 320);   // {sa*sw[n], sa*lw'[n], bias[n], la*(sw*Tall + lw'*K)}
-    float* s_c3 = reinterpret_cast<float*>(s_coef + BN);      // la*sw[n]      (border pixels of inputs with min != 0)
+    // per output channel n: c0 = sa*sw[n], c1 = sa*lw'[n], c2 = bias[n], w = la*(sw*Tall + lw'*K).  c0 / c1 are stored per
+    // channel PAIR {c0[2p], c0[2p+1], c1[2p], c1[2p+1]} so that one 128-bit load feeds two packed FMAs
+    float* s_pair = reinterpret_cast<float*>(tail + 320);     // [BN/2][4]
+    float* s_c2 = s_pair + 2 * BN;                             // [BN]
+    float* s_w = s_c2 + BN;                                    // [BN]
+    float* s_c3 = s_w + BN;                                    // la*sw[n]      (border pixels of inputs with min != 0)
     float* s_c4 = s_c3 + BN;                                   // la*lw'[n]
     int32_t* s_tap = reinterpret_cast<int32_t*>(s_c4 + BN);   // [BN][taps]
 
@@ -145,10 +198,8 @@ k_conv_i8(const __grid_constant__ CUtensorMap tmap_x, const __grid_constant__ CU
             for (int tap = 0; tap < taps; ++tap) tma_load_2d(wres + (size_t)tap * b_bytes, &tmap_w, wfull_bar, tap * g.Cin, 0);
             uint32_t it = 0;
             for (int t = blockIdx.x; t < total_tiles; t += gridDim.x, ++it) {
-                int tm = t;                                     // tiles_n == 1 in halo mode
-                const int tw_i = tm % g.tiles_w; tm /= g.tiles_w;
-                const int th_i = tm % g.tiles_h; tm /= g.tiles_h;
-                const int b0 = tm * g.TN, ho0 = th_i * g.TH, wo0 = tw_i * g.TW;
+                int tn, b0, ho0, wo0;                           // tiles_n == 1 in halo mode: tn == 0
+                conv_decode_tile(t, g, tiles_m, tn, b0, ho0, wo0);
                 const int s = it % g.stages;
                 const uint32_t ph = (it / g.stages) & 1;
                 mbar_wait(&empty_bar[s], ph ^ 1);
@@ -160,11 +211,9 @@ k_conv_i8(const __grid_constant__ CUtensorMap tmap_x, const __grid_constant__ CU
         } else if (lead) {
             uint32_t it = 0;
             for (int t = blockIdx.x; t < total_tiles; t += gridDim.x) {
-                const int tn = t / tiles_m;
-                int tm = t - tn * tiles_m;
-                const int tw_i = tm % g.tiles_w; tm /= g.tiles_w;
-                const int th_i = tm % g.tiles_h; tm /= g.tiles_h;
-                const int b0 = tm * g.TN, ho0 = th_i * g.TH, wo0 = tw_i * g.TW, n0 = tn * BN;
+                int tn, b0, ho0, wo0;
+                conv_decode_tile(t, g, tiles_m, tn, b0, ho0, wo0);
+                const int n0 = tn * BN;
                 for (int r = 0; r < g.kh; ++r) {
                     for (int s_ = 0; s_ < g.kw; ++s_) {
                         const int tap = r * g.kw + s_;
@@ -248,7 +297,7 @@ k_conv_i8(const __grid_constant__ CUtensorMap tmap_x, const __grid_constant__ CU
         const bool in_box = nl < g.TN;
         uint8_t* my_staging = reinterpret_cast<uint8_t*>(staging) + grp * 2 * CV_SLAB_BYTES;
         const uint32_t stage_u32 = smem_u32(my_staging);
-        const uint32_t coef_u32 = smem_u32(s_coef);
+        const uint32_t pair_u32 = smem_u32(s_pair), c2_u32 = smem_u32(s_c2);
         const uint32_t row_off = (uint32_t)i * 128u, sw = (uint32_t)(i & 7);
         const float kfull = (float)(taps * g.Cin);
         const int bar_id = 1 + grp;
@@ -257,11 +306,9 @@ k_conv_i8(const __grid_constant__ CUtensorMap tmap_x, const __grid_constant__ CU
         // boxsum of this thread's pixel, fetched one tile ahead so its latency hides behind the current tile
         auto fetch_box = [&](int t, bool& valid_out) -> int {
             if (t >= total_tiles) { valid_out = false; return 0; }
-            const int tn = t / tiles_m;
-            int tm = t - tn * tiles_m;
-            const int tw_i = tm % g.tiles_w; tm /= g.tiles_w;
-            const int th_i = tm % g.tiles_h; tm /= g.tiles_h;
-            const int b = tm * g.TN + nl, ho = th_i * g.TH + th, wo = tw_i * g.TW + tw;
+            int tn, b0, ho0, wo0;
+            conv_decode_tile(t, g, tiles_m, tn, b0, ho0, wo0);
+            const int b = b0 + nl, ho = ho0 + th, wo = wo0 + tw;
             valid_out = in_box && (b < g.B) && (ho < g.Ho) && (wo < g.Wo);
             return valid_out ? __ldg(ep.boxsum + ((int64_t)b * g.Ho + ho) * g.Wo + wo) : 0;
         };
@@ -270,11 +317,9 @@ k_conv_i8(const __grid_constant__ CUtensorMap tmap_x, const __grid_constant__ CU
         bool valid_next;
         int box_next = fetch_box(blockIdx.x, valid_next);
         for (int t = blockIdx.x; t < total_tiles; t += gridDim.x, ++j) {
-            const int tn = t / tiles_m;
-            int tm = t - tn * tiles_m;
-            const int tw_i = tm % g.tiles_w; tm /= g.tiles_w;
-            const int th_i = tm % g.tiles_h; tm /= g.tiles_h;
-            const int b0 = tm * g.TN, ho0 = th_i * g.TH, wo0 = tw_i * g.TW, n0 = tn * BN;
+            int tn, b0, ho0, wo0;
+            conv_decode_tile(t, g, tiles_m, tn, b0, ho0, wo0);
+            const int n0 = tn * BN;
             if (tn != cur_tn) {                                      // per-channel coefficients of this channel tile
                 epi_bar_all();                                       // everyone is done with the previous ones
                 for (int jn = e_all; jn < BN; jn += 256) {
@@ -298,7 +343,9 @@ k_conv_i8(const __grid_constant__ CUtensorMap tmap_x, const __grid_constant__ CU
                         c4 = (float)(la * lw);
                         cf.w = fmaf(c3, (float)tall, c4 * kfull);
                     }
-                    s_coef[jn] = cf; s_c3[jn] = c3; s_c4[jn] = c4;
+                    s_pair[(jn >> 1) * 4 + (jn & 1)] = cf.x;
+                    s_pair[(jn >> 1) * 4 + 2 + (jn & 1)] = cf.y;
+                    s_c2[jn] = cf.z; s_w[jn] = cf.w; s_c3[jn] = c3; s_c4[jn] = c4;
                 }
                 epi_bar_all();
                 cur_tn = tn;
@@ -346,15 +393,36 @@ k_conv_i8(const __grid_constant__ CUtensorMap tmap_x, const __grid_constant__ CU
                 }
                 const uint32_t dst = stage_u32 + (slab & 1u) * (uint32_t)CV_SLAB_BYTES + row_off;
                 if (valid) {
-                    const uint32_t cf_addr = coef_u32 + (uint32_t)c * 16u;
+                    const uint32_t pa = pair_u32 + (uint32_t)c * 8u, ca = c2_u32 + (uint32_t)c * 4u;
+                    const uint64_t rs2 = pack2(rs_a, rs_a);
+                    const bool st_fast = want_stats && !need_la && c + 32 <= ncols;
+                    uint64_t sum2 = 0ull, sq2 = 0ull;                    // (0.f, 0.f)
 #pragma unroll
-                    for (int q = 0; q < 32; ++q) {
-                        const float4 cf = lds128(cf_addr + q * 16);
-                        const float v = fmaf(cf.x, (float)(int32_t)r[q], fmaf(cf.y, rs_a, cf.z));
-                        r[q] = __float_as_uint(v);
-                        if (want_stats && !need_la && c + q < ncols) {
-                            t_mn = fminf(t_mn, v); t_mx = fmaxf(t_mx, v); t_sum += v; t_sq = fmaf(v, v, t_sq);
+                    for (int q = 0; q < 32; q += 2) {
+                        uint64_t c0p, c1p;
+                        lds_2x64(pa + q * 8, c0p, c1p);
+                        const uint64_t c2p = lds_64(ca + q * 4);
+                        const uint64_t v2 = fma2(c0p, pack2((float)(int32_t)r[q], (float)(int32_t)r[q + 1]), fma2(c1p, rs2, c2p));
+                        float va, vb;
+                        unpack2(v2, va, vb);
+                        r[q] = __float_as_uint(va);
+                        r[q + 1] = __float_as_uint(vb);
+                        if (st_fast) {
+                            sum2 = add2(sum2, v2);
+                            sq2 = fma2(v2, v2, sq2);
+                            t_mn = min3(t_mn, va, vb);
+                            t_mx = max3(t_mx, va, vb);
+                        } else if (want_stats && !need_la) {
+                            if (c + q < ncols) { t_mn = fminf(t_mn, va); t_mx = fmaxf(t_mx, va); t_sum += va; t_sq = fmaf(va, va, t_sq); }
+                            if (c + q + 1 < ncols) { t_mn = fminf(t_mn, vb); t_mx = fmaxf(t_mx, vb); t_sum += vb; t_sq = fmaf(vb, vb, t_sq); }
                         }
+                    }
+                    if (st_fast) {
+                        float a0, a1, b0_, b1_;
+                        unpack2(sum2, a0, a1);
+                        unpack2(sq2, b0_, b1_);
+                        t_sum += a0 + a1;
+                        t_sq += b0_ + b1_;
                     }
 #pragma unroll
                     for (int q = 0; q < 8; ++q)
@@ -363,7 +431,7 @@ k_conv_i8(const __grid_constant__ CUtensorMap tmap_x, const __grid_constant__ CU
                     if (need_la) {                                   // inputs whose range does not start at 0 (rare): fix up
 #pragma unroll 1                                                     // this thread's own row in place, column by column
                         for (int q = 0; q < 32; ++q) {
-                            float add = s_coef[c + q].w;
+                            float add = s_w[c + q];
                             if (!interior) {
                                 int tsum = 0;
                                 for (int tp = 0; tp < taps; ++tp)
@@ -622,6 +690,9 @@ extern "C" int qb_conv_i8_fwd(const uint8_t* x_codes, const uint8_t* w_codes_khw
         g.tiles_h = (int)((Ho + g.TH - 1) / g.TH);
         g.tiles_b = (int)B;
     }
+    g.d_tiles_m = make_fastdiv((uint32_t)(g.tiles_w * g.tiles_h * g.tiles_b));
+    g.d_tiles_w = make_fastdiv((uint32_t)g.tiles_w);
+    g.d_tiles_h = make_fastdiv((uint32_t)g.tiles_h);
     {
         const size_t stage = g.halo ? (size_t)kw * g.BK * g.TW * (g.TH + kh - 1) : (size_t)(128 + BN) * g.BK;
         const size_t fixed = CV_STAGING_BYTES + 1024 + conv_tail_bytes(BN, kh * kw) + (g.halo ? (size_t)kh * kw * BN * g.BK : 0);
