@@ -204,6 +204,167 @@ __global__ void k_rbn_stats_nhwc_merge(const float* pmax, const float* pmin, con
     if (amin_kc) amin_kc[t] = mn.i;
 }
 
+// ---------------------------------------------------------------------------------------------------
+// forward statistics in CODE SPACE (input quantizer fused, q_bits <= 8, C % 8 == 0, rows per chunk <= 2^24).
+// x_hat = deq(code) is a monotone function of the integer code, so max / min / first-arg of x_hat over a chunk are
+// max / min / first-arg of the code, and sum(x_hat) follows from the integer sum of the codes.  Per element the kernel
+// only divides, clamps and adds the rounding constant (packed fp32x2); the trackers are integer keys
+//     key_max = code << 24 | (2^24 - 1 - row_in_chunk)      largest code, smallest row on ties
+//     key_min = code << 24 | row_in_chunk                   smallest code, smallest row on ties
+// built with one PRMT from the raw bits of (t + 1.5*2^23), reduced with VIMNMX (two rows per instruction), and the
+// sums are plain integer adds of those bits - exact and order independent, so no fp64 and no index bookkeeping.
+// Optionally writes the codes (uint8) for the later passes.
+// ---------------------------------------------------------------------------------------------------
+constexpr uint32_t QB_MAGIC_BITS = 0x4B400000u;      // bit pattern of QB_MAGIC = 1.5 * 2^23
+
+struct Q8Row {
+    uint32_t bits[8];
+};
+
+__device__ __forceinline__ Q8Row q8_row(const F8& v, const AffineQ& aq, uint64_t nlo2, uint64_t r2, uint64_t nb2, uint64_t magic2) {
+    Q8Row o;
+    float q[8];
+    bool ok = aq.d.fast;
+    uint64_t t2[4];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+        t2[j] = add2(pack2(v.v[2 * j], v.v[2 * j + 1]), nlo2);           // x - lo
+        float a, b;
+        unpack2(t2[j], a, b);
+        ok = ok && qb_div_ok(a) && qb_div_ok(b);
+    }
+    if (ok) {
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            const uint64_t qq = mul2(t2[j], r2);                         // qb_div_fast, two lanes at a time
+            const uint64_t e = fma2(qq, nb2, t2[j]);
+            unpack2(fma2(r2, e, qq), q[2 * j], q[2 * j + 1]);
+        }
+    } else {
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            float a, b;
+            unpack2(t2[j], a, b);
+            q[2 * j] = __fdiv_rn(a, aq.d.b);
+            q[2 * j + 1] = __fdiv_rn(b, aq.d.b);
+        }
+    }
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+        const float a = fminf(fmaxf(q[2 * j], 0.0f), aq.p.qmax), b = fminf(fmaxf(q[2 * j + 1], 0.0f), aq.p.qmax);
+        float ma, mb;
+        unpack2(add2(pack2(a, b), magic2), ma, mb);                      // RNE to the integer code, in the low mantissa bits
+        o.bits[2 * j] = __float_as_uint(ma);
+        o.bits[2 * j + 1] = __float_as_uint(mb);
+    }
+    return o;
+}
+
+__global__ void __launch_bounds__(NH_THREADS, 3)
+k_rbn_stats_q8_nhwc(const float* __restrict__ x, NhwcGeom g, uint32_t* __restrict__ pkmax, uint32_t* __restrict__ pkmin,
+                    uint32_t* __restrict__ pksum, const float* q_range, int q_bits, uint8_t* __restrict__ codes_out) {
+    extern __shared__ unsigned char smem_raw[];
+    const AffineQ aq = load_affineq(q_range, q_bits);
+    const uint64_t nlo2 = pack2(-aq.p.lo, -aq.p.lo), r2 = pack2(aq.d.r, aq.d.r), nb2 = pack2(aq.d.nb, aq.d.nb),
+                   magic2 = pack2(QB_MAGIC, QB_MAGIC);
+    const int ct = threadIdx.x % g.CT, rl = threadIdx.x / g.CT;
+    const int64_t c0 = (int64_t)blockIdx.y * g.tileC + (int64_t)ct * 8;
+    const int k = blockIdx.x / g.S, sgm = blockIdx.x % g.S;
+    const int64_t chunk0 = (int64_t)k * g.L;
+    const int64_t r_begin = chunk0 + (int64_t)sgm * g.seg_rows;
+    int64_t r_end = r_begin + g.seg_rows;
+    if (r_end > chunk0 + g.L) r_end = chunk0 + g.L;
+    uint32_t kmx[8], kmn[8], acc[8], nrows = 0;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) { kmx[j] = 0u; kmn[j] = 0xffffffffu; acc[j] = 0u; }
+    if (rl < g.RL && c0 < g.C) {
+        auto store = [&](const Q8Row& q, int64_t r) {
+            uint2 pk;
+            pk.x = __byte_perm(__byte_perm(q.bits[0], q.bits[1], 0x0040), __byte_perm(q.bits[2], q.bits[3], 0x0040), 0x5410);
+            pk.y = __byte_perm(__byte_perm(q.bits[4], q.bits[5], 0x0040), __byte_perm(q.bits[6], q.bits[7], 0x0040), 0x5410);
+            *reinterpret_cast<uint2*>(codes_out + r * g.C + c0) = pk;
+        };
+        const int64_t step = g.RL;
+        int64_t r = r_begin + rl;
+        for (; r + step < r_end; r += 2 * step) {                           // two rows per iteration: 3-input min / max
+            const F8 v0 = ld256_stream(x + r * g.C + c0), v1 = ld256_stream(x + (r + step) * g.C + c0);
+            const Q8Row q0 = q8_row(v0, aq, nlo2, r2, nb2, magic2), q1 = q8_row(v1, aq, nlo2, r2, nb2, magic2);
+            const uint32_t lo0 = (uint32_t)(r - chunk0), lo1 = lo0 + (uint32_t)step;
+            const uint32_t hi0 = 0xffffffu - lo0, hi1 = 0xffffffu - lo1;
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+                kmx[j] = max(max(kmx[j], __byte_perm(hi0, q0.bits[j], 0x4210)), __byte_perm(hi1, q1.bits[j], 0x4210));
+                kmn[j] = min(min(kmn[j], __byte_perm(lo0, q0.bits[j], 0x4210)), __byte_perm(lo1, q1.bits[j], 0x4210));
+                acc[j] += q0.bits[j] + q1.bits[j];
+            }
+            nrows += 2;
+            if (codes_out) { store(q0, r); store(q1, r + step); }
+        }
+        for (; r < r_end; r += step) {
+            const Q8Row q0 = q8_row(ld256_stream(x + r * g.C + c0), aq, nlo2, r2, nb2, magic2);
+            const uint32_t lo0 = (uint32_t)(r - chunk0), hi0 = 0xffffffu - lo0;
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+                kmx[j] = max(kmx[j], __byte_perm(hi0, q0.bits[j], 0x4210));
+                kmn[j] = min(kmn[j], __byte_perm(lo0, q0.bits[j], 0x4210));
+                acc[j] += q0.bits[j];
+            }
+            nrows += 1;
+            if (codes_out) store(q0, r);
+        }
+    }
+    // combine the row lanes: [RL][CT*8] of (key_max, key_min, code sum); column `col` is finished by thread `col`
+    const int W = g.CT * 8;
+    uint32_t* s_mx = reinterpret_cast<uint32_t*>(smem_raw);
+    uint32_t* s_mn = s_mx + (size_t)g.RL * W;
+    uint32_t* s_sm = s_mn + (size_t)g.RL * W;
+    if (rl < g.RL) {
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+            const int o = rl * W + ct * 8 + j;
+            s_mx[o] = kmx[j]; s_mn[o] = kmn[j];
+            s_sm[o] = acc[j] - nrows * QB_MAGIC_BITS;               // = sum of the codes (mod 2^32; < 2^32 by the row bound)
+        }
+    }
+    __syncthreads();
+    for (int col = threadIdx.x; col < W; col += NH_THREADS) {
+        const int64_t c = (int64_t)blockIdx.y * g.tileC + col;
+        if (c >= g.C) break;
+        uint32_t a = 0u, b = 0xffffffffu, sm = 0u;
+        for (int q = 0; q < g.RL; ++q) { a = max(a, s_mx[q * W + col]); b = min(b, s_mn[q * W + col]); sm += s_sm[q * W + col]; }
+        const int64_t o = (int64_t)blockIdx.x * g.C + c;            // [(k*S+s)][c]
+        pkmax[o] = a; pkmin[o] = b; pksum[o] = sm;
+    }
+}
+
+// merge the S segment partials of every (chunk k, channel c) and leave them in the generic kernel's output format
+__global__ void k_rbn_stats_q8_merge(const uint32_t* pkmax, const uint32_t* pkmin, const uint32_t* pksum, int64_t C, int K, int S,
+                                     int64_t L, const float* q_range, int q_bits, int32_t* amax, int32_t* amin, int32_t* amax_kc,
+                                     int32_t* amin_kc, float* cmax, float* cmin, double* csum) {
+    const int64_t t = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (t >= C * K) return;
+    const QParams p = make_qparams_d((double)__ldg(q_range), (double)__ldg(q_range + 1), q_bits);
+    const int64_t k = t / C, c = t - k * C;
+    uint32_t a = 0u, b = 0xffffffffu;
+    uint64_t sm = 0;
+#pragma unroll 8
+    for (int s = 0; s < S; ++s) {
+        const int64_t o = (k * S + s) * C + c;
+        a = max(a, pkmax[o]); b = min(b, pkmin[o]); sm += pksum[o];
+    }
+    const int32_t imx = (int32_t)(k * L + (int64_t)(0xffffffu - (a & 0xffffffu))), imn = (int32_t)(k * L + (int64_t)(b & 0xffffffu));
+    cmax[t] = q_affine_deq((float)(a >> 24), p);
+    cmin[t] = q_affine_deq((float)(b >> 24), p);
+    // sum over the chunk of x_hat = code*scale + lo, from the exact integer code sum (each x_hat carries an fp32 rounding
+    // of at most half an ulp that averages out over the L rows; the chunk mean stays within an ulp of the fp64 sum of
+    // the rounded values, the same agreement the generic kernel has with ATen's fp32 sums)
+    csum[t] = (double)L * (double)p.lo + (double)p.scale * (double)sm;
+    if (amax) amax[c * K + k] = imx;
+    if (amin) amin[c * K + k] = imn;
+    if (amax_kc) amax_kc[t] = imx;
+    if (amin_kc) amin_kc[t] = imn;
+}
+
 // red[3][C]: sum over the K chunks in a fixed order
 __global__ void k_rbn_stats_nhwc_pack(const float* cmax, const float* cmin, const double* csum, int64_t C, int K,
                                       double* red) {
@@ -255,8 +416,29 @@ extern "C" int qb_rangebn_stats_nhwc(const float* x, int64_t B, int64_t C, int64
     double* csum = reinterpret_cast<double*>(static_cast<char*>(ws) + (size_t)C * num_chunks * NH_MAX_SEG * 24);
     float* cmax = reinterpret_cast<float*>(csum + nk);
     float* cmin = cmax + nk;
-    dim3 grid((unsigned)(num_chunks * g.S), (unsigned)((C + g.tileC - 1) / g.tileC));
     cudaStream_t st = qb_stream(stream);
+    const bool q8 = q_range && q_bits <= 8 && C % 8 == 0 && (reinterpret_cast<uintptr_t>(x) & 31) == 0 && R / num_chunks <= (1 << 24) &&
+                    (!x_codes_out || (reinterpret_cast<uintptr_t>(x_codes_out) & 7) == 0);
+    if (q8) {
+        NhwcGeom g8 = make_geom<8>(R, C, num_chunks);
+        if ((size_t)num_chunks * g8.S * C * 12 <= (size_t)C * num_chunks * NH_MAX_SEG * 24) {
+            uint32_t* pkmax = static_cast<uint32_t*>(ws);
+            uint32_t* pkmin = pkmax + (size_t)num_chunks * g8.S * C;
+            uint32_t* pksum = pkmin + (size_t)num_chunks * g8.S * C;
+            dim3 grid8((unsigned)(num_chunks * g8.S), (unsigned)((C + g8.tileC - 1) / g8.tileC));
+            k_rbn_stats_q8_nhwc<<<grid8, NH_THREADS, (size_t)g8.RL * g8.CT * 8 * 12, st>>>(x, g8, pkmax, pkmin, pksum, q_range, q_bits,
+                                                                                      x_codes_out);
+            QB_LAUNCH_CHECK();
+            k_rbn_stats_q8_merge<<<(unsigned)((nk + 127) / 128), 128, 0, st>>>(pkmax, pkmin, pksum, C, num_chunks, g8.S, R / num_chunks,
+                                                                              q_range, q_bits, amax, amin, amax_kc, amin_kc, cmax,
+                                                                              cmin, csum);
+            QB_LAUNCH_CHECK();
+            k_rbn_stats_nhwc_pack<<<(unsigned)((C + 127) / 128), 128, 0, st>>>(cmax, cmin, csum, C, num_chunks, red);
+            QB_LAUNCH_CHECK();
+            return QB_OK;
+        }
+    }
+    dim3 grid((unsigned)(num_chunks * g.S), (unsigned)((C + g.tileC - 1) / g.tileC));
     if (vec4 && q_range)
         k_rbn_stats_nhwc<4, true><<<grid, NH_THREADS, nhwc_smem(g, 4, 24), st>>>(x, g, pmax, pmin, imax, imin, psum, q_range, q_bits, x_codes_out);
     else if (vec4)
