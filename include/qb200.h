@@ -268,6 +268,16 @@ int qb_rangebn2_finalize(const double* red, int64_t C, int num_chunks, double co
 int qb_rangebn2_apply(const float* x, float* out, int64_t B, int64_t C, int64_t HW, int nhwc, const float* mean,
                       const float* den, const float* gamma, const float* beta, void* stream);
 
+/* ---------------------------------------------------------------------------------------------------
+ * Glue between the quantized modules: nn.MaxPool2d over channels-last fp32
+ * (models/resnet_quantized.py:150).  Same values, tie-breaking (first maximal element of the window, rows first) and
+ * backward accumulation order as ATen's max_pool2d; idx holds the window-relative position kh*k + kw of the maximum as
+ * one byte per output element.  Needs C % 8 == 0, k <= 15, 2*pad <= k, 32-byte aligned x/out/grad/dx, 8-byte aligned idx. */
+int qb_maxpool2d_nhwc_fwd(const float* x, float* out, uint8_t* idx, int64_t B, int64_t H, int64_t W, int64_t C, int k,
+                          int stride, int pad, void* stream);
+int qb_maxpool2d_nhwc_bwd(const float* grad_out, const uint8_t* idx, float* dx, int64_t B, int64_t H, int64_t W, int64_t C,
+                          int k, int stride, int pad, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -58,6 +58,8 @@ PROTOTYPES = {
     "qb_rangebn2_apply": (_i32, [_p, _p, _i64, _i64, _i64, _i32, _p, _p, _p, _p, _p]),
     "qb_gemm_i8": (_i32, [_p, _p, _p, _i64, _i64, _i64, _i64, _p, _i32, _p, _p, _i32, _p, _p, _p, _i32, _p]),
     "qb_fakequant_rows_conv": (_i32, [_p, _p, _p, _p, _i64, _i64, _i32, _i32, _p, _p, _i32, _p]),
+    "qb_maxpool2d_nhwc_fwd": (_i32, [_p, _p, _p, _i64, _i64, _i64, _i64, _i32, _i32, _i32, _p]),
+    "qb_maxpool2d_nhwc_bwd": (_i32, [_p, _p, _p, _i64, _i64, _i64, _i64, _i32, _i32, _i32, _p]),
     "qb_conv_i8_fwd": (_i32, [_p, _p, _p, _i64, _i64, _i64, _i64, _i64, _i32, _i32, _i32, _i32, _p, _i32, _p, _p, _i32,
                               _p, _p, _p, _p, _p, _p, _sz, _p]),
 }
@@ -467,6 +469,28 @@ def conv_i8_fwd(x_codes, w_codes, B, H, W, Cin, Cout, kh, kw, stride, pad, a_ran
          int(w_bits), _ptr(pixsum), _ptr(boxsum), _ptr(tapsum), _ptr(bias), _ptr(out_stats), _ptr(ws),
          ws.numel() if ws is not None else 0, _stream())
     return out
+
+
+# ----------------------------------------------------------------------------------------------
+# glue
+# ----------------------------------------------------------------------------------------------
+def maxpool2d_nhwc_fwd(x, k, stride, pad):
+    """x: channels-last fp32 [B, C, H, W] -> (out channels-last, idx uint8 flat)."""
+    B, Cn, H, W = x.shape
+    Ho, Wo = (H + 2 * pad - k) // stride + 1, (W + 2 * pad - k) // stride + 1
+    out = torch.empty((B, Cn, Ho, Wo), dtype=torch.float32, device=x.device, memory_format=torch.channels_last)
+    idx = torch.empty(out.numel(), dtype=torch.uint8, device=x.device)
+    _run("qb_maxpool2d_nhwc_fwd", 4 * x.numel() + 5 * out.numel(), _ptr(x), _ptr(out), _ptr(idx), B, H, W, Cn, int(k), int(stride),
+         int(pad), _stream())
+    return out, idx
+
+
+def maxpool2d_nhwc_bwd(g, idx, in_shape, k, stride, pad):
+    B, Cn, H, W = in_shape
+    dx = torch.empty(in_shape, dtype=torch.float32, device=g.device, memory_format=torch.channels_last)
+    _run("qb_maxpool2d_nhwc_bwd", 5 * g.numel() + 4 * dx.numel(), _ptr(g), _ptr(idx), _ptr(dx), B, H, W, Cn, int(k), int(stride),
+         int(pad), _stream())
+    return dx
 
 
 # ----------------------------------------------------------------------------------------------

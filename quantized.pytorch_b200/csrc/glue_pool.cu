@@ -1,0 +1,149 @@
+// glue_pool.cu - SURVEY.md section 8(f) row N1: the stock-torch glue between the quantized modules.  MaxPool2d over
+// channels-last fp32 activations (models/resnet_quantized.py:150, after conv1 / bn1 / relu): torch's NHWC kernels take
+// 0.86 ms forward and 1.75 ms backward on the 256x64x112x112 tensor of ResNet-18 - ten times the traffic bound.
+//
+// Same arithmetic as ATen (aten/src/ATen/native/cuda/DilatedMaxPool2d.cu): the window is scanned rows first, a value
+// replaces the running maximum when it is GREATER (or NaN), so the FIRST maximal element wins ties - which matters
+// here because post-ReLU windows are full of equal zeros; backward adds the output gradient at that position, windows
+// visited in ascending (ho, wo) order.  Forward: thread = one output pixel x 8 adjacent channels (256-bit accesses),
+// the window-relative argmax is kept as one byte per element (9 positions) instead of ATen's int64 index.  Backward is a
+// GATHER: thread = one input pixel x 8 channels looks at the <= ceil(k/s)^2 windows that contain it - no atomics, every
+// dx element written exactly once, coalesced.
+#include "common.cuh"
+
+struct PoolGeom {
+    int B, H, W, C, Ho, Wo, k, stride, pad;
+    FastDiv d_c8, d_wo, d_ho, d_w, d_h;
+};
+
+__global__ void __launch_bounds__(256) k_maxpool_fwd_nhwc(const float* __restrict__ x, float* __restrict__ out, uint8_t* __restrict__ idx,
+                                                          PoolGeom g, uint32_t total) {
+    const uint32_t t = blockIdx.x * 256u + threadIdx.x;
+    if (t >= total) return;
+    const uint32_t c8n = (uint32_t)g.C >> 3;
+    uint32_t q = fdiv(t, g.d_c8);
+    const uint32_t c0 = (t - q * c8n) << 3;
+    uint32_t q2 = fdiv(q, g.d_wo);
+    const int wo = (int)(q - q2 * (uint32_t)g.Wo);
+    const uint32_t b = fdiv(q2, g.d_ho);
+    const int ho = (int)(q2 - b * (uint32_t)g.Ho);
+    const int h0 = ho * g.stride - g.pad, w0 = wo * g.stride - g.pad;
+    float mx[8];
+    uint32_t am[8];
+    bool first = true;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) { mx[j] = -QB_INF; am[j] = 0; }
+    for (int kh = 0; kh < g.k; ++kh) {
+        const int h = h0 + kh;
+        if (h < 0 || h >= g.H) continue;
+        for (int kw = 0; kw < g.k; ++kw) {
+            const int w = w0 + kw;
+            if (w < 0 || w >= g.W) continue;
+            const F8 v = ld256_keep(x + (((size_t)b * g.H + h) * g.W + w) * g.C + c0);
+            const uint32_t code = (uint32_t)(kh * g.k + kw);
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+                if (first) am[j] = code;                          // ATen initialises the index with the first valid element
+                if (v.v[j] > mx[j] || v.v[j] != v.v[j]) { mx[j] = v.v[j]; am[j] = code; }
+            }
+            first = false;
+        }
+    }
+    F8 o;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) o.v[j] = mx[j];
+    const size_t e = (size_t)t << 3;
+    st256(out + e, o);
+    uint2 pk;
+    pk.x = am[0] | (am[1] << 8) | (am[2] << 16) | (am[3] << 24);
+    pk.y = am[4] | (am[5] << 8) | (am[6] << 16) | (am[7] << 24);
+    *reinterpret_cast<uint2*>(idx + e) = pk;
+}
+
+__global__ void __launch_bounds__(256) k_maxpool_bwd_nhwc(const float* __restrict__ go, const uint8_t* __restrict__ idx,
+                                                          float* __restrict__ dx, PoolGeom g, uint32_t total) {
+    const uint32_t t = blockIdx.x * 256u + threadIdx.x;
+    if (t >= total) return;
+    const uint32_t c8n = (uint32_t)g.C >> 3;
+    uint32_t q = fdiv(t, g.d_c8);
+    const uint32_t c0 = (t - q * c8n) << 3;
+    uint32_t q2 = fdiv(q, g.d_w);
+    const int w = (int)(q - q2 * (uint32_t)g.W);
+    const uint32_t b = fdiv(q2, g.d_h);
+    const int h = (int)(q2 - b * (uint32_t)g.H);
+    // windows (ho, wo) with ho*stride - pad <= h <= ho*stride - pad + k - 1
+    int ho_lo = (h + g.pad - g.k + g.stride) / g.stride;            // ceil((h + pad - k + 1) / stride), numerator >= 0 handled below
+    if (h + g.pad - g.k + 1 <= 0) ho_lo = 0;
+    int ho_hi = (h + g.pad) / g.stride;
+    if (ho_hi > g.Ho - 1) ho_hi = g.Ho - 1;
+    int wo_lo = (w + g.pad - g.k + g.stride) / g.stride;
+    if (w + g.pad - g.k + 1 <= 0) wo_lo = 0;
+    int wo_hi = (w + g.pad) / g.stride;
+    if (wo_hi > g.Wo - 1) wo_hi = g.Wo - 1;
+    float acc[8];
+#pragma unroll
+    for (int j = 0; j < 8; ++j) acc[j] = 0.f;
+    for (int ho = ho_lo; ho <= ho_hi; ++ho) {
+        const uint32_t kh = (uint32_t)(h - (ho * g.stride - g.pad));
+        for (int wo = wo_lo; wo <= wo_hi; ++wo) {
+            const uint32_t code = kh * (uint32_t)g.k + (uint32_t)(w - (wo * g.stride - g.pad));
+            const size_t e = ((((size_t)b * g.Ho + ho) * g.Wo + wo) * g.C) + c0;
+            const uint2 pk = __ldg(reinterpret_cast<const uint2*>(idx + e));
+            const uint32_t hit_lo = pk.x ^ (code * 0x01010101u), hit_hi = pk.y ^ (code * 0x01010101u);
+            if (((hit_lo - 0x01010101u) & ~hit_lo & 0x80808080u) | ((hit_hi - 0x01010101u) & ~hit_hi & 0x80808080u)) {   // any byte equal
+                const F8 gv = ld256_keep(go + e);
+#pragma unroll
+                for (int j = 0; j < 8; ++j) {
+                    const uint32_t bj = ((j < 4 ? pk.x : pk.y) >> (8 * (j & 3))) & 0xffu;
+                    if (bj == code) acc[j] += gv.v[j];
+                }
+            }
+        }
+    }
+    F8 o;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) o.v[j] = acc[j];
+    st256(dx + ((size_t)t << 3), o);
+}
+
+static int pool_geom(PoolGeom& g, const char* who, int64_t B, int64_t H, int64_t W, int64_t C, int k, int stride, int pad,
+                     const void* p0, const void* p1, const void* p2) {
+    QB_CHECK_ARG(p0 && p1 && p2, "%s: null pointer", who);
+    QB_CHECK_ARG(B > 0 && H > 0 && W > 0 && C > 0 && k >= 1 && k <= 15 && stride >= 1 && pad >= 0 && 2 * pad <= k,
+                 "%s: bad geometry B=%lld H=%lld W=%lld C=%lld k=%d stride=%d pad=%d", who, (long long)B, (long long)H, (long long)W,
+                 (long long)C, k, stride, pad);
+    const int64_t Ho = (H + 2 * pad - k) / stride + 1, Wo = (W + 2 * pad - k) / stride + 1;
+    QB_CHECK_ARG(Ho > 0 && Wo > 0, "%s: empty output", who);
+    if (C % 8 != 0 || B * H * W * (C / 8) >= 4294967296LL ||
+        ((reinterpret_cast<uintptr_t>(p0) | reinterpret_cast<uintptr_t>(p1)) & 31) != 0 || (reinterpret_cast<uintptr_t>(p2) & 7) != 0) {
+        qb_set_error("%s: needs C %% 8 == 0, < 2^32 octets and 32-byte aligned tensors", who);
+        return QB_ERR_UNSUPPORTED;
+    }
+    g.B = (int)B; g.H = (int)H; g.W = (int)W; g.C = (int)C; g.Ho = (int)Ho; g.Wo = (int)Wo; g.k = k; g.stride = stride; g.pad = pad;
+    g.d_c8 = make_fastdiv((uint32_t)(C / 8));
+    g.d_wo = make_fastdiv((uint32_t)Wo); g.d_ho = make_fastdiv((uint32_t)Ho);
+    g.d_w = make_fastdiv((uint32_t)W); g.d_h = make_fastdiv((uint32_t)H);
+    return QB_OK;
+}
+
+extern "C" int qb_maxpool2d_nhwc_fwd(const float* x, float* out, uint8_t* idx, int64_t B, int64_t H, int64_t W, int64_t C, int k,
+                                     int stride, int pad, void* stream) {
+    PoolGeom g;
+    int rc = pool_geom(g, "qb_maxpool2d_nhwc_fwd", B, H, W, C, k, stride, pad, x, out, idx);
+    if (rc) return rc;
+    const uint32_t total = (uint32_t)((int64_t)B * g.Ho * g.Wo * (C / 8));
+    k_maxpool_fwd_nhwc<<<(total + 255u) / 256u, 256, 0, qb_stream(stream)>>>(x, out, idx, g, total);
+    QB_LAUNCH_CHECK();
+    return QB_OK;
+}
+
+extern "C" int qb_maxpool2d_nhwc_bwd(const float* grad_out, const uint8_t* idx, float* dx, int64_t B, int64_t H, int64_t W,
+                                     int64_t C, int k, int stride, int pad, void* stream) {
+    PoolGeom g;
+    int rc = pool_geom(g, "qb_maxpool2d_nhwc_bwd", B, H, W, C, k, stride, pad, grad_out, dx, idx);
+    if (rc) return rc;
+    const uint32_t total = (uint32_t)((int64_t)B * H * W * (C / 8));
+    k_maxpool_bwd_nhwc<<<(total + 255u) / 256u, 256, 0, qb_stream(stream)>>>(grad_out, idx, dx, g, total);
+    QB_LAUNCH_CHECK();
+    return QB_OK;
+}

@@ -32,6 +32,15 @@ def _qbn(q, c):
     return q.RangeBN(c, num_bits=8, num_bits_grad=8)
 
 
+def _maxpool(q):
+    """nn.MaxPool2d (resnet_quantized.py:150); on the native module set its channels-last CUDA path runs on libqb200
+    (glue.py) - identical values and gradients."""
+    if getattr(q, "NATIVE_GLUE", False):
+        from . import glue
+        return glue.MaxPool2d
+    return nn.MaxPool2d
+
+
 class _Identity(nn.Module):
     def forward(self, x):
         return x
@@ -91,7 +100,7 @@ class QResNet(nn.Module):
         self.conv1 = _qconv(q, 3, width0, stem_k, stem_s, stem_p)
         self.bn1 = _qbn(q, width0)
         self.relu = nn.ReLU(inplace=True)
-        self.maxpool = nn.MaxPool2d(3, 2, 1) if use_maxpool else _Identity()
+        self.maxpool = _maxpool(q)(3, 2, 1) if use_maxpool else _Identity()
         for i in range(4):
             if i < len(stages):
                 planes, n, stride = stages[i]

@@ -22,6 +22,8 @@ import torch.nn.functional as F
 from torch.autograd.function import Function, InplaceFunction
 
 from . import _abi
+
+NATIVE_GLUE = True      # models.py: use glue.MaxPool2d (libqb200) between these modules
 from ._abi import QB200Error, QB_SCALE_DOUBLE, QB_SCALE_FLOAT
 
 __all__ = ["UniformQuantize", "UniformQuantizeGrad", "quantize", "quantize_grad", "conv2d_biprec", "linear_biprec",
