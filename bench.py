@@ -310,7 +310,11 @@ def roofline_pass(step_body, _abi):
 
 # per-launch DRAM traffic of the dominant kernel families from the committed ncu --set full captures (bytes per launch,
 # mean over the launches of one ResNet-18 b256 step); filled from profiles/ncu_*_summary.txt
-TRAFFIC = {}
+TRAFFIC = {
+    # profiles/ncu_conv_step_r01h_summary.txt: 19 launches, 503 MB read + 817 MB written in total (outputs of the small
+    # late layers are still in the 126 MB L2 when their kernel ends, hence less than the algorithmic 118.6 MB/launch)
+    "qb_conv_i8_fwd": 69.5e6,
+}
 
 
 def main():

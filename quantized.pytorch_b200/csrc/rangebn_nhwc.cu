@@ -215,7 +215,6 @@ __global__ void k_rbn_stats_nhwc_merge(const float* pmax, const float* pmin, con
 // sums are plain integer adds of those bits - exact and order independent, so no fp64 and no index bookkeeping.
 // Optionally writes the codes (uint8) for the later passes.
 // ---------------------------------------------------------------------------------------------------
-constexpr uint32_t QB_MAGIC_BITS = 0x4B400000u;      // bit pattern of QB_MAGIC = 1.5 * 2^23
 
 struct Q8Row {
     uint32_t bits[8];
@@ -672,44 +671,44 @@ k_rbn_bwd_reduce_nhwc(const float* __restrict__ gq, const float* __restrict__ x,
     // thread-local partials stay in fp32: the geometry gives a thread at most ~100 rows (S up to 1024 segments), the
     // cross-thread / cross-segment combination below is fp64 in a fixed order
     float fg[VEC], fgx[VEC];
+    uint64_t fg2[4] = {0ull, 0ull, 0ull, 0ull}, fgx2[4] = {0ull, 0ull, 0ull, 0ull};     // VEC == 8: packed (0.f, 0.f) pairs
 #pragma unroll
     for (int j = 0; j < VEC; ++j) { fg[j] = 0.f; fgx[j] = 0.f; }
     auto one_row = [&](const V& av_, const V& bv_, const uint2& pk, int64_t r) {
         float av[VEC], bv[VEC];
         unpack(av_, av);
-        if (QUANT == 2) {
+        if constexpr (VEC == 8) {
+            if (QUANT == 2) affine_deq8(pk, aq.p, bv);                  // x_hat from the forward pass's codes
+            else unpack(bv_, bv);
+            if (NOISE >= 0) {
+                float u[8];
+                const int64_t e = r * g.C + c0;                         // a multiple of 8
+                if (NOISE == NOISE_INJECT) {
+                    const F8 w = ld256_stream(ga.noise.inject + e);
 #pragma unroll
-            for (int j = 0; j < VEC; ++j)
-                bv[j] = q_affine_deq((float)(((j < 4 ? pk.x : pk.y) >> (8 * (j & 3))) & 0xffu), aq.p);
+                    for (int j = 0; j < 8; ++j) u[j] = w.v[j];
+                } else if (NOISE == NOISE_PHILOX) {
+                    philox_noise8(seed, (uint64_t)(e >> 3) + (ga.noise.offset >> 3), u);
+                }
+                uint2 cd;
+                grad_fq8<(NOISE < 0 ? 0 : NOISE)>(av, u, GQ, ga.codes ? &cd : nullptr);
+                if (ga.codes) *reinterpret_cast<uint2*>(ga.codes + e) = cd;
+            }
+            if (QUANT == 1) affine_fq_vec<VEC>(bv, aq);
+#pragma unroll
+            for (int j = 0; j < 4; ++j) {                               // packed accumulation: FADD2 / FFMA2
+                const uint64_t a2 = pack2(av[2 * j], av[2 * j + 1]);
+                fg2[j] = add2(fg2[j], a2);
+                fgx2[j] = fma2(a2, pack2(bv[2 * j], bv[2 * j + 1]), fgx2[j]);
+            }
         } else {
             unpack(bv_, bv);
-        }
-        if (NOISE >= 0) {
-            float u[8];
-            const int64_t e = r * g.C + c0;                       // VEC == 8 on this path: e is a multiple of 8
-            if (NOISE == NOISE_INJECT) {
-                const F8 w = ld256_stream(ga.noise.inject + e);
+            if (QUANT == 1) affine_fq_vec<VEC>(bv, aq);
 #pragma unroll
-                for (int j = 0; j < 8; ++j) u[j] = w.v[j];
-            } else if (NOISE == NOISE_PHILOX) {
-                philox_noise8(seed, (uint64_t)(e >> 3) + (ga.noise.offset >> 3), u);
+            for (int j = 0; j < VEC; ++j) {
+                fg[j] += av[j];
+                fgx[j] += av[j] * bv[j];
             }
-            if (VEC == 8) {
-                uint32_t cd[8];
-                grad_fq_vec<(NOISE < 0 ? 0 : NOISE), 8>(reinterpret_cast<float(&)[8]>(av), u, GQ, ga.codes ? cd : nullptr);
-                if (ga.codes) {
-                    uint2 pk;
-                    pk.x = cd[0] | (cd[1] << 8) | (cd[2] << 16) | (cd[3] << 24);
-                    pk.y = cd[4] | (cd[5] << 8) | (cd[6] << 16) | (cd[7] << 24);
-                    *reinterpret_cast<uint2*>(ga.codes + e) = pk;
-                }
-            }
-        }
-        if (QUANT == 1) affine_fq_vec<VEC>(bv, aq);
-#pragma unroll
-        for (int j = 0; j < VEC; ++j) {
-            fg[j] += av[j];
-            fgx[j] += av[j] * bv[j];
         }
     };
     if (active) {
@@ -734,6 +733,10 @@ k_rbn_bwd_reduce_nhwc(const float* __restrict__ gq, const float* __restrict__ x,
             else b1 = ld_vec_stream<V>(x + r * g.C + c0);
             one_row(ld_vec_stream<V>(gq + r * g.C + c0), b1, pk1, r);
         }
+    }
+    if constexpr (VEC == 8) {
+#pragma unroll
+        for (int j = 0; j < 4; ++j) { unpack2(fg2[j], fg[2 * j], fg[2 * j + 1]); unpack2(fgx2[j], fgx[2 * j], fgx[2 * j + 1]); }
     }
     const int W = g.CT * VEC;
     double* s_g = reinterpret_cast<double*>(smem_raw);
@@ -865,12 +868,13 @@ struct BwdApplyArgs {
     const int32_t *amax_kc, *amin_kc;
     uint32_t C;
     FastDiv dC, dL;          // row = e / C ; chunk = row / L
+    FastDiv d_rl;            // rows a thread advances by per iteration (geometry RL)
     float* range_out;        // float[2] or nullptr
     float* pmin; float* pmax; unsigned int* counter;   // MinMaxWs-style partials (see fakequant_grad.cu)
 };
 
 template <int NOISE, bool RANGE>
-__global__ void __launch_bounds__(NH_THREADS)
+__global__ void __launch_bounds__(NH_THREADS, 3)
 k_rbn_bwd_apply_fused(const float* __restrict__ g, float* __restrict__ dx, NhwcGeom geo, BwdApplyArgs A, GradQuantArg ga) {
     // Column-persistent mapping (same geometry as the statistics kernel): a thread owns 8 adjacent channels for the whole
     // CTA lifetime, so the per-channel coefficients and the chunk's arg rows live in registers - the row loop touches
@@ -893,6 +897,11 @@ k_rbn_bwd_apply_fused(const float* __restrict__ g, float* __restrict__ dx, NhwcG
     if (rl < geo.RL && c0 < geo.C) {
         float sc[8], ca[8], gm[8], ce[8];
         int32_t am[8], an[8];
+        // rows this thread visits: r0 + i*RL.  A 64-bit map marks the few i at which one of the 16 arg rows of its
+        // channels falls, so the +-e fix-up costs one bit test per ROW instead of 16 compares per row
+        const int64_t r0 = r_begin + rl;
+        uint64_t hitmap = 0ull;
+        bool hit_far = false;
 #pragma unroll
         for (int j = 0; j < 8; ++j) {
             sc[j] = __ldg(A.qscale + c0 + j);
@@ -901,16 +910,29 @@ k_rbn_bwd_apply_fused(const float* __restrict__ g, float* __restrict__ dx, NhwcG
             ce[j] = A.amax_kc ? __ldg(A.coef_e + c0 + j) : 0.0f;
             am[j] = A.amax_kc ? __ldg(A.amax_kc + (size_t)k * A.C + c0 + j) : -1;
             an[j] = A.amax_kc ? __ldg(A.amin_kc + (size_t)k * A.C + c0 + j) : -1;
+#pragma unroll
+            for (int w = 0; w < 2; ++w) {
+                const int64_t d = (int64_t)(w ? an[j] : am[j]) - r0;
+                if (A.amax_kc && d >= 0 && d < (int64_t)geo.seg_rows) {
+                    const uint32_t i = fdiv((uint32_t)d, A.d_rl);
+                    if ((int64_t)i * geo.RL == d) {
+                        if (i < 64) hitmap |= 1ull << i;
+                        else hit_far = true;
+                    }
+                }
+            }
         }
-        auto one_row = [&](const F8& raw, const uint2& pk, int64_t r) {
+        uint64_t sc2[4], gm2[4];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+            sc2[j] = pack2(sc[2 * j], sc[2 * j + 1]);
+            gm2[j] = pack2(gm[2 * j], gm[2 * j + 1]);
+        }
+        auto one_row = [&](const F8& raw, const uint2& pk, int64_t r, uint32_t i) {
             const int64_t e = r * geo.C + c0;
             float gq[8];
             if (NOISE == -2) {                            // 8 codes instead of 8 floats: dequantize only
-#pragma unroll
-                for (int j = 0; j < 4; ++j) {
-                    gq[j] = q_zp_deq((float)((pk.x >> (8 * j)) & 0xffu), GQ.p);
-                    gq[4 + j] = q_zp_deq((float)((pk.y >> (8 * j)) & 0xffu), GQ.p);
-                }
+                zp_deq8(pk, GQ.p, gq);
             } else {
 #pragma unroll
                 for (int j = 0; j < 8; ++j) gq[j] = raw.v[j];
@@ -923,43 +945,58 @@ k_rbn_bwd_apply_fused(const float* __restrict__ g, float* __restrict__ dx, NhwcG
                     } else if (NOISE == NOISE_PHILOX) {
                         philox_noise8(seed, (uint64_t)(e >> 3) + (ga.noise.offset >> 3), u);
                     }
-                    grad_fq_vec<(NOISE < 0 ? 0 : NOISE), 8>(gq, u, GQ);
+                    grad_fq8<(NOISE < 0 ? 0 : NOISE)>(gq, u, GQ);
                 }
             }
             F8 o;
-            const int32_t row = (int32_t)r;
 #pragma unroll
-            for (int j = 0; j < 8; ++j) {
-                const float t = A.qgamma ? __fmul_rn(gq[j], gm[j]) : gq[j];
-                float v = __fadd_rn(__fmul_rn(t, sc[j]), ca[j]);
-                if (am[j] == row) v = __fadd_rn(v, ce[j]);
-                if (an[j] == row) v = __fsub_rn(v, ce[j]);
-                o.v[j] = v;
-                if (RANGE) { mn = fminf(mn, v); mx = fmaxf(mx, v); }
+            for (int j = 0; j < 4; ++j) {                 // (gq*gamma)*scale + a, every operation separately rounded: packed
+                uint64_t t = pack2(gq[2 * j], gq[2 * j + 1]);      // multiplies, SCALAR adds (ptxas would contract a packed
+                if (A.qgamma) t = mul2(t, gm2[j]);                 // mul + add pair into one FFMA2)
+                float a, b;
+                unpack2(mul2(t, sc2[j]), a, b);
+                o.v[2 * j] = __fadd_rn(a, ca[2 * j]);
+                o.v[2 * j + 1] = __fadd_rn(b, ca[2 * j + 1]);
+            }
+            if ((i < 64 ? ((hitmap >> i) & 1ull) != 0ull : hit_far)) {
+                const int32_t row = (int32_t)r;
+#pragma unroll
+                for (int j = 0; j < 8; ++j) {
+                    if (am[j] == row) o.v[j] = __fadd_rn(o.v[j], ce[j]);
+                    if (an[j] == row) o.v[j] = __fsub_rn(o.v[j], ce[j]);
+                }
+            }
+            if (RANGE) {
+#pragma unroll
+                for (int j = 0; j < 8; j += 2) { mn = min3(mn, o.v[j], o.v[j + 1]); mx = max3(mx, o.v[j], o.v[j + 1]); }
             }
             st256(dx + e, o);                              // default policy: the next kernel re-reads dx (L2)
         };
         int64_t r = r_begin + rl;
         const int64_t step = geo.RL;
-        for (; r + step < r_end; r += 2 * step) {
-            F8 v0, v1;
-            uint2 p0 = make_uint2(0, 0), p1 = make_uint2(0, 0);
-            if (NOISE == -2) {
-                p0 = __ldcs(reinterpret_cast<const uint2*>(ga.codes + r * geo.C + c0));
-                p1 = __ldcs(reinterpret_cast<const uint2*>(ga.codes + (r + step) * geo.C + c0));
-            } else {
-                v0 = ld256_stream(g + r * geo.C + c0);
-                v1 = ld256_stream(g + (r + step) * geo.C + c0);
+        uint32_t it = 0;
+        if (NOISE == -2) {
+            // code rows are only 8 bytes per thread: keep four of them in flight to cover the memory latency
+            for (; r + 3 * step < r_end; r += 4 * step, it += 4) {
+                uint2 pk[4];
+#pragma unroll
+                for (int u = 0; u < 4; ++u) pk[u] = __ldcs(reinterpret_cast<const uint2*>(ga.codes + (r + u * step) * geo.C + c0));
+#pragma unroll
+                for (int u = 0; u < 4; ++u) one_row(F8{}, pk[u], r + u * step, it + u);
             }
-            one_row(v0, p0, r);
-            one_row(v1, p1, r + step);
+        } else {
+            for (; r + step < r_end; r += 2 * step, it += 2) {
+                const F8 v0 = ld256_stream(g + r * geo.C + c0), v1 = ld256_stream(g + (r + step) * geo.C + c0);
+                one_row(v0, make_uint2(0, 0), r, it);
+                one_row(v1, make_uint2(0, 0), r + step, it + 1);
+            }
         }
-        for (; r < r_end; r += step) {
+        for (; r < r_end; r += step, ++it) {
             F8 v0;
             uint2 p0 = make_uint2(0, 0);
             if (NOISE == -2) p0 = __ldcs(reinterpret_cast<const uint2*>(ga.codes + r * geo.C + c0));
             else v0 = ld256_stream(g + r * geo.C + c0);
-            one_row(v0, p0, r);
+            one_row(v0, p0, r, it);
         }
     }
     const unsigned int nblocks = gridDim.x * gridDim.y, bid = blockIdx.y * gridDim.x + blockIdx.x;
@@ -1059,6 +1096,7 @@ extern "C" int qb_rangebn_bwd_apply_fused_nhwc(const float* g, float* dx, int64_
         geo.seg_rows = (geo.L + geo.S - 1) / geo.S;
         QB_CHECK_ARG((int64_t)Kc * geo.S * ctiles <= 4096, "qb_rangebn_bwd_apply_fused_nhwc: too many chunk x channel tiles");
     }
+    A.d_rl = make_fastdiv((uint32_t)geo.RL);
     dim3 grid((unsigned)(Kc * geo.S), (unsigned)((C + geo.tileC - 1) / geo.tileC));
     cudaStream_t st = qb_stream(stream);
     if (nm == -2) launch_bwd_apply_fused<-2>(grid, st, g, dx, geo, A, ga);
