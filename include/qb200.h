@@ -278,6 +278,17 @@ int qb_maxpool2d_nhwc_fwd(const float* x, float* out, uint8_t* idx, int64_t B, i
 int qb_maxpool2d_nhwc_bwd(const float* grad_out, const uint8_t* idx, float* dx, int64_t B, int64_t H, int64_t W, int64_t C,
                           int k, int stride, int pad, void* stream);
 
+/* ---------------------------------------------------------------------------------------------------
+ * Cross-rank exchange of the statistic blocks of batch-sharded training: a one-shot all-reduce
+ * over NVLink peer memory for latency-bound messages.  The reference has no counterpart (nn.DataParallel keeps
+ * per-replica statistics, main.py:344-345).  Every rank passes the peer-mapped addresses of all ranks' exchange buffers
+ * (qb_allreduce_small_buffer_bytes(world, slot_bytes) bytes each, zero-filled once); data is reduced in place, in rank
+ * order (bit-identical on every rank).  dtype 0 = double, 1 = float; mode 0 = SUM, 1 = QuantMeasure block (element 4 MIN,
+ * 5 MAX, others SUM), 2 = {MIN, MAX} pair.  CUDA-graph safe (the call counter lives in the buffer). */
+size_t qb_allreduce_small_buffer_bytes(int world, size_t slot_bytes);
+int qb_allreduce_small(void* data, int64_t n, int dtype, int mode, const uint64_t* peer_bufs, int rank, int world,
+                       size_t slot_bytes, void* stream);
+
 #ifdef __cplusplus
 }
 #endif

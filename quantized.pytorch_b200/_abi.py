@@ -58,6 +58,8 @@ PROTOTYPES = {
     "qb_rangebn2_apply": (_i32, [_p, _p, _i64, _i64, _i64, _i32, _p, _p, _p, _p, _p]),
     "qb_gemm_i8": (_i32, [_p, _p, _p, _i64, _i64, _i64, _i64, _p, _i32, _p, _p, _i32, _p, _p, _p, _i32, _p]),
     "qb_fakequant_rows_conv": (_i32, [_p, _p, _p, _p, _i64, _i64, _i32, _i32, _p, _p, _i32, _p]),
+    "qb_allreduce_small_buffer_bytes": (_sz, [_i32, _sz]),
+    "qb_allreduce_small": (_i32, [_p, _i64, _i32, _i32, _p, _i32, _i32, _sz, _p]),
     "qb_maxpool2d_nhwc_fwd": (_i32, [_p, _p, _p, _i64, _i64, _i64, _i64, _i32, _i32, _i32, _p]),
     "qb_maxpool2d_nhwc_bwd": (_i32, [_p, _p, _p, _i64, _i64, _i64, _i64, _i32, _i32, _i32, _p]),
     "qb_conv_i8_fwd": (_i32, [_p, _p, _p, _i64, _i64, _i64, _i64, _i64, _i32, _i32, _i32, _i32, _p, _i32, _p, _p, _i32,
@@ -469,6 +471,20 @@ def conv_i8_fwd(x_codes, w_codes, B, H, W, Cin, Cout, kh, kw, stride, pad, a_ran
          int(w_bits), _ptr(pixsum), _ptr(boxsum), _ptr(tapsum), _ptr(bias), _ptr(out_stats), _ptr(ws),
          ws.numel() if ws is not None else 0, _stream())
     return out
+
+
+def allreduce_small(t, mode, peer_ptrs, rank, world, slot_bytes):
+    """In-place one-shot all-reduce of a small contiguous double / float tensor over peer memory (qb_allreduce_small)."""
+    if t.dtype == torch.float64:
+        dt = 0
+    elif t.dtype == torch.float32:
+        dt = 1
+    else:
+        raise QB200Error("allreduce_small: double or float tensors only")
+    if not t.is_contiguous():
+        raise QB200Error("allreduce_small: tensor must be contiguous")
+    _run("qb_allreduce_small", 0, _ptr(t), t.numel(), dt, int(mode), peer_ptrs, int(rank), int(world), int(slot_bytes), _stream())
+    return t
 
 
 # ----------------------------------------------------------------------------------------------

@@ -63,13 +63,74 @@ class StatReducer:
         rng[1:2].copy_(ext[1:2])
 
 
-def init(device=None, group=None):
-    """Install the cross-rank statistic reducer.  torch.distributed must already be initialised."""
+class PeerReducer(StatReducer):
+    """The same reductions as ONE one-shot kernel each over NVLink peer memory (csrc/allreduce_small.cu) instead of one or
+    two NCCL all-reduces plus packing kernels: these messages are latency bound and on every layer's critical path.
+    The exchange buffer is torch symmetric memory (peer-mapped on every rank of the node)."""
+
+    SLOT_BYTES = 64 * 1024          # largest block: RangeBN double[3*C], C <= 2730
+
+    def __init__(self, device, group=None):
+        super().__init__(group)
+        import ctypes
+        import torch.distributed._symmetric_memory as symm
+        from . import _abi
+        self._abi = _abi
+        nbytes = _abi.load().qb_allreduce_small_buffer_bytes(self.world, self.SLOT_BYTES)
+        self.buf = symm.empty(nbytes, dtype=torch.uint8, device=device)
+        self.handle = symm.rendezvous(self.buf, dist.group.WORLD if group is None else group)
+        self.buf.zero_()
+        torch.cuda.synchronize(device)
+        dist.barrier(group=group)                      # every buffer is zero before anyone's first exchange
+        self.ptrs = (ctypes.c_uint64 * self.world)(*[int(p) for p in self.handle.buffer_ptrs])
+
+    def _ar(self, t, mode):
+        if t.numel() * t.element_size() > self.SLOT_BYTES:
+            return False
+        self._abi.allreduce_small(t, mode, self.ptrs, self.rank, self.world, self.SLOT_BYTES)
+        return True
+
+    def measure(self, stats):
+        if not self._ar(stats, 1):
+            super().measure(stats)
+
+    def rangebn(self, red):
+        if not self._ar(red, 0):
+            super().rangebn(red)
+
+    def rangebn_bwd(self, sums):
+        if not self._ar(sums, 0):
+            super().rangebn_bwd(sums)
+
+    def grad_range(self, rng):
+        if not self._ar(rng, 2):
+            super().grad_range(rng)
+
+    def error(self):
+        """True if any exchange timed out waiting for a peer (its results were invalid)."""
+        return bool(self.buf[8:12].view(torch.int32).item())
+
+
+def init(device=None, group=None, peer=None):
+    """Install the cross-rank statistic reducer.  torch.distributed must already be initialised.  On CUDA the
+    peer-memory reducer is used (``peer=False`` or QB_PEER_REDUCE=0 selects plain NCCL all-reduces)."""
+    import os
     if not dist.is_initialized():
         raise RuntimeError("torch.distributed is not initialised")
     _state.update(device=device, world=dist.get_world_size(group), rank=dist.get_rank(group), group=group)
     if _state["world"] > 1:
-        Q.set_stat_reducer(StatReducer(group))
+        if peer is None:
+            peer = os.environ.get("QB_PEER_REDUCE", "1") != "0"
+        red = None
+        if peer and device is not None and torch.device(device).type == "cuda" and dist.get_backend(group) == "nccl":
+            try:
+                red = PeerReducer(torch.device(device), group)
+            except Exception as e:                     # no symmetric memory on this system: NCCL path, same semantics
+                import sys
+                sys.stderr.write("qtorch_b200.dist: peer-memory reducer unavailable (%s); using NCCL all-reduces\n"
+                                 % (str(e).splitlines()[0] if str(e) else type(e).__name__))
+        Q.set_stat_reducer(red if red is not None else StatReducer(group))
+        _state["reducer"] = Q._reducer if hasattr(Q, "_reducer") else None
     return _state["rank"], _state["world"]
 
 

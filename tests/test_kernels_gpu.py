@@ -273,3 +273,46 @@ def test_measure_golden(lib, method, mom):
     r = lib.measure_finalize(None, bufs, mom, False, m, 8)
     y = lib.fakequant_affine(T(g["%s_xe" % tag]).to(DEV), 8, range_dev=r)
     np.testing.assert_allclose(y.cpu().numpy(), g["%s_ye" % tag], rtol=0, atol=5e-6)
+
+
+@pytest.mark.parametrize("world", [1, 2, 4])
+def test_allreduce_small_protocol_virtual_ranks(lib, world):
+    """qb_allreduce_small (the one-shot peer-memory all-reduce of the statistic blocks): `world` virtual ranks on ONE GPU,
+    each with its own exchange buffer and stream, run a sequence of calls of every kind; every rank must end up with the
+    rank-ordered reduction, bit-identical across ranks, and the call counters / error words must be clean."""
+    import ctypes
+    slot = 4096
+    nbytes = lib.load().qb_allreduce_small_buffer_bytes(world, slot)
+    bufs = [torch.zeros(nbytes, dtype=torch.uint8, device=DEV) for _ in range(world)]
+    ptrs = (ctypes.c_uint64 * world)(*[b.data_ptr() for b in bufs])
+    streams = [torch.cuda.Stream() for _ in range(world)]
+    gen = torch.Generator().manual_seed(world)
+    torch.cuda.synchronize()
+    calls = [(torch.float64, 8, 1), (torch.float64, 3 * 64, 0), (torch.float32, 2, 2), (torch.float64, 2 * 64, 0),
+             (torch.float64, 8, 1), (torch.float32, 2, 2), (torch.float64, 512, 0)]
+    for dtype, n, mode in calls * 3:
+        src = [torch.randn(n, generator=gen, dtype=torch.float64).to(dtype).to(DEV) for _ in range(world)]
+        work = [s.clone() for s in src]
+        torch.cuda.synchronize()
+        for r in range(world):
+            with torch.cuda.stream(streams[r]):
+                lib.allreduce_small(work[r], mode, ptrs, r, world, slot)
+        torch.cuda.synchronize()
+        want = src[0].clone()
+        for q in range(1, world):
+            if mode == 0:
+                want = want + src[q]
+            elif mode == 1:
+                w2 = want + src[q]
+                w2[4] = torch.minimum(want[4], src[q][4])
+                w2[5] = torch.maximum(want[5], src[q][5])
+                want = w2
+            else:
+                want = torch.stack([torch.minimum(want[0], src[q][0]), torch.maximum(want[1], src[q][1])])
+        for r in range(world):
+            assert torch.equal(work[r], want), (dtype, n, mode, r)
+    for b in bufs:
+        assert int(b[0:8].view(torch.int64).item()) == len(calls) * 3
+        assert int(b[8:12].view(torch.int32).item()) == 0
+    with pytest.raises(lib.QB200Error):
+        lib.allreduce_small(torch.zeros(slot, dtype=torch.float64, device=DEV), 0, ptrs, 0, world, slot)
