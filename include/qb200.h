@@ -273,6 +273,9 @@ int qb_rangebn2_apply(const float* x, float* out, int64_t B, int64_t C, int64_t 
  * (models/resnet_quantized.py:150).  Same values, tie-breaking (first maximal element of the window, rows first) and
  * backward accumulation order as ATen's max_pool2d; idx holds the window-relative position kh*k + kw of the maximum as
  * one byte per output element.  Needs C % 8 == 0, k <= 15, 2*pad <= k, 32-byte aligned x/out/grad/dx, 8-byte aligned idx. */
+/* nn.ReLU(inplace) between the modules (models/resnet_quantized.py:52-68,147): y = relu(x) (y may alias x) and, in the same
+ * pass, the QuantMeasure statistics block (as qb_measure_stats) of y for the quantized layer that consumes it. */
+int qb_relu_measure(const float* x, float* y, int64_t B, int64_t inner, double* stats, void* ws, size_t ws_bytes, void* stream);
 int qb_maxpool2d_nhwc_fwd(const float* x, float* out, uint8_t* idx, int64_t B, int64_t H, int64_t W, int64_t C, int k,
                           int stride, int pad, void* stream);
 int qb_maxpool2d_nhwc_bwd(const float* grad_out, const uint8_t* idx, float* dx, int64_t B, int64_t H, int64_t W, int64_t C,

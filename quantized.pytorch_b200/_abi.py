@@ -25,6 +25,7 @@ PROTOTYPES = {
     "qb_device_info": (_i32, [_i32, C.POINTER(_i32), C.POINTER(_i32), C.POINTER(_i32), C.POINTER(_sz)]),
     "qb_measure_ws_bytes": (_sz, [_i64]),
     "qb_measure_stats": (_i32, [_p, _i64, _i64, _p, _p, _sz, _p]),
+    "qb_relu_measure": (_i32, [_p, _p, _i64, _i64, _p, _p, _sz, _p]),
     "qb_measure_finalize": (_i32, [_p, _p, _p, _p, _p, _p, _dbl, _i32, _i32, _i32, _p, _p]),
     "qb_fakequant_affine": (_i32, [_p, _p, _p, _i64, _i32, _p, _dbl, _dbl, _i32, _p]),
     "qb_selftest_div": (_i32, [_p, _flt, _p, _p, _i64, _p]),
@@ -201,6 +202,20 @@ def measure_stats(x, stats=None):
     ws = workspace("measure", nb, x.device)
     _run("qb_measure_stats", 4 * x.numel(), _ptr(x), B, inner, _ptr(stats), _ptr(ws), ws.numel(), _stream())
     return stats
+
+
+def relu_measure(x, out=None):
+    """out = relu(x) (out=None: in place) and the QuantMeasure statistics (double[8]) of the result, one pass."""
+    lib = load()
+    x = _f32c(x, "x")
+    if out is None:
+        out = x
+    B = x.size(0)
+    inner = x.numel() // max(B, 1)
+    stats = torch.empty(8, dtype=torch.float64, device=x.device)
+    ws = workspace("measure", lib.qb_measure_ws_bytes(B), x.device)
+    _run("qb_relu_measure", 8 * x.numel(), _ptr(x), _ptr(out), B, inner, _ptr(stats), _ptr(ws), ws.numel(), _stream())
+    return out, stats
 
 
 def measure_finalize(stats, running, momentum, training, method, bits, range_out=None):

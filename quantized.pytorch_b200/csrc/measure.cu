@@ -28,8 +28,13 @@ __device__ __forceinline__ void acc4(float4 v, float& mn, float& mx, float& s, f
     q += (v.x * v.x + v.y * v.y) + (v.z * v.z + v.w * v.w);
 }
 
+// RELU: y = relu(x) is written (y may alias x) and the statistics are those of y - the glue ReLU between the modules
+//  then delivers the next QuantMeasure's statistics for free.  NaNs propagate like ATen's relu.
+__device__ __forceinline__ float relu1(float v) { return v < 0.0f ? 0.0f : v; }
+
+template <bool RELU>
 __global__ void __launch_bounds__(MS_THREADS)
-k_measure_stats(const float* __restrict__ x, int64_t B, int64_t inner, int vec, double* stats, unsigned int* row_max,
+k_measure_stats(const float* x, float* y, int64_t B, int64_t inner, int vec, double* stats, unsigned int* row_max,
                 unsigned int* row_min, double* psum, double* psq, unsigned int* counter) {
     __shared__ float smn[8], smx[8];
     __shared__ double sd[2][8];
@@ -38,49 +43,71 @@ k_measure_stats(const float* __restrict__ x, int64_t B, int64_t inner, int vec, 
     const int64_t tiles_per_row = (inner + MS_TILE - 1) / MS_TILE;
     const int64_t T = B * tiles_per_row;
     double dsum = 0.0, dsq = 0.0;
-    for (int64_t t = blockIdx.x; t < T; t += gridDim.x) {
+    // a CTA owns a CONTIGUOUS range of tiles, so it crosses few sample boundaries: the block-wide min/max reduction and
+    // the two atomics run once per (CTA, sample) instead of once per tile
+    const int64_t per_cta = (T + gridDim.x - 1) / gridDim.x;
+    const int64_t t_begin = (int64_t)blockIdx.x * per_cta, t_end = (t_begin + per_cta < T) ? t_begin + per_cta : T;
+    float mn = QB_INF, mx = -QB_INF;
+    int64_t cur_b = -1;
+    auto flush = [&](int64_t b) {
+        float a = warp_min(mn), c = warp_max(mx);
+        __syncthreads();
+        if (lane == 0) { smn[warp] = a; smx[warp] = c; }
+        __syncthreads();
+        if (threadIdx.x == 0) {
+#pragma unroll
+            for (int w = 1; w < MS_THREADS / 32; ++w) { a = fminf(a, smn[w]); c = fmaxf(c, smx[w]); }
+            atomicMax(&row_max[b], enc_ord(c));
+            atomicMax(&row_min[b], ~enc_ord(a));    // max of complemented code == min
+        }
+        mn = QB_INF; mx = -QB_INF;
+    };
+    for (int64_t t = t_begin; t < t_end; ++t) {
         const int64_t b = t / tiles_per_row, s = t - b * tiles_per_row;
+        if (b != cur_b) {
+            if (cur_b >= 0) flush(cur_b);
+            cur_b = b;
+        }
         const int64_t off = s * MS_TILE;
         const int64_t len = (inner - off < MS_TILE) ? inner - off : MS_TILE;
         const float* src = x + b * inner + off;
-        float mn = QB_INF, mx = -QB_INF, fs = 0.f, fq = 0.f;
+        float fs = 0.f, fq = 0.f;
         if (vec) {
             const int64_t nq = len >> 2;
             float4 v[MS_VEC_PER_THREAD];
 #pragma unroll
             for (int u = 0; u < MS_VEC_PER_THREAD; ++u) {
                 int64_t qi = threadIdx.x + (int64_t)u * MS_THREADS;
-                if (qi < nq) v[u] = __ldcs(reinterpret_cast<const float4*>(src) + qi);
+                if (qi < nq) v[u] = RELU ? reinterpret_cast<const float4*>(src)[qi]          // in place: the line is written next
+                                         : __ldcs(reinterpret_cast<const float4*>(src) + qi);
             }
 #pragma unroll
             for (int u = 0; u < MS_VEC_PER_THREAD; ++u) {
                 int64_t qi = threadIdx.x + (int64_t)u * MS_THREADS;
-                if (qi < nq) acc4(v[u], mn, mx, fs, fq);
+                if (qi < nq) {
+                    if (RELU) {
+                        v[u] = make_float4(relu1(v[u].x), relu1(v[u].y), relu1(v[u].z), relu1(v[u].w));
+                        reinterpret_cast<float4*>(y + b * inner + off)[qi] = v[u];
+                    }
+                    acc4(v[u], mn, mx, fs, fq);
+                }
             }
             if ((int64_t)threadIdx.x < (len & 3)) {     // only the last tile of a row can have a tail (inner%4==0 => none)
                 float e = src[(nq << 2) + threadIdx.x];
+                if (RELU) { e = relu1(e); y[b * inner + off + (nq << 2) + threadIdx.x] = e; }
                 mn = fminf(mn, e); mx = fmaxf(mx, e); fs += e; fq += e * e;
             }
         } else {
             for (int64_t j = threadIdx.x; j < len; j += MS_THREADS) {
                 float e = src[j];
+                if (RELU) { e = relu1(e); y[b * inner + off + j] = e; }
                 mn = fminf(mn, e); mx = fmaxf(mx, e); fs += e; fq += e * e;
             }
         }
         dsum += (double)fs;
         dsq += (double)fq;
-        mn = warp_min(mn);
-        mx = warp_max(mx);
-        __syncthreads();
-        if (lane == 0) { smn[warp] = mn; smx[warp] = mx; }
-        __syncthreads();
-        if (threadIdx.x == 0) {
-#pragma unroll
-            for (int w = 1; w < MS_THREADS / 32; ++w) { mn = fminf(mn, smn[w]); mx = fmaxf(mx, smx[w]); }
-            atomicMax(&row_max[b], enc_ord(mx));
-            atomicMax(&row_min[b], ~enc_ord(mn));    // max of complemented code == min
-        }
     }
+    if (cur_b >= 0) flush(cur_b);
     // per-CTA partial sums, fixed slot per CTA
     dsum = warp_sum(dsum);
     dsq = warp_sum(dsq);
@@ -137,8 +164,21 @@ k_measure_stats(const float* __restrict__ x, int64_t B, int64_t inner, int vec, 
     }
 }
 
+static int measure_launch(const float* x, float* y, int64_t B, int64_t inner, double* stats, void* ws, size_t ws_bytes, void* stream);
+
 extern "C" int qb_measure_stats(const float* x, int64_t B, int64_t inner, double* stats, void* ws, size_t ws_bytes,
                                 void* stream) {
+    return measure_launch(x, nullptr, B, inner, stats, ws, ws_bytes, stream);
+}
+
+/* y = relu(x) (y may be x: in place) plus the QuantMeasure statistics of y in the same pass. */
+extern "C" int qb_relu_measure(const float* x, float* y, int64_t B, int64_t inner, double* stats, void* ws, size_t ws_bytes,
+                               void* stream) {
+    QB_CHECK_ARG(y, "qb_relu_measure: null output");
+    return measure_launch(x, y, B, inner, stats, ws, ws_bytes, stream);
+}
+
+static int measure_launch(const float* x, float* y, int64_t B, int64_t inner, double* stats, void* ws, size_t ws_bytes, void* stream) {
     QB_CHECK_ARG(x && stats && ws, "qb_measure_stats: null pointer");
     QB_CHECK_ARG(B > 0 && inner > 0, "qb_measure_stats: B=%lld inner=%lld (empty input has no range)", (long long)B,
                  (long long)inner);
@@ -152,15 +192,15 @@ extern "C" int qb_measure_stats(const float* x, int64_t B, int64_t inner, double
     double* psq = psum + MS_MAX_BLOCKS;
     unsigned int* row_max = reinterpret_cast<unsigned int*>(base + MS_FIXED_BYTES);
     unsigned int* row_min = row_max + B;
-    const int vec = ((reinterpret_cast<uintptr_t>(x) & 15) == 0) && (inner % 4 == 0);
+    const int vec = (((reinterpret_cast<uintptr_t>(x) | reinterpret_cast<uintptr_t>(y)) & 15) == 0) && (inner % 4 == 0);
     const int64_t T = B * ((inner + MS_TILE - 1) / MS_TILE);
     int sms = qb_sm_count();
     if (sms <= 0) sms = 148;
     int64_t cap = (int64_t)sms * 8;
     if (cap > MS_MAX_BLOCKS) cap = MS_MAX_BLOCKS;
     int grid = (int)(T < cap ? T : cap);
-    k_measure_stats<<<grid, MS_THREADS, 0, qb_stream(stream)>>>(x, B, inner, vec, stats, row_max, row_min, psum, psq,
-                                                                counter);
+    if (y) k_measure_stats<true><<<grid, MS_THREADS, 0, qb_stream(stream)>>>(x, y, B, inner, vec, stats, row_max, row_min, psum, psq, counter);
+    else k_measure_stats<false><<<grid, MS_THREADS, 0, qb_stream(stream)>>>(x, nullptr, B, inner, vec, stats, row_max, row_min, psum, psq, counter);
     QB_LAUNCH_CHECK();
     return QB_OK;
 }

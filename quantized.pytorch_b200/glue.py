@@ -40,3 +40,44 @@ class MaxPool2d(nn.MaxPool2d):
         if self.dilation == 1 and not self.ceil_mode and not self.return_indices and _native_ok(x, k, s, p):
             return _MaxPoolFn.apply(x, k, s, p)
         return F.max_pool2d(x, k, s, p, self.dilation, self.ceil_mode, self.return_indices)
+
+
+_last = {"stats": None}          # statistics block of the most recent _ReLUFn.forward (picked up right after apply)
+
+
+class _ReLUFn(torch.autograd.Function):
+    """relu in place + the statistics of the result for the QuantMeasure of the consuming layer (stashed by tensor)."""
+
+    @staticmethod
+    def forward(ctx, x, inplace):
+        from . import quantize as Q
+        out, stats = _abi.relu_measure(x, None if inplace else torch.empty_like(x))
+        if inplace:
+            ctx.mark_dirty(x)
+        ctx.save_for_backward(out)
+        _last["stats"] = stats
+        return out
+
+    @staticmethod
+    def backward(ctx, g):
+        (out,) = ctx.saved_tensors
+        return torch.ops.aten.threshold_backward(g, out, 0), None
+
+
+class ReLU(nn.ReLU):
+    """torch.nn.ReLU whose dense fp32 CUDA path also delivers the next QuantMeasure's statistics:
+    the quantized layer that consumes the output then skips its own statistics pass.  Values and gradient are torch's."""
+
+    def forward(self, x):
+        from . import quantize as Q
+        dense = x.is_contiguous() or (x.dim() == 4 and x.is_contiguous(memory_format=torch.channels_last))
+        if not (x.is_cuda and x.dtype == torch.float32 and x.dim() >= 2 and dense and x.numel() > 0 and self.training):
+            return super().forward(x)
+        if torch.is_grad_enabled() and x.requires_grad:
+            out = _ReLUFn.apply(x, self.inplace)
+            stats, _last["stats"] = _last["stats"], None
+        else:
+            out, stats = _abi.relu_measure(x, None if self.inplace else torch.empty_like(x))
+        if stats is not None:
+            Q._stash_fwd_stats(out, stats)
+        return out

@@ -41,6 +41,15 @@ def _maxpool(q):
     return nn.MaxPool2d
 
 
+def _relu(q):
+    """nn.ReLU(inplace=True) (resnet_quantized.py:47,147); native module set: glue.ReLU (same values, plus the statistics
+    the next quantized layer needs)."""
+    if getattr(q, "NATIVE_GLUE", False):
+        from . import glue
+        return glue.ReLU(inplace=True)
+    return nn.ReLU(inplace=True)
+
+
 class _Identity(nn.Module):
     def forward(self, x):
         return x
@@ -53,7 +62,7 @@ class BasicBlock(nn.Module):
         super().__init__()
         self.conv1 = _qconv(q, inplanes, planes, 3, stride, 1)
         self.bn1 = _qbn(q, planes)
-        self.relu = nn.ReLU(inplace=True)
+        self.relu = _relu(q)
         self.conv2 = _qconv(q, planes, planes, 3, 1, 1)
         self.bn2 = _qbn(q, planes)
         self.downsample = downsample
@@ -77,7 +86,7 @@ class Bottleneck(nn.Module):
         self.bn2 = _qbn(q, planes)
         self.conv3 = _qconv(q, planes, planes * 4, 1)
         self.bn3 = _qbn(q, planes * 4)
-        self.relu = nn.ReLU(inplace=True)
+        self.relu = _relu(q)
         self.downsample = downsample
         self._last_bn = "bn3"
 
@@ -99,7 +108,7 @@ class QResNet(nn.Module):
         self.inplanes = width0
         self.conv1 = _qconv(q, 3, width0, stem_k, stem_s, stem_p)
         self.bn1 = _qbn(q, width0)
-        self.relu = nn.ReLU(inplace=True)
+        self.relu = _relu(q)
         self.maxpool = _maxpool(q)(3, 2, 1) if use_maxpool else _Identity()
         for i in range(4):
             if i < len(stages):
