@@ -527,6 +527,7 @@ class _QBase(QuantNode):
 # Route QConv2d / QLinear through the int8 tcgen05 kernels whenever the geometry is supported (conv_i8.cu,
 # gemm_i8.cu); otherwise the contraction of the already fake-quantized tensors goes to cuDNN / cuBLAS.
 USE_INT8_TENSOR_CORES = True
+USE_DP4A_FIRST_LAYER = True
 
 
 def _conv_i8_supported(mod, x):
@@ -534,10 +535,20 @@ def _conv_i8_supported(mod, x):
         return False
     kh, kw = mod.kernel_size
     st, pd, dl = _pair(mod.stride), _pair(mod.padding), _pair(mod.dilation)
-    return (dl == (1, 1) and st[0] == st[1] and st[0] in (1, 2) and pd[0] == pd[1] and not isinstance(pd[0], str)
-            and kh * kw <= 9 and mod.in_channels % 32 == 0 and mod.out_channels % 16 == 0
+    if not (dl == (1, 1) and st[0] == st[1] and st[0] in (1, 2) and pd[0] == pd[1] and not isinstance(pd[0], str)
             and mod.num_bits <= 8 and mod.num_bits_weight <= 8
-            and (x.shape[2] + 2 * pd[0] - kh) // st[0] + 1 >= 1 and (x.shape[3] + 2 * pd[1] - kw) // st[1] + 1 >= 1)
+            and (x.shape[2] + 2 * pd[0] - kh) // st[0] + 1 >= 1 and (x.shape[3] + 2 * pd[1] - kw) // st[1] + 1 >= 1):
+        return False
+    if kh * kw <= 9 and mod.in_channels % 32 == 0 and mod.out_channels % 16 == 0:
+        return True
+    return _conv_dp4a_supported(mod)
+
+
+def _conv_dp4a_supported(mod):
+    """First-layer geometry (3 input channels): direct DP4A convolution (conv_dp4a.cu)."""
+    kh, kw = mod.kernel_size
+    return (USE_DP4A_FIRST_LAYER and mod.in_channels % 32 != 0
+            and _abi.conv_dp4a_supported(mod.in_channels, mod.out_channels, kh, kw, _pair(mod.stride)[0]))
 
 
 def _linear_i8_supported(mod, x):
@@ -565,13 +576,18 @@ class _QTensorCoreFn(Function):
         if conv:
             B, Cin, H, W = x.shape
             kh, kw = mod.kernel_size
-            pixsum = _abi.rowsum_u8(codes, B * H * W, Cin)
-            stats = torch.empty(8, dtype=torch.float64, device=x.device) if mod.training else None
-            out = _abi.conv_i8_fwd(codes, wcodes, B, H, W, Cin, mod.out_channels, kh, kw, _pair(mod.stride)[0],
-                                   _pair(mod.padding)[0], rng, bits_a, mod.weight_min, mod.weight_max, bits_w, pixsum, tapsum,
-                                   bias=qbias, out_stats=stats)
-            if stats is not None:
-                _stash_fwd_stats(out, stats)
+            if Cin % 32 != 0:                                               # first layer: direct DP4A convolution
+                out = _abi.conv_dp4a_fwd(codes, wcodes, B, H, W, Cin, mod.out_channels, kh, kw, _pair(mod.stride)[0],
+                                         _pair(mod.padding)[0], rng, bits_a, mod.weight_min, mod.weight_max, bits_w, tapsum,
+                                         bias=qbias)
+            else:
+                pixsum = _abi.rowsum_u8(codes, B * H * W, Cin)
+                stats = torch.empty(8, dtype=torch.float64, device=x.device) if mod.training else None
+                out = _abi.conv_i8_fwd(codes, wcodes, B, H, W, Cin, mod.out_channels, kh, kw, _pair(mod.stride)[0],
+                                       _pair(mod.padding)[0], rng, bits_a, mod.weight_min, mod.weight_max, bits_w, pixsum,
+                                       tapsum, bias=qbias, out_stats=stats)
+                if stats is not None:
+                    _stash_fwd_stats(out, stats)
             ctx.conv = (_pair(mod.stride), _pair(mod.padding), _pair(mod.dilation), mod.groups)
         else:
             M, K = x.shape
