@@ -248,14 +248,16 @@ int qb_conv_i8_fwd(const uint8_t* x_codes, const uint8_t* w_codes_khwc, float* o
                    size_t stats_ws_bytes, void* stream);
 
 /* QConv2d forward contraction of a network's FIRST layer (models/resnet_quantized.py:147 conv1 7x7/2 over 3 input
- * channels; models/mobilenet_quantized.py first 3x3/2 conv): a direct DP4A convolution over the same operands as
- * qb_conv_i8_fwd (x_codes NHWC uint8, centred weight codes [Cout][kh*kw][Cin] + tapsum from qb_fakequant_rows_conv,
- * device-side ranges).  No pixsum / boxsum scratch: the activation code sum of each window is taken in the kernel.
- * Supported (qb_conv_dp4a_supported): 7x7 filters with 21..24-byte rows (kw*Cin) or 3x3 with 9..12-byte rows,
- * Cout % 4 == 0 and <= 128, stride 1 or 2, dilation 1, groups 1; otherwise QB_ERR_UNSUPPORTED.  out fp32 [B,Ho,Wo,Cout]. */
-int qb_conv_dp4a_supported(int64_t Cin, int64_t Cout, int kh, int kw, int stride);
-size_t qb_conv_dp4a_ws_bytes(int64_t Cout, int kh);   /* scratch for the packed operands (16-byte aligned, per call) */
-int qb_conv_dp4a_fwd(const uint8_t* x_codes, const int8_t* w_codes_khwc, float* out, int64_t B, int64_t H, int64_t W,
+ * channels; models/mobilenet_quantized.py first 3x3/2 conv): tcgen05 kind::i8 over a thread-built im2col operand, same
+ * operands as qb_conv_i8_fwd (x_codes NHWC uint8, centred weight codes [Cout][kh*kw][Cin] + tapsum from
+ * qb_fakequant_rows_conv, device-side ranges).  No pixsum / boxsum scratch: the activation code sum of each window is
+ * taken in the kernel; zero padding is exact (per-border-case constants).
+ * Supported (qb_conv_stem_supported): 7x7 filters with 21..24-byte rows (kw*Cin) or 3x3 with 9..12-byte rows,
+ * Cout % 16 == 0 and <= 128, stride 1 or 2, dilation 1, groups 1, at most 8 distinct border cases per axis; otherwise
+ * QB_ERR_UNSUPPORTED.  ws: qb_conv_stem_ws_bytes(Cout) bytes of scratch, 16-byte aligned.  out fp32 [B,Ho,Wo,Cout].   */
+int qb_conv_stem_supported(int64_t H, int64_t W, int64_t Cin, int64_t Cout, int kh, int kw, int stride, int pad);
+size_t qb_conv_stem_ws_bytes(int64_t Cout);
+int qb_conv_stem_fwd(const uint8_t* x_codes, const int8_t* w_codes_khwc, float* out, int64_t B, int64_t H, int64_t W,
                      int64_t Cin, int64_t Cout, int kh, int kw, int stride, int pad, const float* a_range, int a_bits,
                      const float* w_row_min, const float* w_row_max, int w_bits, const int32_t* tapsum,
                      const float* bias, void* ws, size_t ws_bytes, void* stream);

@@ -63,9 +63,9 @@ PROTOTYPES = {
     "qb_allreduce_small": (_i32, [_p, _i64, _i32, _i32, _p, _i32, _i32, _sz, _p]),
     "qb_maxpool2d_nhwc_fwd": (_i32, [_p, _p, _p, _i64, _i64, _i64, _i64, _i32, _i32, _i32, _p]),
     "qb_maxpool2d_nhwc_bwd": (_i32, [_p, _p, _p, _i64, _i64, _i64, _i64, _i32, _i32, _i32, _p]),
-    "qb_conv_dp4a_supported": (_i32, [_i64, _i64, _i32, _i32, _i32]),
-    "qb_conv_dp4a_ws_bytes": (_sz, [_i64, _i32]),
-    "qb_conv_dp4a_fwd": (_i32, [_p, _p, _p, _i64, _i64, _i64, _i64, _i64, _i32, _i32, _i32, _i32, _p, _i32, _p, _p, _i32,
+    "qb_conv_stem_supported": (_i32, [_i64, _i64, _i64, _i64, _i32, _i32, _i32, _i32]),
+    "qb_conv_stem_ws_bytes": (_sz, [_i64]),
+    "qb_conv_stem_fwd": (_i32, [_p, _p, _p, _i64, _i64, _i64, _i64, _i64, _i32, _i32, _i32, _i32, _p, _i32, _p, _p, _i32,
                                 _p, _p, _p, _sz, _p]),
     "qb_conv_i8_fwd": (_i32, [_p, _p, _p, _i64, _i64, _i64, _i64, _i64, _i32, _i32, _i32, _i32, _p, _i32, _p, _p, _i32,
                               _p, _p, _p, _p, _p, _p, _sz, _p]),
@@ -107,7 +107,7 @@ _profile = None       # list of (name, algorithmic_bytes, start_event, end_event
 
 # kernels enqueued per C call
 _NLAUNCH = {"qb_rangebn_stats": 2, "qb_rangebn_bwd_reduce": 2, "qb_rangebn_bwd_apply": 2,
-            "qb_conv_i8_fwd": 2, "qb_conv_dp4a_fwd": 2, "qb_rangebn_stats_nhwc": 3, "qb_rangebn_bwd_reduce_nhwc": 2, "qb_rangebn_bwd_apply_nhwc": 2}
+            "qb_conv_i8_fwd": 2, "qb_conv_stem_fwd": 2, "qb_rangebn_stats_nhwc": 3, "qb_rangebn_bwd_reduce_nhwc": 2, "qb_rangebn_bwd_apply_nhwc": 2}
 
 
 _next_ops = 0          # integer operations (2*M*N*K) of the next tensor-core call, set by the conv / GEMM wrappers
@@ -492,19 +492,20 @@ def conv_i8_fwd(x_codes, w_codes, B, H, W, Cin, Cout, kh, kw, stride, pad, a_ran
     return out
 
 
-def conv_dp4a_supported(Cin, Cout, kh, kw, stride):
-    return bool(load().qb_conv_dp4a_supported(int(Cin), int(Cout), int(kh), int(kw), int(stride)))
+def conv_stem_supported(H, W, Cin, Cout, kh, kw, stride, pad):
+    return bool(load().qb_conv_stem_supported(int(H), int(W), int(Cin), int(Cout), int(kh), int(kw), int(stride), int(pad)))
 
 
-def conv_dp4a_fwd(x_codes, w_codes, B, H, W, Cin, Cout, kh, kw, stride, pad, a_range, a_bits, row_min, row_max, w_bits, tapsum,
+def conv_stem_fwd(x_codes, w_codes, B, H, W, Cin, Cout, kh, kw, stride, pad, a_range, a_bits, row_min, row_max, w_bits, tapsum,
                   bias=None):
     """First-layer convolution (3 input channels) on the integer codes -> fp32 [B, Cout, Ho, Wo] stored channels-last."""
     Ho, Wo = (H + 2 * pad - kh) // stride + 1, (W + 2 * pad - kw) // stride + 1
-    out = torch.empty((B, Cout, Ho, Wo), dtype=torch.float32, device=x_codes.device, memory_format=torch.channels_last)
-    ws = workspace("conv_dp4a", load().qb_conv_dp4a_ws_bytes(Cout, kh), x_codes.device)
+    out = torch.empty((B, Cout, max(Ho, 0), max(Wo, 0)), dtype=torch.float32, device=x_codes.device,
+                      memory_format=torch.channels_last)
+    ws = workspace("conv_stem", load().qb_conv_stem_ws_bytes(Cout), x_codes.device)
     global _next_ops
     _next_ops = 2 * B * Ho * Wo * Cout * kh * kw * Cin
-    _run("qb_conv_dp4a_fwd", B * H * W * Cin + Cout * kh * kw * Cin + 4 * B * Ho * Wo * Cout, _ptr(x_codes), _ptr(w_codes),
+    _run("qb_conv_stem_fwd", B * H * W * Cin + Cout * kh * kw * Cin + 4 * B * Ho * Wo * Cout, _ptr(x_codes), _ptr(w_codes),
          _ptr(out), B, H, W, Cin, Cout, kh, kw, stride, pad, _ptr(a_range), int(a_bits), _ptr(row_min), _ptr(row_max),
          int(w_bits), _ptr(tapsum), _ptr(bias), _ptr(ws), ws.numel(), _stream())
     return out

@@ -527,7 +527,7 @@ class _QBase(QuantNode):
 # Route QConv2d / QLinear through the int8 tcgen05 kernels whenever the geometry is supported (conv_i8.cu,
 # gemm_i8.cu); otherwise the contraction of the already fake-quantized tensors goes to cuDNN / cuBLAS.
 USE_INT8_TENSOR_CORES = True
-USE_DP4A_FIRST_LAYER = True
+USE_STEM_KERNEL = True
 
 
 def _conv_i8_supported(mod, x):
@@ -541,14 +541,15 @@ def _conv_i8_supported(mod, x):
         return False
     if kh * kw <= 9 and mod.in_channels % 32 == 0 and mod.out_channels % 16 == 0:
         return True
-    return _conv_dp4a_supported(mod)
+    return _conv_stem_supported(mod, x)
 
 
-def _conv_dp4a_supported(mod):
-    """First-layer geometry (3 input channels): direct DP4A convolution (conv_dp4a.cu)."""
+def _conv_stem_supported(mod, x):
+    """First-layer geometry (3 input channels): tcgen05 over a thread-built im2col operand (conv_stem.cu)."""
     kh, kw = mod.kernel_size
-    return (USE_DP4A_FIRST_LAYER and mod.in_channels % 32 != 0
-            and _abi.conv_dp4a_supported(mod.in_channels, mod.out_channels, kh, kw, _pair(mod.stride)[0]))
+    return (USE_STEM_KERNEL and mod.in_channels % 32 != 0
+            and _abi.conv_stem_supported(x.shape[2], x.shape[3], mod.in_channels, mod.out_channels, kh, kw,
+                                         _pair(mod.stride)[0], _pair(mod.padding)[0]))
 
 
 def _linear_i8_supported(mod, x):
@@ -576,8 +577,8 @@ class _QTensorCoreFn(Function):
         if conv:
             B, Cin, H, W = x.shape
             kh, kw = mod.kernel_size
-            if Cin % 32 != 0:                                               # first layer: direct DP4A convolution
-                out = _abi.conv_dp4a_fwd(codes, wcodes, B, H, W, Cin, mod.out_channels, kh, kw, _pair(mod.stride)[0],
+            if Cin % 32 != 0:                                               # first layer: thread-built im2col operand
+                out = _abi.conv_stem_fwd(codes, wcodes, B, H, W, Cin, mod.out_channels, kh, kw, _pair(mod.stride)[0],
                                          _pair(mod.padding)[0], rng, bits_a, mod.weight_min, mod.weight_max, bits_w, tapsum,
                                          bias=qbias)
             else:

@@ -79,7 +79,7 @@ def test_conv_i8_unsupported_is_an_error(lib):
         lib.conv_i8_fwd(x, x, 1, 8, 8, 3, 64, 3, 3, 1, 1, z, 8, z, z, 8, zi, zi)
 
 
-DP4A_CASES = [  # B, Cin, H, W, Cout, k, stride, pad
+STEM_CASES = [  # B, Cin, H, W, Cout, k, stride, pad
     (3, 3, 224, 224, 64, 7, 2, 3),       # ResNet conv1
     (2, 3, 61, 45, 64, 7, 2, 3),         # ragged tiles, odd sizes
     (2, 3, 32, 32, 64, 7, 1, 3),         # stride 1 (cifar-style stem with a 7x7)
@@ -90,13 +90,13 @@ DP4A_CASES = [  # B, Cin, H, W, Cout, k, stride, pad
 ]
 
 
-@pytest.mark.parametrize("case", DP4A_CASES)
+@pytest.mark.parametrize("case", STEM_CASES)
 @pytest.mark.parametrize("use_bias", [False, True])
-def test_conv_dp4a_fwd(lib, case, use_bias):
-    """First-layer direct convolution (qb_conv_dp4a_fwd): image-like input (both signs, so the zero-padding terms are
+def test_conv_stem_fwd(lib, case, use_bias):
+    """First-layer convolution (qb_conv_stem_fwd, tcgen05 over a thread-built im2col operand): image-like input (both signs, so the zero-padding terms are
     live) against fp64 and the reference's fp32 F.conv2d on the same fake-quantized tensors."""
     B, Cin, H, W, Cout, k, stride, pad = case
-    assert lib.conv_dp4a_supported(Cin, Cout, k, k, stride)
+    assert lib.conv_stem_supported(H, W, Cin, Cout, k, k, stride, pad)
     gen = torch.Generator().manual_seed(sum(case))
     x = torch.randn(B, Cin, H, W, generator=gen) * 1.1 + 0.3
     w = torch.randn(Cout, Cin, k, k, generator=gen) * 0.08
@@ -108,7 +108,7 @@ def test_conv_dp4a_fwd(lib, case, use_bias):
     xq = lib.fakequant_affine(xd, 8, range_dev=rng, codes=codes)
     rmin, rmax = torch.empty(Cout, device=DEV), torch.empty(Cout, device=DEV)
     wq, wcodes, tapsum = lib.fakequant_rows_conv(w.to(DEV), 8, rmin, rmax)
-    out = lib.conv_dp4a_fwd(codes, wcodes, B, H, W, Cin, Cout, k, k, stride, pad, rng, 8, rmin, rmax, 8, tapsum,
+    out = lib.conv_stem_fwd(codes, wcodes, B, H, W, Cin, Cout, k, k, stride, pad, rng, 8, rmin, rmax, 8, tapsum,
                             bias=bias.to(DEV) if use_bias else None)
     torch.cuda.synchronize()
     assert out.is_contiguous(memory_format=torch.channels_last)
@@ -117,23 +117,24 @@ def test_conv_dp4a_fwd(lib, case, use_bias):
     err = (out.cpu().double() - ref64)
     rel = float(err.norm() / ref64.norm())
     assert rel < 2e-5, rel
-    # borders are as accurate as the interior (the prefix-table correction, not an approximation)
+    # borders are as accurate as the interior (per-border-case constants, not an approximation)
     assert float(err.abs().max()) < 2e-5 * float(ref64.abs().max()) * 10
     ref32 = F.conv2d(xq.cpu(), wq.cpu(), bias, stride, pad)
     assert float((out.cpu() - ref32).norm() / ref32.norm()) < 1e-4
 
 
-def test_conv_dp4a_unsupported_is_an_error(lib):
-    assert not lib.conv_dp4a_supported(16, 64, 3, 3, 1)
-    assert not lib.conv_dp4a_supported(3, 256, 7, 7, 2)
+def test_conv_stem_unsupported_is_an_error(lib):
+    assert not lib.conv_stem_supported(8, 8, 16, 64, 3, 3, 1, 1)
+    assert not lib.conv_stem_supported(224, 224, 3, 256, 7, 7, 2, 3)
+    assert not lib.conv_stem_supported(224, 224, 3, 24, 7, 7, 2, 3)          # Cout % 16
     x = torch.zeros((1, 16, 8, 8), dtype=torch.uint8, device=DEV)
     z = torch.zeros(64, device=DEV)
     zi = torch.zeros(64 * 9, dtype=torch.int32, device=DEV)
     with pytest.raises(lib.QB200Error):
-        lib.conv_dp4a_fwd(x, x, 1, 8, 8, 16, 64, 3, 3, 1, 1, z, 8, z, z, 8, zi)
+        lib.conv_stem_fwd(x, x, 1, 8, 8, 16, 64, 3, 3, 1, 1, z, 8, z, z, 8, zi)
 
 
-def test_qconv2d_first_layer_uses_dp4a(lib):
+def test_qconv2d_first_layer_uses_stem_kernel(lib):
     """QConv2d(3, 64, 7, 2, 3) routes to the native kernel and matches the cuDNN route on the same weights."""
     import qtorch_b200  # noqa: F401
     from qtorch_b200 import quantize as Q
@@ -147,15 +148,15 @@ def test_qconv2d_first_layer_uses_dp4a(lib):
     y1.square().mean().backward()
     g1 = m.weight.grad.clone()
     assert lib.LAUNCHES > before
-    assert "qb_conv_dp4a_fwd" in names, names
+    assert "qb_conv_stem_fwd" in names, names
     m.weight.grad = None
     m2 = Q.QConv2d(3, 64, 7, 2, 3, bias=False, num_bits=8, num_bits_weight=8, num_bits_grad=None).to(DEV)
     m2.load_state_dict(m.state_dict())
-    Q.USE_DP4A_FIRST_LAYER = False
+    Q.USE_STEM_KERNEL = False
     try:
         y2 = m2(x)
         y2.square().mean().backward()
     finally:
-        Q.USE_DP4A_FIRST_LAYER = True
+        Q.USE_STEM_KERNEL = True
     assert float((y1 - y2).detach().norm() / y2.detach().norm()) < 1e-4
     assert float((g1 - m2.weight.grad).norm() / m2.weight.grad.norm()) < 1e-3

@@ -1,4 +1,4 @@
-"""qb_conv_dp4a_fwd on the ResNet-18 stem (256x3x224x224, 7x7/2 -> 64) and the MobileNet stem (3x3/2 -> 32): median time
+"""qb_conv_stem_fwd on the ResNet-18 stem (256x3x224x224, 7x7/2 -> 64) and the MobileNet stem (3x3/2 -> 32): median time
 with L2 flushed, against cuDNN's F.conv2d on the same fake-quantized channels-last tensors and the output-write floor."""
 import os
 import sys
@@ -25,13 +25,13 @@ def main():
         rmin, rmax = torch.empty(Cout, device=dev), torch.empty(Cout, device=dev)
         wq, wcodes, tapsum = _abi.fakequant_rows_conv(w, 8, rmin, rmax)
         wq_cl = wq.contiguous(memory_format=torch.channels_last)
-        t = timeit(lambda: _abi.conv_dp4a_fwd(codes, wcodes, B, 224, 224, 3, Cout, k, k, stride, pad, rng, 8, rmin, rmax, 8, tapsum),
+        t = timeit(lambda: _abi.conv_stem_fwd(codes, wcodes, B, 224, 224, 3, Cout, k, k, stride, pad, rng, 8, rmin, rmax, 8, tapsum),
                    flush)
         t_ref = timeit(lambda: F.conv2d(xq, wq_cl, None, stride, pad), flush)
         Ho = (224 + 2 * pad - k) // stride + 1
         bytes_ = B * 224 * 224 * 3 + 4 * B * Ho * Ho * Cout
         ops = 2 * B * Ho * Ho * Cout * k * k * 3
-        print("%-28s dp4a %.3f ms (%.1f TOP/s, %.0f GB/s of %.0f)   cuDNN fp32 %.3f ms   floor %.3f ms" %
+        print("%-28s stem %.3f ms (%.1f TOP/s, %.0f GB/s of %.0f)   cuDNN fp32 %.3f ms   floor %.3f ms" %
               (name, t, ops / t / 1e9, bytes_ / t / 1e6, HBM_GBS, t_ref, bytes_ / HBM_GBS / 1e6))
 
 
