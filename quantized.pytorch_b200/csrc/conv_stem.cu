@@ -11,12 +11,13 @@
 //   * CTA = 128 threads = 128 output pixels (4 rows x 32) = the 128 rows of the MMA = the 128 TMEM lanes.  Each thread
 //     re-aligns the KH x WPR words of ITS pixel from the shared-memory input patch (funnel shifts), takes the code sum
 //     SUM_V qa with DP4A on the way, and writes its A row in the 128-byte swizzled K-major layout; one thread then issues
-//     <= 6 tcgen05.mma (M=128, N=Cout, K=32) against the resident, pre-swizzled weight operand
-//   * the same thread reads ITS accumulator row back (tcgen05.ld 32x32b), applies the dequantising epilogue and writes
-//     16-byte stores.  The zero-padding terms depend only on which filter rows / columns are in bounds: the host lists
+//     <= 6 tcgen05.mma (M=128, N=Cout, K=32) against the resident, pre-swizzled weight operand; the next tile's
+//     input patch is fetched into registers meanwhile
+//   * the same thread reads ITS accumulator row back (tcgen05.ld 32x32b), applies the dequantising epilogue and stages
+//     it for a TMA store (32-channel slabs, alternating between the A rows and a second buffer).  The zero-padding terms depend only on which filter rows / columns are in bounds: the host lists
 //     the <= 8 x 8 distinct cases, k_stem_prep tabulates R[case][n] = la*sw*SUM_V qc + la*lw'*|V|*Cin + bias, and the
 //     epilogue is two FMAs per output for interior and border pixels alike
-//   * no intra-CTA pipelining: 3-4 CTAs per SM overlap each other's phases
+//   * otherwise no intra-CTA pipelining: 4 CTAs per SM (45 KB each) overlap each other's phases
 // History (256x3x224x224 -> 64 channels): cuDNN fp32 1.32 ms (+ layout conversions in the step); direct DP4A convolution,
 // weights broadcast from shared memory 1.46 ms (LSU bound), 2 pixels per thread 0.93 ms (IDP.4A runs on the half-rate
 // fmaheavy pipe: 8.6 G lane-ops is a 0.54 ms floor); this kernel: see profiles/.
@@ -26,6 +27,7 @@ constexpr int CS_THREADS = 128;
 constexpr int CS_TW = 32, CS_TH = 4;
 constexpr int CS_MAX_COUT = 128, CS_MAX_CLS = 8;
 constexpr uint32_t CS_TMEM_COLS = 128;
+constexpr int CS_SLAB_BYTES = 128 * 128;                 // one staged output slab: 128 pixels x 32 fp32 channels
 
 struct StemCls {                 // distinct in-bounds tap ranges [a, b) along one axis
     int n;
@@ -47,13 +49,27 @@ struct StemEpi {
     const float* bias;
 };
 
-// workspace = what every CTA stages: [ B operand, swizzled: katoms x Cout x 128 B | cf: float2[Cout] | R: float[nh*nw][Cout] ]
+// Operand rows are K-major: bytes [0,128) of every row in a 128-byte-swizzled atom (rows x 128 B), bytes [128,192) - only
+// the 7x7 filter needs them - in a 64-byte-swizzled atom behind it (rows x 64 B), so a 192-byte row costs 192 bytes.
+__host__ __device__ inline size_t stem_operand_bytes(int rows, int katoms) { return (size_t)rows * (katoms == 2 ? 192 : 128); }
+// workspace = what every CTA stages: [ B operand, swizzled | cf: float2[Cout] | R: float[nh*nw][Cout] ]
 __host__ __device__ inline size_t stem_ws_bytes(int Cout, int katoms, int ncls) {
-    return (size_t)katoms * Cout * 128 + (size_t)Cout * 8 + (size_t)ncls * Cout * 4;
+    return stem_operand_bytes(Cout, katoms) + (size_t)Cout * 8 + (size_t)ncls * Cout * 4;
 }
-__host__ __device__ inline uint32_t stem_swz(uint32_t row, uint32_t kbyte, uint32_t rows_per_atom) {   // byte offset of (row, k)
-    const uint32_t atom = kbyte >> 7, kk = kbyte & 127u;
-    return atom * rows_per_atom * 128u + row * 128u + ((((kk >> 4) ^ (row & 7u)) << 4) | (kk & 15u));
+__host__ __device__ inline uint32_t stem_swz(uint32_t row, uint32_t kbyte, uint32_t rows) {   // byte offset of (row, k)
+    if (kbyte < 128u) return row * 128u + ((((kbyte >> 4) ^ (row & 7u)) << 4) | (kbyte & 15u));
+    const uint32_t kk = kbyte - 128u;
+    return rows * 128u + row * 64u + ((((kk >> 4) ^ ((row >> 1) & 3u)) << 4) | (kk & 15u));
+}
+// K-major shared-memory descriptor with the 128- or 64-byte swizzle: 8-row groups are 8 rows apart
+__device__ __forceinline__ uint64_t stem_desc(uint32_t smem_addr, uint32_t row_bytes) {
+    uint64_t d = 0;
+    d |= (uint64_t)((smem_addr & 0x3FFFF) >> 4);
+    d |= (uint64_t)1 << 16;
+    d |= (uint64_t)((8u * row_bytes) >> 4) << 32;
+    d |= (uint64_t)1 << 46;
+    d |= (uint64_t)(row_bytes == 128u ? 2 : 4) << 61;
+    return d;
 }
 
 __device__ __forceinline__ int dp4a_uu(uint32_t a, uint32_t b, int c) {
@@ -65,7 +81,7 @@ __device__ __forceinline__ int dp4a_uu(uint32_t a, uint32_t b, int c) {
 __global__ void __launch_bounds__(256) k_stem_prep(unsigned char* ws, const int8_t* __restrict__ w, StemGeom g, StemEpi ep, int WPR) {
     const int tid = threadIdx.x, KH = g.kh;
     const int row_bytes = g.kw * g.Cin, taps = KH * g.kw;
-    const size_t b_bytes = (size_t)g.katoms * g.Cout * 128;
+    const size_t b_bytes = stem_operand_bytes(g.Cout, g.katoms);
     float2* cf = reinterpret_cast<float2*>(ws + b_bytes);
     float* R = reinterpret_cast<float*>(ws + b_bytes + (size_t)g.Cout * 8);
     for (size_t i = tid; i < b_bytes / 4; i += 256) reinterpret_cast<uint32_t*>(ws)[i] = 0u;
@@ -99,16 +115,18 @@ __global__ void __launch_bounds__(256) k_stem_prep(unsigned char* ws, const int8
 }
 
 template <int KH, int WPR>      // filter rows, 32-bit words per filter row
-__global__ void __launch_bounds__(CS_THREADS, 3)
-k_conv_stem(const uint8_t* __restrict__ x, float* __restrict__ out, const unsigned char* __restrict__ ws, StemGeom g) {
+__global__ void __launch_bounds__(CS_THREADS, 4)
+k_conv_stem(const __grid_constant__ CUtensorMap tmap_o, const uint8_t* __restrict__ x, const unsigned char* __restrict__ ws,
+            StemGeom g) {
     extern __shared__ unsigned char smem_raw[];
-    unsigned char* smem = reinterpret_cast<unsigned char*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+    unsigned char* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);   // pointer arithmetic keeps the address space
     const int ncls = g.ch.n * g.cw.n;
-    const size_t a_bytes = (size_t)g.katoms * 128 * 128;
-    const size_t b_bytes = (size_t)g.katoms * g.Cout * 128;                  // multiple of 1024 (Cout % 16 == 0)
+    const size_t a_bytes = stem_operand_bytes(128, g.katoms);               // multiples of 1024 (Cout % 16 == 0)
+    const size_t b_bytes = stem_operand_bytes(g.Cout, g.katoms);
     const size_t wsb = stem_ws_bytes(g.Cout, g.katoms, ncls);
     unsigned char* s_A = smem;
-    unsigned char* s_B = smem + a_bytes;                                     // staged workspace starts here
+    unsigned char* s_O = smem + a_bytes;                                     // second output staging slab (the first is s_A)
+    unsigned char* s_B = s_O + CS_SLAB_BYTES;                                // staged workspace starts here
     const float2* s_cf = reinterpret_cast<const float2*>(s_B + b_bytes);
     const float* s_R = reinterpret_cast<const float*>(s_B + b_bytes + (size_t)g.Cout * 8);
     unsigned char* s_in = s_B + ((wsb + 15) & ~(size_t)15);
@@ -123,7 +141,10 @@ k_conv_stem(const uint8_t* __restrict__ x, float* __restrict__ out, const unsign
         mbar_init(bar, 1);
         fence_barrier_init();
     }
-    if (warp == 0) tmem_alloc<CS_TMEM_COLS>(tmem_slot);
+    if (warp == 0) {
+        if (g.Cout <= 64) tmem_alloc<64>(tmem_slot);
+        else tmem_alloc<CS_TMEM_COLS>(tmem_slot);
+    }
     fence_proxy_async();
     tc_fence_before_sync();
     __syncthreads();
@@ -138,6 +159,37 @@ k_conv_stem(const uint8_t* __restrict__ x, float* __restrict__ out, const unsign
     const int total = g.B * g.tiles_h * g.tiles_w;
     const uint32_t last_mask = (row_bytes & 3) ? ((1u << (8 * (row_bytes & 3))) - 1u) : 0xffffffffu;
     uint32_t phase = 0;
+    // chunk i (16 bytes) of the input patch of tile t: row r holds the image bytes from the 16-byte aligned address at or
+    // below its first needed byte; zero outside the image
+    auto load_chunk = [&](int t, int i) -> uint4 {
+        uint4 v = make_uint4(0u, 0u, 0u, 0u);
+        if (t >= total || i >= g.rows_in * chunks) return v;
+        uint32_t q = fdiv((uint32_t)t, g.d_tw);
+        const int twi = t - (int)q * g.tiles_w;
+        const uint32_t b = fdiv(q, g.d_th);
+        const int thi = (int)q - (int)b * g.tiles_h;
+        const int r = (int)fdiv((uint32_t)i, g.d_chunks), c = i - r * chunks;
+        const int h = thi * CS_TH * g.stride - g.pad + r;
+        const long long row_addr = (long long)reinterpret_cast<uintptr_t>(x) + ((long long)b * g.H + h) * row_len;
+        const long long first = row_addr + (long long)(twi * CS_TW * g.stride - g.pad) * g.Cin;
+        const long long a0 = (first & ~15LL) + 16LL * c;                           // global address of this chunk
+        if (h >= 0 && h < g.H) {
+            if (a0 >= row_addr && a0 + 16 <= row_addr + row_len) {
+                v = __ldg(reinterpret_cast<const uint4*>(a0));
+            } else if (a0 + 16 > row_addr && a0 < row_addr + row_len) {            // straddles an image edge
+                uint32_t wd[4] = {0u, 0u, 0u, 0u};
+                for (int bt = 0; bt < 16; ++bt) {
+                    const long long a = a0 + bt;
+                    if (a >= row_addr && a < row_addr + row_len)
+                        wd[bt >> 2] |= (uint32_t)__ldg(reinterpret_cast<const uint8_t*>(a)) << (8 * (bt & 3));
+                }
+                v = make_uint4(wd[0], wd[1], wd[2], wd[3]);
+            }
+        }
+        return v;
+    };
+    // the patch of the NEXT tile is fetched into registers while the current tile's MMA and epilogue run
+    uint4 pre0 = load_chunk((int)blockIdx.x, tid), pre1 = load_chunk((int)blockIdx.x, tid + CS_THREADS);
     for (int t = blockIdx.x; t < total; t += gridDim.x) {
         uint32_t q = fdiv((uint32_t)t, g.d_tw);
         const int twi = t - (int)q * g.tiles_w;
@@ -145,30 +197,8 @@ k_conv_stem(const uint8_t* __restrict__ x, float* __restrict__ out, const unsign
         const int thi = (int)q - (int)b * g.tiles_h;
         const int ho0 = thi * CS_TH, wo0 = twi * CS_TW;
         const int h_start = ho0 * g.stride - g.pad, w_start = wo0 * g.stride - g.pad;
-        // ---- input patch -> shared memory: row r holds the image bytes from the 16-byte aligned address at or below its
-        //      first needed byte; zero outside the image ----
-        for (int i = tid; i < g.rows_in * chunks; i += CS_THREADS) {
-            const int r = (int)fdiv((uint32_t)i, g.d_chunks), c = i - r * chunks;
-            const int h = h_start + r;
-            const long long row_addr = (long long)reinterpret_cast<uintptr_t>(x) + ((long long)b * g.H + h) * row_len;
-            const long long first = row_addr + (long long)w_start * g.Cin;
-            const long long a0 = (first & ~15LL) + 16LL * c;                       // global address of this chunk
-            uint4 v = make_uint4(0u, 0u, 0u, 0u);
-            if (h >= 0 && h < g.H) {
-                if (a0 >= row_addr && a0 + 16 <= row_addr + row_len) {
-                    v = __ldg(reinterpret_cast<const uint4*>(a0));
-                } else if (a0 + 16 > row_addr && a0 < row_addr + row_len) {        // straddles an image edge
-                    uint32_t wd[4] = {0u, 0u, 0u, 0u};
-                    for (int bt = 0; bt < 16; ++bt) {
-                        const long long a = a0 + bt;
-                        if (a >= row_addr && a < row_addr + row_len)
-                            wd[bt >> 2] |= (uint32_t)__ldg(reinterpret_cast<const uint8_t*>(a)) << (8 * (bt & 3));
-                    }
-                    v = make_uint4(wd[0], wd[1], wd[2], wd[3]);
-                }
-            }
-            *reinterpret_cast<uint4*>(s_in + (size_t)r * g.pitch_in + 16 * c) = v;
-        }
+        if (tid < g.rows_in * chunks) *reinterpret_cast<uint4*>(s_in + (size_t)tid * 16) = pre0;          // chunk i sits at byte 16*i
+        if (tid + CS_THREADS < g.rows_in * chunks) *reinterpret_cast<uint4*>(s_in + (size_t)(tid + CS_THREADS) * 16) = pre1;
         __syncthreads();
         // ---- this thread's A row: KH x WPR words re-aligned from the byte offset of its pixel; code sum on the way ----
         int s_a = 0;
@@ -199,6 +229,8 @@ k_conv_stem(const uint8_t* __restrict__ x, float* __restrict__ out, const unsign
                 *reinterpret_cast<uint4*>(s_A + stem_swz((uint32_t)tid, (uint32_t)c * 16u, 128u)) =
                     make_uint4(p[4 * c], p[4 * c + 1], p[4 * c + 2], p[4 * c + 3]);
         }
+        pre0 = load_chunk(t + (int)gridDim.x, tid);
+        pre1 = load_chunk(t + (int)gridDim.x, tid + CS_THREADS);
         fence_proxy_async();                                  // generic-proxy writes of A -> visible to the tensor core
         tc_fence_before_sync();
         __syncthreads();
@@ -207,7 +239,8 @@ k_conv_stem(const uint8_t* __restrict__ x, float* __restrict__ out, const unsign
             for (int k = 0; k < g.ksteps; ++k) {
                 const uint32_t off_a = (uint32_t)(k >> 2) * 128u * 128u + (uint32_t)(k & 3) * 32u;
                 const uint32_t off_b = (uint32_t)(k >> 2) * (uint32_t)g.Cout * 128u + (uint32_t)(k & 3) * 32u;
-                umma_i8(tmem, umma_smem_desc_sw128(a_u32 + off_a), umma_smem_desc_sw128(b_u32 + off_b), idesc, k > 0 ? 1u : 0u);
+                const uint32_t rb = k < 4 ? 128u : 64u;       // K steps 4, 5 live in the 64-byte-swizzled atom
+                umma_i8(tmem, stem_desc(a_u32 + off_a, rb), stem_desc(b_u32 + off_b, rb), idesc, k > 0 ? 1u : 0u);
             }
             umma_commit(bar);
         }
@@ -228,7 +261,6 @@ k_conv_stem(const uint8_t* __restrict__ x, float* __restrict__ out, const unsign
             cls = ih * g.cw.n + iw;
         }
         const float* Rrow = s_R + (size_t)cls * g.Cout;
-        float* optr = out + (((size_t)b * g.Ho + ho) * g.Wo + wo) * g.Cout;
         const float fs_a = (float)s_a;
         {   // bounded wait: a lost MMA completion must not hang the GPU
             uint32_t spins = 0;
@@ -238,31 +270,57 @@ k_conv_stem(const uint8_t* __restrict__ x, float* __restrict__ out, const unsign
             phase ^= 1u;
         }
         tc_fence_after_sync();
-        for (int c0 = 0; c0 < g.Cout; c0 += 32) {
+        // ---- epilogue: slabs of 32 channels, staged in the 128-byte-swizzled layout of the output tensor map and written
+        //      by TMA (a thread's own stores would touch 32 different lines per instruction).  Slabs alternate between
+        //      the A rows (free once the MMA has completed) and s_O; ragged tiles are clipped by the TMA unit ----
+        const uint32_t sw = (uint32_t)tid & 7u;
+        const int nslab = (g.Cout + 31) >> 5;
+        for (int sl = 0; sl < nslab; ++sl) {
+            const int c0 = sl * 32;
             uint32_t acc[32];
             tmem_ld_32x32(tmem + ((uint32_t)(warp * 32) << 16) + (uint32_t)c0, acc);
             tmem_ld_wait();
-            if (valid) {
 #pragma unroll
-                for (int u = 0; u < 32; u += 4) {
-                    const float4 cfa = *reinterpret_cast<const float4*>(s_cf + c0 + u);
-                    const float4 cfb = *reinterpret_cast<const float4*>(s_cf + c0 + u + 2);
-                    const float4 rr = *reinterpret_cast<const float4*>(Rrow + c0 + u);
-                    float4 o;
-                    o.x = fmaf(cfa.x, (float)(int)acc[u], fmaf(cfa.y, fs_a, rr.x));
-                    o.y = fmaf(cfa.z, (float)(int)acc[u + 1], fmaf(cfa.w, fs_a, rr.y));
-                    o.z = fmaf(cfb.x, (float)(int)acc[u + 2], fmaf(cfb.y, fs_a, rr.z));
-                    o.w = fmaf(cfb.z, (float)(int)acc[u + 3], fmaf(cfb.w, fs_a, rr.w));
-                    if (c0 + u < g.Cout) *reinterpret_cast<float4*>(optr + c0 + u) = o;
-                }
+            for (int u = 0; u < 32; u += 4) {
+                const float4 cfa = *reinterpret_cast<const float4*>(s_cf + c0 + u);
+                const float4 cfb = *reinterpret_cast<const float4*>(s_cf + c0 + u + 2);
+                const float4 rr = *reinterpret_cast<const float4*>(Rrow + c0 + u);
+                acc[u] = __float_as_uint(fmaf(cfa.x, (float)(int)acc[u], fmaf(cfa.y, fs_a, rr.x)));
+                acc[u + 1] = __float_as_uint(fmaf(cfa.z, (float)(int)acc[u + 1], fmaf(cfa.w, fs_a, rr.y)));
+                acc[u + 2] = __float_as_uint(fmaf(cfb.x, (float)(int)acc[u + 2], fmaf(cfb.y, fs_a, rr.z)));
+                acc[u + 3] = __float_as_uint(fmaf(cfb.z, (float)(int)acc[u + 3], fmaf(cfb.w, fs_a, rr.w)));
             }
+            if (sl >= 1) {                                    // the buffer's previous store (two slabs ago) has been read
+                if (tid == 0) tma_store_wait_read<1>();
+                __syncthreads();
+            }
+            unsigned char* buf = (sl & 1) ? s_O : s_A;
+            const uint32_t dst = smem_u32(buf) + (uint32_t)tid * 128u;
+#pragma unroll
+            for (int q4 = 0; q4 < 8; ++q4)
+                asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(dst + (((uint32_t)q4 ^ sw) << 4)), "r"(acc[4 * q4]),
+                             "r"(acc[4 * q4 + 1]), "r"(acc[4 * q4 + 2]), "r"(acc[4 * q4 + 3]) : "memory");
+            fence_proxy_async();
+            __syncthreads();
+            if (tid == 0) {
+                tma_store_4d(&tmap_o, buf, c0, wo0, ho0, (int)b);
+                tma_store_commit();
+            }
+        }
+        if (tid == 0) {                                       // the A rows are rewritten by the next tile
+            if (nslab & 1) tma_store_wait_read<0>();
+            else tma_store_wait_read<1>();
         }
         tc_fence_before_sync();                               // accumulator reads done before the next tile's MMA
         __syncthreads();                                      // ... and the patch / A rows are free again
     }
+    if (tid == 0) tma_store_wait<0>();
     tc_fence_before_sync();
     __syncthreads();
-    if (warp == 0) tmem_dealloc<CS_TMEM_COLS>(tmem);
+    if (warp == 0) {
+        if (g.Cout <= 64) tmem_dealloc<64>(tmem);
+        else tmem_dealloc<CS_TMEM_COLS>(tmem);
+    }
 }
 
 // distinct in-bounds ranges [a, b) of a k-wide window over n_out positions of an n_in-long axis; class 0 = interior
@@ -305,6 +363,7 @@ static bool stem_geom(StemGeom& g, int64_t B, int64_t H, int64_t W, int64_t Cin,
     g.d_tw = make_fastdiv((uint32_t)g.tiles_w);
     g.d_th = make_fastdiv((uint32_t)g.tiles_h);
     g.d_chunks = make_fastdiv((uint32_t)(g.pitch_in >> 4));
+    if (g.rows_in * (g.pitch_in >> 4) > 2 * CS_THREADS) return false;            // two prefetch registers per thread
     return stem_classes(g.ch, g.H, g.Ho, kh, stride, pad) && stem_classes(g.cw, g.W, g.Wo, kw, stride, pad);
 }
 
@@ -320,7 +379,7 @@ extern "C" size_t qb_conv_stem_ws_bytes(int64_t Cout) {
 template <int KH, int WPR>
 static int stem_launch(const uint8_t* x, float* out, const unsigned char* ws, const StemGeom& g, cudaStream_t st) {
     const size_t wsb = stem_ws_bytes(g.Cout, g.katoms, g.ch.n * g.cw.n);
-    const size_t smem = 1024 + (size_t)g.katoms * 128 * 128 + ((wsb + 15) & ~(size_t)15) +
+    const size_t smem = 1024 + stem_operand_bytes(128, g.katoms) + CS_SLAB_BYTES + ((wsb + 15) & ~(size_t)15) +
                         (((size_t)g.rows_in * g.pitch_in + 15) & ~(size_t)15) + 16;
     if (smem > 200 * 1024) {
         qb_set_error("qb_conv_stem_fwd: %zu bytes of shared memory needed", smem);
@@ -329,12 +388,20 @@ static int stem_launch(const uint8_t* x, float* out, const unsigned char* ws, co
     int sms = qb_sm_count();
     if (sms <= 0) sms = 148;
     int per_sm = (int)((size_t)220 * 1024 / smem);
-    if (per_sm > 4) per_sm = 4;                               // 4 x 128 TMEM columns
+    if (per_sm > 4) per_sm = 4;                               // registers (and 4 x 128 TMEM columns)
     if (per_sm < 1) per_sm = 1;
     const int64_t total = (int64_t)g.B * g.tiles_h * g.tiles_w;
     const unsigned grid = (unsigned)(total < (int64_t)per_sm * sms ? total : (int64_t)per_sm * sms);
+    CUtensorMap to;
+    {   // output fp32 NHWC: dims {Cout, Wo, Ho, B}; one staged slab = 32 channels x the tile's 4 x 32 pixels
+        const uint64_t dims[4] = {(uint64_t)g.Cout, (uint64_t)g.Wo, (uint64_t)g.Ho, (uint64_t)g.B};
+        const uint64_t str[3] = {(uint64_t)g.Cout * 4, (uint64_t)g.Wo * g.Cout * 4, (uint64_t)g.Ho * g.Wo * g.Cout * 4};
+        const uint32_t box[4] = {32u, (uint32_t)CS_TW, (uint32_t)CS_TH, 1u};
+        int rc = qb_make_tmap(&to, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, out, dims, str, box, nullptr, 128);
+        if (rc) return rc;
+    }
     QB_CUDA(cudaFuncSetAttribute(k_conv_stem<KH, WPR>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    k_conv_stem<KH, WPR><<<grid, CS_THREADS, smem, st>>>(x, out, ws, g);
+    k_conv_stem<KH, WPR><<<grid, CS_THREADS, smem, st>>>(to, x, ws, g);
     QB_LAUNCH_CHECK();
     return QB_OK;
 }
