@@ -262,6 +262,16 @@ int qb_conv_stem_fwd(const uint8_t* x_codes, const int8_t* w_codes_khwc, float* 
                      const float* w_row_min, const float* w_row_max, int w_bits, const int32_t* tapsum,
                      const float* bias, void* ws, size_t ws_bytes, void* stream);
 
+/* Weight gradient of that first layer (quantize.py:143-148: the weight branch of the bi-precision backward sees the
+ * unquantized gradient): dW = x_hat^T * g over all output pixels, from the input CODES (x_hat = sa*q + la inside the
+ * image, 0 in the padding) and the fp32 NHWC gradient, on tf32 tensor cores (g rounded to tf32, codes exact),
+ * accumulated per CTA in TMEM and reduced in a fixed order.  C_out 32 or 64.  dw fp32 [C_out][C_in][kh][kw].
+ * ws: qb_conv_stem_wgrad_ws_bytes() bytes, 16-byte aligned.                                                           */
+size_t qb_conv_stem_wgrad_ws_bytes(int64_t Cout, int64_t Cin, int kh, int kw);
+int qb_conv_stem_wgrad(const float* grad_out, const uint8_t* x_codes, float* dw, int64_t B, int64_t H, int64_t W,
+                       int64_t Cin, int64_t Cout, int kh, int kw, int stride, int pad, const float* a_range, int a_bits,
+                       void* ws, size_t ws_bytes, void* stream);
+
 /* ---------------------------------------------------------------------------------------------------
  * quantize2.py flavour: QParams (range, zero_point) are device tensors, one per tensor or one per
  * row of dim 0; no 1e-8 floor on the scale; optional signed codes, optional raw-code output, stochastic rounding on

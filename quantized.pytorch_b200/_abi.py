@@ -65,6 +65,8 @@ PROTOTYPES = {
     "qb_maxpool2d_nhwc_bwd": (_i32, [_p, _p, _p, _i64, _i64, _i64, _i64, _i32, _i32, _i32, _p]),
     "qb_conv_stem_supported": (_i32, [_i64, _i64, _i64, _i64, _i32, _i32, _i32, _i32]),
     "qb_conv_stem_ws_bytes": (_sz, [_i64]),
+    "qb_conv_stem_wgrad_ws_bytes": (_sz, [_i64, _i64, _i32, _i32]),
+    "qb_conv_stem_wgrad": (_i32, [_p, _p, _p, _i64, _i64, _i64, _i64, _i64, _i32, _i32, _i32, _i32, _p, _i32, _p, _sz, _p]),
     "qb_conv_stem_fwd": (_i32, [_p, _p, _p, _i64, _i64, _i64, _i64, _i64, _i32, _i32, _i32, _i32, _p, _i32, _p, _p, _i32,
                                 _p, _p, _p, _sz, _p]),
     "qb_conv_i8_fwd": (_i32, [_p, _p, _p, _i64, _i64, _i64, _i64, _i64, _i32, _i32, _i32, _i32, _p, _i32, _p, _p, _i32,
@@ -107,7 +109,7 @@ _profile = None       # list of (name, algorithmic_bytes, start_event, end_event
 
 # kernels enqueued per C call
 _NLAUNCH = {"qb_rangebn_stats": 2, "qb_rangebn_bwd_reduce": 2, "qb_rangebn_bwd_apply": 2,
-            "qb_conv_i8_fwd": 2, "qb_conv_stem_fwd": 2, "qb_rangebn_stats_nhwc": 3, "qb_rangebn_bwd_reduce_nhwc": 2, "qb_rangebn_bwd_apply_nhwc": 2}
+            "qb_conv_i8_fwd": 2, "qb_conv_stem_fwd": 2, "qb_conv_stem_wgrad": 2, "qb_rangebn_stats_nhwc": 3, "qb_rangebn_bwd_reduce_nhwc": 2, "qb_rangebn_bwd_apply_nhwc": 2}
 
 
 _next_ops = 0          # integer operations (2*M*N*K) of the next tensor-core call, set by the conv / GEMM wrappers
@@ -509,6 +511,21 @@ def conv_stem_fwd(x_codes, w_codes, B, H, W, Cin, Cout, kh, kw, stride, pad, a_r
          _ptr(out), B, H, W, Cin, Cout, kh, kw, stride, pad, _ptr(a_range), int(a_bits), _ptr(row_min), _ptr(row_max),
          int(w_bits), _ptr(tapsum), _ptr(bias), _ptr(ws), ws.numel(), _stream())
     return out
+
+
+def conv_stem_wgrad(grad_out, x_codes, a_range, a_bits, Cout, kh, kw, stride, pad):
+    """Weight gradient of the first-layer convolution from the (channels-last, fp32) output gradient and the input CODES:
+    -> dw fp32 [Cout, Cin, kh, kw] (qb_conv_stem_wgrad; tf32 tensor cores, deterministic)."""
+    B, Cin, H, W = x_codes.shape
+    if not grad_out.is_contiguous(memory_format=torch.channels_last):
+        raise QB200Error("conv_stem_wgrad: grad_out must be channels-last")
+    dw = torch.empty((Cout, Cin, kh, kw), dtype=torch.float32, device=x_codes.device)
+    ws = workspace("conv_stem_wgrad", load().qb_conv_stem_wgrad_ws_bytes(Cout, Cin, kh, kw), x_codes.device)
+    global _next_ops
+    _next_ops = 2 * grad_out.numel() * kh * kw * Cin
+    _run("qb_conv_stem_wgrad", 4 * grad_out.numel() + x_codes.numel(), _ptr(grad_out), _ptr(x_codes), _ptr(dw), B, H, W, Cin, Cout,
+         kh, kw, stride, pad, _ptr(a_range), int(a_bits), _ptr(ws), ws.numel(), _stream())
+    return dw
 
 
 def allreduce_small(t, mode, peer_ptrs, rank, world, slot_bytes):

@@ -430,3 +430,323 @@ extern "C" int qb_conv_stem_fwd(const uint8_t* x_codes, const int8_t* w_codes_kh
     if (kh == 7) return stem_launch<7, 6>(x_codes, out, static_cast<const unsigned char*>(ws), g, st);
     return stem_launch<3, 3>(x_codes, out, static_cast<const unsigned char*>(ws), g, st);
 }
+
+// ------------------------------------------------------------------------------------------------
+// Weight gradient of the stem: dW[n][c][kh][kw] = SUM_pixels g[px][n] * x_hat[px + tap][c]   (quantize.py:143-148: under
+// the bi-precision scheme the weight branch sees the UNQUANTIZED gradient, so this is not an integer contraction).
+// With x_hat = sa*q + la inside the image and exactly 0 in the padding:
+//     dW = sa * SUM g*q  +  la * SUM_{px: tap in bounds} g
+// Both sums come from ONE tf32 tensor-core GEMM over the pixels, D[r][n] = SUM_px P[r][px] * G[n][px]:
+//     rows r <  KH*kw*Cin : P = the code q of patch byte r (exact in tf32),   rows after them: P = 1 if tap (kh,kw) is in bounds
+// Same scheme as the forward kernel, transposed: thread = pixel builds ITS column of both K-major operands (K = pixels, 32
+// per 128-byte swizzled row) - the patch codes from the staged input rows, g from a TMA-loaded, swizzled tile of the
+// gradient (rounded to tf32, round-to-nearest) - one thread issues the MMAs, the accumulators stay in TMEM over all the
+// tiles of the CTA (one CTA per SM), and are written once as a partial result; k_stem_wgrad_reduce adds the partials
+// in CTA order (deterministic) and applies sa / la.   cuDNN: 1.6 ms + layout conversions for this layer.
+// ------------------------------------------------------------------------------------------------
+constexpr int CW_THREADS = 128;
+
+__device__ __forceinline__ void umma_tf32(uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc, uint32_t idesc, uint32_t accumulate) {
+    asm volatile(
+        "{\n\t.reg .pred p;\n\t"
+        "setp.ne.b32 p, %4, 0;\n\t"
+        "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n\t}"
+        ::"r"(d_tmem), "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(accumulate)
+        : "memory");
+}
+__device__ __forceinline__ uint32_t to_tf32(float v) {
+    uint32_t r;
+    asm("cvt.rna.tf32.f32 %0, %1;" : "=r"(r) : "f"(v));
+    return r;
+}
+__device__ __forceinline__ void mbar_wait_bounded(uint64_t* bar, uint32_t parity) {
+    uint32_t spins = 0;
+    while (!mbar_try_wait(bar, parity)) {
+        if (++spins > (1u << 26)) __trap();                   // a lost completion must not hang the GPU
+    }
+}
+
+template <int KH, int WPR>
+__global__ void __launch_bounds__(CW_THREADS, 1)
+k_stem_wgrad(const __grid_constant__ CUtensorMap tmap_g, const uint8_t* __restrict__ x, float* __restrict__ partial, StemGeom g,
+             int mhalves) {
+    extern __shared__ unsigned char smem_raw[];
+    unsigned char* smem = smem_raw + ((1024u - (smem_u32(smem_raw) & 1023u)) & 1023u);
+    const uint32_t a_atom = (uint32_t)mhalves * 128u * 128u, b_atom = (uint32_t)g.Cout * 128u;
+    const uint32_t stage_bytes = 128u * (uint32_t)g.Cout * 4u;               // [Cout/32][128 px][128 B]
+    unsigned char* s_A = smem;                                               // 4 atoms (one per warp = 32 pixels)
+    unsigned char* s_B = s_A + 4 * a_atom;
+    unsigned char* s_G = s_B + 4 * b_atom;                                   // TMA destination, 128-byte swizzle
+    unsigned char* s_in = s_G + stage_bytes;
+    uint64_t* bars = reinterpret_cast<uint64_t*>(s_in + (((size_t)g.rows_in * g.pitch_in + 15) & ~(size_t)15));
+    uint64_t* g_bar = bars;
+    uint64_t* mma_bar = bars + 1;
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2);
+
+    const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+    for (int i = tid; i < (int)((4 * a_atom + 4 * b_atom) / 16); i += CW_THREADS) reinterpret_cast<uint4*>(s_A)[i] = make_uint4(0u, 0u, 0u, 0u);
+    if (tid == 0) {
+        mbar_init(g_bar, 1);
+        mbar_init(mma_bar, 1);
+        fence_barrier_init();
+    }
+    if (warp == 0) tmem_alloc<128>(tmem_slot);
+    fence_proxy_async();
+    tc_fence_before_sync();
+    __syncthreads();
+    tc_fence_after_sync();
+    const uint32_t tmem = *tmem_slot;
+    const uint32_t idesc = umma_idesc(/*F32*/ 1, /*tf32*/ 2, /*tf32*/ 2, 128, (uint32_t)g.Cout);
+    const uint32_t a_u32 = smem_u32(s_A), b_u32 = smem_u32(s_B);
+
+    const int row_bytes = g.kw * g.Cin;
+    const int rows_q = KH * row_bytes;
+    const int th = warp, tw = lane;
+    const int row_len = g.W * g.Cin, chunks = g.pitch_in >> 4;
+    const int total = g.B * g.tiles_h * g.tiles_w;
+    const uint32_t last_mask = (row_bytes & 3) ? ((1u << (8 * (row_bytes & 3))) - 1u) : 0xffffffffu;
+    const int nhalf = g.Cout >> 5;
+
+    auto tile_coords = [&](int t, int& b, int& ho0, int& wo0) {
+        uint32_t q = fdiv((uint32_t)t, g.d_tw);
+        const int twi = t - (int)q * g.tiles_w;
+        const uint32_t bb = fdiv(q, g.d_th);
+        const int thi = (int)q - (int)bb * g.tiles_h;
+        b = (int)bb; ho0 = thi * CS_TH; wo0 = twi * CS_TW;
+    };
+    auto load_chunk = [&](int t, int i) -> uint4 {
+        uint4 v = make_uint4(0u, 0u, 0u, 0u);
+        if (t >= total || i >= g.rows_in * chunks) return v;
+        int b, ho0, wo0;
+        tile_coords(t, b, ho0, wo0);
+        const int r = (int)fdiv((uint32_t)i, g.d_chunks), c = i - r * chunks;
+        const int h = ho0 * g.stride - g.pad + r;
+        const long long row_addr = (long long)reinterpret_cast<uintptr_t>(x) + ((long long)b * g.H + h) * row_len;
+        const long long first = row_addr + (long long)(wo0 * g.stride - g.pad) * g.Cin;
+        const long long a0 = (first & ~15LL) + 16LL * c;
+        if (h >= 0 && h < g.H) {
+            if (a0 >= row_addr && a0 + 16 <= row_addr + row_len) {
+                v = __ldg(reinterpret_cast<const uint4*>(a0));
+            } else if (a0 + 16 > row_addr && a0 < row_addr + row_len) {
+                uint32_t wd[4] = {0u, 0u, 0u, 0u};
+                for (int bt = 0; bt < 16; ++bt) {
+                    const long long a = a0 + bt;
+                    if (a >= row_addr && a < row_addr + row_len)
+                        wd[bt >> 2] |= (uint32_t)__ldg(reinterpret_cast<const uint8_t*>(a)) << (8 * (bt & 3));
+                }
+                v = make_uint4(wd[0], wd[1], wd[2], wd[3]);
+            }
+        }
+        return v;
+    };
+    auto issue_g = [&](int t) {                               // one thread: the gradient tile of tile t -> s_G
+        int b, ho0, wo0;
+        tile_coords(t, b, ho0, wo0);
+        mbar_arrive_expect_tx(g_bar, stage_bytes);
+        for (int hf = 0; hf < nhalf; ++hf) tma_load_4d(s_G + (size_t)hf * 128 * 128, &tmap_g, g_bar, hf * 32, wo0, ho0, b);
+    };
+
+    uint4 pre0 = load_chunk((int)blockIdx.x, tid), pre1 = load_chunk((int)blockIdx.x, tid + CW_THREADS);
+    if (tid == 0 && (int)blockIdx.x < total) issue_g((int)blockIdx.x);
+    uint32_t g_phase = 0, mma_phase = 0;
+    bool first = true;
+    // this thread's column of the K-major operands: pixel `lane` of atom `warp`
+    unsigned char* my_A = s_A + (size_t)warp * a_atom + (size_t)(lane & 3) * 4;
+    unsigned char* my_B = s_B + (size_t)warp * b_atom + (size_t)(lane & 3) * 4;
+    const uint32_t kchunk = (uint32_t)lane >> 2;
+    for (int t = blockIdx.x; t < total; t += gridDim.x) {
+        int b, ho0, wo0;
+        tile_coords(t, b, ho0, wo0);
+        const int h_start = ho0 * g.stride - g.pad, w_start = wo0 * g.stride - g.pad;
+        if (tid < g.rows_in * chunks) *reinterpret_cast<uint4*>(s_in + (size_t)tid * 16) = pre0;
+        if (tid + CW_THREADS < g.rows_in * chunks) *reinterpret_cast<uint4*>(s_in + (size_t)(tid + CW_THREADS) * 16) = pre1;
+        __syncthreads();
+        uint32_t p[KH][WPR];
+#pragma unroll
+        for (int kh = 0; kh < KH; ++kh) {
+            const int r = th * g.stride + kh;
+            const long long firstb = (long long)reinterpret_cast<uintptr_t>(x) + ((long long)b * g.H + h_start + r) * row_len +
+                                     (long long)w_start * g.Cin;
+            const int o = tw * g.stride * g.Cin + (int)(firstb & 15LL);
+            const int sh = (o & 3) * 8;
+            const uint32_t* rowp = reinterpret_cast<const uint32_t*>(s_in + (size_t)r * g.pitch_in + (o & ~3));
+            uint32_t prev = rowp[0];
+#pragma unroll
+            for (int j = 0; j < WPR; ++j) {
+                const uint32_t nxt = rowp[j + 1];
+                uint32_t v = __funnelshift_r(prev, nxt, sh);
+                if (j == WPR - 1) v &= last_mask;
+                p[kh][j] = v;
+                prev = nxt;
+            }
+        }
+        pre0 = load_chunk(t + (int)gridDim.x, tid);
+        pre1 = load_chunk(t + (int)gridDim.x, tid + CW_THREADS);
+        // the previous tile's MMAs have read the operands
+        if (!first) {
+            mbar_wait_bounded(mma_bar, mma_phase);
+            mma_phase ^= 1u;
+        }
+        // ---- P rows: codes, then tap-in-bounds flags ----
+        const int ho = ho0 + th, wo = wo0 + tw;
+        const int h0 = ho * g.stride - g.pad, w0 = wo * g.stride - g.pad;
+#pragma unroll
+        for (int kh = 0; kh < KH; ++kh) {
+#pragma unroll
+            for (int bb = 0; bb < WPR * 4; ++bb) {
+                if (bb < row_bytes) {
+                    const uint32_t r = (uint32_t)(kh * row_bytes + bb);
+                    const float v = (float)((p[kh][bb >> 2] >> (8 * (bb & 3))) & 0xffu);
+                    *reinterpret_cast<float*>(my_A + r * 128u + ((kchunk ^ (r & 7u)) << 4)) = v;
+                }
+            }
+        }
+        for (int kh = 0; kh < KH; ++kh) {
+            const bool vh = (h0 + kh >= 0) && (h0 + kh < g.H);
+            for (int kw = 0; kw < g.kw; ++kw) {
+                const bool vw = (w0 + kw >= 0) && (w0 + kw < g.W);
+                const uint32_t r = (uint32_t)(rows_q + kh * g.kw + kw);
+                *reinterpret_cast<float*>(my_A + r * 128u + ((kchunk ^ (r & 7u)) << 4)) = (vh && vw) ? 1.0f : 0.0f;
+            }
+        }
+        // ---- G rows from the TMA tile (pixel tid of the tile = row tid of each 32-channel half) ----
+        mbar_wait_bounded(g_bar, g_phase);
+        g_phase ^= 1u;
+        for (int hf = 0; hf < nhalf; ++hf) {
+            const unsigned char* src = s_G + (size_t)hf * 128 * 128 + (size_t)tid * 128;
+#pragma unroll
+            for (int c = 0; c < 8; ++c) {
+                const float4 v = *reinterpret_cast<const float4*>(src + ((((uint32_t)c) ^ ((uint32_t)tid & 7u)) << 4));
+                const uint32_t n = (uint32_t)(hf * 32 + c * 4);
+                *reinterpret_cast<uint32_t*>(my_B + (n + 0) * 128u + ((kchunk ^ ((n + 0) & 7u)) << 4)) = to_tf32(v.x);
+                *reinterpret_cast<uint32_t*>(my_B + (n + 1) * 128u + ((kchunk ^ ((n + 1) & 7u)) << 4)) = to_tf32(v.y);
+                *reinterpret_cast<uint32_t*>(my_B + (n + 2) * 128u + ((kchunk ^ ((n + 2) & 7u)) << 4)) = to_tf32(v.z);
+                *reinterpret_cast<uint32_t*>(my_B + (n + 3) * 128u + ((kchunk ^ ((n + 3) & 7u)) << 4)) = to_tf32(v.w);
+            }
+        }
+        fence_proxy_async();
+        tc_fence_before_sync();
+        __syncthreads();
+        if (tid == 0) {
+            if (t + (int)gridDim.x < total) issue_g(t + (int)gridDim.x);      // s_G has been consumed
+            tc_fence_after_sync();
+            for (int w = 0; w < 4; ++w)
+                for (int ks = 0; ks < 4; ++ks)
+                    for (int h = 0; h < mhalves; ++h)
+                        umma_tf32(tmem + (uint32_t)h * 64u,
+                                  umma_smem_desc_sw128(a_u32 + (uint32_t)w * a_atom + (uint32_t)h * 128u * 128u + (uint32_t)ks * 32u),
+                                  umma_smem_desc_sw128(b_u32 + (uint32_t)w * b_atom + (uint32_t)ks * 32u), idesc,
+                                  (first && w == 0 && ks == 0) ? 0u : 1u);
+            umma_commit(mma_bar);
+        }
+        first = false;
+    }
+    const int rows = rows_q + KH * g.kw;
+    if (!first) {
+        mbar_wait_bounded(mma_bar, mma_phase);
+        tc_fence_after_sync();
+        for (int h = 0; h < mhalves; ++h)
+            for (int c0 = 0; c0 < g.Cout; c0 += 32) {
+                uint32_t acc[32];
+                tmem_ld_32x32(tmem + ((uint32_t)(warp * 32) << 16) + (uint32_t)(h * 64 + c0), acc);
+                tmem_ld_wait();
+                const int r = h * 128 + tid;
+                if (r < rows) {
+                    float* dst = partial + ((size_t)blockIdx.x * rows + r) * g.Cout + c0;
+#pragma unroll
+                    for (int u = 0; u < 32; u += 4)
+                        *reinterpret_cast<uint4*>(dst + u) = make_uint4(acc[u], acc[u + 1], acc[u + 2], acc[u + 3]);
+                }
+            }
+    }
+    tc_fence_before_sync();
+    __syncthreads();
+    if (warp == 0) tmem_dealloc<128>(tmem);
+}
+
+// dW[n][c][kh][kw] = sa * SUM_cta Dq[cta][(kh, kw, c)][n] + la * SUM_cta Dm[cta][(kh, kw)][n]
+__global__ void __launch_bounds__(256) k_stem_wgrad_reduce(const float* __restrict__ partial, int nparts, float* __restrict__ dw,
+                                                           const float* __restrict__ a_range, int a_bits, int Cout, int Cin, int kh,
+                                                           int kw) {
+    const int rows_q = kh * kw * Cin, rows = rows_q + kh * kw;
+    const int idx = blockIdx.x * 256 + threadIdx.x;
+    if (idx >= rows_q * Cout) return;
+    const int n = idx % Cout, r = idx / Cout;                 // r = (kh, kw, c)
+    const int c = r % Cin, tap = r / Cin;
+    const QParams pa = make_qparams_d((double)__ldg(a_range), (double)__ldg(a_range + 1), a_bits);
+    double sq = 0.0, sm = 0.0;
+    for (int p = 0; p < nparts; ++p) {
+        sq += (double)partial[((size_t)p * rows + r) * Cout + n];
+        sm += (double)partial[((size_t)p * rows + rows_q + tap) * Cout + n];
+    }
+    dw[((size_t)n * Cin + c) * (kh * kw) + tap] = (float)((double)pa.scale * sq + (double)pa.lo * sm);
+}
+
+static int stem_wgrad_parts(const StemGeom& g) {
+    int sms = qb_sm_count();
+    if (sms <= 0) sms = 148;
+    const int64_t total = (int64_t)g.B * g.tiles_h * g.tiles_w;
+    return (int)(total < sms ? total : sms);
+}
+
+extern "C" size_t qb_conv_stem_wgrad_ws_bytes(int64_t Cout, int64_t Cin, int kh, int kw) {
+    int sms = qb_sm_count();
+    if (sms <= 0) sms = 148;
+    return (size_t)sms * (size_t)(kh * kw * (Cin + 1)) * (size_t)Cout * 4;
+}
+
+template <int KH, int WPR>
+static int stem_wgrad_launch(const CUtensorMap& tg, const uint8_t* x, float* partial, const StemGeom& g, int mhalves, int parts,
+                             cudaStream_t st) {
+    const size_t smem = 1024 + 4 * ((size_t)mhalves * 128 * 128 + (size_t)g.Cout * 128) + (size_t)128 * g.Cout * 4 +
+                        (((size_t)g.rows_in * g.pitch_in + 15) & ~(size_t)15) + 32;
+    if (smem > 226 * 1024) {
+        qb_set_error("qb_conv_stem_wgrad: %zu bytes of shared memory needed", smem);
+        return QB_ERR_UNSUPPORTED;
+    }
+    QB_CUDA(cudaFuncSetAttribute(k_stem_wgrad<KH, WPR>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    k_stem_wgrad<KH, WPR><<<(unsigned)parts, CW_THREADS, smem, st>>>(tg, x, partial, g, mhalves);
+    QB_LAUNCH_CHECK();
+    return QB_OK;
+}
+
+/* grad_out fp32 [B,Ho,Wo,Cout] (NHWC), x_codes uint8 [B,H,W,Cin] with their quantizer's device range -> dw fp32
+ * [Cout][Cin][kh][kw] (contiguous).  Cout 32 or 64.  ws: qb_conv_stem_wgrad_ws_bytes() bytes.                           */
+extern "C" int qb_conv_stem_wgrad(const float* grad_out, const uint8_t* x_codes, float* dw, int64_t B, int64_t H, int64_t W,
+                                  int64_t Cin, int64_t Cout, int kh, int kw, int stride, int pad, const float* a_range, int a_bits,
+                                  void* ws, size_t ws_bytes, void* stream) {
+    QB_CHECK_ARG(grad_out && x_codes && dw && a_range && ws, "qb_conv_stem_wgrad: null pointer");
+    StemGeom g;
+    if (!stem_geom(g, B, H, W, Cin, Cout, kh, kw, stride, pad) || !(Cout == 32 || Cout == 64)) {
+        qb_set_error("qb_conv_stem_wgrad: unsupported geometry (see qb_conv_stem_fwd; C_out must be 32 or 64)");
+        return QB_ERR_UNSUPPORTED;
+    }
+    QB_CHECK_ARG(a_bits >= 1 && a_bits <= 8, "qb_conv_stem_wgrad: codes are 8-bit");
+    QB_CHECK_ARG(ws_bytes >= qb_conv_stem_wgrad_ws_bytes(Cout, Cin, kh, kw) && (reinterpret_cast<uintptr_t>(ws) & 15) == 0,
+                 "qb_conv_stem_wgrad: workspace too small or not 16-byte aligned");
+    QB_CHECK_ARG((reinterpret_cast<uintptr_t>(grad_out) & 15) == 0, "qb_conv_stem_wgrad: grad_out must be 16-byte aligned");
+    const int rows = kh * kw * ((int)Cin + 1);
+    const int mhalves = (rows + 127) / 128;
+    if (mhalves > 2) {
+        qb_set_error("qb_conv_stem_wgrad: %d operand rows", rows);
+        return QB_ERR_UNSUPPORTED;
+    }
+    CUtensorMap tg;
+    {   // gradient fp32 NHWC: dims {Cout, Wo, Ho, B}; box = 32 channels x the tile's 4 x 32 pixels, zero fill outside
+        const uint64_t dims[4] = {(uint64_t)g.Cout, (uint64_t)g.Wo, (uint64_t)g.Ho, (uint64_t)g.B};
+        const uint64_t str[3] = {(uint64_t)g.Cout * 4, (uint64_t)g.Wo * g.Cout * 4, (uint64_t)g.Ho * g.Wo * g.Cout * 4};
+        const uint32_t box[4] = {32u, (uint32_t)CS_TW, (uint32_t)CS_TH, 1u};
+        int rc = qb_make_tmap(&tg, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, grad_out, dims, str, box, nullptr, 128);
+        if (rc) return rc;
+    }
+    const int parts = stem_wgrad_parts(g);
+    cudaStream_t st = qb_stream(stream);
+    int rc = kh == 7 ? stem_wgrad_launch<7, 6>(tg, x_codes, static_cast<float*>(ws), g, mhalves, parts, st)
+                     : stem_wgrad_launch<3, 3>(tg, x_codes, static_cast<float*>(ws), g, mhalves, parts, st);
+    if (rc) return rc;
+    const int outs = kh * kw * (int)Cin * (int)Cout;
+    k_stem_wgrad_reduce<<<(outs + 255) / 256, 256, 0, st>>>(static_cast<const float*>(ws), parts, dw, a_range, a_bits, (int)Cout,
+                                                             (int)Cin, kh, kw);
+    QB_LAUNCH_CHECK();
+    return QB_OK;
+}

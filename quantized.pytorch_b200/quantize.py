@@ -570,7 +570,10 @@ class _QTensorCoreFn(Function):
         bits_a, bits_w = mod.num_bits, mod.num_bits_weight
         update = not mod.freeze_param_dyn_range
         codes = torch.empty_like(x, dtype=torch.uint8)                      # same memory format as x
-        xq = _abi.fakequant_affine(x, bits_a, range_dev=rng, codes=codes, want_y=need_bwd)
+        # first layer whose input needs no gradient: the weight gradient is taken from the codes (conv_stem.cu)
+        stem_bwd = (conv and USE_STEM_KERNEL and x.shape[1] % 32 != 0 and not ctx.needs_input_grad[0]
+                    and mod.out_channels in (32, 64) and mod.kernel_size[0] == 7)
+        xq = _abi.fakequant_affine(x, bits_a, range_dev=rng, codes=codes, want_y=need_bwd and not stem_bwd)
         w4 = weight if conv else weight.view(weight.shape[0], weight.shape[1], 1, 1)
         wq, wcodes, tapsum = _abi.fakequant_rows_conv(w4, bits_w, mod.weight_min, mod.weight_max, compute_range=update,
                                                       want_y=need_bwd)
@@ -599,12 +602,25 @@ class _QTensorCoreFn(Function):
             wq = wq.view(N, K) if wq is not None else None
             ctx.conv = None
         ctx.bits_grad, ctx.grad_mode, ctx.has_bias = mod.num_bits_grad, mod._grad_mode(), qbias is not None
-        if need_bwd:
+        ctx.stem = None
+        if need_bwd and stem_bwd:
+            ctx.stem = (bits_a, mod.out_channels, kh, kw, _pair(mod.stride)[0], _pair(mod.padding)[0])
+            ctx.save_for_backward(codes, rng)
+        elif need_bwd:
             ctx.save_for_backward(xq, wq)
         return out
 
     @staticmethod
     def backward(ctx, g):
+        if ctx.stem is not None:
+            codes, rng = ctx.saved_tensors
+            g = _abi._f32c(g, "grad")
+            if ctx.grad_mode == "quant":
+                g = _quantize_gradient(g, ctx.bits_grad)
+            g = g.contiguous(memory_format=torch.channels_last)
+            dw = _abi.conv_stem_wgrad(g, codes, rng, *ctx.stem) if ctx.needs_input_grad[1] else None
+            db = g.sum((0, 2, 3)) if ctx.has_bias and ctx.needs_input_grad[2] else None
+            return None, dw, db, None, None
         x, w = ctx.saved_tensors
         return _contraction_backward(ctx, g, x, w) + (None, None)
 

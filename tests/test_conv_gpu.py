@@ -160,3 +160,43 @@ def test_qconv2d_first_layer_uses_stem_kernel(lib):
         Q.USE_STEM_KERNEL = True
     assert float((y1 - y2).detach().norm() / y2.detach().norm()) < 1e-4
     assert float((g1 - m2.weight.grad).norm() / m2.weight.grad.norm()) < 1e-3
+
+
+WGRAD_CASES = [  # B, Cin, H, W, Cout, k, stride, pad
+    (4, 3, 224, 224, 64, 7, 2, 3),       # ResNet conv1 (more tiles than SMs: several tiles per CTA)
+    (2, 3, 61, 45, 64, 7, 2, 3),         # ragged tiles
+    (1, 3, 7, 7, 64, 7, 2, 3),           # every pixel on the border
+    (3, 3, 64, 64, 32, 3, 2, 1),         # MobileNet stem
+    (2, 3, 32, 32, 64, 7, 1, 3),
+]
+
+
+@pytest.mark.parametrize("case", WGRAD_CASES)
+def test_conv_stem_wgrad(lib, case):
+    """qb_conv_stem_wgrad (tf32 tensor cores on the codes) against the fp64 weight gradient of F.conv2d on the dequantised
+    input; the bar is the tf32 rounding of the gradient operand (what cuDNN's default path does too)."""
+    B, Cin, H, W, Cout, k, stride, pad = case
+    gen = torch.Generator().manual_seed(sum(case) + 1)
+    x = torch.randn(B, Cin, H, W, generator=gen) * 1.1 + 0.3
+    xd = x.to(DEV).contiguous(memory_format=torch.channels_last)
+    rng = torch.tensor([float(x.min()), float(x.max())], device=DEV)
+    codes = torch.empty_like(xd, dtype=torch.uint8)
+    xq = lib.fakequant_affine(xd, 8, range_dev=rng, codes=codes)
+    Ho, Wo = (H + 2 * pad - k) // stride + 1, (W + 2 * pad - k) // stride + 1
+    g = torch.randn(B, Cout, Ho, Wo, generator=gen)
+    gd = g.to(DEV).contiguous(memory_format=torch.channels_last)
+    dw = lib.conv_stem_wgrad(gd, codes, rng, 8, Cout, k, k, stride, pad)
+    dw2 = lib.conv_stem_wgrad(gd, codes, rng, 8, Cout, k, k, stride, pad)
+    torch.cuda.synchronize()
+    assert torch.equal(dw, dw2)                                  # deterministic
+    w64 = torch.zeros(Cout, Cin, k, k, dtype=torch.float64, requires_grad=True)
+    F.conv2d(xq.double().cpu(), w64, None, stride, pad).backward(g.double())
+    ref = w64.grad
+    rel = float((dw.cpu().double() - ref).norm() / ref.norm())
+    assert rel < 5e-4, rel                                       # tf32 operand rounding: ~2^-12 per term, random sign
+    # same class as the library route this replaces
+    torch.backends.cudnn.allow_tf32 = True
+    w32 = torch.zeros(Cout, Cin, k, k, device=DEV, requires_grad=True)
+    F.conv2d(xq, w32, None, stride, pad).backward(gd)
+    rel_cudnn = float((w32.grad.cpu().double() - ref).norm() / ref.norm())
+    assert rel < max(2.0 * rel_cudnn, 5e-4), (rel, rel_cudnn)      # tiny inputs: cuDNN picks an fp32 kernel, tf32 noise does not average out

@@ -25,12 +25,30 @@ def main():
         rmin, rmax = torch.empty(Cout, device=dev), torch.empty(Cout, device=dev)
         wq, wcodes, tapsum = _abi.fakequant_rows_conv(w, 8, rmin, rmax)
         wq_cl = wq.contiguous(memory_format=torch.channels_last)
+        Ho = (224 + 2 * pad - k) // stride + 1
         t = timeit(lambda: _abi.conv_stem_fwd(codes, wcodes, B, 224, 224, 3, Cout, k, k, stride, pad, rng, 8, rmin, rmax, 8, tapsum),
                    flush)
         t_ref = timeit(lambda: F.conv2d(xq, wq_cl, None, stride, pad), flush)
-        Ho = (224 + 2 * pad - k) // stride + 1
         bytes_ = B * 224 * 224 * 3 + 4 * B * Ho * Ho * Cout
         ops = 2 * B * Ho * Ho * Cout * k * k * 3
+        gout = torch.randn(B, Cout, Ho, Ho, device=dev).contiguous(memory_format=torch.channels_last)
+        t_wg = timeit(lambda: _abi.conv_stem_wgrad(gout, codes, rng, 8, Cout, k, k, stride, pad), flush)
+        w32 = torch.zeros_like(wq_cl)
+
+        def cudnn_wgrad(gg=gout, xx=xq, ww=w32):
+            return torch.ops.aten.convolution_backward(gg, xx, ww, None, [stride, stride], [pad, pad], [1, 1], False, [0, 0], 1,
+                                                       [False, True, False])[1]
+        t_wg_ref = timeit(cudnn_wgrad, flush)
+        dw = _abi.conv_stem_wgrad(gout, codes, rng, 8, Cout, k, k, stride, pad)
+        dw_ref = cudnn_wgrad()
+        g16 = gout[:16].contiguous(memory_format=torch.channels_last)
+        c16 = codes[:16].contiguous(memory_format=torch.channels_last)
+        ref64 = cudnn_wgrad(g16.double(), xq[:16].double(), w32.double())
+        dw16 = _abi.conv_stem_wgrad(g16, c16, rng, 8, Cout, k, k, stride, pad)
+        dw16_ref = cudnn_wgrad(g16, xq[:16], w32)
+        print("%-28s wgrad %.3f ms   cuDNN %.3f ms   rel.diff to cuDNN %.2e;  batch 16 vs fp64: ours %.2e, cuDNN %.2e" %
+              (name, t_wg, t_wg_ref, float((dw - dw_ref).norm() / dw_ref.norm()),
+               float((dw16.double() - ref64).norm() / ref64.norm()), float((dw16_ref.double() - ref64).norm() / ref64.norm())))
         print("%-28s stem %.3f ms (%.1f TOP/s, %.0f GB/s of %.0f)   cuDNN fp32 %.3f ms   floor %.3f ms" %
               (name, t, ops / t / 1e9, bytes_ / t / 1e6, HBM_GBS, t_ref, bytes_ / HBM_GBS / 1e6))
 
