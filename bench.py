@@ -213,14 +213,37 @@ def main_ours(args, rank, world, local_rank):
     ms_dev = e0.elapsed_time(e1)
     # ---- end-to-end leg: pinned host batch -> device every step, loss read back every step ----
     copy_stream = torch.cuda.Stream(dev)
+    stage_x = [torch.empty_like(x_static) for _ in range(2)]
+    stage_y = [torch.empty_like(y_static) for _ in range(2)]
+    ready = [torch.cuda.Event() for _ in range(2)]
+    consumed = [torch.cuda.Event() for _ in range(2)]
     barrier()
     t0 = time.perf_counter()
     e2, e3 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     e2.record()
     losses = []
+    # Input pipeline of the public API's training loop: the pinned batch of step i+1 crosses PCIe on a copy stream
+    # into one of two staging buffers while step i computes; every step's H2D copy (the first one included, fully
+    # exposed) and loss read-back are inside the timed region.
+    cur = torch.cuda.current_stream(dev)
+
+    def prefetch(i):
+        k = i % 2
+        with torch.cuda.stream(copy_stream):
+            copy_stream.wait_event(consumed[k])                 # the staging buffer's previous batch has been taken
+            stage_x[k].copy_(host_x[k], non_blocking=True)
+            stage_y[k].copy_(host_y[k], non_blocking=True)
+            ready[k].record(copy_stream)
+
+    prefetch(0)
     for i in range(args.steps):
-        x_static.copy_(host_x[i % 2], non_blocking=True)
-        y_static.copy_(host_y[i % 2], non_blocking=True)
+        k = i % 2
+        if i + 1 < args.steps:
+            prefetch(i + 1)
+        cur.wait_event(ready[k])
+        x_static.copy_(stage_x[k], non_blocking=True)           # device-to-device into the graph's input tensors
+        y_static.copy_(stage_y[k], non_blocking=True)
+        consumed[k].record(cur)
         run_step()
         losses.append(float(loss_static))           # D2H read of the step's result (syncs)
     e3.record()
@@ -229,7 +252,7 @@ def main_ours(args, rank, world, local_rank):
     wall_e2e = time.perf_counter() - t0
     sampler.stop_flag = True
     sampler.join(timeout=2)
-    del copy_stream
+    del copy_stream, stage_x, stage_y
     # max over ranks
     if world > 1:
         t = torch.tensor([ms_dev, ms_e2e], device=dev, dtype=torch.float64)
@@ -261,7 +284,10 @@ def main_ours(args, rank, world, local_rank):
                    "l2": "inputs+activations per step (>2 GB) exceed the 126 MB L2"},
         "e2e": {"value": round(imgs / (ms_e2e / 1e3), 2), "unit": UNIT, "h2d_bytes_per_step": h2d * world,
                 "d2h_bytes_per_step": 4 * world, "ms_per_step": round(ms_e2e / args.steps, 3),
-                "wall_ms_per_step": round(wall_e2e * 1e3 / args.steps, 3)},
+                "wall_ms_per_step": round(wall_e2e * 1e3 / args.steps, 3),
+                "pipeline": "pinned host batch of step i+1 copied on a second stream into double-buffered staging while "
+                            "step i computes; all K copies (the first fully exposed) and K loss reads are inside the timed "
+                            "region"},
         "gpu_launches": int(step_body_launches * args.steps),
         "clocks": sampler.summary(), "roofline": roof, "cpu_baseline": cpu_base, "loss_last": losses[-1],
     }

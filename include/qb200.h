@@ -262,6 +262,34 @@ int qb_conv_stem_fwd(const uint8_t* x_codes, const int8_t* w_codes_khwc, float* 
                      const float* w_row_min, const float* w_row_max, int w_bits, const int32_t* tapsum,
                      const float* bias, void* ws, size_t ws_bytes, void* stream);
 
+/* QConv2d forward contraction of a DEPTHWISE 3x3 convolution (groups == C_in == C_out; models/mobilenet_quantized.py:21-60
+ * through quantize.py:143-148, 343) on the integer codes.  18 operations per 5 bytes of traffic: a streaming kernel
+ * bounded by HBM (no tensor cores), one thread per output pixel x 4 channels, IDP.4A products, packed code sums.
+ *   x_codes uint8 [B,H,W,C] (NHWC) with device range a_range {min,max}; w_codes int8 [C][9] CENTRED codes (what
+ *   qb_fakequant_rows_conv emits for a [C,1,3,3] weight) with per-channel ranges; bias fp32[C] or NULL
+ *   out fp32 [B,Ho,Wo,C] (NHWC); zero padding exact for any input range
+ *   out_stats / stats_ws: as in qb_conv_i8_fwd (QuantMeasure statistics of the output fused into the kernel)
+ * Supported (qb_conv_dw_supported): 3x3, C % 4 == 0, stride 1 or 2, pad 0..2, dilation 1; else QB_ERR_UNSUPPORTED.     */
+int qb_conv_dw_supported(int64_t C, int kh, int kw, int stride, int pad);
+int qb_conv_dw_fwd(const uint8_t* x_codes, const int8_t* w_codes, float* out, int64_t B, int64_t H, int64_t W, int64_t C,
+                   int kh, int kw, int stride, int pad, const float* a_range, int a_bits, const float* w_row_min,
+                   const float* w_row_max, int w_bits, const float* bias, double* out_stats, void* stats_ws,
+                   size_t stats_ws_bytes, void* stream);
+
+/* Backward of the depthwise 3x3 convolution under conv2d_biprec (quantize.py:142-148; aten::convolution_backward with
+ * groups == C in the reference): fp32 streaming kernels over channels-last tensors, same geometry limits as
+ * qb_conv_dw_fwd.
+ *   qb_conv_dw_dgrad: dx[B,H,W,C] = transposed depthwise convolution of grad_q [B,Ho,Wo,C] (the gradient the caller has
+ *     already quantized to num_bits_grad) with the fake-quantized weights w_hat fp32 [C][9].
+ *   qb_conv_dw_wgrad: dw[C][9] = SUM over output pixels of x_hat (zero outside the image) * grad_out, and db[C] = SUM
+ *     grad_out (db may be NULL); deterministic (fixed-order partial blocks in ws: qb_conv_dw_wgrad_ws_bytes() bytes).
+ *     Needs C/4 to divide 256.                                                                                        */
+int qb_conv_dw_dgrad(const float* grad_q, const float* w_hat, float* dx, int64_t B, int64_t H, int64_t W, int64_t C, int kh,
+                     int kw, int stride, int pad, void* stream);
+size_t qb_conv_dw_wgrad_ws_bytes(int64_t B, int64_t H, int64_t W, int64_t C, int stride, int pad);
+int qb_conv_dw_wgrad(const float* grad_out, const float* x_hat, float* dw, float* db, int64_t B, int64_t H, int64_t W,
+                     int64_t C, int kh, int kw, int stride, int pad, void* ws, size_t ws_bytes, void* stream);
+
 /* Weight gradient of that first layer (quantize.py:143-148: the weight branch of the bi-precision backward sees the
  * unquantized gradient): dW = x_hat^T * g over all output pixels, from the input CODES (x_hat = sa*q + la inside the
  * image, 0 in the padding) and the fp32 NHWC gradient, on tf32 tensor cores (g rounded to tf32, codes exact),
@@ -301,6 +329,11 @@ int qb_rangebn2_apply(const float* x, float* out, int64_t B, int64_t C, int64_t 
 /* nn.ReLU(inplace) between the modules (models/resnet_quantized.py:52-68,147): y = relu(x) (y may alias x) and, in the same
  * pass, the QuantMeasure statistics block (as qb_measure_stats) of y for the quantized layer that consumes it. */
 int qb_relu_measure(const float* x, float* y, int64_t B, int64_t inner, double* stats, void* ws, size_t ws_bytes, void* stream);
+/* The residual add and ReLU that close a ResNet block (`out += residual; out = relu(out)`, models/resnet_quantized.py:62-68,
+ * 105-112) in one pass: y = relu(x + r) (y may alias x, r must not alias y; x + r rounded to fp32 before the clamp, as the
+ * two torch ops do) plus the statistics block of y. */
+int qb_add_relu_measure(const float* x, const float* r, float* y, int64_t B, int64_t inner, double* stats, void* ws,
+                        size_t ws_bytes, void* stream);
 int qb_maxpool2d_nhwc_fwd(const float* x, float* out, uint8_t* idx, int64_t B, int64_t H, int64_t W, int64_t C, int k,
                           int stride, int pad, void* stream);
 int qb_maxpool2d_nhwc_bwd(const float* grad_out, const uint8_t* idx, float* dx, int64_t B, int64_t H, int64_t W, int64_t C,

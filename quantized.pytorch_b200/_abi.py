@@ -26,6 +26,7 @@ PROTOTYPES = {
     "qb_measure_ws_bytes": (_sz, [_i64]),
     "qb_measure_stats": (_i32, [_p, _i64, _i64, _p, _p, _sz, _p]),
     "qb_relu_measure": (_i32, [_p, _p, _i64, _i64, _p, _p, _sz, _p]),
+    "qb_add_relu_measure": (_i32, [_p, _p, _p, _i64, _i64, _p, _p, _sz, _p]),
     "qb_measure_finalize": (_i32, [_p, _p, _p, _p, _p, _p, _dbl, _i32, _i32, _i32, _p, _p]),
     "qb_fakequant_affine": (_i32, [_p, _p, _p, _i64, _i32, _p, _dbl, _dbl, _i32, _p]),
     "qb_selftest_div": (_i32, [_p, _flt, _p, _p, _i64, _p]),
@@ -69,6 +70,12 @@ PROTOTYPES = {
     "qb_conv_stem_wgrad": (_i32, [_p, _p, _p, _i64, _i64, _i64, _i64, _i64, _i32, _i32, _i32, _i32, _p, _i32, _p, _sz, _p]),
     "qb_conv_stem_fwd": (_i32, [_p, _p, _p, _i64, _i64, _i64, _i64, _i64, _i32, _i32, _i32, _i32, _p, _i32, _p, _p, _i32,
                                 _p, _p, _p, _sz, _p]),
+    "qb_conv_dw_supported": (_i32, [_i64, _i32, _i32, _i32, _i32]),
+    "qb_conv_dw_dgrad": (_i32, [_p, _p, _p, _i64, _i64, _i64, _i64, _i32, _i32, _i32, _i32, _p]),
+    "qb_conv_dw_wgrad_ws_bytes": (_sz, [_i64, _i64, _i64, _i64, _i32, _i32]),
+    "qb_conv_dw_wgrad": (_i32, [_p, _p, _p, _p, _i64, _i64, _i64, _i64, _i32, _i32, _i32, _i32, _p, _sz, _p]),
+    "qb_conv_dw_fwd": (_i32, [_p, _p, _p, _i64, _i64, _i64, _i64, _i32, _i32, _i32, _i32, _p, _i32, _p, _p, _i32, _p, _p, _p,
+                              _sz, _p]),
     "qb_conv_i8_fwd": (_i32, [_p, _p, _p, _i64, _i64, _i64, _i64, _i64, _i32, _i32, _i32, _i32, _p, _i32, _p, _p, _i32,
                               _p, _p, _p, _p, _p, _p, _sz, _p]),
 }
@@ -109,7 +116,7 @@ _profile = None       # list of (name, algorithmic_bytes, start_event, end_event
 
 # kernels enqueued per C call
 _NLAUNCH = {"qb_rangebn_stats": 2, "qb_rangebn_bwd_reduce": 2, "qb_rangebn_bwd_apply": 2,
-            "qb_conv_i8_fwd": 2, "qb_conv_stem_fwd": 2, "qb_conv_stem_wgrad": 2, "qb_rangebn_stats_nhwc": 3, "qb_rangebn_bwd_reduce_nhwc": 2, "qb_rangebn_bwd_apply_nhwc": 2}
+            "qb_conv_i8_fwd": 2, "qb_conv_dw_wgrad": 2, "qb_conv_stem_fwd": 2, "qb_conv_stem_wgrad": 2, "qb_rangebn_stats_nhwc": 3, "qb_rangebn_bwd_reduce_nhwc": 2, "qb_rangebn_bwd_apply_nhwc": 2}
 
 
 _next_ops = 0          # integer operations (2*M*N*K) of the next tensor-core call, set by the conv / GEMM wrappers
@@ -221,6 +228,24 @@ def relu_measure(x, out=None):
     stats = torch.empty(8, dtype=torch.float64, device=x.device)
     ws = workspace("measure", lib.qb_measure_ws_bytes(B), x.device)
     _run("qb_relu_measure", 8 * x.numel(), _ptr(x), _ptr(out), B, inner, _ptr(stats), _ptr(ws), ws.numel(), _stream())
+    return out, stats
+
+
+def add_relu_measure(x, r, out=None):
+    """out = relu(x + r) (out=None: in place in x) and the QuantMeasure statistics (double[8]) of the result, one pass.
+    x and r must share shape and memory layout."""
+    lib = load()
+    x, r = _f32c(x, "x"), _f32c(r, "residual")
+    if x.shape != r.shape or x.stride() != r.stride():
+        raise QB200Error("add_relu_measure: x and residual differ in shape or layout")
+    if out is None:
+        out = x
+    B = x.size(0)
+    inner = x.numel() // max(B, 1)
+    stats = torch.empty(8, dtype=torch.float64, device=x.device)
+    ws = workspace("measure", lib.qb_measure_ws_bytes(B), x.device)
+    _run("qb_add_relu_measure", 12 * x.numel(), _ptr(x), _ptr(r), _ptr(out), B, inner, _ptr(stats), _ptr(ws), ws.numel(),
+         _stream())
     return out, stats
 
 
@@ -492,6 +517,55 @@ def conv_i8_fwd(x_codes, w_codes, B, H, W, Cin, Cout, kh, kw, stride, pad, a_ran
          int(w_bits), _ptr(pixsum), _ptr(boxsum), _ptr(tapsum), _ptr(bias), _ptr(out_stats), _ptr(ws),
          ws.numel() if ws is not None else 0, _stream())
     return out
+
+
+def conv_dw_supported(C, kh, kw, stride, pad):
+    return bool(load().qb_conv_dw_supported(int(C), int(kh), int(kw), int(stride), int(pad)))
+
+
+def conv_dw_fwd(x_codes, w_codes, B, H, W, C, kh, kw, stride, pad, a_range, a_bits, row_min, row_max, w_bits, bias=None,
+                out_stats=None):
+    """Depthwise 3x3 convolution on the integer codes -> fp32 [B, C, Ho, Wo] stored channels-last (qb_conv_dw_fwd)."""
+    Ho, Wo = (H + 2 * pad - kh) // stride + 1, (W + 2 * pad - kw) // stride + 1
+    out = torch.empty((B, C, max(Ho, 0), max(Wo, 0)), dtype=torch.float32, device=x_codes.device,
+                      memory_format=torch.channels_last)
+    ws = workspace("measure", load().qb_measure_ws_bytes(B), x_codes.device) if out_stats is not None else None
+    _run("qb_conv_dw_fwd", B * H * W * C + 9 * C + 4 * B * Ho * Wo * C, _ptr(x_codes), _ptr(w_codes), _ptr(out), B, H, W, C,
+         kh, kw, stride, pad, _ptr(a_range), int(a_bits), _ptr(row_min), _ptr(row_max), int(w_bits), _ptr(bias),
+         _ptr(out_stats), _ptr(ws), ws.numel() if ws is not None else 0, _stream())
+    return out
+
+
+def conv_dw_bwd_supported(g, x, w, stride, pad):
+    """Channels-last fp32 tensors of a depthwise 3x3 convolution the native backward kernels take."""
+    C = x.shape[1]
+    return (g.dim() == 4 and x.dim() == 4 and tuple(w.shape) == (C, 1, 3, 3) and C % 4 == 0 and 256 % (C // 4) == 0
+            and conv_dw_supported(C, 3, 3, stride, pad) and x.numel() < 2 ** 32 and g.dtype == torch.float32
+            and x.dtype == torch.float32 and w.dtype == torch.float32 and is_nhwc(x) and x.data_ptr() % 16 == 0)
+
+
+def conv_dw_dgrad(grad_q, w_hat, x_shape, stride, pad):
+    """Input gradient of the depthwise 3x3 convolution: grad_q [B,C,Ho,Wo] (channels-last), w_hat [C,1,3,3] -> dx."""
+    B, C, H, W = x_shape
+    g = grad_q if is_nhwc(grad_q) else grad_q.contiguous(memory_format=torch.channels_last)
+    w = w_hat if w_hat.is_contiguous() else w_hat.contiguous()
+    dx = torch.empty((B, C, H, W), dtype=torch.float32, device=g.device, memory_format=torch.channels_last)
+    _run("qb_conv_dw_dgrad", 4 * g.numel() + 4 * dx.numel(), _ptr(g), _ptr(w), _ptr(dx), B, H, W, C, 3, 3, int(stride), int(pad),
+         _stream())
+    return dx
+
+
+def conv_dw_wgrad(grad_out, x_hat, stride, pad, want_bias):
+    """Weight (and bias) gradient of the depthwise 3x3 convolution from channels-last grad_out / x_hat -> (dw, db|None)."""
+    B, C, H, W = x_hat.shape
+    g = grad_out if is_nhwc(grad_out) else grad_out.contiguous(memory_format=torch.channels_last)
+    dw = torch.empty((C, 1, 3, 3), dtype=torch.float32, device=g.device)
+    db = torch.empty(C, dtype=torch.float32, device=g.device) if want_bias else None
+    nbytes = load().qb_conv_dw_wgrad_ws_bytes(B, H, W, C, int(stride), int(pad))
+    ws = workspace("conv_dw_wgrad", nbytes, g.device)
+    _run("qb_conv_dw_wgrad", 4 * g.numel() + 4 * x_hat.numel(), _ptr(g), _ptr(x_hat), _ptr(dw), _ptr(db), B, H, W, C, 3, 3,
+         int(stride), int(pad), _ptr(ws), ws.numel(), _stream())
+    return dw, db
 
 
 def conv_stem_supported(H, W, Cin, Cout, kh, kw, stride, pad):

@@ -32,10 +32,13 @@ __device__ __forceinline__ void acc4(float4 v, float& mn, float& mx, float& s, f
 //  then delivers the next QuantMeasure's statistics for free.  NaNs propagate like ATen's relu.
 __device__ __forceinline__ float relu1(float v) { return v < 0.0f ? 0.0f : v; }
 
-template <bool RELU>
+// MODE 0: statistics of x; 1: y = relu(x) + statistics of y; 2: y = relu(x + r) + statistics of y (the residual add and
+// the ReLU that close a ResNet block, models/resnet_quantized.py:62-68, in one pass)
+template <int MODE>
 __global__ void __launch_bounds__(MS_THREADS)
-k_measure_stats(const float* x, float* y, int64_t B, int64_t inner, int vec, double* stats, unsigned int* row_max,
+k_measure_stats(const float* x, const float* r, float* y, int64_t B, int64_t inner, int vec, double* stats, unsigned int* row_max,
                 unsigned int* row_min, double* psum, double* psq, unsigned int* counter) {
+    constexpr bool RELU = MODE >= 1, ADD = MODE == 2;
     __shared__ float smn[8], smx[8];
     __shared__ double sd[2][8];
     __shared__ bool last;
@@ -75,16 +78,22 @@ k_measure_stats(const float* x, float* y, int64_t B, int64_t inner, int vec, dou
         if (vec) {
             const int64_t nq = len >> 2;
             float4 v[MS_VEC_PER_THREAD];
+            float4 rv[ADD ? MS_VEC_PER_THREAD : 1];
 #pragma unroll
             for (int u = 0; u < MS_VEC_PER_THREAD; ++u) {
                 int64_t qi = threadIdx.x + (int64_t)u * MS_THREADS;
-                if (qi < nq) v[u] = RELU ? reinterpret_cast<const float4*>(src)[qi]          // in place: the line is written next
-                                         : __ldcs(reinterpret_cast<const float4*>(src) + qi);
+                if (qi < nq) {
+                    v[u] = RELU ? reinterpret_cast<const float4*>(src)[qi]          // in place: the line is written next
+                                : __ldcs(reinterpret_cast<const float4*>(src) + qi);
+                    if (ADD) rv[u] = __ldcs(reinterpret_cast<const float4*>(r + b * inner + off) + qi);
+                }
             }
 #pragma unroll
             for (int u = 0; u < MS_VEC_PER_THREAD; ++u) {
                 int64_t qi = threadIdx.x + (int64_t)u * MS_THREADS;
                 if (qi < nq) {
+                    if (ADD) v[u] = make_float4(__fadd_rn(v[u].x, rv[u].x), __fadd_rn(v[u].y, rv[u].y),
+                                                __fadd_rn(v[u].z, rv[u].z), __fadd_rn(v[u].w, rv[u].w));
                     if (RELU) {
                         v[u] = make_float4(relu1(v[u].x), relu1(v[u].y), relu1(v[u].z), relu1(v[u].w));
                         reinterpret_cast<float4*>(y + b * inner + off)[qi] = v[u];
@@ -94,12 +103,14 @@ k_measure_stats(const float* x, float* y, int64_t B, int64_t inner, int vec, dou
             }
             if ((int64_t)threadIdx.x < (len & 3)) {     // only the last tile of a row can have a tail (inner%4==0 => none)
                 float e = src[(nq << 2) + threadIdx.x];
+                if (ADD) e = __fadd_rn(e, r[b * inner + off + (nq << 2) + threadIdx.x]);
                 if (RELU) { e = relu1(e); y[b * inner + off + (nq << 2) + threadIdx.x] = e; }
                 mn = fminf(mn, e); mx = fmaxf(mx, e); fs += e; fq += e * e;
             }
         } else {
             for (int64_t j = threadIdx.x; j < len; j += MS_THREADS) {
                 float e = src[j];
+                if (ADD) e = __fadd_rn(e, r[b * inner + off + j]);
                 if (RELU) { e = relu1(e); y[b * inner + off + j] = e; }
                 mn = fminf(mn, e); mx = fmaxf(mx, e); fs += e; fq += e * e;
             }
@@ -164,21 +175,29 @@ k_measure_stats(const float* x, float* y, int64_t B, int64_t inner, int vec, dou
     }
 }
 
-static int measure_launch(const float* x, float* y, int64_t B, int64_t inner, double* stats, void* ws, size_t ws_bytes, void* stream);
+static int measure_launch(const float* x, const float* r, float* y, int64_t B, int64_t inner, double* stats, void* ws, size_t ws_bytes, void* stream);
 
 extern "C" int qb_measure_stats(const float* x, int64_t B, int64_t inner, double* stats, void* ws, size_t ws_bytes,
                                 void* stream) {
-    return measure_launch(x, nullptr, B, inner, stats, ws, ws_bytes, stream);
+    return measure_launch(x, nullptr, nullptr, B, inner, stats, ws, ws_bytes, stream);
 }
 
 /* y = relu(x) (y may be x: in place) plus the QuantMeasure statistics of y in the same pass. */
 extern "C" int qb_relu_measure(const float* x, float* y, int64_t B, int64_t inner, double* stats, void* ws, size_t ws_bytes,
                                void* stream) {
     QB_CHECK_ARG(y, "qb_relu_measure: null output");
-    return measure_launch(x, y, B, inner, stats, ws, ws_bytes, stream);
+    return measure_launch(x, nullptr, y, B, inner, stats, ws, ws_bytes, stream);
 }
 
-static int measure_launch(const float* x, float* y, int64_t B, int64_t inner, double* stats, void* ws, size_t ws_bytes, void* stream) {
+/* y = relu(x + r) (y may be x: in place; r must not alias y) plus the QuantMeasure statistics of y in the same pass. */
+extern "C" int qb_add_relu_measure(const float* x, const float* r, float* y, int64_t B, int64_t inner, double* stats, void* ws,
+                                   size_t ws_bytes, void* stream) {
+    QB_CHECK_ARG(y && r, "qb_add_relu_measure: null pointer");
+    QB_CHECK_ARG(r != y, "qb_add_relu_measure: the residual must not alias the output");
+    return measure_launch(x, r, y, B, inner, stats, ws, ws_bytes, stream);
+}
+
+static int measure_launch(const float* x, const float* r, float* y, int64_t B, int64_t inner, double* stats, void* ws, size_t ws_bytes, void* stream) {
     QB_CHECK_ARG(x && stats && ws, "qb_measure_stats: null pointer");
     QB_CHECK_ARG(B > 0 && inner > 0, "qb_measure_stats: B=%lld inner=%lld (empty input has no range)", (long long)B,
                  (long long)inner);
@@ -192,15 +211,16 @@ static int measure_launch(const float* x, float* y, int64_t B, int64_t inner, do
     double* psq = psum + MS_MAX_BLOCKS;
     unsigned int* row_max = reinterpret_cast<unsigned int*>(base + MS_FIXED_BYTES);
     unsigned int* row_min = row_max + B;
-    const int vec = (((reinterpret_cast<uintptr_t>(x) | reinterpret_cast<uintptr_t>(y)) & 15) == 0) && (inner % 4 == 0);
+    const int vec = (((reinterpret_cast<uintptr_t>(x) | reinterpret_cast<uintptr_t>(y) | reinterpret_cast<uintptr_t>(r)) & 15) == 0) && (inner % 4 == 0);
     const int64_t T = B * ((inner + MS_TILE - 1) / MS_TILE);
     int sms = qb_sm_count();
     if (sms <= 0) sms = 148;
     int64_t cap = (int64_t)sms * 8;
     if (cap > MS_MAX_BLOCKS) cap = MS_MAX_BLOCKS;
     int grid = (int)(T < cap ? T : cap);
-    if (y) k_measure_stats<true><<<grid, MS_THREADS, 0, qb_stream(stream)>>>(x, y, B, inner, vec, stats, row_max, row_min, psum, psq, counter);
-    else k_measure_stats<false><<<grid, MS_THREADS, 0, qb_stream(stream)>>>(x, nullptr, B, inner, vec, stats, row_max, row_min, psum, psq, counter);
+    if (y && r) k_measure_stats<2><<<grid, MS_THREADS, 0, qb_stream(stream)>>>(x, r, y, B, inner, vec, stats, row_max, row_min, psum, psq, counter);
+    else if (y) k_measure_stats<1><<<grid, MS_THREADS, 0, qb_stream(stream)>>>(x, nullptr, y, B, inner, vec, stats, row_max, row_min, psum, psq, counter);
+    else k_measure_stats<0><<<grid, MS_THREADS, 0, qb_stream(stream)>>>(x, nullptr, nullptr, B, inner, vec, stats, row_max, row_min, psum, psq, counter);
     QB_LAUNCH_CHECK();
     return QB_OK;
 }

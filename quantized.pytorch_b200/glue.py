@@ -64,6 +64,24 @@ class _ReLUFn(torch.autograd.Function):
         return torch.ops.aten.threshold_backward(g, out, 0), None
 
 
+class _AddReLUFn(torch.autograd.Function):
+    """relu(y + res) written into y, plus the statistics of the result; the masked gradient goes to both addends."""
+
+    @staticmethod
+    def forward(ctx, y, res):
+        out, stats = _abi.add_relu_measure(y, res)
+        ctx.mark_dirty(y)
+        ctx.save_for_backward(out)
+        _last["stats"] = stats
+        return out
+
+    @staticmethod
+    def backward(ctx, g):
+        (out,) = ctx.saved_tensors
+        dg = torch.ops.aten.threshold_backward(g, out, 0)
+        return dg, dg
+
+
 class ReLU(nn.ReLU):
     """torch.nn.ReLU whose dense fp32 CUDA path also delivers the next QuantMeasure's statistics:
     the quantized layer that consumes the output then skips its own statistics pass.  Values and gradient are torch's."""
@@ -78,6 +96,26 @@ class ReLU(nn.ReLU):
             stats, _last["stats"] = _last["stats"], None
         else:
             out, stats = _abi.relu_measure(x, None if self.inplace else torch.empty_like(x))
+        if stats is not None:
+            Q._stash_fwd_stats(out, stats)
+        return out
+
+    def add_relu(self, y, res):
+        """``y += res; return relu(y)`` - the tail of a residual block (models/resnet_quantized.py:62-68, 105-112) - as ONE
+        pass that also delivers the next QuantMeasure's statistics.  Same values as the two torch ops (the sum is rounded
+        to fp32 before the clamp).  Falls back to exactly those two ops whenever the fused kernel does not apply."""
+        from . import quantize as Q
+        dense = y.is_contiguous() or (y.dim() == 4 and y.is_contiguous(memory_format=torch.channels_last))
+        if not (self.inplace and self.training and y.is_cuda and y.dtype == torch.float32 and res.dtype == torch.float32
+                and y.dim() >= 2 and dense and y.numel() > 0 and y.shape == res.shape and y.stride() == res.stride()
+                and y.data_ptr() != res.data_ptr()):
+            y += res
+            return self.forward(y)
+        if torch.is_grad_enabled() and (y.requires_grad or res.requires_grad):
+            out = _AddReLUFn.apply(y, res)
+            stats, _last["stats"] = _last["stats"], None
+        else:
+            out, stats = _abi.add_relu_measure(y, res)
         if stats is not None:
             Q._stash_fwd_stats(out, stats)
         return out

@@ -41,13 +41,13 @@ def _maxpool(q):
     return nn.MaxPool2d
 
 
-def _relu(q):
-    """nn.ReLU(inplace=True) (resnet_quantized.py:47,147); native module set: glue.ReLU (same values, plus the statistics
-    the next quantized layer needs)."""
+def _relu(q, inplace=True):
+    """nn.ReLU(inplace=True) (resnet_quantized.py:47,147) / nn.ReLU() (mobilenet_quantized.py:38-50); native module set:
+    glue.ReLU (same values, plus the statistics the next quantized layer needs)."""
     if getattr(q, "NATIVE_GLUE", False):
         from . import glue
-        return glue.ReLU(inplace=True)
-    return nn.ReLU(inplace=True)
+        return glue.ReLU(inplace=inplace)
+    return nn.ReLU(inplace=inplace)
 
 
 class _Identity(nn.Module):
@@ -71,7 +71,10 @@ class BasicBlock(nn.Module):
     def forward(self, x):
         y = self.relu(self.bn1(self.conv1(x)))
         y = self.bn2(self.conv2(y))
-        y += x if self.downsample is None else self.downsample(x)
+        res = x if self.downsample is None else self.downsample(x)
+        if hasattr(self.relu, "add_relu"):              # native glue: residual add + ReLU + next layer's statistics
+            return self.relu.add_relu(y, res)
+        y += res
         return self.relu(y)
 
 
@@ -94,7 +97,10 @@ class Bottleneck(nn.Module):
         y = self.relu(self.bn1(self.conv1(x)))
         y = self.relu(self.bn2(self.conv2(y)))
         y = self.bn3(self.conv3(y))
-        y += x if self.downsample is None else self.downsample(x)
+        res = x if self.downsample is None else self.downsample(x)
+        if hasattr(self.relu, "add_relu"):
+            return self.relu.add_relu(y, res)
+        y += res
         return self.relu(y)
 
 
@@ -196,8 +202,8 @@ class _DWSeparable(nn.Module):
     def __init__(self, q, cin, cout, stride):
         super().__init__()
         self.components = nn.Sequential(
-            _qconv(q, cin, cin, 3, stride, 1, groups=cin, bias=True), _qbn(q, cin), nn.ReLU(),
-            _qconv(q, cin, cout, 1), _qbn(q, cout), nn.ReLU())
+            _qconv(q, cin, cin, 3, stride, 1, groups=cin, bias=True), _qbn(q, cin), _relu(q, False),
+            _qconv(q, cin, cout, 1), _qbn(q, cout), _relu(q, False))
 
     def forward(self, x):
         return self.components(x)
@@ -214,7 +220,7 @@ class QMobileNet(nn.Module):
         if not shallow:
             plan += [(512, 512, 1)] * 5
         plan += [(512, 1024, 2), (1024, 1024, 1)]
-        layers = [_qconv(q, 3, c(32), 3, 2, 1), _qbn(q, c(32)), nn.ReLU(inplace=True)]
+        layers = [_qconv(q, 3, c(32), 3, 2, 1), _qbn(q, c(32)), _relu(q, True)]
         layers += [_DWSeparable(q, c(a), c(b), s) for a, b, s in plan]
         self.features = nn.Sequential(*layers)
         self.avg_pool = nn.AvgPool2d(7)

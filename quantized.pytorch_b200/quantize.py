@@ -322,6 +322,14 @@ def _contraction_backward(ctx, g, x, w):
     else:
         stride, padding, dilation, groups = ctx.conv
         bias_sizes = [w.shape[0]] if ctx.has_bias else None
+        if (USE_DW_KERNEL and groups > 1 and groups == x.shape[1] and dilation == (1, 1) and stride[0] == stride[1]
+                and padding[0] == padding[1] and g.is_cuda and _abi.conv_dw_bwd_supported(g, x, w, stride[0], padding[0])):
+            # depthwise 3x3: native streaming kernels (conv_dw.cu) instead of cuDNN's grouped backward + a bias reduction
+            if need_x:
+                dx = _abi.conv_dw_dgrad(g_input, w, x.shape, stride[0], padding[0])
+            if need_w or need_b:
+                dw, db = _abi.conv_dw_wgrad(g_param, x, stride[0], padding[0], bool(need_b))
+            return dx, (dw if need_w else None), db
         if need_x:
             dx = torch.ops.aten.convolution_backward(g_input, x, w, bias_sizes, stride, padding, dilation, False,
                                                      [0, 0], groups, [True, False, False])[0]
@@ -528,11 +536,25 @@ class _QBase(QuantNode):
 # gemm_i8.cu); otherwise the contraction of the already fake-quantized tensors goes to cuDNN / cuBLAS.
 USE_INT8_TENSOR_CORES = True
 USE_STEM_KERNEL = True
+USE_DW_KERNEL = True       # depthwise 3x3 convs on the codes (conv_dw.cu); False: F.conv2d on the fake-quantized tensors
+
+
+def _conv_dw_supported(mod, x):
+    """Depthwise (groups == C_in == C_out) 3x3 geometry: streaming integer kernel on the codes (conv_dw.cu)."""
+    st, pd, dl = _pair(mod.stride), _pair(mod.padding), _pair(mod.dilation)
+    kh, kw = mod.kernel_size
+    return (USE_DW_KERNEL and mod.groups == mod.in_channels == mod.out_channels and mod.groups > 1 and dl == (1, 1)
+            and st[0] == st[1] and pd[0] == pd[1] and not isinstance(pd[0], str) and mod.num_bits <= 8
+            and mod.num_bits_weight <= 8 and (x.shape[2] + 2 * pd[0] - kh) // st[0] + 1 >= 1
+            and (x.shape[3] + 2 * pd[1] - kw) // st[1] + 1 >= 1 and x.numel() < 2 ** 31
+            and _abi.conv_dw_supported(mod.in_channels, kh, kw, st[0], pd[0]))
 
 
 def _conv_i8_supported(mod, x):
-    if not (USE_INT8_TENSOR_CORES and x.dim() == 4 and mod.groups == 1 and mod.padding_mode == 'zeros'):
+    if not (USE_INT8_TENSOR_CORES and x.dim() == 4 and mod.padding_mode == 'zeros'):
         return False
+    if mod.groups != 1:
+        return _conv_dw_supported(mod, x)
     kh, kw = mod.kernel_size
     st, pd, dl = _pair(mod.stride), _pair(mod.padding), _pair(mod.dilation)
     if not (dl == (1, 1) and st[0] == st[1] and st[0] in (1, 2) and pd[0] == pd[1] and not isinstance(pd[0], str)
@@ -580,7 +602,13 @@ class _QTensorCoreFn(Function):
         if conv:
             B, Cin, H, W = x.shape
             kh, kw = mod.kernel_size
-            if Cin % 32 != 0:                                               # first layer: thread-built im2col operand
+            if mod.groups != 1:                                             # depthwise: streaming kernel on the codes
+                stats = torch.empty(8, dtype=torch.float64, device=x.device) if mod.training else None
+                out = _abi.conv_dw_fwd(codes, wcodes, B, H, W, Cin, kh, kw, _pair(mod.stride)[0], _pair(mod.padding)[0],
+                                       rng, bits_a, mod.weight_min, mod.weight_max, bits_w, bias=qbias, out_stats=stats)
+                if stats is not None:
+                    _stash_fwd_stats(out, stats)
+            elif Cin % 32 != 0:                                             # first layer: thread-built im2col operand
                 out = _abi.conv_stem_fwd(codes, wcodes, B, H, W, Cin, mod.out_channels, kh, kw, _pair(mod.stride)[0],
                                          _pair(mod.padding)[0], rng, bits_a, mod.weight_min, mod.weight_max, bits_w, tapsum,
                                          bias=qbias)

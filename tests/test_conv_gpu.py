@@ -200,3 +200,170 @@ def test_conv_stem_wgrad(lib, case):
     F.conv2d(xq, w32, None, stride, pad).backward(gd)
     rel_cudnn = float((w32.grad.cpu().double() - ref).norm() / ref.norm())
     assert rel < max(2.0 * rel_cudnn, 5e-4), (rel, rel_cudnn)      # tiny inputs: cuDNN picks an fp32 kernel, tf32 noise does not average out
+
+
+DW_CASES = [  # B, C, H, W, stride, pad
+    (2, 32, 112, 112, 1, 1),      # MobileNet dw1
+    (2, 64, 112, 112, 2, 1),      # dw2 (stride 2)
+    (3, 128, 56, 56, 1, 1),
+    (2, 256, 28, 28, 2, 1),
+    (4, 512, 14, 14, 1, 1),
+    (5, 1024, 7, 7, 1, 1),        # half of the pixels on the border
+    (3, 1024, 7, 7, 2, 1),
+    (2, 24, 9, 13, 1, 1),         # channel groups do not divide the CTA: weights rebuilt on the fly
+    (1, 8, 3, 3, 1, 1),           # every pixel a border pixel
+    (2, 20, 10, 10, 1, 0),        # no padding
+    (300, 8, 6, 6, 1, 1),         # many samples per CTA: per-sample extrema slots
+]
+
+
+@pytest.mark.parametrize("case", DW_CASES)
+@pytest.mark.parametrize("relu", [True, False])
+@pytest.mark.parametrize("use_bias", [False, True])
+def test_conv_dw_fwd(lib, case, relu, use_bias):
+    """qb_conv_dw_fwd (depthwise 3x3 on the codes) against F.conv2d(groups=C) on the same fake-quantized tensors in fp64
+    and in the reference's fp32 (north_star: dequantised conv outputs within 1e-4 relative L2), with the fused output
+    statistics against qb_measure_stats."""
+    B, C, H, W, stride, pad = case
+    gen = torch.Generator().manual_seed(sum(case))
+    x = torch.randn(B, C, H, W, generator=gen)
+    x = x.clamp_min(0) if relu else x + 0.7
+    w = torch.randn(C, 1, 3, 3, generator=gen) * 0.2
+    bias = torch.randn(C, generator=gen) * 0.1 if use_bias else None
+    xd = x.to(DEV).contiguous(memory_format=torch.channels_last)
+    rng = torch.tensor([float(x.min()), float(x.max())], device=DEV)
+    codes = torch.empty((B, C, H, W), dtype=torch.uint8, device=DEV).contiguous(memory_format=torch.channels_last)
+    xq = lib.fakequant_affine(xd, 8, range_dev=rng, codes=codes)
+    rmin, rmax = torch.empty(C, device=DEV), torch.empty(C, device=DEV)
+    wq, wcodes, _ = lib.fakequant_rows_conv(w.to(DEV), 8, rmin, rmax)
+    bd = bias.to(DEV) if use_bias else None
+    stats = torch.empty(8, dtype=torch.float64, device=DEV)
+    out = lib.conv_dw_fwd(codes, wcodes, B, H, W, C, 3, 3, stride, pad, rng, 8, rmin, rmax, 8, bias=bd, out_stats=stats)
+    out_plain = lib.conv_dw_fwd(codes, wcodes, B, H, W, C, 3, 3, stride, pad, rng, 8, rmin, rmax, 8, bias=bd)
+    torch.cuda.synchronize()
+    assert torch.equal(out, out_plain)
+    assert out.is_contiguous(memory_format=torch.channels_last)
+    ref_stats = lib.measure_stats(out)
+    assert torch.equal(stats[[0, 1, 4, 5, 6, 7]], ref_stats[[0, 1, 4, 5, 6, 7]]), (stats, ref_stats)
+    assert torch.allclose(stats[2:4], ref_stats[2:4], rtol=1e-6, atol=1e-6 * float(ref_stats[3].sqrt())), (stats, ref_stats)
+    stats2 = torch.empty(8, dtype=torch.float64, device=DEV)
+    lib.conv_dw_fwd(codes, wcodes, B, H, W, C, 3, 3, stride, pad, rng, 8, rmin, rmax, 8, bias=bd, out_stats=stats2)
+    assert torch.equal(stats[[0, 1, 4, 5, 6, 7]], stats2[[0, 1, 4, 5, 6, 7]])          # workspace left clean
+    ref64 = F.conv2d(xq.double().cpu(), wq.double().cpu(), bias.double() if use_bias else None, stride, pad, 1, C)
+    assert out.shape == ref64.shape
+    rel = float((out.cpu().double() - ref64).norm() / ref64.norm())
+    assert rel < 2e-6, rel
+    ref32 = F.conv2d(xq.cpu(), wq.cpu(), bias, stride, pad, 1, C)       # what the reference computes (fp32, CPU)
+    rel32 = float((out.cpu() - ref32).norm() / ref32.norm())
+    assert rel32 < 1e-5, rel32
+
+
+def test_conv_dw_unsupported_is_an_error(lib):
+    x = torch.zeros((1, 8, 8, 8), dtype=torch.uint8, device=DEV)
+    z = torch.zeros(8, device=DEV)
+    with pytest.raises(lib.QB200Error):
+        lib.conv_dw_fwd(x, x, 1, 8, 8, 8, 5, 5, 1, 2, z, 8, z, z, 8)        # 5x5
+    with pytest.raises(lib.QB200Error):
+        lib.conv_dw_fwd(x, x, 1, 8, 8, 6, 3, 3, 1, 1, z, 8, z, z, 8)        # C % 4 != 0
+
+
+def test_qconv2d_depthwise_uses_dw_kernel_and_matches_oracle(lib):
+    """QConv2d(C, C, 3, groups=C) (mobilenet_quantized.py:24) routes to qb_conv_dw_fwd, hands its output statistics to the
+    following QuantMeasure, and agrees with the CPU oracle module and with the F.conv2d route, forward and backward."""
+    import qtorch_b200  # noqa: F401
+    from qtorch_b200 import quantize as Q
+    from oracle import qref_modules
+    torch.manual_seed(11)
+    kw = dict(kernel_size=3, stride=2, padding=1, groups=64, bias=False, num_bits=8, num_bits_weight=8, num_bits_grad=None)
+    ref = qref_modules.QConv2d(64, 64, **kw).train()
+    m = Q.QConv2d(64, 64, **kw)
+    m.load_state_dict(ref.state_dict())
+    m = m.to(DEV).train()
+    x = torch.randn(4, 64, 30, 30).clamp_min(0)
+    xr = x.clone().requires_grad_(True)
+    yr = ref(xr)
+    yr.square().mean().backward()
+    xd = x.to(DEV).requires_grad_(True)
+    lib.profile_begin()
+    y1 = m(xd)
+    names = [r[0] for r in lib.profile_end()]
+    assert "qb_conv_dw_fwd" in names, names
+    assert Q._take_fwd_stats(y1) is not None          # the next layer's range reduction came with the output
+    y1.square().mean().backward()
+    assert float((y1.detach().cpu() - yr.detach()).norm() / yr.detach().norm()) < 1e-4
+    assert float((m.weight.grad.cpu() - ref.weight.grad).norm() / ref.weight.grad.norm()) < 1e-3
+    assert float((xd.grad.cpu() - xr.grad).norm() / xr.grad.norm()) < 1e-3
+    for k in ("quantize_input.running_min", "quantize_input.running_max"):
+        np.testing.assert_allclose(m.state_dict()[k].cpu().numpy(), ref.state_dict()[k].numpy(), rtol=1e-6, atol=1e-7)
+    m2 = Q.QConv2d(64, 64, **kw)
+    m2.load_state_dict(ref.state_dict())
+    m2 = m2.to(DEV).train()
+    Q.USE_DW_KERNEL = False
+    try:
+        y2 = m2(x.to(DEV))
+    finally:
+        Q.USE_DW_KERNEL = True
+    assert float((y1 - y2).detach().norm() / y2.detach().norm()) < 1e-4
+
+
+DW_BWD_CASES = [  # B, C, H, W, stride, pad
+    (2, 32, 112, 112, 1, 1),
+    (2, 64, 112, 112, 2, 1),
+    (3, 128, 57, 55, 2, 1),       # odd sizes: last row / column of the input receives no stride-2 tap
+    (4, 512, 14, 14, 1, 1),
+    (5, 1024, 7, 7, 1, 1),
+    (3, 1024, 7, 7, 2, 1),
+    (1, 8, 3, 3, 1, 1),
+    (2, 16, 10, 10, 1, 0),
+    (40, 8, 6, 6, 2, 1),
+]
+
+
+@pytest.mark.parametrize("case", DW_BWD_CASES)
+def test_conv_dw_backward(lib, case):
+    """qb_conv_dw_dgrad / qb_conv_dw_wgrad against aten::convolution_backward (groups = C) in fp64 on the same tensors."""
+    B, C, H, W, stride, pad = case
+    gen = torch.Generator().manual_seed(sum(case) + 3)
+    x = torch.randn(B, C, H, W, generator=gen)
+    w = torch.randn(C, 1, 3, 3, generator=gen) * 0.2
+    Ho, Wo = (H + 2 * pad - 3) // stride + 1, (W + 2 * pad - 3) // stride + 1
+    g = torch.randn(B, C, Ho, Wo, generator=gen)
+    xd = x.to(DEV).contiguous(memory_format=torch.channels_last)
+    gd = g.to(DEV).contiguous(memory_format=torch.channels_last)
+    wd = w.to(DEV)
+    assert lib.conv_dw_bwd_supported(gd, xd, wd, stride, pad) or H * W == 1
+    dx = lib.conv_dw_dgrad(gd, wd, x.shape, stride, pad)
+    dw, db = lib.conv_dw_wgrad(gd, xd, stride, pad, True)
+    dw2, db2 = lib.conv_dw_wgrad(gd, xd, stride, pad, False)
+    torch.cuda.synchronize()
+    assert db2 is None and torch.equal(dw, dw2)                           # deterministic
+    rx, rw, rb = torch.ops.aten.convolution_backward(g.double(), x.double(), w.double(), [C], [stride, stride], [pad, pad],
+                                                     [1, 1], False, [0, 0], C, [True, True, True])
+    assert dx.shape == rx.shape and dx.is_contiguous(memory_format=torch.channels_last)
+    for got, ref in ((dx, rx), (dw, rw), (db, rb)):
+        rel = float((got.cpu().double() - ref).norm() / ref.norm())
+        assert rel < 2e-6, rel
+
+
+def test_qconv2d_depthwise_backward_uses_native_kernels(lib):
+    import qtorch_b200  # noqa: F401
+    from qtorch_b200 import quantize as Q
+    torch.manual_seed(12)
+    kw = dict(kernel_size=3, stride=1, padding=1, groups=32, bias=True, num_bits=8, num_bits_weight=8, num_bits_grad=None)
+    m = Q.QConv2d(32, 32, **kw).to(DEV).train()
+    m2 = Q.QConv2d(32, 32, **kw).to(DEV).train()
+    m2.load_state_dict(m.state_dict())
+    x = torch.randn(4, 32, 20, 20, device=DEV).clamp_min(0)
+    xa, xb = x.clone().requires_grad_(), x.clone().requires_grad_()
+    y = m(xa)
+    lib.profile_begin()
+    y.square().mean().backward()
+    names = [r[0] for r in lib.profile_end()]
+    assert "qb_conv_dw_dgrad" in names and "qb_conv_dw_wgrad" in names, names
+    Q.USE_DW_KERNEL = False
+    try:
+        m2(xb).square().mean().backward()
+    finally:
+        Q.USE_DW_KERNEL = True
+    for a, b in ((xa.grad, xb.grad), (m.weight.grad, m2.weight.grad), (m.bias.grad, m2.bias.grad)):
+        assert float((a - b).norm() / b.norm()) < 1e-4

@@ -72,3 +72,36 @@ def test_relu_with_statistics(lib, shape, nhwc):
     qm(y)
     names = [n for n, _, _ in lib.profile_end()]
     assert "qb_measure_stats" not in names and "qb_measure_finalize" in names, names
+
+
+@pytest.mark.parametrize("shape,nhwc", [((4, 64, 20, 20), True), ((3, 16, 9, 7), False), ((5, 32, 1, 1), True), ((6, 40), False)])
+def test_add_relu_with_statistics(lib, shape, nhwc):
+    """glue.ReLU.add_relu: the block tail `y += res; y = relu(y)` (models/resnet_quantized.py:62-68) in one pass: torch's
+    values bit for bit, the masked gradient on both addends, and the statistics of the result for the next QuantMeasure."""
+    from qtorch_b200 import glue, quantize as Q
+    gen = torch.Generator().manual_seed(sum(shape) + 1)
+    a0, r0 = torch.randn(shape, generator=gen).to(DEV), torch.randn(shape, generator=gen).to(DEV)
+    if nhwc:
+        a0, r0 = a0.contiguous(memory_format=torch.channels_last), r0.contiguous(memory_format=torch.channels_last)
+    leaves = [t.clone().requires_grad_() for t in (a0, r0, a0, r0)]
+    m = glue.ReLU(inplace=True).train()
+    lib.profile_begin()
+    ya = m.add_relu(leaves[0] * 1.0, leaves[1] * 1.0)
+    names = [n for n, _, _ in lib.profile_end()]
+    assert names == ["qb_add_relu_measure"], names
+    yb = leaves[2] * 1.0
+    yb += leaves[3] * 1.0
+    yb = torch.nn.functional.relu(yb)
+    assert torch.equal(ya, yb)
+    want = lib.measure_stats(ya.detach())
+    got = Q._take_fwd_stats(ya.detach())
+    assert got is not None and torch.equal(got, want)
+    go = torch.randn(shape, generator=gen).to(DEV)
+    if nhwc:
+        go = go.contiguous(memory_format=torch.channels_last)
+    ya.backward(go); yb.backward(go)
+    assert torch.equal(leaves[0].grad, leaves[2].grad) and torch.equal(leaves[1].grad, leaves[3].grad)
+    # layouts that differ fall back to the two torch ops, same values
+    if len(shape) == 4 and shape[2] > 1:
+        y2 = m.add_relu(a0.clone(), r0.contiguous())
+        assert torch.equal(y2, torch.nn.functional.relu(a0 + r0))

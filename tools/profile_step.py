@@ -1,4 +1,4 @@
-"""One eager ResNet-18 b256 8-bit train step between cudaProfilerStart/Stop, for ncu
+"""One eager ResNet-18 (or MobileNet: argv[2]) b256 8-bit train step between cudaProfilerStart/Stop, for ncu
 (`ncu --profile-from-start off ...`).  Not a benchmark: numbers printed under a profiler are never reported."""
 import os
 import sys
@@ -12,9 +12,11 @@ from qtorch_b200 import models, quantize as Q  # noqa: E402
 
 def main():
     batch = int(sys.argv[1]) if len(sys.argv) > 1 else 256
+    name = sys.argv[2] if len(sys.argv) > 2 else "resnet18"          # or "mobilenet" (BASELINE configs[3])
     dev = torch.device("cuda:0")
     torch.manual_seed(0)
-    model = models.resnet_quantized(Q, depth=18, dataset="imagenet").to(dev).train()
+    model = (models.mobilenet_quantized(Q) if name == "mobilenet" else models.resnet_quantized(Q, depth=18, dataset="imagenet"))
+    model = model.to(dev).train()
     opt = torch.optim.SGD(model.parameters(), lr=0.1, momentum=0.9)
     crit = torch.nn.CrossEntropyLoss()
     x = torch.randn(batch, 3, 224, 224, device=dev)
