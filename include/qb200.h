@@ -329,6 +329,11 @@ int qb_rangebn2_apply(const float* x, float* out, int64_t B, int64_t C, int64_t 
 /* nn.ReLU(inplace) between the modules (models/resnet_quantized.py:52-68,147): y = relu(x) (y may alias x) and, in the same
  * pass, the QuantMeasure statistics block (as qb_measure_stats) of y for the quantized layer that consumes it. */
 int qb_relu_measure(const float* x, float* y, int64_t B, int64_t inner, double* stats, void* ws, size_t ws_bytes, void* stream);
+/* Backward of that ReLU with the range of its result: dx = relu_out <= 0 ? 0 : grad_out (aten::threshold_backward) and
+ * range_out float[2] = {min(dx), max(dx)}, which the gradient quantizer of the layer that receives dx asks for next
+ * (quantize.py:126,132).  dx may alias grad_out.  ws = qb_minmax_ws_bytes() bytes zero-filled once. */
+int qb_relu_bwd_minmax(const float* grad_out, const float* relu_out, float* dx, int64_t n, float* range_out, void* ws,
+                       size_t ws_bytes, void* stream);
 /* The residual add and ReLU that close a ResNet block (`out += residual; out = relu(out)`, models/resnet_quantized.py:62-68,
  * 105-112) in one pass: y = relu(x + r) (y may alias x, r must not alias y; x + r rounded to fp32 before the clamp, as the
  * two torch ops do) plus the statistics block of y. */

@@ -27,6 +27,7 @@ PROTOTYPES = {
     "qb_measure_stats": (_i32, [_p, _i64, _i64, _p, _p, _sz, _p]),
     "qb_relu_measure": (_i32, [_p, _p, _i64, _i64, _p, _p, _sz, _p]),
     "qb_add_relu_measure": (_i32, [_p, _p, _p, _i64, _i64, _p, _p, _sz, _p]),
+    "qb_relu_bwd_minmax": (_i32, [_p, _p, _p, _i64, _p, _p, _sz, _p]),
     "qb_measure_finalize": (_i32, [_p, _p, _p, _p, _p, _p, _dbl, _i32, _i32, _i32, _p, _p]),
     "qb_fakequant_affine": (_i32, [_p, _p, _p, _i64, _i32, _p, _dbl, _dbl, _i32, _p]),
     "qb_selftest_div": (_i32, [_p, _flt, _p, _p, _i64, _p]),
@@ -229,6 +230,18 @@ def relu_measure(x, out=None):
     ws = workspace("measure", lib.qb_measure_ws_bytes(B), x.device)
     _run("qb_relu_measure", 8 * x.numel(), _ptr(x), _ptr(out), B, inner, _ptr(stats), _ptr(ws), ws.numel(), _stream())
     return out, stats
+
+
+def relu_bwd_minmax(g, out):
+    """(dx, range) with dx = where(out <= 0, 0, g) and range = device float[2] {min(dx), max(dx)}; g and out must share
+    shape and (dense) memory layout."""
+    lib = load()
+    dx = torch.empty_like(out)
+    rng = torch.empty(2, dtype=torch.float32, device=g.device)
+    ws = workspace("minmax", lib.qb_minmax_ws_bytes(), g.device)
+    _run("qb_relu_bwd_minmax", 12 * g.numel(), _ptr(g), _ptr(out), _ptr(dx), g.numel(), _ptr(rng), _ptr(ws), ws.numel(),
+         _stream())
+    return dx, rng
 
 
 def add_relu_measure(x, r, out=None):

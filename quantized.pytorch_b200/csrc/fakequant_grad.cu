@@ -136,6 +136,102 @@ extern "C" int qb_minmax(const float* x, int64_t n, float* range_out, void* ws, 
 }
 
 // ------------------------------------------------------------------------------------------------
+// ReLU backward + the range of its result in one pass (SURVEY section 8f N1 glue).  dx = out <= 0 ? 0 : g is what
+// aten::threshold_backward computes for nn.ReLU (models/resnet_quantized.py:47-75); the gradient quantizer of the RangeBN
+// / QConv2d that receives dx needs float(dx.min()), float(dx.max()) next (quantize.py:126,132), so the min/max sweep
+// (a second 4 B/elem read) rides along: 12 B/elem for both instead of 12 + 4.
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(GQ_THREADS)
+k_relu_bwd_minmax(const float* __restrict__ g, const float* __restrict__ out, float* __restrict__ dx, int64_t n, int vec,
+                  float* range_out, MinMaxWs* ws) {
+    __shared__ float sm[64];
+    __shared__ bool last;
+    float mn = QB_INF, mx = -QB_INF;
+    const int64_t stride = (int64_t)gridDim.x * GQ_THREADS;
+    const int64_t tid = (int64_t)blockIdx.x * GQ_THREADS + threadIdx.x;
+    if (vec) {
+        const int64_t noct = n >> 3;
+        constexpr int U = 2;
+        int64_t i = tid;
+        for (; i + (U - 1) * stride < noct; i += U * stride) {
+            F8 a[U], b[U];
+#pragma unroll
+            for (int u = 0; u < U; ++u) {
+                a[u] = ld256_stream(g + 8 * (i + u * stride));
+                b[u] = ld256_stream(out + 8 * (i + u * stride));
+            }
+#pragma unroll
+            for (int u = 0; u < U; ++u) {
+#pragma unroll
+                for (int j = 0; j < 8; ++j) a[u].v[j] = b[u].v[j] <= 0.0f ? 0.0f : a[u].v[j];
+                octet_minmax(a[u], mn, mx);
+                *reinterpret_cast<F8*>(dx + 8 * (i + u * stride)) = a[u];   // default policy: the consumer reads it next
+            }
+        }
+        for (; i < noct; i += stride) {
+            F8 a = ld256_stream(g + 8 * i);
+            const F8 b = ld256_stream(out + 8 * i);
+#pragma unroll
+            for (int j = 0; j < 8; ++j) a.v[j] = b.v[j] <= 0.0f ? 0.0f : a.v[j];
+            octet_minmax(a, mn, mx);
+            *reinterpret_cast<F8*>(dx + 8 * i) = a;
+        }
+        if (tid < (n & 7)) {
+            const int64_t e = (noct << 3) + tid;
+            const float v = out[e] <= 0.0f ? 0.0f : g[e];
+            dx[e] = v;
+            mn = fminf(mn, v);
+            mx = fmaxf(mx, v);
+        }
+    } else {
+        for (int64_t e = tid; e < n; e += stride) {
+            const float v = out[e] <= 0.0f ? 0.0f : g[e];
+            dx[e] = v;
+            mn = fminf(mn, v);
+            mx = fmaxf(mx, v);
+        }
+    }
+    block_reduce_minmax(mn, mx, sm);
+    if (threadIdx.x == 0) {
+        ws->pmin[blockIdx.x] = mn;
+        ws->pmax[blockIdx.x] = mx;
+        __threadfence();
+        last = (atomicAdd(&ws->counter, 1u) == gridDim.x - 1);
+    }
+    __syncthreads();
+    if (!last) return;
+    __threadfence();
+    mn = QB_INF;
+    mx = -QB_INF;
+    for (int i = threadIdx.x; i < (int)gridDim.x; i += GQ_THREADS) {
+        mn = fminf(mn, __ldcg(&ws->pmin[i]));
+        mx = fmaxf(mx, __ldcg(&ws->pmax[i]));
+    }
+    block_reduce_minmax(mn, mx, sm);
+    if (threadIdx.x == 0) {
+        range_out[0] = mn;
+        range_out[1] = mx;
+        ws->counter = 0;
+    }
+}
+
+extern "C" int qb_relu_bwd_minmax(const float* grad_out, const float* relu_out, float* dx, int64_t n, float* range_out, void* ws,
+                                  size_t ws_bytes, void* stream) {
+    QB_CHECK_ARG(grad_out && relu_out && dx && range_out && ws, "qb_relu_bwd_minmax: null pointer");
+    QB_CHECK_ARG(n > 0, "qb_relu_bwd_minmax: n=%lld", (long long)n);
+    if (ws_bytes < sizeof(MinMaxWs)) {
+        qb_set_error("qb_relu_bwd_minmax: workspace %zu < %zu bytes", ws_bytes, sizeof(MinMaxWs));
+        return QB_ERR_WORKSPACE;
+    }
+    const int vec = aligned32(grad_out) && aligned32(relu_out) && aligned32(dx);
+    const int grid = gq_grid(vec ? (n >> 3) / 2 : n / 2, 8);
+    k_relu_bwd_minmax<<<grid, GQ_THREADS, 0, qb_stream(stream)>>>(grad_out, relu_out, dx, n, vec, range_out,
+                                                                 static_cast<MinMaxWs*>(ws));
+    QB_LAUNCH_CHECK();
+    return QB_OK;
+}
+
+// ------------------------------------------------------------------------------------------------
 // zero-point stochastic quantizer (A2), range given
 // ------------------------------------------------------------------------------------------------
 template <int NOISE, bool WRITE_Y, bool WRITE_C>

@@ -42,6 +42,19 @@ class MaxPool2d(nn.MaxPool2d):
         return F.max_pool2d(x, k, s, p, self.dilation, self.ceil_mode, self.return_indices)
 
 
+def _relu_backward(g, out):
+    """aten::threshold_backward(g, out, 0); on dense fp32 CUDA tensors of one layout the native pass also leaves the
+    range of the result for the gradient quantizer that consumes it (RangeBN / QConv2d backward)."""
+    if (g.is_cuda and g.dtype == torch.float32 and out.dtype == torch.float32 and g.shape == out.shape
+            and g.stride() == out.stride() and g.numel() > 0
+            and (out.is_contiguous() or (out.dim() == 4 and out.is_contiguous(memory_format=torch.channels_last)))):
+        from . import quantize as Q
+        dg, rng = _abi.relu_bwd_minmax(g, out)
+        Q._stash_grad_range(dg, rng)
+        return dg
+    return torch.ops.aten.threshold_backward(g, out, 0)
+
+
 _last = {"stats": None}          # statistics block of the most recent _ReLUFn.forward (picked up right after apply)
 
 
@@ -61,7 +74,7 @@ class _ReLUFn(torch.autograd.Function):
     @staticmethod
     def backward(ctx, g):
         (out,) = ctx.saved_tensors
-        return torch.ops.aten.threshold_backward(g, out, 0), None
+        return _relu_backward(g, out), None
 
 
 class _AddReLUFn(torch.autograd.Function):
@@ -78,7 +91,7 @@ class _AddReLUFn(torch.autograd.Function):
     @staticmethod
     def backward(ctx, g):
         (out,) = ctx.saved_tensors
-        dg = torch.ops.aten.threshold_backward(g, out, 0)
+        dg = _relu_backward(g, out)
         return dg, dg
 
 

@@ -755,7 +755,9 @@ class _RangeBNFn(Function):
             gquant = None
             if bits_grad is not None:
                 g = _abi._f32c(g, "grad")
-                r = _abi.minmax(g)
+                r = _take_grad_range(g)                      # left by the ReLU backward that produced g (glue.py)
+                if r is None:
+                    r = _abi.minmax(g)
                 if _reducer is not None:
                     _reducer.grad_range(r)
                 gquant = dict(range=r, bits=bits_grad, noise=_grad_noise(g, True), stochastic=True, seed=_next_seed(),

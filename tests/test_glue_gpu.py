@@ -105,3 +105,47 @@ def test_add_relu_with_statistics(lib, shape, nhwc):
     if len(shape) == 4 and shape[2] > 1:
         y2 = m.add_relu(a0.clone(), r0.contiguous())
         assert torch.equal(y2, torch.nn.functional.relu(a0 + r0))
+
+
+@pytest.mark.parametrize("n", [1, 7, 8, 1000, 8 * 4096 + 3, 3_000_001])
+def test_relu_backward_with_range(lib, n):
+    """qb_relu_bwd_minmax: aten::threshold_backward's values bit for bit plus the exact {min, max} of the result."""
+    gen = torch.Generator().manual_seed(n)
+    g = torch.randn(n, generator=gen).to(DEV)
+    out = torch.randn(n, generator=gen).clamp_min(0).to(DEV)
+    dx, rng = lib.relu_bwd_minmax(g, out)
+    want = torch.ops.aten.threshold_backward(g, out, 0)
+    assert torch.equal(dx, want)
+    assert float(rng[0]) == float(want.min()) and float(rng[1]) == float(want.max())
+    dx2, rng2 = lib.relu_bwd_minmax(g, out)                       # workspace left clean
+    assert torch.equal(dx2, want) and torch.equal(rng, rng2)
+
+
+def test_rangebn_backward_takes_the_relu_range(lib):
+    """RangeBN -> glue.ReLU: the ReLU backward hands its result's range to the RangeBN gradient quantizer (no qb_minmax
+    launch), and the gradients equal those of the stock nn.ReLU route under the same injected noise."""
+    from qtorch_b200 import glue, quantize as Q
+    torch.manual_seed(3)
+    x = torch.randn(8, 32, 12, 12, device=DEV).contiguous(memory_format=torch.channels_last)
+    go = torch.randn(8, 32, 12, 12, device=DEV).contiguous(memory_format=torch.channels_last)
+    noise = (torch.rand(8, 32, 12, 12, device=DEV) - 0.5)
+    res = []
+    state = Q.RangeBN(32).state_dict()                              # reset_params draws gamma at random: share one draw
+    for relu in (glue.ReLU(inplace=True), torch.nn.ReLU(inplace=True)):
+        bn = Q.RangeBN(32)
+        bn.load_state_dict(state)
+        bn = bn.to(DEV).train()
+        relu = relu.train()
+        xi = x.clone().requires_grad_()
+        prev = Q.set_noise_provider(lambda shape: noise.clone())
+        try:
+            y = relu(bn(xi))
+            lib.profile_begin()
+            y.backward(go)
+            names = [r[0] for r in lib.profile_end()]
+        finally:
+            Q.set_noise_provider(prev)
+        res.append((xi.grad.clone(), bn.weight.grad.clone(), names))
+    assert "qb_relu_bwd_minmax" in res[0][2] and "qb_minmax" not in res[0][2], res[0][2]
+    assert "qb_minmax" in res[1][2], res[1][2]
+    assert torch.equal(res[0][0], res[1][0]) and torch.equal(res[0][1], res[1][1])
