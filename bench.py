@@ -140,6 +140,9 @@ def main_ours(args, rank, world, local_rank):
     if world > 1:
         from qtorch_b200 import dist as qdist
         qdist.init(dev)
+    # the reference's training entry point lets cuDNN pick its algorithms by measurement (main.py:106); the backward
+    # contractions that still run in cuDNN are tuned during the eager warm-up steps
+    torch.backends.cudnn.benchmark = os.environ.get("QB_CUDNN_BENCHMARK", "1") != "0"
     torch.manual_seed(0)
     model, shape, ncls = build_model(args.model, Q)
     model = model.to(dev).train()
