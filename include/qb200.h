@@ -343,6 +343,15 @@ int qb_maxpool2d_nhwc_fwd(const float* x, float* out, uint8_t* idx, int64_t B, i
                           int stride, int pad, void* stream);
 int qb_maxpool2d_nhwc_bwd(const float* grad_out, const uint8_t* idx, float* dx, int64_t B, int64_t H, int64_t W, int64_t C,
                           int k, int stride, int pad, void* stream);
+/* Backward of ReLU -> MaxPool2d as one pass (models/resnet_quantized.py:147-150, bn1 -> relu -> maxpool): dx is the gradient
+ * w.r.t. the ReLU's input.  pool_out = the forward output of the pooling (its window maxima): a window whose maximum is not
+ * positive contributes nothing, which is what aten::threshold_backward after max_pool2d_backward yields.  range_out
+ * float[2] = {min(dx), max(dx)} for the gradient quantizer that consumes dx.  ws = qb_maxpool2d_relu_bwd_ws_bytes() bytes
+ * zero-filled once. */
+size_t qb_maxpool2d_relu_bwd_ws_bytes(void);
+int qb_maxpool2d_relu_nhwc_bwd(const float* grad_out, const uint8_t* idx, const float* pool_out, float* dx, int64_t B, int64_t H,
+                               int64_t W, int64_t C, int k, int stride, int pad, float* range_out, void* ws, size_t ws_bytes,
+                               void* stream);
 
 /* ---------------------------------------------------------------------------------------------------
  * Cross-rank exchange of the statistic blocks of batch-sharded training: a one-shot all-reduce

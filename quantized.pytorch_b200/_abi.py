@@ -65,6 +65,8 @@ PROTOTYPES = {
     "qb_allreduce_small": (_i32, [_p, _i64, _i32, _i32, _p, _i32, _i32, _sz, _p]),
     "qb_maxpool2d_nhwc_fwd": (_i32, [_p, _p, _p, _i64, _i64, _i64, _i64, _i32, _i32, _i32, _p]),
     "qb_maxpool2d_nhwc_bwd": (_i32, [_p, _p, _p, _i64, _i64, _i64, _i64, _i32, _i32, _i32, _p]),
+    "qb_maxpool2d_relu_bwd_ws_bytes": (_sz, []),
+    "qb_maxpool2d_relu_nhwc_bwd": (_i32, [_p, _p, _p, _p, _i64, _i64, _i64, _i64, _i32, _i32, _i32, _p, _p, _sz, _p]),
     "qb_conv_stem_supported": (_i32, [_i64, _i64, _i64, _i64, _i32, _i32, _i32, _i32]),
     "qb_conv_stem_ws_bytes": (_sz, [_i64]),
     "qb_conv_stem_wgrad_ws_bytes": (_sz, [_i64, _i64, _i32, _i32]),
@@ -649,6 +651,17 @@ def maxpool2d_nhwc_bwd(g, idx, in_shape, k, stride, pad):
     _run("qb_maxpool2d_nhwc_bwd", 5 * g.numel() + 4 * dx.numel(), _ptr(g), _ptr(idx), _ptr(dx), B, H, W, Cn, int(k), int(stride),
          int(pad), _stream())
     return dx
+
+
+def maxpool2d_relu_nhwc_bwd(g, idx, pool_out, in_shape, k, stride, pad):
+    """Backward of ReLU -> MaxPool2d in one pass: (dx w.r.t. the ReLU input, device float[2] range of dx)."""
+    B, Cn, H, W = in_shape
+    dx = torch.empty(in_shape, dtype=torch.float32, device=g.device, memory_format=torch.channels_last)
+    rng = torch.empty(2, dtype=torch.float32, device=g.device)
+    ws = workspace("pool_range", load().qb_maxpool2d_relu_bwd_ws_bytes(), g.device)
+    _run("qb_maxpool2d_relu_nhwc_bwd", 9 * g.numel() + 4 * dx.numel(), _ptr(g), _ptr(idx), _ptr(pool_out), _ptr(dx), B, H, W, Cn,
+         int(k), int(stride), int(pad), _ptr(rng), _ptr(ws), ws.numel(), _stream())
+    return dx, rng
 
 
 # ----------------------------------------------------------------------------------------------

@@ -60,10 +60,21 @@ __global__ void __launch_bounds__(256) k_maxpool_fwd_nhwc(const float* __restric
     *reinterpret_cast<uint2*>(idx + e) = pk;
 }
 
+// FUSED: the pooled tensor is the output of a ReLU (models/resnet_quantized.py:147-150: bn1 -> relu -> maxpool), and dx is
+// the gradient w.r.t. the ReLU's INPUT: a window's gradient is dropped where its maximum is not positive (the element it
+// would land on has relu_out = pool_out <= 0, which is exactly where aten::threshold_backward writes 0), and {min, max} of
+// dx - the range the gradient quantizer of the RangeBN in front asks for (quantize.py:126,132) - is reduced on the way:
+// the 822 MB intermediate gradient of ResNet-18's stem is never written and re-read.
+struct PoolRangeWs { unsigned int kmax, kmin, counter, pad; };
+
+template <bool FUSED>
 __global__ void __launch_bounds__(256) k_maxpool_bwd_nhwc(const float* __restrict__ go, const uint8_t* __restrict__ idx,
-                                                          float* __restrict__ dx, PoolGeom g, uint32_t total) {
-    const uint32_t t = blockIdx.x * 256u + threadIdx.x;
-    if (t >= total) return;
+                                                          const float* __restrict__ pool_out, float* __restrict__ dx,
+                                                          PoolGeom g, uint32_t total, float* range_out, PoolRangeWs* ws) {
+    float mn = QB_INF, mx = -QB_INF;
+    // grid-stride: the FUSED launch is a few CTAs per SM, so the range costs one reduction + atomic pair per CTA
+    for (uint64_t t64 = blockIdx.x * 256u + threadIdx.x; t64 < total; t64 += (uint64_t)gridDim.x * 256u) {
+    const uint32_t t = (uint32_t)t64;
     const uint32_t c8n = (uint32_t)g.C >> 3;
     uint32_t q = fdiv(t, g.d_c8);
     const uint32_t c0 = (t - q * c8n) << 3;
@@ -92,10 +103,12 @@ __global__ void __launch_bounds__(256) k_maxpool_bwd_nhwc(const float* __restric
             const uint32_t hit_lo = pk.x ^ (code * 0x01010101u), hit_hi = pk.y ^ (code * 0x01010101u);
             if (((hit_lo - 0x01010101u) & ~hit_lo & 0x80808080u) | ((hit_hi - 0x01010101u) & ~hit_hi & 0x80808080u)) {   // any byte equal
                 const F8 gv = ld256_keep(go + e);
+                F8 pv;
+                if (FUSED) pv = ld256_keep(pool_out + e);
 #pragma unroll
                 for (int j = 0; j < 8; ++j) {
                     const uint32_t bj = ((j < 4 ? pk.x : pk.y) >> (8 * (j & 3))) & 0xffu;
-                    if (bj == code) acc[j] += gv.v[j];
+                    if (bj == code && (!FUSED || !(pv.v[j] <= 0.0f))) acc[j] += gv.v[j];
                 }
             }
         }
@@ -104,6 +117,34 @@ __global__ void __launch_bounds__(256) k_maxpool_bwd_nhwc(const float* __restric
 #pragma unroll
     for (int j = 0; j < 8; ++j) o.v[j] = acc[j];
     st256(dx + ((size_t)t << 3), o);
+    if (FUSED) {
+        mn = fminf(mn, fminf(fminf(fminf(o.v[0], o.v[1]), fminf(o.v[2], o.v[3])), fminf(fminf(o.v[4], o.v[5]), fminf(o.v[6], o.v[7]))));
+        mx = fmaxf(mx, fmaxf(fmaxf(fmaxf(o.v[0], o.v[1]), fmaxf(o.v[2], o.v[3])), fmaxf(fmaxf(o.v[4], o.v[5]), fmaxf(o.v[6], o.v[7]))));
+    }
+    }   // grid-stride loop
+    if (!FUSED) return;
+    // range of dx: block reduction, then one atomic pair per block and only when it can improve the running extrema
+    __shared__ float s_mn[8], s_mx[8];
+    __shared__ bool last;
+    mn = warp_min(mn);
+    mx = warp_max(mx);
+    if ((threadIdx.x & 31) == 0) { s_mn[threadIdx.x >> 5] = mn; s_mx[threadIdx.x >> 5] = mx; }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+#pragma unroll
+        for (int k = 1; k < 8; ++k) { mn = fminf(mn, s_mn[k]); mx = fmaxf(mx, s_mx[k]); }
+        const unsigned int emx = enc_ord(mx), emn = ~enc_ord(mn);
+        if (emx > __ldcg(&ws->kmax)) atomicMax(&ws->kmax, emx);
+        if (emn > __ldcg(&ws->kmin)) atomicMax(&ws->kmin, emn);
+        __threadfence();
+        last = (atomicAdd(&ws->counter, 1u) == gridDim.x - 1);
+        if (last) {
+            __threadfence();
+            range_out[0] = dec_ord(~__ldcg(&ws->kmin));
+            range_out[1] = dec_ord(__ldcg(&ws->kmax));
+            ws->kmax = 0u; ws->kmin = 0u; ws->counter = 0u;
+        }
+    }
 }
 
 static int pool_geom(PoolGeom& g, const char* who, int64_t B, int64_t H, int64_t W, int64_t C, int k, int stride, int pad,
@@ -143,7 +184,35 @@ extern "C" int qb_maxpool2d_nhwc_bwd(const float* grad_out, const uint8_t* idx, 
     int rc = pool_geom(g, "qb_maxpool2d_nhwc_bwd", B, H, W, C, k, stride, pad, grad_out, dx, idx);
     if (rc) return rc;
     const uint32_t total = (uint32_t)((int64_t)B * H * W * (C / 8));
-    k_maxpool_bwd_nhwc<<<(total + 255u) / 256u, 256, 0, qb_stream(stream)>>>(grad_out, idx, dx, g, total);
+    k_maxpool_bwd_nhwc<false><<<(total + 255u) / 256u, 256, 0, qb_stream(stream)>>>(grad_out, idx, nullptr, dx, g, total, nullptr,
+                                                                                   nullptr);
+    QB_LAUNCH_CHECK();
+    return QB_OK;
+}
+
+extern "C" size_t qb_maxpool2d_relu_bwd_ws_bytes(void) { return sizeof(PoolRangeWs); }
+
+extern "C" int qb_maxpool2d_relu_nhwc_bwd(const float* grad_out, const uint8_t* idx, const float* pool_out, float* dx, int64_t B,
+                                          int64_t H, int64_t W, int64_t C, int k, int stride, int pad, float* range_out, void* ws,
+                                          size_t ws_bytes, void* stream) {
+    PoolGeom g;
+    int rc = pool_geom(g, "qb_maxpool2d_relu_nhwc_bwd", B, H, W, C, k, stride, pad, grad_out, dx, idx);
+    if (rc) return rc;
+    QB_CHECK_ARG(pool_out && range_out && ws, "qb_maxpool2d_relu_nhwc_bwd: null pointer");
+    if ((reinterpret_cast<uintptr_t>(pool_out) & 31) != 0) {
+        qb_set_error("qb_maxpool2d_relu_nhwc_bwd: pool_out must be 32-byte aligned");
+        return QB_ERR_UNSUPPORTED;
+    }
+    if (ws_bytes < sizeof(PoolRangeWs)) {
+        qb_set_error("qb_maxpool2d_relu_nhwc_bwd: workspace %zu < %zu bytes", ws_bytes, sizeof(PoolRangeWs));
+        return QB_ERR_WORKSPACE;
+    }
+    const uint32_t total = (uint32_t)((int64_t)B * H * W * (C / 8));
+    int sms = qb_sm_count();
+    if (sms <= 0) sms = 148;
+    const uint32_t want = (total + 255u) / 256u, cap = (uint32_t)sms * 16u;
+    k_maxpool_bwd_nhwc<true><<<(want < cap ? want : cap), 256, 0, qb_stream(stream)>>>(grad_out, idx, pool_out, dx, g, total, range_out,
+                                                                                  static_cast<PoolRangeWs*>(ws));
     QB_LAUNCH_CHECK();
     return QB_OK;
 }

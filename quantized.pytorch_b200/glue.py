@@ -10,20 +10,44 @@ import torch.nn.functional as F
 from . import _abi
 
 
+# ReLU -> MaxPool2d (resnet_quantized.py:147-150).  glue.ReLU remembers its latest output; a glue.MaxPool2d that is fed
+# exactly that tensor computes, in its backward, the gradient w.r.t. the ReLU's INPUT (windows whose maximum is not
+# positive contribute nothing) together with its range, and leaves it marked; the ReLU backward that receives the marked
+# tensor passes it on untouched.  If the ReLU output has other consumers autograd sums the gradients first, the mark no
+# longer matches and the ReLU backward masks the sum - masking is idempotent, so the result is the same.
+_relu_out = {"t": None}        # (tensor, version) of the latest glue.ReLU output produced under autograd
+_premasked = {"t": None}       # (dx, version, range) left by the fused pooling backward
+
+
+def _is_latest_relu_output(x):
+    ent = _relu_out["t"]
+    return (ent is not None and ent[0].data_ptr() == x.data_ptr() and ent[0].shape == x.shape
+            and ent[0].stride() == x.stride() and x._version == ent[1])
+
+
 class _MaxPoolFn(torch.autograd.Function):
     @staticmethod
-    def forward(ctx, x, k, stride, pad):
+    def forward(ctx, x, k, stride, pad, after_relu=False):
         out, idx = _abi.maxpool2d_nhwc_fwd(x, k, stride, pad)
-        ctx.save_for_backward(idx)
+        ctx.after_relu = bool(after_relu)
+        if ctx.after_relu:
+            ctx.save_for_backward(idx, out)
+        else:
+            ctx.save_for_backward(idx)
         ctx.geom = (tuple(x.shape), k, stride, pad)
         return out
 
     @staticmethod
     def backward(ctx, g):
-        (idx,) = ctx.saved_tensors
         shape, k, stride, pad = ctx.geom
         g = _abi._f32c(g, "grad").contiguous(memory_format=torch.channels_last)
-        return _abi.maxpool2d_nhwc_bwd(g, idx, shape, k, stride, pad), None, None, None
+        if ctx.after_relu:
+            idx, out = ctx.saved_tensors
+            dx, rng = _abi.maxpool2d_relu_nhwc_bwd(g, idx, out, shape, k, stride, pad)
+            _premasked["t"] = (dx, dx._version, rng)
+            return dx, None, None, None, None
+        (idx,) = ctx.saved_tensors
+        return _abi.maxpool2d_nhwc_bwd(g, idx, shape, k, stride, pad), None, None, None, None
 
 
 def _native_ok(x, k, stride, pad):
@@ -38,13 +62,20 @@ class MaxPool2d(nn.MaxPool2d):
     def forward(self, x):
         k, s, p = self.kernel_size, self.stride, self.padding
         if self.dilation == 1 and not self.ceil_mode and not self.return_indices and _native_ok(x, k, s, p):
-            return _MaxPoolFn.apply(x, k, s, p)
+            fused = torch.is_grad_enabled() and x.requires_grad and _is_latest_relu_output(x) and x.data_ptr() % 32 == 0
+            return _MaxPoolFn.apply(x, k, s, p, fused)
         return F.max_pool2d(x, k, s, p, self.dilation, self.ceil_mode, self.return_indices)
 
 
 def _relu_backward(g, out):
     """aten::threshold_backward(g, out, 0); on dense fp32 CUDA tensors of one layout the native pass also leaves the
     range of the result for the gradient quantizer that consumes it (RangeBN / QConv2d backward)."""
+    ent, _premasked["t"] = _premasked["t"], None
+    if (ent is not None and ent[0].data_ptr() == g.data_ptr() and ent[0].shape == g.shape and ent[0].stride() == g.stride()
+            and g._version == ent[1] and g.shape == out.shape):
+        from . import quantize as Q
+        Q._stash_grad_range(g, ent[2])              # already masked by the fused pooling backward
+        return g
     if (g.is_cuda and g.dtype == torch.float32 and out.dtype == torch.float32 and g.shape == out.shape
             and g.stride() == out.stride() and g.numel() > 0
             and (out.is_contiguous() or (out.dim() == 4 and out.is_contiguous(memory_format=torch.channels_last)))):
@@ -107,6 +138,7 @@ class ReLU(nn.ReLU):
         if torch.is_grad_enabled() and x.requires_grad:
             out = _ReLUFn.apply(x, self.inplace)
             stats, _last["stats"] = _last["stats"], None
+            _relu_out["t"] = (out, out._version)
         else:
             out, stats = _abi.relu_measure(x, None if self.inplace else torch.empty_like(x))
         if stats is not None:

@@ -149,3 +149,36 @@ def test_rangebn_backward_takes_the_relu_range(lib):
     assert "qb_relu_bwd_minmax" in res[0][2] and "qb_minmax" not in res[0][2], res[0][2]
     assert "qb_minmax" in res[1][2], res[1][2]
     assert torch.equal(res[0][0], res[1][0]) and torch.equal(res[0][1], res[1][1])
+
+
+@pytest.mark.parametrize("shape", [(4, 64, 56, 56), (2, 16, 9, 11), (3, 8, 4, 4)])
+def test_relu_maxpool_fused_backward(lib, shape):
+    """glue.ReLU -> glue.MaxPool2d(3, 2, 1): the pooling backward yields the gradient w.r.t. the ReLU input directly (one
+    kernel, with its range); values bit-identical to nn.ReLU -> nn.MaxPool2d."""
+    from qtorch_b200 import glue, quantize as Q
+    gen = torch.Generator().manual_seed(sum(shape) + 5)
+    x0 = torch.randn(shape, generator=gen).to(DEV).contiguous(memory_format=torch.channels_last)
+    xa, xb = x0.clone().requires_grad_(), x0.clone().requires_grad_()
+    relu, pool = glue.ReLU(inplace=True).train(), glue.MaxPool2d(3, 2, 1)
+    ya = pool(relu(xa * 1.0))
+    yb = torch.nn.functional.max_pool2d(torch.relu(xb * 1.0), 3, 2, 1)
+    assert torch.equal(ya, yb)
+    go = torch.randn(ya.shape, generator=gen).to(DEV).contiguous(memory_format=torch.channels_last)
+    lib.profile_begin()
+    ya.backward(go)
+    names = [r[0] for r in lib.profile_end()]
+    yb.backward(go)
+    assert "qb_maxpool2d_relu_nhwc_bwd" in names and "qb_relu_bwd_minmax" not in names and "qb_maxpool2d_nhwc_bwd" not in names, names
+    assert torch.equal(xa.grad, xb.grad)
+    # the range of that gradient was left for the consumer
+    ent = Q._grad_ranges
+    assert len(ent) >= 1
+    rng = list(ent.values())[-1][2]
+    assert float(rng[0]) == float(xb.grad.min()) and float(rng[1]) == float(xb.grad.max())
+    # a second consumer of the ReLU output: autograd sums, the ReLU backward masks the sum - still torch's result
+    xa2, xb2 = x0.clone().requires_grad_(), x0.clone().requires_grad_()
+    ra = relu(xa2 * 1.0)
+    (pool(ra).sum() + (ra * 0.5).sum()).backward()
+    rb = torch.relu(xb2 * 1.0)
+    (torch.nn.functional.max_pool2d(rb, 3, 2, 1).sum() + (rb * 0.5).sum()).backward()
+    assert torch.allclose(xa2.grad, xb2.grad, rtol=0, atol=1e-6)
