@@ -50,6 +50,32 @@ class _MaxPoolFn(torch.autograd.Function):
         return _abi.maxpool2d_nhwc_bwd(g, idx, shape, k, stride, pad), None, None, None, None
 
 
+class _ReLUMaxPoolFn(torch.autograd.Function):
+    """maxpool(relu(x)) computed as relu(maxpool(x)) - max and the monotone clamp commute, and whenever the two argmax
+    choices could differ (a window without a positive element) the window's gradient is zero anyway - so the full-size ReLU
+    output is never written: the clamp and the next QuantMeasure's statistics run on the 4x smaller pooled tensor, and the
+    backward is the one-pass gather of qb_maxpool2d_relu_nhwc_bwd (gradient w.r.t. x with its range)."""
+
+    @staticmethod
+    def forward(ctx, x, k, stride, pad):
+        out, idx = _abi.maxpool2d_nhwc_fwd(x, k, stride, pad)
+        out, stats = _abi.relu_measure(out)
+        ctx.save_for_backward(idx, out)
+        ctx.geom = (tuple(x.shape), k, stride, pad)
+        _last["stats"] = stats
+        return out
+
+    @staticmethod
+    def backward(ctx, g):
+        from . import quantize as Q
+        idx, out = ctx.saved_tensors
+        shape, k, stride, pad = ctx.geom
+        g = _abi._f32c(g, "grad").contiguous(memory_format=torch.channels_last)
+        dx, rng = _abi.maxpool2d_relu_nhwc_bwd(g, idx, out, shape, k, stride, pad)
+        Q._stash_grad_range(dx, rng)
+        return dx, None, None, None
+
+
 def _native_ok(x, k, stride, pad):
     return (x.is_cuda and x.dtype == torch.float32 and x.dim() == 4 and x.shape[1] % 8 == 0 and _abi.is_nhwc(x)
             and isinstance(k, int) and isinstance(stride, int) and isinstance(pad, int) and 1 <= k <= 15 and 2 * pad <= k
@@ -65,6 +91,20 @@ class MaxPool2d(nn.MaxPool2d):
             fused = torch.is_grad_enabled() and x.requires_grad and _is_latest_relu_output(x) and x.data_ptr() % 32 == 0
             return _MaxPoolFn.apply(x, k, s, p, fused)
         return F.max_pool2d(x, k, s, p, self.dilation, self.ceil_mode, self.return_indices)
+
+    def relu_pool(self, x, relu):
+        """``self(relu(x))`` (models/resnet_quantized.py:147-150) without materialising the ReLU output; falls back to
+        exactly that composition whenever the native path does not apply."""
+        from . import quantize as Q
+        k, s, p = self.kernel_size, self.stride, self.padding
+        if not (isinstance(relu, ReLU) and relu.training and self.dilation == 1 and not self.ceil_mode and not self.return_indices
+                and _native_ok(x, k, s, p) and torch.is_grad_enabled() and x.requires_grad):
+            return self(relu(x))
+        out = _ReLUMaxPoolFn.apply(x, k, s, p)
+        stats, _last["stats"] = _last["stats"], None
+        if stats is not None:
+            Q._stash_fwd_stats(out, stats)
+        return out
 
 
 def _relu_backward(g, out):

@@ -154,7 +154,11 @@ class QResNet(nn.Module):
         self.fc.bias.data.zero_()
 
     def forward(self, x):
-        x = self.maxpool(self.relu(self.bn1(self.conv1(x))))
+        x = self.bn1(self.conv1(x))
+        if hasattr(self.maxpool, "relu_pool"):         # native glue: pool first, ReLU on the 4x smaller result (same values)
+            x = self.maxpool.relu_pool(x, self.relu)
+        else:
+            x = self.maxpool(self.relu(x))
         x = self.layer4(self.layer3(self.layer2(self.layer1(x))))
         x = self.avgpool(x)
         return self.fc(x.view(x.size(0), -1))

@@ -182,3 +182,34 @@ def test_relu_maxpool_fused_backward(lib, shape):
     rb = torch.relu(xb2 * 1.0)
     (torch.nn.functional.max_pool2d(rb, 3, 2, 1).sum() + (rb * 0.5).sum()).backward()
     assert torch.allclose(xa2.grad, xb2.grad, rtol=0, atol=1e-6)
+
+
+@pytest.mark.parametrize("shape", [(4, 64, 56, 56), (2, 16, 9, 11), (3, 8, 4, 4)])
+def test_relu_pool_without_the_relu_output(lib, shape):
+    """glue.MaxPool2d.relu_pool (the stem tail of models.py): maxpool(relu(x)) evaluated as relu(maxpool(x)) with the
+    one-pass backward - values, gradient and the stashed statistics / gradient range equal torch's composition."""
+    from qtorch_b200 import glue, quantize as Q
+    gen = torch.Generator().manual_seed(sum(shape) + 9)
+    x0 = torch.randn(shape, generator=gen)
+    x0[0, :, :3, :3] = -x0[0, :, :3, :3].abs()                      # windows without a positive element
+    x0[1, 0, 0, 0] = 0.0
+    x0 = x0.to(DEV).contiguous(memory_format=torch.channels_last)
+    xa, xb = x0.clone().requires_grad_(), x0.clone().requires_grad_()
+    relu, pool = glue.ReLU(inplace=True).train(), glue.MaxPool2d(3, 2, 1)
+    lib.profile_begin()
+    ya = pool.relu_pool(xa * 1.0, relu)
+    names = [r[0] for r in lib.profile_end()]
+    assert names == ["qb_maxpool2d_nhwc_fwd", "qb_relu_measure"], names
+    yb = torch.nn.functional.max_pool2d(torch.relu(xb * 1.0), 3, 2, 1)
+    assert torch.equal(ya, yb)
+    got = Q._take_fwd_stats(ya.detach())
+    assert got is not None and torch.equal(got, lib.measure_stats(yb.detach().contiguous(memory_format=torch.channels_last)))
+    go = torch.randn(ya.shape, generator=gen).to(DEV).contiguous(memory_format=torch.channels_last)
+    ya.backward(go)
+    yb.backward(go)
+    assert torch.equal(xa.grad, xb.grad)
+    rng = list(Q._grad_ranges.values())[-1][2]
+    assert float(rng[0]) == float(xb.grad.min()) and float(rng[1]) == float(xb.grad.max())
+    # eval / no-grad: plain composition
+    with torch.no_grad():
+        assert torch.equal(pool.relu_pool(x0.clone(), relu), torch.nn.functional.max_pool2d(torch.relu(x0), 3, 2, 1))
