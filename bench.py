@@ -162,7 +162,7 @@ def main_ours(args, rank, world, local_rank):
     def step_body():
         out = model(x_static)
         loss = crit(out, y_static) + model.regularization()
-        opt.zero_grad(set_to_none=False)
+        opt.zero_grad(set_to_none=True)      # torch default: no fill + accumulate kernels per parameter
         loss.backward()
         if world > 1:
             qdist.allreduce_gradients(model)

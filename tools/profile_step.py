@@ -24,7 +24,7 @@ def main():
 
     def step():
         loss = crit(model(x), y) + model.regularization()
-        opt.zero_grad(set_to_none=False)
+        opt.zero_grad(set_to_none=True)
         loss.backward()
         opt.step()
         return loss
