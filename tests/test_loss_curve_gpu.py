@@ -12,7 +12,7 @@ O(1) and a relative comparison means something), three times from the same initi
 Single codes flip on ~1e-6 differences of the contractions, so the trajectories are compared the way the oracle is
 compared with itself when only its thread count changes (tests/test_oracle_golden.py): tightly over the first steps,
 and as smoothed curves over the whole run.  The three curves are written to gpurun_out/loss_curve_200.json when that
-directory exists (committed copy: profiles/loss_curve_200_r01p.json)."""
+directory exists (committed copy: profiles/loss_curve_200_r01s.json)."""
 import json
 import os
 
