@@ -354,6 +354,36 @@ int qb_maxpool2d_relu_nhwc_bwd(const float* grad_out, const uint8_t* idx, const 
                                void* stream);
 
 /* ---------------------------------------------------------------------------------------------------
+ * Dense backward contractions of QConv2d / QLinear (conv_bwd.cu) - replace aten::convolution_backward / matmul under
+ * conv2d_biprec / linear_biprec (models/modules/quantize.py:142-156) and the non-biprec branch (:342-346).
+ * tcgen05 kind::f16 (bf16 operands, fp32 accumulation) fed by TMA.  One operand of each contraction is an integer code,
+ * exact in bf16; the other is split into two bf16 planes hi + lo (relative operand error 2^-17).
+ *
+ * qb_bwd_pack: ONE pass over the fp32 output gradient g (n elements, any dense layout):
+ *   gq16 (optional)      bf16 integers (q - zp) of UniformQuantizeGrad.backward's quantizer (:124-139: zero-point,
+ *                        stochastic; range_dev = device {min,max}, bits <= 8; noise as in qb_fakequant_grad)
+ *   g_hi, g_lo (optional, together)   bf16 split of the RAW g
+ * qb_wt_pack: w_hat fp32 [C_out][C_in][taps] (fake-quantized weight) -> wt bf16 [2][C_in][taps][C_out] (hi, lo planes).
+ * qb_conv_dgrad: dx fp32 [B,H,W,C_in] (channels-last) = scale * SUM_{tap,n} a[b,ho,wo,n] * w_hat[n,c,tap];  a = a0 (+ a1):
+ *   bf16 planes [B,Ho,Wo,C_out]; scale = scale_mul * (scale_range ? step of the zero-point quantizer over scale_range at
+ *   scale_bits : 1).  Stride s is evaluated as s*s unit-stride parity classes of dx.  Linear: H = W = kh = kw = 1.
+ * qb_conv_wgrad: dw fp32 [C_out][C_in][kh][kw] = sa * SUM_pixels g * q_a + la * SUM_{pixels whose tap is in bounds} g, and
+ *   db = SUM_pixels g, from the bf16 planes of g, the fp32 g (column sums only) and x16 = bf16 integer codes q_a
+ *   [B,H,W,C_in] of the input quantizer (device range a_range, a_bits).  Split over the pixels, fixed-order reduction
+ *   (deterministic).  ws: qb_conv_wgrad_ws_bytes() bytes, 16-byte aligned.
+ * Unsupported geometries return QB_ERR_UNSUPPORTED (there is no library fallback). */
+int qb_bwd_pack(const float* g, int64_t n, uint16_t* gq16, uint16_t* g_hi, uint16_t* g_lo, int bits, const float* range_dev,
+                const float* noise, int stochastic, uint64_t seed, uint64_t offset, const uint64_t* step_dev, void* stream);
+int qb_wt_pack(const float* w_hat, uint16_t* wt, int64_t Cout, int64_t Cin, int taps, void* stream);
+int qb_conv_dgrad(const uint16_t* a0, const uint16_t* a1, const uint16_t* wt, float* dx, int64_t B, int64_t H, int64_t W,
+                  int64_t Cin, int64_t Cout, int kh, int kw, int stride, int pad, const float* scale_range, int scale_bits,
+                  float scale_mul, void* stream);
+size_t qb_conv_wgrad_ws_bytes(int64_t B, int64_t H, int64_t W, int64_t Cin, int64_t Cout, int kh, int kw, int stride, int pad);
+int qb_conv_wgrad(const uint16_t* g_hi, const uint16_t* g_lo, const float* g_f32, const uint16_t* x16, float* dw, float* db,
+                  int64_t B, int64_t H, int64_t W, int64_t Cin, int64_t Cout, int kh, int kw, int stride, int pad,
+                  const float* a_range, int a_bits, void* ws, size_t ws_bytes, void* stream);
+
+/* ---------------------------------------------------------------------------------------------------
  * Cross-rank exchange of the statistic blocks of batch-sharded training: a one-shot all-reduce
  * over NVLink peer memory for latency-bound messages.  The reference has no counterpart (nn.DataParallel keeps
  * per-replica statistics, main.py:344-345).  Every rank passes the peer-mapped addresses of all ranks' exchange buffers

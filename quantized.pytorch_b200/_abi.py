@@ -79,6 +79,11 @@ PROTOTYPES = {
     "qb_conv_dw_wgrad": (_i32, [_p, _p, _p, _p, _i64, _i64, _i64, _i64, _i32, _i32, _i32, _i32, _p, _sz, _p]),
     "qb_conv_dw_fwd": (_i32, [_p, _p, _p, _i64, _i64, _i64, _i64, _i32, _i32, _i32, _i32, _p, _i32, _p, _p, _i32, _p, _p, _p,
                               _sz, _p]),
+    "qb_bwd_pack": (_i32, [_p, _i64, _p, _p, _p, _i32, _p, _p, _i32, _u64, _u64, _p, _p]),
+    "qb_wt_pack": (_i32, [_p, _p, _i64, _i64, _i32, _p]),
+    "qb_conv_dgrad": (_i32, [_p, _p, _p, _p, _i64, _i64, _i64, _i64, _i64, _i32, _i32, _i32, _i32, _p, _i32, _flt, _p]),
+    "qb_conv_wgrad_ws_bytes": (_sz, [_i64, _i64, _i64, _i64, _i64, _i32, _i32, _i32, _i32]),
+    "qb_conv_wgrad": (_i32, [_p, _p, _p, _p, _p, _p, _i64, _i64, _i64, _i64, _i64, _i32, _i32, _i32, _i32, _p, _i32, _p, _sz, _p]),
     "qb_conv_i8_fwd": (_i32, [_p, _p, _p, _i64, _i64, _i64, _i64, _i64, _i32, _i32, _i32, _i32, _p, _i32, _p, _p, _i32,
                               _p, _p, _p, _p, _p, _p, _sz, _p]),
 }
@@ -119,7 +124,7 @@ _profile = None       # list of (name, algorithmic_bytes, start_event, end_event
 
 # kernels enqueued per C call
 _NLAUNCH = {"qb_rangebn_stats": 2, "qb_rangebn_bwd_reduce": 2, "qb_rangebn_bwd_apply": 2,
-            "qb_conv_i8_fwd": 2, "qb_conv_dw_wgrad": 2, "qb_conv_stem_fwd": 2, "qb_conv_stem_wgrad": 2, "qb_rangebn_stats_nhwc": 3, "qb_rangebn_bwd_reduce_nhwc": 2, "qb_rangebn_bwd_apply_nhwc": 2}
+            "qb_conv_i8_fwd": 2, "qb_conv_wgrad": 3, "qb_conv_dw_wgrad": 2, "qb_conv_stem_fwd": 2, "qb_conv_stem_wgrad": 2, "qb_rangebn_stats_nhwc": 3, "qb_rangebn_bwd_reduce_nhwc": 2, "qb_rangebn_bwd_apply_nhwc": 2}
 
 
 _next_ops = 0          # integer operations (2*M*N*K) of the next tensor-core call, set by the conv / GEMM wrappers
@@ -580,6 +585,69 @@ def conv_dw_wgrad(grad_out, x_hat, stride, pad, want_bias):
     ws = workspace("conv_dw_wgrad", nbytes, g.device)
     _run("qb_conv_dw_wgrad", 4 * g.numel() + 4 * x_hat.numel(), _ptr(g), _ptr(x_hat), _ptr(dw), _ptr(db), B, H, W, C, 3, 3,
          int(stride), int(pad), _ptr(ws), ws.numel(), _stream())
+    return dw, db
+
+
+def bwd_pack(g, range_dev=None, bits=8, noise=None, stochastic=True, seed=0, step_dev=None, want_codes=True, want_split=True):
+    """One pass over the fp32 gradient g -> (gq16 | None, g_hi | None, g_lo | None): bf16 tensors shaped / laid out like g
+    (qb_bwd_pack).  gq16 = integer codes (q - zp) of the gradient quantizer over ``range_dev``; hi / lo = split of raw g."""
+    g = _f32c(g, "grad")
+    gq = torch.empty_like(g, dtype=torch.bfloat16) if want_codes else None
+    hi = torch.empty_like(g, dtype=torch.bfloat16) if want_split else None
+    lo = torch.empty_like(g, dtype=torch.bfloat16) if want_split else None
+    if noise is not None:
+        noise = _f32c(noise, "noise")
+        if noise.numel() != g.numel():
+            raise QB200Error("noise has %d elements, gradient %d" % (noise.numel(), g.numel()))
+    nb = 4 + (2 if want_codes else 0) + (4 if want_split else 0) + (4 if noise is not None else 0)
+    _run("qb_bwd_pack", nb * g.numel(), _ptr(g), g.numel(), _ptr(gq), _ptr(hi), _ptr(lo), int(bits), _ptr(range_dev), _ptr(noise),
+         int(bool(stochastic)), int(seed) & (2 ** 64 - 1), 0, _ptr(step_dev), _stream())
+    return gq, hi, lo
+
+
+def wt_pack(w_hat):
+    """w_hat fp32 [Cout, Cin, kh, kw] (or [Cout, Cin]) -> bf16 [2, Cin, taps, Cout] hi / lo planes (qb_wt_pack)."""
+    w = w_hat if w_hat.is_contiguous() else w_hat.contiguous()
+    Cout, Cin = w.shape[0], w.shape[1]
+    taps = w.numel() // (Cout * Cin)
+    wt = torch.empty(2, Cin, taps, Cout, dtype=torch.bfloat16, device=w.device)
+    _run("qb_wt_pack", 8 * w.numel(), _ptr(w), _ptr(wt), Cout, Cin, taps, _stream())
+    return wt
+
+
+def conv_bwd_supported(Cin, Cout, kh, kw, stride, pad):
+    return Cin % 16 == 0 and Cout % 8 == 0 and kh * kw <= 9 and stride in (1, 2)
+
+
+def conv_dgrad(a0, a1, wt, x_shape, Cout, kh, kw, stride, pad, scale_range=None, scale_bits=8, scale_mul=1.0):
+    """dX [B, Cin, H, W] (channels-last fp32) of a convolution from the bf16 plane(s) of its output gradient (qb_conv_dgrad)."""
+    B, Cin, H, W = x_shape
+    dx = torch.empty((B, Cin, H, W), dtype=torch.float32, device=a0.device, memory_format=torch.channels_last)
+    Ho, Wo = (H + 2 * pad - kh) // stride + 1, (W + 2 * pad - kw) // stride + 1
+    global _next_ops
+    planes = 2 if a1 is None else 3
+    _next_ops = 2 * B * Ho * Wo * Cout * kh * kw * Cin * planes
+    _NLAUNCH["qb_conv_dgrad"] = stride * stride if kh >= stride else 1
+    _run("qb_conv_dgrad", (2 if a1 is None else 4) * a0.numel() + 4 * Cout * Cin * kh * kw + 4 * dx.numel(), _ptr(a0), _ptr(a1),
+         _ptr(wt), _ptr(dx), B, H, W, Cin, Cout, kh, kw, stride, pad, _ptr(scale_range), int(scale_bits), float(scale_mul),
+         _stream())
+    return dx
+
+
+def conv_wgrad(g_hi, g_lo, g_f32, x16, Cout, kh, kw, stride, pad, a_range, a_bits, want_bias=False):
+    """(dW [Cout, Cin, kh, kw], db | None) from the bf16 planes of the output gradient and the bf16 input codes (qb_conv_wgrad)."""
+    B, Cin, H, W = x16.shape
+    dw = torch.empty((Cout, Cin, kh, kw), dtype=torch.float32, device=x16.device)
+    db = torch.empty(Cout, dtype=torch.float32, device=x16.device) if want_bias else None
+    nb = load().qb_conv_wgrad_ws_bytes(B, H, W, Cin, Cout, kh, kw, stride, pad)
+    if nb == 0:
+        raise QB200Error("conv_wgrad: unsupported geometry Cin=%d Cout=%d k=%dx%d stride=%d" % (Cin, Cout, kh, kw, stride))
+    ws = workspace("conv_wgrad", nb, x16.device)
+    global _next_ops
+    _next_ops = 2 * g_hi.numel() * kh * kw * Cin * (2 if g_lo is not None else 1)
+    _run("qb_conv_wgrad", (2 if g_lo is None else 4) * g_hi.numel() + 2 * x16.numel() + 4 * dw.numel(), _ptr(g_hi), _ptr(g_lo),
+         _ptr(g_f32), _ptr(x16), _ptr(dw), _ptr(db), B, H, W, Cin, Cout, kh, kw, stride, pad, _ptr(a_range), int(a_bits), _ptr(ws),
+         ws.numel(), _stream())
     return dw, db
 
 

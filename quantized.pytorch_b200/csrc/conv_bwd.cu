@@ -1,0 +1,916 @@
+// conv_bwd.cu - the dense BACKWARD contractions of QConv2d / QLinear on tcgen05 (kind::f16, bf16 operands, fp32 TMEM
+// accumulators), fed by TMA from integer codes.
+//
+// Reference: conv2d_biprec / linear_biprec (models/modules/quantize.py:142-156) and the non-biprec branch (:342-346):
+//     dX = conv_bwd_data  (Q(g), w_hat)          Q(g) = (q_g - zp) * s_g, q_g in [0, 2^b - 1]      (quantized branch)
+//     dW = conv_bwd_filter(g,    x_hat)          x_hat = q_a * s_a + l_a inside the image, 0 in the padding
+// Neither is an integer GEMM (dX: the per-output-channel weight scale s_w[n] sits INSIDE the contraction over n; dW: g is
+// the unquantized fp32 gradient), but one operand of each IS a small integer and therefore exact in bf16:
+//     dX[m,c] = s_g * SUM_{tap,n} (q_g - zp)[m',n] * w_hat[n,c,tap]       (q_g - zp) exact, w_hat = hi + lo (two bf16 planes)
+//     dW[n,c,tap] = s_a * SUM_m g[m,n] * q_a[m',c] + l_a * SUM_{m: tap in bounds} g[m,n]     q_a exact, g = hi + lo
+// so each is TWO bf16 MMAs per K step with a 2^-17 relative operand error (TF32 would be one MMA at half rate with 2^-11).
+// Operands are 2 bytes (codes) or 2 x 2 bytes (splits) per element instead of the 4-byte fp32 tensors cuDNN reads.
+//
+//   qb_bwd_pack    one pass over g: gradient quantizer (zero-point, stochastic; quantize.py:124-139) -> bf16 (q_g - zp),
+//                  and the bf16 hi / lo split of the raw g
+//   qb_wt_pack     w_hat fp32 [Cout][Cin][taps] -> bf16 hi / lo planes [Cin][taps][Cout] (K-major rows for the dgrad B operand)
+//   qb_conv_dgrad  implicit GEMM over output-pixel tiles of dX, same skeleton as conv_i8.cu (4-D TMA boxes of the NHWC
+//                  operand at the tap-shifted coordinate, zero fill = the padding); stride-s convolutions are s*s parity
+//                  classes of dX, each a unit-stride problem over a subset of the taps writing a strided view of dX
+//   qb_conv_wgrad  D[(tap,c)][n] = SUM_pixels X^T G with BOTH operands MN-major (pixels = K are the slow index of an NHWC
+//                  tensor): TMA boxes {channels, pixels} land as [pixel][channel] rows, which IS the canonical MN-major
+//                  swizzled layout; split-K over CTAs, accumulators stay in TMEM for the whole pixel slice, deterministic
+//                  reduction of the per-slice partials
+#include <cuda_bf16.h>
+#include <stdlib.h>
+
+#include "tc_common.cuh"
+
+// ------------------------------------------------------------------------------------------------
+// small helpers
+// ------------------------------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t bf16x2_rn(float a, float b) {        // {lo half = a, hi half = b}
+    uint32_t r;
+    asm("cvt.rn.bf16x2.f32 %0, %1, %2;" : "=r"(r) : "f"(b), "f"(a));
+    return r;
+}
+__device__ __forceinline__ float bf16_lo_f(uint32_t p) { return __uint_as_float(p << 16); }
+__device__ __forceinline__ float bf16_hi_f(uint32_t p) { return __uint_as_float(p & 0xffff0000u); }
+
+// g = hi + lo (+ O(2^-17 |g|)):  hi = bf16(g), lo = bf16(g - hi)   (g - hi is exact in fp32)
+__device__ __forceinline__ void split2(float a, float b, uint32_t& hi, uint32_t& lo) {
+    hi = bf16x2_rn(a, b);
+    lo = bf16x2_rn(__fsub_rn(a, bf16_lo_f(hi)), __fsub_rn(b, bf16_hi_f(hi)));
+}
+
+// smem descriptor, K-major rows of `rb` bytes (rb-byte swizzle): 8-row groups are 8*rb bytes apart
+__device__ __forceinline__ uint64_t desc_kmajor(uint32_t addr, int rb) {
+    const uint64_t layout = rb == 128 ? 2 : (rb == 64 ? 4 : 6);
+    return (uint64_t)((addr & 0x3FFFF) >> 4) | ((uint64_t)1 << 16) | ((uint64_t)((8 * rb) >> 4) << 32) | ((uint64_t)1 << 46) |
+           (layout << 61);
+}
+// smem descriptor, MN-major: rows = K index, each row holds `rb` bytes of consecutive M (or N) elements, rb-byte swizzle.
+// Canonical form ((T,rb/16,m),(8,k)) : ((1,T,LBO),(rb/16*T,SBO)): `lbo` = bytes between blocks of rb/2 elements along M/N,
+// SBO = bytes between groups of 8 K rows (dense: 8*rb).
+__device__ __forceinline__ uint64_t desc_mnmajor(uint32_t addr, int rb, uint32_t lbo) {
+    const uint64_t layout = rb == 128 ? 2 : (rb == 64 ? 4 : 6);
+    return (uint64_t)((addr & 0x3FFFF) >> 4) | ((uint64_t)((lbo >> 4) & 0x3FFF) << 16) | ((uint64_t)((8 * rb) >> 4) << 32) |
+           ((uint64_t)1 << 46) | (layout << 61);
+}
+// kind::f16 instruction descriptor: fp32 accumulate, bf16 x bf16, optional MN-major operands
+__host__ __device__ constexpr uint32_t idesc_bf16(uint32_t M, uint32_t N, uint32_t a_mn, uint32_t b_mn) {
+    return (1u << 4) | (1u << 7) | (1u << 10) | (a_mn << 15) | (b_mn << 16) | ((N >> 3) << 17) | ((M >> 4) << 24);
+}
+__device__ __forceinline__ void mbar_wait_trap(uint64_t* bar, uint32_t parity) {
+    uint32_t spins = 0;
+    while (!mbar_try_wait(bar, parity)) {
+        if (++spins > (1u << 28)) __trap();                   // a lost completion must not hang the GPU
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// qb_bwd_pack: gradient quantizer -> bf16 integer codes, and / or bf16 hi-lo split of the raw tensor
+// ------------------------------------------------------------------------------------------------
+constexpr int BP_THREADS = 256;
+
+template <int NOISE, bool WQ, bool WS>
+__global__ void __launch_bounds__(BP_THREADS, 4)
+k_bwd_pack(const float* __restrict__ g, uint16_t* __restrict__ gq, uint16_t* __restrict__ ghi, uint16_t* __restrict__ glo, int64_t n,
+           int vec, int bits, const float* __restrict__ range_dev, NoiseArg na) {
+    GradQ Q;
+    if (WQ) Q = make_gradq((double)__ldg(range_dev), (double)__ldg(range_dev + 1), bits);
+    const uint64_t seed = effective_seed(na);
+    const int64_t stride = (int64_t)gridDim.x * BP_THREADS;
+    const int64_t tid = (int64_t)blockIdx.x * BP_THREADS + threadIdx.x;
+    const int64_t noct = vec ? (n >> 3) : 0;
+    for (int64_t i = tid; i < noct; i += stride) {
+        const F8 v = ld256_stream(g + 8 * i);
+        if (WS) {
+            uint4 h, l;
+            split2(v.v[0], v.v[1], h.x, l.x);
+            split2(v.v[2], v.v[3], h.y, l.y);
+            split2(v.v[4], v.v[5], h.z, l.z);
+            split2(v.v[6], v.v[7], h.w, l.w);
+            reinterpret_cast<uint4*>(ghi)[i] = h;
+            reinterpret_cast<uint4*>(glo)[i] = l;
+        }
+        if (WQ) {
+            float u[8];
+            if (NOISE == NOISE_INJECT) {
+                const F8 w = ld256_stream(na.inject + 8 * i);
+#pragma unroll
+                for (int j = 0; j < 8; ++j) u[j] = w.v[j];
+            } else if (NOISE == NOISE_PHILOX) {
+                philox_noise8(seed, (uint64_t)i + (na.offset >> 3), u);
+            }
+            bool ok = Q.d.fast;
+#pragma unroll
+            for (int j = 0; j < 8; ++j) ok = ok && qb_div_ok(v.v[j]);
+            float t[8];
+            if (ok) {
+#pragma unroll
+                for (int j = 0; j < 8; ++j) t[j] = qb_div_fast(v.v[j], Q.d);
+            } else {
+#pragma unroll
+                for (int j = 0; j < 8; ++j) t[j] = __fdiv_rn(v.v[j], Q.d.b);
+            }
+            uint32_t c[8];
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+                float s = __fadd_rn(t[j], Q.p.zp);
+                if (NOISE != NOISE_NONE) s = __fadd_rn(s, u[j]);
+                s = fminf(fmaxf(s, 0.0f), Q.p.qmax);
+                const float q = __fsub_rn(__fadd_rn(s, QB_MAGIC), QB_MAGIC);        // RNE, qmax <= 255 here
+                c[j] = __float_as_uint(__fsub_rn(q, Q.p.zp));                       // |q - zp| <= 255: exact in bf16
+            }
+            uint4 o;
+            o.x = __byte_perm(c[0], c[1], 0x7632);
+            o.y = __byte_perm(c[2], c[3], 0x7632);
+            o.z = __byte_perm(c[4], c[5], 0x7632);
+            o.w = __byte_perm(c[6], c[7], 0x7632);
+            reinterpret_cast<uint4*>(gq)[i] = o;
+        }
+    }
+    // scalar tail (or everything when the pointers are not aligned)
+    for (int64_t e = (noct << 3) + tid; e < n; e += stride) {
+        const float v = g[e];
+        if (WS) {
+            uint32_t h, l;
+            split2(v, 0.f, h, l);
+            ghi[e] = (uint16_t)h;
+            glo[e] = (uint16_t)l;
+        }
+        if (WQ) {
+            float t = __fadd_rn(qb_div(v, Q.d), Q.p.zp);
+            if (NOISE != NOISE_NONE) t = __fadd_rn(t, noise_elem<NOISE>(na, seed, e));
+            const float q = qb_rne(fminf(fmaxf(t, 0.0f), Q.p.qmax), Q.p);
+            gq[e] = (uint16_t)(__float_as_uint(__fsub_rn(q, Q.p.zp)) >> 16);
+        }
+    }
+}
+
+extern "C" int qb_bwd_pack(const float* g, int64_t n, uint16_t* gq16, uint16_t* g_hi, uint16_t* g_lo, int bits,
+                           const float* range_dev, const float* noise, int stochastic, uint64_t seed, uint64_t offset,
+                           const uint64_t* step_dev, void* stream) {
+    QB_CHECK_ARG(n >= 0, "qb_bwd_pack: n=%lld", (long long)n);
+    if (n == 0) return QB_OK;
+    QB_CHECK_ARG(g && (gq16 || (g_hi && g_lo)), "qb_bwd_pack: null g or no output");
+    QB_CHECK_ARG((g_hi == nullptr) == (g_lo == nullptr), "qb_bwd_pack: g_hi and g_lo come together");
+    QB_CHECK_ARG(!gq16 || (range_dev && bits >= 1 && bits <= 8), "qb_bwd_pack: bf16 codes need a device range and bits <= 8");
+    const int nm = !gq16 || !stochastic ? NOISE_NONE : (noise ? NOISE_INJECT : NOISE_PHILOX);
+    NoiseArg na{noise, seed, offset, step_dev};
+    auto al = [](const void* p, size_t a) { return (reinterpret_cast<uintptr_t>(p) & (a - 1)) == 0; };
+    const int vec = al(g, 32) && (!gq16 || al(gq16, 16)) && (!g_hi || (al(g_hi, 16) && al(g_lo, 16))) && (!noise || al(noise, 32)) &&
+                    (offset & 7) == 0;
+    int sms = qb_sm_count();
+    if (sms <= 0) sms = 148;
+    int64_t want = ((vec ? (n >> 3) : n) + BP_THREADS - 1) / BP_THREADS;
+    if (want < 1) want = 1;
+    const int grid = (int)(want < (int64_t)sms * 8 ? want : (int64_t)sms * 8);
+    cudaStream_t st = qb_stream(stream);
+#define QB_PACK(NM, WQ, WS) k_bwd_pack<NM, WQ, WS><<<grid, BP_THREADS, 0, st>>>(g, gq16, g_hi, g_lo, n, vec, bits, range_dev, na)
+    const bool wq = gq16 != nullptr, wsplit = g_hi != nullptr;
+    if (!wq) QB_PACK(NOISE_NONE, false, true);
+    else if (nm == NOISE_NONE) { if (wsplit) QB_PACK(NOISE_NONE, true, true); else QB_PACK(NOISE_NONE, true, false); }
+    else if (nm == NOISE_INJECT) { if (wsplit) QB_PACK(NOISE_INJECT, true, true); else QB_PACK(NOISE_INJECT, true, false); }
+    else { if (wsplit) QB_PACK(NOISE_PHILOX, true, true); else QB_PACK(NOISE_PHILOX, true, false); }
+#undef QB_PACK
+    QB_LAUNCH_CHECK();
+    return QB_OK;
+}
+
+// ------------------------------------------------------------------------------------------------
+// qb_wt_pack: w_hat fp32 [Cout][Cin][taps] -> bf16 planes wt[plane][Cin][taps][Cout] (hi, lo)
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256)
+k_wt_pack(const float* __restrict__ wq, uint16_t* __restrict__ wt, int Cout, int Cin, int taps) {
+    const int64_t total = (int64_t)Cout * Cin * taps;
+    for (int64_t o = (int64_t)blockIdx.x * 256 + threadIdx.x; o < total; o += (int64_t)gridDim.x * 256) {
+        const int n = (int)(o % Cout);
+        const int64_t ct = o / Cout;                                       // c * taps + tap
+        const float v = __ldg(wq + (int64_t)n * Cin * taps + ct);
+        uint32_t h, l;
+        split2(v, 0.f, h, l);
+        wt[o] = (uint16_t)h;
+        wt[total + o] = (uint16_t)l;
+    }
+}
+
+extern "C" int qb_wt_pack(const float* w_hat, uint16_t* wt, int64_t Cout, int64_t Cin, int taps, void* stream) {
+    QB_CHECK_ARG(w_hat && wt && Cout > 0 && Cin > 0 && taps > 0, "qb_wt_pack: bad argument");
+    const int64_t total = Cout * Cin * taps;
+    QB_CHECK_ARG(total < 2147483647LL, "qb_wt_pack: weight too large");
+    int blocks = (int)((total + 255) / 256);
+    if (blocks > 2048) blocks = 2048;
+    k_wt_pack<<<blocks, 256, 0, qb_stream(stream)>>>(w_hat, wt, (int)Cout, (int)Cin, taps);
+    QB_LAUNCH_CHECK();
+    return QB_OK;
+}
+
+// ------------------------------------------------------------------------------------------------
+// dgrad
+// ------------------------------------------------------------------------------------------------
+constexpr int DG_THREADS = 320;      // TMA warp, MMA warp, 2 x 4 epilogue warps
+constexpr int DG_MAX_STAGES = 8;
+constexpr int DG_MAX_TAPS = 9;
+constexpr int DG_SLAB_BYTES = 128 * 128;
+constexpr int DG_STAGING_BYTES = 4 * DG_SLAB_BYTES;
+
+struct DgradGeom {
+    int B, Hc, Wc;              // output pixel grid of THIS parity class of dX
+    int Cn, Ck;                 // GEMM N = conv input channels, GEMM K (per tap) = conv output channels
+    int TW, TH, TN, tiles_w, tiles_h, tiles_b;
+    int BK;                     // K elements per stage: 64 / 32 / 16  (128 / 64 / 32-byte rows)
+    int stages, ntaps, a_planes, b_planes;
+    int dh[DG_MAX_TAPS], dw[DG_MAX_TAPS], wtap[DG_MAX_TAPS];   // operand pixel = class pixel + (dh, dw); weight tap index
+    FastDiv d_tiles_m, d_tiles_w, d_tiles_h;
+};
+
+__device__ __forceinline__ void dg_decode_tile(int t, const DgradGeom& g, int tiles_m, int& tn, int& b0, int& h0, int& w0) {
+    tn = (int)fdiv((uint32_t)t, g.d_tiles_m);
+    uint32_t tm = (uint32_t)(t - tn * tiles_m);
+    uint32_t q = fdiv(tm, g.d_tiles_w);
+    w0 = (int)(tm - q * (uint32_t)g.tiles_w) * g.TW;
+    tm = q;
+    q = fdiv(tm, g.d_tiles_h);
+    h0 = (int)(tm - q * (uint32_t)g.tiles_h) * g.TH;
+    b0 = (int)q * g.TN;
+}
+
+__device__ __forceinline__ void dg_epi_bar(int id) { asm volatile("bar.sync %0, 128;" ::"r"(id) : "memory"); }
+
+template <int BN>
+__global__ void __launch_bounds__(DG_THREADS, 1)
+k_conv_dgrad(const __grid_constant__ CUtensorMap tmap_a0, const __grid_constant__ CUtensorMap tmap_a1,
+             const __grid_constant__ CUtensorMap tmap_w, const __grid_constant__ CUtensorMap tmap_o, DgradGeom g,
+             const float* __restrict__ scale_range, int scale_bits, float scale_mul) {
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+    const int rb = g.BK * 2;                                     // bytes per operand row
+    const uint32_t a_bytes = 128u * rb, b_bytes = (uint32_t)BN * rb;
+    const uint32_t stage_bytes = g.a_planes * a_bytes + g.b_planes * b_bytes;
+    float* staging = reinterpret_cast<float*>(smem + (size_t)g.stages * stage_bytes);       // 1024-byte aligned
+    uint8_t* tail = reinterpret_cast<uint8_t*>(staging) + DG_STAGING_BYTES;
+    uint64_t* full_bar = reinterpret_cast<uint64_t*>(tail);
+    uint64_t* empty_bar = full_bar + DG_MAX_STAGES;
+    uint64_t* tfull_bar = empty_bar + DG_MAX_STAGES;
+    uint64_t* tempty_bar = tfull_bar + 2;
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty_bar + 2);
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int kblocks = (g.Ck + g.BK - 1) / g.BK;
+    const int num_kb = g.ntaps * kblocks;
+    const int tiles_m = g.tiles_w * g.tiles_h * g.tiles_b;
+    const int tiles_n = (g.Cn + BN - 1) / BN;
+    const int total_tiles = tiles_m * tiles_n;
+    constexpr uint32_t ACC = BN < 32 ? 32 : BN;                  // TMEM columns per accumulator buffer
+    constexpr uint32_t TMEM_COLS = 2 * ACC;
+
+    if (warp == 0 && lane == 0) {
+        tma_prefetch_desc(&tmap_a0);
+        tma_prefetch_desc(&tmap_w);
+        tma_prefetch_desc(&tmap_o);
+        for (int s = 0; s < g.stages; ++s) {
+            mbar_init(&full_bar[s], 1);
+            mbar_init(&empty_bar[s], 1);
+        }
+        for (int i = 0; i < 2; ++i) {
+            mbar_init(&tfull_bar[i], 1);
+            mbar_init(&tempty_bar[i], 8);
+        }
+        fence_barrier_init();
+    }
+    if (warp == 1) tmem_alloc<TMEM_COLS>(tmem_slot);
+    tc_fence_before_sync();
+    __syncthreads();
+    tc_fence_after_sync();
+    const uint32_t tmem_base = *tmem_slot;
+
+    if (warp == 0) {
+        // ===== TMA producer =====
+        if (elect_one()) {
+            uint32_t it = 0;
+            const uint32_t a_box = (uint32_t)(g.TN * g.TH * g.TW) * rb;
+            for (int t = blockIdx.x; t < total_tiles; t += gridDim.x) {
+                int tn, b0, h0, w0;
+                dg_decode_tile(t, g, tiles_m, tn, b0, h0, w0);
+                const int n0 = tn * BN;
+                for (int tp = 0; tp < g.ntaps; ++tp) {
+                    for (int kb = 0; kb < kblocks; ++kb, ++it) {
+                        const int s = it % g.stages;
+                        const uint32_t ph = (it / g.stages) & 1;
+                        mbar_wait_trap(&empty_bar[s], ph ^ 1);
+                        mbar_arrive_expect_tx(&full_bar[s], g.a_planes * a_box + g.b_planes * b_bytes);
+                        uint8_t* sa = smem + (size_t)s * stage_bytes;
+                        tma_load_4d(sa, &tmap_a0, &full_bar[s], kb * g.BK, w0 + g.dw[tp], h0 + g.dh[tp], b0);
+                        if (g.a_planes > 1)
+                            tma_load_4d(sa + a_bytes, &tmap_a1, &full_bar[s], kb * g.BK, w0 + g.dw[tp], h0 + g.dh[tp], b0);
+                        uint8_t* sb = sa + g.a_planes * a_bytes;
+                        for (int p = 0; p < g.b_planes; ++p)
+                            tma_load_3d(sb + (size_t)p * b_bytes, &tmap_w, &full_bar[s], kb * g.BK, g.wtap[tp], p * g.Cn + n0);
+                    }
+                }
+            }
+        }
+    } else if (warp == 1) {
+        // ===== MMA issuer =====
+        constexpr uint32_t idesc = idesc_bf16(128, BN, 0, 0);
+        const int ksteps = g.BK / 16;
+        uint32_t it = 0;
+        int j = 0;
+        for (int t = blockIdx.x; t < total_tiles; t += gridDim.x, ++j) {
+            const int buf = j & 1;
+            mbar_wait_trap(&tempty_bar[buf], ((j >> 1) & 1) ^ 1);
+            tc_fence_after_sync();
+            const uint32_t d_tmem = tmem_base + (uint32_t)buf * ACC;
+            for (int kb = 0; kb < num_kb; ++kb, ++it) {
+                const int s = it % g.stages;
+                const uint32_t ph = (it / g.stages) & 1;
+                mbar_wait_trap(&full_bar[s], ph);
+                tc_fence_after_sync();
+                if (elect_one()) {
+                    const uint32_t a_addr = smem_u32(smem + (size_t)s * stage_bytes);
+                    const uint32_t b_addr = a_addr + g.a_planes * a_bytes;
+                    uint32_t acc = kb != 0;
+                    for (int k = 0; k < ksteps; ++k) {
+                        // hi*hi, hi*lo, lo*hi  (lo*lo is below the split error)
+                        for (int pa = 0; pa < g.a_planes; ++pa)
+                            for (int pb = 0; pb < g.b_planes; ++pb) {
+                                if (pa == 1 && pb == 1) continue;
+                                umma_f16(d_tmem, desc_kmajor(a_addr + pa * a_bytes + k * 32, rb),
+                                         desc_kmajor(b_addr + pb * b_bytes + k * 32, rb), idesc, acc);
+                                acc = 1;
+                            }
+                    }
+                    umma_commit(&empty_bar[s]);
+                    if (kb == num_kb - 1) umma_commit(&tfull_bar[buf]);
+                }
+                __syncwarp();
+            }
+        }
+    } else {
+        // ===== epilogue: 2 groups x 4 warps; group `grp` owns the 32-column slabs cs with cs % 2 == grp =====
+        const int e_all = threadIdx.x - 64;
+        const int grp = e_all >> 7, et = e_all & 127;
+        const int sub = warp & 3;
+        float scale = scale_mul;
+        if (scale_range) scale *= make_qparams_d((double)__ldg(scale_range), (double)__ldg(scale_range + 1), scale_bits).scale;
+        const int i = sub * 32 + lane;
+        uint8_t* my_staging = reinterpret_cast<uint8_t*>(staging) + grp * 2 * DG_SLAB_BYTES;
+        const uint32_t stage_u32 = smem_u32(my_staging);
+        const uint32_t row_off = (uint32_t)i * 128u, sw = (uint32_t)(i & 7);
+        const int bar_id = 1 + grp;
+        int j = 0;
+        uint32_t slab = 0;
+        for (int t = blockIdx.x; t < total_tiles; t += gridDim.x, ++j) {
+            int tn, b0, h0, w0;
+            dg_decode_tile(t, g, tiles_m, tn, b0, h0, w0);
+            const int n0 = tn * BN;
+            const int ncols = (g.Cn - n0 < BN) ? g.Cn - n0 : BN;
+            const int nslabs = (ncols + 31) >> 5;
+            const int last_cs = ((nslabs - 1 - grp) & ~1) + grp;
+            const int buf = j & 1;
+            mbar_wait_trap(&tfull_bar[buf], (j >> 1) & 1);
+            tc_fence_after_sync();
+            const uint32_t t_addr = tmem_base + (uint32_t)buf * ACC + ((uint32_t)(sub * 32) << 16);
+            if (nslabs <= grp) {
+                tc_fence_before_sync();
+                __syncwarp();
+                if (lane == 0) mbar_arrive(&tempty_bar[buf]);
+            }
+#pragma unroll 1
+            for (int cs = grp; cs < nslabs; cs += 2, ++slab) {
+                uint32_t r[32];
+                tmem_ld_32x32(t_addr + (uint32_t)(cs * 32), r);
+                tmem_ld_wait();
+                if (cs == last_cs) {
+                    tc_fence_before_sync();
+                    __syncwarp();
+                    if (lane == 0) mbar_arrive(&tempty_bar[buf]);
+                }
+                const uint32_t dst = stage_u32 + (slab & 1u) * (uint32_t)DG_SLAB_BYTES + row_off;
+#pragma unroll
+                for (int q = 0; q < 8; ++q) {
+                    const float v0 = __uint_as_float(r[4 * q]) * scale, v1 = __uint_as_float(r[4 * q + 1]) * scale,
+                                v2 = __uint_as_float(r[4 * q + 2]) * scale, v3 = __uint_as_float(r[4 * q + 3]) * scale;
+                    asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(dst + (((uint32_t)q ^ sw) << 4)), "f"(v0), "f"(v1),
+                                 "f"(v2), "f"(v3) : "memory");
+                }
+                fence_proxy_async();
+                if (et == 0) tma_store_wait_read<0>();
+                dg_epi_bar(bar_id);
+                if (et == 0) {
+                    tma_store_4d(&tmap_o, my_staging + (slab & 1u) * DG_SLAB_BYTES, n0 + cs * 32, w0, h0, b0);
+                    tma_store_commit();
+                }
+            }
+        }
+        if (et == 0) tma_store_wait<0>();
+    }
+    tc_fence_before_sync();
+    __syncthreads();
+    if (warp == 1) tmem_dealloc<TMEM_COLS>(tmem_base);
+}
+
+template <int BN>
+static int dgrad_launch(const CUtensorMap& ta0, const CUtensorMap& ta1, const CUtensorMap& tw, const CUtensorMap& to, DgradGeom& g,
+                        const float* scale_range, int scale_bits, float scale_mul, cudaStream_t st) {
+    const size_t stage = (size_t)g.a_planes * 128 * g.BK * 2 + (size_t)g.b_planes * BN * g.BK * 2;
+    const size_t fixed = DG_STAGING_BYTES + 1024 + 512;
+    int s = (int)((225 * 1024 - fixed) / stage);
+    g.stages = s > DG_MAX_STAGES ? DG_MAX_STAGES : s;
+    if (g.stages < 2) {
+        qb_set_error("qb_conv_dgrad: a pipeline stage of %zu bytes does not fit twice", stage);
+        return QB_ERR_UNSUPPORTED;
+    }
+    const size_t smem = (size_t)g.stages * stage + fixed;
+    QB_CUDA(cudaFuncSetAttribute(k_conv_dgrad<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    const int64_t total = (int64_t)g.tiles_w * g.tiles_h * g.tiles_b * ((g.Cn + BN - 1) / BN);
+    int sms = qb_sm_count();
+    if (sms <= 0) sms = 148;
+    const unsigned grid = (unsigned)(total < sms ? total : sms);
+    k_conv_dgrad<BN><<<grid, DG_THREADS, smem, st>>>(ta0, ta1, tw, to, g, scale_range, scale_bits, scale_mul);
+    QB_LAUNCH_CHECK();
+    return QB_OK;
+}
+
+/* dX of y = conv2d(x, w_hat) (groups 1, dilation 1, square stride / padding):
+ *   a0 (and a1): bf16 [B,Ho,Wo,Cout] channels-last planes of the output gradient (one plane: integer codes q - zp, or two
+ *   planes: hi / lo split);  wt: qb_wt_pack's planes;  dx: fp32 [B,H,W,Cin] channels-last.
+ *   dx = scale * SUM, scale = scale_mul * (scale_range ? s(scale_range, scale_bits) : 1)  (s = the zero-point quantizer's
+ *   step, quantize.py:78-80).  Linear layers: H = W = kh = kw = 1.                                                       */
+extern "C" int qb_conv_dgrad(const uint16_t* a0, const uint16_t* a1, const uint16_t* wt, float* dx, int64_t B, int64_t H, int64_t W,
+                             int64_t Cin, int64_t Cout, int kh, int kw, int stride, int pad, const float* scale_range,
+                             int scale_bits, float scale_mul, void* stream) {
+    QB_CHECK_ARG(a0 && wt && dx, "qb_conv_dgrad: null pointer");
+    QB_CHECK_ARG(B > 0 && H > 0 && W > 0 && Cin > 0 && Cout > 0 && kh > 0 && kw > 0 && stride > 0 && pad >= 0, "qb_conv_dgrad: bad shape");
+    const int64_t Ho = (H + 2 * pad - kh) / stride + 1, Wo = (W + 2 * pad - kw) / stride + 1;
+    if (Ho < 1 || Wo < 1 || Cin % 4 != 0 || Cout % 8 != 0 || stride > 4 ||
+        ((reinterpret_cast<uintptr_t>(a0) | reinterpret_cast<uintptr_t>(a1) | reinterpret_cast<uintptr_t>(wt) |
+          reinterpret_cast<uintptr_t>(dx)) & 15) != 0) {
+        qb_set_error("qb_conv_dgrad: unsupported geometry (need Cin%%4==0, Cout%%8==0, stride<=4, 16-byte aligned tensors): "
+                     "Cin=%lld Cout=%lld k=%dx%d stride=%d", (long long)Cin, (long long)Cout, kh, kw, stride);
+        return QB_ERR_UNSUPPORTED;
+    }
+    QB_CHECK_ARG(B * H * W < 2147483647LL && B * Ho * Wo < 2147483647LL, "qb_conv_dgrad: pixel count exceeds int32");
+    cudaStream_t st = qb_stream(stream);
+    const int BK = Cout > 32 ? 64 : (Cout > 16 ? 32 : 16);
+    const int BN = Cin >= 128 ? 128 : (Cin > 32 ? 64 : (Cin > 16 ? 32 : 16));
+    CUtensorMap ta0, ta1, tw;
+    {
+        const uint64_t dims[4] = {(uint64_t)Cout, (uint64_t)Wo, (uint64_t)Ho, (uint64_t)B};
+        const uint64_t str[3] = {(uint64_t)Cout * 2, (uint64_t)Wo * Cout * 2, (uint64_t)Ho * Wo * Cout * 2};
+        // box filled in per class (tile shape)
+        (void)dims; (void)str;
+    }
+    {   // weights: dims {Cout (K), taps, planes * Cin (rows)}
+        const uint64_t dims[3] = {(uint64_t)Cout, (uint64_t)(kh * kw), (uint64_t)(2 * Cin)};
+        const uint64_t str[2] = {(uint64_t)Cout * 2, (uint64_t)Cout * 2 * kh * kw};
+        const uint32_t box[3] = {(uint32_t)BK, 1u, (uint32_t)BN};
+        int rc = qb_make_tmap(&tw, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3, wt, dims, str, box, nullptr, BK * 2);
+        if (rc) return rc;
+    }
+    // parity classes of dX: pixel h = stride*i + ph receives tap r iff (ph + pad - r) % stride == 0, from ho = i + (ph + pad - r)/stride
+    bool any_empty = false;
+    for (int ph = 0; ph < stride && ph < H; ++ph)
+        for (int pw = 0; pw < stride && pw < W; ++pw) {
+            int cnt = 0;
+            for (int r = 0; r < kh; ++r)
+                for (int s = 0; s < kw; ++s)
+                    if ((ph + pad - r) % stride == 0 && (pw + pad - s) % stride == 0) ++cnt;
+            if (cnt == 0) any_empty = true;
+        }
+    if (any_empty) QB_CUDA(cudaMemsetAsync(dx, 0, (size_t)B * H * W * Cin * 4, st));
+    for (int ph = 0; ph < stride && ph < H; ++ph) {
+        for (int pw = 0; pw < stride && pw < W; ++pw) {
+            DgradGeom g;
+            memset(&g, 0, sizeof(g));
+            g.ntaps = 0;
+            for (int r = 0; r < kh; ++r)
+                for (int s = 0; s < kw; ++s) {
+                    // C's % on negative numbers: compare against a non-negative residue
+                    const int ah = ph + pad - r, aw = pw + pad - s;
+                    if (((ah % stride) + stride) % stride != 0 || ((aw % stride) + stride) % stride != 0) continue;
+                    if (g.ntaps == DG_MAX_TAPS) {
+                        qb_set_error("qb_conv_dgrad: more than %d taps per parity class (k=%dx%d stride=%d)", DG_MAX_TAPS, kh, kw, stride);
+                        return QB_ERR_UNSUPPORTED;
+                    }
+                    // floor division (ah may be negative)
+                    g.dh[g.ntaps] = (ah >= 0 ? ah : ah - stride + 1) / stride;
+                    g.dw[g.ntaps] = (aw >= 0 ? aw : aw - stride + 1) / stride;
+                    g.wtap[g.ntaps] = r * kw + s;
+                    ++g.ntaps;
+                }
+            if (g.ntaps == 0) continue;
+            const int64_t Hc = (H - ph + stride - 1) / stride, Wc = (W - pw + stride - 1) / stride;
+            g.B = (int)B; g.Hc = (int)Hc; g.Wc = (int)Wc; g.Cn = (int)Cin; g.Ck = (int)Cout;
+            g.BK = BK;
+            g.a_planes = a1 ? 2 : 1;
+            g.b_planes = 2;
+            g.TW = (int)(Wc < 128 ? Wc : 128);
+            g.TH = (int)(128 / g.TW < Hc ? 128 / g.TW : Hc);
+            g.TN = (g.TH == Hc && g.TW == Wc) ? (int)(128 / (Hc * Wc) < B ? 128 / (Hc * Wc) : B) : 1;
+            if (g.TN < 1) g.TN = 1;
+            g.tiles_w = (int)((Wc + g.TW - 1) / g.TW);
+            g.tiles_h = (int)((Hc + g.TH - 1) / g.TH);
+            g.tiles_b = (int)((B + g.TN - 1) / g.TN);
+            g.d_tiles_m = make_fastdiv((uint32_t)(g.tiles_w * g.tiles_h * g.tiles_b));
+            g.d_tiles_w = make_fastdiv((uint32_t)g.tiles_w);
+            g.d_tiles_h = make_fastdiv((uint32_t)g.tiles_h);
+            {
+                const uint64_t dims[4] = {(uint64_t)Cout, (uint64_t)Wo, (uint64_t)Ho, (uint64_t)B};
+                const uint64_t str[3] = {(uint64_t)Cout * 2, (uint64_t)Wo * Cout * 2, (uint64_t)Ho * Wo * Cout * 2};
+                const uint32_t box[4] = {(uint32_t)BK, (uint32_t)g.TW, (uint32_t)g.TH, (uint32_t)g.TN};
+                int rc = qb_make_tmap(&ta0, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, a0, dims, str, box, nullptr, BK * 2);
+                if (rc) return rc;
+                rc = qb_make_tmap(&ta1, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, a1 ? a1 : a0, dims, str, box, nullptr, BK * 2);
+                if (rc) return rc;
+            }
+            CUtensorMap to;
+            {   // strided view of dX holding this class: dims {Cin, Wc, Hc, B}
+                float* base = dx + ((int64_t)ph * W + pw) * Cin;
+                const uint64_t dims[4] = {(uint64_t)Cin, (uint64_t)Wc, (uint64_t)Hc, (uint64_t)B};
+                const uint64_t str[3] = {(uint64_t)stride * Cin * 4, (uint64_t)stride * W * Cin * 4, (uint64_t)H * W * Cin * 4};
+                const uint32_t box[4] = {32u, (uint32_t)g.TW, (uint32_t)g.TH, (uint32_t)g.TN};
+                int rc = qb_make_tmap(&to, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, base, dims, str, box, nullptr, 128);
+                if (rc) return rc;
+            }
+            int rc;
+            if (BN == 128) rc = dgrad_launch<128>(ta0, ta1, tw, to, g, scale_range, scale_bits, scale_mul, st);
+            else if (BN == 64) rc = dgrad_launch<64>(ta0, ta1, tw, to, g, scale_range, scale_bits, scale_mul, st);
+            else if (BN == 32) rc = dgrad_launch<32>(ta0, ta1, tw, to, g, scale_range, scale_bits, scale_mul, st);
+            else rc = dgrad_launch<16>(ta0, ta1, tw, to, g, scale_range, scale_bits, scale_mul, st);
+            if (rc) return rc;
+        }
+    }
+    return QB_OK;
+}
+
+// ------------------------------------------------------------------------------------------------
+// wgrad
+// ------------------------------------------------------------------------------------------------
+constexpr int WG_THREADS = 192;      // TMA warp, MMA warp, 4 drain warps
+constexpr int WG_MAX_STAGES = 8;
+constexpr int WG_MAX_ACC = 16;
+
+struct WgradGeom {
+    int B, Ho, Wo, Cin, Cout, kh, kw, stride, pad;
+    int TW, TH, TN, tiles_w, tiles_h, tiles_b, P;     // pixel tile (= K block), P = TW*TH*TN, P % 16 == 0
+    int RC, RN;                 // channels per TMA box ("run") of the x / g operand: 64 / 32 / 16
+    int rpm;                    // runs per 128-row M tile = 128 / RC
+    int total_runs, mtiles;     // taps * Cin / RC;  ceil(total_runs / rpm)
+    int J;                      // M tiles (accumulators) per CTA
+    int mgroups, nblocks, slices, BN;
+    int g_planes, a_stages, b_stages, total_tiles, mrows;
+    FastDiv d_tiles_w, d_tiles_h, d_cin_runs, d_kw;
+};
+
+__global__ void __launch_bounds__(WG_THREADS, 1)
+k_conv_wgrad(const __grid_constant__ CUtensorMap tmap_x, const __grid_constant__ CUtensorMap tmap_g0,
+             const __grid_constant__ CUtensorMap tmap_g1, float* __restrict__ partial, WgradGeom g) {
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+    const uint32_t a_slot = 128u * (uint32_t)g.P * 2u;                        // rpm runs x [P][RC] bf16
+    const uint32_t b_plane = (uint32_t)g.BN * (uint32_t)g.P * 2u;
+    const uint32_t b_slot = (uint32_t)g.g_planes * b_plane;
+    uint8_t* s_a = smem;
+    uint8_t* s_b = s_a + (size_t)g.a_stages * a_slot;
+    uint8_t* tail = s_b + (size_t)g.b_stages * b_slot;
+    uint64_t* a_full = reinterpret_cast<uint64_t*>(tail);
+    uint64_t* a_empty = a_full + WG_MAX_STAGES;
+    uint64_t* b_full = a_empty + WG_MAX_STAGES;
+    uint64_t* b_empty = b_full + WG_MAX_STAGES;
+    uint64_t* done_bar = b_empty + WG_MAX_STAGES;
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(done_bar + 1);
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    // unit -> (slice, M group, N block)
+    const int unit = blockIdx.x;
+    const int nb = unit % g.nblocks;
+    const int mg = (unit / g.nblocks) % g.mgroups;
+    const int slice = unit / (g.nblocks * g.mgroups);
+    const int n0 = nb * g.BN;
+    const int mt0 = mg * g.J;
+    const int jn = (g.mtiles - mt0 < g.J) ? g.mtiles - mt0 : g.J;             // accumulators of this CTA
+    const int t_begin = (int)(((int64_t)g.total_tiles * slice) / g.slices);
+    const int t_end = (int)(((int64_t)g.total_tiles * (slice + 1)) / g.slices);
+    const uint32_t acc_stride = (uint32_t)(g.BN < 32 ? 32 : g.BN);
+
+    // a tail M tile has fewer runs than rpm: its unused operand rows must not hold NaN patterns
+    for (uint32_t i = threadIdx.x; i < (uint32_t)g.a_stages * a_slot / 16; i += WG_THREADS)
+        reinterpret_cast<uint4*>(s_a)[i] = make_uint4(0u, 0u, 0u, 0u);
+    if (warp == 0 && lane == 0) {
+        tma_prefetch_desc(&tmap_x);
+        tma_prefetch_desc(&tmap_g0);
+        for (int s = 0; s < g.a_stages; ++s) { mbar_init(&a_full[s], 1); mbar_init(&a_empty[s], 1); }
+        for (int s = 0; s < g.b_stages; ++s) { mbar_init(&b_full[s], 1); mbar_init(&b_empty[s], 1); }
+        mbar_init(done_bar, 1);
+        fence_barrier_init();
+    }
+    if (warp == 1) tmem_alloc<512>(tmem_slot);
+    fence_proxy_async();
+    tc_fence_before_sync();
+    __syncthreads();
+    tc_fence_after_sync();
+    const uint32_t tmem_base = *tmem_slot;
+    const int rbA = g.RC * 2, rbB = g.RN * 2;
+    const uint32_t runA = (uint32_t)g.P * rbA, runB = (uint32_t)g.P * rbB;     // bytes of one TMA box = LBO
+    const int nruns_b = g.BN / g.RN;
+
+    auto decode = [&](int t, int& b0, int& ho0, int& wo0) {
+        uint32_t q = fdiv((uint32_t)t, g.d_tiles_w);
+        wo0 = (int)((uint32_t)t - q * (uint32_t)g.tiles_w) * g.TW;
+        const uint32_t q2 = fdiv(q, g.d_tiles_h);
+        ho0 = (int)(q - q2 * (uint32_t)g.tiles_h) * g.TH;
+        b0 = (int)q2 * g.TN;
+    };
+
+    if (warp == 0) {
+        if (elect_one()) {
+            uint32_t ia = 0, ib = 0;
+            for (int t = t_begin; t < t_end; ++t) {
+                int b0, ho0, wo0;
+                decode(t, b0, ho0, wo0);
+                {   // gradient tile (B operand), shared by every accumulator of this CTA
+                    const int s = ib % g.b_stages;
+                    const uint32_t ph = (ib / g.b_stages) & 1;
+                    mbar_wait_trap(&b_empty[s], ph ^ 1);
+                    mbar_arrive_expect_tx(&b_full[s], b_slot);
+                    uint8_t* sb = s_b + (size_t)s * b_slot;
+                    for (int p = 0; p < g.g_planes; ++p)
+                        for (int r = 0; r < nruns_b; ++r)
+                            tma_load_4d(sb + (size_t)p * b_plane + (size_t)r * runB, p ? &tmap_g1 : &tmap_g0, &b_full[s],
+                                        n0 + r * g.RN, wo0, ho0, b0);
+                    ++ib;
+                }
+                for (int j = 0; j < jn; ++j, ++ia) {
+                    const int s = ia % g.a_stages;
+                    const uint32_t ph = (ia / g.a_stages) & 1;
+                    const int run0 = (mt0 + j) * g.rpm;
+                    const int nr = (g.total_runs - run0 < g.rpm) ? g.total_runs - run0 : g.rpm;
+                    mbar_wait_trap(&a_empty[s], ph ^ 1);
+                    mbar_arrive_expect_tx(&a_full[s], (uint32_t)nr * runA);
+                    uint8_t* sa = s_a + (size_t)s * a_slot;
+                    for (int rr = 0; rr < nr; ++rr) {
+                        const uint32_t run = (uint32_t)(run0 + rr);
+                        const uint32_t tap = fdiv(run, g.d_cin_runs);                       // run / (Cin / RC)
+                        const int c0 = (int)(run - tap * (uint32_t)(g.Cin / g.RC)) * g.RC;
+                        const uint32_t r = fdiv(tap, g.d_kw);
+                        const int s_ = (int)(tap - r * (uint32_t)g.kw);
+                        tma_load_4d(sa + (size_t)rr * runA, &tmap_x, &a_full[s], c0, wo0 * g.stride - g.pad + s_,
+                                    ho0 * g.stride - g.pad + (int)r, b0);
+                    }
+                }
+            }
+        }
+    } else if (warp == 1) {
+        const uint32_t idesc = idesc_bf16(128, (uint32_t)g.BN, 1, 1);
+        const int ksteps = g.P / 16;
+        uint32_t ia = 0, ib = 0;
+        for (int t = t_begin; t < t_end; ++t, ++ib) {
+            const int sbi = ib % g.b_stages;
+            mbar_wait_trap(&b_full[sbi], (ib / g.b_stages) & 1);
+            const uint32_t b_addr = smem_u32(s_b + (size_t)sbi * b_slot);
+            for (int j = 0; j < jn; ++j, ++ia) {
+                const int s = ia % g.a_stages;
+                mbar_wait_trap(&a_full[s], (ia / g.a_stages) & 1);
+                tc_fence_after_sync();
+                if (elect_one()) {
+                    const uint32_t a_addr = smem_u32(s_a + (size_t)s * a_slot);
+                    const uint32_t d_tmem = tmem_base + (uint32_t)j * acc_stride;
+                    uint32_t acc = t != t_begin;
+                    for (int ks = 0; ks < ksteps; ++ks)
+                        for (int p = 0; p < g.g_planes; ++p) {
+                            umma_f16(d_tmem, desc_mnmajor(a_addr + (uint32_t)(ks * 16 * rbA), rbA, runA),
+                                     desc_mnmajor(b_addr + (uint32_t)p * b_plane + (uint32_t)(ks * 16 * rbB), rbB, runB), idesc, acc);
+                            acc = 1;
+                        }
+                    umma_commit(&a_empty[s]);
+                    if (j == jn - 1) umma_commit(&b_empty[sbi]);
+                    if (j == jn - 1 && t == t_end - 1) umma_commit(done_bar);
+                }
+                __syncwarp();
+            }
+        }
+    } else if (t_end > t_begin) {
+        // ===== drain: partial[slice][row][n], rows = (tap, c) of this CTA's M tiles =====
+        const int sub = warp & 3;
+        mbar_wait_trap(done_bar, 0);
+        tc_fence_after_sync();
+        for (int j = 0; j < jn; ++j) {
+            const int row = (mt0 + j) * 128 + sub * 32 + lane;
+            for (int c0 = 0; c0 < g.BN; c0 += 32) {
+                uint32_t r[32];
+                tmem_ld_32x32(tmem_base + (uint32_t)j * acc_stride + (uint32_t)c0 + ((uint32_t)(sub * 32) << 16), r);
+                tmem_ld_wait();
+                if (row < g.mrows) {
+                    float* dst = partial + ((size_t)slice * g.mrows + row) * g.Cout + n0 + c0;
+#pragma unroll
+                    for (int u = 0; u < 32; u += 4)
+                        if (n0 + c0 + u < g.Cout)
+                            *reinterpret_cast<uint4*>(dst + u) = make_uint4(r[u], r[u + 1], r[u + 2], r[u + 3]);
+                }
+            }
+        }
+    }
+    tc_fence_before_sync();
+    __syncthreads();
+    if (warp == 1) tmem_dealloc<512>(tmem_base);
+}
+
+// Column sums of g: acc[tap][n] = SUM over the output pixels whose tap (r,s) reads inside the image, acc[taps][n] = SUM over all
+// pixels (= the bias gradient).  Partials per block in a fixed order (deterministic).  Exits at once when neither is needed.
+constexpr int CS_BLOCKS = 296;
+__global__ void __launch_bounds__(256)
+k_wgrad_colsums(const float* __restrict__ gf, float* __restrict__ cpart, int B, int Ho, int Wo, int Cout, int H, int W, int kh, int kw,
+                int stride, int pad, const float* __restrict__ a_range, int a_bits, int want_db) {
+    const int taps = kh * kw;
+    if (!want_db) {
+        const QParams pa = make_qparams_d((double)__ldg(a_range), (double)__ldg(a_range + 1), a_bits);
+        if (pa.lo == 0.0f) return;
+    }
+    const int64_t rows = (int64_t)B * Ho;                                       // (b, ho) rows split over the blocks
+    const int64_t r_begin = rows * blockIdx.x / gridDim.x, r_end = rows * (blockIdx.x + 1) / gridDim.x;
+    for (int n = threadIdx.x; n < Cout; n += 256) {
+        float acc[10];
+#pragma unroll
+        for (int k = 0; k < 10; ++k) acc[k] = 0.f;
+        for (int64_t rw = r_begin; rw < r_end; ++rw) {
+            const int ho = (int)(rw % Ho);
+            uint32_t vh = 0;
+            for (int r = 0; r < kh; ++r) {
+                const int hi = ho * stride - pad + r;
+                if (hi >= 0 && hi < H) vh |= 1u << r;
+            }
+            const float* src = gf + (rw * Wo) * Cout + n;
+            for (int wo = 0; wo < Wo; ++wo) {
+                const float v = __ldg(src + (int64_t)wo * Cout);
+                acc[9] += v;
+#pragma unroll
+                for (int tp = 0; tp < 9; ++tp) {
+                    if (tp < taps) {
+                        const int r = tp / kw, s = tp - r * kw;
+                        const int wi = wo * stride - pad + s;
+                        if (((vh >> r) & 1u) && wi >= 0 && wi < W) acc[tp] += v;
+                    }
+                }
+            }
+        }
+        for (int tp = 0; tp < taps; ++tp) cpart[((size_t)blockIdx.x * (taps + 1) + tp) * Cout + n] = acc[tp];
+        cpart[((size_t)blockIdx.x * (taps + 1) + taps) * Cout + n] = acc[9];
+    }
+}
+
+// dW[n][c][tap] = sa * SUM_slices partial[slice][tap*Cin + c][n] + la * SUM_blocks cpart[blk][tap][n];  db[n] = SUM_blocks cpart[blk][taps][n]
+__global__ void __launch_bounds__(256)
+k_wgrad_reduce(const float* __restrict__ partial, int slices, const float* __restrict__ cpart, int cblocks, float* __restrict__ dw,
+               float* __restrict__ db, int Cout, int Cin, int taps, const float* __restrict__ a_range, int a_bits) {
+    const int mrows = taps * Cin;
+    const int64_t idx = (int64_t)blockIdx.x * 256 + threadIdx.x;
+    const QParams pa = make_qparams_d((double)__ldg(a_range), (double)__ldg(a_range + 1), a_bits);
+    if (idx < (int64_t)mrows * Cout) {
+        const int n = (int)(idx % Cout), row = (int)(idx / Cout);
+        const int tap = row / Cin, c = row - tap * Cin;
+        double sq = 0.0;
+        for (int s = 0; s < slices; ++s) sq += (double)partial[((size_t)s * mrows + row) * Cout + n];
+        double v = (double)pa.scale * sq;
+        if (pa.lo != 0.0f) {
+            double sm = 0.0;
+            for (int k = 0; k < cblocks; ++k) sm += (double)cpart[((size_t)k * (taps + 1) + tap) * Cout + n];
+            v += (double)pa.lo * sm;
+        }
+        dw[((size_t)n * Cin + c) * taps + tap] = (float)v;
+    }
+    if (db && idx < Cout) {
+        double sm = 0.0;
+        for (int k = 0; k < cblocks; ++k) sm += (double)cpart[((size_t)k * (taps + 1) + taps) * Cout + idx];
+        db[idx] = (float)sm;
+    }
+}
+
+static int wgrad_geom(WgradGeom& g, int64_t B, int64_t H, int64_t W, int64_t Cin, int64_t Cout, int kh, int kw, int stride, int pad,
+                      int g_planes) {
+    memset(&g, 0, sizeof(g));
+    const int64_t Ho = (H + 2 * pad - kh) / stride + 1, Wo = (W + 2 * pad - kw) / stride + 1;
+    if (Ho < 1 || Wo < 1 || Cin % 16 != 0 || Cout % 8 != 0 || kh * kw > 9 || stride > 2) return 0;
+    g.B = (int)B; g.Ho = (int)Ho; g.Wo = (int)Wo; g.Cin = (int)Cin; g.Cout = (int)Cout; g.kh = kh; g.kw = kw; g.stride = stride; g.pad = pad;
+    g.g_planes = g_planes;
+    g.RC = Cin % 64 == 0 ? 64 : (Cin % 32 == 0 ? 32 : 16);
+    g.RN = Cout > 32 ? 64 : (Cout > 16 ? 32 : 16);
+    g.BN = Cout >= 128 ? 128 : (int)((Cout + g.RN - 1) / g.RN) * g.RN;
+    g.rpm = 128 / g.RC;
+    g.total_runs = kh * kw * (int)Cin / g.RC;
+    g.mtiles = (g.total_runs + g.rpm - 1) / g.rpm;
+    g.mrows = kh * kw * (int)Cin;
+    g.nblocks = (int)((Cout + g.BN - 1) / g.BN);
+    const int acc_stride = g.BN < 32 ? 32 : g.BN;
+    int jmax = 512 / acc_stride;
+    if (jmax > WG_MAX_ACC) jmax = WG_MAX_ACC;
+    g.mgroups = (g.mtiles + jmax - 1) / jmax;
+    g.J = (g.mtiles + g.mgroups - 1) / g.mgroups;
+    // pixel tile: P = TW*TH*TN pixels, P % 16 == 0, P <= pmax, covering the (Wo, Ho, B) grid with the least padding
+    const int64_t b_bytes_per_px = (int64_t)g_planes * g.BN * 2;
+    const int pmax = b_bytes_per_px * 128 * 2 + 3 * 128 * 256 <= 200 * 1024 ? 128 : 64;
+    double best = -1.0;
+    for (int tw = 1; tw <= 128 && tw <= Wo + 7; ++tw) {
+        if (tw > Wo && tw != ((Wo + 7) / 8) * 8) continue;
+        for (int th = 1; th * tw <= pmax && th <= Ho + 7; ++th) {
+            if (th > Ho && th != ((Ho + 7) / 8) * 8) continue;
+            for (int tn = 1; tn * th * tw <= pmax && tn <= B; tn *= 2) {
+                const int P = tw * th * tn;
+                if (P % 16 != 0) continue;
+                const double cover = (double)((Wo + tw - 1) / tw) * tw * (double)((Ho + th - 1) / th) * th * (double)((B + tn - 1) / tn) * tn;
+                const double eff = (double)Wo * Ho * B / cover + 1e-4 * P / 128.0;
+                if (eff > best) { best = eff; g.TW = tw; g.TH = th; g.TN = tn; }
+            }
+        }
+    }
+    if (best < 0) return 0;
+    g.P = g.TW * g.TH * g.TN;
+    g.tiles_w = (int)((Wo + g.TW - 1) / g.TW);
+    g.tiles_h = (int)((Ho + g.TH - 1) / g.TH);
+    g.tiles_b = (int)((B + g.TN - 1) / g.TN);
+    g.total_tiles = g.tiles_w * g.tiles_h * g.tiles_b;
+    int sms = qb_sm_count();
+    if (sms <= 0) sms = 148;
+    const int units = g.mgroups * g.nblocks;
+    g.slices = units >= sms ? 1 : sms / units;
+    if (g.slices > g.total_tiles) g.slices = g.total_tiles;
+    if (g.slices < 1) g.slices = 1;
+    const size_t a_slot = (size_t)128 * g.P * 2, b_slot = (size_t)g_planes * g.BN * g.P * 2;
+    g.b_stages = 2;
+    int as = (int)((220 * 1024 - 1024 - 512 - (size_t)g.b_stages * b_slot) / a_slot);
+    g.a_stages = as > WG_MAX_STAGES ? WG_MAX_STAGES : as;
+    if (g.a_stages < 2) return 0;
+    g.d_tiles_w = make_fastdiv((uint32_t)g.tiles_w);
+    g.d_tiles_h = make_fastdiv((uint32_t)g.tiles_h);
+    g.d_cin_runs = make_fastdiv((uint32_t)(Cin / g.RC));
+    g.d_kw = make_fastdiv((uint32_t)kw);
+    return 1;
+}
+
+extern "C" size_t qb_conv_wgrad_ws_bytes(int64_t B, int64_t H, int64_t W, int64_t Cin, int64_t Cout, int kh, int kw, int stride, int pad) {
+    WgradGeom g;
+    if (!wgrad_geom(g, B, H, W, Cin, Cout, kh, kw, stride, pad, 2)) return 0;
+    return ((size_t)g.slices * g.mrows * Cout + (size_t)CS_BLOCKS * (kh * kw + 1) * Cout) * 4 + 256;
+}
+
+/* dW (and db) of y = conv2d(x_hat, w) + b from
+ *   g_hi / g_lo : bf16 hi / lo planes [B,Ho,Wo,Cout] (channels-last) of the output gradient (g_lo may be null: one plane)
+ *   g_f32       : the same gradient in fp32 (bias gradient and the zero-padding term when the input range does not start at 0)
+ *   x16         : bf16 integer codes q_a [B,H,W,Cin] (channels-last) of the input quantizer with its device range
+ * -> dw fp32 [Cout][Cin][kh][kw], db fp32 [Cout] (optional).  Deterministic.                                              */
+extern "C" int qb_conv_wgrad(const uint16_t* g_hi, const uint16_t* g_lo, const float* g_f32, const uint16_t* x16, float* dw, float* db,
+                             int64_t B, int64_t H, int64_t W, int64_t Cin, int64_t Cout, int kh, int kw, int stride, int pad,
+                             const float* a_range, int a_bits, void* ws, size_t ws_bytes, void* stream) {
+    QB_CHECK_ARG(g_hi && g_f32 && x16 && dw && a_range && ws, "qb_conv_wgrad: null pointer");
+    QB_CHECK_ARG(B > 0 && H > 0 && W > 0 && Cin > 0 && Cout > 0 && kh > 0 && kw > 0 && stride > 0 && pad >= 0, "qb_conv_wgrad: bad shape");
+    WgradGeom g;
+    if (!wgrad_geom(g, B, H, W, Cin, Cout, kh, kw, stride, pad, g_lo ? 2 : 1) ||
+        ((reinterpret_cast<uintptr_t>(g_hi) | reinterpret_cast<uintptr_t>(g_lo) | reinterpret_cast<uintptr_t>(x16) |
+          reinterpret_cast<uintptr_t>(ws)) & 15) != 0) {
+        qb_set_error("qb_conv_wgrad: unsupported geometry (need Cin%%16==0, Cout%%8==0, kh*kw<=9, stride<=2, 16-byte aligned "
+                     "tensors): Cin=%lld Cout=%lld k=%dx%d stride=%d", (long long)Cin, (long long)Cout, kh, kw, stride);
+        return QB_ERR_UNSUPPORTED;
+    }
+    QB_CHECK_ARG(B * H * W < 2147483647LL, "qb_conv_wgrad: pixel count exceeds int32");
+    const size_t need = qb_conv_wgrad_ws_bytes(B, H, W, Cin, Cout, kh, kw, stride, pad);
+    if (ws_bytes < need) {
+        qb_set_error("qb_conv_wgrad: workspace %zu < %zu bytes", ws_bytes, need);
+        return QB_ERR_WORKSPACE;
+    }
+    float* partial = static_cast<float*>(ws);
+    float* cpart = partial + (size_t)g.slices * g.mrows * Cout;
+    cudaStream_t st = qb_stream(stream);
+    CUtensorMap tx, tg0, tg1;
+    {
+        const uint64_t dims[4] = {(uint64_t)Cin, (uint64_t)W, (uint64_t)H, (uint64_t)B};
+        const uint64_t str[3] = {(uint64_t)Cin * 2, (uint64_t)W * Cin * 2, (uint64_t)H * W * Cin * 2};
+        const uint32_t box[4] = {(uint32_t)g.RC, (uint32_t)(g.TW * stride), (uint32_t)(g.TH * stride), (uint32_t)g.TN};
+        const uint32_t es[4] = {1, (uint32_t)stride, (uint32_t)stride, 1};
+        int rc = qb_make_tmap(&tx, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, x16, dims, str, box, es, g.RC * 2);
+        if (rc) return rc;
+    }
+    {
+        const uint64_t dims[4] = {(uint64_t)Cout, (uint64_t)g.Wo, (uint64_t)g.Ho, (uint64_t)B};
+        const uint64_t str[3] = {(uint64_t)Cout * 2, (uint64_t)g.Wo * Cout * 2, (uint64_t)g.Ho * g.Wo * Cout * 2};
+        const uint32_t box[4] = {(uint32_t)g.RN, (uint32_t)g.TW, (uint32_t)g.TH, (uint32_t)g.TN};
+        int rc = qb_make_tmap(&tg0, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, g_hi, dims, str, box, nullptr, g.RN * 2);
+        if (rc) return rc;
+        rc = qb_make_tmap(&tg1, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, g_lo ? g_lo : g_hi, dims, str, box, nullptr, g.RN * 2);
+        if (rc) return rc;
+    }
+    const size_t smem = 1024 + (size_t)g.a_stages * 128 * g.P * 2 + (size_t)g.b_stages * g.g_planes * g.BN * g.P * 2 + 512;
+    QB_CUDA(cudaFuncSetAttribute(k_conv_wgrad, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    const unsigned grid = (unsigned)(g.slices * g.mgroups * g.nblocks);
+    k_conv_wgrad<<<grid, WG_THREADS, smem, st>>>(tx, tg0, tg1, partial, g);
+    QB_LAUNCH_CHECK();
+    k_wgrad_colsums<<<CS_BLOCKS, 256, 0, st>>>(g_f32, cpart, (int)B, g.Ho, g.Wo, (int)Cout, (int)H, (int)W, kh, kw, stride, pad, a_range,
+                                              a_bits, db != nullptr);
+    QB_LAUNCH_CHECK();
+    const int64_t outs = (int64_t)g.mrows * Cout;
+    k_wgrad_reduce<<<(unsigned)((outs + 255) / 256), 256, 0, st>>>(partial, g.slices, cpart, CS_BLOCKS, dw, db, (int)Cout, (int)Cin,
+                                                                 kh * kw, a_range, a_bits);
+    QB_LAUNCH_CHECK();
+    return QB_OK;
+}
