@@ -72,6 +72,9 @@ int qb_measure_finalize(const double* stats, float* running_min, float* running_
  *   y          may alias x (in place) or be NULL when only codes are wanted                      */
 int qb_fakequant_affine(const float* x, float* y, uint8_t* codes, int64_t n, int bits, const float* range_dev,
                         double lo, double hi, int scale_mode, void* stream);
+/* Same, plus codes16 (optional): the integer codes as bf16 (exact for bits <= 8), the x operand of qb_conv_wgrad. */
+int qb_fakequant_affine16(const float* x, float* y, uint8_t* codes, uint16_t* codes16, int64_t n, int bits,
+                          const float* range_dev, double lo, double hi, int scale_mode, void* stream);
 
 /* Self-test hook (no reference counterpart): the quantizers divide by the scale with an FMA sequence that must equal
  * IEEE division (ATen's div_, quantize.py:90,92); this evaluates that sequence and __fdiv_rn on the same operands

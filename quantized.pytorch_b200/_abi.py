@@ -30,6 +30,7 @@ PROTOTYPES = {
     "qb_relu_bwd_minmax": (_i32, [_p, _p, _p, _i64, _p, _p, _sz, _p]),
     "qb_measure_finalize": (_i32, [_p, _p, _p, _p, _p, _p, _dbl, _i32, _i32, _i32, _p, _p]),
     "qb_fakequant_affine": (_i32, [_p, _p, _p, _i64, _i32, _p, _dbl, _dbl, _i32, _p]),
+    "qb_fakequant_affine16": (_i32, [_p, _p, _p, _p, _i64, _i32, _p, _dbl, _dbl, _i32, _p]),
     "qb_selftest_div": (_i32, [_p, _flt, _p, _p, _i64, _p]),
     "qb_fakequant_rows": (_i32, [_p, _p, _p, _i64, _i64, _i32, _p, _p, _i32, _p]),
     "qb_minmax_ws_bytes": (_sz, []),
@@ -282,11 +283,16 @@ def measure_finalize(stats, running, momentum, training, method, bits, range_out
 
 
 def fakequant_affine(x, bits, range_dev=None, lo=0.0, hi=0.0, scale_mode=QB_SCALE_DOUBLE, out=None, codes=None,
-                     want_y=True):
+                     want_y=True, codes16=None):
     lib = load()
     x = _f32c(x, "x")
     if want_y and out is None:
         out = torch.empty_like(x)
+    if codes16 is not None:
+        nb = 4 + (4 if want_y else 0) + (1 if codes is not None else 0) + 2
+        _run("qb_fakequant_affine16", nb * x.numel(), _ptr(x), _ptr(out) if want_y else None, _ptr(codes), _ptr(codes16), x.numel(),
+             int(bits), _ptr(range_dev), float(lo), float(hi), int(scale_mode), _stream())
+        return out
     _run("qb_fakequant_affine", (4 + (4 if want_y else 0) + (1 if codes is not None else 0)) * x.numel(), _ptr(x), _ptr(out) if want_y else None, _ptr(codes), x.numel(), int(bits),
                                    _ptr(range_dev), float(lo), float(hi), int(scale_mode), _stream())
     return out

@@ -135,7 +135,7 @@ k_conv_i8(const __grid_constant__ CUtensorMap tmap_x, const __grid_constant__ CU
 
     const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
     const int taps = g.kh * g.kw;
-    const int cblocks = g.Cin / g.BK;
+    const int cblocks = (g.Cin + g.BK - 1) / g.BK;                // Cin % BK != 0 (Cin = 16): TMA zero-fills the rest of the row
     const int num_kb = taps * cblocks;
     const int tiles_m = g.tiles_w * g.tiles_h * g.tiles_b;
     const int tiles_n = (g.Cout + BN - 1) / BN;
@@ -168,7 +168,7 @@ k_conv_i8(const __grid_constant__ CUtensorMap tmap_x, const __grid_constant__ CU
         const bool lead = elect_one();
         if (lead && g.halo) {
             mbar_arrive_expect_tx(wfull_bar, wres_bytes);
-            for (int tap = 0; tap < taps; ++tap) tma_load_2d(wres + (size_t)tap * b_bytes, &tmap_w, wfull_bar, tap * g.Cin, 0);
+            for (int tap = 0; tap < taps; ++tap) tma_load_3d(wres + (size_t)tap * b_bytes, &tmap_w, wfull_bar, 0, tap, 0);
             uint32_t it = 0;
             for (int t = blockIdx.x; t < total_tiles; t += gridDim.x, ++it) {
                 int tn, b0, ho0, wo0;                           // tiles_n == 1 in halo mode: tn == 0
@@ -198,7 +198,7 @@ k_conv_i8(const __grid_constant__ CUtensorMap tmap_x, const __grid_constant__ CU
                             uint8_t* sa = smem + (size_t)s * stage_bytes;
                             tma_load_4d(sa, &tmap_x, &full_bar[s], cb * g.BK, wo0 * g.stride - g.pad + s_,
                                         ho0 * g.stride - g.pad + r, b0);
-                            tma_load_2d(sa + a_bytes, &tmap_w, &full_bar[s], tap * g.Cin + cb * g.BK, n0);
+                            tma_load_3d(sa + a_bytes, &tmap_w, &full_bar[s], cb * g.BK, tap, n0);
                         }
                     }
                 }
@@ -632,9 +632,9 @@ extern "C" int qb_conv_i8_fwd(const uint8_t* x_codes, const uint8_t* w_codes_khw
     QB_CHECK_ARG(B > 0 && H > 0 && W > 0 && Cin > 0 && Cout > 0 && kh > 0 && kw > 0 && stride > 0 && pad >= 0,
                  "qb_conv_i8_fwd: bad shape");
     const int64_t Ho = (H + 2 * pad - kh) / stride + 1, Wo = (W + 2 * pad - kw) / stride + 1;
-    if (Cin % 32 != 0 || kh * kw > CV_MAX_TAPS || stride > 2 || Ho < 1 || Wo < 1 || Cout % 16 != 0 ||
+    if (Cin % 16 != 0 || kh * kw > CV_MAX_TAPS || stride > 2 || Ho < 1 || Wo < 1 || Cout % 16 != 0 ||
         ((reinterpret_cast<uintptr_t>(x_codes) | reinterpret_cast<uintptr_t>(w_codes_khwc) | reinterpret_cast<uintptr_t>(out)) & 15) != 0) {
-        qb_set_error("qb_conv_i8_fwd: unsupported geometry (need Cin%%32==0, Cout%%16==0, kh*kw<=9, stride<=2, 16-byte "
+        qb_set_error("qb_conv_i8_fwd: unsupported geometry (need Cin%%16==0, Cout%%16==0, kh*kw<=9, stride<=2, 16-byte "
                      "aligned tensors): Cin=%lld Cout=%lld k=%dx%d stride=%d", (long long)Cin, (long long)Cout, kh, kw, stride);
         return QB_ERR_UNSUPPORTED;
     }
@@ -689,11 +689,11 @@ extern "C" int qb_conv_i8_fwd(const uint8_t* x_codes, const uint8_t* w_codes_khw
         int rc = qb_make_tmap(&tx, CU_TENSOR_MAP_DATA_TYPE_UINT8, 4, x_codes, dims, str, box, es, g.BK);
         if (rc) return rc;
     }
-    {   // weights: [Cout][K = kh*kw*Cin]
-        const uint64_t K = (uint64_t)kh * kw * Cin;
-        const uint64_t dims[2] = {K, (uint64_t)Cout}, str[1] = {K};
-        const uint32_t box[2] = {(uint32_t)g.BK, (uint32_t)BN};
-        int rc = qb_make_tmap(&tw, CU_TENSOR_MAP_DATA_TYPE_UINT8, 2, w_codes_khwc, dims, str, box, nullptr, g.BK);
+    {   // weights: [Cout][tap][Cin] (a box row = BK channels of ONE tap; zero fill beyond Cin)
+        const uint64_t dims[3] = {(uint64_t)Cin, (uint64_t)(kh * kw), (uint64_t)Cout};
+        const uint64_t str[2] = {(uint64_t)Cin, (uint64_t)kh * kw * Cin};
+        const uint32_t box[3] = {(uint32_t)g.BK, 1u, (uint32_t)BN};
+        int rc = qb_make_tmap(&tw, CU_TENSOR_MAP_DATA_TYPE_UINT8, 3, w_codes_khwc, dims, str, box, nullptr, g.BK);
         if (rc) return rc;
     }
     {   // output fp32 NHWC: dims {Cout, Wo, Ho, B}; one staged slab = 32 channels x the tile's pixels

@@ -30,9 +30,9 @@ __device__ __forceinline__ QParams load_qparams(const RangeArg& r, int bits, int
 // ------------------------------------------------------------------------------------------------
 // min-anchored affine (A1): thread = one 32-byte octet per step, FQ_U octets in flight
 // ------------------------------------------------------------------------------------------------
-template <bool WRITE_Y, bool WRITE_C, bool SMALL>
+template <bool WRITE_Y, bool WRITE_C, bool SMALL, bool WRITE_H = false>
 __device__ __forceinline__ void affine_octet(const F8& v, float* y, uint8_t* codes, int64_t oct, const QParams& p,
-                                             const Divisor& d) {
+                                             const Divisor& d, uint16_t* codes16 = nullptr) {
     float a[8];
     bool ok = d.fast;
 #pragma unroll
@@ -71,11 +71,22 @@ __device__ __forceinline__ void affine_octet(const F8& v, float* y, uint8_t* cod
         pk.y = __byte_perm(__byte_perm(c[4], c[5], 0x0040), __byte_perm(c[6], c[7], 0x0040), 0x5410);
         reinterpret_cast<uint2*>(codes)[oct] = pk;
     }
+    if (WRITE_H) {   // the codes as bf16 (exact for bits <= 8): the upper half of (float)code
+        uint32_t f[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) f[j] = __float_as_uint(SMALL ? __fsub_rn(__uint_as_float(c[j]), QB_MAGIC) : (float)c[j]);
+        uint4 o;
+        o.x = __byte_perm(f[0], f[1], 0x7632);
+        o.y = __byte_perm(f[2], f[3], 0x7632);
+        o.z = __byte_perm(f[4], f[5], 0x7632);
+        o.w = __byte_perm(f[6], f[7], 0x7632);
+        reinterpret_cast<uint4*>(codes16)[oct] = o;
+    }
 }
 
-template <bool WRITE_Y, bool WRITE_C, bool SMALL>
+template <bool WRITE_Y, bool WRITE_C, bool SMALL, bool WRITE_H = false>
 __device__ __forceinline__ void affine_sweep(const float* __restrict__ x, float* y, uint8_t* codes, int64_t n,
-                                             const QParams& p, const Divisor& d) {
+                                             const QParams& p, const Divisor& d, uint16_t* codes16 = nullptr) {
     const int64_t noct = n >> 3;
     const int64_t stride = (int64_t)gridDim.x * FQ_THREADS;
     int64_t i = (int64_t)blockIdx.x * FQ_THREADS + threadIdx.x;
@@ -84,37 +95,41 @@ __device__ __forceinline__ void affine_sweep(const float* __restrict__ x, float*
 #pragma unroll
         for (int u = 0; u < FQ_U; ++u) v[u] = ld256_stream(x + 8 * (i + u * stride));
 #pragma unroll
-        for (int u = 0; u < FQ_U; ++u) affine_octet<WRITE_Y, WRITE_C, SMALL>(v[u], y, codes, i + u * stride, p, d);
+        for (int u = 0; u < FQ_U; ++u) affine_octet<WRITE_Y, WRITE_C, SMALL, WRITE_H>(v[u], y, codes, i + u * stride, p, d, codes16);
     }
-    for (; i < noct; i += stride) affine_octet<WRITE_Y, WRITE_C, SMALL>(ld256_stream(x + 8 * i), y, codes, i, p, d);
+    for (; i < noct; i += stride) affine_octet<WRITE_Y, WRITE_C, SMALL, WRITE_H>(ld256_stream(x + 8 * i), y, codes, i, p, d, codes16);
     // n % 8 tail
     if (blockIdx.x == 0 && threadIdx.x < (n & 7)) {
         const int64_t e = (noct << 3) + threadIdx.x;
         const float q = q_affine_code(x[e], p, d);
         if (WRITE_Y) y[e] = q_affine_deq(q, p);
         if (WRITE_C) codes[e] = (uint8_t)q;
+        if (WRITE_H) codes16[e] = (uint16_t)(__float_as_uint(q) >> 16);
     }
 }
 
-template <bool WRITE_Y, bool WRITE_C>
+template <bool WRITE_Y, bool WRITE_C, bool WRITE_H = false>
 __global__ void __launch_bounds__(FQ_THREADS, 4)
-k_fq_affine_v8(const float* __restrict__ x, float* y, uint8_t* codes, int64_t n, int bits, RangeArg r, int mode) {
+k_fq_affine_v8(const float* __restrict__ x, float* y, uint8_t* codes, int64_t n, int bits, RangeArg r, int mode,
+               uint16_t* codes16 = nullptr) {
     const QParams p = load_qparams(r, bits, mode);
     const Divisor d = make_divisor(p.scale);
     if (p.qmax < 4194304.0f)
-        affine_sweep<WRITE_Y, WRITE_C, true>(x, y, codes, n, p, d);
+        affine_sweep<WRITE_Y, WRITE_C, true, WRITE_H>(x, y, codes, n, p, d, codes16);
     else
-        affine_sweep<WRITE_Y, WRITE_C, false>(x, y, codes, n, p, d);
+        affine_sweep<WRITE_Y, WRITE_C, false, WRITE_H>(x, y, codes, n, p, d, codes16);
 }
 
 // scalar path for pointers that are not 32-byte aligned (views into larger tensors)
 __global__ void __launch_bounds__(FQ_THREADS)
-k_fq_affine_scalar(const float* __restrict__ x, float* y, uint8_t* codes, int64_t n, int bits, RangeArg r, int mode) {
+k_fq_affine_scalar(const float* __restrict__ x, float* y, uint8_t* codes, int64_t n, int bits, RangeArg r, int mode,
+                   uint16_t* codes16 = nullptr) {
     const QParams p = load_qparams(r, bits, mode);
     for (int64_t e = (int64_t)blockIdx.x * FQ_THREADS + threadIdx.x; e < n; e += (int64_t)gridDim.x * FQ_THREADS) {
         float q = q_affine_code(x[e], p);
         if (y) y[e] = q_affine_deq(q, p);
         if (codes) codes[e] = (uint8_t)q;
+        if (codes16) codes16[e] = (uint16_t)(__float_as_uint(q) >> 16);
     }
 }
 
@@ -151,6 +166,31 @@ extern "C" int qb_fakequant_affine(const float* x, float* y, uint8_t* codes, int
             k_fq_affine_v8<false, true><<<grid, FQ_THREADS, 0, st>>>(x, y, codes, n, bits, r, scale_mode);
     } else {
         k_fq_affine_scalar<<<fq_grid(n, 8), FQ_THREADS, 0, st>>>(x, y, codes, n, bits, r, scale_mode);
+    }
+    QB_LAUNCH_CHECK();
+    return QB_OK;
+}
+
+/* As qb_fakequant_affine, plus codes16: the integer codes as bf16 (bits <= 8; exact) - the x operand of qb_conv_wgrad. */
+extern "C" int qb_fakequant_affine16(const float* x, float* y, uint8_t* codes, uint16_t* codes16, int64_t n, int bits,
+                                     const float* range_dev, double lo, double hi, int scale_mode, void* stream) {
+    if (!codes16) return qb_fakequant_affine(x, y, codes, n, bits, range_dev, lo, hi, scale_mode, stream);
+    QB_CHECK_ARG(n >= 0, "qb_fakequant_affine16: n=%lld", (long long)n);
+    if (n == 0) return QB_OK;
+    QB_CHECK_ARG(x, "qb_fakequant_affine16: null x");
+    QB_CHECK_ARG(bits >= 1 && bits <= 8, "qb_fakequant_affine16: bf16 codes need bits<=8 (bits=%d)", bits);
+    QB_CHECK_ARG(scale_mode == QB_SCALE_DOUBLE || scale_mode == QB_SCALE_FLOAT, "qb_fakequant_affine16: scale_mode=%d", scale_mode);
+    RangeArg r{range_dev, lo, hi};
+    cudaStream_t st = qb_stream(stream);
+    const bool vec = aligned(x, 32) && (!y || aligned(y, 32)) && (!codes || aligned(codes, 8)) && aligned(codes16, 16);
+    if (vec) {
+        int grid = fq_grid(n >> 3, 4);
+        if (y && codes) k_fq_affine_v8<true, true, true><<<grid, FQ_THREADS, 0, st>>>(x, y, codes, n, bits, r, scale_mode, codes16);
+        else if (y) k_fq_affine_v8<true, false, true><<<grid, FQ_THREADS, 0, st>>>(x, y, codes, n, bits, r, scale_mode, codes16);
+        else if (codes) k_fq_affine_v8<false, true, true><<<grid, FQ_THREADS, 0, st>>>(x, y, codes, n, bits, r, scale_mode, codes16);
+        else k_fq_affine_v8<false, false, true><<<grid, FQ_THREADS, 0, st>>>(x, y, codes, n, bits, r, scale_mode, codes16);
+    } else {
+        k_fq_affine_scalar<<<fq_grid(n, 8), FQ_THREADS, 0, st>>>(x, y, codes, n, bits, r, scale_mode, codes16);
     }
     QB_LAUNCH_CHECK();
     return QB_OK;

@@ -152,6 +152,27 @@ def _quantize_gradient(g, bits, stochastic=True):
                                step_dev=noise_step(g.device))
 
 
+def _pack_gradient(g, bits, want_codes, want_split, pad_cols=0):
+    """UniformQuantizeGrad.backward's quantizer (quantize.py:124-139) feeding the native backward contractions: one pass
+    over g -> (range, g (padded), bf16 codes (q - zp) | None, bf16 hi | None, bf16 lo | None).  ``pad_cols`` zero columns
+    are appended to a 2-D g first (linear layers whose width is not a multiple of 8); the range is that of the unpadded
+    tensor and a padded zero keeps code zp, i.e. contributes nothing."""
+    g = _abi._f32c(g, "grad")
+    r = _take_grad_range(g)
+    if r is None:
+        r = _abi.minmax(g)
+    if _reducer is not None:
+        _reducer.grad_range(r)
+    noise = _grad_noise(g, True) if want_codes else None
+    if pad_cols:
+        g = F.pad(g, (0, pad_cols))
+        if noise is not None:
+            noise = F.pad(noise.reshape(g.shape[0], -1), (0, pad_cols))
+    gq, hi, lo = _abi.bwd_pack(g, r, bits, noise=noise, stochastic=True, seed=_next_seed() if want_codes else 0,
+                               step_dev=noise_step(g.device), want_codes=want_codes, want_split=want_split)
+    return r, g, gq, hi, lo
+
+
 # ---------------------------------------------------------------------------------------------------
 # UniformQuantize / UniformQuantizeGrad / quantize / quantize_grad         (quantize.py:39-164)
 # ---------------------------------------------------------------------------------------------------
@@ -535,6 +556,10 @@ class _QBase(QuantNode):
 # Route QConv2d / QLinear through the int8 tcgen05 kernels whenever the geometry is supported (conv_i8.cu,
 # gemm_i8.cu); otherwise the contraction of the already fake-quantized tensors goes to cuDNN / cuBLAS.
 USE_INT8_TENSOR_CORES = True
+USE_NATIVE_BACKWARD = True    # dX / dW / db of the dense contractions on conv_bwd.cu (tcgen05 bf16) instead of cuDNN / cuBLAS
+# The reference's F.conv2d / F.linear on the fake-quantized tensors (cuDNN / cuBLAS) is NOT a product path: a geometry the
+# native kernels do not take raises QB200Error unless a test sets this flag to compare against the library.
+ALLOW_LIBRARY_FALLBACK = False
 USE_STEM_KERNEL = True
 USE_DW_KERNEL = True       # depthwise 3x3 convs on the codes (conv_dw.cu); False: F.conv2d on the fake-quantized tensors
 
@@ -561,7 +586,7 @@ def _conv_i8_supported(mod, x):
             and mod.num_bits <= 8 and mod.num_bits_weight <= 8
             and (x.shape[2] + 2 * pd[0] - kh) // st[0] + 1 >= 1 and (x.shape[3] + 2 * pd[1] - kw) // st[1] + 1 >= 1):
         return False
-    if kh * kw <= 9 and mod.in_channels % 32 == 0 and mod.out_channels % 16 == 0:
+    if kh * kw <= 9 and mod.in_channels % 16 == 0 and mod.out_channels % 16 == 0:
         return True
     return _conv_stem_supported(mod, x)
 
@@ -569,7 +594,7 @@ def _conv_i8_supported(mod, x):
 def _conv_stem_supported(mod, x):
     """First-layer geometry (3 input channels): tcgen05 over a thread-built im2col operand (conv_stem.cu)."""
     kh, kw = mod.kernel_size
-    return (USE_STEM_KERNEL and mod.in_channels % 32 != 0
+    return (USE_STEM_KERNEL and mod.in_channels % 16 != 0
             and _abi.conv_stem_supported(x.shape[2], x.shape[3], mod.in_channels, mod.out_channels, kh, kw,
                                          _pair(mod.stride)[0], _pair(mod.padding)[0]))
 
@@ -579,10 +604,23 @@ def _linear_i8_supported(mod, x):
             and mod.num_bits_weight <= 8)
 
 
+def _native_bwd_supported(mod, x):
+    """Geometry of the dense backward kernels (conv_bwd.cu): groups 1, C_in % 16 == 0, at most 9 taps, stride 1 or 2."""
+    if not USE_NATIVE_BACKWARD or mod.num_bits > 8:
+        return False
+    if isinstance(mod, nn.Conv2d):
+        kh, kw = mod.kernel_size
+        return (mod.groups == 1 and mod.in_channels % 16 == 0 and mod.out_channels % 8 == 0
+                and _abi.conv_bwd_supported(mod.in_channels, mod.out_channels, kh, kw, _pair(mod.stride)[0], _pair(mod.padding)[0]))
+    return mod.in_features % 16 == 0
+
+
 class _QTensorCoreFn(Function):
-    """QConv2d / QLinear forward on the integer codes: activation fake-quant (codes + fp32 copy for the backward),
-    per-channel weight fake-quant (centred codes), int8 tcgen05 implicit GEMM with the dequantising epilogue.
-    Backward is the same as _QContraction's (straight-through for both quantizers, quantize.py:105-109)."""
+    """QConv2d / QLinear on the integer codes.  Forward: activation fake-quant (uint8 codes for the int8 tensor cores, the
+    same codes as bf16 for the weight gradient), per-channel weight fake-quant (centred int8 codes; bf16 hi / lo planes
+    of w_hat for the input gradient), int8 tcgen05 implicit GEMM with the dequantising epilogue.  Backward
+    (quantize.py:142-156, 342-346; straight-through for both quantizers, :105-109): one pass packs the output gradient
+    (quantizer -> bf16 codes, raw g -> bf16 hi / lo), then qb_conv_dgrad / qb_conv_wgrad (conv_bwd.cu)."""
 
     @staticmethod
     def forward(ctx, input, weight, qbias, mod, rng):
@@ -595,7 +633,15 @@ class _QTensorCoreFn(Function):
         # first layer whose input needs no gradient: the weight gradient is taken from the codes (conv_stem.cu)
         stem_bwd = (conv and USE_STEM_KERNEL and x.shape[1] % 32 != 0 and not ctx.needs_input_grad[0]
                     and mod.out_channels in (32, 64) and mod.kernel_size[0] == 7)
-        xq = _abi.fakequant_affine(x, bits_a, range_dev=rng, codes=codes, want_y=need_bwd and not stem_bwd)
+        dense = not conv or (mod.groups == 1 and x.shape[1] % 16 == 0)
+        native_bwd = need_bwd and dense and _native_bwd_supported(mod, x)
+        if need_bwd and dense and not native_bwd and not stem_bwd and not ALLOW_LIBRARY_FALLBACK:
+            raise QB200Error("no native backward kernel for this geometry (%r); set quantize.ALLOW_LIBRARY_FALLBACK to "
+                             "route it to cuDNN / cuBLAS for a comparison" % (mod,))
+        want_x16 = native_bwd and ctx.needs_input_grad[1]
+        x16 = torch.empty_like(x, dtype=torch.bfloat16) if want_x16 else None
+        xq = _abi.fakequant_affine(x, bits_a, range_dev=rng, codes=codes, codes16=x16,
+                                   want_y=need_bwd and not stem_bwd and not native_bwd)
         w4 = weight if conv else weight.view(weight.shape[0], weight.shape[1], 1, 1)
         wq, wcodes, tapsum = _abi.fakequant_rows_conv(w4, bits_w, mod.weight_min, mod.weight_max, compute_range=update,
                                                       want_y=need_bwd)
@@ -608,7 +654,7 @@ class _QTensorCoreFn(Function):
                                        rng, bits_a, mod.weight_min, mod.weight_max, bits_w, bias=qbias, out_stats=stats)
                 if stats is not None:
                     _stash_fwd_stats(out, stats)
-            elif Cin % 32 != 0:                                             # first layer: thread-built im2col operand
+            elif Cin % 16 != 0:                                             # first layer: thread-built im2col operand
                 out = _abi.conv_stem_fwd(codes, wcodes, B, H, W, Cin, mod.out_channels, kh, kw, _pair(mod.stride)[0],
                                          _pair(mod.padding)[0], rng, bits_a, mod.weight_min, mod.weight_max, bits_w, tapsum,
                                          bias=qbias)
@@ -630,10 +676,19 @@ class _QTensorCoreFn(Function):
             wq = wq.view(N, K) if wq is not None else None
             ctx.conv = None
         ctx.bits_grad, ctx.grad_mode, ctx.has_bias = mod.num_bits_grad, mod._grad_mode(), qbias is not None
-        ctx.stem = None
+        ctx.grad_quantizer = getattr(mod, "_grad_quantizer", None)
+        ctx.stem = ctx.native = None
         if need_bwd and stem_bwd:
             ctx.stem = (bits_a, mod.out_channels, kh, kw, _pair(mod.stride)[0], _pair(mod.padding)[0])
             ctx.save_for_backward(codes, rng)
+        elif native_bwd:
+            n_out = wq.shape[0]
+            pad = (-n_out) % 8                                              # linear layers: width padded to 16-byte rows
+            wt = None
+            if ctx.needs_input_grad[0]:
+                wt = _abi.wt_pack(F.pad(wq, (0, 0) * (wq.dim() - 1) + (0, pad)) if pad else wq)
+            ctx.native = (bits_a, tuple(x.shape), tuple(w4.shape), pad)
+            ctx.save_for_backward(x16, rng, wt)
         elif need_bwd:
             ctx.save_for_backward(xq, wq)
         return out
@@ -649,8 +704,70 @@ class _QTensorCoreFn(Function):
             dw = _abi.conv_stem_wgrad(g, codes, rng, *ctx.stem) if ctx.needs_input_grad[1] else None
             db = g.sum((0, 2, 3)) if ctx.has_bias and ctx.needs_input_grad[2] else None
             return None, dw, db, None, None
+        if ctx.native is not None:
+            return _native_backward(ctx, g) + (None, None)
         x, w = ctx.saved_tensors
         return _contraction_backward(ctx, g, x, w) + (None, None)
+
+
+def _native_backward(ctx, g):
+    """dX, dW, db of the dense contraction on conv_bwd.cu, for the three gradient modes of _QContraction."""
+    x16, a_rng, wt = ctx.saved_tensors
+    bits_a, x_shape, w_shape, pad = ctx.native
+    need_x, need_w, need_b = ctx.needs_input_grad[0], ctx.needs_input_grad[1], ctx.has_bias and ctx.needs_input_grad[2]
+    conv = ctx.conv is not None
+    n_out, c_in, kh, kw = w_shape
+    stride, padding = (ctx.conv[0][0], ctx.conv[1][0]) if conv else (1, 0)
+    g = _abi._f32c(g, "grad")
+    if conv:
+        g = g.contiguous(memory_format=torch.channels_last)
+    elif not g.is_contiguous():
+        g = g.contiguous()
+    mode, bits = ctx.grad_mode, ctx.bits_grad
+    scale_range = None
+    a0 = a1 = None                      # planes of the input-gradient branch
+    if mode == "biprec" and ctx.grad_quantizer is None and bits <= 8:
+        scale_range, g, a0, hi, lo = _pack_gradient(g, bits, need_x, need_w or need_b, pad_cols=pad)
+        g_param = g
+    else:
+        if mode == "full":
+            g_in = g_param = g
+        else:
+            gq = ctx.grad_quantizer(g) if ctx.grad_quantizer is not None else _quantize_gradient(g, bits)
+            g_in, g_param = gq, (gq if mode == "quant" else g)
+        same = g_in is g_param
+        if pad:
+            g_in = F.pad(g_in, (0, pad))
+            g_param = g_in if same else F.pad(g_param, (0, pad))
+        hi = lo = None
+        if need_w or need_b:
+            _, hi, lo = _abi.bwd_pack(g_param, want_codes=False)
+        if need_x:
+            if g_in is g_param and hi is not None:
+                a0, a1 = hi, lo
+            else:
+                _, a0, a1 = _abi.bwd_pack(g_in, want_codes=False)
+    shape4 = x_shape if conv else (x_shape[0], x_shape[1], 1, 1)
+    dx = dw = db = None
+    if need_x:
+        a0v = a0 if conv else a0.view(a0.shape[0], a0.shape[1], 1, 1)
+        a1v = a1 if (a1 is None or conv) else a1.view(a1.shape[0], a1.shape[1], 1, 1)
+        dx = _abi.conv_dgrad(a0v, a1v, wt, shape4, n_out + pad, kh, kw, stride, padding, scale_range=scale_range,
+                             scale_bits=bits if scale_range is not None else 8)
+        if not conv:
+            dx = dx.permute(0, 2, 3, 1).reshape(x_shape)
+    if need_b and not need_w:             # frozen weight, trainable bias: a plain column sum
+        db = g_param.sum((0, 2, 3) if conv else 0)[:n_out]
+    elif need_w:
+        v4 = (lambda t: t) if conv else (lambda t: t.view(t.shape[0], t.shape[1], 1, 1))
+        dw, db = _abi.conv_wgrad(v4(hi), v4(lo), g_param, v4(x16), n_out + pad, kh, kw, stride, padding, a_rng, bits_a,
+                                 want_bias=bool(need_b))
+        if pad:
+            dw = dw[:n_out]
+            db = db[:n_out] if db is not None else None
+        if not conv:
+            dw = dw.reshape(n_out, c_in)
+    return dx, dw, db
 
 
 class QConv2d(nn.Conv2d, _QBase):
