@@ -381,6 +381,9 @@ int qb_wt_pack(const float* w_hat, uint16_t* wt, int64_t Cout, int64_t Cin, int 
 int qb_conv_dgrad(const uint16_t* a0, const uint16_t* a1, const uint16_t* wt, float* dx, int64_t B, int64_t H, int64_t W,
                   int64_t Cin, int64_t Cout, int kh, int kw, int stride, int pad, const float* scale_range, int scale_bits,
                   float scale_mul, void* stream);
+/* Hardware probe used by tools/umma_shift_probe.py (UMMA descriptors that start inside an 8-row swizzle atom); not on any
+ * product path. */
+int qb_debug_umma_shift(const uint16_t* a, const uint16_t* b, float* out, int mn, int r0, int use_boff, void* stream);
 size_t qb_conv_wgrad_ws_bytes(int64_t B, int64_t H, int64_t W, int64_t Cin, int64_t Cout, int kh, int kw, int stride, int pad);
 int qb_conv_wgrad(const uint16_t* g_hi, const uint16_t* g_lo, const float* g_f32, const uint16_t* x16, float* dw, float* db,
                   int64_t B, int64_t H, int64_t W, int64_t Cin, int64_t Cout, int kh, int kw, int stride, int pad,

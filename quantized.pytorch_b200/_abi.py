@@ -81,6 +81,7 @@ PROTOTYPES = {
     "qb_conv_dw_fwd": (_i32, [_p, _p, _p, _i64, _i64, _i64, _i64, _i32, _i32, _i32, _i32, _p, _i32, _p, _p, _i32, _p, _p, _p,
                               _sz, _p]),
     "qb_bwd_pack": (_i32, [_p, _i64, _p, _p, _p, _i32, _p, _p, _i32, _u64, _u64, _p, _p]),
+    "qb_debug_umma_shift": (_i32, [_p, _p, _p, _i32, _i32, _i32, _p]),
     "qb_wt_pack": (_i32, [_p, _p, _i64, _i64, _i32, _p]),
     "qb_conv_dgrad": (_i32, [_p, _p, _p, _p, _i64, _i64, _i64, _i64, _i64, _i32, _i32, _i32, _i32, _p, _i32, _flt, _p]),
     "qb_conv_wgrad_ws_bytes": (_sz, [_i64, _i64, _i64, _i64, _i64, _i32, _i32, _i32, _i32]),

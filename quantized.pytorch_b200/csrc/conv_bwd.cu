@@ -914,3 +914,99 @@ extern "C" int qb_conv_wgrad(const uint16_t* g_hi, const uint16_t* g_lo, const f
     QB_LAUNCH_CHECK();
     return QB_OK;
 }
+
+// ------------------------------------------------------------------------------------------------
+// Hardware probe (tools/umma_shift_probe.py): may a UMMA shared-memory descriptor START at a row that is not a multiple of
+// the 8-row swizzle atom?  mn = 0: K-major A (rows = M), D[128 x 64] = A[r0 .. r0+127][0..63] * B[64][64]^T;
+// mn = 1: both operands MN-major (rows = K), D[128 x 64] = SUM_{k<64} A[r0+k][0..127] * B[r0+k][0..63].
+// use_boff: put ((start >> 7) & 7) into the descriptor's base-offset field.
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(128, 1)
+k_umma_shift_probe(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_b, float* __restrict__ out,
+                   int mn, int r0, int use_boff) {
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+    uint8_t* sA = smem;                       // K-major: 144 rows x 128 B; MN-major: 2 boxes of [80][64 ch]
+    uint8_t* sB = smem + 32768;               // K-major: 64 rows x 128 B;  MN-major: [80][64 ch]
+    uint64_t* bar = reinterpret_cast<uint64_t*>(smem + 49152);
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bar + 2);
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    if (threadIdx.x == 0) {
+        mbar_init(&bar[0], 1);
+        mbar_init(&bar[1], 1);
+        fence_barrier_init();
+    }
+    if (warp == 0) tmem_alloc<64>(tmem_slot);
+    tc_fence_before_sync();
+    __syncthreads();
+    tc_fence_after_sync();
+    const uint32_t tmem = *tmem_slot;
+    if (threadIdx.x == 0) {
+        if (!mn) {
+            mbar_arrive_expect_tx(&bar[0], 144 * 128 + 64 * 128);
+            tma_load_2d(sA, &tmap_a, &bar[0], 0, 0);
+            tma_load_2d(sB, &tmap_b, &bar[0], 0, 0);
+        } else {
+            mbar_arrive_expect_tx(&bar[0], 3 * 80 * 128);
+            tma_load_2d(sA, &tmap_a, &bar[0], 0, 0);
+            tma_load_2d(sA + 80 * 128, &tmap_a, &bar[0], 64, 0);
+            tma_load_2d(sB, &tmap_b, &bar[0], 0, 0);
+        }
+        mbar_wait_trap(&bar[0], 0);
+        tc_fence_after_sync();
+        const uint32_t a = smem_u32(sA) + (uint32_t)r0 * 128u, b = smem_u32(sB) + (mn ? (uint32_t)r0 * 128u : 0u);
+        for (int k = 0; k < 4; ++k) {
+            uint64_t da, db;
+            if (!mn) {
+                da = desc_kmajor(a + k * 32, 128);
+                db = desc_kmajor(b + k * 32, 128);
+            } else {
+                da = desc_mnmajor(a + k * 16 * 128, 128, 80 * 128);
+                db = desc_mnmajor(b + k * 16 * 128, 128, 80 * 128);
+            }
+            if (use_boff) {
+                da |= (uint64_t)(((a + (mn ? k * 2048 : 0)) >> 7) & 7) << 49;
+                if (mn) db |= (uint64_t)(((b + k * 2048) >> 7) & 7) << 49;
+            }
+            umma_f16(tmem, da, db, idesc_bf16(128, 64, mn, mn), k > 0);
+        }
+        umma_commit(&bar[1]);
+    }
+    __syncthreads();
+    mbar_wait_trap(&bar[1], 0);
+    tc_fence_after_sync();
+    for (int c0 = 0; c0 < 64; c0 += 32) {
+        uint32_t r[32];
+        tmem_ld_32x32(tmem + (uint32_t)c0 + ((uint32_t)(warp * 32) << 16), r);
+        tmem_ld_wait();
+        for (int u = 0; u < 32; ++u) out[(warp * 32 + lane) * 64 + c0 + u] = __uint_as_float(r[u]);
+    }
+    tc_fence_before_sync();
+    __syncthreads();
+    if (warp == 0) tmem_dealloc<64>(tmem);
+}
+
+/* a: bf16 [144][64] (mn = 0) or [80][128] (mn = 1); b: bf16 [64][64] (mn = 0) or [80][64] (mn = 1); out fp32 [128][64]. */
+extern "C" int qb_debug_umma_shift(const uint16_t* a, const uint16_t* b, float* out, int mn, int r0, int use_boff, void* stream) {
+    QB_CHECK_ARG(a && b && out && r0 >= 0 && r0 <= 16, "qb_debug_umma_shift: bad argument");
+    CUtensorMap ta, tb;
+    if (!mn) {
+        const uint64_t da[2] = {64, 144}, sa[1] = {128}, db[2] = {64, 64};
+        const uint32_t ba[2] = {64, 144}, bb[2] = {64, 64};
+        int rc = qb_make_tmap(&ta, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, a, da, sa, ba, nullptr, 128);
+        if (rc) return rc;
+        rc = qb_make_tmap(&tb, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, b, db, sa, bb, nullptr, 128);
+        if (rc) return rc;
+    } else {
+        const uint64_t da[2] = {128, 80}, sa[1] = {256}, db[2] = {64, 80}, sb[1] = {128};
+        const uint32_t bx[2] = {64, 80};
+        int rc = qb_make_tmap(&ta, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, a, da, sa, bx, nullptr, 128);
+        if (rc) return rc;
+        rc = qb_make_tmap(&tb, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, b, db, sb, bx, nullptr, 128);
+        if (rc) return rc;
+    }
+    QB_CUDA(cudaFuncSetAttribute(k_umma_shift_probe, cudaFuncAttributeMaxDynamicSharedMemorySize, 51200));
+    k_umma_shift_probe<<<1, 128, 51200, qb_stream(stream)>>>(ta, tb, out, mn, r0, use_boff);
+    QB_LAUNCH_CHECK();
+    return QB_OK;
+}
