@@ -278,7 +278,9 @@ def measure_finalize(stats, running, momentum, training, method, bits, range_out
     if range_out is None:
         range_out = torch.empty(2, dtype=torch.float32, device=rmin.device)
     _run("qb_measure_finalize", 0, _ptr(stats), _ptr(rmin), _ptr(rmax), _ptr(nmeas), _ptr(rvar), _ptr(rmean),
-                                   -1.0 if momentum is None else float(momentum), int(training), int(method), int(bits),
+                                   # quantize.py:217 `momentum or self.momentum or n/(n+1)`: a falsy momentum (None, 0, 0.0)
+                                   # selects the cumulative average
+                                   -1.0 if not momentum else float(momentum), int(training), int(method), int(bits),
                                    _ptr(range_out), _stream())
     return range_out
 

@@ -40,6 +40,8 @@ __device__ __forceinline__ unsigned long long ld_acquire_sys(const unsigned long
     return v;
 }
 
+constexpr unsigned long long AR_TIMEOUT_NS = 120ull * 1000ull * 1000ull * 1000ull;
+
 struct ArPeers {
     unsigned char* buf[AR_MAX_WORLD];
 };
@@ -77,13 +79,27 @@ __global__ void __launch_bounds__(AR_THREADS) k_allreduce_oneshot(T* __restrict_
     // (c) wait for every rank's flag in MY buffer
     if (threadIdx.x < world) {
         const unsigned long long* f = &ctrl->flags[par][threadIdx.x];
+        // Rank skew of seconds is normal in training (a rank writing a checkpoint, a data-loader stall, first-step autotune),
+        // so the wait is long (AR_TIMEOUT_NS, two minutes) and a timeout is FATAL: reducing stale slots would silently
+        // de-synchronise the running statistics of the ranks.  The flag is left for the host (PeerReducer.error()).
         unsigned int spins = 0;
+        unsigned long long t0 = 0ull;
         while (ld_acquire_sys(f) < seq) {
-            if (++spins > (1u << 22)) { s_fail = 1; break; }
-            if (spins > 64) __nanosleep(100);
+            if (++spins > 64) {
+                __nanosleep(200);
+                unsigned long long now;
+                asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(now));
+                if (t0 == 0ull) t0 = now;
+                else if (now - t0 > AR_TIMEOUT_NS) { s_fail = 1; break; }
+            }
         }
     }
     __syncthreads();
+    if (s_fail) {
+        if (threadIdx.x == 0) { ctrl->error = 1u; __threadfence_system(); }
+        __syncthreads();
+        __trap();
+    }
     // (d) reduce the slots in rank order
     const unsigned char* mine = peers.buf[rank] + (size_t)AR_CTRL_BYTES + (size_t)par * world * slot_bytes;
     for (int i = threadIdx.x; i < n; i += AR_THREADS) {

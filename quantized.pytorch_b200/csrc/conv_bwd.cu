@@ -330,15 +330,14 @@ k_conv_dgrad(const __grid_constant__ CUtensorMap tmap_a0, const __grid_constant_
                 tc_fence_after_sync();
                 if (elect_one()) {
                     const uint32_t a_addr = smem_u32(smem + (size_t)s * stage_bytes);
-                    const uint32_t b_addr = a_addr + g.a_planes * a_bytes;
+                    const uint64_t a_desc = desc_kmajor(a_addr, rb), b_desc = desc_kmajor(a_addr + g.a_planes * a_bytes, rb);
                     uint32_t acc = kb != 0;
                     for (int k = 0; k < ksteps; ++k) {
                         // hi*hi, hi*lo, lo*hi  (lo*lo is below the split error)
                         for (int pa = 0; pa < g.a_planes; ++pa)
                             for (int pb = 0; pb < g.b_planes; ++pb) {
                                 if (pa == 1 && pb == 1) continue;
-                                umma_f16(d_tmem, desc_kmajor(a_addr + pa * a_bytes + k * 32, rb),
-                                         desc_kmajor(b_addr + pb * b_bytes + k * 32, rb), idesc, acc);
+                                umma_f16(d_tmem, desc_add(a_desc, pa * a_bytes + k * 32), desc_add(b_desc, pb * b_bytes + k * 32), idesc, acc);
                                 acc = 1;
                             }
                     }
@@ -434,6 +433,299 @@ static int dgrad_launch(const CUtensorMap& ta0, const CUtensorMap& ta1, const CU
     return QB_OK;
 }
 
+// ------------------------------------------------------------------------------------------------
+// dgrad, "flat strip" form (unit-stride problems: every parity class is one).
+//
+// A strip is ONE TMA box {BK channels, Wp, RH, TN} of the gradient codes whose origin lies (dw_min, dh_min) off the strip's
+// first output pixel: it lands in shared memory as rows of BK channels in flat order f' = (tn*RH + y')*Wp + x'.  With the
+// OUTPUT pixels numbered on the same pitch, f = (tn*RH + y)*Wp + x, the operand row of output f under tap t is f + off[t],
+// off[t] = (dh[t]-dh_min)*Wp + (dw[t]-dw_min): every tap reads the SAME box through a UMMA descriptor that simply starts
+// off[t] rows later (descriptors may start inside a swizzle atom: tools/umma_shift_probe.py).  The operand is loaded once
+// instead of once per tap; zero padding is the TMA's out-of-bounds fill.  Output rows with x >= Wc or y >= Hc are
+// garbage: they are staged like the others and clipped by the TMA store.  A strip is <= 256 flat rows = two TMEM
+// accumulators that share every weight stage; two accumulator sets alternate between MMA and epilogue.
+// ------------------------------------------------------------------------------------------------
+constexpr int DF_MAX_WSTAGES = 8;
+
+struct DflatGeom {
+    int B, Hc, Wc, Cn, Ck;
+    int Wp, RH, RHo, TN;        // box = {BK, Wp, RH, TN}; output rows per image slot RHo (row mode: TH, image mode: RH)
+    int TH;                     // output rows advanced per strip (row mode) / Hc (image mode)
+    int R_out, J;               // flat output rows per strip (<= 256), accumulators (1 or 2)
+    int AR;                     // operand rows allocated per A slot
+    int tiles_h, tiles_b;
+    int BK, kblocks, ntaps, wstages, b_planes;
+    int dh_min, dw_min;
+    int off[DG_MAX_TAPS], wtap[DG_MAX_TAPS];
+    int nstage;                 // staging slab buffers (1 or 2)
+    FastDiv d_tiles_m, d_tiles_h;
+};
+
+template <int BN>
+__global__ void __launch_bounds__(DG_THREADS, 1)
+k_conv_dgrad_flat(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_w,
+                  const __grid_constant__ CUtensorMap tmap_o, DflatGeom g, const float* __restrict__ scale_range, int scale_bits,
+                  float scale_mul) {
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+    const int rb = g.BK * 2;
+    const uint32_t a_slot = ((uint32_t)g.AR * rb + 1023u) & ~1023u;
+    const uint32_t w_plane = (uint32_t)BN * rb, w_slot = (uint32_t)g.b_planes * w_plane;
+    const uint32_t slab_bytes = ((uint32_t)g.R_out * 128u + 1023u) & ~1023u;
+    uint8_t* s_a = smem;                                        // 2 slots
+    uint8_t* s_w = s_a + 2 * a_slot;
+    uint8_t* staging = s_w + (size_t)g.wstages * w_slot;
+    uint8_t* tail = staging + (size_t)g.nstage * slab_bytes;
+    uint64_t* a_full = reinterpret_cast<uint64_t*>(tail);       // [2]
+    uint64_t* a_empty = a_full + 2;
+    uint64_t* w_full = a_empty + 2;                             // [DF_MAX_WSTAGES]
+    uint64_t* w_empty = w_full + DF_MAX_WSTAGES;
+    uint64_t* tfull_bar = w_empty + DF_MAX_WSTAGES;             // [2]
+    uint64_t* tempty_bar = tfull_bar + 2;
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(tempty_bar + 2);
+
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+    const int tiles_m = g.tiles_h * g.tiles_b;
+    const int tiles_n = (g.Cn + BN - 1) / BN;
+    const int total = tiles_m * tiles_n;
+    constexpr uint32_t ACC = BN < 32 ? 32 : BN;
+    constexpr uint32_t TMEM_COLS = 4 * ACC;                     // 2 sets x 2 accumulators
+
+    if (warp == 0 && lane == 0) {
+        tma_prefetch_desc(&tmap_a);
+        tma_prefetch_desc(&tmap_w);
+        tma_prefetch_desc(&tmap_o);
+        for (int s = 0; s < 2; ++s) { mbar_init(&a_full[s], 1); mbar_init(&a_empty[s], 1); }
+        for (int s = 0; s < g.wstages; ++s) { mbar_init(&w_full[s], 1); mbar_init(&w_empty[s], 1); }
+        for (int i = 0; i < 2; ++i) { mbar_init(&tfull_bar[i], 1); mbar_init(&tempty_bar[i], 8); }
+        fence_barrier_init();
+    }
+    if (warp == 1) tmem_alloc<TMEM_COLS>(tmem_slot);
+    // operand rows behind the box are read (for garbage outputs only) but never written: no NaN patterns there
+    for (uint32_t i = threadIdx.x; i < 2 * a_slot / 16; i += DG_THREADS) reinterpret_cast<uint4*>(s_a)[i] = make_uint4(0u, 0u, 0u, 0u);
+    fence_proxy_async();
+    tc_fence_before_sync();
+    __syncthreads();
+    tc_fence_after_sync();
+    const uint32_t tmem_base = *tmem_slot;
+
+    auto decode = [&](int t, int& tn, int& b0, int& h0) {
+        tn = (int)fdiv((uint32_t)t, g.d_tiles_m);
+        const uint32_t tm = (uint32_t)(t - tn * tiles_m);
+        const uint32_t q = fdiv(tm, g.d_tiles_h);
+        h0 = (int)(tm - q * (uint32_t)g.tiles_h) * g.TH;
+        b0 = (int)q * g.TN;
+    };
+
+    if (warp == 0) {
+        if (elect_one()) {
+            const uint32_t a_box = (uint32_t)(g.Wp * g.RH * g.TN) * rb;
+            uint32_t ia = 0, iw = 0;
+            for (int t = blockIdx.x; t < total; t += gridDim.x) {
+                int tn, b0, h0;
+                decode(t, tn, b0, h0);
+                const int n0 = tn * BN;
+                for (int kb = 0; kb < g.kblocks; ++kb, ++ia) {
+                    const int sa = ia & 1;
+                    mbar_wait_trap(&a_empty[sa], ((ia >> 1) & 1) ^ 1);
+                    mbar_arrive_expect_tx(&a_full[sa], a_box);
+                    tma_load_4d(s_a + (size_t)sa * a_slot, &tmap_a, &a_full[sa], kb * g.BK, g.dw_min, h0 + g.dh_min, b0);
+                    for (int tp = 0; tp < g.ntaps; ++tp, ++iw) {
+                        const int sw = iw % g.wstages;
+                        mbar_wait_trap(&w_empty[sw], ((iw / g.wstages) & 1) ^ 1);
+                        mbar_arrive_expect_tx(&w_full[sw], w_slot);
+                        for (int p = 0; p < g.b_planes; ++p)
+                            tma_load_3d(s_w + (size_t)sw * w_slot + (size_t)p * w_plane, &tmap_w, &w_full[sw], kb * g.BK, g.wtap[tp],
+                                        p * g.Cn + n0);
+                    }
+                }
+            }
+        }
+    } else if (warp == 1) {
+        constexpr uint32_t idesc = idesc_bf16(128, BN, 0, 0);
+        const int ksteps = g.BK / 16;
+        uint32_t ia = 0, iw = 0;
+        int it = 0;
+        for (int t = blockIdx.x; t < total; t += gridDim.x, ++it) {
+            const int set = it & 1;
+            mbar_wait_trap(&tempty_bar[set], ((it >> 1) & 1) ^ 1);
+            tc_fence_after_sync();
+            const uint32_t d0 = tmem_base + (uint32_t)(set * 2) * ACC;
+            for (int kb = 0; kb < g.kblocks; ++kb, ++ia) {
+                const int sa = ia & 1;
+                mbar_wait_trap(&a_full[sa], (ia >> 1) & 1);
+                const uint64_t a_desc0 = desc_kmajor(smem_u32(s_a + (size_t)sa * a_slot), rb);
+                for (int tp = 0; tp < g.ntaps; ++tp, ++iw) {
+                    const int sw = iw % g.wstages;
+                    mbar_wait_trap(&w_full[sw], (iw / g.wstages) & 1);
+                    tc_fence_after_sync();
+                    if (elect_one()) {
+                        const uint64_t w_desc = desc_kmajor(smem_u32(s_w + (size_t)sw * w_slot), rb);
+                        const uint32_t first = (kb | tp) == 0;
+                        for (int j = 0; j < g.J; ++j) {
+                            const uint64_t a_desc = desc_add(a_desc0, (uint32_t)(128 * j + g.off[tp]) * (uint32_t)rb);
+                            const uint32_t dj = d0 + (uint32_t)j * ACC;
+                            if (ksteps == 4 && g.b_planes == 2) {
+                                umma_f16(dj, a_desc, w_desc, idesc, first ? 0u : 1u);
+                                umma_f16(dj, a_desc, desc_add(w_desc, w_plane), idesc, 1u);
+#pragma unroll
+                                for (int k = 1; k < 4; ++k) {
+                                    umma_f16(dj, desc_add(a_desc, k * 32), desc_add(w_desc, k * 32), idesc, 1u);
+                                    umma_f16(dj, desc_add(a_desc, k * 32), desc_add(w_desc, w_plane + k * 32), idesc, 1u);
+                                }
+                            } else {
+                                uint32_t acc = first ? 0u : 1u;
+                                for (int k = 0; k < ksteps; ++k)
+                                    for (int p = 0; p < g.b_planes; ++p) {
+                                        umma_f16(dj, desc_add(a_desc, k * 32), desc_add(w_desc, (uint32_t)p * w_plane + k * 32), idesc, acc);
+                                        acc = 1u;
+                                    }
+                            }
+                        }
+                        umma_commit(&w_empty[sw]);
+                        if (tp == g.ntaps - 1) umma_commit(&a_empty[sa]);
+                        if (tp == g.ntaps - 1 && kb == g.kblocks - 1) umma_commit(&tfull_bar[set]);
+                    }
+                    __syncwarp();
+                }
+            }
+        }
+    } else {
+        // ===== epilogue: warps 2-5 drain accumulator 0, warps 6-9 accumulator 1 (one warp per TMEM lane quarter) =====
+        const int e_all = threadIdx.x - 64;
+        const int sub = warp & 3, j = (warp - 2) >> 2;
+        float scale = scale_mul;
+        if (scale_range) scale *= make_qparams_d((double)__ldg(scale_range), (double)__ldg(scale_range + 1), scale_bits).scale;
+        const int f = j * 128 + sub * 32 + lane;                 // flat output row of this thread
+        const bool live = j < g.J && f < g.R_out;
+        const uint32_t row_off = (uint32_t)f * 128u, sw = (uint32_t)(f & 7);
+        const uint32_t stage_u32 = smem_u32(staging);
+        int it = 0;
+        uint32_t slab = 0;
+        for (int t = blockIdx.x; t < total; t += gridDim.x, ++it) {
+            int tn, b0, h0;
+            decode(t, tn, b0, h0);
+            const int n0 = tn * BN;
+            const int ncols = (g.Cn - n0 < BN) ? g.Cn - n0 : BN;
+            const int nslabs = (ncols + 31) >> 5;
+            const int set = it & 1;
+            mbar_wait_trap(&tfull_bar[set], (it >> 1) & 1);
+            tc_fence_after_sync();
+            const uint32_t t_addr = tmem_base + (uint32_t)(set * 2 + j) * ACC + ((uint32_t)(sub * 32) << 16);
+#pragma unroll 1
+            for (int cs = 0; cs < nslabs; ++cs, ++slab) {
+                uint32_t r[32];
+                if (j < g.J) {
+                    tmem_ld_32x32(t_addr + (uint32_t)(cs * 32), r);
+                    tmem_ld_wait();
+                }
+                if (cs == nslabs - 1) {
+                    tc_fence_before_sync();
+                    __syncwarp();
+                    if (lane == 0) mbar_arrive(&tempty_bar[set]);
+                }
+                const uint32_t sbuf = g.nstage == 2 ? (slab & 1u) : 0u;
+                // the store that last used this staging buffer has finished reading it
+                if (e_all == 0) { if (g.nstage == 2) tma_store_wait_read<1>(); else tma_store_wait_read<0>(); }
+                asm volatile("bar.sync 1, 256;" ::: "memory");
+                if (live) {
+                    const uint32_t dst = stage_u32 + sbuf * slab_bytes + row_off;
+#pragma unroll
+                    for (int q = 0; q < 8; ++q) {
+                        const float v0 = __uint_as_float(r[4 * q]) * scale, v1 = __uint_as_float(r[4 * q + 1]) * scale,
+                                    v2 = __uint_as_float(r[4 * q + 2]) * scale, v3 = __uint_as_float(r[4 * q + 3]) * scale;
+                        asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" ::"r"(dst + (((uint32_t)q ^ sw) << 4)), "f"(v0),
+                                     "f"(v1), "f"(v2), "f"(v3) : "memory");
+                    }
+                }
+                fence_proxy_async();
+                asm volatile("bar.sync 2, 256;" ::: "memory");
+                if (e_all == 0) {
+                    tma_store_4d(&tmap_o, staging + (size_t)sbuf * slab_bytes, n0 + cs * 32, 0, h0, b0);
+                    tma_store_commit();
+                }
+            }
+        }
+        if (e_all == 0) tma_store_wait<0>();
+    }
+    tc_fence_before_sync();
+    __syncthreads();
+    if (warp == 1) tmem_dealloc<TMEM_COLS>(tmem_base);
+}
+
+template <int BN>
+static int dgrad_flat_launch(const CUtensorMap& ta, const CUtensorMap& tw, const CUtensorMap& to, const DflatGeom& g, size_t smem,
+                             const float* scale_range, int scale_bits, float scale_mul, cudaStream_t st) {
+    QB_CUDA(cudaFuncSetAttribute(k_conv_dgrad_flat<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    const int64_t total = (int64_t)g.tiles_h * g.tiles_b * ((g.Cn + BN - 1) / BN);
+    int sms = qb_sm_count();
+    if (sms <= 0) sms = 148;
+    const unsigned grid = (unsigned)(total < sms ? total : sms);
+    k_conv_dgrad_flat<BN><<<grid, DG_THREADS, smem, st>>>(ta, tw, to, g, scale_range, scale_bits, scale_mul);
+    QB_LAUNCH_CHECK();
+    return QB_OK;
+}
+
+// Strip geometry of one parity class; returns the dynamic shared memory it needs, 0 if the flat form does not apply.
+static size_t dgrad_flat_geom(DflatGeom& g, int B, int Hc, int Wc, int Cn, int Ck, int BK, int BN, const int* dh, const int* dw,
+                              const int* wtap, int ntaps) {
+    memset(&g, 0, sizeof(g));
+    int dh_min = dh[0], dh_max = dh[0], dw_min = dw[0], dw_max = dw[0];
+    for (int i = 1; i < ntaps; ++i) {
+        dh_min = dh[i] < dh_min ? dh[i] : dh_min; dh_max = dh[i] > dh_max ? dh[i] : dh_max;
+        dw_min = dw[i] < dw_min ? dw[i] : dw_min; dw_max = dw[i] > dw_max ? dw[i] : dw_max;
+    }
+    const int halo_h = dh_max - dh_min, halo_w = dw_max - dw_min;
+    g.B = B; g.Hc = Hc; g.Wc = Wc; g.Cn = Cn; g.Ck = Ck; g.BK = BK; g.ntaps = ntaps; g.b_planes = 2;
+    g.dh_min = dh_min; g.dw_min = dw_min;
+    g.Wp = Wc + halo_w;
+    if (g.Wp > 256) return 0;
+    const int Hp = Hc + halo_h;
+    if (Hp * g.Wp <= 256) {                      // image mode: whole padded images
+        g.RH = g.RHo = Hp;
+        g.TN = 256 / (Hp * g.Wp);
+        if (g.TN > B) g.TN = B;
+        g.TH = Hc;
+        g.tiles_h = 1;
+    } else {                                     // row mode
+        g.TN = 1;
+        g.TH = 256 / g.Wp;
+        if (g.TH > Hc) g.TH = Hc;
+        g.RHo = g.TH;
+        g.RH = g.TH + halo_h;
+        if (g.RH > 256) return 0;
+        g.tiles_h = (Hc + g.TH - 1) / g.TH;
+    }
+    g.tiles_b = (B + g.TN - 1) / g.TN;
+    g.R_out = g.TN * g.RHo * g.Wp;
+    g.J = (g.R_out + 127) / 128;
+    const int box_rows = g.Wp * g.RH * g.TN;
+    int need = 128 * g.J + halo_h * g.Wp + halo_w;
+    if (need < box_rows) need = box_rows;
+    g.AR = (need + 7) & ~7;
+    for (int i = 0; i < ntaps; ++i) {
+        g.off[i] = (dh[i] - dh_min) * g.Wp + (dw[i] - dw_min);
+        g.wtap[i] = wtap[i];
+    }
+    g.kblocks = (Ck + BK - 1) / BK;
+    g.d_tiles_m = make_fastdiv((uint32_t)(g.tiles_h * g.tiles_b));
+    g.d_tiles_h = make_fastdiv((uint32_t)g.tiles_h);
+    const int rb = BK * 2;
+    const size_t a_slot = ((size_t)g.AR * rb + 1023) & ~(size_t)1023, w_slot = (size_t)2 * BN * rb;
+    const size_t slab = ((size_t)g.R_out * 128 + 1023) & ~(size_t)1023;
+    const size_t limit = 226 * 1024, fixed = 1024 + 512 + 2 * a_slot;
+    if (fixed + slab + 2 * w_slot > limit) return 0;
+    // weight ring first (the stream that must stay in flight), then a second staging buffer if it still fits
+    int ws = (int)((limit - fixed - slab) / w_slot);
+    g.nstage = 1;
+    if (ws >= 5 && fixed + 2 * slab + 4 * w_slot <= limit) {
+        g.nstage = 2;
+        ws = (int)((limit - fixed - 2 * slab) / w_slot);
+    }
+    g.wstages = ws > DF_MAX_WSTAGES ? DF_MAX_WSTAGES : ws;
+    return fixed + (size_t)g.nstage * slab + (size_t)g.wstages * w_slot;
+}
+
 /* dX of y = conv2d(x, w_hat) (groups 1, dilation 1, square stride / padding):
  *   a0 (and a1): bf16 [B,Ho,Wo,Cout] channels-last planes of the output gradient (one plane: integer codes q - zp, or two
  *   planes: hi / lo split);  wt: qb_wt_pack's planes;  dx: fp32 [B,H,W,Cin] channels-last.
@@ -503,6 +795,31 @@ extern "C" int qb_conv_dgrad(const uint16_t* a0, const uint16_t* a1, const uint1
                 }
             if (g.ntaps == 0) continue;
             const int64_t Hc = (H - ph + stride - 1) / stride, Wc = (W - pw + stride - 1) / stride;
+            static const bool flat_off = getenv("QB_DGRAD_FLAT") && getenv("QB_DGRAD_FLAT")[0] == '0';
+            if (!a1 && !flat_off) {
+                DflatGeom fg;
+                const size_t fsmem = dgrad_flat_geom(fg, (int)B, (int)Hc, (int)Wc, (int)Cin, (int)Cout, BK, BN, g.dh, g.dw, g.wtap, g.ntaps);
+                if (fsmem) {
+                    CUtensorMap fa, fo;
+                    const uint64_t adims[4] = {(uint64_t)Cout, (uint64_t)Wo, (uint64_t)Ho, (uint64_t)B};
+                    const uint64_t astr[3] = {(uint64_t)Cout * 2, (uint64_t)Wo * Cout * 2, (uint64_t)Ho * Wo * Cout * 2};
+                    const uint32_t abox[4] = {(uint32_t)BK, (uint32_t)fg.Wp, (uint32_t)fg.RH, (uint32_t)fg.TN};
+                    int rc = qb_make_tmap(&fa, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, a0, adims, astr, abox, nullptr, BK * 2);
+                    if (rc) return rc;
+                    float* base = dx + ((int64_t)ph * W + pw) * Cin;
+                    const uint64_t odims[4] = {(uint64_t)Cin, (uint64_t)Wc, (uint64_t)Hc, (uint64_t)B};
+                    const uint64_t ostr[3] = {(uint64_t)stride * Cin * 4, (uint64_t)stride * W * Cin * 4, (uint64_t)H * W * Cin * 4};
+                    const uint32_t obox[4] = {32u, (uint32_t)fg.Wp, (uint32_t)fg.RHo, (uint32_t)fg.TN};
+                    rc = qb_make_tmap(&fo, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, base, odims, ostr, obox, nullptr, 128);
+                    if (rc) return rc;
+                    if (BN == 128) rc = dgrad_flat_launch<128>(fa, tw, fo, fg, fsmem, scale_range, scale_bits, scale_mul, st);
+                    else if (BN == 64) rc = dgrad_flat_launch<64>(fa, tw, fo, fg, fsmem, scale_range, scale_bits, scale_mul, st);
+                    else if (BN == 32) rc = dgrad_flat_launch<32>(fa, tw, fo, fg, fsmem, scale_range, scale_bits, scale_mul, st);
+                    else rc = dgrad_flat_launch<16>(fa, tw, fo, fg, fsmem, scale_range, scale_bits, scale_mul, st);
+                    if (rc) return rc;
+                    continue;
+                }
+            }
             g.B = (int)B; g.Hc = (int)Hc; g.Wc = (int)Wc; g.Cn = (int)Cin; g.Ck = (int)Cout;
             g.BK = BK;
             g.a_planes = a1 ? 2 : 1;
@@ -670,21 +987,28 @@ k_conv_wgrad(const __grid_constant__ CUtensorMap tmap_x, const __grid_constant__
         for (int t = t_begin; t < t_end; ++t, ++ib) {
             const int sbi = ib % g.b_stages;
             mbar_wait_trap(&b_full[sbi], (ib / g.b_stages) & 1);
-            const uint32_t b_addr = smem_u32(s_b + (size_t)sbi * b_slot);
+            const uint64_t b_desc = desc_mnmajor(smem_u32(s_b + (size_t)sbi * b_slot), rbB, runB);
             for (int j = 0; j < jn; ++j, ++ia) {
                 const int s = ia % g.a_stages;
                 mbar_wait_trap(&a_full[s], (ia / g.a_stages) & 1);
                 tc_fence_after_sync();
                 if (elect_one()) {
-                    const uint32_t a_addr = smem_u32(s_a + (size_t)s * a_slot);
+                    const uint64_t a_desc = desc_mnmajor(smem_u32(s_a + (size_t)s * a_slot), rbA, runA);
                     const uint32_t d_tmem = tmem_base + (uint32_t)j * acc_stride;
+                    const uint32_t stepA = 16u * (uint32_t)rbA, stepB = 16u * (uint32_t)rbB;
                     uint32_t acc = t != t_begin;
-                    for (int ks = 0; ks < ksteps; ++ks)
-                        for (int p = 0; p < g.g_planes; ++p) {
-                            umma_f16(d_tmem, desc_mnmajor(a_addr + (uint32_t)(ks * 16 * rbA), rbA, runA),
-                                     desc_mnmajor(b_addr + (uint32_t)p * b_plane + (uint32_t)(ks * 16 * rbB), rbB, runB), idesc, acc);
-                            acc = 1;
+                    if (g.g_planes == 2) {
+                        for (int ks = 0; ks < ksteps; ++ks) {
+                            umma_f16(d_tmem, desc_add(a_desc, ks * stepA), desc_add(b_desc, ks * stepB), idesc, acc);
+                            umma_f16(d_tmem, desc_add(a_desc, ks * stepA), desc_add(b_desc, b_plane + ks * stepB), idesc, 1u);
+                            acc = 1u;
                         }
+                    } else {
+                        for (int ks = 0; ks < ksteps; ++ks) {
+                            umma_f16(d_tmem, desc_add(a_desc, ks * stepA), desc_add(b_desc, ks * stepB), idesc, acc);
+                            acc = 1u;
+                        }
+                    }
                     umma_commit(&a_empty[s]);
                     if (j == jn - 1) umma_commit(&b_empty[sbi]);
                     if (j == jn - 1 && t == t_end - 1) umma_commit(done_bar);

@@ -222,14 +222,14 @@ k_conv_i8(const __grid_constant__ CUtensorMap tmap_x, const __grid_constant__ CU
                 mbar_wait(&full_bar[s], ph);
                 tc_fence_after_sync();
                 if (elect_one()) {
-                    const uint32_t st_addr = smem_u32(smem + (size_t)s * stage_bytes), w_addr = smem_u32(wres);
+                    const uint64_t st_desc = umma_smem_desc(smem_u32(smem + (size_t)s * stage_bytes), g.BK);
+                    const uint64_t w_desc = umma_smem_desc(smem_u32(wres), g.BK);
                     for (int r = 0; r < g.kh; ++r)
                         for (int s_ = 0; s_ < g.kw; ++s_) {
-                            const uint32_t a_addr = st_addr + (uint32_t)s_ * hbox_bytes + (uint32_t)(r * g.TW * g.BK);
-                            const uint32_t b_addr = w_addr + (uint32_t)(r * g.kw + s_) * b_bytes;
+                            const uint64_t a_desc = desc_add(st_desc, (uint32_t)s_ * hbox_bytes + (uint32_t)(r * g.TW * g.BK));
+                            const uint64_t b_desc = desc_add(w_desc, (uint32_t)(r * g.kw + s_) * b_bytes);
                             for (int k = 0; k < mmas; ++k)
-                                umma_i8(d_tmem, umma_smem_desc(a_addr + k * 32, g.BK), umma_smem_desc(b_addr + k * 32, g.BK),
-                                        idesc, (r | s_ | k) != 0);
+                                umma_i8(d_tmem, desc_add(a_desc, k * 32), desc_add(b_desc, k * 32), idesc, (r | s_ | k) != 0);
                         }
                     umma_commit(&empty_bar[s]);
                     umma_commit(&tfull_bar[buf]);
@@ -244,11 +244,16 @@ k_conv_i8(const __grid_constant__ CUtensorMap tmap_x, const __grid_constant__ CU
                 mbar_wait(&full_bar[s], ph);
                 tc_fence_after_sync();
                 if (elect_one()) {
-                    const uint32_t a_addr = smem_u32(smem + (size_t)s * stage_bytes);
-                    const uint32_t b_addr = a_addr + a_bytes;
-                    for (int k = 0; k < mmas; ++k)
-                        umma_i8(d_tmem, umma_smem_desc(a_addr + k * 32, g.BK), umma_smem_desc(b_addr + k * 32, g.BK), idesc,
-                                (kb | k) != 0);
+                    const uint64_t a_desc = umma_smem_desc(smem_u32(smem + (size_t)s * stage_bytes), g.BK);
+                    const uint64_t b_desc = desc_add(a_desc, a_bytes);
+                    if (mmas == 4) {
+                        umma_i8(d_tmem, a_desc, b_desc, idesc, kb != 0);
+#pragma unroll
+                        for (int k = 1; k < 4; ++k) umma_i8(d_tmem, desc_add(a_desc, k * 32), desc_add(b_desc, k * 32), idesc, 1u);
+                    } else {
+                        for (int k = 0; k < mmas; ++k)
+                            umma_i8(d_tmem, desc_add(a_desc, k * 32), desc_add(b_desc, k * 32), idesc, (kb | k) != 0);
+                    }
                     umma_commit(&empty_bar[s]);
                     if (kb == num_kb - 1) umma_commit(&tfull_bar[buf]);
                 }

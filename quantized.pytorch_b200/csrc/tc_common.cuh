@@ -166,6 +166,14 @@ __device__ __forceinline__ uint64_t umma_smem_desc_sw128(uint32_t smem_addr) {
     d |= (uint64_t)2 << 61;
     return d;
 }
+// descriptor + byte offset (a multiple of 16 that stays inside the 14-bit address field): ONE 32-bit add, so that the
+// single MMA-issuing thread spends ~2 instructions per tcgen05.mma (a descriptor rebuilt per MMA made the issue loop
+// the bottleneck: ~10 dependent uniform-datapath instructions for 32 tensor cycles of work)
+__device__ __forceinline__ uint64_t desc_add(uint64_t d, uint32_t bytes) {
+    uint64_t r;
+    asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "r"((uint32_t)d + (bytes >> 4)), "r"((uint32_t)(d >> 32)));
+    return r;
+}
 // Instruction descriptor (32 bit): c_format [4,6) (1 = F32, 2 = S32), a_format [7,10), b_format [10,13)
 // (8-bit int: 0 = unsigned, 1 = signed; f16 kind: 0 = F16, 1 = BF16), a_major bit 15, b_major bit 16 (0 = K-major),
 // N>>3 in [17,23), M>>4 in [24,29).

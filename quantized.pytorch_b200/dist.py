@@ -107,8 +107,15 @@ class PeerReducer(StatReducer):
             super().grad_range(rng)
 
     def error(self):
-        """True if any exchange timed out waiting for a peer (its results were invalid)."""
+        """True if an exchange timed out waiting for a peer.  The kernel traps in that case (a timeout is fatal: reducing
+        stale slots would de-synchronise the ranks), so this is only ever seen by a process inspecting a peer's buffer."""
         return bool(self.buf[8:12].view(torch.int32).item())
+
+    def check(self):
+        """Host-side watchdog, call once per step (synchronises): raises if any exchange of this rank failed."""
+        if self.error():
+            raise Q.QB200Error("cross-rank statistic exchange timed out on rank %d (a peer did not arrive within 120 s)"
+                               % self.rank)
 
 
 def init(device=None, group=None, peer=None):
@@ -130,12 +137,21 @@ def init(device=None, group=None, peer=None):
                 sys.stderr.write("qtorch_b200.dist: peer-memory reducer unavailable (%s); using NCCL all-reduces\n"
                                  % (str(e).splitlines()[0] if str(e) else type(e).__name__))
         Q.set_stat_reducer(red if red is not None else StatReducer(group))
+        Q.set_noise_rank(_state["rank"])
         _state["reducer"] = Q._reducer if hasattr(Q, "_reducer") else None
     return _state["rank"], _state["world"]
 
 
+def check():
+    """Raise if the peer-memory exchange of this rank reported a failure (PeerReducer.check)."""
+    red = getattr(Q, "_reducer", None)
+    if isinstance(red, PeerReducer):
+        red.check()
+
+
 def shutdown():
     Q.set_stat_reducer(None)
+    Q.set_noise_rank(0)
 
 
 def broadcast_parameters(model, src=0, group=None):

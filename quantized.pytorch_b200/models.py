@@ -185,8 +185,13 @@ def resnet_quantized(q=None, depth=None, dataset="imagenet", num_classes=None):
         block, layers = _IMAGENET_LAYERS[depth or 50]
         stages = [(64 * 2 ** i, n, 1 if i == 0 else 2) for i, n in enumerate(layers)]
         model = QResNet(q, block, stages, num_classes or 1000, stem=(64, 7, 2, 3, True), pool=7)
-        model.regime = [{"epoch": 0, "optimizer": "SGD", "momentum": 0.9, "lr": 0.1},
-                        {"epoch": 30, "lr": 1e-2}, {"epoch": 60, "lr": 1e-3}, {"epoch": 80, "lr": 1e-4}]
+        # resnet_quantized.py:187-201: linear warm-up of the learning rate over the first 5 epochs (5004 steps each at
+        # batch 256), expressed - as in the reference - as the source of a step lambda for its regime scheduler
+        scale, rate = 1.0, (0.1 - 0.0) / (5004 * 5)
+        model.regime = [{"epoch": 0, "optimizer": "SGD", "momentum": 0.9,
+                         "step_lambda": "lambda t: {'lr': %s + t * %s}" % (0, rate)},
+                        {"epoch": 5, "lr": scale * 1e-1}, {"epoch": 30, "lr": scale * 1e-2},
+                        {"epoch": 60, "lr": scale * 1e-3}, {"epoch": 80, "lr": scale * 1e-4}]
         return model
     if dataset == "cifar10":
         n = int(((depth or 56) - 2) / 6)

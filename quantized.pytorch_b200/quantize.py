@@ -10,7 +10,7 @@ Differences that are deliberate and documented in DESIGN.md:
   * the batch-mean of per-sample minima / maxima and the RangeBN chunk means are accumulated in fp64 and
     rounded once (ATen sums in fp32 in an unspecified order): ranges agree to <= 1 ulp, and given the same
     range the integer codes are bit-identical;
-  * stochastic-rounding noise comes from Philox4x32-10 inside the kernel (torch's CPU mt19937 stream cannot
+  * stochastic-rounding noise comes from Philox4x32-7 inside the kernel (torch's CPU mt19937 stream cannot
     be reproduced on a GPU); ``set_noise_provider`` injects a recorded noise tensor for parity tests.
 """
 import itertools
@@ -30,7 +30,7 @@ __all__ = ["UniformQuantize", "UniformQuantizeGrad", "quantize", "quantize_grad"
            "QuantNode", "QuantMeasure", "QConv2d", "QLinear", "RangeBN", "set_measure_mode", "set_quant_mode",
            "overwrite_params", "freeze_quant_params", "set_bn_is_train", "set_global_quantization_method",
            "distill_set_train", "is_bn", "is_quant", "recursive_apply", "set_noise_provider", "manual_seed",
-           "noise_step", "set_stat_reducer"]
+           "noise_step", "set_stat_reducer", "set_noise_rank"]
 
 # ---------------------------------------------------------------------------------------------------
 # noise source of the stochastic branch + cross-rank statistic hooks
@@ -71,8 +71,18 @@ def noise_step(device=None):
     return t
 
 
+_seed_rank = 0
+
+
+def set_noise_rank(rank):
+    """Batch-sharded training (dist.py): mix the rank into every Philox key so that the shards draw INDEPENDENT noise
+    fields (the same local element index on two ranks is a different element of the global batch)."""
+    global _seed_rank
+    _seed_rank = int(rank)
+
+
 def _next_seed():
-    return (_seed_base + next(_seed_counter) * 0x9E3779B97F4A7C15) & (2 ** 64 - 1)
+    return (_seed_base + next(_seed_counter) * 0x9E3779B97F4A7C15 + _seed_rank * 0xD1B54A32D192ED03) & (2 ** 64 - 1)
 
 
 def set_stat_reducer(reducer):
