@@ -76,6 +76,13 @@ int qb_fakequant_affine(const float* x, float* y, uint8_t* codes, int64_t n, int
 int qb_fakequant_affine16(const float* x, float* y, uint8_t* codes, uint16_t* codes16, int64_t n, int bits,
                           const float* range_dev, double lo, double hi, int scale_mode, void* stream);
 
+/* The min-anchored branch with stochastic rounding (quantize.py:90-100, enforce_true_zero=False, stochastic=True; reached
+ * through quantize(x, num_chunks=<truthy>), :159-160): y = rne(clamp((x - min)/s + u, 0, 2^bits-1)) * s + min, u = noise
+ * (injected tensor, or in-kernel Philox as in qb_fakequant_grad).  y may alias x. */
+int qb_fakequant_affine_stochastic(const float* x, float* y, int64_t n, int bits, const float* range_dev, double lo, double hi,
+                                   int scale_mode, const float* noise, uint64_t seed, uint64_t offset, const uint64_t* step_dev,
+                                   void* stream);
+
 /* Self-test hook (no reference counterpart): the quantizers divide by the scale with an FMA sequence that must equal
  * IEEE division (ATen's div_, quantize.py:90,92); this evaluates that sequence and __fdiv_rn on the same operands
  * so a test can compare them bit for bit.  a, out_fast, out_ieee: fp32[n].                                          */

@@ -61,7 +61,7 @@ def affine_scale(lo, hi, bits):
     return max(s, 1e-8)
 
 
-def fq_affine(x, bits=8, lo=None, hi=None, want_codes=False):
+def fq_affine(x, bits=8, lo=None, hi=None, want_codes=False, noise=None):
     """quantize.py:42-75, 90, 95, 100 (deterministic, min-anchored).
 
     lo/hi: Python floats (activation ranges), broadcastable tensors (per-channel
@@ -75,6 +75,8 @@ def fq_affine(x, bits=8, lo=None, hi=None, want_codes=False):
     s = affine_scale(lo, hi, bits)
     t = x.clone()
     t.add_(-lo).div_(s).add_(0.0)          # :90
+    if noise is not None:                  # :92-94 (stochastic := num_chunks through quantize()'s positional shuffle)
+        t.add_(noise)
     t.clamp_(0.0, qmax).round_()           # :95
     codes = t.clone() if want_codes else None
     t.add_(-0.0).mul_(s).add_(lo)          # :100

@@ -31,6 +31,7 @@ PROTOTYPES = {
     "qb_measure_finalize": (_i32, [_p, _p, _p, _p, _p, _p, _dbl, _i32, _i32, _i32, _p, _p]),
     "qb_fakequant_affine": (_i32, [_p, _p, _p, _i64, _i32, _p, _dbl, _dbl, _i32, _p]),
     "qb_fakequant_affine16": (_i32, [_p, _p, _p, _p, _i64, _i32, _p, _dbl, _dbl, _i32, _p]),
+    "qb_fakequant_affine_stochastic": (_i32, [_p, _p, _i64, _i32, _p, _dbl, _dbl, _i32, _p, _u64, _u64, _p, _p]),
     "qb_selftest_div": (_i32, [_p, _flt, _p, _p, _i64, _p]),
     "qb_fakequant_rows": (_i32, [_p, _p, _p, _i64, _i64, _i32, _p, _p, _i32, _p]),
     "qb_minmax_ws_bytes": (_sz, []),
@@ -298,6 +299,21 @@ def fakequant_affine(x, bits, range_dev=None, lo=0.0, hi=0.0, scale_mode=QB_SCAL
         return out
     _run("qb_fakequant_affine", (4 + (4 if want_y else 0) + (1 if codes is not None else 0)) * x.numel(), _ptr(x), _ptr(out) if want_y else None, _ptr(codes), x.numel(), int(bits),
                                    _ptr(range_dev), float(lo), float(hi), int(scale_mode), _stream())
+    return out
+
+
+def fakequant_affine_stochastic(x, bits, range_dev=None, lo=0.0, hi=0.0, scale_mode=QB_SCALE_DOUBLE, noise=None, seed=0,
+                                step_dev=None, out=None):
+    """Min-anchored fake-quant with stochastic rounding (qb_fakequant_affine_stochastic)."""
+    x = _f32c(x, "x")
+    if out is None:
+        out = torch.empty_like(x)
+    if noise is not None:
+        noise = _f32c(noise, "noise")
+        if noise.numel() != x.numel():
+            raise QB200Error("noise has %d elements, input %d" % (noise.numel(), x.numel()))
+    _run("qb_fakequant_affine_stochastic", (8 + (4 if noise is not None else 0)) * x.numel(), _ptr(x), _ptr(out), x.numel(), int(bits),
+         _ptr(range_dev), float(lo), float(hi), int(scale_mode), _ptr(noise), int(seed) & (2 ** 64 - 1), 0, _ptr(step_dev), _stream())
     return out
 
 

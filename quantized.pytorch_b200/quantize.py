@@ -236,9 +236,14 @@ class UniformQuantize(InplaceFunction):
                                     stochastic=bool(stochastic), seed=_next_seed(), step_dev=noise_step(x.device), out=out)
         else:
             if stochastic:
-                raise QB200Error("UniformQuantize: stochastic rounding on the min-anchored branch is not implemented "
-                                 "(no call site of the reference reaches it)")
-            if per_row:
+                if per_row:
+                    raise QB200Error("UniformQuantize: stochastic rounding with per-row ranges is not implemented")
+                noise = _noise_provider(tuple(x.shape)) if _noise_provider is not None else None
+                if noise is not None and _abi.is_nhwc(x):
+                    noise = noise.reshape(x.shape).contiguous(memory_format=torch.channels_last)
+                y = _abi.fakequant_affine_stochastic(x, num_bits, range_dev=dev_range, lo=lo, hi=hi, scale_mode=mode, noise=noise,
+                                                     seed=_next_seed(), step_dev=noise_step(x.device), out=out)
+            elif per_row:
                 y, _, _ = _abi.fakequant_rows(x, num_bits, row_min=min_value.detach().reshape(-1).contiguous().float(),
                                               row_max=max_value.detach().reshape(-1).contiguous().float(),
                                               compute_range=False, out=out)

@@ -116,3 +116,20 @@ def test_module_api_surface(nets):
         b = inspect.signature(getattr(ref_q, cls).__init__)
         assert list(a.parameters) == list(b.parameters), cls
         assert [p.default for p in a.parameters.values()] == [p.default for p in b.parameters.values()], cls
+
+
+def test_oracle_stochastic_min_anchored_branch_matches_reference(nets):
+    """quantize(x, num_chunks=<truthy>) of the reference = min-anchored branch WITH noise (quantize.py:92-94, 159-160); the
+    oracle restatement (qref.fq_affine(noise=...)) reproduces it bit for bit with the recorded uniform_ noise."""
+    from oracle import qref
+    ref_q = nets[1]
+    torch.manual_seed(11)
+    x = torch.randn(4, 8, 16, 16)
+    lo, hi = float(x.min()), float(x.max())
+    log = []
+    with ref_import.record_uniform(log):
+        want = ref_q.quantize(x, 8, lo, hi, num_chunks=4)
+    assert len(log) == 1
+    got = qref.fq_affine(x, 8, lo, hi, noise=log[0])
+    assert torch.equal(got, want)
+    assert not torch.equal(want, ref_q.quantize(x, 8, lo, hi))
