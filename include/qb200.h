@@ -320,6 +320,10 @@ int qb_conv_stem_wgrad(const float* grad_out, const uint8_t* x_codes, float* dw,
 int qb_fakequant2(const float* x, float* y, int64_t rows, int64_t cols, const float* zero_point, const float* range,
                   int per_row, int bits, int is_signed, int dequantize, const float* noise, int stochastic,
                   uint64_t seed, uint64_t offset, const uint64_t* step_dev, void* stream);
+/* Per-tensor, unsigned, deterministic form of the same quantizer that also emits the integer codes as uint8 and bf16 (bits <= 8):
+ * feeds quantize2.QConv2d / QLinear (quantize2.py:204-272) to qb_conv_i8_fwd / qb_gemm_i8 / qb_conv_wgrad.  y optional. */
+int qb_fakequant2_codes(const float* x, float* y, uint8_t* codes, uint16_t* codes16, int64_t n, const float* zero_point,
+                        const float* range, int bits, void* stream);
 /* calculate_qparams with flatten_dims=(1,-1) (quantize2.py:19-28): min / max of every row of x [rows, cols].         */
 int qb_row_minmax(const float* x, int64_t rows, int64_t cols, float* row_min, float* row_max, void* stream);
 /* quantize2.RangeBN (quantize2.py:275-349): red = double[3C] from qb_rangebn_stats[_nhwc]; scale is neither inverted
@@ -388,6 +392,17 @@ int qb_wt_pack(const float* w_hat, uint16_t* wt, int64_t Cout, int64_t Cin, int 
 int qb_conv_dgrad(const uint16_t* a0, const uint16_t* a1, const uint16_t* wt, float* dx, int64_t B, int64_t H, int64_t W,
                   int64_t Cin, int64_t Cout, int kh, int kw, int stride, int pad, const float* scale_range, int scale_bits,
                   float scale_mul, void* stream);
+/* Direct convolution / linear kernels for every geometry the tensor-core kernels do not take (conv_generic.cu): the
+ * reference's F.conv2d(x_hat, w_hat, b_hat) / F.linear and their gradients (models/modules/quantize.py:142-156, 343, 424) on
+ * the fake-quantized fp32 tensors, CUDA cores, fp64 accumulation, deterministic.  They keep EVERY quantized layer off cuDNN /
+ * cuBLAS.  conv = {kh, kw, stride_h, stride_w, pad_h, pad_w, dil_h, dil_w, groups}; x_strides / o_strides = element strides
+ * (n, c, h, w) of x (dx) and out (grad_out); w [C_out][C_in/groups][kh][kw].  Linear: H = W = kh = kw = 1. */
+int qb_conv_generic_fwd(const float* x, const float* w, const float* bias, float* out, int64_t B, int64_t Cin, int64_t H, int64_t W,
+                        int64_t Cout, const int* conv, const int64_t* x_strides, const int64_t* o_strides, void* stream);
+int qb_conv_generic_dgrad(const float* grad_out, const float* w, float* dx, int64_t B, int64_t Cin, int64_t H, int64_t W, int64_t Cout,
+                          const int* conv, const int64_t* x_strides, const int64_t* o_strides, void* stream);
+int qb_conv_generic_wgrad(const float* grad_out, const float* x, float* dw, float* db, int64_t B, int64_t Cin, int64_t H, int64_t W,
+                          int64_t Cout, const int* conv, const int64_t* x_strides, const int64_t* o_strides, void* stream);
 /* Hardware probe used by tools/umma_shift_probe.py (UMMA descriptors that start inside an 8-row swizzle atom); not on any
  * product path. */
 int qb_debug_umma_shift(const uint16_t* a, const uint16_t* b, float* out, int mn, int r0, int use_boff, void* stream);

@@ -122,6 +122,46 @@ def gen_modules(r2):
     save("q2_modules.npz", d)
 
 
+TC_CASES = {"tc_conv": ("conv", dict(cin=16, cout=32, k=3, stride=1, pad=1, bias=True, biprec=True, bits_grad=8), (4, 16, 8, 8)),
+            "tc_conv_s2_nobias": ("conv", dict(cin=32, cout=16, k=3, stride=2, pad=1, bias=False, biprec=True, bits_grad=8), (2, 32, 9, 9)),
+            "tc_conv_1x1_nobiprec": ("conv", dict(cin=16, cout=16, k=1, stride=1, pad=0, bias=True, biprec=False, bits_grad=8), (3, 16, 5, 5)),
+            "tc_conv_64": ("conv", dict(cin=64, cout=64, k=3, stride=1, pad=1, bias=False, biprec=True, bits_grad=8), (2, 64, 14, 14)),
+            "tc_linear": ("lin", dict(cin=64, cout=10, bias=True, biprec=True, bits_grad=8), (6, 64)),
+            "tc_linear_nograd": ("lin", dict(cin=32, cout=24, bias=True, biprec=True, bits_grad=None), (5, 32))}
+
+
+def build_tc(ns, tag):
+    kind, c, _ = TC_CASES[tag]
+    if kind == "conv":
+        return ns.QConv2d(c["cin"], c["cout"], c["k"], stride=c["stride"], padding=c["pad"], bias=c["bias"], num_bits_grad=c["bits_grad"],
+                          biprecision=c["biprec"])
+    return ns.QLinear(c["cin"], c["cout"], bias=c["bias"], num_bits_grad=c["bits_grad"], biprecision=c["biprec"])
+
+
+def gen_modules_tc(r2):
+    """Shapes the tensor-core kernels take (C_in % 16 == 0): quantize2.QConv2d / QLinear fwd + bwd with recorded noise."""
+    g = torch.Generator().manual_seed(29)
+    d = {}
+    for i, (tag, (_, _, shape)) in enumerate(TC_CASES.items()):
+        torch.manual_seed(100 + i)
+        m = build_tc(r2, tag).train()
+        x = torch.randn(shape, generator=g, requires_grad=True)
+        log = []
+        with ref_import.record_uniform(log):
+            out = m(x)
+            go = torch.randn(out.shape, generator=g) * 1e-2
+            out.backward(go)
+        d[tag + "_w"] = m.weight
+        if m.bias is not None:
+            d[tag + "_b"], d[tag + "_db"] = m.bias, m.bias.grad
+        d[tag + "_x"], d[tag + "_out"], d[tag + "_go"], d[tag + "_dx"], d[tag + "_dw"] = x, out, go, x.grad, m.weight.grad
+        d[tag + "_nnoise"] = len(log)
+        for k, n in enumerate(log):
+            d["%s_noise%d" % (tag, k)] = n
+        d[tag + "_zp"], d[tag + "_rng"] = m.quantize_input.running_zero_point, m.quantize_input.running_range
+    save("q2_modules_tc.npz", d)
+
+
 def gen_rangebn(r2):
     g = torch.Generator().manual_seed(24)
     d = {}
@@ -153,4 +193,5 @@ if __name__ == "__main__":
     gen_grad(r2)
     gen_measure(r2)
     gen_modules(r2)
+    gen_modules_tc(r2)
     gen_rangebn(r2)

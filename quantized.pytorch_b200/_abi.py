@@ -58,6 +58,7 @@ PROTOTYPES = {
     "qb_rangebn_bwd_apply_nhwc": (_i32, [_p, _p, _i64, _i64, _i64, _i32, _p, _p, _p, _p, _p, _p, _p]),
     "qb_rowsum_u8": (_i32, [_p, _i64, _i64, _p, _p]),
     "qb_fakequant2": (_i32, [_p, _p, _i64, _i64, _p, _p, _i32, _i32, _i32, _i32, _p, _i32, _u64, _u64, _p, _p]),
+    "qb_fakequant2_codes": (_i32, [_p, _p, _p, _p, _i64, _p, _p, _i32, _p]),
     "qb_row_minmax": (_i32, [_p, _i64, _i64, _p, _p, _p]),
     "qb_rangebn2_finalize": (_i32, [_p, _i64, _i32, _dbl, _dbl, _flt, _dbl, _i32, _p, _p, _p, _p, _p, _p, _p]),
     "qb_rangebn2_apply": (_i32, [_p, _p, _i64, _i64, _i64, _i32, _p, _p, _p, _p, _p]),
@@ -82,6 +83,9 @@ PROTOTYPES = {
     "qb_conv_dw_fwd": (_i32, [_p, _p, _p, _i64, _i64, _i64, _i64, _i32, _i32, _i32, _i32, _p, _i32, _p, _p, _i32, _p, _p, _p,
                               _sz, _p]),
     "qb_bwd_pack": (_i32, [_p, _i64, _p, _p, _p, _i32, _p, _p, _i32, _u64, _u64, _p, _p]),
+    "qb_conv_generic_fwd": (_i32, [_p, _p, _p, _p, _i64, _i64, _i64, _i64, _i64, _p, _p, _p, _p]),
+    "qb_conv_generic_dgrad": (_i32, [_p, _p, _p, _i64, _i64, _i64, _i64, _i64, _p, _p, _p, _p]),
+    "qb_conv_generic_wgrad": (_i32, [_p, _p, _p, _p, _i64, _i64, _i64, _i64, _i64, _p, _p, _p, _p]),
     "qb_debug_umma_shift": (_i32, [_p, _p, _p, _i32, _i32, _i32, _p]),
     "qb_wt_pack": (_i32, [_p, _p, _i64, _i64, _i32, _p]),
     "qb_conv_dgrad": (_i32, [_p, _p, _p, _p, _i64, _i64, _i64, _i64, _i64, _i32, _i32, _i32, _i32, _p, _i32, _flt, _p]),
@@ -676,6 +680,81 @@ def conv_wgrad(g_hi, g_lo, g_f32, x16, Cout, kh, kw, stride, pad, a_range, a_bit
     return dw, db
 
 
+# ----------------------------------------------------------------------------------------------
+# generic direct convolution / linear (conv_generic.cu): every geometry the tensor-core kernels do not take
+# ----------------------------------------------------------------------------------------------
+def _gc_args(x_like, o_like, conv):
+    """conv: (stride, padding, dilation, groups) with 2-tuples, or None for a linear layer."""
+    def st4(t):
+        if t.dim() == 4:
+            return (C.c_int64 * 4)(*t.stride())
+        return (C.c_int64 * 4)(t.stride(0), t.stride(1), 0, 0)
+    return st4(x_like), st4(o_like)
+
+
+def _gc_conv(w, conv):
+    kh, kw = (w.shape[2], w.shape[3]) if w.dim() == 4 else (1, 1)
+    if conv is None:
+        return (C.c_int * 9)(1, 1, 1, 1, 0, 0, 1, 1, 1)
+    (sh, sw), (ph, pw), (dh, dw), groups = conv
+    return (C.c_int * 9)(kh, kw, sh, sw, ph, pw, dh, dw, groups)
+
+
+def conv_generic_fwd(x, w, bias, conv):
+    """F.conv2d(x, w, bias, *conv) / F.linear(x, w, bias) (conv=None; x [M, K]) on the native direct kernel."""
+    x = _f32c(x, "x") if x.dim() == 4 else (x if x.is_contiguous() else x.contiguous())
+    w = w if w.is_contiguous() else w.contiguous()
+    if x.dim() == 4:
+        B, Cin, H, W = x.shape
+        (sh, sw), (ph, pw), (dh, dw), groups = conv
+        Ho = (H + 2 * ph - dh * (w.shape[2] - 1) - 1) // sh + 1
+        Wo = (W + 2 * pw - dw * (w.shape[3] - 1) - 1) // sw + 1
+        out = torch.empty((B, w.shape[0], Ho, Wo), dtype=torch.float32, device=x.device,
+                          memory_format=torch.channels_last if is_nhwc(x) else torch.contiguous_format)
+    else:
+        (B, Cin), H, W = x.shape, 1, 1
+        out = torch.empty((B, w.shape[0]), dtype=torch.float32, device=x.device)
+    xs, os_ = _gc_args(x, out, conv)
+    _run("qb_conv_generic_fwd", 4 * (x.numel() + w.numel() + out.numel()), _ptr(x), _ptr(w), _ptr(bias), _ptr(out), B, Cin, H, W,
+         w.shape[0], _gc_conv(w, conv), xs, os_, _stream())
+    return out
+
+
+def conv_generic_dgrad(g, w, x_shape, conv, like=None):
+    g = g if (g.is_contiguous() or (g.dim() == 4 and g.is_contiguous(memory_format=torch.channels_last))) else g.contiguous()
+    w = w if w.is_contiguous() else w.contiguous()
+    nhwc = like is not None and like.dim() == 4 and is_nhwc(like)
+    if len(x_shape) == 4:
+        B, Cin, H, W = x_shape
+        dx = torch.empty(tuple(x_shape), dtype=torch.float32, device=g.device,
+                         memory_format=torch.channels_last if nhwc else torch.contiguous_format)
+    else:
+        (B, Cin), H, W = x_shape, 1, 1
+        dx = torch.empty(tuple(x_shape), dtype=torch.float32, device=g.device)
+    xs, os_ = _gc_args(dx, g, conv)
+    _run("qb_conv_generic_dgrad", 4 * (g.numel() + w.numel() + dx.numel()), _ptr(g), _ptr(w), _ptr(dx), B, Cin, H, W, w.shape[0],
+         _gc_conv(w, conv), xs, os_, _stream())
+    return dx
+
+
+def conv_generic_wgrad(g, x, w_shape, conv, want_w=True, want_bias=False):
+    g = g if (g.is_contiguous() or (g.dim() == 4 and g.is_contiguous(memory_format=torch.channels_last))) else g.contiguous()
+    x = x if (x.is_contiguous() or (x.dim() == 4 and x.is_contiguous(memory_format=torch.channels_last))) else x.contiguous()
+    dw = torch.empty(tuple(w_shape), dtype=torch.float32, device=g.device) if want_w else None
+    db = torch.empty(w_shape[0], dtype=torch.float32, device=g.device) if want_bias else None
+    if x.dim() == 4:
+        B, Cin, H, W = x.shape
+    else:
+        (B, Cin), H, W = x.shape, 1, 1
+    xs, os_ = _gc_args(x, g, conv)
+    kh, kw = (w_shape[2], w_shape[3]) if len(w_shape) == 4 else (1, 1)
+    cv = (C.c_int * 9)(1, 1, 1, 1, 0, 0, 1, 1, 1) if conv is None else (C.c_int * 9)(kh, kw, conv[0][0], conv[0][1], conv[1][0], conv[1][1],
+                                                                                       conv[2][0], conv[2][1], conv[3])
+    _run("qb_conv_generic_wgrad", 4 * (g.numel() + x.numel()), _ptr(g), _ptr(x), _ptr(dw), _ptr(db), B, Cin, H, W, w_shape[0], cv, xs, os_,
+         _stream())
+    return dw, db
+
+
 def conv_stem_supported(H, W, Cin, Cout, kh, kw, stride, pad):
     return bool(load().qb_conv_stem_supported(int(H), int(W), int(Cin), int(Cout), int(kh), int(kw), int(stride), int(pad)))
 
@@ -777,6 +856,20 @@ def fakequant2(x, zero_point, rng, bits, per_row=False, signed=False, dequantize
          int(bool(signed)), int(bool(dequantize)), _ptr(noise), int(bool(stochastic)), int(seed) & (2 ** 64 - 1), 0,
          _ptr(step_dev), _stream())
     return out
+
+
+def fakequant2_codes(x, zero_point, rng, bits, codes=None, codes16=None, want_y=False):
+    """quantize2's per-tensor unsigned quantizer -> integer codes (uint8 / bf16) [+ dequantised y] (qb_fakequant2_codes)."""
+    x = _f32c(x, "x")
+    y = torch.empty_like(x) if want_y else None
+    zp = zero_point.detach().reshape(-1).contiguous().float()
+    rg = rng.detach().reshape(-1).contiguous().float()
+    if zp.numel() != 1 or rg.numel() != 1:
+        raise QB200Error("fakequant2_codes: per-tensor qparams only")
+    nb = 4 + (4 if want_y else 0) + (1 if codes is not None else 0) + (2 if codes16 is not None else 0)
+    _run("qb_fakequant2_codes", nb * x.numel(), _ptr(x), _ptr(y), _ptr(codes), _ptr(codes16), x.numel(), _ptr(zp), _ptr(rg), int(bits),
+         _stream())
+    return y
 
 
 def row_minmax(x):

@@ -110,6 +110,35 @@ extern "C" int qb_fakequant2(const float* x, float* y, int64_t rows, int64_t col
     return QB_OK;
 }
 
+// Per-tensor, unsigned, deterministic quantize2 quantizer that ALSO emits the integer codes as uint8 (operand of the int8
+// tensor-core contractions) and bf16 (operand of qb_conv_wgrad): what routes quantize2.QConv2d / QLinear onto the native
+// contractions.  y (optional) = the dequantised tensor, bit-identical to qb_fakequant2.
+__global__ void __launch_bounds__(F2_THREADS)
+k_fakequant2_codes(const float* __restrict__ x, float* __restrict__ y, uint8_t* __restrict__ codes, uint16_t* __restrict__ codes16,
+                   int64_t n, const float* __restrict__ zp, const float* __restrict__ range, int bits) {
+    const Q2Params p = make_q2(__ldg(zp), __ldg(range), bits, 0);
+    for (int64_t e = (int64_t)blockIdx.x * F2_THREADS + threadIdx.x; e < n; e += (int64_t)gridDim.x * F2_THREADS) {
+        const float q = q2_one(x[e], 0.f, false, false, p);
+        if (y) y[e] = __fadd_rn(__fmul_rn(q, p.scale), p.add_out);
+        if (codes) codes[e] = (uint8_t)q;
+        if (codes16) codes16[e] = (uint16_t)(__float_as_uint(q) >> 16);
+    }
+}
+
+extern "C" int qb_fakequant2_codes(const float* x, float* y, uint8_t* codes, uint16_t* codes16, int64_t n, const float* zero_point,
+                                   const float* range, int bits, void* stream) {
+    QB_CHECK_ARG(n >= 0, "qb_fakequant2_codes: n=%lld", (long long)n);
+    if (n == 0) return QB_OK;
+    QB_CHECK_ARG(x && zero_point && range && (y || codes || codes16), "qb_fakequant2_codes: null pointer");
+    QB_CHECK_ARG(bits >= 1 && bits <= 8, "qb_fakequant2_codes: 8-bit codes need bits<=8 (bits=%d)", bits);
+    int sms = qb_sm_count();
+    if (sms <= 0) sms = 148;
+    int64_t want = (n + F2_THREADS - 1) / F2_THREADS, cap = (int64_t)sms * 16;
+    k_fakequant2_codes<<<(int)(want < cap ? want : cap), F2_THREADS, 0, qb_stream(stream)>>>(x, y, codes, codes16, n, zero_point, range, bits);
+    QB_LAUNCH_CHECK();
+    return QB_OK;
+}
+
 // ---------------------------------------------------------------------------------------------------
 // per-row min / max (calculate_qparams with flatten_dims=(1,-1), quantize2.py:19-28): one CTA per row
 // ---------------------------------------------------------------------------------------------------

@@ -326,10 +326,15 @@ class _QContraction(Function):
         ctx.grad_quantizer = grad_quantizer          # quantize2 flavour: callable(g) -> Q(g); None = quantize.py's
         ctx.has_bias = b is not None
         ctx.save_for_backward(x, w)
-        if conv is None:
-            return F.linear(x, w, b)
-        stride, padding, dilation, groups = conv
-        return F.conv2d(x, w, b, stride, padding, dilation, groups)
+        if ALLOW_LIBRARY_FALLBACK or not x.is_cuda:
+            if conv is None:
+                return F.linear(x, w, b)
+            stride, padding, dilation, groups = conv
+            return F.conv2d(x, w, b, stride, padding, dilation, groups)
+        # no tensor-core kernel for this geometry: the native direct kernels (conv_generic.cu), never cuDNN / cuBLAS
+        if conv is None and x.dim() != 2:
+            return _abi.conv_generic_fwd(x.reshape(-1, x.shape[-1]), w, b, None).reshape(x.shape[:-1] + (w.shape[0],))
+        return _abi.conv_generic_fwd(x, w, b, conv)
 
     @staticmethod
     def backward(ctx, g):
@@ -348,6 +353,20 @@ def _contraction_backward(ctx, g, x, w):
     g_param = gq if ctx.grad_mode == "quant" else g          # weight / bias branch
     g_input = g if ctx.grad_mode == "full" else gq           # input branch
     dx = dw = db = None
+    if g.is_cuda and not ALLOW_LIBRARY_FALLBACK and not (
+            ctx.conv is not None and USE_DW_KERNEL and ctx.conv[3] > 1 and ctx.conv[3] == x.shape[1] and ctx.conv[2] == (1, 1)
+            and ctx.conv[0][0] == ctx.conv[0][1] and ctx.conv[1][0] == ctx.conv[1][1]
+            and _abi.conv_dw_bwd_supported(g, x, w, ctx.conv[0][0], ctx.conv[1][0])):
+        # native direct kernels for the geometries without a tensor-core / depthwise kernel (conv_generic.cu)
+        if ctx.conv is None and x.dim() != 2:
+            x2, gi2, gp2 = x.reshape(-1, x.shape[-1]), g_input.reshape(-1, w.shape[0]), g_param.reshape(-1, w.shape[0])
+        else:
+            x2, gi2, gp2 = x, g_input, g_param
+        if need_x:
+            dx = _abi.conv_generic_dgrad(gi2, w, tuple(x2.shape), ctx.conv, like=x2).reshape(x.shape)
+        if need_w or need_b:
+            dw, db = _abi.conv_generic_wgrad(gp2, x2, tuple(w.shape), ctx.conv, want_w=bool(need_w), want_bias=bool(need_b))
+        return dx, dw, db
     if ctx.conv is None:
         if need_x:
             dx = g_input.matmul(w)
@@ -573,7 +592,8 @@ class _QBase(QuantNode):
 USE_INT8_TENSOR_CORES = True
 USE_NATIVE_BACKWARD = True    # dX / dW / db of the dense contractions on conv_bwd.cu (tcgen05 bf16) instead of cuDNN / cuBLAS
 # The reference's F.conv2d / F.linear on the fake-quantized tensors (cuDNN / cuBLAS) is NOT a product path: a geometry the
-# native kernels do not take raises QB200Error unless a test sets this flag to compare against the library.
+# tensor-core kernels do not take runs on the native direct kernels (conv_generic.cu).  Tests set this flag to compare against
+# the library.
 ALLOW_LIBRARY_FALLBACK = False
 USE_STEM_KERNEL = True
 USE_DW_KERNEL = True       # depthwise 3x3 convs on the codes (conv_dw.cu); False: F.conv2d on the fake-quantized tensors
@@ -643,20 +663,23 @@ class _QTensorCoreFn(Function):
         need_bwd = any(ctx.needs_input_grad[:3])
         x = _abi._f32c(input, "input")
         bits_a, bits_w = mod.num_bits, mod.num_bits_weight
-        update = not mod.freeze_param_dyn_range
+        update = not getattr(mod, "freeze_param_dyn_range", False)
         codes = torch.empty_like(x, dtype=torch.uint8)                      # same memory format as x
         # first layer whose input needs no gradient: the weight gradient is taken from the codes (conv_stem.cu)
         stem_bwd = (conv and USE_STEM_KERNEL and x.shape[1] % 32 != 0 and not ctx.needs_input_grad[0]
-                    and mod.out_channels in (32, 64) and mod.kernel_size[0] == 7)
+                    and mod.out_channels in (32, 64) and mod.kernel_size[0] in (3, 7)
+                    and mod.kernel_size[0] == mod.kernel_size[1])
         dense = not conv or (mod.groups == 1 and x.shape[1] % 16 == 0)
         native_bwd = need_bwd and dense and _native_bwd_supported(mod, x)
-        if need_bwd and dense and not native_bwd and not stem_bwd and not ALLOW_LIBRARY_FALLBACK:
-            raise QB200Error("no native backward kernel for this geometry (%r); set quantize.ALLOW_LIBRARY_FALLBACK to "
-                             "route it to cuDNN / cuBLAS for a comparison" % (mod,))
         want_x16 = native_bwd and ctx.needs_input_grad[1]
         x16 = torch.empty_like(x, dtype=torch.bfloat16) if want_x16 else None
-        xq = _abi.fakequant_affine(x, bits_a, range_dev=rng, codes=codes, codes16=x16,
-                                   want_y=need_bwd and not stem_bwd and not native_bwd)
+        q2 = getattr(mod, "_q2_params", None)        # quantize2 flavour: (zero_point, range) device tensors of its quantizer
+        if q2 is not None:
+            xq = _abi.fakequant2_codes(x, q2[0], q2[1], bits_a, codes=codes, codes16=x16,
+                                       want_y=need_bwd and not stem_bwd and not native_bwd)
+        else:
+            xq = _abi.fakequant_affine(x, bits_a, range_dev=rng, codes=codes, codes16=x16,
+                                       want_y=need_bwd and not stem_bwd and not native_bwd)
         w4 = weight if conv else weight.view(weight.shape[0], weight.shape[1], 1, 1)
         wq, wcodes, tapsum = _abi.fakequant_rows_conv(w4, bits_w, mod.weight_min, mod.weight_max, compute_range=update,
                                                       want_y=need_bwd)

@@ -224,6 +224,57 @@ class QuantMeasure(nn.Module, QuantNode):
         return quantize(input, qparams=qparams, dequantize=self.dequantize, stochastic=self.stochastic, inplace=self.inplace)
 
 
+def _tc_route(mod, input):
+    """quantize2.QConv2d / QLinear on the native tensor-core contractions (row A9): possible when the input quantizer is the
+    plain per-tensor unsigned one (its codes are then the int8 operand) and the geometry is one quantize.py's kernels take."""
+    qi = mod.quantize_input
+    if not (_q1.USE_INT8_TENSOR_CORES and input.is_cuda and input.dtype == torch.float32 and qi.dequantize and not qi.stochastic
+            and not qi.measure and qi.num_bits <= 8 and mod.num_bits_weight <= 8 and tuple(qi.running_range.shape) in ((1, 1, 1, 1), (1,))
+            and not getattr(qi, "inplace", False)):
+        return False
+    if isinstance(mod, nn.Conv2d):
+        return input.dim() == 4 and mod.groups == 1 and _q1._conv_i8_supported(mod, input) and mod.in_channels % 16 == 0
+    return input.dim() == 2 and mod.in_features % 16 == 0
+
+
+def _tc_forward(mod, input, conv):
+    """The input quantizer's bookkeeping (QuantMeasure.forward, quantize2.py:176-196), then quantize._QTensorCoreFn on its
+    (zero_point, range): activation codes by qb_fakequant2_codes, weights per row (quantize2.py:225-226 is the same affine
+    quantizer as quantize.py:318-334), int8 tcgen05 forward, native backward with this flavour's gradient quantizer."""
+    qi = mod.quantize_input
+    x = input
+    if conv is not None and _q1.CHANNELS_LAST and not x.is_contiguous(memory_format=torch.channels_last):
+        x = x.contiguous(memory_format=torch.channels_last)
+    if qi.training:
+        qp = calculate_qparams(x, num_bits=qi.num_bits, flatten_dims=qi.flatten_dims, reduce_dim=0)
+        with torch.no_grad():
+            qi.running_zero_point.mul_(qi.momentum).add_(qp.zero_point * (1 - qi.momentum))
+            qi.running_range.mul_(qi.momentum).add_(qp.range * (1 - qi.momentum))
+        zp, rg = qp.zero_point, qp.range
+    else:
+        zp, rg = qi.running_zero_point, qi.running_range
+    zp, rg = zp.detach().reshape(1).float(), rg.detach().reshape(1).float()
+    qbias = None
+    if mod.bias is not None:
+        qbias = quantize(mod.bias, num_bits=mod.num_bits_weight + mod.num_bits, flatten_dims=(0, -1))
+    n = mod.weight.shape[0]
+    mod._q2_params = (zp, rg)
+    mod.weight_min = torch.empty(n, dtype=torch.float32, device=x.device)      # scratch of the row kernel (not buffers here)
+    mod.weight_max = torch.empty(n, dtype=torch.float32, device=x.device)
+    fd = (1, -1) if conv is not None else _DEFAULT_FLATTEN_GRAD
+    mod._grad_quantizer = _grad_quantizer(mod.num_bits_grad, fd) if mod.num_bits_grad is not None else None
+    try:
+        return _q1._QTensorCoreFn.apply(x, mod.weight, qbias, mod, torch.cat([zp, zp + rg]))
+    finally:
+        del mod._q2_params, mod.weight_min, mod.weight_max
+
+
+def _q2_grad_mode(mod):
+    if mod.num_bits_grad is None:
+        return "full"
+    return "biprec" if mod.biprecision else "quant"
+
+
 def _contract(mod, qinput, qweight, qbias, conv):
     """Shared tail of QConv2d / QLinear forward (:225-234, :261-268)."""
     fd = (1, -1) if conv is not None else _DEFAULT_FLATTEN_GRAD
@@ -246,14 +297,19 @@ class QConv2d(nn.Conv2d):
         self.quantize_input = QuantMeasure(self.num_bits, shape_measure=(1, 1, 1, 1), flatten_dims=(1, -1))
         self.biprecision = biprecision
 
+    def _grad_mode(self):
+        return _q2_grad_mode(self)
+
     def forward(self, input):
+        conv = (_q1._pair(self.stride), _q1._pair(self.padding), _q1._pair(self.dilation), self.groups)
+        if _tc_route(self, input):
+            return _tc_forward(self, input, conv)
         qinput = self.quantize_input(input)
         weight_qparams = calculate_qparams(self.weight, num_bits=self.num_bits_weight, flatten_dims=(1, -1), reduce_dim=None)
         qweight = quantize(self.weight, qparams=weight_qparams)
         qbias = None
         if self.bias is not None:
             qbias = quantize(self.bias, num_bits=self.num_bits_weight + self.num_bits, flatten_dims=(0, -1))
-        conv = (_q1._pair(self.stride), _q1._pair(self.padding), _q1._pair(self.dilation), self.groups)
         return _contract(self, qinput, qweight, qbias, conv)
 
 
@@ -269,7 +325,12 @@ class QLinear(nn.Linear):
         self.biprecision = biprecision
         self.quantize_input = QuantMeasure(self.num_bits)
 
+    def _grad_mode(self):
+        return _q2_grad_mode(self)
+
     def forward(self, input):
+        if _tc_route(self, input):
+            return _tc_forward(self, input, None)
         qinput = self.quantize_input(input)
         weight_qparams = calculate_qparams(self.weight, num_bits=self.num_bits_weight, flatten_dims=(1, -1), reduce_dim=None)
         qweight = quantize(self.weight, qparams=weight_qparams)

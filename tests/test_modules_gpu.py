@@ -176,12 +176,21 @@ def test_contract_golden(tag):
     g = golden("contract.npz")
     m = build_contract(Q, tag, g).to(DEV)
     x = T(g[tag + "_x"]).to(DEV).requires_grad_()
+    from qtorch_b200 import _abi
     prev = Q.set_noise_provider(CudaReplay([T(g[tag + "_noise"])]))
     try:
+        _abi.profile_begin()
         out = m(x)
         out.backward(T(g[tag + "_go"]).to(DEV))
+        names = [r[0] for r in _abi.profile_end()]
     finally:
         Q.set_noise_provider(prev)
+    # the contraction and both of its gradients ran on the library's own kernels (these tiny odd channel counts take the
+    # direct kernels of conv_generic.cu, the depthwise one conv_dw.cu) - no cuDNN / cuBLAS route exists
+    fwd = {"qb_conv_generic_fwd", "qb_conv_i8_fwd", "qb_gemm_i8", "qb_conv_dw_fwd", "qb_conv_stem_fwd"}
+    bwd = {"qb_conv_generic_dgrad", "qb_conv_dgrad", "qb_conv_dw_dgrad"}
+    wgr = {"qb_conv_generic_wgrad", "qb_conv_wgrad", "qb_conv_dw_wgrad", "qb_conv_stem_wgrad"}
+    assert fwd & set(names) and bwd & set(names) and wgr & set(names), names
     # north_star: dequantised GEMM/conv outputs within 1e-4 relative L2 of the fp32 reference
     assert rel_l2(out, g[tag + "_out"]) < 1e-4
     assert rel_l2(x.grad, g[tag + "_dx"]) < 1e-4

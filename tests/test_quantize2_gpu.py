@@ -165,6 +165,42 @@ def test_modules2(tag):
     assert torch.allclose(m.quantize_input.running_range.cpu(), T(g[tag + "_rng"]), rtol=3e-7, atol=0)
 
 
+@pytest.mark.parametrize("tag", ["tc_conv", "tc_conv_s2_nobias", "tc_conv_1x1_nobiprec", "tc_conv_64", "tc_linear", "tc_linear_nograd"])
+def test_modules2_on_tensor_cores(tag):
+    """quantize2.QConv2d / QLinear (quantize2.py:204-272) on the SAME native contractions as quantize.py's
+    modules - int8 tcgen05 forward on the codes of this flavour's quantizer, qb_conv_dgrad / qb_conv_wgrad backward with its
+    per-sample 'extreme' gradient quantizer - against goldens from the unmodified reference (oracle/gen_golden2.py)."""
+    Q2 = q2()
+    from oracle.gen_golden2 import TC_CASES, build_tc
+    from qtorch_b200 import _abi, quantize as Q
+    g = golden("q2_modules_tc.npz")
+    kind, cfg, _ = TC_CASES[tag]
+    m = build_tc(Q2, tag)
+    with torch.no_grad():
+        m.weight.copy_(T(g[tag + "_w"]))
+        if m.bias is not None:
+            m.bias.copy_(T(g[tag + "_b"]))
+    m = m.to(DEV).train()
+    x = T(g[tag + "_x"]).to(DEV).requires_grad_()
+    prev = Q.set_noise_provider(Replay([T(g["%s_noise%d" % (tag, k)]) for k in range(int(g[tag + "_nnoise"]))]))
+    try:
+        _abi.profile_begin()
+        out = m(x)
+        out.backward(T(g[tag + "_go"]).to(DEV))
+        names = [r[0] for r in _abi.profile_end()]
+    finally:
+        Q.set_noise_provider(prev)
+    assert ("qb_conv_i8_fwd" if kind == "conv" else "qb_gemm_i8") in names, names
+    assert "qb_conv_dgrad" in names and "qb_conv_wgrad" in names and "qb_fakequant2_codes" in names, names
+    assert rel_l2(out, g[tag + "_out"]) < 1e-4
+    assert rel_l2(x.grad, g[tag + "_dx"]) < 2e-3         # a 1-ulp input range moves a few activation codes by one step
+    assert rel_l2(m.weight.grad, g[tag + "_dw"]) < 2e-3
+    if m.bias is not None:
+        assert rel_l2(m.bias.grad, g[tag + "_db"]) < 1e-5
+    assert torch.allclose(m.quantize_input.running_zero_point.cpu(), T(g[tag + "_zp"]), rtol=3e-7, atol=1e-9)
+    assert torch.allclose(m.quantize_input.running_range.cpu(), T(g[tag + "_rng"]), rtol=3e-7, atol=0)
+
+
 @pytest.mark.parametrize("tag,chunks", [("4d", 4), ("2d", 8)])
 @pytest.mark.parametrize("nhwc", [False, True])
 def test_rangebn2(tag, chunks, nhwc):
