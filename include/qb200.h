@@ -392,6 +392,16 @@ int qb_wt_pack(const float* w_hat, uint16_t* wt, int64_t Cout, int64_t Cin, int 
 int qb_conv_dgrad(const uint16_t* a0, const uint16_t* a1, const uint16_t* wt, float* dx, int64_t B, int64_t H, int64_t W,
                   int64_t Cin, int64_t Cout, int kh, int kw, int stride, int pad, const float* scale_range, int scale_bits,
                   float scale_mul, void* stream);
+/* Weight gradient of the FIRST layer (3 input channels; 7x7/stride 2/pad 3 or 3x3/stride 2/pad 1, even W) on the qb_conv_wgrad
+ * kernel: the uint8 input codes [B,H,W,3] are expanded to zero-padded 4-channel bf16 and read through an OVERLAPPING tensor
+ * map as a virtual operand whose "channels" are a filter row's window (conv_bwd.cu).  g_hi / g_lo: bf16 planes of the output
+ * gradient [B,Ho,Wo,C_out]; dw fp32 [C_out][3][k][k] = sa * SUM g*q + la * SUM_{tap in bounds} g.  ws_bytes() == 0: geometry
+ * not taken (qb_conv_stem_wgrad remains). */
+size_t qb_conv_stem_wgrad16_ws_bytes(int64_t B, int64_t H, int64_t W, int64_t Cout, int k, int stride, int pad);
+int qb_conv_stem_wgrad16(const uint16_t* g_hi, const uint16_t* g_lo, const uint8_t* x_codes, float* dw, int64_t B, int64_t H, int64_t W,
+                         int64_t Cout, int k, int stride, int pad, const float* a_range, int a_bits, void* ws, size_t ws_bytes,
+                         void* stream);
+
 /* Direct convolution / linear kernels for every geometry the tensor-core kernels do not take (conv_generic.cu): the
  * reference's F.conv2d(x_hat, w_hat, b_hat) / F.linear and their gradients (models/modules/quantize.py:142-156, 343, 424) on
  * the fake-quantized fp32 tensors, CUDA cores, fp64 accumulation, deterministic.  They keep EVERY quantized layer off cuDNN /
@@ -403,6 +413,20 @@ int qb_conv_generic_dgrad(const float* grad_out, const float* w, float* dx, int6
                           const int* conv, const int64_t* x_strides, const int64_t* o_strides, void* stream);
 int qb_conv_generic_wgrad(const float* grad_out, const float* x, float* dw, float* db, int64_t B, int64_t Cin, int64_t H, int64_t W,
                           int64_t Cout, const int* conv, const int64_t* x_strides, const int64_t* o_strides, void* stream);
+/* Optimizer / regulariser glue of the training step as multi-tensor kernels (glue_opt.cu; SURVEY.md section 8f N1;
+ * main.py:362-380, models/resnet_quantized.py:157-165).  Up to 96 fp32 tensors per call, passed as arrays of pointers and
+ * element counts.
+ *   qb_l2_sumsq: out[0] (= or +=) 0.5 * wd * SUM_t SUM_i w_t[i]^2 (fp64 accumulation, fixed order); ws: qb_mt_ws_bytes().
+ *   qb_l2_grad : grad_t = (upstream[0] * wd) * w_t (upstream NULL = 1).
+ *   qb_sgd_step: torch.optim.SGD step (dampening 0, no Nesterov): g' = g + wd*p; buf = first ? g' : buf*momentum + g';
+ *                p -= lr*buf, every operation rounded as torch's kernels round it. */
+size_t qb_mt_ws_bytes(int count, const int64_t* sizes);
+int qb_l2_sumsq(const void* const* w, const int64_t* sizes, int count, double weight_decay, float* out, int accumulate, void* ws,
+                size_t ws_bytes, void* stream);
+int qb_l2_grad(const void* const* w, void* const* grad, const int64_t* sizes, int count, double weight_decay, const float* upstream,
+               void* stream);
+int qb_sgd_step(const void* const* grad, void* const* param, void* const* buf, const int64_t* sizes, int count, double lr,
+                double momentum, double weight_decay, int first, void* stream);
 /* Hardware probe used by tools/umma_shift_probe.py (UMMA descriptors that start inside an 8-row swizzle atom); not on any
  * product path. */
 int qb_debug_umma_shift(const uint16_t* a, const uint16_t* b, float* out, int mn, int r0, int use_boff, void* stream);

@@ -83,9 +83,15 @@ PROTOTYPES = {
     "qb_conv_dw_fwd": (_i32, [_p, _p, _p, _i64, _i64, _i64, _i64, _i32, _i32, _i32, _i32, _p, _i32, _p, _p, _i32, _p, _p, _p,
                               _sz, _p]),
     "qb_bwd_pack": (_i32, [_p, _i64, _p, _p, _p, _i32, _p, _p, _i32, _u64, _u64, _p, _p]),
+    "qb_conv_stem_wgrad16_ws_bytes": (_sz, [_i64, _i64, _i64, _i64, _i32, _i32, _i32]),
+    "qb_conv_stem_wgrad16": (_i32, [_p, _p, _p, _p, _i64, _i64, _i64, _i64, _i32, _i32, _i32, _p, _i32, _p, _sz, _p]),
     "qb_conv_generic_fwd": (_i32, [_p, _p, _p, _p, _i64, _i64, _i64, _i64, _i64, _p, _p, _p, _p]),
     "qb_conv_generic_dgrad": (_i32, [_p, _p, _p, _i64, _i64, _i64, _i64, _i64, _p, _p, _p, _p]),
     "qb_conv_generic_wgrad": (_i32, [_p, _p, _p, _p, _i64, _i64, _i64, _i64, _i64, _p, _p, _p, _p]),
+    "qb_mt_ws_bytes": (_sz, [_i32, _p]),
+    "qb_l2_sumsq": (_i32, [_p, _p, _i32, _dbl, _p, _i32, _p, _sz, _p]),
+    "qb_l2_grad": (_i32, [_p, _p, _p, _i32, _dbl, _p, _p]),
+    "qb_sgd_step": (_i32, [_p, _p, _p, _p, _i32, _dbl, _dbl, _dbl, _i32, _p]),
     "qb_debug_umma_shift": (_i32, [_p, _p, _p, _i32, _i32, _i32, _p]),
     "qb_wt_pack": (_i32, [_p, _p, _i64, _i64, _i32, _p]),
     "qb_conv_dgrad": (_i32, [_p, _p, _p, _p, _i64, _i64, _i64, _i64, _i64, _i32, _i32, _i32, _i32, _p, _i32, _flt, _p]),
@@ -654,8 +660,7 @@ def conv_dgrad(a0, a1, wt, x_shape, Cout, kh, kw, stride, pad, scale_range=None,
     dx = torch.empty((B, Cin, H, W), dtype=torch.float32, device=a0.device, memory_format=torch.channels_last)
     Ho, Wo = (H + 2 * pad - kh) // stride + 1, (W + 2 * pad - kw) // stride + 1
     global _next_ops
-    planes = 2 if a1 is None else 3
-    _next_ops = 2 * B * Ho * Wo * Cout * kh * kw * Cin * planes
+    _next_ops = 2 * B * Ho * Wo * Cout * kh * kw * Cin          # useful operations (the kernel executes 2-3 bf16 planes of them)
     _NLAUNCH["qb_conv_dgrad"] = stride * stride if kh >= stride else 1
     _run("qb_conv_dgrad", (2 if a1 is None else 4) * a0.numel() + 4 * Cout * Cin * kh * kw + 4 * dx.numel(), _ptr(a0), _ptr(a1),
          _ptr(wt), _ptr(dx), B, H, W, Cin, Cout, kh, kw, stride, pad, _ptr(scale_range), int(scale_bits), float(scale_mul),
@@ -673,7 +678,7 @@ def conv_wgrad(g_hi, g_lo, g_f32, x16, Cout, kh, kw, stride, pad, a_range, a_bit
         raise QB200Error("conv_wgrad: unsupported geometry Cin=%d Cout=%d k=%dx%d stride=%d" % (Cin, Cout, kh, kw, stride))
     ws = workspace("conv_wgrad", nb, x16.device)
     global _next_ops
-    _next_ops = 2 * g_hi.numel() * kh * kw * Cin * (2 if g_lo is not None else 1)
+    _next_ops = 2 * g_hi.numel() * kh * kw * Cin                # useful operations (executed twice: hi + lo planes of g)
     _run("qb_conv_wgrad", (2 if g_lo is None else 4) * g_hi.numel() + 2 * x16.numel() + 4 * dw.numel(), _ptr(g_hi), _ptr(g_lo),
          _ptr(g_f32), _ptr(x16), _ptr(dw), _ptr(db), B, H, W, Cin, Cout, kh, kw, stride, pad, _ptr(a_range), int(a_bits), _ptr(ws),
          ws.numel(), _stream())
@@ -789,6 +794,26 @@ def conv_stem_wgrad(grad_out, x_codes, a_range, a_bits, Cout, kh, kw, stride, pa
     return dw
 
 
+def conv_stem_wgrad16_supported(B, H, W, Cout, k, stride, pad):
+    return load().qb_conv_stem_wgrad16_ws_bytes(B, H, W, Cout, k, stride, pad) > 0
+
+
+def conv_stem_wgrad16(g_hi, g_lo, x_codes, a_range, a_bits, Cout, k, stride, pad):
+    """First-layer weight gradient on the bf16 wgrad kernel (qb_conv_stem_wgrad16) -> dw fp32 [Cout, 3, k, k]."""
+    B, Cin, H, W = x_codes.shape
+    nb = load().qb_conv_stem_wgrad16_ws_bytes(B, H, W, Cout, k, stride, pad)
+    if nb == 0 or Cin != 3:
+        raise QB200Error("conv_stem_wgrad16: unsupported geometry")
+    ws = workspace("conv_stem_wgrad16", nb, x_codes.device)
+    dw = torch.empty((Cout, 3, k, k), dtype=torch.float32, device=x_codes.device)
+    global _next_ops
+    _next_ops = 2 * g_hi.numel() * k * k * 3
+    _NLAUNCH["qb_conv_stem_wgrad16"] = 3
+    _run("qb_conv_stem_wgrad16", 4 * g_hi.numel() + x_codes.numel(), _ptr(g_hi), _ptr(g_lo), _ptr(x_codes), _ptr(dw), B, H, W, Cout, int(k),
+         int(stride), int(pad), _ptr(a_range), int(a_bits), _ptr(ws), ws.numel(), _stream())
+    return dw
+
+
 def allreduce_small(t, mode, peer_ptrs, rank, world, slot_bytes):
     """In-place one-shot all-reduce of a small contiguous double / float tensor over peer memory (qb_allreduce_small)."""
     if t.dtype == torch.float64:
@@ -834,6 +859,60 @@ def maxpool2d_relu_nhwc_bwd(g, idx, pool_out, in_shape, k, stride, pad):
     _run("qb_maxpool2d_relu_nhwc_bwd", 9 * g.numel() + 4 * dx.numel(), _ptr(g), _ptr(idx), _ptr(pool_out), _ptr(dx), B, H, W, Cn,
          int(k), int(stride), int(pad), _ptr(rng), _ptr(ws), ws.numel(), _stream())
     return dx, rng
+
+
+# ----------------------------------------------------------------------------------------------
+# multi-tensor optimizer / regulariser glue (glue_opt.cu)
+# ----------------------------------------------------------------------------------------------
+MT_MAX = 96
+
+
+def _mt_arrays(*lists):
+    n = len(lists[0])
+    ptrs = [(C.c_void_p * n)(*[t.data_ptr() for t in lst]) if lst is not None else None for lst in lists]
+    sizes = (C.c_int64 * n)(*[t.numel() for t in lists[0]])
+    return ptrs, sizes, n
+
+
+def _mt_check(ts, name):
+    for t in ts:
+        if not (t.is_cuda and t.dtype == torch.float32 and t.is_contiguous()):
+            raise QB200Error("%s: tensors must be contiguous CUDA float32" % name)
+
+
+def l2_sumsq(tensors, weight_decay, out=None):
+    """-> device scalar 0.5 * wd * SUM w^2 over all tensors (qb_l2_sumsq; one launch pair per 96 tensors)."""
+    _mt_check(tensors, "l2_sumsq")
+    dev = tensors[0].device
+    if out is None:
+        out = torch.empty((), dtype=torch.float32, device=dev)
+    for k in range(0, len(tensors), MT_MAX):
+        (w,), sizes, n = _mt_arrays(tensors[k:k + MT_MAX])
+        ws = workspace("mt_sumsq", load().qb_mt_ws_bytes(n, sizes), dev)
+        _NLAUNCH["qb_l2_sumsq"] = 2
+        _run("qb_l2_sumsq", 4 * sum(t.numel() for t in tensors[k:k + MT_MAX]), w, sizes, n, float(weight_decay), _ptr(out), int(k > 0),
+             _ptr(ws), ws.numel(), _stream())
+    return out
+
+
+def l2_grad(tensors, weight_decay, upstream=None):
+    """-> [wd * upstream * w for w in tensors] in ONE launch per 96 tensors (qb_l2_grad)."""
+    _mt_check(tensors, "l2_grad")
+    grads = [torch.empty_like(t) for t in tensors]
+    for k in range(0, len(tensors), MT_MAX):
+        (w, g), sizes, n = _mt_arrays(tensors[k:k + MT_MAX], grads[k:k + MT_MAX])
+        _run("qb_l2_grad", 8 * sum(t.numel() for t in tensors[k:k + MT_MAX]), w, g, sizes, n, float(weight_decay), _ptr(upstream), _stream())
+    return grads
+
+
+def sgd_step(params, grads, bufs, lr, momentum, weight_decay, first):
+    """torch.optim.SGD update of every parameter in one launch per 96 tensors (qb_sgd_step)."""
+    _mt_check(params, "sgd_step")
+    _mt_check(grads, "sgd_step")
+    for k in range(0, len(params), MT_MAX):
+        (g, p, b), sizes, n = _mt_arrays(grads[k:k + MT_MAX], params[k:k + MT_MAX], bufs[k:k + MT_MAX] if bufs is not None else None)
+        _run("qb_sgd_step", 16 * sum(t.numel() for t in params[k:k + MT_MAX]), g, p, b, sizes, n, float(lr), float(momentum),
+             float(weight_decay), int(bool(first)), _stream())
 
 
 # ----------------------------------------------------------------------------------------------

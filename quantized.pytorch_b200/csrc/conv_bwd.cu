@@ -461,7 +461,10 @@ struct DflatGeom {
     FastDiv d_tiles_m, d_tiles_h;
 };
 
-template <int BN>
+// SBS: the hi and lo weight planes sit side by side on the MMA's N axis (one N = 2*BN instruction per K step instead of two
+// N = BN ones: the pixel operand is read from shared memory once, which a 64-column MMA needs to keep the tensor pipe fed);
+// the epilogue adds the two column halves.
+template <int BN, bool SBS>
 __global__ void __launch_bounds__(DG_THREADS, 1)
 k_conv_dgrad_flat(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_w,
                   const __grid_constant__ CUtensorMap tmap_o, DflatGeom g, const float* __restrict__ scale_range, int scale_bits,
@@ -488,7 +491,7 @@ k_conv_dgrad_flat(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
     const int tiles_m = g.tiles_h * g.tiles_b;
     const int tiles_n = (g.Cn + BN - 1) / BN;
     const int total = tiles_m * tiles_n;
-    constexpr uint32_t ACC = BN < 32 ? 32 : BN;
+    constexpr uint32_t ACC = SBS ? (2 * BN < 32 ? 32 : 2 * BN) : (BN < 32 ? 32 : BN);
     constexpr uint32_t TMEM_COLS = 4 * ACC;                     // 2 sets x 2 accumulators
 
     if (warp == 0 && lane == 0) {
@@ -542,7 +545,7 @@ k_conv_dgrad_flat(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
             }
         }
     } else if (warp == 1) {
-        constexpr uint32_t idesc = idesc_bf16(128, BN, 0, 0);
+        constexpr uint32_t idesc = idesc_bf16(128, SBS ? 2 * BN : BN, 0, 0);
         const int ksteps = g.BK / 16;
         uint32_t ia = 0, iw = 0;
         int it = 0;
@@ -565,7 +568,13 @@ k_conv_dgrad_flat(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
                         for (int j = 0; j < g.J; ++j) {
                             const uint64_t a_desc = desc_add(a_desc0, (uint32_t)(128 * j + g.off[tp]) * (uint32_t)rb);
                             const uint32_t dj = d0 + (uint32_t)j * ACC;
-                            if (ksteps == 4 && g.b_planes == 2) {
+                            if (SBS) {
+                                uint32_t acc = first ? 0u : 1u;
+                                for (int k = 0; k < ksteps; ++k) {
+                                    umma_f16(dj, desc_add(a_desc, k * 32), desc_add(w_desc, k * 32), idesc, acc);
+                                    acc = 1u;
+                                }
+                            } else if (ksteps == 4 && g.b_planes == 2) {
                                 umma_f16(dj, a_desc, w_desc, idesc, first ? 0u : 1u);
                                 umma_f16(dj, a_desc, desc_add(w_desc, w_plane), idesc, 1u);
 #pragma unroll
@@ -617,7 +626,15 @@ k_conv_dgrad_flat(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
                 uint32_t r[32];
                 if (j < g.J) {
                     tmem_ld_32x32(t_addr + (uint32_t)(cs * 32), r);
-                    tmem_ld_wait();
+                    if (SBS) {
+                        uint32_t r2[32];
+                        tmem_ld_32x32(t_addr + (uint32_t)(BN + cs * 32), r2);
+                        tmem_ld_wait();
+#pragma unroll
+                        for (int q = 0; q < 32; ++q) r[q] = __float_as_uint(__uint_as_float(r[q]) + __uint_as_float(r2[q]));
+                    } else {
+                        tmem_ld_wait();
+                    }
                 }
                 if (cs == nslabs - 1) {
                     tc_fence_before_sync();
@@ -653,15 +670,15 @@ k_conv_dgrad_flat(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
     if (warp == 1) tmem_dealloc<TMEM_COLS>(tmem_base);
 }
 
-template <int BN>
+template <int BN, bool SBS>
 static int dgrad_flat_launch(const CUtensorMap& ta, const CUtensorMap& tw, const CUtensorMap& to, const DflatGeom& g, size_t smem,
                              const float* scale_range, int scale_bits, float scale_mul, cudaStream_t st) {
-    QB_CUDA(cudaFuncSetAttribute(k_conv_dgrad_flat<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    QB_CUDA(cudaFuncSetAttribute(k_conv_dgrad_flat<BN, SBS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     const int64_t total = (int64_t)g.tiles_h * g.tiles_b * ((g.Cn + BN - 1) / BN);
     int sms = qb_sm_count();
     if (sms <= 0) sms = 148;
     const unsigned grid = (unsigned)(total < sms ? total : sms);
-    k_conv_dgrad_flat<BN><<<grid, DG_THREADS, smem, st>>>(ta, tw, to, g, scale_range, scale_bits, scale_mul);
+    k_conv_dgrad_flat<BN, SBS><<<grid, DG_THREADS, smem, st>>>(ta, tw, to, g, scale_range, scale_bits, scale_mul);
     QB_LAUNCH_CHECK();
     return QB_OK;
 }
@@ -678,9 +695,16 @@ static size_t dgrad_flat_geom(DflatGeom& g, int B, int Hc, int Wc, int Cn, int C
     const int halo_h = dh_max - dh_min, halo_w = dw_max - dw_min;
     g.B = B; g.Hc = Hc; g.Wc = Wc; g.Cn = Cn; g.Ck = Ck; g.BK = BK; g.ntaps = ntaps; g.b_planes = 2;
     g.dh_min = dh_min; g.dw_min = dw_min;
-    g.Wp = Wc + halo_w;
+    // Shared padding: on the flat pitch the right-hand zero columns of row y ARE the left-hand zero columns of row y+1 (and
+    // the bottom zero rows of an image the top zero rows of the next one), so the pitch only needs the larger of the two
+    // halos: Wp = Wc + max(dw_max, -dw_min) instead of Wc + (dw_max - dw_min).  49 of 64 rows are real for a 7x7 image
+    // under a 3x3 filter instead of 49 of 81.
+    auto pos = [](int v) { return v > 0 ? v : 0; };
+    const int ext_w = pos(dw_max) > pos(-dw_min) ? pos(dw_max) : pos(-dw_min);
+    const int ext_h = pos(dh_max) > pos(-dh_min) ? pos(dh_max) : pos(-dh_min);
+    g.Wp = Wc + ext_w;
     if (g.Wp > 256) return 0;
-    const int Hp = Hc + halo_h;
+    const int Hp = Hc + ext_h;
     if (Hp * g.Wp <= 256) {                      // image mode: whole padded images
         g.RH = g.RHo = Hp;
         g.TN = 256 / (Hp * g.Wp);
@@ -812,10 +836,12 @@ extern "C" int qb_conv_dgrad(const uint16_t* a0, const uint16_t* a1, const uint1
                     const uint32_t obox[4] = {32u, (uint32_t)fg.Wp, (uint32_t)fg.RHo, (uint32_t)fg.TN};
                     rc = qb_make_tmap(&fo, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, base, odims, ostr, obox, nullptr, 128);
                     if (rc) return rc;
-                    if (BN == 128) rc = dgrad_flat_launch<128>(fa, tw, fo, fg, fsmem, scale_range, scale_bits, scale_mul, st);
-                    else if (BN == 64) rc = dgrad_flat_launch<64>(fa, tw, fo, fg, fsmem, scale_range, scale_bits, scale_mul, st);
-                    else if (BN == 32) rc = dgrad_flat_launch<32>(fa, tw, fo, fg, fsmem, scale_range, scale_bits, scale_mul, st);
-                    else rc = dgrad_flat_launch<16>(fa, tw, fo, fg, fsmem, scale_range, scale_bits, scale_mul, st);
+                    static const bool sbs_off = getenv("QB_DGRAD_SBS") && getenv("QB_DGRAD_SBS")[0] == '0';
+                    if (BN == 128) rc = dgrad_flat_launch<128, false>(fa, tw, fo, fg, fsmem, scale_range, scale_bits, scale_mul, st);
+                    else if (BN == 64 && !sbs_off) rc = dgrad_flat_launch<64, true>(fa, tw, fo, fg, fsmem, scale_range, scale_bits, scale_mul, st);
+                    else if (BN == 64) rc = dgrad_flat_launch<64, false>(fa, tw, fo, fg, fsmem, scale_range, scale_bits, scale_mul, st);
+                    else if (BN == 32) rc = dgrad_flat_launch<32, true>(fa, tw, fo, fg, fsmem, scale_range, scale_bits, scale_mul, st);
+                    else rc = dgrad_flat_launch<16, true>(fa, tw, fo, fg, fsmem, scale_range, scale_bits, scale_mul, st);
                     if (rc) return rc;
                     continue;
                 }
@@ -871,7 +897,7 @@ constexpr int WG_MAX_STAGES = 8;
 constexpr int WG_MAX_ACC = 16;
 
 struct WgradGeom {
-    int B, Ho, Wo, Cin, Cout, kh, kw, stride, pad;
+    int B, Ho, Wo, Cin, Cout, kh, kw, sh, sw, ph, pw;     // (Cin, kh, kw, strides, pads) may describe a VIRTUAL operand (stem)
     int TW, TH, TN, tiles_w, tiles_h, tiles_b, P;     // pixel tile (= K block), P = TW*TH*TN, P % 16 == 0
     int RC, RN;                 // channels per TMA box ("run") of the x / g operand: 64 / 32 / 16
     int rpm;                    // runs per 128-row M tile = 128 / RC
@@ -974,8 +1000,8 @@ k_conv_wgrad(const __grid_constant__ CUtensorMap tmap_x, const __grid_constant__
                         const int c0 = (int)(run - tap * (uint32_t)(g.Cin / g.RC)) * g.RC;
                         const uint32_t r = fdiv(tap, g.d_kw);
                         const int s_ = (int)(tap - r * (uint32_t)g.kw);
-                        tma_load_4d(sa + (size_t)rr * runA, &tmap_x, &a_full[s], c0, wo0 * g.stride - g.pad + s_,
-                                    ho0 * g.stride - g.pad + (int)r, b0);
+                        tma_load_4d(sa + (size_t)rr * runA, &tmap_x, &a_full[s], c0, wo0 * g.sw - g.pw + s_,
+                                    ho0 * g.sh - g.ph + (int)r, b0);
                     }
                 }
             }
@@ -1112,12 +1138,19 @@ k_wgrad_reduce(const float* __restrict__ partial, int slices, const float* __res
     }
 }
 
+static int wgrad_geom2(WgradGeom& g, int64_t B, int64_t Ho, int64_t Wo, int64_t Cin, int64_t Cout, int kh, int kw, int sh, int sw, int ph,
+                       int pw, int g_planes);
 static int wgrad_geom(WgradGeom& g, int64_t B, int64_t H, int64_t W, int64_t Cin, int64_t Cout, int kh, int kw, int stride, int pad,
                       int g_planes) {
-    memset(&g, 0, sizeof(g));
     const int64_t Ho = (H + 2 * pad - kh) / stride + 1, Wo = (W + 2 * pad - kw) / stride + 1;
     if (Ho < 1 || Wo < 1 || Cin % 16 != 0 || Cout % 8 != 0 || kh * kw > 9 || stride > 2) return 0;
-    g.B = (int)B; g.Ho = (int)Ho; g.Wo = (int)Wo; g.Cin = (int)Cin; g.Cout = (int)Cout; g.kh = kh; g.kw = kw; g.stride = stride; g.pad = pad;
+    return wgrad_geom2(g, B, Ho, Wo, Cin, Cout, kh, kw, stride, stride, pad, pad, g_planes);
+}
+static int wgrad_geom2(WgradGeom& g, int64_t B, int64_t Ho, int64_t Wo, int64_t Cin, int64_t Cout, int kh, int kw, int sh, int sw, int ph,
+                       int pw, int g_planes) {
+    memset(&g, 0, sizeof(g));
+    g.B = (int)B; g.Ho = (int)Ho; g.Wo = (int)Wo; g.Cin = (int)Cin; g.Cout = (int)Cout; g.kh = kh; g.kw = kw;
+    g.sh = sh; g.sw = sw; g.ph = ph; g.pw = pw;
     g.g_planes = g_planes;
     g.RC = Cin % 64 == 0 ? 64 : (Cin % 32 == 0 ? 32 : 16);
     g.RN = Cout > 32 ? 64 : (Cout > 16 ? 32 : 16);
@@ -1173,6 +1206,24 @@ static int wgrad_geom(WgradGeom& g, int64_t B, int64_t H, int64_t W, int64_t Cin
     return 1;
 }
 
+// tensor maps of the gradient planes + the launch of k_conv_wgrad for a prepared geometry / x operand map
+static int wgrad_core(const WgradGeom& g, const CUtensorMap& tx, const uint16_t* g_hi, const uint16_t* g_lo, float* partial, cudaStream_t st) {
+    CUtensorMap tg0, tg1;
+    const uint64_t dims[4] = {(uint64_t)g.Cout, (uint64_t)g.Wo, (uint64_t)g.Ho, (uint64_t)g.B};
+    const uint64_t str[3] = {(uint64_t)g.Cout * 2, (uint64_t)g.Wo * g.Cout * 2, (uint64_t)g.Ho * g.Wo * g.Cout * 2};
+    const uint32_t box[4] = {(uint32_t)g.RN, (uint32_t)g.TW, (uint32_t)g.TH, (uint32_t)g.TN};
+    int rc = qb_make_tmap(&tg0, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, g_hi, dims, str, box, nullptr, g.RN * 2);
+    if (rc) return rc;
+    rc = qb_make_tmap(&tg1, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, g_lo ? g_lo : g_hi, dims, str, box, nullptr, g.RN * 2);
+    if (rc) return rc;
+    const size_t smem = 1024 + (size_t)g.a_stages * 128 * g.P * 2 + (size_t)g.b_stages * g.g_planes * g.BN * g.P * 2 + 512;
+    QB_CUDA(cudaFuncSetAttribute(k_conv_wgrad, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    const unsigned grid = (unsigned)(g.slices * g.mgroups * g.nblocks);
+    k_conv_wgrad<<<grid, WG_THREADS, smem, st>>>(tx, tg0, tg1, partial, g);
+    QB_LAUNCH_CHECK();
+    return QB_OK;
+}
+
 extern "C" size_t qb_conv_wgrad_ws_bytes(int64_t B, int64_t H, int64_t W, int64_t Cin, int64_t Cout, int kh, int kw, int stride, int pad) {
     WgradGeom g;
     if (!wgrad_geom(g, B, H, W, Cin, Cout, kh, kw, stride, pad, 2)) return 0;
@@ -1206,7 +1257,7 @@ extern "C" int qb_conv_wgrad(const uint16_t* g_hi, const uint16_t* g_lo, const f
     float* partial = static_cast<float*>(ws);
     float* cpart = partial + (size_t)g.slices * g.mrows * Cout;
     cudaStream_t st = qb_stream(stream);
-    CUtensorMap tx, tg0, tg1;
+    CUtensorMap tx;
     {
         const uint64_t dims[4] = {(uint64_t)Cin, (uint64_t)W, (uint64_t)H, (uint64_t)B};
         const uint64_t str[3] = {(uint64_t)Cin * 2, (uint64_t)W * Cin * 2, (uint64_t)H * W * Cin * 2};
@@ -1216,25 +1267,133 @@ extern "C" int qb_conv_wgrad(const uint16_t* g_hi, const uint16_t* g_lo, const f
         if (rc) return rc;
     }
     {
-        const uint64_t dims[4] = {(uint64_t)Cout, (uint64_t)g.Wo, (uint64_t)g.Ho, (uint64_t)B};
-        const uint64_t str[3] = {(uint64_t)Cout * 2, (uint64_t)g.Wo * Cout * 2, (uint64_t)g.Ho * g.Wo * Cout * 2};
-        const uint32_t box[4] = {(uint32_t)g.RN, (uint32_t)g.TW, (uint32_t)g.TH, (uint32_t)g.TN};
-        int rc = qb_make_tmap(&tg0, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, g_hi, dims, str, box, nullptr, g.RN * 2);
-        if (rc) return rc;
-        rc = qb_make_tmap(&tg1, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, g_lo ? g_lo : g_hi, dims, str, box, nullptr, g.RN * 2);
+        int rc = wgrad_core(g, tx, g_hi, g_lo, partial, st);
         if (rc) return rc;
     }
-    const size_t smem = 1024 + (size_t)g.a_stages * 128 * g.P * 2 + (size_t)g.b_stages * g.g_planes * g.BN * g.P * 2 + 512;
-    QB_CUDA(cudaFuncSetAttribute(k_conv_wgrad, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-    const unsigned grid = (unsigned)(g.slices * g.mgroups * g.nblocks);
-    k_conv_wgrad<<<grid, WG_THREADS, smem, st>>>(tx, tg0, tg1, partial, g);
-    QB_LAUNCH_CHECK();
     k_wgrad_colsums<<<CS_BLOCKS, 256, 0, st>>>(g_f32, cpart, (int)B, g.Ho, g.Wo, (int)Cout, (int)H, (int)W, kh, kw, stride, pad, a_range,
                                               a_bits, db != nullptr);
     QB_LAUNCH_CHECK();
     const int64_t outs = (int64_t)g.mrows * Cout;
     k_wgrad_reduce<<<(unsigned)((outs + 255) / 256), 256, 0, st>>>(partial, g.slices, cpart, CS_BLOCKS, dw, db, (int)Cout, (int)Cin,
                                                                  kh * kw, a_range, a_bits);
+    QB_LAUNCH_CHECK();
+    return QB_OK;
+}
+
+// ------------------------------------------------------------------------------------------------
+// Weight gradient of the FIRST layer (3 input channels; 7x7 / stride 2 / pad 3 of ResNet, 3x3 / stride 2 / pad 1 of MobileNet)
+// on the same kernel.  A filter tap is 3 channels = 6 bytes of bf16 codes - no TMA box - but a filter ROW is a contiguous
+// window of the NHWC image.  The codes are expanded once into xs[B][H][W + 2*PL][4] bf16 (channel 3 = 1.0 on real pixels, 0 in
+// the PL zero columns added left and right), and the kernel is pointed at a VIRTUAL operand through an OVERLAPPING tensor
+// map: "pixel" wo of a virtual row is the window of WN pixels x 4 channels (RC = 4*WN = 32 or 16 "channels") that starts at
+// stored column 2*wo, i.e. dims {RC, Wo, H, B} with a W stride of two stored pixels = 16 bytes.  The convolution the kernel
+// then sees has kw = 1, kh taps, stride (2 in h, 1 in w), pad (pad in h, 0 in w): row (r, s', c') of D is
+//     c' < 3 : SUM_px g * q[2ho + r - pad][2wo + s' - PL][c']           -> dW[n][c'][r][s' - (PL - pad)]
+//     c' = 3 : SUM_px g * [that input pixel is inside the image]        -> the zero-padding term of la (image inputs have la != 0)
+// (h bounds by the TMA's zero fill, w bounds by the physical zero columns).  Replaces the thread-built tf32 kernel of
+// conv_stem.cu (1.2 ms, tf32 operand rounding) for these geometries.
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256)
+k_stem_expand16(const uint8_t* __restrict__ codes, uint2* __restrict__ xs, int64_t rows, int W, int PL) {
+    // one thread per stored pixel (4 bf16 = 8 bytes)
+    const int Ws = W + 2 * PL;
+    const int64_t total = rows * Ws;
+    for (int64_t i = (int64_t)blockIdx.x * 256 + threadIdx.x; i < total; i += (int64_t)gridDim.x * 256) {
+        const int64_t row = i / Ws;
+        const int col = (int)(i - row * Ws) - PL;
+        uint2 v = make_uint2(0u, 0u);
+        if (col >= 0 && col < W) {
+            const uint8_t* p = codes + (row * W + col) * 3;
+            const uint32_t c0 = __float_as_uint((float)p[0]) >> 16, c1 = __float_as_uint((float)p[1]) >> 16,
+                           c2 = __float_as_uint((float)p[2]) >> 16;
+            v.x = c0 | (c1 << 16);
+            v.y = c2 | (0x3F80u << 16);                     // bf16 1.0
+        }
+        xs[i] = v;
+    }
+}
+
+// dW[n][c][r][s] = sa * SUM_slices D[(r, s + PL - pad, c)][n] + la * SUM_slices D[(r, s + PL - pad, 3)][n]
+__global__ void __launch_bounds__(256)
+k_stem_wgrad16_reduce(const float* __restrict__ partial, int slices, int mrows, float* __restrict__ dw, int Cout, int kh, int kw, int WN,
+                      int shift, const float* __restrict__ a_range, int a_bits) {
+    const int idx = blockIdx.x * 256 + threadIdx.x;
+    if (idx >= Cout * 3 * kh * kw) return;
+    const int n = idx % Cout;
+    const int t = idx / Cout;                    // (r, s, c)
+    const int c = t % 3, s = (t / 3) % kw, r = t / (3 * kw);
+    const QParams pa = make_qparams_d((double)__ldg(a_range), (double)__ldg(a_range + 1), a_bits);
+    const int rq = (r * WN + s + shift) * 4 + c, rm = (r * WN + s + shift) * 4 + 3;
+    double sq = 0.0, sm = 0.0;
+    for (int k = 0; k < slices; ++k) {
+        sq += (double)partial[((size_t)k * mrows + rq) * Cout + n];
+        sm += (double)partial[((size_t)k * mrows + rm) * Cout + n];
+    }
+    dw[((size_t)n * 3 + c) * (kh * kw) + r * kw + s] = (float)((double)pa.scale * sq + (double)pa.lo * sm);
+}
+
+static int stem16_geom(WgradGeom& g, int& WN, int& PL, int64_t B, int64_t H, int64_t W, int64_t Cout, int k, int stride, int pad) {
+    if (stride != 2 || !((k == 7 && pad == 3) || (k == 3 && pad == 1)) || Cout % 8 != 0 || W % 2 != 0) return 0;
+    WN = k == 7 ? 8 : 4;
+    PL = k == 7 ? 4 : 2;                          // window of output wo starts at pixel 2*wo - PL (stored column 2*wo)
+    const int64_t Ho = (H + 2 * pad - k) / stride + 1, Wo = (W + 2 * pad - k) / stride + 1;
+    if (Ho < 1 || Wo < 1) return 0;
+    return wgrad_geom2(g, B, Ho, Wo, 4 * WN, Cout, k, 1, 2, 1, pad, 0, 2);
+}
+
+extern "C" size_t qb_conv_stem_wgrad16_ws_bytes(int64_t B, int64_t H, int64_t W, int64_t Cout, int k, int stride, int pad) {
+    WgradGeom g;
+    int WN, PL;
+    if (!stem16_geom(g, WN, PL, B, H, W, Cout, k, stride, pad)) return 0;
+    const size_t xs = (size_t)B * H * (W + 2 * PL) * 8 + 256;
+    return xs + (size_t)g.slices * g.mrows * Cout * 4 + 256;
+}
+
+/* dW of the first layer from the bf16 hi / lo planes of its output gradient and the uint8 input codes [B,H,W,3]:
+ * dw fp32 [Cout][3][k][k].  0 from qb_conv_stem_wgrad16_ws_bytes = geometry not taken (use qb_conv_stem_wgrad). */
+extern "C" int qb_conv_stem_wgrad16(const uint16_t* g_hi, const uint16_t* g_lo, const uint8_t* x_codes, float* dw, int64_t B, int64_t H,
+                                    int64_t W, int64_t Cout, int k, int stride, int pad, const float* a_range, int a_bits, void* ws,
+                                    size_t ws_bytes, void* stream) {
+    QB_CHECK_ARG(g_hi && g_lo && x_codes && dw && a_range && ws, "qb_conv_stem_wgrad16: null pointer");
+    WgradGeom g;
+    int WN, PL;
+    if (!stem16_geom(g, WN, PL, B, H, W, Cout, k, stride, pad) ||
+        ((reinterpret_cast<uintptr_t>(g_hi) | reinterpret_cast<uintptr_t>(g_lo) | reinterpret_cast<uintptr_t>(ws)) & 15) != 0) {
+        qb_set_error("qb_conv_stem_wgrad16: unsupported geometry (3 channels, 7x7/2/3 or 3x3/2/1, even W, Cout%%8==0)");
+        return QB_ERR_UNSUPPORTED;
+    }
+    QB_CHECK_ARG(a_bits >= 1 && a_bits <= 8, "qb_conv_stem_wgrad16: codes are 8-bit");
+    const size_t need = qb_conv_stem_wgrad16_ws_bytes(B, H, W, Cout, k, stride, pad);
+    if (ws_bytes < need) {
+        qb_set_error("qb_conv_stem_wgrad16: workspace %zu < %zu bytes", ws_bytes, need);
+        return QB_ERR_WORKSPACE;
+    }
+    cudaStream_t st = qb_stream(stream);
+    const int64_t Ws = W + 2 * PL;
+    const size_t xs_bytes = (((size_t)B * H * Ws * 8) + 255) & ~(size_t)255;
+    uint16_t* xs = static_cast<uint16_t*>(ws);
+    float* partial = reinterpret_cast<float*>(static_cast<char*>(ws) + xs_bytes);
+    {
+        const int64_t total = B * H * Ws;
+        int sms = qb_sm_count();
+        if (sms <= 0) sms = 148;
+        int64_t want = (total + 255) / 256, cap = (int64_t)sms * 16;
+        k_stem_expand16<<<(unsigned)(want < cap ? want : cap), 256, 0, st>>>(x_codes, reinterpret_cast<uint2*>(xs), B * H, (int)W, PL);
+        QB_LAUNCH_CHECK();
+    }
+    CUtensorMap tx;
+    {   // virtual operand: {RC = 4*WN "channels", Wo windows (stride 2 stored pixels = 16 B: overlapping), H rows, B}
+        const uint64_t dims[4] = {(uint64_t)(4 * WN), (uint64_t)g.Wo, (uint64_t)H, (uint64_t)B};
+        const uint64_t str[3] = {16, (uint64_t)Ws * 8, (uint64_t)H * Ws * 8};
+        const uint32_t box[4] = {(uint32_t)g.RC, (uint32_t)g.TW, (uint32_t)(g.TH * 2), (uint32_t)g.TN};
+        const uint32_t es[4] = {1, 1, 2, 1};
+        int rc = qb_make_tmap(&tx, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, xs, dims, str, box, es, g.RC * 2);
+        if (rc) return rc;
+    }
+    int rc = wgrad_core(g, tx, g_hi, g_lo, partial, st);
+    if (rc) return rc;
+    const int outs = (int)Cout * 3 * k * k;
+    k_stem_wgrad16_reduce<<<(outs + 255) / 256, 256, 0, st>>>(partial, g.slices, g.mrows, dw, (int)Cout, k, k, WN, PL - pad, a_range, a_bits);
     QB_LAUNCH_CHECK();
     return QB_OK;
 }

@@ -204,3 +204,90 @@ class ReLU(nn.ReLU):
         if stats is not None:
             Q._stash_fwd_stats(out, stats)
         return out
+
+
+# ---------------------------------------------------------------------------------------------------
+# Optimizer / regulariser glue of the training step (main.py:362-380) on multi-tensor kernels (glue_opt.cu)
+# ---------------------------------------------------------------------------------------------------
+class _L2RegFn(torch.autograd.Function):
+    """0.5 * wd * SUM_t SUM w_t^2 (models/resnet_quantized.py:157-165) in one launch pair; backward: one launch."""
+
+    @staticmethod
+    def forward(ctx, weight_decay, *tensors):
+        ctx.wd = weight_decay
+        ctx.save_for_backward(*tensors)
+        return _abi.l2_sumsq([t.detach() for t in tensors], weight_decay)
+
+    @staticmethod
+    def backward(ctx, g):
+        tensors = [t.detach() for t in ctx.saved_tensors]
+        up = g.detach().reshape(1).float().contiguous()
+        return (None,) + tuple(_abi.l2_grad(tensors, ctx.wd, upstream=up))
+
+
+def regularization(model, weight_decay=1e-4):
+    """``model.regularization()`` of the reference (resnet_quantized.py:157-165 / mobilenet_quantized.py:150-158): L2 penalty over
+    the weights and biases of every Conv2d / Linear, as a differentiable device scalar - 3 launches instead of ~66 + ~66."""
+    ts = []
+    for m in model.modules():
+        if isinstance(m, (nn.Conv2d, nn.Linear)):
+            ts.append(m.weight)
+            if m.bias is not None:
+                ts.append(m.bias)
+    if not ts:
+        return 0.0
+    if not all(t.is_cuda and t.dtype == torch.float32 and t.is_contiguous() for t in ts):
+        total = 0
+        for t in ts:
+            total = total + t.pow(2).sum()
+        return weight_decay * 0.5 * total
+    return _L2RegFn.apply(weight_decay, *ts)
+
+
+class SGD(torch.optim.SGD):
+    """torch.optim.SGD whose step() is ONE multi-tensor launch per parameter group (qb_sgd_step) - same arithmetic, same state
+    dict ("momentum_buffer"), CUDA-graph capturable.  Groups using dampening / Nesterov / maximize, or non-CUDA parameters,
+    take torch's own step."""
+
+    @torch.no_grad()
+    def step(self, closure=None):
+        loss = None
+        if closure is not None:
+            with torch.enable_grad():
+                loss = closure()
+        for group in self.param_groups:
+            ps = [p for p in group["params"] if p.grad is not None]
+            if not ps:
+                continue
+            native = (group["dampening"] == 0 and not group["nesterov"] and not group.get("maximize", False)
+                      and all(p.is_cuda and p.dtype == torch.float32 and p.is_contiguous() and p.grad.is_contiguous()
+                              and not p.grad.is_sparse for p in ps))
+            if not native:
+                for p in ps:
+                    self._torch_single(p, group)
+                continue
+            mom = group["momentum"]
+            first_flags = {("momentum_buffer" not in self.state[p]) for p in ps} if mom != 0 else {False}
+            for first in sorted(first_flags):
+                sel = [p for p in ps if mom == 0 or (("momentum_buffer" not in self.state[p]) == first)]
+                bufs = None
+                if mom != 0:
+                    if first:
+                        for p in sel:
+                            self.state[p]["momentum_buffer"] = torch.empty_like(p)
+                    bufs = [self.state[p]["momentum_buffer"] for p in sel]
+                _abi.sgd_step([p.data for p in sel], [p.grad for p in sel], bufs, group["lr"], mom, group["weight_decay"], first)
+        return loss
+
+    def _torch_single(self, p, group):
+        g = p.grad
+        if group["weight_decay"] != 0:
+            g = g.add(p, alpha=group["weight_decay"])
+        if group["momentum"] != 0:
+            buf = self.state[p].get("momentum_buffer")
+            if buf is None:
+                buf = self.state[p]["momentum_buffer"] = torch.clone(g).detach()
+            else:
+                buf.mul_(group["momentum"]).add_(g, alpha=1 - group["dampening"])
+            g = g.add(buf, alpha=group["momentum"]) if group["nesterov"] else buf
+        p.add_(g, alpha=-group["lr"])

@@ -739,7 +739,15 @@ class _QTensorCoreFn(Function):
             if ctx.grad_mode == "quant":
                 g = _quantize_gradient(g, ctx.bits_grad)
             g = g.contiguous(memory_format=torch.channels_last)
-            dw = _abi.conv_stem_wgrad(g, codes, rng, *ctx.stem) if ctx.needs_input_grad[1] else None
+            dw = None
+            if ctx.needs_input_grad[1]:
+                bits_a, cout, kh, kw, st, pd = ctx.stem
+                B, _, H, W = codes.shape
+                if USE_NATIVE_BACKWARD and kh == kw and _abi.conv_stem_wgrad16_supported(B, H, W, cout, kh, st, pd):
+                    _, hi, lo = _abi.bwd_pack(g, want_codes=False)
+                    dw = _abi.conv_stem_wgrad16(hi, lo, codes, rng, bits_a, cout, kh, st, pd)
+                else:
+                    dw = _abi.conv_stem_wgrad(g, codes, rng, *ctx.stem)
             db = g.sum((0, 2, 3)) if ctx.has_bias and ctx.needs_input_grad[2] else None
             return None, dw, db, None, None
         if ctx.native is not None:
@@ -825,10 +833,13 @@ class QConv2d(nn.Conv2d, _QBase):
             rng = self.quantize_input.measure(input)
             return _QTensorCoreFn.apply(input, self.weight, self._quantized_bias(), self, rng)
         input_ = self.quantize_input(input)
+        conv = (_pair(self.stride), _pair(self.padding), _pair(self.dilation), self.groups)
         if not self.enable_quant:
+            # measure mode / set_quant_mode(False): the float layer (:351-352), in true fp32 on the native direct kernels
+            if input.is_cuda and input.dtype == torch.float32 and self.padding_mode == 'zeros' and not ALLOW_LIBRARY_FALLBACK:
+                return _QContraction.apply(input, self.weight, self.bias, conv, None, "full")
             return F.conv2d(input, self.weight, self.bias, self.stride, self.padding, self.dilation, self.groups)
         qweight, qbias = self._quantized_params()
-        conv = (_pair(self.stride), _pair(self.padding), _pair(self.dilation), self.groups)
         return _QContraction.apply(input_, qweight, qbias, conv, self.num_bits_grad, self._grad_mode())
 
 
@@ -846,6 +857,8 @@ class QLinear(nn.Linear, _QBase):
             return _QTensorCoreFn.apply(input, self.weight, self._quantized_bias(), self, rng)
         input_ = self.quantize_input(input)
         if not self.enable_quant:
+            if input.is_cuda and input.dtype == torch.float32 and not ALLOW_LIBRARY_FALLBACK:
+                return _QContraction.apply(input, self.weight, self.bias, None, None, "full")
             return F.linear(input, self.weight, self.bias)
         qweight, qbias = self._quantized_params()
         return _QContraction.apply(input_, qweight, qbias, None, self.num_bits_grad, self._grad_mode())

@@ -155,3 +155,35 @@ def test_generic_linear(lib):
     dw, db = lib.conv_generic_wgrad(go.to(DEV), x.to(DEV), (10, 24), None, want_w=True, want_bias=True)
     assert rel(dx, go.double() @ w.double()) < 1e-6
     assert rel(dw, go.double().t() @ x.double()) < 1e-6 and rel(db, go.double().sum(0)) < 1e-6
+
+
+STEM16 = [  # B, H, W, Cout, k, stride, pad
+    (4, 224, 224, 64, 7, 2, 3),          # ResNet conv1
+    (2, 62, 46, 64, 7, 2, 3),            # ragged tiles
+    (1, 8, 8, 64, 7, 2, 3),              # every pixel on the border
+    (3, 64, 64, 32, 3, 2, 1),            # MobileNet stem
+    (2, 224, 224, 32, 3, 2, 1),
+]
+
+
+@pytest.mark.parametrize("case", STEM16)
+def test_conv_stem_wgrad16(lib, case):
+    """First-layer weight gradient through the overlapping-window tensor map (qb_conv_stem_wgrad16) against fp64: image inputs
+    have min != 0, so the border-aware zero-padding term (the 'ones' channel of the virtual operand) is exercised."""
+    B, H, W, Cout, k, stride, pad = case
+    gen = torch.Generator().manual_seed(sum(case) + 3)
+    x = torch.randn(B, 3, H, W, generator=gen) * 1.1 + 0.3
+    xd = x.to(DEV).contiguous(memory_format=torch.channels_last)
+    rng = torch.tensor([float(x.min()), float(x.max())], device=DEV)
+    codes = torch.empty_like(xd, dtype=torch.uint8)
+    xq = lib.fakequant_affine(xd, 8, range_dev=rng, codes=codes)
+    Ho, Wo = (H + 2 * pad - k) // stride + 1, (W + 2 * pad - k) // stride + 1
+    g = torch.randn(B, Cout, Ho, Wo, generator=gen)
+    gd = g.to(DEV).contiguous(memory_format=torch.channels_last)
+    _, hi, lo = lib.bwd_pack(gd, want_codes=False)
+    assert lib.conv_stem_wgrad16_supported(B, H, W, Cout, k, stride, pad)
+    dw = lib.conv_stem_wgrad16(hi, lo, codes, rng, 8, Cout, k, stride, pad)
+    dw2 = lib.conv_stem_wgrad16(hi, lo, codes, rng, 8, Cout, k, stride, pad)
+    assert torch.equal(dw, dw2)
+    ref = torch.nn.grad.conv2d_weight(xq.double().cpu(), (Cout, 3, k, k), g.double(), stride, pad)
+    assert rel(dw, ref) < 2e-5, rel(dw, ref)
