@@ -187,7 +187,8 @@ def main_ours(args, rank, world, local_rank):
     model = model.to(dev).train()
     if world > 1:
         qdist.broadcast_parameters(model)
-    opt = torch.optim.SGD(model.parameters(), lr=0.1, momentum=0.9)
+    from qtorch_b200 import glue
+    opt = glue.SGD(model.parameters(), lr=0.1, momentum=0.9)     # torch.optim.SGD arithmetic, one multi-tensor launch
     crit = torch.nn.CrossEntropyLoss()
     if args.scaling == "strong":
         if args.batch % world != 0:

@@ -1195,8 +1195,14 @@ static int wgrad_geom2(WgradGeom& g, int64_t B, int64_t Ho, int64_t Wo, int64_t 
     if (g.slices > g.total_tiles) g.slices = g.total_tiles;
     if (g.slices < 1) g.slices = 1;
     const size_t a_slot = (size_t)128 * g.P * 2, b_slot = (size_t)g_planes * g.BN * g.P * 2;
-    g.b_stages = 2;
+    // the gradient tile is the stream every accumulator waits for: keep three of them in flight when the x ring still gets
+    // at least J + 2 slots (one pixel tile of x boxes plus a head start on the next)
+    g.b_stages = 3;
     int as = (int)((220 * 1024 - 1024 - 512 - (size_t)g.b_stages * b_slot) / a_slot);
+    if (as < g.J + 2 || as < 4) {
+        g.b_stages = 2;
+        as = (int)((220 * 1024 - 1024 - 512 - (size_t)g.b_stages * b_slot) / a_slot);
+    }
     g.a_stages = as > WG_MAX_STAGES ? WG_MAX_STAGES : as;
     if (g.a_stages < 2) return 0;
     g.d_tiles_w = make_fastdiv((uint32_t)g.tiles_w);

@@ -110,6 +110,7 @@ class QResNet(nn.Module):
     def __init__(self, q, block, stages, num_classes, stem, pool, weight_decay=1e-4):
         super().__init__()
         self._q = (q.QConv2d, q.QLinear, q.RangeBN)
+        self._native_glue = bool(getattr(q, "NATIVE_GLUE", False))
         width0, stem_k, stem_s, stem_p, use_maxpool = stem
         self.inplanes = width0
         self.conv1 = _qconv(q, 3, width0, stem_k, stem_s, stem_p)
@@ -164,7 +165,11 @@ class QResNet(nn.Module):
         return self.fc(x.view(x.size(0), -1))
 
     def regularization(self):
-        """resnet_quantized.py:157-165: 0.5*wd*sum(w^2) over conv/linear weights and biases."""
+        """resnet_quantized.py:157-165: 0.5*wd*sum(w^2) over conv/linear weights and biases (native module set: one
+        multi-tensor launch pair, glue.regularization)."""
+        if self._native_glue and next(self.parameters()).is_cuda:
+            from . import glue
+            return glue.regularization(self, self.weight_decay)
         total = 0
         for m in self.modules():
             if isinstance(m, (nn.Conv2d, nn.Linear)):
@@ -224,6 +229,7 @@ class QMobileNet(nn.Module):
     def __init__(self, q, width=1.0, shallow=False, num_classes=1000):
         super().__init__()
         self._q = (q.QConv2d, q.QLinear, q.RangeBN)
+        self._native_glue = bool(getattr(q, "NATIVE_GLUE", False))
         c = lambda n: int(round(width * n))
         plan = [(32, 64, 1), (64, 128, 2), (128, 128, 1), (128, 256, 2), (256, 256, 1), (256, 512, 2)]
         if not shallow:
@@ -252,6 +258,9 @@ class QMobileNet(nn.Module):
         return self.fc(x.view(x.size(0), -1))
 
     def regularization(self, weight_decay=4e-5):
+        if self._native_glue and next(self.parameters()).is_cuda:
+            from . import glue
+            return glue.regularization(self, weight_decay)
         total = 0
         for m in self.modules():
             if isinstance(m, (nn.Conv2d, nn.Linear)):

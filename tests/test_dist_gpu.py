@@ -1,0 +1,51 @@
+"""an N-rank batch-sharded run equals the single-process run on the global batch - on real GPUs, on the
+BENCHMARKED network (ResNet-18) - by launching tools/dist_check.py under torch.distributed.run for N = 2, 4, 8 (skipped when
+the box has fewer GPUs; the round-end driver's single-GPU run therefore skips them, `gpurun --gpus N` runs them)."""
+import json
+import os
+import subprocess
+import sys
+
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def _run(n, model, batch, steps, port):
+    cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", "--nproc-per-node", str(n), "--master-addr", "127.0.0.1",
+           "--master-port", str(port), os.path.join(ROOT, "tools", "dist_check.py"), "--steps", str(steps), "--model", model,
+           "--batch", str(batch)]
+    p = subprocess.run(cmd, capture_output=True, text=True, timeout=900, cwd=ROOT)
+    lines = [l for l in p.stdout.splitlines() if l.startswith("{")]
+    assert lines, "no result line\nstdout:\n%s\nstderr:\n%s" % (p.stdout[-2000:], p.stderr[-3000:])
+    return json.loads(lines[-1]), p.returncode
+
+
+@pytest.mark.parametrize("n", [2, 4, 8])
+@pytest.mark.parametrize("model,batch_per_rank", [("resnet18", 32), ("resnet20_cifar", 16)])
+def test_sharded_equals_single_process(n, model, batch_per_rank):
+    if torch.cuda.device_count() < n:
+        pytest.skip("needs %d GPUs" % n)
+    out, rc = _run(n, model, batch_per_rank * n, 1, 29600 + n)
+    print(out)
+    # one step from identical state with the same global noise draw: identical statistics on every rank, hence identical
+    # buffers; losses and gradients differ only by the fp32 summation order of the gradient all-reduce
+    assert out["world"] == n
+    assert out["loss_rel"] < 1e-5
+    assert out["buffers_rel_l2_max"] < 1e-6
+    assert out["last_step_grad_rel_l2_max"] < 1e-4
+    assert out["params_rel_l2_max"] < 1e-5
+    assert rc == 0
+
+
+def test_sharded_global_batch_256():
+    """BASELINE configs[2] as written: global batch 256 sharded over the GPUs of the box (strong scaling)."""
+    n = torch.cuda.device_count()
+    if n < 2:
+        pytest.skip("needs >= 2 GPUs")
+    n = 8 if n >= 8 else (4 if n >= 4 else 2)
+    out, rc = _run(n, "resnet18", 256, 1, 29650)
+    print(out)
+    assert out["loss_rel"] < 1e-5 and out["buffers_rel_l2_max"] < 1e-6 and out["last_step_grad_rel_l2_max"] < 1e-4 and rc == 0

@@ -213,3 +213,51 @@ def test_relu_pool_without_the_relu_output(lib, shape):
     # eval / no-grad: plain composition
     with torch.no_grad():
         assert torch.equal(pool.relu_pool(x0.clone(), relu), torch.nn.functional.max_pool2d(torch.relu(x0), 3, 2, 1))
+
+
+def test_l2_regularization_matches_torch(lib):
+    """glue.regularization == the reference's model.regularization() (resnet_quantized.py:157-165), value and gradients."""
+    import qtorch_b200  # noqa: F401
+    from qtorch_b200 import glue
+    torch.manual_seed(0)
+    net = torch.nn.Sequential(torch.nn.Conv2d(3, 8, 3), torch.nn.Conv2d(8, 16, 1, bias=False), torch.nn.Flatten(),
+                              torch.nn.Linear(16, 10)).to(DEV)
+    wd = 1e-4
+    ref = 0
+    for m in net.modules():
+        if isinstance(m, (torch.nn.Conv2d, torch.nn.Linear)):
+            ref = ref + m.weight.double().pow(2).sum()
+            if m.bias is not None:
+                ref = ref + m.bias.double().pow(2).sum()
+    ref = wd * 0.5 * ref
+    val = glue.regularization(net, wd)
+    assert abs(float(val) - float(ref)) <= 1e-6 * abs(float(ref))
+    (3.0 * val).backward()
+    for p in net.parameters():
+        assert torch.allclose(p.grad, 3.0 * wd * p.detach(), rtol=1e-6, atol=0)
+
+
+def test_fused_sgd_matches_torch_bitwise(lib):
+    """glue.SGD (qb_sgd_step) against torch.optim.SGD over 4 steps: momentum, weight decay, mixed tensor sizes (several
+    chunks per tensor, scalars), same state-dict layout."""
+    import qtorch_b200  # noqa: F401
+    from qtorch_b200 import glue
+    gen = torch.Generator().manual_seed(5)
+    shapes = [(64, 3, 7, 7), (64,), (512, 512, 3, 3), (1000, 512), (1000,), (1,), (17, 5)]
+    for momentum, wd in ((0.9, 0.0), (0.9, 1e-4), (0.0, 5e-4)):
+        pa = [torch.randn(s, generator=gen).to(DEV).requires_grad_() for s in shapes]
+        pb = [p.detach().clone().requires_grad_() for p in pa]
+        oa = glue.SGD(pa, lr=0.1, momentum=momentum, weight_decay=wd)
+        ob = torch.optim.SGD(pb, lr=0.1, momentum=momentum, weight_decay=wd)
+        for step in range(4):
+            for a, b in zip(pa, pb):
+                g = torch.randn(a.shape, generator=gen).to(DEV) * 0.01
+                a.grad, b.grad = g.clone(), g.clone()
+            oa.step()
+            ob.step()
+            for a, b in zip(pa, pb):
+                assert torch.equal(a, b), (momentum, wd, step, tuple(a.shape), float((a - b).abs().max()))
+        if momentum:
+            for a, b in zip(pa, pb):
+                assert torch.equal(oa.state[a]["momentum_buffer"], ob.state[b]["momentum_buffer"])
+        assert sorted(oa.state_dict()["state"].keys()) == sorted(ob.state_dict()["state"].keys())

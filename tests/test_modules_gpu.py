@@ -256,6 +256,20 @@ def test_resnet20_loss_curve_vs_oracle():
         ref_losses = _train_steps(ref, x, y, steps, lr, "cpu")
     finally:
         qref.set_noise_provider(prev)
+    # the oracle against ITSELF when only its summation order (CPU thread count) changes: single codes flip on 1e-7
+    # differences and the trajectories separate (measured: +-2 % at step 5) - this spread, not a constant, is the tolerance
+    band = [ref_losses]
+    nthreads = torch.get_num_threads()
+    try:
+        for t in (1, 3):
+            torch.set_num_threads(t)
+            other = models.resnet_quantized(qref_modules, depth=20, dataset="cifar10").train()
+            seeding.reseed_parameters(other, 1234)
+            torch.manual_seed(99)
+            band.append(_train_steps(other, x, y, steps, lr, "cpu"))
+    finally:
+        torch.set_num_threads(nthreads)
+    band = np.asarray(band)
     prev = Q.set_noise_provider(CudaReplay(log))
     try:
         losses = _train_steps(mod, x, y, steps, lr, DEV)
@@ -265,7 +279,9 @@ def test_resnet20_loss_curve_vs_oracle():
     # convs with Cin % 32 == 0 run as exact integer GEMMs (closer to the true product than the oracle's fp32 sum);
     # the ~1e-6 difference flips a few downstream codes: 1e-3 relative on the loss
     assert abs(losses[0] - ref_losses[0]) <= 2e-3 * abs(ref_losses[0])
-    np.testing.assert_allclose(losses, ref_losses, rtol=5e-2)
+    centre, half = band.mean(0), 0.5 * (band.max(0) - band.min(0))
+    print("oracle band", band.tolist())
+    assert np.all(np.abs(np.asarray(losses) - centre) <= 3.0 * half + 0.02 * centre), (losses, centre.tolist(), half.tolist())
     sd, sr = mod.state_dict(), ref.state_dict()
     for k in ("bn1.quantize_input.running_min", "bn1.quantize_input.running_max", "fc.quantize_input.running_max"):
         np.testing.assert_allclose(sd[k].cpu().numpy(), sr[k].numpy(), rtol=2e-2, atol=1e-3)
