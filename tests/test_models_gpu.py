@@ -32,6 +32,29 @@ def _build(name, q):
     return models.mobilenet_quantized(q)
 
 
+def _oracle_self_spread(name, noise_log, x, y, loss0, g0):
+    """-> (max relative loss change, max 1 - cosine of fc dW) of the CPU oracle under a (1 +- 1e-7) scaling of its parameters."""
+    d_loss = d_cos = 0.0
+    for eps in (1e-7, -1e-7):
+        torch.manual_seed(0)
+        ref = _build(name, qref_modules).train()
+        seeding.reseed_parameters(ref, 4321)
+        with torch.no_grad():
+            for p in ref.parameters():
+                p.mul_(1.0 + eps)
+        replay = list(noise_log)
+        prev = qref.set_noise_provider(lambda shape: replay.pop(0).reshape(shape))
+        try:
+            loss = torch.nn.CrossEntropyLoss()(ref(x), y)
+            loss.backward()
+        finally:
+            qref.set_noise_provider(prev)
+        g = ref.fc.weight.grad.flatten()
+        d_loss = max(d_loss, abs(float(loss) - loss0) / abs(loss0))
+        d_cos = max(d_cos, 1.0 - float(torch.dot(g, g0) / (g.norm() * g0.norm())))
+    return d_loss, d_cos
+
+
 @pytest.mark.parametrize("name", ["resnet18", "mobilenet"])
 def test_benchmarked_model_train_step_vs_oracle(name):
     import qtorch_b200  # noqa: F401
@@ -114,7 +137,16 @@ def test_benchmarked_model_train_step_vs_oracle(name):
     print("%s: loss cuda %.6f oracle %.6f | first RangeBN rel-L2 %.2e | fc dW cosine %.5f | first-layer dW cosine %.4f"
           % (name, float(loss), float(loss_ref), rel1, cos, cos1))
     assert rel1 < 1e-3
-    assert abs(float(loss) - float(loss_ref)) <= 1e-2 * abs(float(loss_ref))
-    assert cos > 0.98
+    # How far the END of the network can be held: the oracle against ITSELF with every parameter scaled by (1 +- 1e-7) (less
+    # than one fp32 ulp for half of them) and the same noise replayed.  MobileNet at initialisation is chaotic in that sense
+    # (28 quantized layers, RangeBN scales that re-normalise every flipped code): measured 0.6 % of the loss and an fc dW
+    # cosine of 0.974 from that perturbation alone; ResNet-18 stays inside the floors below.
+    d_loss, d_cos = _oracle_self_spread(name, log, x, y, float(loss_ref), g_ref)
+    tol_loss = max(1e-2, 3.0 * d_loss)
+    min_cos = min(0.98, 1.0 - 3.0 * d_cos)
+    print("%s: oracle self-spread under 1e-7 parameter scaling: loss %.2e rel, fc dW 1-cosine %.2e -> tolerances %.2e / %.4f"
+          % (name, d_loss, d_cos, tol_loss, min_cos))
+    assert abs(float(loss) - float(loss_ref)) <= tol_loss * abs(float(loss_ref))
+    assert cos > min_cos
     for p in mod.parameters():
         assert p.grad is not None and torch.isfinite(p.grad).all()
