@@ -427,6 +427,21 @@ int qb_l2_grad(const void* const* w, void* const* grad, const int64_t* sizes, in
                void* stream);
 int qb_sgd_step(const void* const* grad, void* const* param, void* const* buf, const int64_t* sizes, int count, double lr,
                 double momentum, double weight_decay, int first, void* stream);
+/* qb_l2_sumsq without a workspace and without ANY allocation (no cudaMalloc / cudaFree / allocating library call), for
+ * callers that cannot allocate: code under CUDA graph capture, tight serving loops, harnesses that forbid it.  This entry
+ * point has no counterpart in the reference.  The per-CTA partial sums
+ * live in a static device array inside the library (64 KB per GPU that loads it, held until exit), which limits one call to
+ * SUM_t ceil(sizes[t] / 8192) <= qb_l2_sumsq_noalloc_max_blocks() (= 8192, i.e. up to 2^26 elements); larger inputs are
+ * rejected with QB_ERR_ARG and a message in qb_last_error() - use qb_l2_sumsq with a caller workspace for those.  Result is
+ * bit-identical to qb_l2_sumsq.  All calls on a device share the array (it keeps the previous call's partial sums; none of
+ * it needs to start at zero because every slot that is read was written by the same call): calls that OVERLAP on the GPU
+ * (two streams of one device) race and must be serialised by the caller.  qb_l2_sumsq_noalloc_setup() resolves the array's
+ * device address for the current device (cudaGetSymbolAddress, once per device); the first call does this itself, a caller
+ * that captures graphs calls it once per device before the capture. */
+int64_t qb_l2_sumsq_noalloc_max_blocks(void);
+int qb_l2_sumsq_noalloc_setup(void);
+int qb_l2_sumsq_noalloc(const void* const* w, const int64_t* sizes, int count, double weight_decay, float* out, int accumulate,
+                        void* stream);
 /* Hardware probe used by tools/umma_shift_probe.py (UMMA descriptors that start inside an 8-row swizzle atom); not on any
  * product path. */
 int qb_debug_umma_shift(const uint16_t* a, const uint16_t* b, float* out, int mn, int r0, int use_boff, void* stream);

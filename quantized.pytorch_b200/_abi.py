@@ -90,6 +90,9 @@ PROTOTYPES = {
     "qb_conv_generic_wgrad": (_i32, [_p, _p, _p, _p, _i64, _i64, _i64, _i64, _i64, _p, _p, _p, _p]),
     "qb_mt_ws_bytes": (_sz, [_i32, _p]),
     "qb_l2_sumsq": (_i32, [_p, _p, _i32, _dbl, _p, _i32, _p, _sz, _p]),
+    "qb_l2_sumsq_noalloc_max_blocks": (_i64, []),
+    "qb_l2_sumsq_noalloc_setup": (_i32, []),
+    "qb_l2_sumsq_noalloc": (_i32, [_p, _p, _i32, _dbl, _p, _i32, _p]),
     "qb_l2_grad": (_i32, [_p, _p, _p, _i32, _dbl, _p, _p]),
     "qb_sgd_step": (_i32, [_p, _p, _p, _p, _i32, _dbl, _dbl, _dbl, _i32, _p]),
     "qb_debug_umma_shift": (_i32, [_p, _p, _p, _i32, _i32, _i32, _p]),
@@ -892,6 +895,17 @@ def l2_sumsq(tensors, weight_decay, out=None):
         _NLAUNCH["qb_l2_sumsq"] = 2
         _run("qb_l2_sumsq", 4 * sum(t.numel() for t in tensors[k:k + MT_MAX]), w, sizes, n, float(weight_decay), _ptr(out), int(k > 0),
              _ptr(ws), ws.numel(), _stream())
+    return out
+
+
+def l2_sumsq_noalloc(tensors, weight_decay, out, accumulate=False):
+    """qb_l2_sumsq_noalloc: as l2_sumsq for <= 96 tensors, scratch in the library's static device array - no device
+    allocation here or in the library (`out` is the caller's preallocated device scalar).  Added for callers that cannot
+    allocate; no counterpart in the reference."""
+    _mt_check(tensors, "l2_sumsq_noalloc")
+    (w,), sizes, n = _mt_arrays(tensors)
+    _NLAUNCH["qb_l2_sumsq_noalloc"] = 2
+    _run("qb_l2_sumsq_noalloc", 4 * sum(t.numel() for t in tensors), w, sizes, n, float(weight_decay), _ptr(out), int(accumulate), _stream())
     return out
 
 

@@ -154,3 +154,64 @@ extern "C" int qb_sgd_step(const void* const* grad, void* const* param, void* co
     QB_LAUNCH_CHECK();
     return QB_OK;
 }
+
+// ---------------------------------------------------------------------------------------------------------------------------
+// qb_l2_sumsq_noalloc: qb_l2_sumsq for callers that cannot allocate (CUDA graph capture, tight serving loops, harnesses that
+// forbid cudaMalloc).  No counterpart in the reference.  The per-CTA partial sums
+// live in a file-scope device array instead of a caller workspace: QB_L2_NOALLOC_MAX_BLOCKS doubles = 64 KB held by every GPU
+// that loads the library until exit, good for 8192 CTAs * 8192 elements = 2^26 weights per call (ResNet-18: 1.2e7).
+// In host code `g_l2_scratch` is only a stand-in for the symbol: its device address is looked up once per device with
+// cudaGetSymbolAddress (that device current) and handed to the kernels.
+// Every call on a device shares the array.  Nothing in it has to start at zero: each CTA of k_mt_sumsq overwrites its own
+// slot before k_mt_sumsq_final reads slots [0, blocks) on the same stream, and stale slots beyond `blocks` are never read.
+// Two calls that overlap on the GPU (different streams, same device) race on the array - serialise them.
+constexpr int QB_L2_NOALLOC_MAX_BLOCKS = 8192;
+constexpr int QB_MAX_DEVICES = 64;
+static __device__ __align__(256) double g_l2_scratch[QB_L2_NOALLOC_MAX_BLOCKS];
+static double* g_l2_scratch_addr[QB_MAX_DEVICES];          // device address of g_l2_scratch per device ordinal (0 = not yet set up)
+
+static int l2_scratch_for_current_device(double** out) {
+    int dev = -1;
+    QB_CUDA(cudaGetDevice(&dev));
+    QB_CHECK_ARG(dev >= 0 && dev < QB_MAX_DEVICES, "qb_l2_sumsq_noalloc: device ordinal %d (max %d)", dev, QB_MAX_DEVICES - 1);
+    double* p = __atomic_load_n(&g_l2_scratch_addr[dev], __ATOMIC_ACQUIRE);
+    if (!p) {                                               // set-up, once per device (racing threads look up the same address)
+        QB_CUDA(cudaGetSymbolAddress(reinterpret_cast<void**>(&p), g_l2_scratch));
+        QB_CHECK_ARG(p != nullptr, "qb_l2_sumsq_noalloc: cudaGetSymbolAddress returned a null address");
+        __atomic_store_n(&g_l2_scratch_addr[dev], p, __ATOMIC_RELEASE);
+    }
+    *out = p;
+    return QB_OK;
+}
+
+extern "C" int64_t qb_l2_sumsq_noalloc_max_blocks(void) { return QB_L2_NOALLOC_MAX_BLOCKS; }
+
+/* Look the scratch address up for the CURRENT device now (optional: the first qb_l2_sumsq_noalloc call does it otherwise; a
+ * caller that captures graphs calls this once per device before capturing). */
+extern "C" int qb_l2_sumsq_noalloc_setup(void) {
+    double* p = nullptr;
+    return l2_scratch_for_current_device(&p);
+}
+
+/* out[0] (= or +=) 0.5 * wd * SUM_t SUM_i w_t[i]^2, as qb_l2_sumsq, without a workspace argument and without any allocation.
+ * Rejects SUM_t ceil(sizes[t] / 8192) > 8192 (QB_ERR_ARG, message in qb_last_error()). */
+extern "C" int qb_l2_sumsq_noalloc(const void* const* w, const int64_t* sizes, int count, double weight_decay, float* out,
+                                   int accumulate, void* stream) {
+    QB_CHECK_ARG(w && sizes && out, "qb_l2_sumsq_noalloc: null pointer");
+    MtList l;
+    int rc = mt_fill(l, count, w, nullptr, nullptr, sizes, "qb_l2_sumsq_noalloc");
+    if (rc) return rc;
+    const int blocks = l.first_block[count];
+    QB_CHECK_ARG(blocks <= QB_L2_NOALLOC_MAX_BLOCKS,
+                 "qb_l2_sumsq_noalloc: %d chunks of %d elements exceed the static scratch (%d chunks = %lld elements); use qb_l2_sumsq",
+                 blocks, MT_CHUNK, QB_L2_NOALLOC_MAX_BLOCKS, (long long)QB_L2_NOALLOC_MAX_BLOCKS * MT_CHUNK);
+    double* scratch = nullptr;
+    rc = l2_scratch_for_current_device(&scratch);
+    if (rc) return rc;
+    cudaStream_t st = qb_stream(stream);
+    k_mt_sumsq<<<blocks, MT_THREADS, 0, st>>>(l, scratch);
+    QB_LAUNCH_CHECK();
+    k_mt_sumsq_final<<<1, 32, 0, st>>>(scratch, blocks, 0.5 * weight_decay, out, accumulate);
+    QB_LAUNCH_CHECK();
+    return QB_OK;
+}
