@@ -353,6 +353,16 @@ int qb_relu_bwd_minmax(const float* grad_out, const float* relu_out, float* dx, 
  * two torch ops do) plus the statistics block of y. */
 int qb_add_relu_measure(const float* x, const float* r, float* y, int64_t B, int64_t inner, double* stats, void* ws,
                         size_t ws_bytes, void* stream);
+/* RangeBN normalisation (models/modules/quantize.py:488-499) + the nn.ReLU that follows it in every block of
+ * models/resnet_quantized.py:47-75 / models/mobilenet_quantized.py:21-60 [+ the residual add in front of that ReLU, residual
+ * != NULL] + the statistics block of the result, in ONE pass over the uint8 codes of RangeBN's fake-quantized input that
+ * qb_rangebn_stats_nhwc wrote:  y = relu(((deq(code) - mean_c) * qscale_c) * qgamma_c + qbeta_c [+ residual]).
+ * Bit-identical to qb_rangebn_apply_nhwc followed by qb_relu_measure / qb_add_relu_measure (values and statistics); moves
+ * 5 (+4) B/elem instead of 13 (+4): the normalised tensor is never written.  Channels-last, C % 4 == 0, q_bits <= 8,
+ * 16-byte aligned fp32 tensors; qgamma / qbeta may be NULL; ws = qb_measure_ws_bytes(B). */
+int qb_rangebn_apply_relu_measure(const uint8_t* x_codes, const float* residual, float* y, int64_t B, int64_t C, int64_t HW,
+                                  const float* mean, const float* qscale, const float* qgamma, const float* qbeta,
+                                  const float* q_range, int q_bits, double* stats, void* ws, size_t ws_bytes, void* stream);
 int qb_maxpool2d_nhwc_fwd(const float* x, float* out, uint8_t* idx, int64_t B, int64_t H, int64_t W, int64_t C, int k,
                           int stride, int pad, void* stream);
 int qb_maxpool2d_nhwc_bwd(const float* grad_out, const uint8_t* idx, float* dx, int64_t B, int64_t H, int64_t W, int64_t C,

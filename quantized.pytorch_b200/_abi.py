@@ -27,6 +27,7 @@ PROTOTYPES = {
     "qb_measure_stats": (_i32, [_p, _i64, _i64, _p, _p, _sz, _p]),
     "qb_relu_measure": (_i32, [_p, _p, _i64, _i64, _p, _p, _sz, _p]),
     "qb_add_relu_measure": (_i32, [_p, _p, _p, _i64, _i64, _p, _p, _sz, _p]),
+    "qb_rangebn_apply_relu_measure": (_i32, [_p, _p, _p, _i64, _i64, _i64, _p, _p, _p, _p, _p, _i32, _p, _p, _sz, _p]),
     "qb_relu_bwd_minmax": (_i32, [_p, _p, _p, _i64, _p, _p, _sz, _p]),
     "qb_measure_finalize": (_i32, [_p, _p, _p, _p, _p, _p, _dbl, _i32, _i32, _i32, _p, _p]),
     "qb_fakequant_affine": (_i32, [_p, _p, _p, _i64, _i32, _p, _dbl, _dbl, _i32, _p]),
@@ -282,6 +283,24 @@ def add_relu_measure(x, r, out=None):
     ws = workspace("measure", lib.qb_measure_ws_bytes(B), x.device)
     _run("qb_add_relu_measure", 12 * x.numel(), _ptr(x), _ptr(r), _ptr(out), B, inner, _ptr(stats), _ptr(ws), ws.numel(),
          _stream())
+    return out, stats
+
+
+def rangebn_apply_relu_measure(x_codes, like, B, Cn, HW, vec, has_gamma, has_beta, q_range, q_bits, residual=None):
+    """-> (out, stats): relu(RangeBN-normalise(codes) [+ residual]) and the QuantMeasure statistics of the result in one pass
+    (qb_rangebn_apply_relu_measure); ``like`` gives shape / layout of the output (the raw RangeBN input)."""
+    lib = load()
+    out = torch.empty_like(like)
+    if residual is not None:
+        residual = _f32c(residual, "residual")
+        if residual.shape != out.shape or residual.stride() != out.stride():
+            raise QB200Error("rangebn_apply_relu_measure: residual differs from the output in shape or layout")
+    stats = torch.empty(8, dtype=torch.float64, device=like.device)
+    ws = workspace("measure", lib.qb_measure_ws_bytes(B), like.device)
+    n = B * Cn * HW
+    _run("qb_rangebn_apply_relu_measure", (9 if residual is not None else 5) * n, _ptr(x_codes), _ptr(residual), _ptr(out), B, Cn, HW,
+         _ptr(vec[0]), _ptr(vec[2]), _ptr(vec[3]) if has_gamma else None, _ptr(vec[4]) if has_beta else None, _ptr(q_range),
+         int(q_bits), _ptr(stats), _ptr(ws), ws.numel(), _stream())
     return out, stats
 
 

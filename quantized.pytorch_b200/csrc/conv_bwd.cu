@@ -1122,7 +1122,17 @@ k_wgrad_reduce(const float* __restrict__ partial, int slices, const float* __res
         const int n = (int)(idx % Cout), row = (int)(idx / Cout);
         const int tap = row / Cin, c = row - tap * Cin;
         double sq = 0.0;
-        for (int s = 0; s < slices; ++s) sq += (double)partial[((size_t)s * mrows + row) * Cout + n];
+        const float* src = partial + (size_t)row * Cout + n;
+        const size_t pitch = (size_t)mrows * Cout;
+        int s = 0;
+        for (; s + 8 <= slices; s += 8) {                       // eight independent loads in flight; the sum keeps its slice order
+            float v[8];
+#pragma unroll
+            for (int u = 0; u < 8; ++u) v[u] = __ldcs(src + (size_t)(s + u) * pitch);
+#pragma unroll
+            for (int u = 0; u < 8; ++u) sq += (double)v[u];
+        }
+        for (; s < slices; ++s) sq += (double)__ldcs(src + (size_t)s * pitch);
         double v = (double)pa.scale * sq;
         if (pa.lo != 0.0f) {
             double sm = 0.0;

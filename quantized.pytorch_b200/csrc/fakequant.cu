@@ -252,6 +252,97 @@ k_fq_rows(const float* __restrict__ w, float* wq, uint8_t* codes, int64_t cols, 
     }
 }
 
+// Long rows (cols >= 8192: per-channel ranges of activation-sized tensors, BASELINE configs[4]): one CTA per row leaves most
+// SMs idle (64 rows x 65 536: 558 GB/s).  Here a row is split over a thread-block CLUSTER of FQ_ROW_CL CTAs: each CTA reduces
+// its segment, the CL partial extrema meet through distributed shared memory, then each CTA quantizes its own segment, which
+// is still in L1/L2.  Same arithmetic as k_fq_rows (min / max are order independent), 128-bit accesses when the row pitch allows.
+constexpr int FQ_ROW_CL = 8;
+
+__global__ void __cluster_dims__(FQ_ROW_CL, 1, 1) __launch_bounds__(ROW_THREADS)
+k_fq_rows_cluster(const float* __restrict__ w, float* wq, uint8_t* codes, int64_t cols, int bits, float* row_min, float* row_max,
+                  int compute_range, int vec4) {
+    __shared__ float sm[64];
+    __shared__ float s_part[2];
+    const int64_t row = blockIdx.x / FQ_ROW_CL;
+    uint32_t part;
+    asm("mov.u32 %0, %%cluster_ctarank;" : "=r"(part));
+    int64_t seg = (cols + FQ_ROW_CL - 1) / FQ_ROW_CL;
+    seg = (seg + 3) & ~(int64_t)3;
+    const int64_t j0 = (int64_t)part * seg < cols ? (int64_t)part * seg : cols;
+    const int64_t j1 = j0 + seg < cols ? j0 + seg : cols;
+    const float* src = w + row * cols;
+    float lo, hi;
+    if (compute_range) {
+        float mn = QB_INF, mx = -QB_INF;
+        if (vec4) {
+            for (int64_t j = j0 + 4 * (int64_t)threadIdx.x; j + 3 < j1; j += 4 * ROW_THREADS) {
+                const float4 v = *reinterpret_cast<const float4*>(src + j);
+                mn = fminf(fminf(mn, fminf(v.x, v.y)), fminf(v.z, v.w));
+                mx = fmaxf(fmaxf(mx, fmaxf(v.x, v.y)), fmaxf(v.z, v.w));
+            }
+            for (int64_t j = j0 + ((j1 - j0) & ~(int64_t)3) + threadIdx.x; j < j1; j += ROW_THREADS) {
+                mn = fminf(mn, src[j]);
+                mx = fmaxf(mx, src[j]);
+            }
+        } else {
+            for (int64_t j = j0 + threadIdx.x; j < j1; j += ROW_THREADS) {
+                mn = fminf(mn, src[j]);
+                mx = fmaxf(mx, src[j]);
+            }
+        }
+        const float2 r = block_minmax(mn, mx, sm);
+        if (threadIdx.x == 0) { s_part[0] = r.x; s_part[1] = r.y; }
+        asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+        lo = QB_INF; hi = -QB_INF;
+        const uint32_t local = (uint32_t)__cvta_generic_to_shared(s_part);
+#pragma unroll
+        for (uint32_t c = 0; c < FQ_ROW_CL; ++c) {
+            uint32_t remote;
+            asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(remote) : "r"(local), "r"(c));
+            float a, b;
+            asm volatile("ld.shared::cluster.f32 %0, [%1];" : "=f"(a) : "r"(remote));
+            asm volatile("ld.shared::cluster.f32 %0, [%1];" : "=f"(b) : "r"(remote + 4));
+            lo = fminf(lo, a);
+            hi = fmaxf(hi, b);
+        }
+        // nobody leaves (and frees its shared memory) before every CTA of the cluster has read the partial extrema
+        asm volatile("barrier.cluster.arrive.release.aligned;\n\tbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+        if (part == 0 && threadIdx.x == 0) {
+            row_min[row] = lo;
+            row_max[row] = hi;
+        }
+    } else {
+        lo = row_min[row];
+        hi = row_max[row];
+    }
+    const QParams p = make_qparams_f(lo, hi, bits);
+    const Divisor d = make_divisor(p.scale);
+    if (vec4) {
+        for (int64_t j = j0 + 4 * (int64_t)threadIdx.x; j + 3 < j1; j += 4 * ROW_THREADS) {
+            const float4 v = *reinterpret_cast<const float4*>(src + j);
+            const float q0 = q_affine_code(v.x, p, d), q1 = q_affine_code(v.y, p, d), q2 = q_affine_code(v.z, p, d),
+                        q3 = q_affine_code(v.w, p, d);
+            if (wq)
+                *reinterpret_cast<float4*>(wq + row * cols + j) =
+                    make_float4(q_affine_deq(q0, p), q_affine_deq(q1, p), q_affine_deq(q2, p), q_affine_deq(q3, p));
+            if (codes)
+                *reinterpret_cast<uint32_t*>(codes + row * cols + j) =
+                    (uint32_t)q0 | ((uint32_t)q1 << 8) | ((uint32_t)q2 << 16) | ((uint32_t)q3 << 24);
+        }
+        for (int64_t j = j0 + ((j1 - j0) & ~(int64_t)3) + threadIdx.x; j < j1; j += ROW_THREADS) {
+            const float q = q_affine_code(src[j], p, d);
+            if (wq) wq[row * cols + j] = q_affine_deq(q, p);
+            if (codes) codes[row * cols + j] = (uint8_t)q;
+        }
+    } else {
+        for (int64_t j = j0 + threadIdx.x; j < j1; j += ROW_THREADS) {
+            const float q = q_affine_code(src[j], p, d);
+            if (wq) wq[row * cols + j] = q_affine_deq(q, p);
+            if (codes) codes[row * cols + j] = (uint8_t)q;
+        }
+    }
+}
+
 extern "C" int qb_fakequant_rows(const float* w, float* wq, uint8_t* codes, int64_t rows, int64_t cols, int bits,
                                  float* row_min, float* row_max, int compute_range, void* stream) {
     QB_CHECK_ARG(rows >= 0 && cols >= 0, "qb_fakequant_rows: rows=%lld cols=%lld", (long long)rows, (long long)cols);
@@ -260,6 +351,13 @@ extern "C" int qb_fakequant_rows(const float* w, float* wq, uint8_t* codes, int6
     QB_CHECK_ARG(bits >= 1 && bits <= 24, "qb_fakequant_rows: bits=%d outside 1..24", bits);
     QB_CHECK_ARG(!codes || bits <= 8, "qb_fakequant_rows: uint8 codes need bits<=8");
     QB_CHECK_ARG(rows <= 2147483647LL, "qb_fakequant_rows: too many rows");
+    if (cols >= 8192 && rows * FQ_ROW_CL <= 2147483647LL) {
+        const int vec4 = cols % 4 == 0 && aligned(w, 16) && (!wq || aligned(wq, 16)) && (!codes || aligned(codes, 4));
+        k_fq_rows_cluster<<<(unsigned)(rows * FQ_ROW_CL), ROW_THREADS, 0, qb_stream(stream)>>>(w, wq, codes, cols, bits, row_min,
+                                                                                            row_max, compute_range, vec4);
+        QB_LAUNCH_CHECK();
+        return QB_OK;
+    }
     k_fq_rows<<<(unsigned)rows, ROW_THREADS, 0, qb_stream(stream)>>>(w, wq, codes, cols, bits, row_min, row_max,
                                                                     compute_range);
     QB_LAUNCH_CHECK();

@@ -34,11 +34,53 @@ __device__ __forceinline__ float relu1(float v) { return v < 0.0f ? 0.0f : v; }
 
 // MODE 0: statistics of x; 1: y = relu(x) + statistics of y; 2: y = relu(x + r) + statistics of y (the residual add and
 // the ReLU that close a ResNet block, models/resnet_quantized.py:62-68, in one pass)
+// MODE 3 / 4 (qb_rangebn_apply_relu_measure): x is NOT an fp32 tensor but the uint8 codes of RangeBN's fake-quantized input
+// (channels-last, written by the statistics pass); the element is first dequantised and normalised exactly as
+// k_rbn_apply_codes_nhwc does it (quantize.py:488-499, four separately rounded fp32 operations), then MODE 3 = MODE 1 and
+// MODE 4 = MODE 2 on that value: the normalised tensor itself is never written.
+struct ApplyArg {
+    const float *mean, *qscale, *qgamma, *qbeta;   // per channel; qgamma / qbeta may be null
+    const float* q_range;
+    int q_bits;
+    int C;
+    int fixed;                                      // (MS_THREADS*4) % C == 0: a thread's four channels never change
+};
+
+__device__ __forceinline__ float4 apply_quad(uint32_t word, const AffineQ& aq, const float4& mu, const float4& sc, const float4& gm,
+                                             const float4& be, bool has_g, bool has_b) {
+    float4 o;
+    float t;
+#define QB_APPLY_ONE(dst, sh, f)                                                              \
+    t = __fmul_rn(__fsub_rn(q_affine_deq((float)((word >> sh) & 0xffu), aq.p), mu.f), sc.f);    \
+    if (has_g) t = __fmul_rn(t, gm.f);                                                          \
+    if (has_b) t = __fadd_rn(t, be.f);                                                          \
+    dst = t;
+    QB_APPLY_ONE(o.x, 0, x)
+    QB_APPLY_ONE(o.y, 8, y)
+    QB_APPLY_ONE(o.z, 16, z)
+    QB_APPLY_ONE(o.w, 24, w)
+#undef QB_APPLY_ONE
+    return o;
+}
+
 template <int MODE>
 __global__ void __launch_bounds__(MS_THREADS)
 k_measure_stats(const float* x, const float* r, float* y, int64_t B, int64_t inner, int vec, double* stats, unsigned int* row_max,
-                unsigned int* row_min, double* psum, double* psq, unsigned int* counter) {
-    constexpr bool RELU = MODE >= 1, ADD = MODE == 2;
+                unsigned int* row_min, double* psum, double* psq, unsigned int* counter, ApplyArg ap) {
+    constexpr bool RELU = MODE >= 1, ADD = MODE == 2 || MODE == 4, CODES = MODE >= 3;
+    AffineQ aq;
+    float4 mu = make_float4(0.f, 0.f, 0.f, 0.f), sc = mu, gm = mu, be = mu;
+    const bool has_g = CODES && ap.qgamma != nullptr, has_b = CODES && ap.qbeta != nullptr;
+    auto load_params = [&](int c) {
+        mu = __ldg(reinterpret_cast<const float4*>(ap.mean + c));
+        sc = __ldg(reinterpret_cast<const float4*>(ap.qscale + c));
+        if (has_g) gm = __ldg(reinterpret_cast<const float4*>(ap.qgamma + c));
+        if (has_b) be = __ldg(reinterpret_cast<const float4*>(ap.qbeta + c));
+    };
+    if (CODES) {
+        aq = load_affineq(ap.q_range, ap.q_bits);
+        if (ap.fixed) load_params((int)((threadIdx.x * 4u) % (unsigned)ap.C));
+    }
     __shared__ float smn[8], smx[8];
     __shared__ double sd[2][8];
     __shared__ bool last;
@@ -79,12 +121,16 @@ k_measure_stats(const float* x, const float* r, float* y, int64_t B, int64_t inn
             const int64_t nq = len >> 2;
             float4 v[MS_VEC_PER_THREAD];
             float4 rv[ADD ? MS_VEC_PER_THREAD : 1];
+            uint32_t cw[CODES ? MS_VEC_PER_THREAD : 1];
 #pragma unroll
             for (int u = 0; u < MS_VEC_PER_THREAD; ++u) {
                 int64_t qi = threadIdx.x + (int64_t)u * MS_THREADS;
                 if (qi < nq) {
-                    v[u] = RELU ? reinterpret_cast<const float4*>(src)[qi]          // in place: the line is written next
-                                : __ldcs(reinterpret_cast<const float4*>(src) + qi);
+                    if (CODES)
+                        cw[u] = __ldcs(reinterpret_cast<const uint32_t*>(reinterpret_cast<const uint8_t*>(x) + b * inner + off) + qi);
+                    else
+                        v[u] = (RELU && x == y) ? reinterpret_cast<const float4*>(src)[qi]   // in place: the line is written next
+                                                : __ldcs(reinterpret_cast<const float4*>(src) + qi);
                     if (ADD) rv[u] = __ldcs(reinterpret_cast<const float4*>(r + b * inner + off) + qi);
                 }
             }
@@ -92,6 +138,10 @@ k_measure_stats(const float* x, const float* r, float* y, int64_t B, int64_t inn
             for (int u = 0; u < MS_VEC_PER_THREAD; ++u) {
                 int64_t qi = threadIdx.x + (int64_t)u * MS_THREADS;
                 if (qi < nq) {
+                    if (CODES) {
+                        if (!ap.fixed) load_params((int)((uint64_t)(off + 4 * qi) % (uint64_t)ap.C));
+                        v[u] = apply_quad(cw[u], aq, mu, sc, gm, be, has_g, has_b);
+                    }
                     if (ADD) v[u] = make_float4(__fadd_rn(v[u].x, rv[u].x), __fadd_rn(v[u].y, rv[u].y),
                                                 __fadd_rn(v[u].z, rv[u].z), __fadd_rn(v[u].w, rv[u].w));
                     if (RELU) {
@@ -175,7 +225,8 @@ k_measure_stats(const float* x, const float* r, float* y, int64_t B, int64_t inn
     }
 }
 
-static int measure_launch(const float* x, const float* r, float* y, int64_t B, int64_t inner, double* stats, void* ws, size_t ws_bytes, void* stream);
+static int measure_launch(const float* x, const float* r, float* y, int64_t B, int64_t inner, double* stats, void* ws, size_t ws_bytes, void* stream,
+                          const ApplyArg* ap = nullptr);
 
 extern "C" int qb_measure_stats(const float* x, int64_t B, int64_t inner, double* stats, void* ws, size_t ws_bytes,
                                 void* stream) {
@@ -197,7 +248,32 @@ extern "C" int qb_add_relu_measure(const float* x, const float* r, float* y, int
     return measure_launch(x, r, y, B, inner, stats, ws, ws_bytes, stream);
 }
 
-static int measure_launch(const float* x, const float* r, float* y, int64_t B, int64_t inner, double* stats, void* ws, size_t ws_bytes, void* stream) {
+/* RangeBN normalisation (quantize.py:488-499) + the ReLU that follows it [+ the residual add in front of that ReLU] + the
+ * QuantMeasure statistics of the result in ONE pass over the uint8 codes of RangeBN's fake-quantized input:
+ *   y = relu(((deq(code) - mean_c) * qscale_c) * qgamma_c + qbeta_c [+ residual])
+ * 1 (+4) B/elem read, 4 written - the normalised tensor is never materialised (qb_rangebn_apply_nhwc + qb_relu_measure /
+ * qb_add_relu_measure move 5 + 8 (+4)).  Bit-identical to that composition, statistics included.  Channels-last, C % 4 == 0,
+ * H*W*C % 4 == 0, 16-byte aligned tensors, q_bits <= 8. */
+extern "C" int qb_rangebn_apply_relu_measure(const uint8_t* x_codes, const float* residual, float* y, int64_t B, int64_t C, int64_t HW,
+                                             const float* mean, const float* qscale, const float* qgamma, const float* qbeta,
+                                             const float* q_range, int q_bits, double* stats, void* ws, size_t ws_bytes, void* stream) {
+    QB_CHECK_ARG(x_codes && y && mean && qscale && q_range, "qb_rangebn_apply_relu_measure: null pointer");
+    QB_CHECK_ARG(B > 0 && C > 0 && HW > 0 && C % 4 == 0 && C < (1 << 30), "qb_rangebn_apply_relu_measure: bad shape (C %% 4 == 0 required)");
+    QB_CHECK_ARG(q_bits >= 1 && q_bits <= 8, "qb_rangebn_apply_relu_measure: q_bits=%d", q_bits);
+    QB_CHECK_ARG(((reinterpret_cast<uintptr_t>(x_codes) & 3) | (reinterpret_cast<uintptr_t>(y) & 15) |
+                  (reinterpret_cast<uintptr_t>(residual) & 15) | (reinterpret_cast<uintptr_t>(mean) & 15) |
+                  (reinterpret_cast<uintptr_t>(qscale) & 15) | (reinterpret_cast<uintptr_t>(qgamma) & 15) |
+                  (reinterpret_cast<uintptr_t>(qbeta) & 15)) == 0,
+                 "qb_rangebn_apply_relu_measure: misaligned tensor");
+    QB_CHECK_ARG(residual != y, "qb_rangebn_apply_relu_measure: the residual must not alias the output");
+    const int64_t inner = HW * C;
+    ApplyArg ap{mean, qscale, qgamma, qbeta, q_range, q_bits, (int)C, 0};
+    ap.fixed = ((MS_THREADS * 4) % C == 0 && MS_TILE % C == 0) ? 1 : 0;
+    return measure_launch(reinterpret_cast<const float*>(x_codes), residual, y, B, inner, stats, ws, ws_bytes, stream, &ap);
+}
+
+static int measure_launch(const float* x, const float* r, float* y, int64_t B, int64_t inner, double* stats, void* ws, size_t ws_bytes, void* stream,
+                          const ApplyArg* ap) {
     QB_CHECK_ARG(x && stats && ws, "qb_measure_stats: null pointer");
     QB_CHECK_ARG(B > 0 && inner > 0, "qb_measure_stats: B=%lld inner=%lld (empty input has no range)", (long long)B,
                  (long long)inner);
@@ -211,16 +287,19 @@ static int measure_launch(const float* x, const float* r, float* y, int64_t B, i
     double* psq = psum + MS_MAX_BLOCKS;
     unsigned int* row_max = reinterpret_cast<unsigned int*>(base + MS_FIXED_BYTES);
     unsigned int* row_min = row_max + B;
-    const int vec = (((reinterpret_cast<uintptr_t>(x) | reinterpret_cast<uintptr_t>(y) | reinterpret_cast<uintptr_t>(r)) & 15) == 0) && (inner % 4 == 0);
+    const int vec = ap ? 1 : (((reinterpret_cast<uintptr_t>(x) | reinterpret_cast<uintptr_t>(y) | reinterpret_cast<uintptr_t>(r)) & 15) == 0) && (inner % 4 == 0);
     const int64_t T = B * ((inner + MS_TILE - 1) / MS_TILE);
     int sms = qb_sm_count();
     if (sms <= 0) sms = 148;
     int64_t cap = (int64_t)sms * 8;
     if (cap > MS_MAX_BLOCKS) cap = MS_MAX_BLOCKS;
     int grid = (int)(T < cap ? T : cap);
-    if (y && r) k_measure_stats<2><<<grid, MS_THREADS, 0, qb_stream(stream)>>>(x, r, y, B, inner, vec, stats, row_max, row_min, psum, psq, counter);
-    else if (y) k_measure_stats<1><<<grid, MS_THREADS, 0, qb_stream(stream)>>>(x, nullptr, y, B, inner, vec, stats, row_max, row_min, psum, psq, counter);
-    else k_measure_stats<0><<<grid, MS_THREADS, 0, qb_stream(stream)>>>(x, nullptr, nullptr, B, inner, vec, stats, row_max, row_min, psum, psq, counter);
+    const ApplyArg none{};
+    if (ap && r) k_measure_stats<4><<<grid, MS_THREADS, 0, qb_stream(stream)>>>(x, r, y, B, inner, vec, stats, row_max, row_min, psum, psq, counter, *ap);
+    else if (ap) k_measure_stats<3><<<grid, MS_THREADS, 0, qb_stream(stream)>>>(x, nullptr, y, B, inner, vec, stats, row_max, row_min, psum, psq, counter, *ap);
+    else if (y && r) k_measure_stats<2><<<grid, MS_THREADS, 0, qb_stream(stream)>>>(x, r, y, B, inner, vec, stats, row_max, row_min, psum, psq, counter, none);
+    else if (y) k_measure_stats<1><<<grid, MS_THREADS, 0, qb_stream(stream)>>>(x, nullptr, y, B, inner, vec, stats, row_max, row_min, psum, psq, counter, none);
+    else k_measure_stats<0><<<grid, MS_THREADS, 0, qb_stream(stream)>>>(x, nullptr, nullptr, B, inner, vec, stats, row_max, row_min, psum, psq, counter, none);
     QB_LAUNCH_CHECK();
     return QB_OK;
 }

@@ -26,8 +26,19 @@ struct NhwcGeom {
     int tileC;            // channels per CTA (gridDim.y tiles)
 };
 
+// CTAs that are resident at once (SMs x occupancy of `kernel`): grids are sized to ONE full wave of them - 512 CTAs on 444
+// slots ran as 1.15 waves, i.e. a second wave of 68 CTAs on an otherwise idle GPU (profiles/ncu_rbn_r02d.txt)
+template <typename Kern>
+static int nh_slots(Kern kernel, size_t smem) {
+    int occ = 0;
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&occ, kernel, NH_THREADS, smem) != cudaSuccess || occ < 1) occ = 2;
+    int sms = qb_sm_count();
+    if (sms <= 0) sms = 148;
+    return occ * sms;
+}
+
 template <int VEC>
-static NhwcGeom make_geom(int64_t R, int64_t C, int K, int max_seg = NH_MAX_SEG) {
+static NhwcGeom make_geom(int64_t R, int64_t C, int K, int max_seg = NH_MAX_SEG, int slots = 0) {
     NhwcGeom g;
     g.R = R; g.C = C; g.K = K; g.L = R / K;
     g.tileC = (int)(C < (int64_t)NH_THREADS * VEC ? C : (int64_t)NH_THREADS * VEC);
@@ -35,7 +46,7 @@ static NhwcGeom make_geom(int64_t R, int64_t C, int K, int max_seg = NH_MAX_SEG)
     g.RL = NH_THREADS / g.CT;
     int ctiles = (int)((C + g.tileC - 1) / g.tileC);
     // enough CTAs to fill 148 SMs a few times over, each segment at least RL*NH_UNROLL rows
-    int64_t want = (148 * 4 + (int64_t)K * ctiles - 1) / ((int64_t)K * ctiles);
+    int64_t want = slots > 0 ? slots / ((int64_t)K * ctiles) : (148 * 4 + (int64_t)K * ctiles - 1) / ((int64_t)K * ctiles);
     int64_t max_by_rows = g.L / ((int64_t)g.RL * NH_UNROLL);
     if (want > max_by_rows) want = max_by_rows;
     if (want > max_seg) want = max_seg;
@@ -220,6 +231,16 @@ struct Q8Row {
     uint32_t bits[8];
 };
 
+// One accumulator per (chunk k, channel c), combined across the segment CTAs with integer atomics (max / max of the
+// complement / add: exact and order independent, hence deterministic).  All-zero is the identity; k_rbn_stats_q8_finish
+// resets what it has read, so the workspace region stays clean between calls.
+struct Q8Acc {
+    uint32_t kmax;               // largest key_max
+    uint32_t nkmin;              // largest ~key_min
+    unsigned long long sum;      // SUM of the codes
+};
+constexpr size_t NH_ACC_BYTES = (size_t)1 << 20;                     // fixed region at the head of the workspace: 65 536 (k, c) pairs
+
 __device__ __forceinline__ Q8Row q8_row(const F8& v, const AffineQ& aq, uint64_t nlo2, uint64_t r2, uint64_t nb2, uint64_t magic2) {
     Q8Row o;
     float q[8];
@@ -261,7 +282,8 @@ __device__ __forceinline__ Q8Row q8_row(const F8& v, const AffineQ& aq, uint64_t
 
 __global__ void __launch_bounds__(NH_THREADS, 3)
 k_rbn_stats_q8_nhwc(const float* __restrict__ x, NhwcGeom g, uint32_t* __restrict__ pkmax, uint32_t* __restrict__ pkmin,
-                    uint32_t* __restrict__ pksum, const float* q_range, int q_bits, uint8_t* __restrict__ codes_out) {
+                    uint32_t* __restrict__ pksum, const float* q_range, int q_bits, uint8_t* __restrict__ codes_out,
+                    Q8Acc* __restrict__ acc_kc) {
     extern __shared__ unsigned char smem_raw[];
     const AffineQ aq = load_affineq(q_range, q_bits);
     const uint64_t nlo2 = pack2(-aq.p.lo, -aq.p.lo), r2 = pack2(aq.d.r, aq.d.r), nb2 = pack2(aq.d.nb, aq.d.nb),
@@ -331,9 +353,44 @@ k_rbn_stats_q8_nhwc(const float* __restrict__ x, NhwcGeom g, uint32_t* __restric
         if (c >= g.C) break;
         uint32_t a = 0u, b = 0xffffffffu, sm = 0u;
         for (int q = 0; q < g.RL; ++q) { a = max(a, s_mx[q * W + col]); b = min(b, s_mn[q * W + col]); sm += s_sm[q * W + col]; }
+        if (acc_kc) {
+            Q8Acc* dst = acc_kc + (int64_t)k * g.C + c;
+            atomicMax(&dst->kmax, a);
+            atomicMax(&dst->nkmin, ~b);
+            atomicAdd(&dst->sum, (unsigned long long)sm);
+            continue;
+        }
         const int64_t o = (int64_t)blockIdx.x * g.C + c;            // [(k*S+s)][c]
         pkmax[o] = a; pkmin[o] = b; pksum[o] = sm;
     }
+}
+
+// Atomic-combine path: per channel, walk the K chunk accumulators in order - arg rows, chunk extrema and the chunk sums the
+// merge kernel produced, plus the red[3][C] block of k_rbn_stats_nhwc_pack - and reset them.  One thread per channel
+// (coalesced over c); K is small (16).
+__global__ void k_rbn_stats_q8_finish(Q8Acc* acc_kc, int64_t C, int K, int64_t L, const float* q_range, int q_bits, int32_t* amax,
+                                      int32_t* amin, int32_t* amax_kc, int32_t* amin_kc, double* red) {
+    const int64_t c = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (c >= C) return;
+    const QParams p = make_qparams_d((double)__ldg(q_range), (double)__ldg(q_range + 1), q_bits);
+    double smax = 0.0, smin = 0.0, ssum = 0.0;
+    for (int k = 0; k < K; ++k) {
+        const int64_t t = (int64_t)k * C + c;
+        const uint32_t a = acc_kc[t].kmax, b = ~acc_kc[t].nkmin;
+        const unsigned long long sm = acc_kc[t].sum;
+        acc_kc[t].kmax = 0u; acc_kc[t].nkmin = 0u; acc_kc[t].sum = 0ull;
+        const int32_t imx = (int32_t)(k * L + (int64_t)(0xffffffu - (a & 0xffffffu))), imn = (int32_t)(k * L + (int64_t)(b & 0xffffffu));
+        smax += (double)q_affine_deq((float)(a >> 24), p);
+        smin += (double)q_affine_deq((float)(b >> 24), p);
+        ssum += (double)L * (double)p.lo + (double)p.scale * (double)sm;          // as k_rbn_stats_q8_merge
+        if (amax) amax[c * K + k] = imx;
+        if (amin) amin[c * K + k] = imn;
+        if (amax_kc) amax_kc[t] = imx;
+        if (amin_kc) amin_kc[t] = imn;
+    }
+    red[c] = smax;
+    red[C + c] = smin;
+    red[2 * C + c] = ssum;
 }
 
 // merge the S segment partials of every (chunk k, channel c) and leave them in the generic kernel's output format
@@ -382,7 +439,7 @@ __global__ void k_rbn_stats_nhwc_pack(const float* cmax, const float* cmin, cons
 
 extern "C" size_t qb_rangebn_nhwc_ws_bytes(int64_t C, int num_chunks) {
     if (C < 0 || num_chunks < 0) return 0;
-    return (size_t)C * num_chunks * (NH_MAX_SEG * 24 + 16);
+    return NH_ACC_BYTES + (size_t)C * num_chunks * (NH_MAX_SEG * 24 + 16);
 }
 
 static size_t nhwc_smem(const NhwcGeom& g, int vec, int per_elem) { return (size_t)g.RL * g.CT * vec * per_elem; }
@@ -403,6 +460,8 @@ extern "C" int qb_rangebn_stats_nhwc(const float* x, int64_t B, int64_t C, int64
         qb_set_error("qb_rangebn_stats_nhwc: workspace %zu < %zu bytes", ws_bytes, qb_rangebn_nhwc_ws_bytes(C, num_chunks));
         return QB_ERR_WORKSPACE;
     }
+    Q8Acc* acc_kc = static_cast<Q8Acc*>(ws);                          // fixed-size head region, zero between calls
+    ws = static_cast<char*>(ws) + NH_ACC_BYTES;
     const bool vec4 = (C % 4 == 0) && ((reinterpret_cast<uintptr_t>(x) & 15) == 0);
     NhwcGeom g = vec4 ? make_geom<4>(R, C, num_chunks) : make_geom<1>(R, C, num_chunks);
     const size_t n = (size_t)num_chunks * g.S * C;
@@ -419,14 +478,24 @@ extern "C" int qb_rangebn_stats_nhwc(const float* x, int64_t B, int64_t C, int64
     const bool q8 = q_range && q_bits <= 8 && C % 8 == 0 && (reinterpret_cast<uintptr_t>(x) & 31) == 0 && R / num_chunks <= (1 << 24) &&
                     (!x_codes_out || (reinterpret_cast<uintptr_t>(x_codes_out) & 7) == 0);
     if (q8) {
-        NhwcGeom g8 = make_geom<8>(R, C, num_chunks);
+        static const int slots8 = nh_slots(k_rbn_stats_q8_nhwc, (size_t)NH_THREADS * 8 * 12);
+        NhwcGeom g8 = make_geom<8>(R, C, num_chunks, NH_MAX_SEG, slots8);
         if ((size_t)num_chunks * g8.S * C * 12 <= (size_t)C * num_chunks * NH_MAX_SEG * 24) {
             uint32_t* pkmax = static_cast<uint32_t*>(ws);
             uint32_t* pkmin = pkmax + (size_t)num_chunks * g8.S * C;
             uint32_t* pksum = pkmin + (size_t)num_chunks * g8.S * C;
             dim3 grid8((unsigned)(num_chunks * g8.S), (unsigned)((C + g8.tileC - 1) / g8.tileC));
+            if (nk * sizeof(Q8Acc) <= NH_ACC_BYTES) {                // two launches: the segment CTAs combine with integer atomics
+                k_rbn_stats_q8_nhwc<<<grid8, NH_THREADS, (size_t)g8.RL * g8.CT * 8 * 12, st>>>(x, g8, nullptr, nullptr, nullptr, q_range,
+                                                                                          q_bits, x_codes_out, acc_kc);
+                QB_LAUNCH_CHECK();
+                k_rbn_stats_q8_finish<<<(unsigned)((C + 127) / 128), 128, 0, st>>>(acc_kc, C, num_chunks, R / num_chunks, q_range, q_bits,
+                                                                                  amax, amin, amax_kc, amin_kc, red);
+                QB_LAUNCH_CHECK();
+                return QB_OK;
+            }
             k_rbn_stats_q8_nhwc<<<grid8, NH_THREADS, (size_t)g8.RL * g8.CT * 8 * 12, st>>>(x, g8, pkmax, pkmin, pksum, q_range, q_bits,
-                                                                                      x_codes_out);
+                                                                                      x_codes_out, nullptr);
             QB_LAUNCH_CHECK();
             k_rbn_stats_q8_merge<<<(unsigned)((nk + 127) / 128), 128, 0, st>>>(pkmax, pkmin, pksum, C, num_chunks, g8.S, R / num_chunks,
                                                                               q_range, q_bits, amax, amin, amax_kc, amin_kc, cmax,
@@ -615,7 +684,9 @@ extern "C" int qb_rangebn_apply_nhwc(const float* x, const uint8_t* x_codes, flo
         const int64_t R = B * HW;
         NhwcGeom geo = make_geom<8>(R, C, 1, 1 << 20);
         const int ctiles = (int)((C + geo.tileC - 1) / geo.tileC);
-        int64_t want = (148 * 8 + ctiles - 1) / ctiles;                      // ~8 CTAs per SM
+        static const int slots = nh_slots(k_rbn_apply_codes_nhwc, 0);
+        int64_t want = (2 * slots) / ctiles;                                 // two full waves of resident CTAs
+        if (want < 1) want = 1;
         const int64_t max_by_rows = R / ((int64_t)geo.RL * 4) > 0 ? R / ((int64_t)geo.RL * 4) : 1;
         if (want > max_by_rows) want = max_by_rows;
         geo.S = (int)want;
@@ -813,8 +884,9 @@ extern "C" int qb_rangebn_bwd_reduce_nhwc(const float* gq, const float* x, const
         qb_set_error("qb_rangebn_bwd_reduce_nhwc: on-the-fly gradient quantization / x_codes need C %% 8 == 0 and 32-byte alignment");
         return QB_ERR_UNSUPPORTED;
     }
-    NhwcGeom g = vec8 ? make_geom<8>(R, C, 1, NH_MAX_SEG_BWD) : vec4 ? make_geom<4>(R, C, 1, NH_MAX_SEG_BWD)
-                                                                      : make_geom<1>(R, C, 1, NH_MAX_SEG_BWD);
+    static const int slots8 = nh_slots(k_rbn_bwd_reduce_nhwc<8, 2, NOISE_PHILOX>, (size_t)NH_THREADS * 8 * 16);
+    NhwcGeom g = vec8 ? make_geom<8>(R, C, 1, NH_MAX_SEG_BWD, slots8) : vec4 ? make_geom<4>(R, C, 1, NH_MAX_SEG_BWD)
+                                                                              : make_geom<1>(R, C, 1, NH_MAX_SEG_BWD);
     double* part = static_cast<double*>(ws);
     dim3 grid((unsigned)g.S, (unsigned)((C + g.tileC - 1) / g.tileC));
     cudaStream_t st = qb_stream(stream);
@@ -1088,7 +1160,9 @@ extern "C" int qb_rangebn_bwd_apply_fused_nhwc(const float* g, float* dx, int64_
     NhwcGeom geo = make_geom<8>(R, C, Kc, 256);
     {
         const int ctiles = (int)((C + geo.tileC - 1) / geo.tileC);
-        int64_t want = (148 * 8 + (int64_t)Kc * ctiles - 1) / ((int64_t)Kc * ctiles);
+        int sms = qb_sm_count();
+        if (sms <= 0) sms = 148;
+        int64_t want = (int64_t)(sms * 3 * 2) / ((int64_t)Kc * ctiles);      // two full waves at 3 resident CTAs per SM (80 registers)
         const int64_t max_by_rows = geo.L / ((int64_t)geo.RL * 2) > 0 ? geo.L / ((int64_t)geo.RL * 2) : 1;
         if (want > max_by_rows) want = max_by_rows;
         while ((int64_t)Kc * want * ctiles > 4096 && want > 1) --want;

@@ -50,6 +50,21 @@ def _relu(q, inplace=True):
     return nn.ReLU(inplace=inplace)
 
 
+def _bn_relu(bn, relu, x, res=None):
+    """``relu(bn(x))`` / ``y = bn(x); y += res; relu(y)`` (models/resnet_quantized.py:47-75, 100-112); one fused pass when the
+    modules are this package's (RangeBN.forward_relu), the plain composition for any other module namespace (the oracle)."""
+    if hasattr(bn, "forward_relu"):
+        return bn.forward_relu(x, relu, res)
+    y = bn(x)
+    if res is None:
+        return relu(y)
+    res = res() if callable(res) else res              # after bn(x), as in the reference (order of the noise draws in backward)
+    if hasattr(relu, "add_relu"):
+        return relu.add_relu(y, res)
+    y += res
+    return relu(y)
+
+
 class _Identity(nn.Module):
     def forward(self, x):
         return x
@@ -69,13 +84,9 @@ class BasicBlock(nn.Module):
         self._last_bn = "bn2"
 
     def forward(self, x):
-        y = self.relu(self.bn1(self.conv1(x)))
-        y = self.bn2(self.conv2(y))
-        res = x if self.downsample is None else self.downsample(x)
-        if hasattr(self.relu, "add_relu"):              # native glue: residual add + ReLU + next layer's statistics
-            return self.relu.add_relu(y, res)
-        y += res
-        return self.relu(y)
+        y = _bn_relu(self.bn1, self.relu, self.conv1(x))
+        res = (lambda: x) if self.downsample is None else (lambda: self.downsample(x))
+        return _bn_relu(self.bn2, self.relu, self.conv2(y), res)   # native: normalise + add + ReLU + next layer's statistics
 
 
 class Bottleneck(nn.Module):
@@ -94,14 +105,10 @@ class Bottleneck(nn.Module):
         self._last_bn = "bn3"
 
     def forward(self, x):
-        y = self.relu(self.bn1(self.conv1(x)))
-        y = self.relu(self.bn2(self.conv2(y)))
-        y = self.bn3(self.conv3(y))
-        res = x if self.downsample is None else self.downsample(x)
-        if hasattr(self.relu, "add_relu"):
-            return self.relu.add_relu(y, res)
-        y += res
-        return self.relu(y)
+        y = _bn_relu(self.bn1, self.relu, self.conv1(x))
+        y = _bn_relu(self.bn2, self.relu, self.conv2(y))
+        res = (lambda: x) if self.downsample is None else (lambda: self.downsample(x))
+        return _bn_relu(self.bn3, self.relu, self.conv3(y), res)
 
 
 class QResNet(nn.Module):
@@ -220,7 +227,9 @@ class _DWSeparable(nn.Module):
             _qconv(q, cin, cout, 1), _qbn(q, cout), _relu(q, False))
 
     def forward(self, x):
-        return self.components(x)
+        c = self.components
+        x = _bn_relu(c[1], c[2], c[0](x))
+        return _bn_relu(c[4], c[5], c[3](x))
 
 
 class QMobileNet(nn.Module):
@@ -254,7 +263,11 @@ class QMobileNet(nn.Module):
         self.fc.bias.data.zero_()
 
     def forward(self, x):
-        x = self.avg_pool(self.features(x))
+        f = self.features
+        x = _bn_relu(f[1], f[2], f[0](x))
+        for i in range(3, len(f)):
+            x = f[i](x)
+        x = self.avg_pool(x)
         return self.fc(x.view(x.size(0), -1))
 
     def regularization(self, weight_decay=4e-5):

@@ -877,7 +877,7 @@ class _RangeBNFn(Function):
 
     @staticmethod
     def forward(ctx, xq, gamma, beta, running_mean, running_var, training, momentum, num_chunks, eps, bits, bits_grad,
-                q_range, q_bits):
+                q_range, q_bits, deferred=None):
         xq = _abi._f32c(xq, "x")
         nhwc = _abi.is_nhwc(xq)
         B, Cn = xq.shape[0], xq.shape[1]
@@ -903,12 +903,19 @@ class _RangeBNFn(Function):
             ctx.local_chunks = local_chunks
         vec = _abi.rangebn_finalize(red, Cn, chunks_global, count, chunk_len, eps, momentum, training, bits, gamma, beta,
                                     running_mean, running_var)
-        out = _abi.rangebn_apply(xq, B, Cn, HW, vec, gamma is not None, beta is not None, nhwc=nhwc, q_range=q_range,
-                                 q_bits=q_bits, x_codes=xc)
         ctx.dims = (B, Cn, HW, chunks_global, count, chunk_len, training, bits_grad, gamma is not None, beta is not None)
         ctx.nhwc, ctx.q_bits = nhwc, q_bits
         ctx.save_for_backward(None if xc is not None else xq, vec, amax, amin, q_range, xc)
-        return out
+        if deferred is not None:
+            # RangeBN.forward_relu: the normalisation runs later, fused with the ReLU (_ApplyReLUFn); this node only owns the
+            # statistics and the RangeBN backward.  Its output is a storage-less placeholder of the right shape.
+            if xc is None:
+                raise _abi.QB200Error("RangeBN.forward_relu: the fused pass needs the uint8 codes of the statistics pass")
+            deferred.update(xc=xc, vec=vec, like=xq, dims=(B, Cn, HW), has_gamma=gamma is not None, has_beta=beta is not None,
+                            q_range=q_range, q_bits=q_bits)
+            return xq.new_empty(1).expand(xq.shape)
+        return _abi.rangebn_apply(xq, B, Cn, HW, vec, gamma is not None, beta is not None, nhwc=nhwc, q_range=q_range,
+                                  q_bits=q_bits, x_codes=xc)
 
     @staticmethod
     def backward(ctx, g):
@@ -939,7 +946,31 @@ class _RangeBNFn(Function):
             dx, dgamma, dbeta = _abi.rangebn_backward(gq, xq, B, Cn, HW, lc, count, chunk_len, training, vec, has_gamma,
                                                       amax, amin, **common)
         return (dx if ctx.needs_input_grad[0] else None, dgamma if has_gamma else None, dbeta if has_beta else None,
-                None, None, None, None, None, None, None, None, None, None)
+                None, None, None, None, None, None, None, None, None, None, None)
+
+
+class _ApplyReLUFn(Function):
+    """Second half of RangeBN.forward_relu: normalisation from the codes [+ residual] + ReLU + the statistics of the result
+    in one pass (qb_rangebn_apply_relu_measure).  ``h`` is the placeholder output of the _RangeBNFn node that ran the
+    statistics; the masked gradient goes back through it (and to the residual).  Keeping the RangeBN backward in its own
+    node - created where the reference calls ``bn(x)`` - keeps autograd's execution order, hence the order of the
+    stochastic-rounding noise draws, that of the unfused graph."""
+
+    @staticmethod
+    def forward(ctx, h, residual, d):
+        from . import glue
+        B, Cn, HW = d["dims"]
+        out, glue._last["stats"] = _abi.rangebn_apply_relu_measure(d["xc"], d["like"], B, Cn, HW, d["vec"], d["has_gamma"],
+                                                                   d["has_beta"], d["q_range"], d["q_bits"], residual=residual)
+        ctx.save_for_backward(out)
+        return out
+
+    @staticmethod
+    def backward(ctx, g):
+        from . import glue
+        (out,) = ctx.saved_tensors
+        dg = glue._relu_backward(g.contiguous(memory_format=torch.channels_last), out)
+        return dg, (dg if ctx.needs_input_grad[1] else None), None
 
 
 class RangeBN(nn.Module):
@@ -985,6 +1016,41 @@ class RangeBN(nn.Module):
                                self.momentum, self.num_chunks, self.eps, self.num_bits, self.num_bits_grad, q_range, q_bits)
         if two_d:
             out = out.squeeze(-1).squeeze(-1)
+        return out
+
+    def forward_relu(self, x, relu, residual=None):
+        """``relu(self(x))`` - or, with ``residual``, ``out = self(x); out += residual; relu(out)``, the tail of a residual
+        block (models/resnet_quantized.py:62-68, 105-112) - with the normalisation, the add, the clamp and the statistics of
+        the next QuantMeasure in ONE pass over the uint8 codes (qb_rangebn_apply_relu_measure): the normalised tensor is
+        never written.  ``residual`` may be a callable (the block's downsample branch): it is evaluated AFTER the
+        statistics of this module, where the reference evaluates it.  Same values and gradients as the composition, which is
+        what runs whenever the fused pass does not apply."""
+        from . import glue
+        qi = self.quantize_input
+        ok = (isinstance(relu, glue.ReLU) and relu.training and self.training and x.dim() == 4 and x.is_cuda
+              and x.dtype == torch.float32 and _abi.is_nhwc(x) and qi.enable_quant and qi.num_bits <= 8 and x.shape[1] % 8 == 0
+              and x.numel() < 2 ** 32 and x.data_ptr() % 32 == 0 and torch.is_grad_enabled())
+        if not ok:
+            out = self(x)
+            if residual is None:
+                return relu(out)
+            res = residual() if callable(residual) else residual
+            if hasattr(relu, "add_relu"):
+                return relu.add_relu(out, res)
+            out += res
+            return relu(out)
+        d = {}
+        h = _RangeBNFn.apply(x, self.weight, self.bias, self.running_mean, self.running_var, self.training, self.momentum,
+                             self.num_chunks, self.eps, self.num_bits, self.num_bits_grad, qi.measure(x), qi.num_bits, d)
+        res = residual() if callable(residual) else residual
+        if res is not None:
+            res = res.contiguous(memory_format=torch.channels_last)
+        out = _ApplyReLUFn.apply(h, res, d)
+        stats, glue._last["stats"] = glue._last["stats"], None
+        if stats is not None:
+            _stash_fwd_stats(out, stats)
+        if out.requires_grad:
+            glue._relu_out["t"] = (out, out._version)
         return out
 
 

@@ -151,6 +151,55 @@ def test_rangebn_backward_takes_the_relu_range(lib):
     assert torch.equal(res[0][0], res[1][0]) and torch.equal(res[0][1], res[1][1])
 
 
+@pytest.mark.parametrize("shape", [(16, 64, 14, 14), (32, 24, 6, 6), (16, 1024, 2, 2), (16, 48, 5, 4)])
+@pytest.mark.parametrize("with_residual", [False, True])
+def test_rangebn_forward_relu_equals_the_composition(lib, shape, with_residual):
+    """RangeBN.forward_relu (qb_rangebn_apply_relu_measure: normalise [+ residual] + ReLU + next layer's statistics in one
+    pass over the codes) == relu(bn(x)) / relu.add_relu(bn(x), res) bit for bit: output, stashed statistics, running
+    buffers, and - under the same injected noise - every gradient.  Channel counts that divide the kernel's 1024-element
+    thread row (64, 1024) and ones that do not (24, 48)."""
+    from qtorch_b200 import glue, quantize as Q
+    torch.manual_seed(11)
+    C = shape[1]
+    x = (torch.randn(shape, device=DEV) * 2).contiguous(memory_format=torch.channels_last)
+    r = torch.randn(shape, device=DEV).contiguous(memory_format=torch.channels_last)
+    go = torch.randn(shape, device=DEV).contiguous(memory_format=torch.channels_last)
+    noise = torch.rand(shape, device=DEV) - 0.5
+    state = Q.RangeBN(C).state_dict()
+    res = []
+    for fused in (True, False):
+        bn = Q.RangeBN(C)
+        bn.load_state_dict(state)
+        bn = bn.to(DEV).train()
+        relu = glue.ReLU(inplace=True).train()
+        xi, ri = x.clone().requires_grad_(), r.clone().requires_grad_()
+        prev = Q.set_noise_provider(lambda shp: noise.clone())
+        try:
+            lib.profile_begin()
+            if fused:
+                y = bn.forward_relu(xi, relu, ri if with_residual else None)
+            else:
+                y = relu.add_relu(bn(xi), ri) if with_residual else relu(bn(xi))
+            names = [n[0] for n in lib.profile_end()]
+            stats = Q._take_fwd_stats(y.detach())
+            out = y.detach().clone()
+            y.backward(go)
+        finally:
+            Q.set_noise_provider(prev)
+        res.append(dict(out=out, stats=stats.clone(), names=names, dx=xi.grad.clone(), dr=ri.grad.clone() if with_residual else None,
+                        dgamma=bn.weight.grad.clone(), dbeta=bn.bias.grad.clone(),
+                        buffers={k: v.clone() for k, v in bn.state_dict().items()}))
+    f, c = res
+    assert "qb_rangebn_apply_relu_measure" in f["names"] and "qb_rangebn_apply_nhwc" not in f["names"], f["names"]
+    assert "qb_rangebn_apply_nhwc" in c["names"]
+    assert torch.equal(f["out"], c["out"])
+    assert torch.equal(f["stats"], c["stats"]), (f["stats"], c["stats"])
+    for k in ("dx", "dgamma", "dbeta") + (("dr",) if with_residual else ()):
+        assert torch.equal(f[k], c[k]), k
+    for k, v in c["buffers"].items():
+        assert torch.equal(f["buffers"][k], v), k
+
+
 @pytest.mark.parametrize("shape", [(4, 64, 56, 56), (2, 16, 9, 11), (3, 8, 4, 4)])
 def test_relu_maxpool_fused_backward(lib, shape):
     """glue.ReLU -> glue.MaxPool2d(3, 2, 1): the pooling backward yields the gradient w.r.t. the ReLU input directly (one

@@ -99,7 +99,8 @@ def test_affine_empty(lib):
     assert lib.fakequant_affine(x, 8, lo=0.0, hi=1.0).numel() == 0
 
 
-@pytest.mark.parametrize("rows,cols", [(1, 1), (64, 27), (64, 147), (512, 4608), (1000, 512), (7, 4099)])
+@pytest.mark.parametrize("rows,cols", [(1, 1), (64, 27), (64, 147), (512, 4608), (1000, 512), (7, 4099),
+                                       (5, 8192), (3, 20004), (4, 9001), (2, 65536 + 6)])    # >= 8192: cluster-split rows
 def test_rows_vs_oracle(lib, rows, cols):
     gen = torch.Generator().manual_seed(rows * 7 + cols)
     w = torch.randn(rows, cols, generator=gen) * 0.1

@@ -69,10 +69,12 @@ def test_benchmarked_model_train_step_vs_oracle(name):
     x, y = seeding.synthetic_batch((16, 3, 224, 224), 1000, seed=5)
     crit = torch.nn.CrossEntropyLoss()
     first = {}
-    bn_ref = ref.bn1 if name == "resnet18" else ref.features[1]
-    bn_mod = mod.bn1 if name == "resnet18" else mod.features[1]
-    bn_ref.register_forward_hook(lambda m, i, o: first.__setitem__("ref", o.detach().clone()))
-    bn_mod.register_forward_hook(lambda m, i, o: first.__setitem__("cuda", o.detach().cpu().clone()))
+    if name == "resnet18":
+        ref.bn1.register_forward_hook(lambda m, i, o: first.__setitem__("ref", o.detach().clone()))
+        mod.bn1.register_forward_hook(lambda m, i, o: first.__setitem__("cuda", o.detach().cpu().clone()))
+    else:      # MobileNet's first RangeBN runs fused with its ReLU (RangeBN.forward_relu): compare what the next block receives
+        ref.features[3].register_forward_pre_hook(lambda m, i: first.__setitem__("ref", i[0].detach().clone()))
+        mod.features[3].register_forward_pre_hook(lambda m, i: first.__setitem__("cuda", i[0].detach().cpu().clone()))
     log = []
 
     def record(shape):

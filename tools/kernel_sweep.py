@@ -33,7 +33,7 @@ def main():
         pass
     dev = torch.device("cuda")
     rows = []
-    exps = [int(a) for a in sys.argv[1:]] or [18, 22, 26, 28]
+    exps = [int(a) for a in sys.argv[1:]] or [18, 20, 22, 24, 26, 28, 30]       # 1 MB ... 4 GB of fp32
     for e in exps:
         n = 1 << e
         x = torch.randn(n, device=dev) * 3
@@ -59,12 +59,19 @@ def main():
             ms = timeit(fn)
             gbs = bpe * n / ms / 1e6
             rows.append(dict(kernel=name, log2n=e, ms=round(ms, 4), gbs=round(gbs, 1), frac=round(gbs / peak, 3)))
-            print("%-28s n=2^%d  %8.4f ms  %8.1f GB/s  %.3f of measured %.0f" % (name, e, ms, gbs, gbs / peak, peak), flush=True)
+            print("%-28s n=2^%d  %8.4f ms  %8.1f GB/s  %.3f of measured %.0f  %.3f of the 8000 GB/s datasheet"
+                  % (name, e, ms, gbs, gbs / peak, peak, gbs / 8000.0), flush=True)
         del x, y, codes, xr
-    for rows_, cols in [(64, 1 << 16), (512, 4608), (1000, 512)]:
-        w = torch.randn(rows_, cols, device=dev)
-        ms = timeit(lambda: _abi.fakequant_rows(w, 8))
-        print("rows %dx%d  %.4f ms  %.1f GB/s" % (rows_, cols, ms, 8 * w.numel() / ms / 1e6), flush=True)
+    # per-channel ranges (quantize.py:318-334): C rows of `cols` elements, range from the data + quantize (8 B/elem)
+    for rows_, cols in [(64, 1 << 16), (64, 1 << 20), (512, 1 << 17), (1000, 1 << 16), (512, 4608), (1000, 512)]:
+        for bits in (8, 4):
+            w = torch.randn(rows_, cols, device=dev)
+            out = torch.empty_like(w)
+            ms = timeit(lambda: _abi.fakequant_rows(w, bits, out=out))
+            gbs = 8 * w.numel() / ms / 1e6
+            rows.append(dict(kernel="rows_%dbit" % bits, rows=rows_, cols=cols, ms=round(ms, 4), gbs=round(gbs, 1), frac=round(gbs / peak, 3)))
+            print("per-channel %d-bit  %5d x %-8d %8.4f ms  %8.1f GB/s  %.3f of measured  %.3f of datasheet"
+                  % (bits, rows_, cols, ms, gbs, gbs / peak, gbs / 8000.0), flush=True)
     out = os.path.join(os.path.dirname(__file__), "..", "gpurun_out")
     os.makedirs(out, exist_ok=True)
     json.dump(rows, open(os.path.join(out, "kernel_sweep.json"), "w"), indent=1)
