@@ -201,7 +201,11 @@ size_t qb_rangebn_bwd_nhwc_ws_bytes(int64_t C);
 int qb_rangebn_bwd_reduce_nhwc(const float* gq, const float* x, const uint8_t* x_codes, int64_t B, int64_t C, int64_t HW,
                                double* sg, double* sgx, const float* q_range, int q_bits, const float* g_range, int g_bits,
                                const float* noise, int stochastic, uint64_t seed, uint64_t offset,
-                               const uint64_t* step_dev, uint8_t* gq_codes_out, void* ws, size_t ws_bytes, void* stream);
+                               const uint64_t* step_dev, uint8_t* gq_codes_out, const uint8_t* relu_bits, void* ws,
+                               size_t ws_bytes, void* stream);
+/* relu_bits (optional): gq is the gradient w.r.t. the OUTPUT of the nn.ReLU that follows this RangeBN and relu_bits the
+ * bit mask qb_rangebn_apply_relu_measure wrote; the ReLU backward (threshold_backward) then happens on the fly and the
+ * masked gradient is never written.  g_range must be the range of the MASKED gradient (qb_relu_bwd_minmax_bits, dx = NULL). */
 /* dx = (Q(g)*qgamma)*qscale + a, +-e at the chunk arg-max/arg-min rows, in ONE pass, plus min/max of the final dx
  * (gq_codes: optional uint8 codes of Q(g) written by qb_rangebn_bwd_reduce_nhwc's gq_codes_out - the pass then reads
  * 1 B/elem and only dequantizes instead of reading g and regenerating the noise;
@@ -353,16 +357,24 @@ int qb_relu_bwd_minmax(const float* grad_out, const float* relu_out, float* dx, 
  * two torch ops do) plus the statistics block of y. */
 int qb_add_relu_measure(const float* x, const float* r, float* y, int64_t B, int64_t inner, double* stats, void* ws,
                         size_t ws_bytes, void* stream);
+/* qb_relu_bwd_minmax with the ReLU output given as a bit mask (bit e%8 of byte e/8 set = the gradient passes; written by
+ * qb_rangebn_apply_relu_measure): 8.125 B/elem instead of 12.  dx == NULL: only range_out = {min, max} of the masked
+ * gradient (4.125 B/elem), for a consumer that applies the mask itself (qb_rangebn_bwd_reduce_nhwc's relu_bits).
+ * n % 8 == 0, 32-byte aligned tensors. */
+int qb_relu_bwd_minmax_bits(const float* grad_out, const uint8_t* relu_bits, float* dx, int64_t n, float* range_out, void* ws,
+                            size_t ws_bytes, void* stream);
 /* RangeBN normalisation (models/modules/quantize.py:488-499) + the nn.ReLU that follows it in every block of
  * models/resnet_quantized.py:47-75 / models/mobilenet_quantized.py:21-60 [+ the residual add in front of that ReLU, residual
  * != NULL] + the statistics block of the result, in ONE pass over the uint8 codes of RangeBN's fake-quantized input that
  * qb_rangebn_stats_nhwc wrote:  y = relu(((deq(code) - mean_c) * qscale_c) * qgamma_c + qbeta_c [+ residual]).
  * Bit-identical to qb_rangebn_apply_nhwc followed by qb_relu_measure / qb_add_relu_measure (values and statistics); moves
  * 5 (+4) B/elem instead of 13 (+4): the normalised tensor is never written.  Channels-last, C % 4 == 0, q_bits <= 8,
- * 16-byte aligned fp32 tensors; qgamma / qbeta may be NULL; ws = qb_measure_ws_bytes(B). */
+ * 16-byte aligned fp32 tensors; qgamma / qbeta may be NULL; ws = qb_measure_ws_bytes(B).  relu_bits_out (optional, H*W*C % 8
+ * == 0): bit e%8 of byte e/8 = "y[e] is not <= 0" - all the ReLU backward needs, so y need not be kept for it. */
 int qb_rangebn_apply_relu_measure(const uint8_t* x_codes, const float* residual, float* y, int64_t B, int64_t C, int64_t HW,
                                   const float* mean, const float* qscale, const float* qgamma, const float* qbeta,
-                                  const float* q_range, int q_bits, double* stats, void* ws, size_t ws_bytes, void* stream);
+                                  const float* q_range, int q_bits, uint8_t* relu_bits_out, double* stats, void* ws,
+                                  size_t ws_bytes, void* stream);
 int qb_maxpool2d_nhwc_fwd(const float* x, float* out, uint8_t* idx, int64_t B, int64_t H, int64_t W, int64_t C, int k,
                           int stride, int pad, void* stream);
 int qb_maxpool2d_nhwc_bwd(const float* grad_out, const uint8_t* idx, float* dx, int64_t B, int64_t H, int64_t W, int64_t C,
@@ -455,6 +467,10 @@ int qb_l2_sumsq_noalloc(const void* const* w, const int64_t* sizes, int count, d
 /* Hardware probe used by tools/umma_shift_probe.py (UMMA descriptors that start inside an 8-row swizzle atom); not on any
  * product path. */
 int qb_debug_umma_shift(const uint16_t* a, const uint16_t* b, float* out, int mn, int r0, int use_boff, void* stream);
+/* Tensor-pipe rate probe (tools/umma_rate_probe.py): `blocks` CTAs each issue n back-to-back kind::f16 MMAs (M 128, N, K 16) on
+ * zero-filled shared memory and report elapsed cycles; mode bits: 1 A MN-major, 2 B MN-major, 4 walk a K window, 8 A starts
+ * inside a swizzle atom.  Not on any product path. */
+int qb_debug_umma_rate(long long* cycles, int blocks, int n, int N, int mode, void* stream);
 size_t qb_conv_wgrad_ws_bytes(int64_t B, int64_t H, int64_t W, int64_t Cin, int64_t Cout, int kh, int kw, int stride, int pad);
 int qb_conv_wgrad(const uint16_t* g_hi, const uint16_t* g_lo, const float* g_f32, const uint16_t* x16, float* dw, float* db,
                   int64_t B, int64_t H, int64_t W, int64_t Cin, int64_t Cout, int kh, int kw, int stride, int pad,

@@ -27,7 +27,7 @@ PROTOTYPES = {
     "qb_measure_stats": (_i32, [_p, _i64, _i64, _p, _p, _sz, _p]),
     "qb_relu_measure": (_i32, [_p, _p, _i64, _i64, _p, _p, _sz, _p]),
     "qb_add_relu_measure": (_i32, [_p, _p, _p, _i64, _i64, _p, _p, _sz, _p]),
-    "qb_rangebn_apply_relu_measure": (_i32, [_p, _p, _p, _i64, _i64, _i64, _p, _p, _p, _p, _p, _i32, _p, _p, _sz, _p]),
+    "qb_rangebn_apply_relu_measure": (_i32, [_p, _p, _p, _i64, _i64, _i64, _p, _p, _p, _p, _p, _i32, _p, _p, _p, _sz, _p]),
     "qb_relu_bwd_minmax": (_i32, [_p, _p, _p, _i64, _p, _p, _sz, _p]),
     "qb_measure_finalize": (_i32, [_p, _p, _p, _p, _p, _p, _dbl, _i32, _i32, _i32, _p, _p]),
     "qb_fakequant_affine": (_i32, [_p, _p, _p, _i64, _i32, _p, _dbl, _dbl, _i32, _p]),
@@ -53,7 +53,8 @@ PROTOTYPES = {
     "qb_rangebn_apply_nhwc": (_i32, [_p, _p, _p, _i64, _i64, _i64, _p, _p, _p, _p, _p, _i32, _p]),
     "qb_rangebn_bwd_nhwc_ws_bytes": (_sz, [_i64]),
     "qb_rangebn_bwd_reduce_nhwc": (_i32, [_p, _p, _p, _i64, _i64, _i64, _p, _p, _p, _i32, _p, _i32, _p, _i32, _u64, _u64, _p,
-                                          _p, _p, _sz, _p]),
+                                          _p, _p, _p, _sz, _p]),
+    "qb_relu_bwd_minmax_bits": (_i32, [_p, _p, _p, _i64, _p, _p, _sz, _p]),
     "qb_rangebn_bwd_apply_fused_nhwc": (_i32, [_p, _p, _i64, _i64, _i64, _i32, _p, _p, _p, _p, _p, _p, _p, _i32, _p, _i32,
                                                _u64, _u64, _p, _p, _p, _p, _sz, _p]),
     "qb_rangebn_bwd_apply_nhwc": (_i32, [_p, _p, _i64, _i64, _i64, _i32, _p, _p, _p, _p, _p, _p, _p]),
@@ -97,6 +98,7 @@ PROTOTYPES = {
     "qb_l2_grad": (_i32, [_p, _p, _p, _i32, _dbl, _p, _p]),
     "qb_sgd_step": (_i32, [_p, _p, _p, _p, _i32, _dbl, _dbl, _dbl, _i32, _p]),
     "qb_debug_umma_shift": (_i32, [_p, _p, _p, _i32, _i32, _i32, _p]),
+    "qb_debug_umma_rate": (_i32, [_p, _i32, _i32, _i32, _i32, _p]),
     "qb_wt_pack": (_i32, [_p, _p, _i64, _i64, _i32, _p]),
     "qb_conv_dgrad": (_i32, [_p, _p, _p, _p, _i64, _i64, _i64, _i64, _i64, _i32, _i32, _i32, _i32, _p, _i32, _flt, _p]),
     "qb_conv_wgrad_ws_bytes": (_sz, [_i64, _i64, _i64, _i64, _i64, _i32, _i32, _i32, _i32]),
@@ -141,7 +143,7 @@ _profile = None       # list of (name, algorithmic_bytes, start_event, end_event
 
 # kernels enqueued per C call
 _NLAUNCH = {"qb_rangebn_stats": 2, "qb_rangebn_bwd_reduce": 2, "qb_rangebn_bwd_apply": 2,
-            "qb_conv_i8_fwd": 2, "qb_conv_wgrad": 3, "qb_conv_dw_wgrad": 2, "qb_conv_stem_fwd": 2, "qb_conv_stem_wgrad": 2, "qb_rangebn_stats_nhwc": 3, "qb_rangebn_bwd_reduce_nhwc": 2, "qb_rangebn_bwd_apply_nhwc": 2}
+            "qb_conv_i8_fwd": 2, "qb_conv_wgrad": 3, "qb_conv_dw_wgrad": 2, "qb_conv_stem_fwd": 2, "qb_conv_stem_wgrad": 2, "qb_rangebn_stats_nhwc": 2, "qb_rangebn_bwd_reduce_nhwc": 2, "qb_rangebn_apply_relu_measure": 1, "qb_rangebn_bwd_apply_nhwc": 2}
 
 
 _next_ops = 0          # integer operations (2*M*N*K) of the next tensor-core call, set by the conv / GEMM wrappers
@@ -268,6 +270,18 @@ def relu_bwd_minmax(g, out):
     return dx, rng
 
 
+def relu_bwd_minmax_bits(g, bits, want_dx=True):
+    """(dx | None, range): ReLU backward from the bit mask of qb_rangebn_apply_relu_measure; ``want_dx=False`` yields only
+    the range of the masked gradient (the consumer applies the mask itself)."""
+    lib = load()
+    dx = torch.empty_like(g) if want_dx else None
+    rng = torch.empty(2, dtype=torch.float32, device=g.device)
+    ws = workspace("minmax", lib.qb_minmax_ws_bytes(), g.device)
+    _run("qb_relu_bwd_minmax_bits", (8 if want_dx else 4) * g.numel() + g.numel() // 8, _ptr(g), _ptr(bits), _ptr(dx), g.numel(),
+         _ptr(rng), _ptr(ws), ws.numel(), _stream())
+    return dx, rng
+
+
 def add_relu_measure(x, r, out=None):
     """out = relu(x + r) (out=None: in place in x) and the QuantMeasure statistics (double[8]) of the result, one pass.
     x and r must share shape and memory layout."""
@@ -286,9 +300,10 @@ def add_relu_measure(x, r, out=None):
     return out, stats
 
 
-def rangebn_apply_relu_measure(x_codes, like, B, Cn, HW, vec, has_gamma, has_beta, q_range, q_bits, residual=None):
-    """-> (out, stats): relu(RangeBN-normalise(codes) [+ residual]) and the QuantMeasure statistics of the result in one pass
-    (qb_rangebn_apply_relu_measure); ``like`` gives shape / layout of the output (the raw RangeBN input)."""
+def rangebn_apply_relu_measure(x_codes, like, B, Cn, HW, vec, has_gamma, has_beta, q_range, q_bits, residual=None, want_bits=False):
+    """-> (out, stats[, bits]): relu(RangeBN-normalise(codes) [+ residual]) and the QuantMeasure statistics of the result in
+    one pass (qb_rangebn_apply_relu_measure); ``like`` gives shape / layout of the output (the raw RangeBN input);
+    ``want_bits``: also the 1-bit-per-element mask "out is not <= 0" for the ReLU backward."""
     lib = load()
     out = torch.empty_like(like)
     if residual is not None:
@@ -298,9 +313,12 @@ def rangebn_apply_relu_measure(x_codes, like, B, Cn, HW, vec, has_gamma, has_bet
     stats = torch.empty(8, dtype=torch.float64, device=like.device)
     ws = workspace("measure", lib.qb_measure_ws_bytes(B), like.device)
     n = B * Cn * HW
+    bits = torch.empty(n // 8, dtype=torch.uint8, device=like.device) if (want_bits and (HW * Cn) % 8 == 0) else None
     _run("qb_rangebn_apply_relu_measure", (9 if residual is not None else 5) * n, _ptr(x_codes), _ptr(residual), _ptr(out), B, Cn, HW,
          _ptr(vec[0]), _ptr(vec[2]), _ptr(vec[3]) if has_gamma else None, _ptr(vec[4]) if has_beta else None, _ptr(q_range),
-         int(q_bits), _ptr(stats), _ptr(ws), ws.numel(), _stream())
+         int(q_bits), _ptr(bits), _ptr(stats), _ptr(ws), ws.numel(), _stream())
+    if want_bits:
+        return out, stats, bits
     return out, stats
 
 
@@ -481,7 +499,7 @@ def rangebn_apply(x, B, Cn, HW, vec, has_gamma, has_beta, out=None, nhwc=False, 
 
 def rangebn_backward(gq, xq, B, Cn, HW, num_chunks, count, chunk_len, training, vec, has_gamma, amax, amin,
                      reduce_hook=None, chunks_global=None, nhwc=False, q_range=None, q_bits=8, grad_quant=None,
-                     want_dx_range=False, x_codes=None):
+                     want_dx_range=False, x_codes=None, relu_bits=None):
     """Returns (dx, dgamma, dbeta[, dx_range]).  ``reduce_hook(sums)`` may all-reduce the double[2*C] sums in place
     (batch-sharded training); ``num_chunks`` is this rank's chunk count (layout of amax/amin),
     ``chunks_global`` the count the chunk-mean was taken over.
@@ -511,7 +529,7 @@ def rangebn_backward(gq, xq, B, Cn, HW, num_chunks, count, chunk_len, training, 
     if nhwc:
         nb = 4 + (1 if x_codes is not None else 4) + (1 if codes is not None else 0)
         _run("qb_rangebn_bwd_reduce_nhwc", nb * B * Cn * HW, _ptr(gq), _ptr(xq), _ptr(x_codes), B, Cn, HW, _ptr(sums[:Cn]),
-             _ptr(sums[Cn:]), _ptr(q_range), int(q_bits), *gqa, _ptr(codes), _ptr(ws), ws.numel(), _stream())
+             _ptr(sums[Cn:]), _ptr(q_range), int(q_bits), *gqa, _ptr(codes), _ptr(relu_bits), _ptr(ws), ws.numel(), _stream())
     else:
         if q_range is not None or x_codes is not None:
             raise QB200Error("rangebn_backward: on-the-fly input quantization / x_codes are channels-last features")

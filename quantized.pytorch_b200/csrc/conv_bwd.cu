@@ -492,7 +492,8 @@ k_conv_dgrad_flat(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
     const int tiles_n = (g.Cn + BN - 1) / BN;
     const int total = tiles_m * tiles_n;
     constexpr uint32_t ACC = SBS ? (2 * BN < 32 ? 32 : 2 * BN) : (BN < 32 ? 32 : BN);
-    constexpr uint32_t TMEM_COLS = 4 * ACC;                     // 2 sets x 2 accumulators
+    constexpr uint32_t JMAX = ACC >= 256 ? 1 : 2;               // accumulators per set (a strip is <= 128 * JMAX rows)
+    constexpr uint32_t TMEM_COLS = 2 * JMAX * ACC;              // 2 sets x JMAX accumulators
 
     if (warp == 0 && lane == 0) {
         tma_prefetch_desc(&tmap_a);
@@ -553,7 +554,7 @@ k_conv_dgrad_flat(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
             const int set = it & 1;
             mbar_wait_trap(&tempty_bar[set], ((it >> 1) & 1) ^ 1);
             tc_fence_after_sync();
-            const uint32_t d0 = tmem_base + (uint32_t)(set * 2) * ACC;
+            const uint32_t d0 = tmem_base + (uint32_t)set * JMAX * ACC;
             for (int kb = 0; kb < g.kblocks; ++kb, ++ia) {
                 const int sa = ia & 1;
                 mbar_wait_trap(&a_full[sa], (ia >> 1) & 1);
@@ -620,7 +621,7 @@ k_conv_dgrad_flat(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
             const int set = it & 1;
             mbar_wait_trap(&tfull_bar[set], (it >> 1) & 1);
             tc_fence_after_sync();
-            const uint32_t t_addr = tmem_base + (uint32_t)(set * 2 + j) * ACC + ((uint32_t)(sub * 32) << 16);
+            const uint32_t t_addr = tmem_base + ((uint32_t)set * JMAX + (uint32_t)j) * ACC + ((uint32_t)(sub * 32) << 16);
 #pragma unroll 1
             for (int cs = 0; cs < nslabs; ++cs, ++slab) {
                 uint32_t r[32];
@@ -685,7 +686,7 @@ static int dgrad_flat_launch(const CUtensorMap& ta, const CUtensorMap& tw, const
 
 // Strip geometry of one parity class; returns the dynamic shared memory it needs, 0 if the flat form does not apply.
 static size_t dgrad_flat_geom(DflatGeom& g, int B, int Hc, int Wc, int Cn, int Ck, int BK, int BN, const int* dh, const int* dw,
-                              const int* wtap, int ntaps) {
+                              const int* wtap, int ntaps, int max_rows = 256) {
     memset(&g, 0, sizeof(g));
     int dh_min = dh[0], dh_max = dh[0], dw_min = dw[0], dw_max = dw[0];
     for (int i = 1; i < ntaps; ++i) {
@@ -703,17 +704,17 @@ static size_t dgrad_flat_geom(DflatGeom& g, int B, int Hc, int Wc, int Cn, int C
     const int ext_w = pos(dw_max) > pos(-dw_min) ? pos(dw_max) : pos(-dw_min);
     const int ext_h = pos(dh_max) > pos(-dh_min) ? pos(dh_max) : pos(-dh_min);
     g.Wp = Wc + ext_w;
-    if (g.Wp > 256) return 0;
+    if (g.Wp > max_rows) return 0;
     const int Hp = Hc + ext_h;
-    if (Hp * g.Wp <= 256) {                      // image mode: whole padded images
+    if (Hp * g.Wp <= max_rows) {                      // image mode: whole padded images
         g.RH = g.RHo = Hp;
-        g.TN = 256 / (Hp * g.Wp);
+        g.TN = max_rows / (Hp * g.Wp);
         if (g.TN > B) g.TN = B;
         g.TH = Hc;
         g.tiles_h = 1;
     } else {                                     // row mode
         g.TN = 1;
-        g.TH = 256 / g.Wp;
+        g.TH = max_rows / g.Wp;
         if (g.TH > Hc) g.TH = Hc;
         g.RHo = g.TH;
         g.RH = g.TH + halo_h;
@@ -822,7 +823,9 @@ extern "C" int qb_conv_dgrad(const uint16_t* a0, const uint16_t* a1, const uint1
             static const bool flat_off = getenv("QB_DGRAD_FLAT") && getenv("QB_DGRAD_FLAT")[0] == '0';
             if (!a1 && !flat_off) {
                 DflatGeom fg;
-                const size_t fsmem = dgrad_flat_geom(fg, (int)B, (int)Hc, (int)Wc, (int)Cin, (int)Cout, BK, BN, g.dh, g.dw, g.wtap, g.ntaps);
+                static const bool sbs128 = getenv("QB_DGRAD_SBS128") && getenv("QB_DGRAD_SBS128")[0] == '1';
+                const size_t fsmem = dgrad_flat_geom(fg, (int)B, (int)Hc, (int)Wc, (int)Cin, (int)Cout, BK, BN, g.dh, g.dw, g.wtap, g.ntaps,
+                                                     (BN == 128 && sbs128) ? 128 : 256);
                 if (fsmem) {
                     CUtensorMap fa, fo;
                     const uint64_t adims[4] = {(uint64_t)Cout, (uint64_t)Wo, (uint64_t)Ho, (uint64_t)B};
@@ -837,7 +840,8 @@ extern "C" int qb_conv_dgrad(const uint16_t* a0, const uint16_t* a1, const uint1
                     rc = qb_make_tmap(&fo, CU_TENSOR_MAP_DATA_TYPE_FLOAT32, 4, base, odims, ostr, obox, nullptr, 128);
                     if (rc) return rc;
                     static const bool sbs_off = getenv("QB_DGRAD_SBS") && getenv("QB_DGRAD_SBS")[0] == '0';
-                    if (BN == 128) rc = dgrad_flat_launch<128, false>(fa, tw, fo, fg, fsmem, scale_range, scale_bits, scale_mul, st);
+                    if (BN == 128 && sbs128) rc = dgrad_flat_launch<128, true>(fa, tw, fo, fg, fsmem, scale_range, scale_bits, scale_mul, st);
+                    else if (BN == 128) rc = dgrad_flat_launch<128, false>(fa, tw, fo, fg, fsmem, scale_range, scale_bits, scale_mul, st);
                     else if (BN == 64 && !sbs_off) rc = dgrad_flat_launch<64, true>(fa, tw, fo, fg, fsmem, scale_range, scale_bits, scale_mul, st);
                     else if (BN == 64) rc = dgrad_flat_launch<64, false>(fa, tw, fo, fg, fsmem, scale_range, scale_bits, scale_mul, st);
                     else if (BN == 32) rc = dgrad_flat_launch<32, true>(fa, tw, fo, fg, fsmem, scale_range, scale_bits, scale_mul, st);
@@ -905,6 +909,20 @@ struct WgradGeom {
     int J;                      // M tiles (accumulators) per CTA
     int mgroups, nblocks, slices, BN;
     int g_planes, a_stages, b_stages, total_tiles, mrows;
+    // "flat row" mode (unit stride, Cin % 128 == 0): a CTA owns ONE filter row r and one block of 128 input channels; its kw
+    // accumulators (the taps (r, 0..kw-1)) all read the SAME x strip - pixels on a padded pitch Wp = Wo + kw - 1, one TMA box
+    // per 64-channel run - through MN-major descriptors that start s rows (pixels) later, so x is fetched once per filter row
+    // instead of once per tap.  The gradient tile sits on the same pitch (its out-of-range columns are the TMA's zero fill,
+    // so products that wrap into the next image row vanish).  P is the K extent (padded to 16), Pbox the pixels a box holds.
+    int flat, Wp, Pbox, arows;
+    // flat == 2 (unit stride, Cin == 64, all taps in one CTA): the strip also carries the kh-1 halo rows, tap (r, s) starts
+    // r*Wp + s rows into it, and ONE M = 128 accumulator holds TWO taps: its second 64-row column block is the same strip read
+    // foff-difference rows later - the descriptor's leading-dimension byte offset is simply that distance (blocks overlap).
+    int uissue;                 // sbs with the issue loop on the uniform datapath (experiment: QB_WGRAD_UISSUE=1)
+    int sbs;                    // hi | lo gradient planes side by side on N: ONE N = 256 MMA per K step (the single issuing
+                                // thread, not the tensor pipe, bounds this kernel), column halves added in the drain
+    int xrows;                  // rows of the x box (TH + kh - 1) in mode 2
+    int foff[WG_MAX_ACC], flbo[WG_MAX_ACC];     // per accumulator: first strip row, block distance in rows
     FastDiv d_tiles_w, d_tiles_h, d_cin_runs, d_kw;
 };
 
@@ -913,7 +931,9 @@ k_conv_wgrad(const __grid_constant__ CUtensorMap tmap_x, const __grid_constant__
              const __grid_constant__ CUtensorMap tmap_g1, float* __restrict__ partial, WgradGeom g) {
     extern __shared__ uint8_t smem_raw[];
     uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
-    const uint32_t a_slot = 128u * (uint32_t)g.P * 2u;                        // rpm runs x [P][RC] bf16
+    const uint32_t a_slot = g.flat == 2 ? (uint32_t)g.arows * 128u             // one 64-channel strip
+                            : g.flat ? 2u * (uint32_t)g.arows * 128u          // two 64-channel runs x [arows][64] bf16
+                                   : 128u * (uint32_t)g.P * 2u;               // rpm runs x [P][RC] bf16
     const uint32_t b_plane = (uint32_t)g.BN * (uint32_t)g.P * 2u;
     const uint32_t b_slot = (uint32_t)g.g_planes * b_plane;
     uint8_t* s_a = smem;
@@ -934,13 +954,16 @@ k_conv_wgrad(const __grid_constant__ CUtensorMap tmap_x, const __grid_constant__
     const int slice = unit / (g.nblocks * g.mgroups);
     const int n0 = nb * g.BN;
     const int mt0 = mg * g.J;
-    const int jn = (g.mtiles - mt0 < g.J) ? g.mtiles - mt0 : g.J;             // accumulators of this CTA
+    const int jn = g.flat ? g.J : ((g.mtiles - mt0 < g.J) ? g.mtiles - mt0 : g.J);   // accumulators of this CTA
+    const int cgroups = g.Cin >> 7;                                           // flat mode 1: mg = r * cgroups + cg
+    const int fr = g.flat == 1 ? mg / cgroups : 0, fcg = g.flat == 1 ? mg - fr * cgroups : 0;
     const int t_begin = (int)(((int64_t)g.total_tiles * slice) / g.slices);
     const int t_end = (int)(((int64_t)g.total_tiles * (slice + 1)) / g.slices);
-    const uint32_t acc_stride = (uint32_t)(g.BN < 32 ? 32 : g.BN);
+    const uint32_t acc_stride = g.sbs ? 256u : (uint32_t)(g.BN < 32 ? 32 : g.BN);
 
     // a tail M tile has fewer runs than rpm: its unused operand rows must not hold NaN patterns
-    for (uint32_t i = threadIdx.x; i < (uint32_t)g.a_stages * a_slot / 16; i += WG_THREADS)
+    // (flat: neither the x rows behind a box - read by the shifted taps - nor the gradient rows between Pbox and P)
+    for (uint32_t i = threadIdx.x; i < ((uint32_t)g.a_stages * a_slot + (g.flat ? (uint32_t)g.b_stages * b_slot : 0u)) / 16; i += WG_THREADS)
         reinterpret_cast<uint4*>(s_a)[i] = make_uint4(0u, 0u, 0u, 0u);
     if (warp == 0 && lane == 0) {
         tma_prefetch_desc(&tmap_x);
@@ -957,7 +980,7 @@ k_conv_wgrad(const __grid_constant__ CUtensorMap tmap_x, const __grid_constant__
     tc_fence_after_sync();
     const uint32_t tmem_base = *tmem_slot;
     const int rbA = g.RC * 2, rbB = g.RN * 2;
-    const uint32_t runA = (uint32_t)g.P * rbA, runB = (uint32_t)g.P * rbB;     // bytes of one TMA box = LBO
+    const uint32_t runA = (g.flat ? (uint32_t)g.arows : (uint32_t)g.P) * rbA, runB = (uint32_t)g.P * rbB;   // run pitch = LBO
     const int nruns_b = g.BN / g.RN;
 
     auto decode = [&](int t, int& b0, int& ho0, int& wo0) {
@@ -978,13 +1001,28 @@ k_conv_wgrad(const __grid_constant__ CUtensorMap tmap_x, const __grid_constant__
                     const int s = ib % g.b_stages;
                     const uint32_t ph = (ib / g.b_stages) & 1;
                     mbar_wait_trap(&b_empty[s], ph ^ 1);
-                    mbar_arrive_expect_tx(&b_full[s], b_slot);
+                    mbar_arrive_expect_tx(&b_full[s], g.flat ? (uint32_t)(g.g_planes * g.BN * g.Pbox * 2) : b_slot);
                     uint8_t* sb = s_b + (size_t)s * b_slot;
                     for (int p = 0; p < g.g_planes; ++p)
                         for (int r = 0; r < nruns_b; ++r)
                             tma_load_4d(sb + (size_t)p * b_plane + (size_t)r * runB, p ? &tmap_g1 : &tmap_g0, &b_full[s],
                                         n0 + r * g.RN, wo0, ho0, b0);
                     ++ib;
+                }
+                if (g.flat) {                                  // one x strip per pixel tile: two 64-channel boxes on the padded pitch
+                    const int s = ia % g.a_stages;
+                    mbar_wait_trap(&a_empty[s], ((ia / g.a_stages) & 1) ^ 1);
+                    uint8_t* sa = s_a + (size_t)s * a_slot;
+                    if (g.flat == 2) {
+                        mbar_arrive_expect_tx(&a_full[s], (uint32_t)(g.xrows * g.Wp) * rbA);
+                        tma_load_4d(sa, &tmap_x, &a_full[s], 0, -g.pw, ho0 - g.ph, b0);
+                    } else {
+                        mbar_arrive_expect_tx(&a_full[s], 2u * (uint32_t)g.Pbox * rbA);
+                        for (int rr = 0; rr < 2; ++rr)
+                            tma_load_4d(sa + (size_t)rr * runA, &tmap_x, &a_full[s], fcg * 128 + rr * 64, -g.pw, ho0 - g.ph + fr, b0);
+                    }
+                    ++ia;
+                    continue;
                 }
                 for (int j = 0; j < jn; ++j, ++ia) {
                     const int s = ia % g.a_stages;
@@ -1009,11 +1047,64 @@ k_conv_wgrad(const __grid_constant__ CUtensorMap tmap_x, const __grid_constant__
     } else if (warp == 1) {
         const uint32_t idesc = idesc_bf16(128, (uint32_t)g.BN, 1, 1);
         const int ksteps = g.P / 16;
+        const uint32_t lead = elect_one() ? 1u : 0u;           // the one lane that issues (uissue mode)
         uint32_t ia = 0, ib = 0;
         for (int t = t_begin; t < t_end; ++t, ++ib) {
             const int sbi = ib % g.b_stages;
             mbar_wait_trap(&b_full[sbi], (ib / g.b_stages) & 1);
             const uint64_t b_desc = desc_mnmajor(smem_u32(s_b + (size_t)sbi * b_slot), rbB, runB);
+            if (g.uissue) {                                     // N = 256 planes side by side, descriptors on the uniform datapath
+                const uint32_t idesc2 = idesc_bf16(128, 256u, 1, 1);
+                const uint32_t stepA = 16u * (uint32_t)rbA, stepB = 16u * (uint32_t)rbB;
+                for (int j = 0; j < jn; ++j, ++ia) {
+                    const int s = ia % g.a_stages;
+                    mbar_wait_trap(&a_full[s], (ia / g.a_stages) & 1);
+                    tc_fence_after_sync();
+                    uint64_t a_desc = desc_mnmajor(smem_u32(s_a + (size_t)s * a_slot), rbA, runA);
+                    uint64_t b_d = b_desc;
+                    const uint32_t d_tmem = tmem_base + (uint32_t)j * acc_stride;
+                    uint32_t acc = t != t_begin;
+                    for (int ks = 0; ks < ksteps; ++ks) {
+                        umma_f16_if(lead, d_tmem, a_desc, b_d, idesc2, acc);
+                        a_desc = desc_add(a_desc, stepA);
+                        b_d = desc_add(b_d, stepB);
+                        acc = 1u;
+                    }
+                    umma_commit_if(lead, &a_empty[s]);
+                    if (j == jn - 1) umma_commit_if(lead, &b_empty[sbi]);
+                    if (j == jn - 1 && t == t_end - 1) umma_commit_if(lead, done_bar);
+                }
+                continue;
+            }
+            if (g.flat) {
+                const int s = ia % g.a_stages;
+                mbar_wait_trap(&a_full[s], (ia / g.a_stages) & 1);
+                tc_fence_after_sync();
+                if (elect_one()) {
+                    const uint64_t a_desc0 = desc_mnmajor(smem_u32(s_a + (size_t)s * a_slot), rbA, runA);
+                    const uint32_t stepA = 16u * (uint32_t)rbA, stepB = 16u * (uint32_t)rbB;
+                    const uint32_t acc0 = t != t_begin;
+                    for (int j = 0; j < jn; ++j) {               // mode 1: tap (fr, j) = the strip read j pixels later
+                        const uint64_t a_desc = g.flat == 2
+                            ? desc_mnmajor(smem_u32(s_a + (size_t)s * a_slot) + (uint32_t)g.foff[j] * (uint32_t)rbA, rbA,
+                                           (uint32_t)g.flbo[j] * (uint32_t)rbA)
+                            : desc_add(a_desc0, (uint32_t)j * (uint32_t)rbA);
+                        const uint32_t d_tmem = tmem_base + (uint32_t)j * acc_stride;
+                        uint32_t acc = acc0;
+                        for (int ks = 0; ks < ksteps; ++ks) {
+                            umma_f16(d_tmem, desc_add(a_desc, ks * stepA), desc_add(b_desc, ks * stepB), idesc, acc);
+                            umma_f16(d_tmem, desc_add(a_desc, ks * stepA), desc_add(b_desc, b_plane + ks * stepB), idesc, 1u);
+                            acc = 1u;
+                        }
+                    }
+                    umma_commit(&a_empty[s]);
+                    umma_commit(&b_empty[sbi]);
+                    if (t == t_end - 1) umma_commit(done_bar);
+                }
+                __syncwarp();
+                ++ia;
+                continue;
+            }
             for (int j = 0; j < jn; ++j, ++ia) {
                 const int s = ia % g.a_stages;
                 mbar_wait_trap(&a_full[s], (ia / g.a_stages) & 1);
@@ -1023,7 +1114,13 @@ k_conv_wgrad(const __grid_constant__ CUtensorMap tmap_x, const __grid_constant__
                     const uint32_t d_tmem = tmem_base + (uint32_t)j * acc_stride;
                     const uint32_t stepA = 16u * (uint32_t)rbA, stepB = 16u * (uint32_t)rbB;
                     uint32_t acc = t != t_begin;
-                    if (g.g_planes == 2) {
+                    if (g.sbs) {                                 // planes are 2 + 2 consecutive 64-channel runs: N = 256 spans both
+                        const uint32_t idesc2 = idesc_bf16(128, 256u, 1, 1);
+                        for (int ks = 0; ks < ksteps; ++ks) {
+                            umma_f16(d_tmem, desc_add(a_desc, ks * stepA), desc_add(b_desc, ks * stepB), idesc2, acc);
+                            acc = 1u;
+                        }
+                    } else if (g.g_planes == 2) {
                         for (int ks = 0; ks < ksteps; ++ks) {
                             umma_f16(d_tmem, desc_add(a_desc, ks * stepA), desc_add(b_desc, ks * stepB), idesc, acc);
                             umma_f16(d_tmem, desc_add(a_desc, ks * stepA), desc_add(b_desc, b_plane + ks * stepB), idesc, 1u);
@@ -1048,11 +1145,19 @@ k_conv_wgrad(const __grid_constant__ CUtensorMap tmap_x, const __grid_constant__
         mbar_wait_trap(done_bar, 0);
         tc_fence_after_sync();
         for (int j = 0; j < jn; ++j) {
-            const int row = (mt0 + j) * 128 + sub * 32 + lane;
+            const int row = (g.flat == 1 ? ((fr * g.kw + j) * g.Cin + fcg * 128) : (mt0 + j) * 128) + sub * 32 + lane;
             for (int c0 = 0; c0 < g.BN; c0 += 32) {
                 uint32_t r[32];
                 tmem_ld_32x32(tmem_base + (uint32_t)j * acc_stride + (uint32_t)c0 + ((uint32_t)(sub * 32) << 16), r);
-                tmem_ld_wait();
+                if (g.sbs) {
+                    uint32_t r2[32];
+                    tmem_ld_32x32(tmem_base + (uint32_t)j * acc_stride + 128u + (uint32_t)c0 + ((uint32_t)(sub * 32) << 16), r2);
+                    tmem_ld_wait();
+#pragma unroll
+                    for (int u = 0; u < 32; ++u) r[u] = __float_as_uint(__uint_as_float(r[u]) + __uint_as_float(r2[u]));
+                } else {
+                    tmem_ld_wait();
+                }
                 if (row < g.mrows) {
                     float* dst = partial + ((size_t)slice * g.mrows + row) * g.Cout + n0 + c0;
 #pragma unroll
@@ -1150,6 +1255,7 @@ k_wgrad_reduce(const float* __restrict__ partial, int slices, const float* __res
 
 static int wgrad_geom2(WgradGeom& g, int64_t B, int64_t Ho, int64_t Wo, int64_t Cin, int64_t Cout, int kh, int kw, int sh, int sw, int ph,
                        int pw, int g_planes);
+static void wgrad_try_flat(WgradGeom& g);
 static int wgrad_geom(WgradGeom& g, int64_t B, int64_t H, int64_t W, int64_t Cin, int64_t Cout, int kh, int kw, int stride, int pad,
                       int g_planes) {
     const int64_t Ho = (H + 2 * pad - kh) / stride + 1, Wo = (W + 2 * pad - kw) / stride + 1;
@@ -1170,7 +1276,11 @@ static int wgrad_geom2(WgradGeom& g, int64_t B, int64_t Ho, int64_t Wo, int64_t 
     g.mtiles = (g.total_runs + g.rpm - 1) / g.rpm;
     g.mrows = kh * kw * (int)Cin;
     g.nblocks = (int)((Cout + g.BN - 1) / g.BN);
-    const int acc_stride = g.BN < 32 ? 32 : g.BN;
+    static const bool sbs_off = getenv("QB_WGRAD_SBS") && getenv("QB_WGRAD_SBS")[0] == '0';
+    g.sbs = (!sbs_off && g_planes == 2 && g.BN == 128 && g.RN == 64) ? 1 : 0;
+    static const bool uissue_on = getenv("QB_WGRAD_UISSUE") && getenv("QB_WGRAD_UISSUE")[0] == '1';
+    g.uissue = (g.sbs && uissue_on) ? 1 : 0;
+    const int acc_stride = g.sbs ? 256 : (g.BN < 32 ? 32 : g.BN);
     int jmax = 512 / acc_stride;
     if (jmax > WG_MAX_ACC) jmax = WG_MAX_ACC;
     g.mgroups = (g.mtiles + jmax - 1) / jmax;
@@ -1219,7 +1329,109 @@ static int wgrad_geom2(WgradGeom& g, int64_t B, int64_t Ho, int64_t Wo, int64_t 
     g.d_tiles_h = make_fastdiv((uint32_t)g.tiles_h);
     g.d_cin_runs = make_fastdiv((uint32_t)(Cin / g.RC));
     g.d_kw = make_fastdiv((uint32_t)kw);
+    wgrad_try_flat(g);
     return 1;
+}
+
+// Switch a prepared geometry to the flat-row mode when it applies (see WgradGeom); leaves it untouched otherwise.
+static void wgrad_try_flat(WgradGeom& g) {
+    // Measured on B200 (profiles/bwd_sweep_r02f.txt against bwd_sweep_r02f_noflat.txt): the flat-row form moves 1.7x fewer
+    // operand bytes and is nevertheless SLOWER (layer2 164 vs 147 us, layer3 255 vs 164 us) - the kernel is not bound by the
+    // operand feed - so it stays an experiment behind QB_WGRAD_FLAT=1.
+    static const bool off = !(getenv("QB_WGRAD_FLAT") && getenv("QB_WGRAD_FLAT")[0] == '1');
+    static const bool on64 = getenv("QB_WGRAD_FLAT64") && getenv("QB_WGRAD_FLAT64")[0] == '1';
+    const int Wp = g.Wo + g.kw - 1;
+    const int taps = g.kh * g.kw, J2 = (taps + 1) / 2;
+    if (on64 && g.sh == 1 && g.sw == 1 && g.Cin == 64 && g.g_planes == 2 && taps >= 2 && g.nblocks * g.BN == g.Cout &&
+        J2 * (g.BN < 32 ? 32 : g.BN) <= 512 && J2 <= WG_MAX_ACC && Wp <= 128) {
+        int bth = 0;
+        double best = -1.0;
+        for (int th = 1; th <= g.Ho && Wp * th <= 128; ++th) {
+            const int P = (Wp * th + 15) & ~15;
+            const double eff = (double)g.Wo * g.Ho / ((double)((g.Ho + th - 1) / th) * P);
+            if (eff > best) { best = eff; bth = th; }
+        }
+        if (best >= 0.70) {
+            WgradGeom f = g;
+            f.sbs = 0; f.uissue = 0;
+            f.flat = 2; f.Wp = Wp; f.TW = Wp; f.TH = bth; f.TN = 1;
+            f.Pbox = Wp * bth;
+            f.P = (f.Pbox + 15) & ~15;
+            f.xrows = bth + g.kh - 1;
+            const int max_off = (g.kh - 1) * Wp + g.kw - 1;
+            int need = f.P + max_off + 1;
+            if (need < f.xrows * Wp) need = f.xrows * Wp;
+            f.arows = (need + 7) & ~7;
+            f.tiles_w = 1;
+            f.tiles_h = (g.Ho + bth - 1) / bth;
+            f.tiles_b = g.B;
+            f.total_tiles = f.tiles_h * f.tiles_b;
+            f.mgroups = 1;
+            f.J = J2;
+            f.mtiles = J2;
+            for (int j = 0; j < J2; ++j) {
+                const int t1 = 2 * j, t2 = (2 * j + 1 < taps) ? 2 * j + 1 : 2 * j;
+                const int o1 = (t1 / g.kw) * Wp + t1 % g.kw, o2 = (t2 / g.kw) * Wp + t2 % g.kw;
+                f.foff[j] = o1;
+                f.flbo[j] = o2 - o1;
+            }
+            int sms = qb_sm_count();
+            if (sms <= 0) sms = 148;
+            f.slices = f.nblocks >= sms ? 1 : sms / f.nblocks;
+            if (f.slices > f.total_tiles) f.slices = f.total_tiles;
+            const size_t a_slot = (size_t)f.arows * 128, b_slot = (size_t)2 * f.BN * f.P * 2;
+            f.b_stages = 3;
+            int as = (int)((220 * 1024 - 1024 - 512 - (size_t)f.b_stages * b_slot) / a_slot);
+            if (as >= 2) {
+                f.a_stages = as > 4 ? 4 : as;
+                f.d_tiles_w = make_fastdiv(1u);
+                f.d_tiles_h = make_fastdiv((uint32_t)f.tiles_h);
+                g = f;
+                return;
+            }
+        }
+    }
+    if (off || g.sh != 1 || g.sw != 1 || g.kw < 2 || g.kw > 4 || g.Cin % 128 != 0 || g.g_planes != 2 || g.RN != 64 || g.BN != 128 ||
+        Wp > 128)
+        return;
+    // pixel tile {Wp, TH, TN}: K extent P = ceil16(Wp*TH*TN) <= 128, fewest padded K steps per useful pixel
+    double best = -1.0;
+    int bth = 0, btn = 0;
+    for (int th = 1; th <= g.Ho && Wp * th <= 128; ++th)
+        for (int tn = 1; tn <= g.B && Wp * th * tn <= 128; tn *= 2) {
+            if (tn > 1 && th != g.Ho) continue;                          // several images only when one holds a whole image
+            const int P = (Wp * th * tn + 15) & ~15;
+            const double cost = (double)((g.Ho + th - 1) / th) * ((g.B + tn - 1) / tn) * P;
+            const double eff = (double)g.Wo * g.Ho * g.B / cost;
+            if (eff > best) { best = eff; bth = th; btn = tn; }
+        }
+    if (best < 0.70) return;
+    WgradGeom f = g;
+    f.sbs = 0; f.uissue = 0;
+    f.flat = 1; f.Wp = Wp; f.TW = Wp; f.TH = bth; f.TN = btn;
+    f.Pbox = Wp * bth * btn;
+    f.P = (f.Pbox + 15) & ~15;
+    f.arows = f.P + 8;
+    f.tiles_w = 1;
+    f.tiles_h = (g.Ho + bth - 1) / bth;
+    f.tiles_b = (g.B + btn - 1) / btn;
+    f.total_tiles = f.tiles_h * f.tiles_b;
+    f.mgroups = g.kh * (g.Cin / 128);
+    f.J = g.kw;
+    int sms = qb_sm_count();
+    if (sms <= 0) sms = 148;
+    const int units = f.mgroups * f.nblocks;
+    f.slices = units >= sms ? 1 : sms / units;
+    if (f.slices > f.total_tiles) f.slices = f.total_tiles;
+    if (f.slices < 1) f.slices = 1;
+    const size_t a_slot = (size_t)2 * f.arows * 128, b_slot = (size_t)2 * f.BN * f.P * 2;
+    f.b_stages = 2;
+    int as = (int)((220 * 1024 - 1024 - 512 - (size_t)f.b_stages * b_slot) / a_slot);
+    if (as < 2) return;
+    f.a_stages = as > 3 ? 3 : as;
+    f.d_tiles_w = make_fastdiv(1u);
+    f.d_tiles_h = make_fastdiv((uint32_t)f.tiles_h);
+    g = f;
 }
 
 // tensor maps of the gradient planes + the launch of k_conv_wgrad for a prepared geometry / x operand map
@@ -1232,7 +1444,8 @@ static int wgrad_core(const WgradGeom& g, const CUtensorMap& tx, const uint16_t*
     if (rc) return rc;
     rc = qb_make_tmap(&tg1, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, g_lo ? g_lo : g_hi, dims, str, box, nullptr, g.RN * 2);
     if (rc) return rc;
-    const size_t smem = 1024 + (size_t)g.a_stages * 128 * g.P * 2 + (size_t)g.b_stages * g.g_planes * g.BN * g.P * 2 + 512;
+    const size_t a_slot = g.flat == 2 ? (size_t)g.arows * 128 : g.flat ? (size_t)2 * g.arows * 128 : (size_t)128 * g.P * 2;
+    const size_t smem = 1024 + (size_t)g.a_stages * a_slot + (size_t)g.b_stages * g.g_planes * g.BN * g.P * 2 + 512;
     QB_CUDA(cudaFuncSetAttribute(k_conv_wgrad, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     const unsigned grid = (unsigned)(g.slices * g.mgroups * g.nblocks);
     k_conv_wgrad<<<grid, WG_THREADS, smem, st>>>(tx, tg0, tg1, partial, g);
@@ -1277,7 +1490,8 @@ extern "C" int qb_conv_wgrad(const uint16_t* g_hi, const uint16_t* g_lo, const f
     {
         const uint64_t dims[4] = {(uint64_t)Cin, (uint64_t)W, (uint64_t)H, (uint64_t)B};
         const uint64_t str[3] = {(uint64_t)Cin * 2, (uint64_t)W * Cin * 2, (uint64_t)H * W * Cin * 2};
-        const uint32_t box[4] = {(uint32_t)g.RC, (uint32_t)(g.TW * stride), (uint32_t)(g.TH * stride), (uint32_t)g.TN};
+        const uint32_t box[4] = {(uint32_t)g.RC, (uint32_t)(g.TW * stride), (uint32_t)((g.flat == 2 ? g.xrows : g.TH) * stride),
+                                 (uint32_t)g.TN};
         const uint32_t es[4] = {1, (uint32_t)stride, (uint32_t)stride, 1};
         int rc = qb_make_tmap(&tx, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, x16, dims, str, box, es, g.RC * 2);
         if (rc) return rc;
@@ -1459,15 +1673,18 @@ k_umma_shift_probe(const __grid_constant__ CUtensorMap tmap_a, const __grid_cons
             if (!mn) {
                 da = desc_kmajor(a + k * 32, 128);
                 db = desc_kmajor(b + k * 32, 128);
+            } else if (mn == 2) {         // overlapping column blocks: M rows 64..127 = the SAME 64-channel strip, use_boff rows later
+                da = desc_mnmajor(a + k * 16 * 128, 128, (uint32_t)use_boff * 128u);
+                db = desc_mnmajor(b + k * 16 * 128, 128, 80 * 128);
             } else {
                 da = desc_mnmajor(a + k * 16 * 128, 128, 80 * 128);
                 db = desc_mnmajor(b + k * 16 * 128, 128, 80 * 128);
             }
-            if (use_boff) {
+            if (use_boff && mn != 2) {
                 da |= (uint64_t)(((a + (mn ? k * 2048 : 0)) >> 7) & 7) << 49;
                 if (mn) db |= (uint64_t)(((b + k * 2048) >> 7) & 7) << 49;
             }
-            umma_f16(tmem, da, db, idesc_bf16(128, 64, mn, mn), k > 0);
+            umma_f16(tmem, da, db, idesc_bf16(128, 64, mn != 0, mn != 0), k > 0);
         }
         umma_commit(&bar[1]);
     }
@@ -1483,6 +1700,55 @@ k_umma_shift_probe(const __grid_constant__ CUtensorMap tmap_a, const __grid_cons
     tc_fence_before_sync();
     __syncthreads();
     if (warp == 0) tmem_dealloc<64>(tmem);
+}
+
+// ------------------------------------------------------------------------------------------------
+// tensor-pipe rate probe (tools/umma_rate_probe.py): one CTA per SM issues `n` back-to-back tcgen05.mma kind::f16
+// (M = 128, N, K = 16) on zero-filled shared memory - no TMA, no waits - and reports the cycles from the first issue to the
+// completion of the last.  mode bit 0: A MN-major, bit 1: B MN-major, bit 2: descriptors advance through a 16 KB window (as
+// a K loop does) instead of re-reading one address, bit 3: A starts 3 rows into a swizzle atom.
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(128, 1) k_umma_rate_probe(long long* __restrict__ cycles, int n, int N, int mode) {
+    extern __shared__ uint8_t smem_raw[];
+    uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+    uint64_t* bar = reinterpret_cast<uint64_t*>(smem + 128 * 1024);          // A window 64 KB, B window 64 KB
+    uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bar + 1);
+    for (uint32_t i = threadIdx.x; i < 128 * 1024 / 16; i += 128) reinterpret_cast<uint4*>(smem)[i] = make_uint4(0u, 0u, 0u, 0u);
+    if (threadIdx.x == 0) { mbar_init(bar, 1); fence_barrier_init(); }
+    if (threadIdx.x < 32) tmem_alloc<256>(tmem_slot);
+    fence_proxy_async();
+    tc_fence_before_sync();
+    __syncthreads();
+    tc_fence_after_sync();
+    const uint32_t tmem = *tmem_slot;
+    if (threadIdx.x == 0) {
+        const bool a_mn = mode & 1, b_mn = mode & 2, walk = mode & 4;
+        const uint32_t a0 = smem_u32(smem) + ((mode & 8) ? 3u * 128u : 0u), b0 = smem_u32(smem + 64 * 1024);
+        const uint32_t idesc = idesc_bf16(128, (uint32_t)N, a_mn, b_mn);
+        const uint64_t da0 = a_mn ? desc_mnmajor(a0, 128, 16 * 1024) : desc_kmajor(a0, 128);
+        const uint64_t db0 = b_mn ? desc_mnmajor(b0, 128, 16 * 1024) : desc_kmajor(b0, 128);
+        const uint32_t stepA = a_mn ? 16u * 128u : 32u, stepB = b_mn ? 16u * 128u : 32u;     // one K = 16 step
+        const uint32_t wrapA = a_mn ? 8u : 4u, wrapB = b_mn ? 8u : 4u;
+        const long long t0 = clock64();
+        for (int i = 0; i < n; ++i) {
+            const uint32_t ka = walk ? (uint32_t)i % wrapA : 0u, kb = walk ? (uint32_t)i % wrapB : 0u;
+            umma_f16(tmem, desc_add(da0, ka * stepA), desc_add(db0, kb * stepB), idesc, i > 0);
+        }
+        umma_commit(bar);
+        mbar_wait_trap(bar, 0);
+        cycles[blockIdx.x] = clock64() - t0;
+    }
+    tc_fence_before_sync();
+    __syncthreads();
+    if (threadIdx.x < 32) tmem_dealloc<256>(tmem);
+}
+
+extern "C" int qb_debug_umma_rate(long long* cycles, int blocks, int n, int N, int mode, void* stream) {
+    QB_CHECK_ARG(cycles && blocks > 0 && n > 0 && N >= 16 && N <= 256 && N % 16 == 0, "qb_debug_umma_rate: bad argument");
+    QB_CUDA(cudaFuncSetAttribute(k_umma_rate_probe, cudaFuncAttributeMaxDynamicSharedMemorySize, 132 * 1024));
+    k_umma_rate_probe<<<blocks, 128, 132 * 1024, qb_stream(stream)>>>(cycles, n, N, mode);
+    QB_LAUNCH_CHECK();
+    return QB_OK;
 }
 
 /* a: bf16 [144][64] (mn = 0) or [80][128] (mn = 1); b: bf16 [64][64] (mn = 0) or [80][64] (mn = 1); out fp32 [128][64]. */

@@ -141,6 +141,10 @@ extern "C" int qb_minmax(const float* x, int64_t n, float* range_out, void* ws, 
 // / QConv2d that receives dx needs float(dx.min()), float(dx.max()) next (quantize.py:126,132), so the min/max sweep
 // (a second 4 B/elem read) rides along: 12 B/elem for both instead of 12 + 4.
 // ------------------------------------------------------------------------------------------------
+// BITS: the ReLU output is given as the bit mask qb_rangebn_apply_relu_measure wrote (bit e%8 of byte e/8 = "out[e] is not
+// <= 0"): 1/8 B/elem instead of 4, octets only.  WRITE = false: only the range of the masked gradient is produced (the
+// RangeBN backward that consumes it applies the same mask on the fly), 4.125 B/elem in total.
+template <bool BITS, bool WRITE>
 __global__ void __launch_bounds__(GQ_THREADS)
 k_relu_bwd_minmax(const float* __restrict__ g, const float* __restrict__ out, float* __restrict__ dx, int64_t n, int vec,
                   float* range_out, MinMaxWs* ws) {
@@ -149,7 +153,36 @@ k_relu_bwd_minmax(const float* __restrict__ g, const float* __restrict__ out, fl
     float mn = QB_INF, mx = -QB_INF;
     const int64_t stride = (int64_t)gridDim.x * GQ_THREADS;
     const int64_t tid = (int64_t)blockIdx.x * GQ_THREADS + threadIdx.x;
-    if (vec) {
+    if (BITS) {
+        const uint8_t* bits = reinterpret_cast<const uint8_t*>(out);
+        const int64_t noct = n >> 3;
+        constexpr int U = 4;
+        int64_t i = tid;
+        for (; i + (U - 1) * stride < noct; i += U * stride) {
+            F8 a[U];
+            uint32_t m[U];
+#pragma unroll
+            for (int u = 0; u < U; ++u) {
+                a[u] = ld256_stream(g + 8 * (i + u * stride));
+                m[u] = __ldcs(bits + i + u * stride);
+            }
+#pragma unroll
+            for (int u = 0; u < U; ++u) {
+#pragma unroll
+                for (int j = 0; j < 8; ++j) a[u].v[j] = ((m[u] >> j) & 1u) ? a[u].v[j] : 0.0f;
+                octet_minmax(a[u], mn, mx);
+                if (WRITE) *reinterpret_cast<F8*>(dx + 8 * (i + u * stride)) = a[u];
+            }
+        }
+        for (; i < noct; i += stride) {
+            F8 a = ld256_stream(g + 8 * i);
+            const uint32_t m = __ldcs(bits + i);
+#pragma unroll
+            for (int j = 0; j < 8; ++j) a.v[j] = ((m >> j) & 1u) ? a.v[j] : 0.0f;
+            octet_minmax(a, mn, mx);
+            if (WRITE) *reinterpret_cast<F8*>(dx + 8 * i) = a;
+        }
+    } else if (vec) {
         const int64_t noct = n >> 3;
         constexpr int U = 2;
         int64_t i = tid;
@@ -225,8 +258,28 @@ extern "C" int qb_relu_bwd_minmax(const float* grad_out, const float* relu_out, 
     }
     const int vec = aligned32(grad_out) && aligned32(relu_out) && aligned32(dx);
     const int grid = gq_grid(vec ? (n >> 3) / 2 : n / 2, 8);
-    k_relu_bwd_minmax<<<grid, GQ_THREADS, 0, qb_stream(stream)>>>(grad_out, relu_out, dx, n, vec, range_out,
-                                                                 static_cast<MinMaxWs*>(ws));
+    k_relu_bwd_minmax<false, true><<<grid, GQ_THREADS, 0, qb_stream(stream)>>>(grad_out, relu_out, dx, n, vec, range_out,
+                                                                              static_cast<MinMaxWs*>(ws));
+    QB_LAUNCH_CHECK();
+    return QB_OK;
+}
+
+/* qb_relu_bwd_minmax with the ReLU output given as the bit mask written by qb_rangebn_apply_relu_measure (bit e%8 of byte
+ * e/8 set = gradient passes).  dx == NULL: only range_out = {min, max} of the masked gradient is produced (4.125 B/elem) -
+ * for a consumer that applies the mask itself (qb_rangebn_bwd_reduce_nhwc's relu_bits).  n % 8 == 0, 32-byte aligned. */
+extern "C" int qb_relu_bwd_minmax_bits(const float* grad_out, const uint8_t* relu_bits, float* dx, int64_t n, float* range_out,
+                                       void* ws, size_t ws_bytes, void* stream) {
+    QB_CHECK_ARG(grad_out && relu_bits && range_out && ws, "qb_relu_bwd_minmax_bits: null pointer");
+    QB_CHECK_ARG(n > 0 && n % 8 == 0, "qb_relu_bwd_minmax_bits: n=%lld (a positive multiple of 8)", (long long)n);
+    QB_CHECK_ARG(aligned32(grad_out) && (!dx || aligned32(dx)), "qb_relu_bwd_minmax_bits: tensors must be 32-byte aligned");
+    if (ws_bytes < sizeof(MinMaxWs)) {
+        qb_set_error("qb_relu_bwd_minmax_bits: workspace %zu < %zu bytes", ws_bytes, sizeof(MinMaxWs));
+        return QB_ERR_WORKSPACE;
+    }
+    const int grid = gq_grid((n >> 3) / 4, 8);
+    const float* bits = reinterpret_cast<const float*>(relu_bits);
+    if (dx) k_relu_bwd_minmax<true, true><<<grid, GQ_THREADS, 0, qb_stream(stream)>>>(grad_out, bits, dx, n, 1, range_out, static_cast<MinMaxWs*>(ws));
+    else k_relu_bwd_minmax<true, false><<<grid, GQ_THREADS, 0, qb_stream(stream)>>>(grad_out, bits, nullptr, n, 1, range_out, static_cast<MinMaxWs*>(ws));
     QB_LAUNCH_CHECK();
     return QB_OK;
 }

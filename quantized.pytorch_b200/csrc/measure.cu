@@ -44,6 +44,7 @@ struct ApplyArg {
     int q_bits;
     int C;
     int fixed;                                      // (MS_THREADS*4) % C == 0: a thread's four channels never change
+    uint8_t* mask_out;                              // optional: bit e%8 of byte e/8 = (y[e] is not <= 0), what the ReLU backward needs
 };
 
 __device__ __forceinline__ float4 apply_quad(uint32_t word, const AffineQ& aq, const float4& mu, const float4& sc, const float4& gm,
@@ -147,6 +148,13 @@ k_measure_stats(const float* x, const float* r, float* y, int64_t B, int64_t inn
                     if (RELU) {
                         v[u] = make_float4(relu1(v[u].x), relu1(v[u].y), relu1(v[u].z), relu1(v[u].w));
                         reinterpret_cast<float4*>(y + b * inner + off)[qi] = v[u];
+                    }
+                    if (CODES && ap.mask_out) {
+                        // H*W*C % 8 == 0: quads come in (even, odd) lane pairs that are both inside the row
+                        uint32_t nib = (v[u].x <= 0.0f ? 0u : 1u) | (v[u].y <= 0.0f ? 0u : 2u) | (v[u].z <= 0.0f ? 0u : 4u) |
+                                       (v[u].w <= 0.0f ? 0u : 8u);
+                        const uint32_t hi = __shfl_down_sync(__activemask(), nib, 1);
+                        if ((qi & 1) == 0) ap.mask_out[((b * inner + off) >> 3) + (qi >> 1)] = (uint8_t)(nib | (hi << 4));
                     }
                     acc4(v[u], mn, mx, fs, fq);
                 }
@@ -256,8 +264,10 @@ extern "C" int qb_add_relu_measure(const float* x, const float* r, float* y, int
  * H*W*C % 4 == 0, 16-byte aligned tensors, q_bits <= 8. */
 extern "C" int qb_rangebn_apply_relu_measure(const uint8_t* x_codes, const float* residual, float* y, int64_t B, int64_t C, int64_t HW,
                                              const float* mean, const float* qscale, const float* qgamma, const float* qbeta,
-                                             const float* q_range, int q_bits, double* stats, void* ws, size_t ws_bytes, void* stream) {
+                                             const float* q_range, int q_bits, uint8_t* relu_bits_out, double* stats, void* ws,
+                                             size_t ws_bytes, void* stream) {
     QB_CHECK_ARG(x_codes && y && mean && qscale && q_range, "qb_rangebn_apply_relu_measure: null pointer");
+    QB_CHECK_ARG(!relu_bits_out || (HW * C) % 8 == 0, "qb_rangebn_apply_relu_measure: the ReLU bit mask needs H*W*C %% 8 == 0");
     QB_CHECK_ARG(B > 0 && C > 0 && HW > 0 && C % 4 == 0 && C < (1 << 30), "qb_rangebn_apply_relu_measure: bad shape (C %% 4 == 0 required)");
     QB_CHECK_ARG(q_bits >= 1 && q_bits <= 8, "qb_rangebn_apply_relu_measure: q_bits=%d", q_bits);
     QB_CHECK_ARG(((reinterpret_cast<uintptr_t>(x_codes) & 3) | (reinterpret_cast<uintptr_t>(y) & 15) |
@@ -267,7 +277,7 @@ extern "C" int qb_rangebn_apply_relu_measure(const uint8_t* x_codes, const float
                  "qb_rangebn_apply_relu_measure: misaligned tensor");
     QB_CHECK_ARG(residual != y, "qb_rangebn_apply_relu_measure: the residual must not alias the output");
     const int64_t inner = HW * C;
-    ApplyArg ap{mean, qscale, qgamma, qbeta, q_range, q_bits, (int)C, 0};
+    ApplyArg ap{mean, qscale, qgamma, qbeta, q_range, q_bits, (int)C, 0, relu_bits_out};
     ap.fixed = ((MS_THREADS * 4) % C == 0 && MS_TILE % C == 0) ? 1 : 0;
     return measure_launch(reinterpret_cast<const float*>(x_codes), residual, y, B, inner, stats, ws, ws_bytes, stream, &ap);
 }

@@ -714,6 +714,8 @@ struct GradQuantArg {
     NoiseArg noise;
     uint8_t* codes;       // reduce pass: optional uint8 copy of the integer codes of Q(g) (bits <= 8), same indexing as g;
                           // apply pass (NOISE == -2): the codes to dequantize INSTEAD of reading and re-quantizing g
+    const uint8_t* relu_bits = nullptr;   // reduce pass, VEC == 8: g is the gradient w.r.t. the OUTPUT of the ReLU that follows
+                          // this RangeBN; bit e%8 of byte e/8 says whether it passes (written by qb_rangebn_apply_relu_measure)
 };
 
 // QUANT: 0 = x is x_hat already, 1 = x is the raw input, quantized on the fly with q_range, 2 = x_hat comes as the uint8
@@ -745,10 +747,14 @@ k_rbn_bwd_reduce_nhwc(const float* __restrict__ gq, const float* __restrict__ x,
     uint64_t fg2[4] = {0ull, 0ull, 0ull, 0ull}, fgx2[4] = {0ull, 0ull, 0ull, 0ull};     // VEC == 8: packed (0.f, 0.f) pairs
 #pragma unroll
     for (int j = 0; j < VEC; ++j) { fg[j] = 0.f; fgx[j] = 0.f; }
-    auto one_row = [&](const V& av_, const V& bv_, const uint2& pk, int64_t r) {
+    auto one_row = [&](const V& av_, const V& bv_, const uint2& pk, int64_t r, uint32_t rmask = 0xffu) {
         float av[VEC], bv[VEC];
         unpack(av_, av);
         if constexpr (VEC == 8) {
+            if (rmask != 0xffu) {
+#pragma unroll
+                for (int j = 0; j < 8; ++j) av[j] = ((rmask >> j) & 1u) ? av[j] : 0.0f;
+            }
             if (QUANT == 2) affine_deq8(pk, aq.p, bv);                  // x_hat from the forward pass's codes
             else unpack(bv_, bv);
             if (NOISE >= 0) {
@@ -788,21 +794,24 @@ k_rbn_bwd_reduce_nhwc(const float* __restrict__ gq, const float* __restrict__ x,
         for (; r + (UN - 1) * step < r_end; r += UN * step) {
             V a[UN], b[UN];
             uint2 pk[UN];
+            uint32_t rm[UN];
 #pragma unroll
             for (int u = 0; u < UN; ++u) {
                 a[u] = ld_vec_stream<V>(gq + (r + u * step) * g.C + c0);
                 if (QUANT == 2) pk[u] = __ldcs(reinterpret_cast<const uint2*>(x_codes + (r + u * step) * g.C + c0));
                 else b[u] = ld_vec_stream<V>(x + (r + u * step) * g.C + c0);
+                rm[u] = (VEC == 8 && ga.relu_bits) ? __ldcs(ga.relu_bits + (((r + u * step) * g.C + c0) >> 3)) : 0xffu;
             }
 #pragma unroll
-            for (int u = 0; u < UN; ++u) one_row(a[u], b[u], pk[u], r + u * step);
+            for (int u = 0; u < UN; ++u) one_row(a[u], b[u], pk[u], r + u * step, rm[u]);
         }
         for (; r < r_end; r += step) {
             V b1;
             uint2 pk1 = make_uint2(0u, 0u);
             if (QUANT == 2) pk1 = __ldcs(reinterpret_cast<const uint2*>(x_codes + r * g.C + c0));
             else b1 = ld_vec_stream<V>(x + r * g.C + c0);
-            one_row(ld_vec_stream<V>(gq + r * g.C + c0), b1, pk1, r);
+            const uint32_t rm1 = (VEC == 8 && ga.relu_bits) ? __ldcs(ga.relu_bits + ((r * g.C + c0) >> 3)) : 0xffu;
+            one_row(ld_vec_stream<V>(gq + r * g.C + c0), b1, pk1, r, rm1);
         }
     }
     if constexpr (VEC == 8) {
@@ -860,8 +869,8 @@ extern "C" int qb_rangebn_bwd_reduce_nhwc(const float* gq, const float* x, const
                                           int64_t HW, double* sg, double* sgx, const float* q_range, int q_bits,
                                           const float* g_range, int g_bits,
                                           const float* noise, int stochastic, uint64_t seed, uint64_t offset,
-                                          const uint64_t* step_dev, uint8_t* gq_codes_out, void* ws, size_t ws_bytes,
-                                          void* stream) {
+                                          const uint64_t* step_dev, uint8_t* gq_codes_out, const uint8_t* relu_bits, void* ws,
+                                          size_t ws_bytes, void* stream) {
     QB_CHECK_ARG(gq && (x || x_codes) && sg && sgx && ws, "qb_rangebn_bwd_reduce_nhwc: null pointer");
     QB_CHECK_ARG(!x_codes || (q_range && q_bits <= 8 && C % 8 == 0 && (reinterpret_cast<uintptr_t>(x_codes) & 7) == 0),
                  "qb_rangebn_bwd_reduce_nhwc: x_codes needs q_range, q_bits <= 8, C %% 8 == 0 and 8-byte alignment");
@@ -890,7 +899,11 @@ extern "C" int qb_rangebn_bwd_reduce_nhwc(const float* gq, const float* x, const
     double* part = static_cast<double*>(ws);
     dim3 grid((unsigned)g.S, (unsigned)((C + g.tileC - 1) / g.tileC));
     cudaStream_t st = qb_stream(stream);
-    GradQuantArg ga{g_range, g_bits, nm, NoiseArg{noise, seed, offset, step_dev}, gq_codes_out};
+    GradQuantArg ga{g_range, g_bits, nm, NoiseArg{noise, seed, offset, step_dev}, gq_codes_out, relu_bits};
+    if (relu_bits && !(vec8 && nm >= 0)) {
+        qb_set_error("qb_rangebn_bwd_reduce_nhwc: relu_bits needs the fused gradient quantizer on the 8-channel path");
+        return QB_ERR_UNSUPPORTED;
+    }
     const bool qx = q_range != nullptr;
     if (vec8) {
         const size_t sm = nhwc_smem(g, 8, 16);

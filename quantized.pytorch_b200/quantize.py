@@ -906,13 +906,14 @@ class _RangeBNFn(Function):
         ctx.dims = (B, Cn, HW, chunks_global, count, chunk_len, training, bits_grad, gamma is not None, beta is not None)
         ctx.nhwc, ctx.q_bits = nhwc, q_bits
         ctx.save_for_backward(None if xc is not None else xq, vec, amax, amin, q_range, xc)
+        ctx.deferred = deferred
         if deferred is not None:
             # RangeBN.forward_relu: the normalisation runs later, fused with the ReLU (_ApplyReLUFn); this node only owns the
             # statistics and the RangeBN backward.  Its output is a storage-less placeholder of the right shape.
             if xc is None:
                 raise _abi.QB200Error("RangeBN.forward_relu: the fused pass needs the uint8 codes of the statistics pass")
             deferred.update(xc=xc, vec=vec, like=xq, dims=(B, Cn, HW), has_gamma=gamma is not None, has_beta=beta is not None,
-                            q_range=q_range, q_bits=q_bits)
+                            q_range=q_range, q_bits=q_bits, bits_grad=bits_grad)
             return xq.new_empty(1).expand(xq.shape)
         return _abi.rangebn_apply(xq, B, Cn, HW, vec, gamma is not None, beta is not None, nhwc=nhwc, q_range=q_range,
                                   q_bits=q_bits, x_codes=xc)
@@ -925,12 +926,23 @@ class _RangeBNFn(Function):
         hook = _reducer.rangebn_bwd if (_reducer is not None and training) else None
         common = dict(reduce_hook=hook, chunks_global=K, nhwc=ctx.nhwc, q_range=q_range, q_bits=ctx.q_bits, x_codes=xc)
         lc = ctx.local_chunks if training else 0
-        if (ctx.nhwc and Cn % 8 == 0 and g.numel() < 2 ** 32 and g.data_ptr() % 32 == 0
-                and (xc is not None or xq.data_ptr() % 32 == 0)):
+        # _ApplyReLUFn left the backward of the fused ReLU to this node: g is still the gradient w.r.t. the ReLU OUTPUT
+        relu_bits = ctx.deferred.pop("relu_bits", None) if ctx.deferred is not None else None
+        fused = (ctx.nhwc and Cn % 8 == 0 and g.numel() < 2 ** 32 and g.data_ptr() % 32 == 0
+                 and (xc is not None or xq.data_ptr() % 32 == 0))
+        if relu_bits is not None and not (fused and bits_grad is not None and bits_grad <= 8):
+            g, rr = _abi.relu_bwd_minmax_bits(_abi._f32c(g, "grad"), relu_bits)
+            _stash_grad_range(g, rr)
+            relu_bits = None
+        if fused:
             gquant = None
             if bits_grad is not None:
                 g = _abi._f32c(g, "grad")
-                r = _take_grad_range(g)                      # left by the ReLU backward that produced g (glue.py)
+                if relu_bits is not None:                    # range of the MASKED gradient; the reduce pass masks on the fly
+                    r = _abi.relu_bwd_minmax_bits(g, relu_bits, want_dx=False)[1]
+                    common["relu_bits"] = relu_bits
+                else:
+                    r = _take_grad_range(g)                  # left by the ReLU backward that produced g (glue.py)
                 if r is None:
                     r = _abi.minmax(g)
                 if _reducer is not None:
@@ -960,16 +972,29 @@ class _ApplyReLUFn(Function):
     def forward(ctx, h, residual, d):
         from . import glue
         B, Cn, HW = d["dims"]
-        out, glue._last["stats"] = _abi.rangebn_apply_relu_measure(d["xc"], d["like"], B, Cn, HW, d["vec"], d["has_gamma"],
-                                                                   d["has_beta"], d["q_range"], d["q_bits"], residual=residual)
-        ctx.save_for_backward(out)
+        out, glue._last["stats"], bits = _abi.rangebn_apply_relu_measure(d["xc"], d["like"], B, Cn, HW, d["vec"], d["has_gamma"],
+                                                                         d["has_beta"], d["q_range"], d["q_bits"],
+                                                                         residual=residual, want_bits=True)
+        # the ReLU backward needs one bit per element, not the fp32 output
+        ctx.has_bits = bits is not None
+        ctx.save_for_backward(bits if ctx.has_bits else out)
+        ctx.d = d
+        ctx.has_residual = residual is not None
         return out
 
     @staticmethod
     def backward(ctx, g):
         from . import glue
-        (out,) = ctx.saved_tensors
-        dg = glue._relu_backward(g.contiguous(memory_format=torch.channels_last), out)
+        (saved,) = ctx.saved_tensors
+        g = _abi._f32c(g, "grad").contiguous(memory_format=torch.channels_last)
+        if not ctx.has_bits:
+            dg = glue._relu_backward(g, saved)
+        elif not ctx.has_residual and g.data_ptr() % 32 == 0:
+            ctx.d["relu_bits"] = saved                      # the RangeBN node that follows masks on the fly (no dx tensor)
+            return g, None, None
+        else:
+            dg, rng = _abi.relu_bwd_minmax_bits(g, saved)
+            _stash_grad_range(dg, rng)
         return dg, (dg if ctx.needs_input_grad[1] else None), None
 
 

@@ -121,6 +121,22 @@ def test_relu_backward_with_range(lib, n):
     assert torch.equal(dx2, want) and torch.equal(rng, rng2)
 
 
+@pytest.mark.parametrize("n", [8, 8 * 1000, 8 * 123457])
+def test_relu_backward_from_bit_mask(lib, n):
+    """qb_relu_bwd_minmax_bits == qb_relu_bwd_minmax with the ReLU output reduced to one bit per element (bit e%8 of byte e/8),
+    with and without the dx tensor."""
+    torch.manual_seed(n)
+    g = torch.randn(n, device=DEV)
+    out = torch.relu(torch.randn(n, device=DEV))
+    want, rng = lib.relu_bwd_minmax(g, out)
+    keep = (~(out <= 0)).view(-1, 8).to(torch.int32)
+    bits = (keep << torch.arange(8, device=DEV, dtype=torch.int32)).sum(1).to(torch.uint8)
+    dx, rng2 = lib.relu_bwd_minmax_bits(g, bits)
+    assert torch.equal(dx, want) and torch.equal(rng, rng2)
+    none, rng3 = lib.relu_bwd_minmax_bits(g, bits, want_dx=False)
+    assert none is None and torch.equal(rng, rng3)
+
+
 def test_rangebn_backward_takes_the_relu_range(lib):
     """RangeBN -> glue.ReLU: the ReLU backward hands its result's range to the RangeBN gradient quantizer (no qb_minmax
     launch), and the gradients equal those of the stock nn.ReLU route under the same injected noise."""
@@ -183,15 +199,20 @@ def test_rangebn_forward_relu_equals_the_composition(lib, shape, with_residual):
             names = [n[0] for n in lib.profile_end()]
             stats = Q._take_fwd_stats(y.detach())
             out = y.detach().clone()
+            lib.profile_begin()
             y.backward(go)
+            bwd_names = [n[0] for n in lib.profile_end()]
         finally:
             Q.set_noise_provider(prev)
-        res.append(dict(out=out, stats=stats.clone(), names=names, dx=xi.grad.clone(), dr=ri.grad.clone() if with_residual else None,
+        res.append(dict(out=out, stats=stats.clone(), names=names, bwd_names=bwd_names, dx=xi.grad.clone(), dr=ri.grad.clone() if with_residual else None,
                         dgamma=bn.weight.grad.clone(), dbeta=bn.bias.grad.clone(),
                         buffers={k: v.clone() for k, v in bn.state_dict().items()}))
     f, c = res
     assert "qb_rangebn_apply_relu_measure" in f["names"] and "qb_rangebn_apply_nhwc" not in f["names"], f["names"]
     assert "qb_rangebn_apply_nhwc" in c["names"]
+    # backward of the fused ReLU from its 1-bit mask; without a residual the masked gradient is never written
+    assert "qb_relu_bwd_minmax_bits" in f["bwd_names"] and "qb_relu_bwd_minmax" not in f["bwd_names"], f["bwd_names"]
+    assert "qb_relu_bwd_minmax" in c["bwd_names"]
     assert torch.equal(f["out"], c["out"])
     assert torch.equal(f["stats"], c["stats"]), (f["stats"], c["stats"])
     for k in ("dx", "dgamma", "dbeta") + (("dr",) if with_residual else ()):
