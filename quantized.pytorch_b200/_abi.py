@@ -146,6 +146,7 @@ _NLAUNCH = {"qb_rangebn_stats": 2, "qb_rangebn_bwd_reduce": 2, "qb_rangebn_bwd_a
             "qb_conv_i8_fwd": 2, "qb_conv_wgrad": 3, "qb_conv_dw_wgrad": 2, "qb_conv_stem_fwd": 2, "qb_conv_stem_wgrad": 2, "qb_rangebn_stats_nhwc": 2, "qb_rangebn_bwd_reduce_nhwc": 2, "qb_rangebn_apply_relu_measure": 1, "qb_rangebn_bwd_apply_nhwc": 2}
 
 
+_SYNC_EACH = os.environ.get("QB_SYNC_EACH", "") == "1"
 _next_ops = 0          # integer operations (2*M*N*K) of the next tensor-core call, set by the conv / GEMM wrappers
 PROFILE_OPS = {}       # name -> operations recorded between profile_begin() and profile_end()
 
@@ -169,6 +170,11 @@ def _run(name, nbytes, *args):
         _profile.append((name, nbytes, a, b))
     if rc != 0:
         raise QB200Error("%s failed (%d): %s" % (name, rc, last_error()))
+    if _SYNC_EACH:                                   # debugging aid (QB_SYNC_EACH=1): name the entry point whose kernel faults
+        try:
+            torch.cuda.synchronize()
+        except Exception as e:  # noqa: BLE001
+            raise QB200Error("%s: device fault after this call: %s | args %r" % (name, str(e).splitlines()[0], args[-12:])) from e
 
 
 def profile_begin():

@@ -446,6 +446,7 @@ static int dgrad_launch(const CUtensorMap& ta0, const CUtensorMap& ta1, const CU
 // accumulators that share every weight stage; two accumulator sets alternate between MMA and epilogue.
 // ------------------------------------------------------------------------------------------------
 constexpr int DF_MAX_WSTAGES = 8;
+constexpr int DF_THREADS = DG_THREADS + 32;      // + a second MMA-issuing warp (warp 10) for the second accumulator of a strip
 
 struct DflatGeom {
     int B, Hc, Wc, Cn, Ck;
@@ -458,6 +459,7 @@ struct DflatGeom {
     int dh_min, dw_min;
     int off[DG_MAX_TAPS], wtap[DG_MAX_TAPS];
     int nstage;                 // staging slab buffers (1 or 2)
+    int mma2;                   // second MMA-issuing warp (QB_DGRAD_MMA2=0 disables)
     FastDiv d_tiles_m, d_tiles_h;
 };
 
@@ -465,7 +467,7 @@ struct DflatGeom {
 // N = BN ones: the pixel operand is read from shared memory once, which a 64-column MMA needs to keep the tensor pipe fed);
 // the epilogue adds the two column halves.
 template <int BN, bool SBS>
-__global__ void __launch_bounds__(DG_THREADS, 1)
+__global__ void __launch_bounds__(DF_THREADS, 1)
 k_conv_dgrad_flat(const __grid_constant__ CUtensorMap tmap_a, const __grid_constant__ CUtensorMap tmap_w,
                   const __grid_constant__ CUtensorMap tmap_o, DflatGeom g, const float* __restrict__ scale_range, int scale_bits,
                   float scale_mul) {
@@ -494,19 +496,22 @@ k_conv_dgrad_flat(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
     constexpr uint32_t ACC = SBS ? (2 * BN < 32 ? 32 : 2 * BN) : (BN < 32 ? 32 : BN);
     constexpr uint32_t JMAX = ACC >= 256 ? 1 : 2;               // accumulators per set (a strip is <= 128 * JMAX rows)
     constexpr uint32_t TMEM_COLS = 2 * JMAX * ACC;              // 2 sets x JMAX accumulators
+    // one thread issuing every MMA is what bounds this kernel (see k_conv_wgrad): with two accumulators per strip a second
+    // warp issues the second one - independent accumulators, no ordering between the warps
+    const uint32_t nmma = (g.J == 2 && g.mma2) ? 2u : 1u;
 
     if (warp == 0 && lane == 0) {
         tma_prefetch_desc(&tmap_a);
         tma_prefetch_desc(&tmap_w);
         tma_prefetch_desc(&tmap_o);
-        for (int s = 0; s < 2; ++s) { mbar_init(&a_full[s], 1); mbar_init(&a_empty[s], 1); }
-        for (int s = 0; s < g.wstages; ++s) { mbar_init(&w_full[s], 1); mbar_init(&w_empty[s], 1); }
-        for (int i = 0; i < 2; ++i) { mbar_init(&tfull_bar[i], 1); mbar_init(&tempty_bar[i], 8); }
+        for (int s = 0; s < 2; ++s) { mbar_init(&a_full[s], 1); mbar_init(&a_empty[s], nmma); }
+        for (int s = 0; s < g.wstages; ++s) { mbar_init(&w_full[s], 1); mbar_init(&w_empty[s], nmma); }
+        for (int i = 0; i < 2; ++i) { mbar_init(&tfull_bar[i], nmma); mbar_init(&tempty_bar[i], 8); }
         fence_barrier_init();
     }
     if (warp == 1) tmem_alloc<TMEM_COLS>(tmem_slot);
     // operand rows behind the box are read (for garbage outputs only) but never written: no NaN patterns there
-    for (uint32_t i = threadIdx.x; i < 2 * a_slot / 16; i += DG_THREADS) reinterpret_cast<uint4*>(s_a)[i] = make_uint4(0u, 0u, 0u, 0u);
+    for (uint32_t i = threadIdx.x; i < 2 * a_slot / 16; i += DF_THREADS) reinterpret_cast<uint4*>(s_a)[i] = make_uint4(0u, 0u, 0u, 0u);
     fence_proxy_async();
     tc_fence_before_sync();
     __syncthreads();
@@ -545,7 +550,8 @@ k_conv_dgrad_flat(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
                 }
             }
         }
-    } else if (warp == 1) {
+    } else if (warp == 1 || (warp == 10 && nmma == 2)) {
+        const int mw = warp == 1 ? 0 : 1;
         constexpr uint32_t idesc = idesc_bf16(128, SBS ? 2 * BN : BN, 0, 0);
         const int ksteps = g.BK / 16;
         uint32_t ia = 0, iw = 0;
@@ -567,6 +573,7 @@ k_conv_dgrad_flat(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
                         const uint64_t w_desc = desc_kmajor(smem_u32(s_w + (size_t)sw * w_slot), rb);
                         const uint32_t first = (kb | tp) == 0;
                         for (int j = 0; j < g.J; ++j) {
+                            if ((uint32_t)j % nmma != (uint32_t)mw) continue;
                             const uint64_t a_desc = desc_add(a_desc0, (uint32_t)(128 * j + g.off[tp]) * (uint32_t)rb);
                             const uint32_t dj = d0 + (uint32_t)j * ACC;
                             if (SBS) {
@@ -600,7 +607,7 @@ k_conv_dgrad_flat(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
                 }
             }
         }
-    } else {
+    } else if (warp >= 2 && warp <= 9) {
         // ===== epilogue: warps 2-5 drain accumulator 0, warps 6-9 accumulator 1 (one warp per TMEM lane quarter) =====
         const int e_all = threadIdx.x - 64;
         const int sub = warp & 3, j = (warp - 2) >> 2;
@@ -679,7 +686,7 @@ static int dgrad_flat_launch(const CUtensorMap& ta, const CUtensorMap& tw, const
     int sms = qb_sm_count();
     if (sms <= 0) sms = 148;
     const unsigned grid = (unsigned)(total < sms ? total : sms);
-    k_conv_dgrad_flat<BN, SBS><<<grid, DG_THREADS, smem, st>>>(ta, tw, to, g, scale_range, scale_bits, scale_mul);
+    k_conv_dgrad_flat<BN, SBS><<<grid, DF_THREADS, smem, st>>>(ta, tw, to, g, scale_range, scale_bits, scale_mul);
     QB_LAUNCH_CHECK();
     return QB_OK;
 }
@@ -733,6 +740,8 @@ static size_t dgrad_flat_geom(DflatGeom& g, int B, int Hc, int Wc, int Cn, int C
         g.wtap[i] = wtap[i];
     }
     g.kblocks = (Ck + BK - 1) / BK;
+    static const bool mma2_off = getenv("QB_DGRAD_MMA2") && getenv("QB_DGRAD_MMA2")[0] == '0';
+    g.mma2 = mma2_off ? 0 : 1;
     g.d_tiles_m = make_fastdiv((uint32_t)(g.tiles_h * g.tiles_b));
     g.d_tiles_h = make_fastdiv((uint32_t)g.tiles_h);
     const int rb = BK * 2;
@@ -896,7 +905,10 @@ extern "C" int qb_conv_dgrad(const uint16_t* a0, const uint16_t* a1, const uint1
 // ------------------------------------------------------------------------------------------------
 // wgrad
 // ------------------------------------------------------------------------------------------------
-constexpr int WG_THREADS = 192;      // TMA warp, MMA warp, 4 drain warps
+constexpr int WG_THREADS = 224;      // TMA warp, MMA warp, 4 drain warps, second MMA warp
+// The tensor pipe idles half of the time in this kernel although its operands are there (profiles/ncu_conv_l2_r02e.txt): ONE
+// thread issuing the MMAs (descriptor arithmetic, uniform-register moves, barrier waits) is the bottleneck.  With two or more
+// accumulators per CTA a second warp issues the odd ones: they are independent, so no ordering between the warps is needed.
 constexpr int WG_MAX_STAGES = 8;
 constexpr int WG_MAX_ACC = 16;
 
@@ -918,6 +930,7 @@ struct WgradGeom {
     // flat == 2 (unit stride, Cin == 64, all taps in one CTA): the strip also carries the kh-1 halo rows, tap (r, s) starts
     // r*Wp + s rows into it, and ONE M = 128 accumulator holds TWO taps: its second 64-row column block is the same strip read
     // foff-difference rows later - the descriptor's leading-dimension byte offset is simply that distance (blocks overlap).
+    int mma2;                   // a second warp issues the odd accumulators (QB_WGRAD_MMA2=0 disables)
     int uissue;                 // sbs with the issue loop on the uniform datapath (experiment: QB_WGRAD_UISSUE=1)
     int sbs;                    // hi | lo gradient planes side by side on N: ONE N = 256 MMA per K step (the single issuing
                                 // thread, not the tensor pipe, bounds this kernel), column halves added in the drain
@@ -960,6 +973,7 @@ k_conv_wgrad(const __grid_constant__ CUtensorMap tmap_x, const __grid_constant__
     const int t_begin = (int)(((int64_t)g.total_tiles * slice) / g.slices);
     const int t_end = (int)(((int64_t)g.total_tiles * (slice + 1)) / g.slices);
     const uint32_t acc_stride = g.sbs ? 256u : (uint32_t)(g.BN < 32 ? 32 : g.BN);
+    const int nmma = (g.mma2 && !g.flat && !g.uissue && jn >= 2) ? 2 : 1;    // MMA-issuing warps of this CTA
 
     // a tail M tile has fewer runs than rpm: its unused operand rows must not hold NaN patterns
     // (flat: neither the x rows behind a box - read by the shifted taps - nor the gradient rows between Pbox and P)
@@ -969,8 +983,8 @@ k_conv_wgrad(const __grid_constant__ CUtensorMap tmap_x, const __grid_constant__
         tma_prefetch_desc(&tmap_x);
         tma_prefetch_desc(&tmap_g0);
         for (int s = 0; s < g.a_stages; ++s) { mbar_init(&a_full[s], 1); mbar_init(&a_empty[s], 1); }
-        for (int s = 0; s < g.b_stages; ++s) { mbar_init(&b_full[s], 1); mbar_init(&b_empty[s], 1); }
-        mbar_init(done_bar, 1);
+        for (int s = 0; s < g.b_stages; ++s) { mbar_init(&b_full[s], 1); mbar_init(&b_empty[s], (uint32_t)nmma); }
+        mbar_init(done_bar, (uint32_t)nmma);
         fence_barrier_init();
     }
     if (warp == 1) tmem_alloc<512>(tmem_slot);
@@ -1044,10 +1058,13 @@ k_conv_wgrad(const __grid_constant__ CUtensorMap tmap_x, const __grid_constant__
                 }
             }
         }
-    } else if (warp == 1) {
+    } else if (warp == 1 || (warp == 6 && nmma == 2)) {
+        const int mw = warp == 1 ? 0 : 1;                       // this warp issues the accumulators j with j % nmma == mw
         const uint32_t idesc = idesc_bf16(128, (uint32_t)g.BN, 1, 1);
         const int ksteps = g.P / 16;
         const uint32_t lead = elect_one() ? 1u : 0u;           // the one lane that issues (uissue mode)
+        int j_last = jn - 1;                                    // the last accumulator this warp owns
+        while (j_last % nmma != mw) --j_last;
         uint32_t ia = 0, ib = 0;
         for (int t = t_begin; t < t_end; ++t, ++ib) {
             const int sbi = ib % g.b_stages;
@@ -1106,6 +1123,7 @@ k_conv_wgrad(const __grid_constant__ CUtensorMap tmap_x, const __grid_constant__
                 continue;
             }
             for (int j = 0; j < jn; ++j, ++ia) {
+                if (j % nmma != mw) continue;                   // (the slot counter ia still advances)
                 const int s = ia % g.a_stages;
                 mbar_wait_trap(&a_full[s], (ia / g.a_stages) & 1);
                 tc_fence_after_sync();
@@ -1133,13 +1151,13 @@ k_conv_wgrad(const __grid_constant__ CUtensorMap tmap_x, const __grid_constant__
                         }
                     }
                     umma_commit(&a_empty[s]);
-                    if (j == jn - 1) umma_commit(&b_empty[sbi]);
-                    if (j == jn - 1 && t == t_end - 1) umma_commit(done_bar);
+                    if (j == j_last) umma_commit(&b_empty[sbi]);
+                    if (j == j_last && t == t_end - 1) umma_commit(done_bar);
                 }
                 __syncwarp();
             }
         }
-    } else if (t_end > t_begin) {
+    } else if (warp >= 2 && warp <= 5 && t_end > t_begin) {
         // ===== drain: partial[slice][row][n], rows = (tap, c) of this CTA's M tiles =====
         const int sub = warp & 3;
         mbar_wait_trap(done_bar, 0);
@@ -1278,6 +1296,11 @@ static int wgrad_geom2(WgradGeom& g, int64_t B, int64_t Ho, int64_t Wo, int64_t 
     g.nblocks = (int)((Cout + g.BN - 1) / g.BN);
     static const bool sbs_off = getenv("QB_WGRAD_SBS") && getenv("QB_WGRAD_SBS")[0] == '0';
     g.sbs = (!sbs_off && g_planes == 2 && g.BN == 128 && g.RN == 64) ? 1 : 0;
+    // OFF by default: with the second issuing warp this kernel faults intermittently on the layer1 geometry (five accumulators,
+    // odd count) inside a training step although every isolated run passes (the same scheme in k_conv_dgrad_flat, where both
+    // warps walk the same stages, is stable and stays on); QB_WGRAD_MMA2=1 enables it for experiments.
+    static const bool mma2_on = getenv("QB_WGRAD_MMA2") && getenv("QB_WGRAD_MMA2")[0] == '1';
+    g.mma2 = mma2_on ? 1 : 0;
     static const bool uissue_on = getenv("QB_WGRAD_UISSUE") && getenv("QB_WGRAD_UISSUE")[0] == '1';
     g.uissue = (g.sbs && uissue_on) ? 1 : 0;
     const int acc_stride = g.sbs ? 256 : (g.BN < 32 ? 32 : g.BN);

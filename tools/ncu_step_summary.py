@@ -65,5 +65,33 @@ def main():
                                                                      " ".join("%7.1f" % x for x in w)))
 
 
+    # --json PATH: DRAM bytes (read + written) per launch of the dominant kernel of each C-ABI entry point, the `traffic`
+    # figure of bench.py's roofline (profiles/traffic_rNN.json)
+    if "--json" in sys.argv:
+        import json
+        entry = {"k_conv_wgrad": "qb_conv_wgrad", "k_conv_dgrad_flat": "qb_conv_dgrad", "k_conv_dgrad": "qb_conv_dgrad",
+                 "k_conv_i8": "qb_conv_i8_fwd", "k_conv_stem": "qb_conv_stem_fwd", "k_rbn_stats_q8_nhwc": "qb_rangebn_stats_nhwc",
+                 "k_rbn_bwd_reduce_nhwc": "qb_rangebn_bwd_reduce_nhwc", "k_rbn_bwd_apply_fused": "qb_rangebn_bwd_apply_fused_nhwc",
+                 "k_rbn_apply_codes_nhwc": "qb_rangebn_apply_nhwc", "k_bwd_pack": "qb_bwd_pack", "k_fq_affine_v8": "qb_fakequant_affine16",
+                 "k_relu_bwd_minmax": "qb_relu_bwd_minmax_bits", "k_maxpool_bwd_3s2": "qb_maxpool2d_relu_nhwc_bwd",
+                 "k_maxpool_fwd_nhwc": "qb_maxpool2d_nhwc_fwd", "k_conv_dw3x3": "qb_conv_dw_fwd", "k_conv_dw_dgrad": "qb_conv_dw_dgrad",
+                 "k_conv_dw_wgrad": "qb_conv_dw_wgrad", "k_gemm_i8": "qb_gemm_i8"}
+        out, acc = {}, {}
+        for name, f in fam.items():
+            base = re.sub(r"<.*$", "", name)
+            e = entry.get(base)
+            if name.startswith("k_measure_stats"):
+                e = "qb_rangebn_apply_relu_measure" if ("<3" in name or "<4" in name) else "qb_measure_stats"
+            if e is None:
+                continue
+            b = sum((val(r, "dram__bytes_read.sum") or 0.0) + (val(r, "dram__bytes_write.sum") or 0.0) for r in f)
+            a = acc.setdefault(e, [0.0, 0])
+            a[0] += b
+            a[1] += len(f)
+        for e, (b, n) in acc.items():
+            out[e] = round(b / n)
+        json.dump(out, open(sys.argv[sys.argv.index("--json") + 1], "w"), indent=1, sort_keys=True)
+
+
 if __name__ == "__main__":
     main()
