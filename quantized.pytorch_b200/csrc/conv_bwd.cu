@@ -289,16 +289,16 @@ k_conv_dgrad(const __grid_constant__ CUtensorMap tmap_a0, const __grid_constant_
     if (warp == 0) {
         // ===== TMA producer =====
         if (elect_one()) {
-            uint32_t it = 0;
+            RingPos rp;
             const uint32_t a_box = (uint32_t)(g.TN * g.TH * g.TW) * rb;
             for (int t = blockIdx.x; t < total_tiles; t += gridDim.x) {
                 int tn, b0, h0, w0;
                 dg_decode_tile(t, g, tiles_m, tn, b0, h0, w0);
                 const int n0 = tn * BN;
                 for (int tp = 0; tp < g.ntaps; ++tp) {
-                    for (int kb = 0; kb < kblocks; ++kb, ++it) {
-                        const int s = it % g.stages;
-                        const uint32_t ph = (it / g.stages) & 1;
+                    for (int kb = 0; kb < kblocks; ++kb, rp.next(g.stages)) {
+                        const int s = rp.s;
+                        const uint32_t ph = rp.ph;
                         mbar_wait_trap(&empty_bar[s], ph ^ 1);
                         mbar_arrive_expect_tx(&full_bar[s], g.a_planes * a_box + g.b_planes * b_bytes);
                         uint8_t* sa = smem + (size_t)s * stage_bytes;
@@ -316,16 +316,16 @@ k_conv_dgrad(const __grid_constant__ CUtensorMap tmap_a0, const __grid_constant_
         // ===== MMA issuer =====
         constexpr uint32_t idesc = idesc_bf16(128, BN, 0, 0);
         const int ksteps = g.BK / 16;
-        uint32_t it = 0;
+        RingPos rp;
         int j = 0;
         for (int t = blockIdx.x; t < total_tiles; t += gridDim.x, ++j) {
             const int buf = j & 1;
             mbar_wait_trap(&tempty_bar[buf], ((j >> 1) & 1) ^ 1);
             tc_fence_after_sync();
             const uint32_t d_tmem = tmem_base + (uint32_t)buf * ACC;
-            for (int kb = 0; kb < num_kb; ++kb, ++it) {
-                const int s = it % g.stages;
-                const uint32_t ph = (it / g.stages) & 1;
+            for (int kb = 0; kb < num_kb; ++kb, rp.next(g.stages)) {
+                const int s = rp.s;
+                const uint32_t ph = rp.ph;
                 mbar_wait_trap(&full_bar[s], ph);
                 tc_fence_after_sync();
                 if (elect_one()) {
@@ -529,7 +529,8 @@ k_conv_dgrad_flat(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
     if (warp == 0) {
         if (elect_one()) {
             const uint32_t a_box = (uint32_t)(g.Wp * g.RH * g.TN) * rb;
-            uint32_t ia = 0, iw = 0;
+            uint32_t ia = 0;
+            RingPos rw;
             for (int t = blockIdx.x; t < total; t += gridDim.x) {
                 int tn, b0, h0;
                 decode(t, tn, b0, h0);
@@ -539,9 +540,9 @@ k_conv_dgrad_flat(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
                     mbar_wait_trap(&a_empty[sa], ((ia >> 1) & 1) ^ 1);
                     mbar_arrive_expect_tx(&a_full[sa], a_box);
                     tma_load_4d(s_a + (size_t)sa * a_slot, &tmap_a, &a_full[sa], kb * g.BK, g.dw_min, h0 + g.dh_min, b0);
-                    for (int tp = 0; tp < g.ntaps; ++tp, ++iw) {
-                        const int sw = iw % g.wstages;
-                        mbar_wait_trap(&w_empty[sw], ((iw / g.wstages) & 1) ^ 1);
+                    for (int tp = 0; tp < g.ntaps; ++tp, rw.next(g.wstages)) {
+                        const int sw = rw.s;
+                        mbar_wait_trap(&w_empty[sw], rw.ph ^ 1);
                         mbar_arrive_expect_tx(&w_full[sw], w_slot);
                         for (int p = 0; p < g.b_planes; ++p)
                             tma_load_3d(s_w + (size_t)sw * w_slot + (size_t)p * w_plane, &tmap_w, &w_full[sw], kb * g.BK, g.wtap[tp],
@@ -554,7 +555,9 @@ k_conv_dgrad_flat(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
         const int mw = warp == 1 ? 0 : 1;
         constexpr uint32_t idesc = idesc_bf16(128, SBS ? 2 * BN : BN, 0, 0);
         const int ksteps = g.BK / 16;
-        uint32_t ia = 0, iw = 0;
+        const uint64_t w_desc0 = desc_kmajor(smem_u32(s_w), rb);               // weight stage sw: + sw * w_slot
+        uint32_t ia = 0;
+        RingPos rw;
         int it = 0;
         for (int t = blockIdx.x; t < total; t += gridDim.x, ++it) {
             const int set = it & 1;
@@ -565,12 +568,12 @@ k_conv_dgrad_flat(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
                 const int sa = ia & 1;
                 mbar_wait_trap(&a_full[sa], (ia >> 1) & 1);
                 const uint64_t a_desc0 = desc_kmajor(smem_u32(s_a + (size_t)sa * a_slot), rb);
-                for (int tp = 0; tp < g.ntaps; ++tp, ++iw) {
-                    const int sw = iw % g.wstages;
-                    mbar_wait_trap(&w_full[sw], (iw / g.wstages) & 1);
+                for (int tp = 0; tp < g.ntaps; ++tp, rw.next(g.wstages)) {
+                    const int sw = rw.s;
+                    mbar_wait_trap(&w_full[sw], rw.ph);
                     tc_fence_after_sync();
                     if (elect_one()) {
-                        const uint64_t w_desc = desc_kmajor(smem_u32(s_w + (size_t)sw * w_slot), rb);
+                        const uint64_t w_desc = desc_add(w_desc0, (uint32_t)sw * w_slot);
                         const uint32_t first = (kb | tp) == 0;
                         for (int j = 0; j < g.J; ++j) {
                             if ((uint32_t)j % nmma != (uint32_t)mw) continue;
@@ -1007,13 +1010,13 @@ k_conv_wgrad(const __grid_constant__ CUtensorMap tmap_x, const __grid_constant__
 
     if (warp == 0) {
         if (elect_one()) {
-            uint32_t ia = 0, ib = 0;
+            RingPos ra, rb_;
             for (int t = t_begin; t < t_end; ++t) {
                 int b0, ho0, wo0;
                 decode(t, b0, ho0, wo0);
                 {   // gradient tile (B operand), shared by every accumulator of this CTA
-                    const int s = ib % g.b_stages;
-                    const uint32_t ph = (ib / g.b_stages) & 1;
+                    const int s = rb_.s;
+                    const uint32_t ph = rb_.ph;
                     mbar_wait_trap(&b_empty[s], ph ^ 1);
                     mbar_arrive_expect_tx(&b_full[s], g.flat ? (uint32_t)(g.g_planes * g.BN * g.Pbox * 2) : b_slot);
                     uint8_t* sb = s_b + (size_t)s * b_slot;
@@ -1021,11 +1024,11 @@ k_conv_wgrad(const __grid_constant__ CUtensorMap tmap_x, const __grid_constant__
                         for (int r = 0; r < nruns_b; ++r)
                             tma_load_4d(sb + (size_t)p * b_plane + (size_t)r * runB, p ? &tmap_g1 : &tmap_g0, &b_full[s],
                                         n0 + r * g.RN, wo0, ho0, b0);
-                    ++ib;
+                    rb_.next(g.b_stages);
                 }
                 if (g.flat) {                                  // one x strip per pixel tile: two 64-channel boxes on the padded pitch
-                    const int s = ia % g.a_stages;
-                    mbar_wait_trap(&a_empty[s], ((ia / g.a_stages) & 1) ^ 1);
+                    const int s = ra.s;
+                    mbar_wait_trap(&a_empty[s], ra.ph ^ 1);
                     uint8_t* sa = s_a + (size_t)s * a_slot;
                     if (g.flat == 2) {
                         mbar_arrive_expect_tx(&a_full[s], (uint32_t)(g.xrows * g.Wp) * rbA);
@@ -1035,12 +1038,12 @@ k_conv_wgrad(const __grid_constant__ CUtensorMap tmap_x, const __grid_constant__
                         for (int rr = 0; rr < 2; ++rr)
                             tma_load_4d(sa + (size_t)rr * runA, &tmap_x, &a_full[s], fcg * 128 + rr * 64, -g.pw, ho0 - g.ph + fr, b0);
                     }
-                    ++ia;
+                    ra.next(g.a_stages);
                     continue;
                 }
-                for (int j = 0; j < jn; ++j, ++ia) {
-                    const int s = ia % g.a_stages;
-                    const uint32_t ph = (ia / g.a_stages) & 1;
+                for (int j = 0; j < jn; ++j, ra.next(g.a_stages)) {
+                    const int s = ra.s;
+                    const uint32_t ph = ra.ph;
                     const int run0 = (mt0 + j) * g.rpm;
                     const int nr = (g.total_runs - run0 < g.rpm) ? g.total_runs - run0 : g.rpm;
                     mbar_wait_trap(&a_empty[s], ph ^ 1);
@@ -1065,17 +1068,17 @@ k_conv_wgrad(const __grid_constant__ CUtensorMap tmap_x, const __grid_constant__
         const uint32_t lead = elect_one() ? 1u : 0u;           // the one lane that issues (uissue mode)
         int j_last = jn - 1;                                    // the last accumulator this warp owns
         while (j_last % nmma != mw) --j_last;
-        uint32_t ia = 0, ib = 0;
-        for (int t = t_begin; t < t_end; ++t, ++ib) {
-            const int sbi = ib % g.b_stages;
-            mbar_wait_trap(&b_full[sbi], (ib / g.b_stages) & 1);
+        RingPos ra, rb_;
+        for (int t = t_begin; t < t_end; ++t, rb_.next(g.b_stages)) {
+            const int sbi = rb_.s;
+            mbar_wait_trap(&b_full[sbi], rb_.ph);
             const uint64_t b_desc = desc_mnmajor(smem_u32(s_b + (size_t)sbi * b_slot), rbB, runB);
             if (g.uissue) {                                     // N = 256 planes side by side, descriptors on the uniform datapath
                 const uint32_t idesc2 = idesc_bf16(128, 256u, 1, 1);
                 const uint32_t stepA = 16u * (uint32_t)rbA, stepB = 16u * (uint32_t)rbB;
-                for (int j = 0; j < jn; ++j, ++ia) {
-                    const int s = ia % g.a_stages;
-                    mbar_wait_trap(&a_full[s], (ia / g.a_stages) & 1);
+                for (int j = 0; j < jn; ++j, ra.next(g.a_stages)) {
+                    const int s = ra.s;
+                    mbar_wait_trap(&a_full[s], ra.ph);
                     tc_fence_after_sync();
                     uint64_t a_desc = desc_mnmajor(smem_u32(s_a + (size_t)s * a_slot), rbA, runA);
                     uint64_t b_d = b_desc;
@@ -1094,8 +1097,8 @@ k_conv_wgrad(const __grid_constant__ CUtensorMap tmap_x, const __grid_constant__
                 continue;
             }
             if (g.flat) {
-                const int s = ia % g.a_stages;
-                mbar_wait_trap(&a_full[s], (ia / g.a_stages) & 1);
+                const int s = ra.s;
+                mbar_wait_trap(&a_full[s], ra.ph);
                 tc_fence_after_sync();
                 if (elect_one()) {
                     const uint64_t a_desc0 = desc_mnmajor(smem_u32(s_a + (size_t)s * a_slot), rbA, runA);
@@ -1119,13 +1122,13 @@ k_conv_wgrad(const __grid_constant__ CUtensorMap tmap_x, const __grid_constant__
                     if (t == t_end - 1) umma_commit(done_bar);
                 }
                 __syncwarp();
-                ++ia;
+                ra.next(g.a_stages);
                 continue;
             }
-            for (int j = 0; j < jn; ++j, ++ia) {
-                if (j % nmma != mw) continue;                   // (the slot counter ia still advances)
-                const int s = ia % g.a_stages;
-                mbar_wait_trap(&a_full[s], (ia / g.a_stages) & 1);
+            for (int j = 0; j < jn; ++j, ra.next(g.a_stages)) {
+                if (j % nmma != mw) continue;                   // (the slot position still advances)
+                const int s = ra.s;
+                mbar_wait_trap(&a_full[s], ra.ph);
                 tc_fence_after_sync();
                 if (elect_one()) {
                     const uint64_t a_desc = desc_mnmajor(smem_u32(s_a + (size_t)s * a_slot), rbA, runA);

@@ -169,12 +169,12 @@ k_conv_i8(const __grid_constant__ CUtensorMap tmap_x, const __grid_constant__ CU
         if (lead && g.halo) {
             mbar_arrive_expect_tx(wfull_bar, wres_bytes);
             for (int tap = 0; tap < taps; ++tap) tma_load_3d(wres + (size_t)tap * b_bytes, &tmap_w, wfull_bar, 0, tap, 0);
-            uint32_t it = 0;
-            for (int t = blockIdx.x; t < total_tiles; t += gridDim.x, ++it) {
+            RingPos rp;
+            for (int t = blockIdx.x; t < total_tiles; t += gridDim.x, rp.next(g.stages)) {
                 int tn, b0, ho0, wo0;                           // tiles_n == 1 in halo mode: tn == 0
                 conv_decode_tile(t, g, tiles_m, tn, b0, ho0, wo0);
-                const int s = it % g.stages;
-                const uint32_t ph = (it / g.stages) & 1;
+                const int s = rp.s;
+                const uint32_t ph = rp.ph;
                 mbar_wait(&empty_bar[s], ph ^ 1);
                 mbar_arrive_expect_tx(&full_bar[s], stage_bytes);
                 uint8_t* sa = smem + (size_t)s * stage_bytes;
@@ -182,7 +182,7 @@ k_conv_i8(const __grid_constant__ CUtensorMap tmap_x, const __grid_constant__ CU
                     tma_load_4d(sa + (size_t)s_ * hbox_bytes, &tmap_x, &full_bar[s], 0, wo0 - g.pad + s_, ho0 - g.pad, b0);
             }
         } else if (lead) {
-            uint32_t it = 0;
+            RingPos rp;
             for (int t = blockIdx.x; t < total_tiles; t += gridDim.x) {
                 int tn, b0, ho0, wo0;
                 conv_decode_tile(t, g, tiles_m, tn, b0, ho0, wo0);
@@ -190,9 +190,9 @@ k_conv_i8(const __grid_constant__ CUtensorMap tmap_x, const __grid_constant__ CU
                 for (int r = 0; r < g.kh; ++r) {
                     for (int s_ = 0; s_ < g.kw; ++s_) {
                         const int tap = r * g.kw + s_;
-                        for (int cb = 0; cb < cblocks; ++cb, ++it) {
-                            const int s = it % g.stages;
-                            const uint32_t ph = (it / g.stages) & 1;
+                        for (int cb = 0; cb < cblocks; ++cb, rp.next(g.stages)) {
+                            const int s = rp.s;
+                            const uint32_t ph = rp.ph;
                             mbar_wait(&empty_bar[s], ph ^ 1);
                             mbar_arrive_expect_tx(&full_bar[s], (uint32_t)(g.TN * g.TH * g.TW * g.BK) + b_bytes);
                             uint8_t* sa = smem + (size_t)s * stage_bytes;
@@ -208,7 +208,8 @@ k_conv_i8(const __grid_constant__ CUtensorMap tmap_x, const __grid_constant__ CU
         // ===== MMA issuer =====
         constexpr uint32_t idesc = umma_idesc(/*S32*/ 2, /*A u8*/ 0, /*B s8*/ 1, 128, BN);
         const int mmas = g.BK / 32;
-        uint32_t it = 0;
+        const uint64_t ring_desc0 = umma_smem_desc(smem_u32(smem), g.BK);      // stage s: + s * stage_bytes (one add per stage)
+        RingPos rp;
         int j = 0;
         for (int t = blockIdx.x; t < total_tiles; t += gridDim.x, ++j) {
             const int buf = j & 1;
@@ -217,8 +218,8 @@ k_conv_i8(const __grid_constant__ CUtensorMap tmap_x, const __grid_constant__ CU
             const uint32_t d_tmem = tmem_base + (uint32_t)(buf * BN);
             if (g.halo) {
                 if (j == 0) mbar_wait(wfull_bar, 0);
-                const int s = it % g.stages;
-                const uint32_t ph = (it / g.stages) & 1;
+                const int s = rp.s;
+                const uint32_t ph = rp.ph;
                 mbar_wait(&full_bar[s], ph);
                 tc_fence_after_sync();
                 if (elect_one()) {
@@ -235,16 +236,16 @@ k_conv_i8(const __grid_constant__ CUtensorMap tmap_x, const __grid_constant__ CU
                     umma_commit(&tfull_bar[buf]);
                 }
                 __syncwarp();
-                ++it;
+                rp.next(g.stages);
                 continue;
             }
-            for (int kb = 0; kb < num_kb; ++kb, ++it) {
-                const int s = it % g.stages;
-                const uint32_t ph = (it / g.stages) & 1;
+            for (int kb = 0; kb < num_kb; ++kb, rp.next(g.stages)) {
+                const int s = rp.s;
+                const uint32_t ph = rp.ph;
                 mbar_wait(&full_bar[s], ph);
                 tc_fence_after_sync();
                 if (elect_one()) {
-                    const uint64_t a_desc = umma_smem_desc(smem_u32(smem + (size_t)s * stage_bytes), g.BK);
+                    const uint64_t a_desc = desc_add(ring_desc0, (uint32_t)s * stage_bytes);
                     const uint64_t b_desc = desc_add(a_desc, a_bytes);
                     if (mmas == 4) {
                         umma_i8(d_tmem, a_desc, b_desc, idesc, kb != 0);

@@ -130,6 +130,17 @@ __device__ __forceinline__ void umma_f16(uint32_t d_tmem, uint64_t a_desc, uint6
         ::"r"(d_tmem), "l"(a_desc), "l"(b_desc), "r"(idesc), "r"(accumulate)
         : "memory");
 }
+// Position in a ring of `stages` pipeline slots: slot index and the parity of the pass over the ring.  Advanced incrementally -
+// `it % stages` / `it / stages` with a run-time divisor cost the single MMA-issuing thread ~20 instructions (I2F, MUFU, F2I ...)
+// per stage, on the critical path of a kernel whose bound is exactly that thread.
+struct RingPos {
+    int s = 0;
+    uint32_t ph = 0;
+    __device__ __forceinline__ void next(int stages) {
+        if (++s == stages) { s = 0; ph ^= 1u; }
+    }
+};
+
 // Predicated forms: every lane of the issuing warp runs the (warp-uniform) descriptor arithmetic, so the compiler keeps it on
 // the uniform datapath, and only the lane with pred != 0 issues.  `pred` must select the same single lane every time.
 __device__ __forceinline__ void umma_f16_if(uint32_t pred, uint32_t d_tmem, uint64_t a_desc, uint64_t b_desc, uint32_t idesc,

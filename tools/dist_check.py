@@ -76,7 +76,7 @@ def main():
     torch.backends.cudnn.allow_tf32 = False
     torch.backends.cuda.matmul.allow_tf32 = False
     if args.model == "resnet18":
-        mk, shape, ncls = (lambda: models.resnet_quantized(Q, depth=18, dataset="imagenet")), (3, 64, 64), 1000
+        mk, shape, ncls = (lambda: models.resnet_quantized(Q, depth=18, dataset="imagenet")), (3, 224, 224), 1000
     else:
         mk, shape, ncls = (lambda: models.resnet_quantized(Q, depth=20, dataset="cifar10")), (3, 32, 32), 10
     torch.manual_seed(5)
