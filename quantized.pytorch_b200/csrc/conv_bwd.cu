@@ -975,7 +975,7 @@ k_conv_wgrad(const __grid_constant__ CUtensorMap tmap_x, const __grid_constant__
     const int fr = g.flat == 1 ? mg / cgroups : 0, fcg = g.flat == 1 ? mg - fr * cgroups : 0;
     const int t_begin = (int)(((int64_t)g.total_tiles * slice) / g.slices);
     const int t_end = (int)(((int64_t)g.total_tiles * (slice + 1)) / g.slices);
-    const uint32_t acc_stride = g.sbs ? 256u : (uint32_t)(g.BN < 32 ? 32 : g.BN);
+    const uint32_t acc_stride = g.sbs ? 2u * (uint32_t)g.BN : (uint32_t)(g.BN < 32 ? 32 : g.BN);
     const int nmma = (g.mma2 && !g.flat && !g.uissue && jn >= 2) ? 2 : 1;    // MMA-issuing warps of this CTA
 
     // a tail M tile has fewer runs than rpm: its unused operand rows must not hold NaN patterns
@@ -1069,10 +1069,11 @@ k_conv_wgrad(const __grid_constant__ CUtensorMap tmap_x, const __grid_constant__
         int j_last = jn - 1;                                    // the last accumulator this warp owns
         while (j_last % nmma != mw) --j_last;
         RingPos ra, rb_;
+        const uint64_t a_ring0 = desc_mnmajor(smem_u32(s_a), rbA, runA), b_ring0 = desc_mnmajor(smem_u32(s_b), rbB, runB);
         for (int t = t_begin; t < t_end; ++t, rb_.next(g.b_stages)) {
             const int sbi = rb_.s;
             mbar_wait_trap(&b_full[sbi], rb_.ph);
-            const uint64_t b_desc = desc_mnmajor(smem_u32(s_b + (size_t)sbi * b_slot), rbB, runB);
+            const uint64_t b_desc = desc_add(b_ring0, (uint32_t)sbi * b_slot);
             if (g.uissue) {                                     // N = 256 planes side by side, descriptors on the uniform datapath
                 const uint32_t idesc2 = idesc_bf16(128, 256u, 1, 1);
                 const uint32_t stepA = 16u * (uint32_t)rbA, stepB = 16u * (uint32_t)rbB;
@@ -1131,12 +1132,12 @@ k_conv_wgrad(const __grid_constant__ CUtensorMap tmap_x, const __grid_constant__
                 mbar_wait_trap(&a_full[s], ra.ph);
                 tc_fence_after_sync();
                 if (elect_one()) {
-                    const uint64_t a_desc = desc_mnmajor(smem_u32(s_a + (size_t)s * a_slot), rbA, runA);
+                    const uint64_t a_desc = desc_add(a_ring0, (uint32_t)s * a_slot);
                     const uint32_t d_tmem = tmem_base + (uint32_t)j * acc_stride;
                     const uint32_t stepA = 16u * (uint32_t)rbA, stepB = 16u * (uint32_t)rbB;
                     uint32_t acc = t != t_begin;
-                    if (g.sbs) {                                 // planes are 2 + 2 consecutive 64-channel runs: N = 256 spans both
-                        const uint32_t idesc2 = idesc_bf16(128, 256u, 1, 1);
+                    if (g.sbs) {                                 // the planes are consecutive 64-channel runs: N = 2*BN spans both
+                        const uint32_t idesc2 = idesc_bf16(128, 2u * (uint32_t)g.BN, 1, 1);
                         for (int ks = 0; ks < ksteps; ++ks) {
                             umma_f16(d_tmem, desc_add(a_desc, ks * stepA), desc_add(b_desc, ks * stepB), idesc2, acc);
                             acc = 1u;
@@ -1172,7 +1173,7 @@ k_conv_wgrad(const __grid_constant__ CUtensorMap tmap_x, const __grid_constant__
                 tmem_ld_32x32(tmem_base + (uint32_t)j * acc_stride + (uint32_t)c0 + ((uint32_t)(sub * 32) << 16), r);
                 if (g.sbs) {
                     uint32_t r2[32];
-                    tmem_ld_32x32(tmem_base + (uint32_t)j * acc_stride + 128u + (uint32_t)c0 + ((uint32_t)(sub * 32) << 16), r2);
+                    tmem_ld_32x32(tmem_base + (uint32_t)j * acc_stride + (uint32_t)g.BN + (uint32_t)c0 + ((uint32_t)(sub * 32) << 16), r2);
                     tmem_ld_wait();
 #pragma unroll
                     for (int u = 0; u < 32; ++u) r[u] = __float_as_uint(__uint_as_float(r[u]) + __uint_as_float(r2[u]));
@@ -1298,15 +1299,17 @@ static int wgrad_geom2(WgradGeom& g, int64_t B, int64_t Ho, int64_t Wo, int64_t 
     g.mrows = kh * kw * (int)Cin;
     g.nblocks = (int)((Cout + g.BN - 1) / g.BN);
     static const bool sbs_off = getenv("QB_WGRAD_SBS") && getenv("QB_WGRAD_SBS")[0] == '0';
-    g.sbs = (!sbs_off && g_planes == 2 && g.BN == 128 && g.RN == 64) ? 1 : 0;
+    // (BN = 64: an N = 64 MMA costs the same 75 cycles as an N = 128 one - profiles/umma_rate_probe_r02h.txt - so putting the two
+    // planes of a 64-channel tile side by side halves the tensor time of the C_out = 64 layers)
+    g.sbs = (!sbs_off && g_planes == 2 && (g.BN == 128 || g.BN == 64) && g.RN == 64) ? 1 : 0;
     // OFF by default: with the second issuing warp this kernel faults intermittently on the layer1 geometry (five accumulators,
     // odd count) inside a training step although every isolated run passes (the same scheme in k_conv_dgrad_flat, where both
     // warps walk the same stages, is stable and stays on); QB_WGRAD_MMA2=1 enables it for experiments.
     static const bool mma2_on = getenv("QB_WGRAD_MMA2") && getenv("QB_WGRAD_MMA2")[0] == '1';
     g.mma2 = mma2_on ? 1 : 0;
     static const bool uissue_on = getenv("QB_WGRAD_UISSUE") && getenv("QB_WGRAD_UISSUE")[0] == '1';
-    g.uissue = (g.sbs && uissue_on) ? 1 : 0;
-    const int acc_stride = g.sbs ? 256 : (g.BN < 32 ? 32 : g.BN);
+    g.uissue = (g.sbs && g.BN == 128 && uissue_on) ? 1 : 0;
+    const int acc_stride = g.sbs ? 2 * g.BN : (g.BN < 32 ? 32 : g.BN);
     int jmax = 512 / acc_stride;
     if (jmax > WG_MAX_ACC) jmax = WG_MAX_ACC;
     g.mgroups = (g.mtiles + jmax - 1) / jmax;

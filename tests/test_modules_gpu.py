@@ -306,14 +306,33 @@ def test_tensorcore_modules_vs_oracle(kind, cfg, shape, relu_input):
     """QConv2d / QLinear on the int8 tcgen05 path (geometry supported) against the CPU oracle modules: forward within
     1e-4 relative L2 of the fp32 reference, bi-precision backward (dW from g, dX from the quantized g) with the same
     injected noise."""
+    _tc_case(kind, cfg, shape, relu_input, (8, 8, 8))
+
+
+@pytest.mark.parametrize("kind,cfg,shape", [
+    ("conv", dict(cin=64, cout=64, k=3, stride=1, pad=1, bias=False), (4, 64, 14, 14)),
+    ("conv", dict(cin=64, cout=128, k=3, stride=2, pad=1, bias=True), (4, 64, 14, 14)),
+    ("conv", dict(cin=128, cout=256, k=1, stride=2, pad=0, bias=False), (2, 128, 8, 8)),
+    ("lin", dict(cin=512, cout=1000, bias=True), (32, 512)),
+])
+@pytest.mark.parametrize("bits", [(4, 4, 8), (4, 2, 4), (8, 4, 8), (2, 2, 8)])
+def test_mixed_bit_modules_vs_oracle(kind, cfg, shape, bits):
+    """the mixed-bit configurations of the distillation workload (activations / weights / gradients at
+    4/4/8, 4/2/4, 8/4/8, 2/2/8 bits; models/resnet.py:933-987) run on the SAME tensor-core kernels - sub-byte codes ride in
+    uint8 / bf16 containers - and match the oracle to the 8-bit tolerances, forward and bi-precision backward."""
+    _tc_case(kind, cfg, shape, True, bits)
+
+
+def _tc_case(kind, cfg, shape, relu_input, bits):
+    ba, bw, bg = bits
     Q = q()
     gen = torch.Generator().manual_seed(sum(shape) + cfg["cout"])
 
     def build(ns):
         if kind == "conv":
             return ns.QConv2d(cfg["cin"], cfg["cout"], cfg["k"], stride=cfg["stride"], padding=cfg["pad"], bias=cfg["bias"],
-                              num_bits=8, num_bits_weight=8, num_bits_grad=8, biprecision=True)
-        return ns.QLinear(cfg["cin"], cfg["cout"], bias=cfg["bias"], num_bits=8, num_bits_weight=8, num_bits_grad=8,
+                              num_bits=ba, num_bits_weight=bw, num_bits_grad=bg, biprecision=True)
+        return ns.QLinear(cfg["cin"], cfg["cout"], bias=cfg["bias"], num_bits=ba, num_bits_weight=bw, num_bits_grad=bg,
                           biprecision=True)
 
     ref, mod = build(qref_modules).train(), build(Q)
