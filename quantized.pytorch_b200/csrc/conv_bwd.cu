@@ -61,12 +61,6 @@ __device__ __forceinline__ uint64_t desc_mnmajor(uint32_t addr, int rb, uint32_t
 __host__ __device__ constexpr uint32_t idesc_bf16(uint32_t M, uint32_t N, uint32_t a_mn, uint32_t b_mn) {
     return (1u << 4) | (1u << 7) | (1u << 10) | (a_mn << 15) | (b_mn << 16) | ((N >> 3) << 17) | ((M >> 4) << 24);
 }
-__device__ __forceinline__ void mbar_wait_trap(uint64_t* bar, uint32_t parity) {
-    uint32_t spins = 0;
-    while (!mbar_try_wait(bar, parity)) {
-        if (++spins > (1u << 28)) __trap();                   // a lost completion must not hang the GPU
-    }
-}
 
 // ------------------------------------------------------------------------------------------------
 // qb_bwd_pack: gradient quantizer -> bf16 integer codes, and / or bf16 hi-lo split of the raw tensor
