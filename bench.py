@@ -356,7 +356,7 @@ def main_ours(args, rank, world, local_rank):
     print(json.dumps(line))
 
 
-TENSOR_FAMILIES = {"qb_conv_i8_fwd": "i8", "qb_gemm_i8": "i8", "qb_conv_stem_fwd": "i8", "qb_conv_dgrad": "bf16", "qb_conv_wgrad": "bf16",
+TENSOR_FAMILIES = {"qb_conv_i8_fwd": "i8", "qb_gemm_i8": "i8", "qb_conv_stem_fwd": "i8", "qb_conv_dgrad": "bf16", "qb_conv_dgrad_acc": "bf16", "qb_conv_wgrad": "bf16",
                    "qb_conv_stem_wgrad": "tf32", "qb_conv_stem_wgrad16": "bf16"}
 
 

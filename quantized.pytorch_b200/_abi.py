@@ -101,6 +101,7 @@ PROTOTYPES = {
     "qb_debug_umma_rate": (_i32, [_p, _i32, _i32, _i32, _i32, _p]),
     "qb_wt_pack": (_i32, [_p, _p, _i64, _i64, _i32, _p]),
     "qb_conv_dgrad": (_i32, [_p, _p, _p, _p, _i64, _i64, _i64, _i64, _i64, _i32, _i32, _i32, _i32, _p, _i32, _flt, _p]),
+    "qb_conv_dgrad_acc": (_i32, [_p, _p, _p, _i64, _i64, _i64, _i64, _i64, _i32, _i32, _i32, _p, _i32, _flt, _p]),
     "qb_conv_wgrad_ws_bytes": (_sz, [_i64, _i64, _i64, _i64, _i64, _i32, _i32, _i32, _i32]),
     "qb_conv_wgrad": (_i32, [_p, _p, _p, _p, _p, _p, _i64, _i64, _i64, _i64, _i64, _i32, _i32, _i32, _i32, _p, _i32, _p, _sz, _p]),
     "qb_conv_i8_fwd": (_i32, [_p, _p, _p, _i64, _i64, _i64, _i64, _i64, _i32, _i32, _i32, _i32, _p, _i32, _p, _p, _i32,
@@ -700,12 +701,29 @@ def conv_bwd_supported(Cin, Cout, kh, kw, stride, pad):
     return Cin % 16 == 0 and Cout % 8 == 0 and kh * kw <= 9 and stride in (1, 2)
 
 
-def conv_dgrad(a0, a1, wt, x_shape, Cout, kh, kw, stride, pad, scale_range=None, scale_bits=8, scale_mul=1.0):
-    """dX [B, Cin, H, W] (channels-last fp32) of a convolution from the bf16 plane(s) of its output gradient (qb_conv_dgrad)."""
+def conv_dgrad(a0, a1, wt, x_shape, Cout, kh, kw, stride, pad, scale_range=None, scale_bits=8, scale_mul=1.0, accumulate_into=None):
+    """dX [B, Cin, H, W] (channels-last fp32) of a convolution from the bf16 plane(s) of its output gradient (qb_conv_dgrad).
+    ``accumulate_into``: a tensor of dX's shape and layout holding the other gradient of the layer's input (a residual skip);
+    the result is added INTO it by the kernel's reduce-add stores (qb_conv_dgrad_acc) and that tensor is returned - or, where
+    the accumulating kernel does not apply, by a separate in-place add."""
+    global _next_ops
     B, Cin, H, W = x_shape
+    if accumulate_into is not None:
+        acc = accumulate_into
+        ok = (a1 is None and stride == 1 and acc.dtype == torch.float32 and tuple(acc.shape) == (B, Cin, H, W) and is_nhwc(acc)
+              and acc.data_ptr() % 16 == 0)
+        if ok:
+            _next_ops = 2 * B * H * W * Cout * kh * kw * Cin
+            try:
+                _run("qb_conv_dgrad_acc", 2 * a0.numel() + 4 * Cout * Cin * kh * kw + 8 * acc.numel(), _ptr(a0), _ptr(wt), _ptr(acc), B, H,
+                     W, Cin, Cout, kh, kw, pad, _ptr(scale_range), int(scale_bits), float(scale_mul), _stream())
+                return acc
+            except QB200Error:
+                _next_ops = 0
+        dx = conv_dgrad(a0, a1, wt, x_shape, Cout, kh, kw, stride, pad, scale_range, scale_bits, scale_mul)
+        return acc.add_(dx) if acc.shape == dx.shape else dx + acc
     dx = torch.empty((B, Cin, H, W), dtype=torch.float32, device=a0.device, memory_format=torch.channels_last)
     Ho, Wo = (H + 2 * pad - kh) // stride + 1, (W + 2 * pad - kw) // stride + 1
-    global _next_ops
     _next_ops = 2 * B * Ho * Wo * Cout * kh * kw * Cin          # useful operations (the kernel executes 2-3 bf16 planes of them)
     _NLAUNCH["qb_conv_dgrad"] = stride * stride if kh >= stride else 1
     _run("qb_conv_dgrad", (2 if a1 is None else 4) * a0.numel() + 4 * Cout * Cin * kh * kw + 4 * dx.numel(), _ptr(a0), _ptr(a1),

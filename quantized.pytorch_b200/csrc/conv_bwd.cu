@@ -454,6 +454,7 @@ struct DflatGeom {
     int off[DG_MAX_TAPS], wtap[DG_MAX_TAPS];
     int nstage;                 // staging slab buffers (1 or 2)
     int mma2;                   // second MMA-issuing warp (QB_DGRAD_MMA2=0 disables)
+    int accumulate;             // dx += result (TMA reduce-add stores): the skip-connection gradient is already in dx
     FastDiv d_tiles_m, d_tiles_h;
 };
 
@@ -663,7 +664,8 @@ k_conv_dgrad_flat(const __grid_constant__ CUtensorMap tmap_a, const __grid_const
                 fence_proxy_async();
                 asm volatile("bar.sync 2, 256;" ::: "memory");
                 if (e_all == 0) {
-                    tma_store_4d(&tmap_o, staging + (size_t)sbuf * slab_bytes, n0 + cs * 32, 0, h0, b0);
+                    if (g.accumulate) tma_reduce_add_4d(&tmap_o, staging + (size_t)sbuf * slab_bytes, n0 + cs * 32, 0, h0, b0);
+                    else tma_store_4d(&tmap_o, staging + (size_t)sbuf * slab_bytes, n0 + cs * 32, 0, h0, b0);
                     tma_store_commit();
                 }
             }
@@ -762,9 +764,29 @@ static size_t dgrad_flat_geom(DflatGeom& g, int B, int Hc, int Wc, int Cn, int C
  *   planes: hi / lo split);  wt: qb_wt_pack's planes;  dx: fp32 [B,H,W,Cin] channels-last.
  *   dx = scale * SUM, scale = scale_mul * (scale_range ? s(scale_range, scale_bits) : 1)  (s = the zero-point quantizer's
  *   step, quantize.py:78-80).  Linear layers: H = W = kh = kw = 1.                                                       */
+static int conv_dgrad_impl(const uint16_t* a0, const uint16_t* a1, const uint16_t* wt, float* dx, int64_t B, int64_t H, int64_t W,
+                           int64_t Cin, int64_t Cout, int kh, int kw, int stride, int pad, const float* scale_range,
+                           int scale_bits, float scale_mul, int accumulate, void* stream);
+
 extern "C" int qb_conv_dgrad(const uint16_t* a0, const uint16_t* a1, const uint16_t* wt, float* dx, int64_t B, int64_t H, int64_t W,
                              int64_t Cin, int64_t Cout, int kh, int kw, int stride, int pad, const float* scale_range,
                              int scale_bits, float scale_mul, void* stream) {
+    return conv_dgrad_impl(a0, a1, wt, dx, B, H, W, Cin, Cout, kh, kw, stride, pad, scale_range, scale_bits, scale_mul, 0, stream);
+}
+
+/* As qb_conv_dgrad, but dx += result: dx already holds the OTHER gradient that reaches the layer's input - the skip connection
+ * of a residual block (models/resnet_quantized.py:62-68: `out += residual`; autograd's separate accumulation pass of 12 B/elem
+ * disappears into TMA reduce-add stores).  Unit stride, single-plane (code) gradients, geometries the flat-strip kernel takes;
+ * anything else returns QB_ERR_UNSUPPORTED with dx untouched. */
+extern "C" int qb_conv_dgrad_acc(const uint16_t* a0, const uint16_t* wt, float* dx, int64_t B, int64_t H, int64_t W, int64_t Cin,
+                                 int64_t Cout, int kh, int kw, int pad, const float* scale_range, int scale_bits, float scale_mul,
+                                 void* stream) {
+    return conv_dgrad_impl(a0, nullptr, wt, dx, B, H, W, Cin, Cout, kh, kw, 1, pad, scale_range, scale_bits, scale_mul, 1, stream);
+}
+
+static int conv_dgrad_impl(const uint16_t* a0, const uint16_t* a1, const uint16_t* wt, float* dx, int64_t B, int64_t H, int64_t W,
+                           int64_t Cin, int64_t Cout, int kh, int kw, int stride, int pad, const float* scale_range,
+                           int scale_bits, float scale_mul, int accumulate, void* stream) {
     QB_CHECK_ARG(a0 && wt && dx, "qb_conv_dgrad: null pointer");
     QB_CHECK_ARG(B > 0 && H > 0 && W > 0 && Cin > 0 && Cout > 0 && kh > 0 && kw > 0 && stride > 0 && pad >= 0, "qb_conv_dgrad: bad shape");
     const int64_t Ho = (H + 2 * pad - kh) / stride + 1, Wo = (W + 2 * pad - kw) / stride + 1;
@@ -803,6 +825,10 @@ extern "C" int qb_conv_dgrad(const uint16_t* a0, const uint16_t* a1, const uint1
                     if ((ph + pad - r) % stride == 0 && (pw + pad - s) % stride == 0) ++cnt;
             if (cnt == 0) any_empty = true;
         }
+    if (accumulate && (any_empty || stride != 1 || a1)) {
+        qb_set_error("qb_conv_dgrad_acc: needs unit stride and a single-plane gradient");
+        return QB_ERR_UNSUPPORTED;
+    }
     if (any_empty) QB_CUDA(cudaMemsetAsync(dx, 0, (size_t)B * H * W * Cin * 4, st));
     for (int ph = 0; ph < stride && ph < H; ++ph) {
         for (int pw = 0; pw < stride && pw < W; ++pw) {
@@ -833,6 +859,7 @@ extern "C" int qb_conv_dgrad(const uint16_t* a0, const uint16_t* a1, const uint1
                 const size_t fsmem = dgrad_flat_geom(fg, (int)B, (int)Hc, (int)Wc, (int)Cin, (int)Cout, BK, BN, g.dh, g.dw, g.wtap, g.ntaps,
                                                      (BN == 128 && sbs128) ? 128 : 256);
                 if (fsmem) {
+                    fg.accumulate = accumulate;
                     CUtensorMap fa, fo;
                     const uint64_t adims[4] = {(uint64_t)Cout, (uint64_t)Wo, (uint64_t)Ho, (uint64_t)B};
                     const uint64_t astr[3] = {(uint64_t)Cout * 2, (uint64_t)Wo * Cout * 2, (uint64_t)Ho * Wo * Cout * 2};
@@ -855,6 +882,10 @@ extern "C" int qb_conv_dgrad(const uint16_t* a0, const uint16_t* a1, const uint1
                     if (rc) return rc;
                     continue;
                 }
+            }
+            if (accumulate) {
+                qb_set_error("qb_conv_dgrad_acc: geometry not taken by the flat-strip kernel");
+                return QB_ERR_UNSUPPORTED;
             }
             g.B = (int)B; g.Hc = (int)Hc; g.Wc = (int)Wc; g.Cn = (int)Cin; g.Ck = (int)Cout;
             g.BK = BK;
@@ -1310,7 +1341,10 @@ static int wgrad_geom2(WgradGeom& g, int64_t B, int64_t Ho, int64_t Wo, int64_t 
     g.J = (g.mtiles + g.mgroups - 1) / g.mgroups;
     // pixel tile: P = TW*TH*TN pixels, P % 16 == 0, P <= pmax, covering the (Wo, Ho, B) grid with the least padding
     const int64_t b_bytes_per_px = (int64_t)g_planes * g.BN * 2;
-    const int pmax = b_bytes_per_px * 128 * 2 + 3 * 128 * 256 <= 200 * 1024 ? 128 : 64;
+    static const int pmax_env = getenv("QB_WGRAD_PMAX") ? atoi(getenv("QB_WGRAD_PMAX")) : 0;     // experiment: 64 / 96 / 128
+    // 128 pixels per K block whenever two gradient stages and two x stages of that size fit: twice the MMAs per barrier round
+    // trip of the issuing thread (measured 7 % on the wgrad total against 64-pixel blocks, profiles/bwd_sweep_r02n_pmax128.txt)
+    const int pmax = pmax_env >= 16 ? pmax_env : (b_bytes_per_px * 128 * 2 + 2 * 128 * 256 <= 218 * 1024 ? 128 : 64);
     double best = -1.0;
     for (int tw = 1; tw <= 128 && tw <= Wo + 7; ++tw) {
         if (tw > Wo && tw != ((Wo + 7) / 8) * 8) continue;

@@ -50,11 +50,11 @@ def _relu(q, inplace=True):
     return nn.ReLU(inplace=inplace)
 
 
-def _bn_relu(bn, relu, x, res=None):
+def _bn_relu(bn, relu, x, res=None, skip=None):
     """``relu(bn(x))`` / ``y = bn(x); y += res; relu(y)`` (models/resnet_quantized.py:47-75, 100-112); one fused pass when the
     modules are this package's (RangeBN.forward_relu), the plain composition for any other module namespace (the oracle)."""
     if hasattr(bn, "forward_relu"):
-        return bn.forward_relu(x, relu, res)
+        return bn.forward_relu(x, relu, res, skip) if skip is not None else bn.forward_relu(x, relu, res)
     y = bn(x)
     if res is None:
         return relu(y)
@@ -84,9 +84,13 @@ class BasicBlock(nn.Module):
         self._last_bn = "bn2"
 
     def forward(self, x):
+        # identity skip on the native modules: conv1's input-gradient kernel accumulates into the skip gradient (no autograd add)
+        skip = {} if (self.downsample is None and hasattr(self.bn2, "forward_relu")) else None
+        if skip is not None:
+            self.conv1._skip_holder = skip
         y = _bn_relu(self.bn1, self.relu, self.conv1(x))
         res = (lambda: x) if self.downsample is None else (lambda: self.downsample(x))
-        return _bn_relu(self.bn2, self.relu, self.conv2(y), res)   # native: normalise + add + ReLU + next layer's statistics
+        return _bn_relu(self.bn2, self.relu, self.conv2(y), res, skip)   # native: normalise + add + ReLU + next layer's statistics
 
 
 class Bottleneck(nn.Module):
@@ -105,10 +109,13 @@ class Bottleneck(nn.Module):
         self._last_bn = "bn3"
 
     def forward(self, x):
+        skip = {} if (self.downsample is None and hasattr(self.bn3, "forward_relu")) else None
+        if skip is not None:
+            self.conv1._skip_holder = skip
         y = _bn_relu(self.bn1, self.relu, self.conv1(x))
         y = _bn_relu(self.bn2, self.relu, self.conv2(y))
         res = (lambda: x) if self.downsample is None else (lambda: self.downsample(x))
-        return _bn_relu(self.bn3, self.relu, self.conv3(y), res)
+        return _bn_relu(self.bn3, self.relu, self.conv3(y), res, skip)
 
 
 class QResNet(nn.Module):

@@ -716,6 +716,14 @@ class _QTensorCoreFn(Function):
         ctx.bits_grad, ctx.grad_mode, ctx.has_bias = mod.num_bits_grad, mod._grad_mode(), qbias is not None
         ctx.grad_quantizer = getattr(mod, "_grad_quantizer", None)
         ctx.stem = ctx.native = None
+        # residual block: the skip gradient of this layer's input is handed over by the fused RangeBN+add+ReLU node of the
+        # block (RangeBN.forward_relu(skip=...)) and the input-gradient kernel accumulates into it
+        holder, ctx.skip = getattr(mod, "_skip_holder", None), None
+        if holder is not None:
+            mod._skip_holder = None
+            if native_bwd and conv and ctx.needs_input_grad[0] and _pair(mod.stride) == (1, 1):
+                ctx.skip = holder
+                holder["armed"] = True
         if need_bwd and stem_bwd:
             ctx.stem = (bits_a, mod.out_channels, kh, kw, _pair(mod.stride)[0], _pair(mod.padding)[0])
             ctx.save_for_backward(codes, rng)
@@ -798,8 +806,10 @@ def _native_backward(ctx, g):
     if need_x:
         a0v = a0 if conv else a0.view(a0.shape[0], a0.shape[1], 1, 1)
         a1v = a1 if (a1 is None or conv) else a1.view(a1.shape[0], a1.shape[1], 1, 1)
+        skip = getattr(ctx, "skip", None)
+        acc = skip.pop("g", None) if skip is not None else None
         dx = _abi.conv_dgrad(a0v, a1v, wt, shape4, n_out + pad, kh, kw, stride, padding, scale_range=scale_range,
-                             scale_bits=bits if scale_range is not None else 8)
+                             scale_bits=bits if scale_range is not None else 8, accumulate_into=acc)
         if not conv:
             dx = dx.permute(0, 2, 3, 1).reshape(x_shape)
     if need_b and not need_w:             # frozen weight, trainable bias: a plain column sum
@@ -995,6 +1005,9 @@ class _ApplyReLUFn(Function):
         else:
             dg, rng = _abi.relu_bwd_minmax_bits(g, saved)
             _stash_grad_range(dg, rng)
+        skip = ctx.d.get("skip")
+        if skip is not None:                                # the block's first convolution adds its dX into this tensor
+            skip["g"] = dg
         return dg, (dg if ctx.needs_input_grad[1] else None), None
 
 
@@ -1043,7 +1056,7 @@ class RangeBN(nn.Module):
             out = out.squeeze(-1).squeeze(-1)
         return out
 
-    def forward_relu(self, x, relu, residual=None):
+    def forward_relu(self, x, relu, residual=None, skip=None):
         """``relu(self(x))`` - or, with ``residual``, ``out = self(x); out += residual; relu(out)``, the tail of a residual
         block (models/resnet_quantized.py:62-68, 105-112) - with the normalisation, the add, the clamp and the statistics of
         the next QuantMeasure in ONE pass over the uint8 codes (qb_rangebn_apply_relu_measure): the normalised tensor is
@@ -1070,6 +1083,12 @@ class RangeBN(nn.Module):
         res = residual() if callable(residual) else residual
         if res is not None:
             res = res.contiguous(memory_format=torch.channels_last)
+            # ``skip``: the holder the block handed to its FIRST convolution, whose input IS this residual; if that layer
+            # armed it, the skip gradient does not travel through autograd (no separate accumulation pass): the masked
+            # gradient is left in the holder and the convolution's input-gradient kernel accumulates into it
+            if skip is not None and skip.get("armed") and res.requires_grad:
+                d["skip"] = skip
+                res = res.detach()
         out = _ApplyReLUFn.apply(h, res, d)
         stats, glue._last["stats"] = glue._last["stats"], None
         if stats is not None:

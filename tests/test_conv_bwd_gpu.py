@@ -78,6 +78,17 @@ def test_conv_dgrad(lib, case):
     dx2 = lib.conv_dgrad(hi, lo, wt, (B, Cin, H, W), Cout, k, k, stride, pad)
     ref2 = torch.nn.grad.conv2d_input((B, Cin, H, W), w.double(), gf.double(), stride, pad)
     assert rel(dx2, ref2) < 3e-5, rel(dx2, ref2)
+    # accumulating form (the skip gradient of a residual block is already in the output): bit-identical to dx + skip, whether
+    # the reduce-add kernel takes the geometry or the wrapper falls back to a separate add
+    skip = torch.randn(B, Cin, H, W, generator=gen).to(DEV).contiguous(memory_format=torch.channels_last)
+    want = dx + skip
+    lib.profile_begin()
+    got = lib.conv_dgrad(ad, None, wt, (B, Cin, H, W), Cout, k, k, stride, pad, scale_mul=0.5, accumulate_into=skip)
+    names = [r[0] for r in lib.profile_end()]
+    assert got.data_ptr() == skip.data_ptr()
+    assert torch.equal(got, want), rel(got, want.cpu())
+    if case in ((4, 64, 56, 56, 64, 3, 1, 1), (4, 128, 28, 28, 128, 3, 1, 1), (7, 512, 7, 7, 512, 3, 1, 1)):   # ResNet-18 identity blocks
+        assert names == ["qb_conv_dgrad_acc"], names
 
 
 @pytest.mark.parametrize("case", CASES)
