@@ -416,10 +416,11 @@ int qb_conv_dgrad(const uint16_t* a0, const uint16_t* a1, const uint16_t* wt, fl
                   float scale_mul, void* stream);
 /* qb_conv_dgrad that ACCUMULATES: dx += dX.  dx already holds the other gradient that reaches the layer's input - the skip
  * connection of a residual block (`out += residual`, models/resnet_quantized.py:62-68) - so autograd's separate accumulation
- * pass (12 B/elem) becomes TMA reduce-add stores.  Unit stride, one gradient plane (integer codes), geometries the flat-strip
- * kernel takes; otherwise QB_ERR_UNSUPPORTED and dx is left untouched. */
+ * pass (12 B/elem) becomes TMA reduce-add stores.  One gradient plane (integer codes); every pixel parity class of the stride
+ * must be reached by the filter and taken by the flat-strip kernel (checked first); otherwise QB_ERR_UNSUPPORTED and dx is left
+ * untouched.  With a downsample branch (models/resnet_quantized.py:58-60) dx holds that branch's input gradient. */
 int qb_conv_dgrad_acc(const uint16_t* a0, const uint16_t* wt, float* dx, int64_t B, int64_t H, int64_t W, int64_t Cin, int64_t Cout,
-                      int kh, int kw, int pad, const float* scale_range, int scale_bits, float scale_mul, void* stream);
+                      int kh, int kw, int stride, int pad, const float* scale_range, int scale_bits, float scale_mul, void* stream);
 /* Weight gradient of the FIRST layer (3 input channels; 7x7/stride 2/pad 3 or 3x3/stride 2/pad 1, even W) on the qb_conv_wgrad
  * kernel: the uint8 input codes [B,H,W,3] are expanded to zero-padded 4-channel bf16 and read through an OVERLAPPING tensor
  * map as a virtual operand whose "channels" are a filter row's window (conv_bwd.cu).  g_hi / g_lo: bf16 planes of the output

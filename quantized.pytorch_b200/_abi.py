@@ -101,7 +101,7 @@ PROTOTYPES = {
     "qb_debug_umma_rate": (_i32, [_p, _i32, _i32, _i32, _i32, _p]),
     "qb_wt_pack": (_i32, [_p, _p, _i64, _i64, _i32, _p]),
     "qb_conv_dgrad": (_i32, [_p, _p, _p, _p, _i64, _i64, _i64, _i64, _i64, _i32, _i32, _i32, _i32, _p, _i32, _flt, _p]),
-    "qb_conv_dgrad_acc": (_i32, [_p, _p, _p, _i64, _i64, _i64, _i64, _i64, _i32, _i32, _i32, _p, _i32, _flt, _p]),
+    "qb_conv_dgrad_acc": (_i32, [_p, _p, _p, _i64, _i64, _i64, _i64, _i64, _i32, _i32, _i32, _i32, _p, _i32, _flt, _p]),
     "qb_conv_wgrad_ws_bytes": (_sz, [_i64, _i64, _i64, _i64, _i64, _i32, _i32, _i32, _i32]),
     "qb_conv_wgrad": (_i32, [_p, _p, _p, _p, _p, _p, _i64, _i64, _i64, _i64, _i64, _i32, _i32, _i32, _i32, _p, _i32, _p, _sz, _p]),
     "qb_conv_i8_fwd": (_i32, [_p, _p, _p, _i64, _i64, _i64, _i64, _i64, _i32, _i32, _i32, _i32, _p, _i32, _p, _p, _i32,
@@ -710,13 +710,14 @@ def conv_dgrad(a0, a1, wt, x_shape, Cout, kh, kw, stride, pad, scale_range=None,
     B, Cin, H, W = x_shape
     if accumulate_into is not None:
         acc = accumulate_into
-        ok = (a1 is None and stride == 1 and acc.dtype == torch.float32 and tuple(acc.shape) == (B, Cin, H, W) and is_nhwc(acc)
+        ok = (a1 is None and acc.dtype == torch.float32 and tuple(acc.shape) == (B, Cin, H, W) and is_nhwc(acc)
               and acc.data_ptr() % 16 == 0)
         if ok:
-            _next_ops = 2 * B * H * W * Cout * kh * kw * Cin
+            _next_ops = 2 * a0.numel() * kh * kw * Cin
+            _NLAUNCH["qb_conv_dgrad_acc"] = stride * stride
             try:
                 _run("qb_conv_dgrad_acc", 2 * a0.numel() + 4 * Cout * Cin * kh * kw + 8 * acc.numel(), _ptr(a0), _ptr(wt), _ptr(acc), B, H,
-                     W, Cin, Cout, kh, kw, pad, _ptr(scale_range), int(scale_bits), float(scale_mul), _stream())
+                     W, Cin, Cout, kh, kw, stride, pad, _ptr(scale_range), int(scale_bits), float(scale_mul), _stream())
                 return acc
             except QB200Error:
                 _next_ops = 0

@@ -776,12 +776,13 @@ extern "C" int qb_conv_dgrad(const uint16_t* a0, const uint16_t* a1, const uint1
 
 /* As qb_conv_dgrad, but dx += result: dx already holds the OTHER gradient that reaches the layer's input - the skip connection
  * of a residual block (models/resnet_quantized.py:62-68: `out += residual`; autograd's separate accumulation pass of 12 B/elem
- * disappears into TMA reduce-add stores).  Unit stride, single-plane (code) gradients, geometries the flat-strip kernel takes;
- * anything else returns QB_ERR_UNSUPPORTED with dx untouched. */
+ * disappears into TMA reduce-add stores).  Single-plane (code) gradients, every pixel parity class of the stride reached by the
+ * filter and taken by the flat-strip kernel (checked before anything is added); anything else returns QB_ERR_UNSUPPORTED with dx
+ * untouched. */
 extern "C" int qb_conv_dgrad_acc(const uint16_t* a0, const uint16_t* wt, float* dx, int64_t B, int64_t H, int64_t W, int64_t Cin,
-                                 int64_t Cout, int kh, int kw, int pad, const float* scale_range, int scale_bits, float scale_mul,
-                                 void* stream) {
-    return conv_dgrad_impl(a0, nullptr, wt, dx, B, H, W, Cin, Cout, kh, kw, 1, pad, scale_range, scale_bits, scale_mul, 1, stream);
+                                 int64_t Cout, int kh, int kw, int stride, int pad, const float* scale_range, int scale_bits,
+                                 float scale_mul, void* stream) {
+    return conv_dgrad_impl(a0, nullptr, wt, dx, B, H, W, Cin, Cout, kh, kw, stride, pad, scale_range, scale_bits, scale_mul, 1, stream);
 }
 
 static int conv_dgrad_impl(const uint16_t* a0, const uint16_t* a1, const uint16_t* wt, float* dx, int64_t B, int64_t H, int64_t W,
@@ -825,11 +826,14 @@ static int conv_dgrad_impl(const uint16_t* a0, const uint16_t* a1, const uint16_
                     if ((ph + pad - r) % stride == 0 && (pw + pad - s) % stride == 0) ++cnt;
             if (cnt == 0) any_empty = true;
         }
-    if (accumulate && (any_empty || stride != 1 || a1)) {
-        qb_set_error("qb_conv_dgrad_acc: needs unit stride and a single-plane gradient");
+    if (accumulate && (any_empty || a1)) {
+        qb_set_error("qb_conv_dgrad_acc: needs a single-plane gradient and a filter that reaches every pixel parity");
         return QB_ERR_UNSUPPORTED;
     }
     if (any_empty) QB_CUDA(cudaMemsetAsync(dx, 0, (size_t)B * H * W * Cin * 4, st));
+    // accumulate: a dry pass first - every parity class must be taken by the flat-strip kernel BEFORE anything is added to dx
+    for (int pass = accumulate ? 0 : 1; pass < 2; ++pass) {
+    const bool dry = pass == 0;
     for (int ph = 0; ph < stride && ph < H; ++ph) {
         for (int pw = 0; pw < stride && pw < W; ++pw) {
             DgradGeom g;
@@ -858,6 +862,7 @@ static int conv_dgrad_impl(const uint16_t* a0, const uint16_t* a1, const uint16_
                 static const bool sbs128 = getenv("QB_DGRAD_SBS128") && getenv("QB_DGRAD_SBS128")[0] == '1';
                 const size_t fsmem = dgrad_flat_geom(fg, (int)B, (int)Hc, (int)Wc, (int)Cin, (int)Cout, BK, BN, g.dh, g.dw, g.wtap, g.ntaps,
                                                      (BN == 128 && sbs128) ? 128 : 256);
+                if (fsmem && dry) continue;
                 if (fsmem) {
                     fg.accumulate = accumulate;
                     CUtensorMap fa, fo;
@@ -927,6 +932,7 @@ static int conv_dgrad_impl(const uint16_t* a0, const uint16_t* a1, const uint16_
             if (rc) return rc;
         }
     }
+    }   // pass
     return QB_OK;
 }
 

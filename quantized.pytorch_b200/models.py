@@ -65,6 +65,20 @@ def _bn_relu(bn, relu, x, res=None, skip=None):
     return relu(y)
 
 
+def _arm_skip(block, last_bn):
+    """-> the holder to pass to the block's final fused RangeBN (identity skip), or None."""
+    if not hasattr(last_bn, "forward_relu"):
+        return None
+    holder = {}
+    block.conv1._skip_holder = holder
+    if block.downsample is None:
+        return holder
+    ds0 = block.downsample[0] if isinstance(block.downsample, nn.Sequential) and len(block.downsample) else None
+    if ds0 is not None and hasattr(ds0, "quantize_input"):
+        ds0._skip_out_holder = holder
+    return None
+
+
 class _Identity(nn.Module):
     def forward(self, x):
         return x
@@ -84,10 +98,9 @@ class BasicBlock(nn.Module):
         self._last_bn = "bn2"
 
     def forward(self, x):
-        # identity skip on the native modules: conv1's input-gradient kernel accumulates into the skip gradient (no autograd add)
-        skip = {} if (self.downsample is None and hasattr(self.bn2, "forward_relu")) else None
-        if skip is not None:
-            self.conv1._skip_holder = skip
+        # native modules: conv1's input-gradient kernel accumulates into the other gradient of x - the skip gradient of an
+        # identity block, or the downsample convolution's input gradient - instead of autograd adding the two tensors
+        skip = _arm_skip(self, self.bn2)
         y = _bn_relu(self.bn1, self.relu, self.conv1(x))
         res = (lambda: x) if self.downsample is None else (lambda: self.downsample(x))
         return _bn_relu(self.bn2, self.relu, self.conv2(y), res, skip)   # native: normalise + add + ReLU + next layer's statistics
@@ -109,9 +122,7 @@ class Bottleneck(nn.Module):
         self._last_bn = "bn3"
 
     def forward(self, x):
-        skip = {} if (self.downsample is None and hasattr(self.bn3, "forward_relu")) else None
-        if skip is not None:
-            self.conv1._skip_holder = skip
+        skip = _arm_skip(self, self.bn3)
         y = _bn_relu(self.bn1, self.relu, self.conv1(x))
         y = _bn_relu(self.bn2, self.relu, self.conv2(y))
         res = (lambda: x) if self.downsample is None else (lambda: self.downsample(x))

@@ -721,9 +721,16 @@ class _QTensorCoreFn(Function):
         holder, ctx.skip = getattr(mod, "_skip_holder", None), None
         if holder is not None:
             mod._skip_holder = None
-            if native_bwd and conv and ctx.needs_input_grad[0] and _pair(mod.stride) == (1, 1):
+            if native_bwd and conv and ctx.needs_input_grad[0]:
                 ctx.skip = holder
                 holder["armed"] = True
+        # ... and the downsample convolution of a block (same input) leaves ITS input gradient in the holder instead of returning
+        # it to autograd, so that the first convolution accumulates into it
+        holder, ctx.skip_out = getattr(mod, "_skip_out_holder", None), None
+        if holder is not None:
+            mod._skip_out_holder = None
+            if holder.get("armed") and native_bwd and conv and ctx.needs_input_grad[0]:
+                ctx.skip_out = holder
         if need_bwd and stem_bwd:
             ctx.stem = (bits_a, mod.out_channels, kh, kw, _pair(mod.stride)[0], _pair(mod.padding)[0])
             ctx.save_for_backward(codes, rng)
@@ -812,6 +819,9 @@ def _native_backward(ctx, g):
                              scale_bits=bits if scale_range is not None else 8, accumulate_into=acc)
         if not conv:
             dx = dx.permute(0, 2, 3, 1).reshape(x_shape)
+        if getattr(ctx, "skip_out", None) is not None:       # handed to the block's first convolution (runs later in backward)
+            ctx.skip_out["g"] = dx
+            dx = None
     if need_b and not need_w:             # frozen weight, trainable bias: a plain column sum
         db = g_param.sum((0, 2, 3) if conv else 0)[:n_out]
     elif need_w:

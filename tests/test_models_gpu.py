@@ -123,7 +123,7 @@ def test_benchmarked_model_train_step_vs_oracle(name):
     # (identity residual blocks: the first convolution's input gradient accumulates into the skip gradient, qb_conv_dgrad_acc)
     assert calls.count("qb_conv_dgrad") + calls.count("qb_conv_dgrad_acc") == len(dense) + n_lin
     if name == "resnet18":
-        assert calls.count("qb_conv_dgrad_acc") == 5, calls.count("qb_conv_dgrad_acc")
+        assert calls.count("qb_conv_dgrad_acc") == 8, calls.count("qb_conv_dgrad_acc")      # every block's first convolution
     assert calls.count("qb_conv_stem_fwd") == 1 and calls.count("qb_gemm_i8") == n_lin
     if name == "mobilenet":
         n_dw = sum(m.groups > 1 for m in convs)
