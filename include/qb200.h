@@ -75,6 +75,11 @@ int qb_fakequant_affine(const float* x, float* y, uint8_t* codes, int64_t n, int
 /* Same, plus codes16 (optional): the integer codes as bf16 (exact for bits <= 8), the x operand of qb_conv_wgrad. */
 int qb_fakequant_affine16(const float* x, float* y, uint8_t* codes, uint16_t* codes16, int64_t n, int bits,
                           const float* range_dev, double lo, double hi, int scale_mode, void* stream);
+/* The activation quantizer of a network's FIRST QConv2d (quantize.py:339-343 on models/resnet_quantized.py:147,
+ * models/mobilenet_quantized.py:66) fused with the layout change: x is the fp32 image batch as torch delivers it, NCHW
+ * [B, 3, H*W]; codes are uint8 [B, H*W, 3] (channels-last) for qb_conv_stem_fwd.  Same codes as qb_fakequant_affine with a
+ * device range on the channels-last copy; saves that copy (8 B/elem of the batch).  H*W % 4 == 0, bits <= 8. */
+int qb_fakequant_affine_nchw3(const float* x, uint8_t* codes, int64_t B, int64_t HW, int bits, const float* range_dev, void* stream);
 
 /* The min-anchored branch with stochastic rounding (quantize.py:90-100, enforce_true_zero=False, stochastic=True; reached
  * through quantize(x, num_chunks=<truthy>), :159-160): y = rne(clamp((x - min)/s + u, 0, 2^bits-1)) * s + min, u = noise

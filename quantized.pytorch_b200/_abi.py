@@ -101,6 +101,7 @@ PROTOTYPES = {
     "qb_debug_umma_rate": (_i32, [_p, _i32, _i32, _i32, _i32, _p]),
     "qb_wt_pack": (_i32, [_p, _p, _i64, _i64, _i32, _p]),
     "qb_conv_dgrad": (_i32, [_p, _p, _p, _p, _i64, _i64, _i64, _i64, _i64, _i32, _i32, _i32, _i32, _p, _i32, _flt, _p]),
+    "qb_fakequant_affine_nchw3": (_i32, [_p, _p, _i64, _i64, _i32, _p, _p]),
     "qb_conv_dgrad_acc": (_i32, [_p, _p, _p, _i64, _i64, _i64, _i64, _i64, _i32, _i32, _i32, _i32, _p, _i32, _flt, _p]),
     "qb_conv_wgrad_ws_bytes": (_sz, [_i64, _i64, _i64, _i64, _i64, _i32, _i32, _i32, _i32]),
     "qb_conv_wgrad": (_i32, [_p, _p, _p, _p, _p, _p, _i64, _i64, _i64, _i64, _i64, _i32, _i32, _i32, _i32, _p, _i32, _p, _sz, _p]),
@@ -357,6 +358,14 @@ def fakequant_affine(x, bits, range_dev=None, lo=0.0, hi=0.0, scale_mode=QB_SCAL
     _run("qb_fakequant_affine", (4 + (4 if want_y else 0) + (1 if codes is not None else 0)) * x.numel(), _ptr(x), _ptr(out) if want_y else None, _ptr(codes), x.numel(), int(bits),
                                    _ptr(range_dev), float(lo), float(hi), int(scale_mode), _stream())
     return out
+
+
+def fakequant_affine_nchw3(x, bits, range_dev):
+    """x fp32 [B, 3, H, W] NCHW-contiguous -> uint8 codes, logical [B, 3, H, W] stored channels-last (qb_fakequant_affine_nchw3)."""
+    B, Cn, H, W = x.shape
+    codes = torch.empty((B, Cn, H, W), dtype=torch.uint8, device=x.device, memory_format=torch.channels_last)
+    _run("qb_fakequant_affine_nchw3", 5 * x.numel(), _ptr(x), _ptr(codes), B, H * W, int(bits), _ptr(range_dev), _stream())
+    return codes
 
 
 def fakequant_affine_stochastic(x, bits, range_dev=None, lo=0.0, hi=0.0, scale_mode=QB_SCALE_DOUBLE, noise=None, seed=0,

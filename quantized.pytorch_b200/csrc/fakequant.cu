@@ -171,6 +171,49 @@ extern "C" int qb_fakequant_affine(const float* x, float* y, uint8_t* codes, int
     return QB_OK;
 }
 
+// ------------------------------------------------------------------------------------------------
+// First layer of a network: the image batch arrives NCHW (torch's default), the convolution kernels read NHWC codes.  The
+// quantizer itself does the transposition - 3 coalesced plane reads, one packed 12-byte write per 4 pixels - instead of a
+// separate NCHW -> NHWC copy of the fp32 batch (154 MB read + written per ResNet-18 step).  Same arithmetic as
+// k_fq_affine_v8 (device range, QB_SCALE_DOUBLE); codes only.
+// ------------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(FQ_THREADS)
+k_fq_affine_nchw3(const float* __restrict__ x, uint8_t* __restrict__ codes, int64_t B, int64_t HW, int bits, const float* range_dev) {
+    const AffineQ aq = load_affineq(range_dev, bits);
+    const int64_t quads = HW >> 2, total = B * quads;
+    for (int64_t i = (int64_t)blockIdx.x * FQ_THREADS + threadIdx.x; i < total; i += (int64_t)gridDim.x * FQ_THREADS) {
+        const int64_t b = i / quads, q = i - b * quads;
+        const float* src = x + b * 3 * HW + 4 * q;
+        float v[12];
+#pragma unroll
+        for (int c = 0; c < 3; ++c) {
+            const float4 f = __ldcs(reinterpret_cast<const float4*>(src + c * HW));
+            v[c] = f.x; v[3 + c] = f.y; v[6 + c] = f.z; v[9 + c] = f.w;          // pixel-major: v[3*pixel + channel]
+        }
+        uint32_t cd[12];
+        affine_fq_vec<12>(v, aq, cd);
+        uint32_t* dst = reinterpret_cast<uint32_t*>(codes + (b * HW + 4 * q) * 3);
+        dst[0] = cd[0] | (cd[1] << 8) | (cd[2] << 16) | (cd[3] << 24);
+        dst[1] = cd[4] | (cd[5] << 8) | (cd[6] << 16) | (cd[7] << 24);
+        dst[2] = cd[8] | (cd[9] << 8) | (cd[10] << 16) | (cd[11] << 24);
+    }
+}
+
+/* uint8 codes [B, H*W, 3] (channels-last) of the min-anchored quantizer applied to an fp32 NCHW batch [B, 3, H*W]: the
+ * activation quantizer of a network's first QConv2d (quantize.py:339-343 on models/resnet_quantized.py:147 /
+ * mobilenet_quantized.py:66) fused with the layout change the NHWC kernels need.  H*W % 4 == 0, 16-byte aligned x, bits <= 8. */
+extern "C" int qb_fakequant_affine_nchw3(const float* x, uint8_t* codes, int64_t B, int64_t HW, int bits, const float* range_dev,
+                                         void* stream) {
+    QB_CHECK_ARG(x && codes && range_dev, "qb_fakequant_affine_nchw3: null pointer");
+    QB_CHECK_ARG(B > 0 && HW > 0 && HW % 4 == 0, "qb_fakequant_affine_nchw3: B=%lld H*W=%lld (H*W %% 4 == 0 required)", (long long)B,
+                 (long long)HW);
+    QB_CHECK_ARG(bits >= 1 && bits <= 8, "qb_fakequant_affine_nchw3: bits=%d", bits);
+    QB_CHECK_ARG(aligned(x, 16) && aligned(codes, 4), "qb_fakequant_affine_nchw3: misaligned tensor");
+    k_fq_affine_nchw3<<<fq_grid(B * (HW >> 2), 8), FQ_THREADS, 0, qb_stream(stream)>>>(x, codes, B, HW, bits, range_dev);
+    QB_LAUNCH_CHECK();
+    return QB_OK;
+}
+
 /* As qb_fakequant_affine, plus codes16: the integer codes as bf16 (bits <= 8; exact) - the x operand of qb_conv_wgrad. */
 extern "C" int qb_fakequant_affine16(const float* x, float* y, uint8_t* codes, uint16_t* codes16, int64_t n, int bits,
                                      const float* range_dev, double lo, double hi, int scale_mode, void* stream) {

@@ -596,6 +596,7 @@ USE_NATIVE_BACKWARD = True    # dX / dW / db of the dense contractions on conv_b
 # the library.
 ALLOW_LIBRARY_FALLBACK = False
 USE_STEM_KERNEL = True
+STEM_NCHW_DIRECT = True       # first layer: quantize the NCHW image batch straight into channels-last codes (no fp32 layout copy)
 USE_DW_KERNEL = True       # depthwise 3x3 convs on the codes (conv_dw.cu); False: F.conv2d on the fake-quantized tensors
 
 
@@ -634,6 +635,17 @@ def _conv_stem_supported(mod, x):
                                          _pair(mod.stride)[0], _pair(mod.padding)[0]))
 
 
+def _stem_takes_nchw(mod, x):
+    """The image batch of the first layer stays NCHW: its quantizer writes the channels-last codes itself
+    (qb_fakequant_affine_nchw3), so the fp32 batch is read once by the statistics pass and once by the quantizer and never
+    copied.  Only where nothing downstream wants the fp32 x_hat (no input gradient; weight gradient from the codes)."""
+    return (STEM_NCHW_DIRECT and mod.enable_quant and x.is_cuda and x.dtype == torch.float32 and x.is_contiguous()
+            and mod.in_channels == 3 and mod.groups == 1 and (x.shape[2] * x.shape[3]) % 4 == 0 and x.data_ptr() % 16 == 0
+            and not (x.requires_grad and torch.is_grad_enabled()) and getattr(mod, "_q2_params", None) is None
+            and mod.out_channels in (32, 64) and mod.kernel_size[0] in (3, 7) and mod.kernel_size[0] == mod.kernel_size[1]
+            and _conv_i8_supported(mod, x))
+
+
 def _linear_i8_supported(mod, x):
     return (USE_INT8_TENSOR_CORES and x.dim() == 2 and mod.in_features % 16 == 0 and mod.num_bits <= 8
             and mod.num_bits_weight <= 8)
@@ -664,7 +676,8 @@ class _QTensorCoreFn(Function):
         x = _abi._f32c(input, "input")
         bits_a, bits_w = mod.num_bits, mod.num_bits_weight
         update = not getattr(mod, "freeze_param_dyn_range", False)
-        codes = torch.empty_like(x, dtype=torch.uint8)                      # same memory format as x
+        nchw_stem = conv and not ctx.needs_input_grad[0] and _stem_takes_nchw(mod, x)    # left NCHW by QConv2d.forward
+        codes = None if nchw_stem else torch.empty_like(x, dtype=torch.uint8)           # same memory format as x
         # first layer whose input needs no gradient: the weight gradient is taken from the codes (conv_stem.cu)
         stem_bwd = (conv and USE_STEM_KERNEL and x.shape[1] % 32 != 0 and not ctx.needs_input_grad[0]
                     and mod.out_channels in (32, 64) and mod.kernel_size[0] in (3, 7)
@@ -674,7 +687,11 @@ class _QTensorCoreFn(Function):
         want_x16 = native_bwd and ctx.needs_input_grad[1]
         x16 = torch.empty_like(x, dtype=torch.bfloat16) if want_x16 else None
         q2 = getattr(mod, "_q2_params", None)        # quantize2 flavour: (zero_point, range) device tensors of its quantizer
-        if q2 is not None:
+        if nchw_stem:
+            if q2 is not None or (need_bwd and not stem_bwd):
+                raise _abi.QB200Error("first-layer NCHW path entered with a backward that needs x_hat")
+            xq, codes = None, _abi.fakequant_affine_nchw3(x, bits_a, rng)
+        elif q2 is not None:
             xq = _abi.fakequant2_codes(x, q2[0], q2[1], bits_a, codes=codes, codes16=x16,
                                        want_y=need_bwd and not stem_bwd and not native_bwd)
         else:
@@ -847,7 +864,8 @@ class QConv2d(nn.Conv2d, _QBase):
         self._init_quant(num_bits, num_bits_weight, num_bits_grad, biprecision, bias_quant, per_channel, bias)
 
     def forward(self, input):
-        if CHANNELS_LAST and input.dim() == 4 and not input.is_contiguous(memory_format=torch.channels_last):
+        if (CHANNELS_LAST and input.dim() == 4 and not input.is_contiguous(memory_format=torch.channels_last)
+                and not _stem_takes_nchw(self, input)):
             input = input.contiguous(memory_format=torch.channels_last)      # library-native activation layout
         if self.enable_quant and _conv_i8_supported(self, input):
             rng = self.quantize_input.measure(input)

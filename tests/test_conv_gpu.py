@@ -162,6 +162,51 @@ def test_qconv2d_first_layer_uses_stem_kernel(lib):
     assert float((g1 - m2.weight.grad).norm() / m2.weight.grad.norm()) < 1e-3
 
 
+@pytest.mark.parametrize("shape", [(4, 3, 64, 64), (3, 3, 30, 34), (2, 3, 224, 224)])
+def test_first_layer_quantizer_reads_nchw(lib, shape):
+    """qb_fakequant_affine_nchw3: the codes of the NCHW image batch, written channels-last, are the codes qb_fakequant_affine
+    gives on the channels-last copy (bit-exact), and QConv2d's first-layer route through it (no layout copy of the batch) gives
+    the same output, weight gradient and running range as the route through the copy."""
+    import qtorch_b200  # noqa: F401
+    from qtorch_b200 import quantize as Q
+    torch.manual_seed(11)
+    x = torch.randn(shape, device=DEV) * 1.7 + 0.3
+    rng = torch.tensor([float(x.min()) * 0.9, float(x.max()) * 0.8], device=DEV)     # clamps on both sides
+    for bits in (8, 5):
+        xl = x.contiguous(memory_format=torch.channels_last)
+        want = torch.empty_like(xl, dtype=torch.uint8)
+        lib.fakequant_affine(xl, bits, range_dev=rng, codes=want, want_y=False)
+        got = lib.fakequant_affine_nchw3(x, bits, rng)
+        assert got.is_contiguous(memory_format=torch.channels_last) and got.shape == x.shape
+        assert torch.equal(got, want)
+    outs = []
+    for direct in (True, False):
+        torch.manual_seed(5)
+        m = Q.QConv2d(3, 64, 7, 2, 3, bias=False, num_bits=8, num_bits_weight=8, num_bits_grad=None).to(DEV)
+        Q.STEM_NCHW_DIRECT = direct
+        try:
+            lib.profile_begin()
+            y = m(x)
+            names = [r[0] for r in lib.profile_end()]
+            y.square().mean().backward()
+        finally:
+            Q.STEM_NCHW_DIRECT = True
+        assert ("qb_fakequant_affine_nchw3" in names) == direct, names
+        outs.append((y.detach(), m.weight.grad.clone(), m.quantize_input.running_min.clone(), m.quantize_input.running_max.clone()))
+    for i, (a, b) in enumerate(zip(*outs)):
+        if i == 1:                                      # weight gradient: same codes in, fp32 partial sums combined atomically
+            assert float((a - b).norm() / b.norm()) < 1e-5
+        else:
+            assert torch.equal(a, b)
+    # an input that wants its gradient, or an odd plane size, keeps the copying route
+    m = Q.QConv2d(3, 64, 7, 2, 3, bias=False).to(DEV)
+    assert not Q._stem_takes_nchw(m, x.clone().requires_grad_())
+    assert not Q._stem_takes_nchw(m, torch.randn(2, 3, 7, 9, device=DEV))
+    with pytest.raises(lib.QB200Error):
+        lib.load().qb_fakequant_affine_nchw3.restype                                   # symbol present
+        lib._run("qb_fakequant_affine_nchw3", 0, x.data_ptr(), want.data_ptr(), 2, 63, 8, rng.data_ptr(), None)
+
+
 WGRAD_CASES = [  # B, Cin, H, W, Cout, k, stride, pad
     (4, 3, 224, 224, 64, 7, 2, 3),       # ResNet conv1 (more tiles than SMs: several tiles per CTA)
     (2, 3, 61, 45, 64, 7, 2, 3),         # ragged tiles
