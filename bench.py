@@ -189,7 +189,7 @@ def main_ours(args, rank, world, local_rank):
         qdist.broadcast_parameters(model)
     from qtorch_b200 import glue
     opt = glue.SGD(model.parameters(), lr=0.1, momentum=0.9)     # torch.optim.SGD arithmetic, one multi-tensor launch
-    crit = torch.nn.CrossEntropyLoss()
+    crit = glue.CrossEntropyLoss()                               # nn.CrossEntropyLoss arithmetic, one pass each way on libqb200
     if args.scaling == "strong":
         if args.batch % world != 0:
             raise SystemExit("--scaling strong: global batch %d is not divisible by %d GPUs" % (args.batch, world))

@@ -80,6 +80,12 @@ int qb_fakequant_affine16(const float* x, float* y, uint8_t* codes, uint16_t* co
  * [B, 3, H*W]; codes are uint8 [B, H*W, 3] (channels-last) for qb_conv_stem_fwd.  Same codes as qb_fakequant_affine with a
  * device range on the channels-last copy; saves that copy (8 B/elem of the batch).  H*W % 4 == 0, bits <= 8. */
 int qb_fakequant_affine_nchw3(const float* x, uint8_t* codes, int64_t B, int64_t HW, int bits, const float* range_dev, void* stream);
+/* The activation quantizer of a tensor-core contraction (quantize.py:339-343) together with the per-row code sums its
+ * zero-point correction needs: qb_fakequant_affine16(y = NULL, device range) + qb_rowsum_u8 in one pass over x [rows, cols]
+ * (the sums are taken from the registers that hold the codes).  codes16 optional.  cols a power of two in 16..256, bits <= 8. */
+int qb_fakequant_affine_rowsum_supported(int64_t cols, int bits);
+int qb_fakequant_affine_rowsum(const float* x, uint8_t* codes, uint16_t* codes16, int64_t rows, int64_t cols, int bits,
+                               const float* range_dev, int32_t* rowsum, void* stream);
 
 /* The min-anchored branch with stochastic rounding (quantize.py:90-100, enforce_true_zero=False, stochastic=True; reached
  * through quantize(x, num_chunks=<truthy>), :159-160): y = rne(clamp((x - min)/s + u, 0, 2^bits-1)) * s + min, u = noise
@@ -199,6 +205,14 @@ size_t qb_rangebn_nhwc_ws_bytes(int64_t C, int num_chunks);
 int qb_rangebn_stats_nhwc(const float* x, int64_t B, int64_t C, int64_t HW, int num_chunks, int32_t* amax,
                           int32_t* amin, int32_t* amax_kc, int32_t* amin_kc, double* red, const float* q_range,
                           int q_bits, uint8_t* x_codes_out, void* ws, size_t ws_bytes, void* stream);
+/* qb_rangebn_stats_nhwc followed by qb_rangebn_finalize(training = 1) (quantize.py:467-498) in one call: where the
+ * statistics pass ends in a single-CTA kernel the per-channel finalize runs at its tail (one launch less per layer).  Same
+ * results as the two calls.  Single-process use: across ranks `red` is exchanged between the two calls, which then stay apart. */
+int qb_rangebn_stats_finalize_nhwc(const float* x, int64_t B, int64_t C, int64_t HW, int num_chunks, int32_t* amax, int32_t* amin,
+                                   int32_t* amax_kc, int32_t* amin_kc, double* red, const float* q_range, int q_bits,
+                                   uint8_t* x_codes_out, float eps, double momentum, int bits, const float* gamma,
+                                   const float* beta, float* running_mean, float* running_var, float* mean, float* scale_raw,
+                                   float* qscale, float* qgamma, float* qbeta, void* ws, size_t ws_bytes, void* stream);
 int qb_rangebn_apply_nhwc(const float* x, const uint8_t* x_codes, float* out, int64_t B, int64_t C, int64_t HW,
                           const float* mean, const float* qscale, const float* qgamma, const float* qbeta,
                           const float* q_range, int q_bits, void* stream);
@@ -208,6 +222,16 @@ int qb_rangebn_bwd_reduce_nhwc(const float* gq, const float* x, const uint8_t* x
                                const float* noise, int stochastic, uint64_t seed, uint64_t offset,
                                const uint64_t* step_dev, uint8_t* gq_codes_out, const uint8_t* relu_bits, void* ws,
                                size_t ws_bytes, void* stream);
+/* qb_rangebn_bwd_reduce_nhwc followed by qb_rangebn_bwd_coeffs in one call (autograd of quantize.py:467-499): the warp that
+ * folds a channel's partial sums derives its coefficients on the spot (one launch less per layer; same arithmetic).
+ * Single-process use: across ranks the sums are exchanged between the two calls. */
+int qb_rangebn_bwd_reduce_coeffs_nhwc(const float* gq, const float* x, const uint8_t* x_codes, int64_t B, int64_t C, int64_t HW,
+                                      double* sg, double* sgx, const float* q_range, int q_bits, const float* g_range, int g_bits,
+                                      const float* noise, int stochastic, uint64_t seed, uint64_t offset, const uint64_t* step_dev,
+                                      uint8_t* gq_codes_out, const uint8_t* relu_bits, int num_chunks, double count,
+                                      double chunk_len, int training, const float* mean, const float* scale_raw,
+                                      const float* qscale, const float* qgamma, float* dgamma, float* dbeta, float* coef_a,
+                                      float* coef_e, void* ws, size_t ws_bytes, void* stream);
 /* relu_bits (optional): gq is the gradient w.r.t. the OUTPUT of the nn.ReLU that follows this RangeBN and relu_bits the
  * bit mask qb_rangebn_apply_relu_measure wrote; the ReLU backward (threshold_backward) then happens on the fly and the
  * masked gradient is never written.  g_range must be the range of the MASKED gradient (qb_relu_bwd_minmax_bits, dx = NULL). */
@@ -393,6 +417,21 @@ size_t qb_maxpool2d_relu_bwd_ws_bytes(void);
 int qb_maxpool2d_relu_nhwc_bwd(const float* grad_out, const uint8_t* idx, const float* pool_out, float* dx, int64_t B, int64_t H,
                                int64_t W, int64_t C, int k, int stride, int pad, float* range_out, void* ws, size_t ws_bytes,
                                void* stream);
+
+/* ---- the tail of the training step (glue_loss.cu) ----------------------------------------------------------------------
+ * nn.AvgPool2d(k) with stride k, no padding (models/resnet_quantized.py:153,189; models/mobilenet_quantized.py:114,124) on
+ * channels-last fp32 x [B, H, W, C], C % 4 == 0: out [B, H/k, W/k, C]; window sums in raster order, one IEEE division. */
+int qb_avgpool2d_nhwc_fwd(const float* x, float* out, int64_t B, int64_t H, int64_t W, int64_t C, int k, void* stream);
+int qb_avgpool2d_nhwc_bwd(const float* grad_out, float* dx, int64_t B, int64_t H, int64_t W, int64_t C, int k, void* stream);
+/* nn.CrossEntropyLoss() (main.py:362-380: mean reduction, no class weights, no label smoothing) on fp32 logits [B, C] and
+ * int64 targets [B].  fwd: loss (device float), n_valid (device float: rows whose target != ignore_index), row_state
+ * float[2*B] = (row max, log-sum-exp) kept for bwd; ws = qb_cross_entropy_ws_bytes(B).  bwd: dlogits [B, C] =
+ * (softmax - onehot) * grad_out / n_valid, rebuilt from row_state (no [B, C] log-softmax intermediate). */
+size_t qb_cross_entropy_ws_bytes(int64_t B);
+int qb_cross_entropy_fwd(const float* logits, const int64_t* target, int64_t B, int64_t C, int64_t ignore_index, float* loss,
+                         float* row_state, float* n_valid, void* ws, size_t ws_bytes, void* stream);
+int qb_cross_entropy_bwd(const float* logits, const int64_t* target, const float* row_state, const float* n_valid,
+                         const float* grad_out, float* dlogits, int64_t B, int64_t C, int64_t ignore_index, void* stream);
 
 /* ---------------------------------------------------------------------------------------------------
  * Dense backward contractions of QConv2d / QLinear (conv_bwd.cu) - replace aten::convolution_backward / matmul under

@@ -50,10 +50,14 @@ PROTOTYPES = {
     "qb_rangebn_bwd_apply": (_i32, [_p, _p, _i64, _i64, _i64, _i32, _p, _p, _p, _p, _p, _p, _p]),
     "qb_rangebn_nhwc_ws_bytes": (_sz, [_i64, _i32]),
     "qb_rangebn_stats_nhwc": (_i32, [_p, _i64, _i64, _i64, _i32, _p, _p, _p, _p, _p, _p, _i32, _p, _p, _sz, _p]),
+    "qb_rangebn_stats_finalize_nhwc": (_i32, [_p, _i64, _i64, _i64, _i32, _p, _p, _p, _p, _p, _p, _i32, _p, _flt, _dbl, _i32,
+                                              _p, _p, _p, _p, _p, _p, _p, _p, _p, _p, _sz, _p]),
     "qb_rangebn_apply_nhwc": (_i32, [_p, _p, _p, _i64, _i64, _i64, _p, _p, _p, _p, _p, _i32, _p]),
     "qb_rangebn_bwd_nhwc_ws_bytes": (_sz, [_i64]),
     "qb_rangebn_bwd_reduce_nhwc": (_i32, [_p, _p, _p, _i64, _i64, _i64, _p, _p, _p, _i32, _p, _i32, _p, _i32, _u64, _u64, _p,
                                           _p, _p, _p, _sz, _p]),
+    "qb_rangebn_bwd_reduce_coeffs_nhwc": (_i32, [_p, _p, _p, _i64, _i64, _i64, _p, _p, _p, _i32, _p, _i32, _p, _i32, _u64, _u64, _p,
+                                                 _p, _p, _i32, _dbl, _dbl, _i32, _p, _p, _p, _p, _p, _p, _p, _p, _p, _sz, _p]),
     "qb_relu_bwd_minmax_bits": (_i32, [_p, _p, _p, _i64, _p, _p, _sz, _p]),
     "qb_rangebn_bwd_apply_fused_nhwc": (_i32, [_p, _p, _i64, _i64, _i64, _i32, _p, _p, _p, _p, _p, _p, _p, _i32, _p, _i32,
                                                _u64, _u64, _p, _p, _p, _p, _sz, _p]),
@@ -70,6 +74,11 @@ PROTOTYPES = {
     "qb_allreduce_small": (_i32, [_p, _i64, _i32, _i32, _p, _i32, _i32, _sz, _p]),
     "qb_maxpool2d_nhwc_fwd": (_i32, [_p, _p, _p, _i64, _i64, _i64, _i64, _i32, _i32, _i32, _p]),
     "qb_maxpool2d_nhwc_bwd": (_i32, [_p, _p, _p, _i64, _i64, _i64, _i64, _i32, _i32, _i32, _p]),
+    "qb_avgpool2d_nhwc_fwd": (_i32, [_p, _p, _i64, _i64, _i64, _i64, _i32, _p]),
+    "qb_avgpool2d_nhwc_bwd": (_i32, [_p, _p, _i64, _i64, _i64, _i64, _i32, _p]),
+    "qb_cross_entropy_ws_bytes": (_sz, [_i64]),
+    "qb_cross_entropy_fwd": (_i32, [_p, _p, _i64, _i64, _i64, _p, _p, _p, _p, _sz, _p]),
+    "qb_cross_entropy_bwd": (_i32, [_p, _p, _p, _p, _p, _p, _i64, _i64, _i64, _p]),
     "qb_maxpool2d_relu_bwd_ws_bytes": (_sz, []),
     "qb_maxpool2d_relu_nhwc_bwd": (_i32, [_p, _p, _p, _p, _i64, _i64, _i64, _i64, _i32, _i32, _i32, _p, _p, _sz, _p]),
     "qb_conv_stem_supported": (_i32, [_i64, _i64, _i64, _i64, _i32, _i32, _i32, _i32]),
@@ -102,6 +111,8 @@ PROTOTYPES = {
     "qb_wt_pack": (_i32, [_p, _p, _i64, _i64, _i32, _p]),
     "qb_conv_dgrad": (_i32, [_p, _p, _p, _p, _i64, _i64, _i64, _i64, _i64, _i32, _i32, _i32, _i32, _p, _i32, _flt, _p]),
     "qb_fakequant_affine_nchw3": (_i32, [_p, _p, _i64, _i64, _i32, _p, _p]),
+    "qb_fakequant_affine_rowsum_supported": (_i32, [_i64, _i32]),
+    "qb_fakequant_affine_rowsum": (_i32, [_p, _p, _p, _i64, _i64, _i32, _p, _p, _p]),
     "qb_conv_dgrad_acc": (_i32, [_p, _p, _p, _i64, _i64, _i64, _i64, _i64, _i32, _i32, _i32, _i32, _p, _i32, _flt, _p]),
     "qb_conv_wgrad_ws_bytes": (_sz, [_i64, _i64, _i64, _i64, _i64, _i32, _i32, _i32, _i32]),
     "qb_conv_wgrad": (_i32, [_p, _p, _p, _p, _p, _p, _i64, _i64, _i64, _i64, _i64, _i32, _i32, _i32, _i32, _p, _i32, _p, _sz, _p]),
@@ -145,9 +156,10 @@ _profile = None       # list of (name, algorithmic_bytes, start_event, end_event
 
 # kernels enqueued per C call
 _NLAUNCH = {"qb_rangebn_stats": 2, "qb_rangebn_bwd_reduce": 2, "qb_rangebn_bwd_apply": 2,
-            "qb_conv_i8_fwd": 2, "qb_conv_wgrad": 3, "qb_conv_dw_wgrad": 2, "qb_conv_stem_fwd": 2, "qb_conv_stem_wgrad": 2, "qb_rangebn_stats_nhwc": 2, "qb_rangebn_bwd_reduce_nhwc": 2, "qb_rangebn_apply_relu_measure": 1, "qb_rangebn_bwd_apply_nhwc": 2}
+            "qb_conv_i8_fwd": 2, "qb_conv_wgrad": 3, "qb_conv_dw_wgrad": 2, "qb_conv_stem_fwd": 2, "qb_conv_stem_wgrad": 2, "qb_rangebn_stats_nhwc": 2, "qb_rangebn_stats_finalize_nhwc": 2, "qb_rangebn_bwd_reduce_nhwc": 2, "qb_rangebn_bwd_reduce_coeffs_nhwc": 2, "qb_rangebn_apply_relu_measure": 1, "qb_rangebn_bwd_apply_nhwc": 2}
 
 
+FUSE_RANGEBN_COEFFS = os.environ.get("QB_FUSE_RBN_COEFFS", "1") != "0"    # rangebn_backward without a cross-rank hook: sums + coefficients in one call (tests flip it)
 _SYNC_EACH = os.environ.get("QB_SYNC_EACH", "") == "1"
 _next_ops = 0          # integer operations (2*M*N*K) of the next tensor-core call, set by the conv / GEMM wrappers
 PROFILE_OPS = {}       # name -> operations recorded between profile_begin() and profile_end()
@@ -368,6 +380,19 @@ def fakequant_affine_nchw3(x, bits, range_dev):
     return codes
 
 
+def fakequant_affine_rowsum_supported(cols, bits):
+    return bool(load().qb_fakequant_affine_rowsum_supported(int(cols), int(bits)))
+
+
+def fakequant_affine_rowsum(x, rows, cols, bits, range_dev, codes, codes16=None):
+    """Quantizer codes (+ bf16 codes) of x viewed as [rows, cols] and the int32 row sums of the codes, one pass
+    (qb_fakequant_affine_rowsum).  Returns the row sums."""
+    rowsum = torch.empty(rows, dtype=torch.int32, device=x.device)
+    _run("qb_fakequant_affine_rowsum", (5 + (2 if codes16 is not None else 0)) * x.numel(), _ptr(x), _ptr(codes), _ptr(codes16),
+         int(rows), int(cols), int(bits), _ptr(range_dev), _ptr(rowsum), _stream())
+    return rowsum
+
+
 def fakequant_affine_stochastic(x, bits, range_dev=None, lo=0.0, hi=0.0, scale_mode=QB_SCALE_DOUBLE, noise=None, seed=0,
                                 step_dev=None, out=None):
     """Min-anchored fake-quant with stochastic rounding (qb_fakequant_affine_stochastic)."""
@@ -484,6 +509,26 @@ def rangebn_stats(x, B, Cn, HW, num_chunks, want_arg=True, nhwc=False, q_range=N
     return red, amax, amin
 
 
+def rangebn_stats_finalize_nhwc(x, B, Cn, HW, num_chunks, eps, momentum, bits, gamma, beta, running_mean, running_var,
+                                want_arg=True, q_range=None, q_bits=8, x_codes_out=None):
+    """rangebn_stats(nhwc=True) + rangebn_finalize(training=True) in one call (qb_rangebn_stats_finalize_nhwc).
+    Returns (vec float[5, C], amax, amin)."""
+    lib = load()
+    dev = x.device
+    red = torch.empty(3 * Cn, dtype=torch.float64, device=dev)
+    vec = torch.empty(5, Cn, dtype=torch.float32, device=dev)
+    ws = workspace("rangebn_nhwc", lib.qb_rangebn_nhwc_ws_bytes(Cn, num_chunks), dev)
+    amax = torch.empty(2, Cn * num_chunks, dtype=torch.int32, device=dev) if want_arg else None
+    amin = torch.empty(2, Cn * num_chunks, dtype=torch.int32, device=dev) if want_arg else None
+    _run("qb_rangebn_stats_finalize_nhwc", (4 + (1 if x_codes_out is not None else 0)) * B * Cn * HW, _ptr(x), B, Cn, HW,
+         num_chunks, _ptr(amax[0]) if want_arg else None, _ptr(amin[0]) if want_arg else None,
+         _ptr(amax[1]) if want_arg else None, _ptr(amin[1]) if want_arg else None, _ptr(red), _ptr(q_range), int(q_bits),
+         _ptr(x_codes_out), float(eps), float(momentum), int(bits), _ptr(gamma), _ptr(beta), _ptr(running_mean),
+         _ptr(running_var), _ptr(vec[0]), _ptr(vec[1]), _ptr(vec[2]), _ptr(vec[3]) if gamma is not None else None,
+         _ptr(vec[4]) if beta is not None else None, _ptr(ws), ws.numel(), _stream())
+    return vec, amax, amin
+
+
 def rangebn_finalize(red, Cn, num_chunks, count, chunk_len, eps, momentum, training, bits, gamma, beta, running_mean,
                      running_var):
     """Returns vec float[5, C]: rows mean, scale_raw, qscale, qgamma, qbeta."""
@@ -542,10 +587,19 @@ def rangebn_backward(gq, xq, B, Cn, HW, num_chunks, count, chunk_len, training, 
     codes = None
     if fused and grad_quant is not None and int(grad_quant["bits"]) <= 8:
         codes = torch.empty(gq.numel(), dtype=torch.uint8, device=dev)   # Q(g) handed from the reduce to the apply pass
+    coef = torch.empty(4, Cn, dtype=torch.float32, device=dev)     # dgamma, dbeta, a, e
+    coef_args = (int(chunks_global), float(count), float(chunk_len), int(training), _ptr(vec[0]), _ptr(vec[1]), _ptr(vec[2]),
+                 _ptr(vec[3]) if has_gamma else None, _ptr(coef[0]), _ptr(coef[1]), _ptr(coef[2]), _ptr(coef[3]))
+    have_coef = False
     if nhwc:
         nb = 4 + (1 if x_codes is not None else 4) + (1 if codes is not None else 0)
-        _run("qb_rangebn_bwd_reduce_nhwc", nb * B * Cn * HW, _ptr(gq), _ptr(xq), _ptr(x_codes), B, Cn, HW, _ptr(sums[:Cn]),
-             _ptr(sums[Cn:]), _ptr(q_range), int(q_bits), *gqa, _ptr(codes), _ptr(relu_bits), _ptr(ws), ws.numel(), _stream())
+        red_args = (_ptr(gq), _ptr(xq), _ptr(x_codes), B, Cn, HW, _ptr(sums[:Cn]), _ptr(sums[Cn:]), _ptr(q_range), int(q_bits),
+                    *gqa, _ptr(codes), _ptr(relu_bits))
+        if reduce_hook is None and FUSE_RANGEBN_COEFFS:      # nothing to exchange between the sums and the coefficients
+            _run("qb_rangebn_bwd_reduce_coeffs_nhwc", nb * B * Cn * HW, *red_args, *coef_args, _ptr(ws), ws.numel(), _stream())
+            have_coef = True
+        else:
+            _run("qb_rangebn_bwd_reduce_nhwc", nb * B * Cn * HW, *red_args, _ptr(ws), ws.numel(), _stream())
     else:
         if q_range is not None or x_codes is not None:
             raise QB200Error("rangebn_backward: on-the-fly input quantization / x_codes are channels-last features")
@@ -553,11 +607,8 @@ def rangebn_backward(gq, xq, B, Cn, HW, num_chunks, count, chunk_len, training, 
              _ptr(ws), ws.numel(), _stream())
     if reduce_hook is not None:
         reduce_hook(sums)
-    coef = torch.empty(4, Cn, dtype=torch.float32, device=dev)     # dgamma, dbeta, a, e
-    _run("qb_rangebn_bwd_coeffs", 0, _ptr(sums[:Cn]), _ptr(sums[Cn:]), Cn, int(chunks_global), float(count),
-                                     float(chunk_len), int(training), _ptr(vec[0]), _ptr(vec[1]), _ptr(vec[2]),
-                                     _ptr(vec[3]) if has_gamma else None, _ptr(coef[0]), _ptr(coef[1]), _ptr(coef[2]),
-                                     _ptr(coef[3]), _stream())
+    if not have_coef:
+        _run("qb_rangebn_bwd_coeffs", 0, _ptr(sums[:Cn]), _ptr(sums[Cn:]), Cn, *coef_args, _stream())
     dx = torch.empty_like(gq)
     dx_range = None
     if fused:
@@ -921,6 +972,41 @@ def maxpool2d_nhwc_bwd(g, idx, in_shape, k, stride, pad):
     dx = torch.empty(in_shape, dtype=torch.float32, device=g.device, memory_format=torch.channels_last)
     _run("qb_maxpool2d_nhwc_bwd", 5 * g.numel() + 4 * dx.numel(), _ptr(g), _ptr(idx), _ptr(dx), B, H, W, Cn, int(k), int(stride),
          int(pad), _stream())
+    return dx
+
+
+def avgpool2d_nhwc_fwd(x, k):
+    B, Cn, H, W = x.shape
+    out = torch.empty((B, Cn, H // k, W // k), dtype=torch.float32, device=x.device, memory_format=torch.channels_last)
+    _run("qb_avgpool2d_nhwc_fwd", 4 * (x.numel() + out.numel()), _ptr(x), _ptr(out), B, H, W, Cn, int(k), _stream())
+    return out
+
+
+def avgpool2d_nhwc_bwd(g, in_shape, k):
+    B, Cn, H, W = in_shape
+    dx = torch.empty(in_shape, dtype=torch.float32, device=g.device, memory_format=torch.channels_last)
+    _run("qb_avgpool2d_nhwc_bwd", 4 * (g.numel() + dx.numel()), _ptr(g), _ptr(dx), B, H, W, Cn, int(k), _stream())
+    return dx
+
+
+def cross_entropy_fwd(logits, target, ignore_index=-100):
+    """(loss 0-dim tensor, row_state float[2*B], n_valid float[1]) of qb_cross_entropy_fwd."""
+    lib = load()
+    B, Cn = logits.shape
+    out = torch.empty(2, dtype=torch.float32, device=logits.device)           # loss, n_valid
+    row_state = torch.empty(2 * B, dtype=torch.float32, device=logits.device)
+    ws = workspace("cross_entropy", lib.qb_cross_entropy_ws_bytes(B), logits.device)
+    _NLAUNCH["qb_cross_entropy_fwd"] = 2
+    _run("qb_cross_entropy_fwd", 4 * logits.numel(), _ptr(logits), _ptr(target), B, Cn, int(ignore_index), _ptr(out[0:1]),
+         _ptr(row_state), _ptr(out[1:2]), _ptr(ws), ws.numel(), _stream())
+    return out[0], row_state, out[1:2]
+
+
+def cross_entropy_bwd(logits, target, row_state, n_valid, grad_out, ignore_index=-100):
+    B, Cn = logits.shape
+    dx = torch.empty_like(logits)
+    _run("qb_cross_entropy_bwd", 8 * logits.numel(), _ptr(logits), _ptr(target), _ptr(row_state), _ptr(n_valid), _ptr(grad_out),
+         _ptr(dx), B, Cn, int(ignore_index), _stream())
     return dx
 
 

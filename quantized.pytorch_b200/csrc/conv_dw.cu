@@ -719,12 +719,9 @@ extern "C" int qb_conv_dw_wgrad(const float* grad_out, const float* x_hat, float
         return QB_ERR_WORKSPACE;
     }
     const size_t smem = (size_t)40 * DW_THREADS * sizeof(float);
-    static bool configured = false;
-    if (!configured) {
-        QB_CUDA(cudaFuncSetAttribute(k_conv_dw_wgrad_strip, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        QB_CUDA(cudaFuncSetAttribute(k_conv_dw_wgrad<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        configured = true;
-    }
+    // per call, not cached: the attribute belongs to the CURRENT device's copy of the function
+    if (stride == 1) QB_CUDA(cudaFuncSetAttribute(k_conv_dw_wgrad_strip, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    else QB_CUDA(cudaFuncSetAttribute(k_conv_dw_wgrad<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     cudaStream_t st = qb_stream(stream);
     float* partial = static_cast<float*>(ws);
     if (stride == 1) k_conv_dw_wgrad_strip<<<grid, DW_THREADS, smem, st>>>(grad_out, x_hat, partial, g);

@@ -614,11 +614,7 @@ static int launch_conv(const CUtensorMap& tx, const CUtensorMap& tw, const CUten
     const size_t stage = g.halo ? (size_t)g.kw * g.BK * g.TW * (g.TH + g.kh - 1) : (size_t)(128 + BN) * g.BK;
     const size_t smem = (size_t)g.stages * stage + CV_STAGING_BYTES + 1024 + conv_tail_bytes(BN, g.kh * g.kw) +
                         (g.halo ? (size_t)g.kh * g.kw * BN * g.BK : 0);
-    static size_t configured = 0;
-    if (smem > configured) {
-        QB_CUDA(cudaFuncSetAttribute(k_conv_i8<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-        configured = smem;
-    }
+    QB_CUDA(cudaFuncSetAttribute(k_conv_i8<BN>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));   // per device: not cached
     const int64_t total = (int64_t)g.tiles_w * g.tiles_h * g.tiles_b * ((g.Cout + BN - 1) / BN);
     int sms = qb_sm_count();
     if (sms <= 0) sms = 148;

@@ -30,9 +30,10 @@ __device__ __forceinline__ QParams load_qparams(const RangeArg& r, int bits, int
 // ------------------------------------------------------------------------------------------------
 // min-anchored affine (A1): thread = one 32-byte octet per step, FQ_U octets in flight
 // ------------------------------------------------------------------------------------------------
+// returns the sum of the octet's 8 integer codes (dead code unless the caller uses it: k_fq_affine_rowsum)
 template <bool WRITE_Y, bool WRITE_C, bool SMALL, bool WRITE_H = false>
-__device__ __forceinline__ void affine_octet(const F8& v, float* y, uint8_t* codes, int64_t oct, const QParams& p,
-                                             const Divisor& d, uint16_t* codes16 = nullptr) {
+__device__ __forceinline__ uint32_t affine_octet(const F8& v, float* y, uint8_t* codes, int64_t oct, const QParams& p,
+                                                 const Divisor& d, uint16_t* codes16 = nullptr) {
     float a[8];
     bool ok = d.fast;
 #pragma unroll
@@ -82,6 +83,10 @@ __device__ __forceinline__ void affine_octet(const F8& v, float* y, uint8_t* cod
         o.w = __byte_perm(f[6], f[7], 0x7632);
         reinterpret_cast<uint4*>(codes16)[oct] = o;
     }
+    uint32_t sum = 0;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) sum += SMALL ? (c[j] & 0xffffu) : c[j];      // SMALL: the code sits in the low mantissa bits
+    return sum;
 }
 
 template <bool WRITE_Y, bool WRITE_C, bool SMALL, bool WRITE_H = false>
@@ -118,6 +123,39 @@ k_fq_affine_v8(const float* __restrict__ x, float* y, uint8_t* codes, int64_t n,
         affine_sweep<WRITE_Y, WRITE_C, true, WRITE_H>(x, y, codes, n, p, d, codes16);
     else
         affine_sweep<WRITE_Y, WRITE_C, false, WRITE_H>(x, y, codes, n, p, d, codes16);
+}
+
+// The activation quantizer of a tensor-core contraction with the per-pixel (per-row) code sums the zero-point correction of
+// the int8 kernels needs (qb_rowsum_u8) taken from the registers that hold the codes: a row of `cols` = 8 * lpp codes sits in
+// lpp adjacent lanes (lpp = 2 .. 32, a power of two; the octet index of lane 0 is a multiple of 32), so a xor-shuffle tree
+// over lpp lanes yields the row sum - no second pass over the codes, one launch less per layer.  Loop bounds are warp-uniform.
+template <bool WRITE_H>
+__global__ void __launch_bounds__(FQ_THREADS, 4)
+k_fq_affine_rowsum(const float* __restrict__ x, uint8_t* codes, uint16_t* codes16, int64_t n, int bits, RangeArg r, int mode, int lpp,
+                   int lpp_log2, int32_t* __restrict__ rowsum) {
+    const QParams p = load_qparams(r, bits, mode);
+    const Divisor d = make_divisor(p.scale);
+    const int64_t noct = n >> 3, stride = (int64_t)gridDim.x * FQ_THREADS;
+    const int lane = threadIdx.x & 31;
+    for (int64_t iw = (int64_t)blockIdx.x * FQ_THREADS + (threadIdx.x - lane); iw < noct; iw += FQ_U * stride) {
+        F8 v[FQ_U];
+        bool ok[FQ_U];
+#pragma unroll
+        for (int u = 0; u < FQ_U; ++u) {
+            const int64_t i = iw + u * stride + lane;
+            ok[u] = i < noct;
+            if (ok[u]) v[u] = ld256_stream(x + 8 * i);
+        }
+#pragma unroll
+        for (int u = 0; u < FQ_U; ++u) {
+            if (iw + u * stride >= noct) break;                                  // warp-uniform
+            const int64_t i = iw + u * stride + lane;
+            uint32_t sum = 0;
+            if (ok[u]) sum = affine_octet<false, true, true, WRITE_H>(v[u], nullptr, codes, i, p, d, codes16);
+            for (int o = 1; o < lpp; o <<= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
+            if (ok[u] && (lane & (lpp - 1)) == 0) rowsum[i >> lpp_log2] = (int32_t)sum;
+        }
+    }
 }
 
 // scalar path for pointers that are not 32-byte aligned (views into larger tensors)
@@ -235,6 +273,32 @@ extern "C" int qb_fakequant_affine16(const float* x, float* y, uint8_t* codes, u
     } else {
         k_fq_affine_scalar<<<fq_grid(n, 8), FQ_THREADS, 0, st>>>(x, y, codes, n, bits, r, scale_mode, codes16);
     }
+    QB_LAUNCH_CHECK();
+    return QB_OK;
+}
+
+extern "C" int qb_fakequant_affine_rowsum_supported(int64_t cols, int bits) {
+    return bits >= 1 && bits <= 8 && cols >= 16 && cols <= 256 && (cols & (cols - 1)) == 0;
+}
+
+/* Codes (uint8, and optionally as bf16 in codes16) of the min-anchored quantizer over x [rows, cols] with a device range, plus
+ * rowsum[r] = SUM_c codes[r][c] - qb_fakequant_affine16(y = NULL) + qb_rowsum_u8 in one pass.  cols a power of two in 16..256. */
+extern "C" int qb_fakequant_affine_rowsum(const float* x, uint8_t* codes, uint16_t* codes16, int64_t rows, int64_t cols, int bits,
+                                          const float* range_dev, int32_t* rowsum, void* stream) {
+    QB_CHECK_ARG(x && codes && range_dev && rowsum, "qb_fakequant_affine_rowsum: null pointer");
+    QB_CHECK_ARG(rows > 0 && qb_fakequant_affine_rowsum_supported(cols, bits),
+                 "qb_fakequant_affine_rowsum: rows=%lld cols=%lld bits=%d (cols a power of two in 16..256, bits <= 8)", (long long)rows,
+                 (long long)cols, bits);
+    QB_CHECK_ARG(aligned(x, 32) && aligned(codes, 8) && (!codes16 || aligned(codes16, 16)), "qb_fakequant_affine_rowsum: misaligned tensor");
+    const int lpp = (int)(cols >> 3);
+    int lg = 0;
+    while ((1 << lg) < lpp) ++lg;
+    const int64_t n = rows * cols;
+    RangeArg r{range_dev, 0.0, 0.0};
+    const int grid = fq_grid(n >> 3, 4);
+    cudaStream_t st = qb_stream(stream);
+    if (codes16) k_fq_affine_rowsum<true><<<grid, FQ_THREADS, 0, st>>>(x, codes, codes16, n, bits, r, QB_SCALE_DOUBLE, lpp, lg, rowsum);
+    else k_fq_affine_rowsum<false><<<grid, FQ_THREADS, 0, st>>>(x, codes, codes16, n, bits, r, QB_SCALE_DOUBLE, lpp, lg, rowsum);
     QB_LAUNCH_CHECK();
     return QB_OK;
 }

@@ -264,11 +264,7 @@ extern "C" int qb_gemm_i8(const uint8_t* A, const uint8_t* B, float* C, int64_t 
     if (rc) return rc;
     rc = qb_make_tmap(&tb, CU_TENSOR_MAP_DATA_TYPE_UINT8, 2, B, db, st, box, nullptr);
     if (rc) return rc;
-    static bool attr_set = false;
-    if (!attr_set) {
-        QB_CUDA(cudaFuncSetAttribute(k_gemm_i8, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)G_SMEM_BYTES));
-        attr_set = true;
-    }
+    QB_CUDA(cudaFuncSetAttribute(k_gemm_i8, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)G_SMEM_BYTES));   // per device: not cached
     GemmEpilogue ep{a_range, a_bits, b_row_min, b_row_max, b_bits, a_rowsum, b_rowsum, bias, b_offset};
     dim3 grid((unsigned)((N + G_BN - 1) / G_BN), (unsigned)((M + G_BM - 1) / G_BM));
     k_gemm_i8<<<grid, G_THREADS, G_SMEM_BYTES, qb_stream(stream)>>>(ta, tb, C, (int)M, (int)N, (int)K, ldc, ep);

@@ -6,6 +6,7 @@
 #include <math.h>
 
 #include "common.cuh"
+#include "rangebn_common.cuh"
 
 constexpr int RB_THREADS = 256;
 
@@ -164,59 +165,9 @@ extern "C" int qb_rangebn_stats(const float* x, int64_t B, int64_t C, int64_t HW
 // ---------------------------------------------------------------------------------------------------
 // per-channel finalize (quantize.py:470-498), single CTA
 // ---------------------------------------------------------------------------------------------------
-constexpr int RF_THREADS = 1024;
-
-__device__ __forceinline__ void block_minmax3(float (&mn)[3], float (&mx)[3], float* sm /* 6*32 */) {
-    const int w = threadIdx.x >> 5, l = threadIdx.x & 31, nw = RF_THREADS / 32;
-#pragma unroll
-    for (int j = 0; j < 3; ++j) { mn[j] = warp_min(mn[j]); mx[j] = warp_max(mx[j]); }
-    if (l == 0) {
-#pragma unroll
-        for (int j = 0; j < 3; ++j) { sm[j * 32 + w] = mn[j]; sm[(3 + j) * 32 + w] = mx[j]; }
-    }
-    __syncthreads();
-#pragma unroll
-    for (int j = 0; j < 3; ++j) {
-        mn[j] = warp_min(l < nw ? sm[j * 32 + l] : QB_INF);
-        mx[j] = warp_max(l < nw ? sm[(3 + j) * 32 + l] : -QB_INF);
-    }
-}
-
-__global__ void __launch_bounds__(RF_THREADS)
-k_rangebn_finalize(const double* red, int64_t C, double K, double count, double scale_fix, float eps, double momentum,
-                   int training, int bits, const float* gamma, const float* beta, float* running_mean,
-                   float* running_var, float* mean_out, float* scale_raw, float* qscale, float* qgamma, float* qbeta) {
+__global__ void __launch_bounds__(RF_THREADS) k_rangebn_finalize(const double* red, int64_t C, RbnFinalizeArg a) {
     __shared__ float sm[6 * 32];
-    const float fix_f = (float)scale_fix, m_f = (float)momentum, om_f = (float)(1.0 - momentum);
-    float mn[3] = {QB_INF, QB_INF, QB_INF}, mx[3] = {-QB_INF, -QB_INF, -QB_INF};
-    for (int64_t c = threadIdx.x; c < C; c += RF_THREADS) {
-        float mean, r;
-        if (training) {
-            const float mean_max = (float)(red[c] / K), mean_min = (float)(red[C + c] / K);
-            mean = (float)(red[2 * C + c] / count);
-            const float u = __fadd_rn(__fmul_rn(__fsub_rn(mean_max, mean_min), fix_f), eps);
-            r = __fdiv_rn(1.0f, u);
-            running_mean[c] = __fadd_rn(__fmul_rn(running_mean[c], m_f), __fmul_rn(mean, om_f));
-            running_var[c] = __fadd_rn(__fmul_rn(running_var[c], m_f), __fmul_rn(r, om_f));
-        } else {
-            mean = running_mean[c];
-            r = running_var[c];
-        }
-        mean_out[c] = mean;
-        scale_raw[c] = r;
-        mn[0] = fminf(mn[0], r); mx[0] = fmaxf(mx[0], r);
-        if (gamma) { float g = gamma[c]; mn[1] = fminf(mn[1], g); mx[1] = fmaxf(mx[1], g); }
-        if (beta) { float b = beta[c]; mn[2] = fminf(mn[2], b); mx[2] = fmaxf(mx[2], b); }
-    }
-    block_minmax3(mn, mx, sm);
-    const QParams ps = make_qparams_d((double)mn[0], (double)mx[0], bits);   // float(scale.min()), float(scale.max())
-    const QParams pg = make_qparams_d((double)mn[1], (double)mx[1], bits);   // float(weight.min()), float(weight.max())
-    const QParams pb = make_qparams_f(mn[2], mx[2], bits);                   // quantize(bias): tensor range from data
-    for (int64_t c = threadIdx.x; c < C; c += RF_THREADS) {
-        qscale[c] = q_affine_deq(q_affine_code(scale_raw[c], ps), ps);
-        if (gamma) qgamma[c] = q_affine_deq(q_affine_code(gamma[c], pg), pg);
-        if (beta) qbeta[c] = q_affine_deq(q_affine_code(beta[c], pb), pb);
-    }
+    rbn_finalize_body(red, C, a, sm);
 }
 
 extern "C" int qb_rangebn_finalize(const double* red, int64_t C, int num_chunks, double count, double chunk_len,
@@ -228,13 +179,9 @@ extern "C" int qb_rangebn_finalize(const double* red, int64_t C, int num_chunks,
                  "qb_rangebn_finalize: training needs red, num_chunks>0, count>0, chunk_len>1");
     QB_CHECK_ARG((!gamma || qgamma) && (!beta || qbeta), "qb_rangebn_finalize: gamma/beta without output");
     QB_CHECK_ARG(bits >= 1 && bits <= 24, "qb_rangebn_finalize: bits=%d", bits);
-    // quantize.py:473-474, Python double
-    double scale_fix = 0.0;
-    if (training)
-        scale_fix = (0.5 * 0.35) * (1.0 + sqrt(3.14159265358979323846 * log(4.0))) / sqrt(2.0 * log(chunk_len));
-    k_rangebn_finalize<<<1, RF_THREADS, 0, qb_stream(stream)>>>(red, C, (double)num_chunks, count, scale_fix, eps, momentum,
-                                                              training, bits, gamma, beta, running_mean, running_var,
-                                                              mean, scale_raw, qscale, qgamma, qbeta);
+    RbnFinalizeArg a{(double)num_chunks, count, training ? rbn_scale_fix(chunk_len) : 0.0, momentum, eps, training, bits, gamma, beta,
+                     running_mean, running_var, mean, scale_raw, qscale, qgamma, qbeta};
+    k_rangebn_finalize<<<1, RF_THREADS, 0, qb_stream(stream)>>>(red, C, a);
     QB_LAUNCH_CHECK();
     return QB_OK;
 }
@@ -413,25 +360,10 @@ extern "C" int qb_rangebn_bwd_reduce(const float* gq, const float* x, int64_t B,
     return QB_OK;
 }
 
-__global__ void k_rangebn_bwd_coeffs(const double* sg, const double* sgx, int64_t C, double K, double count,
-                                     double scale_fix, int training, const float* mean, const float* scale_raw,
-                                     const float* qscale, const float* qgamma, float* dgamma, float* dbeta, float* coef_a,
-                                     float* coef_e) {
+__global__ void k_rangebn_bwd_coeffs(const double* sg, const double* sgx, int64_t C, RbnCoefArg a) {
     int64_t c = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
     if (c >= C) return;
-    const double g = sg[c], gx = sgx[c], mu = (double)mean[c], s = (double)qscale[c];
-    const double gam = qgamma ? (double)qgamma[c] : 1.0;
-    const double centered = gx - mu * g;                 // sum gq (xq - mu)
-    if (dbeta) dbeta[c] = (float)g;
-    if (dgamma) dgamma[c] = (float)(s * centered);
-    if (training) {
-        const double r = (double)scale_raw[c];
-        coef_a[c] = (float)(-(s * gam * g) / count);
-        coef_e[c] = (float)(-(scale_fix * r * r * gam * centered) / K);
-    } else {
-        coef_a[c] = 0.0f;
-        coef_e[c] = 0.0f;
-    }
+    rbn_bwd_coeffs_channel(sg[c], sgx[c], c, a);
 }
 
 extern "C" int qb_rangebn_bwd_coeffs(const double* sg, const double* sgx, int64_t C, int num_chunks, double count,
@@ -440,12 +372,9 @@ extern "C" int qb_rangebn_bwd_coeffs(const double* sg, const double* sgx, int64_
                                      float* coef_e, void* stream) {
     QB_CHECK_ARG(sg && sgx && mean && scale_raw && qscale && coef_a && coef_e && C > 0, "qb_rangebn_bwd_coeffs: null pointer");
     QB_CHECK_ARG(!training || (num_chunks > 0 && count > 0 && chunk_len > 1), "qb_rangebn_bwd_coeffs: bad chunking");
-    double scale_fix = 0.0;
-    if (training)
-        scale_fix = (0.5 * 0.35) * (1.0 + sqrt(3.14159265358979323846 * log(4.0))) / sqrt(2.0 * log(chunk_len));
-    k_rangebn_bwd_coeffs<<<(unsigned)((C + 127) / 128), 128, 0, qb_stream(stream)>>>(
-        sg, sgx, C, (double)num_chunks, count, scale_fix, training, mean, scale_raw, qscale, qgamma, dgamma, dbeta, coef_a,
-        coef_e);
+    const RbnCoefArg a{(double)num_chunks, count, training ? rbn_scale_fix(chunk_len) : 0.0, training, mean, scale_raw, qscale, qgamma,
+                       dgamma, dbeta, coef_a, coef_e};
+    k_rangebn_bwd_coeffs<<<(unsigned)((C + 127) / 128), 128, 0, qb_stream(stream)>>>(sg, sgx, C, a);
     QB_LAUNCH_CHECK();
     return QB_OK;
 }

@@ -9,6 +9,7 @@
 #include <math.h>
 
 #include "common.cuh"
+#include "rangebn_common.cuh"
 
 constexpr int NH_THREADS = 256;
 constexpr int NH_UNROLL = 4;
@@ -368,29 +369,75 @@ k_rbn_stats_q8_nhwc(const float* __restrict__ x, NhwcGeom g, uint32_t* __restric
 // Atomic-combine path: per channel, walk the K chunk accumulators in order - arg rows, chunk extrema and the chunk sums the
 // merge kernel produced, plus the red[3][C] block of k_rbn_stats_nhwc_pack - and reset them.  One thread per channel
 // (coalesced over c); K is small (16).
-__global__ void k_rbn_stats_q8_finish(Q8Acc* acc_kc, int64_t C, int K, int64_t L, const float* q_range, int q_bits, int32_t* amax,
-                                      int32_t* amin, int32_t* amax_kc, int32_t* amin_kc, double* red) {
-    const int64_t c = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
-    if (c >= C) return;
-    const QParams p = make_qparams_d((double)__ldg(q_range), (double)__ldg(q_range + 1), q_bits);
+struct Q8FinishArg {
+    Q8Acc* acc_kc;
+    int64_t C, L;
+    int K;
+    const float* q_range;
+    int q_bits;
+    int32_t *amax, *amin, *amax_kc, *amin_kc;
+    double* red;
+};
+
+// channel c: the K accumulators are fetched KB at a time before anything is stored (the resets alias the loads, so a plain
+// loop serialises K round trips to L2), then folded in chunk order - the summation order of k_rbn_stats_nhwc_pack
+template <int KB>
+__device__ __forceinline__ void q8_finish_channel(const Q8FinishArg& f, const QParams& p, int64_t c) {
     double smax = 0.0, smin = 0.0, ssum = 0.0;
-    for (int k = 0; k < K; ++k) {
-        const int64_t t = (int64_t)k * C + c;
-        const uint32_t a = acc_kc[t].kmax, b = ~acc_kc[t].nkmin;
-        const unsigned long long sm = acc_kc[t].sum;
-        acc_kc[t].kmax = 0u; acc_kc[t].nkmin = 0u; acc_kc[t].sum = 0ull;
-        const int32_t imx = (int32_t)(k * L + (int64_t)(0xffffffu - (a & 0xffffffu))), imn = (int32_t)(k * L + (int64_t)(b & 0xffffffu));
-        smax += (double)q_affine_deq((float)(a >> 24), p);
-        smin += (double)q_affine_deq((float)(b >> 24), p);
-        ssum += (double)L * (double)p.lo + (double)p.scale * (double)sm;          // as k_rbn_stats_q8_merge
-        if (amax) amax[c * K + k] = imx;
-        if (amin) amin[c * K + k] = imn;
-        if (amax_kc) amax_kc[t] = imx;
-        if (amin_kc) amin_kc[t] = imn;
+    for (int k0 = 0; k0 < f.K; k0 += KB) {
+        uint32_t a[KB], b[KB];
+        unsigned long long sm[KB];
+#pragma unroll
+        for (int j = 0; j < KB; ++j) {
+            if (k0 + j < f.K) {
+                const Q8Acc* q = f.acc_kc + (int64_t)(k0 + j) * f.C + c;
+                a[j] = q->kmax; b[j] = ~q->nkmin; sm[j] = q->sum;
+            }
+        }
+#pragma unroll
+        for (int j = 0; j < KB; ++j) {
+            if (k0 + j < f.K) {
+                const int k = k0 + j;
+                const int64_t t = (int64_t)k * f.C + c;
+                f.acc_kc[t].kmax = 0u; f.acc_kc[t].nkmin = 0u; f.acc_kc[t].sum = 0ull;
+                const int32_t imx = (int32_t)(k * f.L + (int64_t)(0xffffffu - (a[j] & 0xffffffu)));
+                const int32_t imn = (int32_t)(k * f.L + (int64_t)(b[j] & 0xffffffu));
+                smax += (double)q_affine_deq((float)(a[j] >> 24), p);
+                smin += (double)q_affine_deq((float)(b[j] >> 24), p);
+                ssum += (double)f.L * (double)p.lo + (double)p.scale * (double)sm[j];          // as k_rbn_stats_q8_merge
+                if (f.amax) f.amax[c * f.K + k] = imx;
+                if (f.amin) f.amin[c * f.K + k] = imn;
+                if (f.amax_kc) f.amax_kc[t] = imx;
+                if (f.amin_kc) f.amin_kc[t] = imn;
+            }
+        }
     }
-    red[c] = smax;
-    red[C + c] = smin;
-    red[2 * C + c] = ssum;
+    f.red[c] = smax;
+    f.red[f.C + c] = smin;
+    f.red[2 * f.C + c] = ssum;
+}
+
+__global__ void k_rbn_stats_q8_finish(Q8FinishArg f) {
+    const int64_t c = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (c >= f.C) return;
+    const QParams p = make_qparams_d((double)__ldg(f.q_range), (double)__ldg(f.q_range + 1), f.q_bits);
+    q8_finish_channel<16>(f, p, c);
+}
+
+// ... and with the per-channel finalize of quantize.py:470-498 behind it in the same (single) CTA: one launch instead of two
+// per RangeBN layer when no cross-rank exchange sits between the two (qb_rangebn_stats_finalize_nhwc)
+__global__ void __launch_bounds__(RF_THREADS) k_rbn_stats_q8_finish_finalize(Q8FinishArg f, RbnFinalizeArg a) {
+    __shared__ float sm[6 * 32];
+    if ((int64_t)threadIdx.x < f.C) {
+        const QParams p = make_qparams_d((double)__ldg(f.q_range), (double)__ldg(f.q_range + 1), f.q_bits);
+        for (int64_t c = threadIdx.x; c < f.C; c += RF_THREADS) q8_finish_channel<16>(f, p, c);
+    }
+    rbn_finalize_body(f.red, f.C, a, sm);            // thread t reads back the red[] entries thread t wrote
+}
+
+__global__ void __launch_bounds__(RF_THREADS) k_rbn_finalize_after(const double* red, int64_t C, RbnFinalizeArg a) {
+    __shared__ float sm[6 * 32];
+    rbn_finalize_body(red, C, a, sm);
 }
 
 // merge the S segment partials of every (chunk k, channel c) and leave them in the generic kernel's output format
@@ -444,9 +491,9 @@ extern "C" size_t qb_rangebn_nhwc_ws_bytes(int64_t C, int num_chunks) {
 
 static size_t nhwc_smem(const NhwcGeom& g, int vec, int per_elem) { return (size_t)g.RL * g.CT * vec * per_elem; }
 
-extern "C" int qb_rangebn_stats_nhwc(const float* x, int64_t B, int64_t C, int64_t HW, int num_chunks, int32_t* amax,
-                                     int32_t* amin, int32_t* amax_kc, int32_t* amin_kc, double* red, const float* q_range,
-                                     int q_bits, uint8_t* x_codes_out, void* ws, size_t ws_bytes, void* stream) {
+static int stats_nhwc_impl(const float* x, int64_t B, int64_t C, int64_t HW, int num_chunks, int32_t* amax, int32_t* amin,
+                           int32_t* amax_kc, int32_t* amin_kc, double* red, const float* q_range, int q_bits, uint8_t* x_codes_out,
+                           void* ws, size_t ws_bytes, void* stream, const RbnFinalizeArg* fin) {
     QB_CHECK_ARG(!x_codes_out || (q_range && q_bits <= 8), "qb_rangebn_stats_nhwc: x_codes_out needs q_range and q_bits <= 8");
     QB_CHECK_ARG(!q_range || (q_bits >= 1 && q_bits <= 24), "qb_rangebn_stats_nhwc: q_bits=%d", q_bits);
     QB_CHECK_ARG(x && red && ws, "qb_rangebn_stats_nhwc: null pointer");
@@ -489,8 +536,9 @@ extern "C" int qb_rangebn_stats_nhwc(const float* x, int64_t B, int64_t C, int64
                 k_rbn_stats_q8_nhwc<<<grid8, NH_THREADS, (size_t)g8.RL * g8.CT * 8 * 12, st>>>(x, g8, nullptr, nullptr, nullptr, q_range,
                                                                                           q_bits, x_codes_out, acc_kc);
                 QB_LAUNCH_CHECK();
-                k_rbn_stats_q8_finish<<<(unsigned)((C + 127) / 128), 128, 0, st>>>(acc_kc, C, num_chunks, R / num_chunks, q_range, q_bits,
-                                                                                  amax, amin, amax_kc, amin_kc, red);
+                const Q8FinishArg f{acc_kc, C, R / num_chunks, num_chunks, q_range, q_bits, amax, amin, amax_kc, amin_kc, red};
+                if (fin) k_rbn_stats_q8_finish_finalize<<<1, RF_THREADS, 0, st>>>(f, *fin);
+                else k_rbn_stats_q8_finish<<<(unsigned)((C + 127) / 128), 128, 0, st>>>(f);
                 QB_LAUNCH_CHECK();
                 return QB_OK;
             }
@@ -503,6 +551,10 @@ extern "C" int qb_rangebn_stats_nhwc(const float* x, int64_t B, int64_t C, int64
             QB_LAUNCH_CHECK();
             k_rbn_stats_nhwc_pack<<<(unsigned)((C + 127) / 128), 128, 0, st>>>(cmax, cmin, csum, C, num_chunks, red);
             QB_LAUNCH_CHECK();
+            if (fin) {
+                k_rbn_finalize_after<<<1, RF_THREADS, 0, st>>>(red, C, *fin);
+                QB_LAUNCH_CHECK();
+            }
             return QB_OK;
         }
     }
@@ -521,7 +573,39 @@ extern "C" int qb_rangebn_stats_nhwc(const float* x, int64_t B, int64_t C, int64
     QB_LAUNCH_CHECK();
     k_rbn_stats_nhwc_pack<<<(unsigned)((C + 127) / 128), 128, 0, st>>>(cmax, cmin, csum, C, num_chunks, red);
     QB_LAUNCH_CHECK();
+    if (fin) {
+        k_rbn_finalize_after<<<1, RF_THREADS, 0, st>>>(red, C, *fin);
+        QB_LAUNCH_CHECK();
+    }
     return QB_OK;
+}
+
+extern "C" int qb_rangebn_stats_nhwc(const float* x, int64_t B, int64_t C, int64_t HW, int num_chunks, int32_t* amax,
+                                     int32_t* amin, int32_t* amax_kc, int32_t* amin_kc, double* red, const float* q_range,
+                                     int q_bits, uint8_t* x_codes_out, void* ws, size_t ws_bytes, void* stream) {
+    return stats_nhwc_impl(x, B, C, HW, num_chunks, amax, amin, amax_kc, amin_kc, red, q_range, q_bits, x_codes_out, ws, ws_bytes,
+                           stream, nullptr);
+}
+
+/* qb_rangebn_stats_nhwc followed by qb_rangebn_finalize(training = 1) on the same stream, with the finalize folded into the
+ * tail kernel of the statistics pass where that is a single CTA.  Same results as the two calls (same arithmetic, same
+ * order).  For the single-process case: across ranks `red` has to be exchanged between the two, so the calls stay apart. */
+extern "C" int qb_rangebn_stats_finalize_nhwc(const float* x, int64_t B, int64_t C, int64_t HW, int num_chunks, int32_t* amax,
+                                              int32_t* amin, int32_t* amax_kc, int32_t* amin_kc, double* red,
+                                              const float* q_range, int q_bits, uint8_t* x_codes_out, float eps, double momentum,
+                                              int bits, const float* gamma, const float* beta, float* running_mean,
+                                              float* running_var, float* mean, float* scale_raw, float* qscale, float* qgamma,
+                                              float* qbeta, void* ws, size_t ws_bytes, void* stream) {
+    QB_CHECK_ARG(running_mean && running_var && mean && scale_raw && qscale, "qb_rangebn_stats_finalize_nhwc: null pointer");
+    QB_CHECK_ARG((!gamma || qgamma) && (!beta || qbeta), "qb_rangebn_stats_finalize_nhwc: gamma/beta without output");
+    QB_CHECK_ARG(bits >= 1 && bits <= 24, "qb_rangebn_stats_finalize_nhwc: bits=%d", bits);
+    QB_CHECK_ARG(B > 0 && HW > 0 && num_chunks > 0 && (B * HW) / num_chunks > 1,
+                 "qb_rangebn_stats_finalize_nhwc: chunk length must exceed 1");
+    const double count = (double)B * (double)HW, chunk_len = count / num_chunks;
+    const RbnFinalizeArg a{(double)num_chunks, count, rbn_scale_fix(chunk_len), momentum, eps, 1, bits, gamma, beta,
+                           running_mean, running_var, mean, scale_raw, qscale, qgamma, qbeta};
+    return stats_nhwc_impl(x, B, C, HW, num_chunks, amax, amin, amax_kc, amin_kc, red, q_range, q_bits, x_codes_out, ws, ws_bytes,
+                           stream, &a);
 }
 
 // ---------------------------------------------------------------------------------------------------
@@ -838,7 +922,8 @@ k_rbn_bwd_reduce_nhwc(const float* __restrict__ gq, const float* __restrict__ x,
 }
 
 // one warp per channel: lanes stride over the segments, fixed-order shuffle tree => deterministic
-__global__ void k_rbn_bwd_pack_nhwc(const double* part, int64_t C, int S, double* sg, double* sgx) {
+template <bool COEFFS>
+__global__ void k_rbn_bwd_pack_nhwc(const double* part, int64_t C, int S, double* sg, double* sgx, RbnCoefArg ca) {
     const int64_t c = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
     const int lane = threadIdx.x & 31;
     if (c >= C) return;
@@ -847,7 +932,10 @@ __global__ void k_rbn_bwd_pack_nhwc(const double* part, int64_t C, int S, double
     for (int s = lane; s < S; s += 32) { a += part[(int64_t)s * C + c]; b += part[((int64_t)S + s) * C + c]; }
     a = warp_sum(a);
     b = warp_sum(b);
-    if (lane == 0) { sg[c] = a; sgx[c] = b; }
+    if (lane == 0) {
+        sg[c] = a; sgx[c] = b;
+        if (COEFFS) rbn_bwd_coeffs_channel(a, b, c, ca);                   // qb_rangebn_bwd_reduce_coeffs_nhwc: one launch less
+    }
 }
 
 extern "C" size_t qb_rangebn_bwd_nhwc_ws_bytes(int64_t C) { return C < 0 ? 0 : (size_t)C * NH_MAX_SEG_BWD * 16; }
@@ -865,12 +953,10 @@ static int grad_noise_mode(const float* g_range, const float* noise, int stochas
 
 /* g_range != NULL: g is the raw gradient, quantized on the fly to g_bits with this device range (needs C % 8 == 0 and
  * 32-byte aligned tensors); noise/stochastic/seed/offset/step_dev as in qb_fakequant_grad. */
-extern "C" int qb_rangebn_bwd_reduce_nhwc(const float* gq, const float* x, const uint8_t* x_codes, int64_t B, int64_t C,
-                                          int64_t HW, double* sg, double* sgx, const float* q_range, int q_bits,
-                                          const float* g_range, int g_bits,
-                                          const float* noise, int stochastic, uint64_t seed, uint64_t offset,
-                                          const uint64_t* step_dev, uint8_t* gq_codes_out, const uint8_t* relu_bits, void* ws,
-                                          size_t ws_bytes, void* stream) {
+static int bwd_reduce_nhwc_impl(const float* gq, const float* x, const uint8_t* x_codes, int64_t B, int64_t C, int64_t HW, double* sg,
+                                double* sgx, const float* q_range, int q_bits, const float* g_range, int g_bits, const float* noise,
+                                int stochastic, uint64_t seed, uint64_t offset, const uint64_t* step_dev, uint8_t* gq_codes_out,
+                                const uint8_t* relu_bits, void* ws, size_t ws_bytes, void* stream, const RbnCoefArg* ca) {
     QB_CHECK_ARG(gq && (x || x_codes) && sg && sgx && ws, "qb_rangebn_bwd_reduce_nhwc: null pointer");
     QB_CHECK_ARG(!x_codes || (q_range && q_bits <= 8 && C % 8 == 0 && (reinterpret_cast<uintptr_t>(x_codes) & 7) == 0),
                  "qb_rangebn_bwd_reduce_nhwc: x_codes needs q_range, q_bits <= 8, C %% 8 == 0 and 8-byte alignment");
@@ -923,9 +1009,39 @@ extern "C" int qb_rangebn_bwd_reduce_nhwc(const float* gq, const float* x, const
         else launch_bwd_reduce<1, 0, -1>(grid, nhwc_smem(g, 1, 16), st, gq, x, nullptr, g, part, q_range, q_bits, ga);
     }
     QB_LAUNCH_CHECK();
-    k_rbn_bwd_pack_nhwc<<<(unsigned)((C * 32 + 127) / 128), 128, 0, st>>>(part, C, g.S, sg, sgx);
+    if (ca) k_rbn_bwd_pack_nhwc<true><<<(unsigned)((C * 32 + 127) / 128), 128, 0, st>>>(part, C, g.S, sg, sgx, *ca);
+    else k_rbn_bwd_pack_nhwc<false><<<(unsigned)((C * 32 + 127) / 128), 128, 0, st>>>(part, C, g.S, sg, sgx, RbnCoefArg{});
     QB_LAUNCH_CHECK();
     return QB_OK;
+}
+
+extern "C" int qb_rangebn_bwd_reduce_nhwc(const float* gq, const float* x, const uint8_t* x_codes, int64_t B, int64_t C,
+                                          int64_t HW, double* sg, double* sgx, const float* q_range, int q_bits,
+                                          const float* g_range, int g_bits,
+                                          const float* noise, int stochastic, uint64_t seed, uint64_t offset,
+                                          const uint64_t* step_dev, uint8_t* gq_codes_out, const uint8_t* relu_bits, void* ws,
+                                          size_t ws_bytes, void* stream) {
+    return bwd_reduce_nhwc_impl(gq, x, x_codes, B, C, HW, sg, sgx, q_range, q_bits, g_range, g_bits, noise, stochastic, seed, offset,
+                                step_dev, gq_codes_out, relu_bits, ws, ws_bytes, stream, nullptr);
+}
+
+/* qb_rangebn_bwd_reduce_nhwc followed by qb_rangebn_bwd_coeffs on the same stream in one call: the warp that folds a channel's
+ * partial sums also derives its coefficients (same arithmetic).  Single-process use - across ranks the sums are exchanged
+ * between the two calls. */
+extern "C" int qb_rangebn_bwd_reduce_coeffs_nhwc(const float* gq, const float* x, const uint8_t* x_codes, int64_t B, int64_t C,
+                                                 int64_t HW, double* sg, double* sgx, const float* q_range, int q_bits,
+                                                 const float* g_range, int g_bits, const float* noise, int stochastic,
+                                                 uint64_t seed, uint64_t offset, const uint64_t* step_dev, uint8_t* gq_codes_out,
+                                                 const uint8_t* relu_bits, int num_chunks, double count, double chunk_len,
+                                                 int training, const float* mean, const float* scale_raw, const float* qscale,
+                                                 const float* qgamma, float* dgamma, float* dbeta, float* coef_a, float* coef_e,
+                                                 void* ws, size_t ws_bytes, void* stream) {
+    QB_CHECK_ARG(mean && scale_raw && qscale && coef_a && coef_e, "qb_rangebn_bwd_reduce_coeffs_nhwc: null pointer");
+    QB_CHECK_ARG(!training || (num_chunks > 0 && count > 0 && chunk_len > 1), "qb_rangebn_bwd_reduce_coeffs_nhwc: bad chunking");
+    const RbnCoefArg a{(double)num_chunks, count, training ? rbn_scale_fix(chunk_len) : 0.0, training, mean, scale_raw, qscale, qgamma,
+                       dgamma, dbeta, coef_a, coef_e};
+    return bwd_reduce_nhwc_impl(gq, x, x_codes, B, C, HW, sg, sgx, q_range, q_bits, g_range, g_bits, noise, stochastic, seed, offset,
+                                step_dev, gq_codes_out, relu_bits, ws, ws_bytes, stream, &a);
 }
 
 // scatter: flat (b,h,w) index == row index in channels-last

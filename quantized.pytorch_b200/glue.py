@@ -107,6 +107,64 @@ class MaxPool2d(nn.MaxPool2d):
         return out
 
 
+class _AvgPoolFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, x, k):
+        ctx.geom = (tuple(x.shape), k)
+        return _abi.avgpool2d_nhwc_fwd(x, k)
+
+    @staticmethod
+    def backward(ctx, g):
+        shape, k = ctx.geom
+        g = _abi._f32c(g, "grad")
+        if not g.is_contiguous(memory_format=torch.channels_last):
+            g = g.contiguous(memory_format=torch.channels_last)
+        return _abi.avgpool2d_nhwc_bwd(g, shape, k), None
+
+
+class AvgPool2d(nn.AvgPool2d):
+    """torch.nn.AvgPool2d (models/resnet_quantized.py:153, models/mobilenet_quantized.py:114) whose channels-last CUDA path
+    runs on libqb200 for the geometry those models use: stride == kernel, no padding, floor mode."""
+
+    def forward(self, x):
+        k, s = self.kernel_size, self.stride
+        if (isinstance(k, int) and s == k and self.padding == 0 and not self.ceil_mode and self.divisor_override is None
+                and x.is_cuda and x.dtype == torch.float32 and x.dim() == 4 and x.shape[1] % 4 == 0
+                and x.is_contiguous(memory_format=torch.channels_last) and x.shape[2] >= k and x.shape[3] >= k
+                and x.data_ptr() % 16 == 0):
+            return _AvgPoolFn.apply(x, k)
+        return super().forward(x)
+
+
+class _CrossEntropyFn(torch.autograd.Function):
+    @staticmethod
+    def forward(ctx, logits, target, ignore_index):
+        loss, row_state, n_valid = _abi.cross_entropy_fwd(logits, target, ignore_index)
+        ctx.save_for_backward(logits, target, row_state, n_valid)
+        ctx.ignore_index = ignore_index
+        return loss
+
+    @staticmethod
+    def backward(ctx, g):
+        logits, target, row_state, n_valid = ctx.saved_tensors
+        g = g.to(torch.float32).contiguous()
+        return _abi.cross_entropy_bwd(logits, target, row_state, n_valid, g, ctx.ignore_index), None, None
+
+
+class CrossEntropyLoss(nn.CrossEntropyLoss):
+    """torch.nn.CrossEntropyLoss as the reference's training loop uses it (main.py:362: ``criterion(output, target)`` with class
+    index targets, mean reduction): forward and backward are one pass each over the logits on libqb200, the [B, C]
+    log-softmax is never stored.  Any other configuration (class weights, label smoothing, probabilities as targets, other
+    reductions, non-CUDA tensors) takes torch's own path."""
+
+    def forward(self, input, target):
+        if (input.is_cuda and input.dtype == torch.float32 and input.dim() == 2 and input.is_contiguous()
+                and target.dtype == torch.int64 and target.dim() == 1 and target.is_contiguous() and self.weight is None
+                and self.reduction == "mean" and self.label_smoothing == 0.0):
+            return _CrossEntropyFn.apply(input, target, self.ignore_index)
+        return super().forward(input, target)
+
+
 def _relu_backward(g, out):
     """aten::threshold_backward(g, out, 0); on dense fp32 CUDA tensors of one layout the native pass also leaves the
     range of the result for the gradient quantizer that consumes it (RangeBN / QConv2d backward)."""

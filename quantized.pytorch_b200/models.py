@@ -41,6 +41,14 @@ def _maxpool(q):
     return nn.MaxPool2d
 
 
+def _avgpool(q):
+    """nn.AvgPool2d (resnet_quantized.py:153, mobilenet_quantized.py:114); native module set: glue.AvgPool2d, same values."""
+    if getattr(q, "NATIVE_GLUE", False):
+        from . import glue
+        return glue.AvgPool2d
+    return nn.AvgPool2d
+
+
 def _relu(q, inplace=True):
     """nn.ReLU(inplace=True) (resnet_quantized.py:47,147) / nn.ReLU() (mobilenet_quantized.py:38-50); native module set:
     glue.ReLU (same values, plus the statistics the next quantized layer needs)."""
@@ -149,7 +157,7 @@ class QResNet(nn.Module):
             else:
                 layer = _Identity()
             setattr(self, "layer%d" % (i + 1), layer)
-        self.avgpool = nn.AvgPool2d(pool)
+        self.avgpool = _avgpool(q)(pool)
         self.fc = q.QLinear(self.inplanes, num_classes, **BITS)
         self.weight_decay = weight_decay
         self._init()
@@ -265,7 +273,7 @@ class QMobileNet(nn.Module):
         layers = [_qconv(q, 3, c(32), 3, 2, 1), _qbn(q, c(32)), _relu(q, True)]
         layers += [_DWSeparable(q, c(a), c(b), s) for a, b, s in plan]
         self.features = nn.Sequential(*layers)
-        self.avg_pool = nn.AvgPool2d(7)
+        self.avg_pool = _avgpool(q)(7)
         self.fc = q.QLinear(c(1024), num_classes, **BITS)
         self.regime = [{"epoch": 0, "optimizer": "SGD", "lr": 1e-1, "momentum": 0.9},
                        {"epoch": 30, "lr": 1e-2}, {"epoch": 60, "lr": 1e-3}, {"epoch": 80, "lr": 1e-4}]

@@ -13,6 +13,7 @@ Differences that are deliberate and documented in DESIGN.md:
   * stochastic-rounding noise comes from Philox4x32-7 inside the kernel (torch's CPU mt19937 stream cannot
     be reproduced on a GPU); ``set_noise_provider`` injects a recorded noise tensor for parity tests.
 """
+import os
 import itertools
 import math
 
@@ -596,7 +597,12 @@ USE_NATIVE_BACKWARD = True    # dX / dW / db of the dense contractions on conv_b
 # the library.
 ALLOW_LIBRARY_FALLBACK = False
 USE_STEM_KERNEL = True
-STEM_NCHW_DIRECT = True       # first layer: quantize the NCHW image batch straight into channels-last codes (no fp32 layout copy)
+FUSE_QUANT_ROWSUM = os.environ.get("QB_FUSE_ROWSUM", "1") != "0"      # conv input quantizer also emits the per-pixel code sums (qb_fakequant_affine_rowsum)
+# one process: RangeBN statistics + per-channel finalize in one call (qb_rangebn_stats_finalize_nhwc).  Off by default: measured
+# 0.3 % SLOWER per training step than the two launches (profiles/ab_fusions_r02r.txt) - the single CTA serialises the fold of
+# the chunk accumulators and the finalize, two small kernels overlap their tails inside the CUDA graph
+FUSE_RANGEBN_FINALIZE = os.environ.get("QB_FUSE_RBN_FINALIZE", "0") == "1"
+STEM_NCHW_DIRECT = os.environ.get("QB_STEM_NCHW", "1") != "0"       # first layer: quantize the NCHW image batch straight into channels-last codes (no fp32 layout copy)
 USE_DW_KERNEL = True       # depthwise 3x3 convs on the codes (conv_dw.cu); False: F.conv2d on the fake-quantized tensors
 
 
@@ -687,7 +693,15 @@ class _QTensorCoreFn(Function):
         want_x16 = native_bwd and ctx.needs_input_grad[1]
         x16 = torch.empty_like(x, dtype=torch.bfloat16) if want_x16 else None
         q2 = getattr(mod, "_q2_params", None)        # quantize2 flavour: (zero_point, range) device tensors of its quantizer
-        if nchw_stem:
+        want_y = need_bwd and not stem_bwd and not native_bwd
+        pixsum = None
+        if (conv and FUSE_QUANT_ROWSUM and q2 is None and not want_y and not nchw_stem and mod.groups == 1 and x.shape[1] % 16 == 0
+                and x.is_contiguous(memory_format=torch.channels_last) and x.data_ptr() % 32 == 0
+                and _abi.fakequant_affine_rowsum_supported(x.shape[1], bits_a)):
+            # the per-pixel code sums of the zero-point correction come out of the quantizer's registers
+            xq = None
+            pixsum = _abi.fakequant_affine_rowsum(x, x.numel() // x.shape[1], x.shape[1], bits_a, rng, codes, x16)
+        elif nchw_stem:
             if q2 is not None or (need_bwd and not stem_bwd):
                 raise _abi.QB200Error("first-layer NCHW path entered with a backward that needs x_hat")
             xq, codes = None, _abi.fakequant_affine_nchw3(x, bits_a, rng)
@@ -714,7 +728,8 @@ class _QTensorCoreFn(Function):
                                          _pair(mod.padding)[0], rng, bits_a, mod.weight_min, mod.weight_max, bits_w, tapsum,
                                          bias=qbias)
             else:
-                pixsum = _abi.rowsum_u8(codes, B * H * W, Cin)
+                if pixsum is None:
+                    pixsum = _abi.rowsum_u8(codes, B * H * W, Cin)
                 stats = torch.empty(8, dtype=torch.float64, device=x.device) if mod.training else None
                 out = _abi.conv_i8_fwd(codes, wcodes, B, H, W, Cin, mod.out_channels, kh, kw, _pair(mod.stride)[0],
                                        _pair(mod.padding)[0], rng, bits_a, mod.weight_min, mod.weight_max, bits_w, pixsum,
@@ -921,7 +936,7 @@ class _RangeBNFn(Function):
         B, Cn = xq.shape[0], xq.shape[1]
         HW = xq.numel() // (B * Cn)
         count, chunk_len, chunks_global = float(B * HW), 0.0, num_chunks
-        red = amax = amin = xc = None
+        red = amax = amin = xc = vec = None
         ctx.local_chunks = num_chunks
         if training:
             local_chunks = num_chunks
@@ -933,14 +948,22 @@ class _RangeBNFn(Function):
                 # x_hat leaves the statistics pass as uint8 codes: apply and backward read 1 B/elem, the raw conv output
                 # is not kept for backward
                 xc = torch.empty(xq.numel(), dtype=torch.uint8, device=xq.device)
-            red, amax, amin = _abi.rangebn_stats(xq, B, Cn, HW, local_chunks, want_arg=want_arg, nhwc=nhwc,
-                                                 q_range=q_range, q_bits=q_bits, x_codes_out=xc)
-            if _reducer is not None:
-                _reducer.rangebn(red)
             chunk_len = count / chunks_global
             ctx.local_chunks = local_chunks
-        vec = _abi.rangebn_finalize(red, Cn, chunks_global, count, chunk_len, eps, momentum, training, bits, gamma, beta,
-                                    running_mean, running_var)
+            if nhwc and _reducer is None and FUSE_RANGEBN_FINALIZE and chunk_len > 1:
+                # one process: nothing to exchange between the statistics and the per-channel finalize - one call, and the
+                # finalize rides at the tail of the statistics pass' last kernel
+                vec, amax, amin = _abi.rangebn_stats_finalize_nhwc(xq, B, Cn, HW, num_chunks, eps, momentum, bits, gamma, beta,
+                                                                   running_mean, running_var, want_arg=want_arg,
+                                                                   q_range=q_range, q_bits=q_bits, x_codes_out=xc)
+            else:
+                red, amax, amin = _abi.rangebn_stats(xq, B, Cn, HW, local_chunks, want_arg=want_arg, nhwc=nhwc,
+                                                     q_range=q_range, q_bits=q_bits, x_codes_out=xc)
+                if _reducer is not None:
+                    _reducer.rangebn(red)
+        if vec is None:
+            vec = _abi.rangebn_finalize(red, Cn, chunks_global, count, chunk_len, eps, momentum, training, bits, gamma, beta,
+                                        running_mean, running_var)
         ctx.dims = (B, Cn, HW, chunks_global, count, chunk_len, training, bits_grad, gamma is not None, beta is not None)
         ctx.nhwc, ctx.q_bits = nhwc, q_bits
         ctx.save_for_backward(None if xc is not None else xq, vec, amax, amin, q_range, xc)

@@ -207,6 +207,55 @@ def test_first_layer_quantizer_reads_nchw(lib, shape):
         lib._run("qb_fakequant_affine_nchw3", 0, x.data_ptr(), want.data_ptr(), 2, 63, 8, rng.data_ptr(), None)
 
 
+@pytest.mark.parametrize("rows,cols", [(7, 16), (33, 32), (1000, 64), (12544, 64), (3001, 128), (777, 256), (200704, 64)])
+def test_quantizer_with_row_sums(lib, rows, cols):
+    """qb_fakequant_affine_rowsum: codes, bf16 codes and per-row code sums in one pass == qb_fakequant_affine16 + qb_rowsum_u8
+    (bit-exact); row counts that leave a partial last warp included."""
+    gen = torch.Generator().manual_seed(rows + cols)
+    x = (torch.randn(rows, cols, generator=gen) * 1.3 + 0.2).to(DEV)
+    rng = torch.tensor([float(x.min()) * 0.85, float(x.max()) * 0.9], device=DEV)
+    for bits in (8, 4):
+        assert lib.fakequant_affine_rowsum_supported(cols, bits)
+        want_c = torch.empty(rows, cols, dtype=torch.uint8, device=DEV)
+        want_h = torch.empty(rows, cols, dtype=torch.bfloat16, device=DEV)
+        lib.fakequant_affine(x, bits, range_dev=rng, codes=want_c, codes16=want_h, want_y=False)
+        want_s = lib.rowsum_u8(want_c, rows, cols)
+        for with16 in (True, False):
+            got_c = torch.zeros(rows, cols, dtype=torch.uint8, device=DEV)
+            got_h = torch.zeros(rows, cols, dtype=torch.bfloat16, device=DEV) if with16 else None
+            got_s = lib.fakequant_affine_rowsum(x, rows, cols, bits, rng, got_c, got_h)
+            assert torch.equal(got_c, want_c) and torch.equal(got_s, want_s)
+            assert not with16 or torch.equal(got_h, want_h)
+            assert int(got_s.sum()) == int(want_c.sum(dtype=torch.int64))
+    assert not lib.fakequant_affine_rowsum_supported(512, 8) and not lib.fakequant_affine_rowsum_supported(48, 8)
+    with pytest.raises(lib.QB200Error):
+        lib.fakequant_affine_rowsum(x[:, :8].contiguous(), rows, 8, 8, rng, got_c)
+
+
+def test_qconv2d_quantizer_row_sum_route(lib):
+    """QConv2d on the fused quantizer + row-sum route gives bit-identical output and gradients to the two-call route."""
+    import qtorch_b200  # noqa: F401
+    from qtorch_b200 import quantize as Q
+    x = torch.randn(8, 64, 14, 14, device=DEV).contiguous(memory_format=torch.channels_last)
+    outs = []
+    for fused in (True, False):
+        torch.manual_seed(3)
+        m = Q.QConv2d(64, 128, 3, 1, 1, bias=False, num_bits=8, num_bits_weight=8, num_bits_grad=None).to(DEV)
+        xi = x.clone().requires_grad_()
+        Q.FUSE_QUANT_ROWSUM = fused
+        try:
+            lib.profile_begin()
+            y = m(xi)
+            names = [r[0] for r in lib.profile_end()]
+            y.square().mean().backward()
+        finally:
+            Q.FUSE_QUANT_ROWSUM = True
+        assert ("qb_fakequant_affine_rowsum" in names) == fused and ("qb_rowsum_u8" in names) != fused, names
+        outs.append((y.detach(), xi.grad.clone(), m.weight.grad.clone()))
+    for a, b in zip(*outs):
+        assert torch.equal(a, b)
+
+
 WGRAD_CASES = [  # B, Cin, H, W, Cout, k, stride, pad
     (4, 3, 224, 224, 64, 7, 2, 3),       # ResNet conv1 (more tiles than SMs: several tiles per CTA)
     (2, 3, 61, 45, 64, 7, 2, 3),         # ragged tiles

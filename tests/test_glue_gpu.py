@@ -331,3 +331,61 @@ def test_fused_sgd_matches_torch_bitwise(lib):
             for a, b in zip(pa, pb):
                 assert torch.equal(oa.state[a]["momentum_buffer"], ob.state[b]["momentum_buffer"])
         assert sorted(oa.state_dict()["state"].keys()) == sorted(ob.state_dict()["state"].keys())
+
+
+@pytest.mark.parametrize("shape,k", [((256, 512, 7, 7), 7), ((16, 1024, 7, 7), 7), ((8, 64, 8, 8), 2), ((4, 32, 9, 10), 3), ((2, 8, 4, 4), 4)])
+def test_avgpool_matches_torch(lib, shape, k):
+    """glue.AvgPool2d (qb_avgpool2d_nhwc_fwd/_bwd) against torch.nn.AvgPool2d on the same channels-last tensor: forward within
+    1 ulp (same raster-order sum, one division), backward bit-exact; ragged borders (floor mode) get zero gradient."""
+    import torch.nn as nn
+    from qtorch_b200 import glue
+    gen = torch.Generator().manual_seed(1)
+    x = torch.randn(shape, generator=gen).to(DEV).contiguous(memory_format=torch.channels_last)
+    xa, xb = x.clone().requires_grad_(), x.clone().requires_grad_()
+    lib.profile_begin()
+    ya = glue.AvgPool2d(k)(xa)
+    names = [r[0] for r in lib.profile_end()]
+    assert "qb_avgpool2d_nhwc_fwd" in names
+    yb = nn.AvgPool2d(k)(xb)
+    assert ya.shape == yb.shape and ya.is_contiguous(memory_format=torch.channels_last)
+    assert float((ya - yb).abs().max()) <= 1.2e-7 * float(yb.abs().max())
+    g = torch.randn(yb.shape, generator=gen).to(DEV)
+    ya.backward(g)
+    yb.backward(g)
+    assert torch.equal(xa.grad, xb.grad)
+    # other geometries keep torch's path
+    z = glue.AvgPool2d(3, stride=2, padding=1)(x)
+    assert torch.equal(z, nn.AvgPool2d(3, stride=2, padding=1)(x))
+
+
+@pytest.mark.parametrize("B,C", [(256, 1000), (16, 10), (37, 1001), (5, 7), (1024, 32)])
+def test_cross_entropy_matches_torch(lib, B, C):
+    """glue.CrossEntropyLoss (qb_cross_entropy_fwd/_bwd) against torch.nn.CrossEntropyLoss on CUDA: loss to 2e-7 relative,
+    gradient to 1e-6 of its largest entry (same log-softmax recipe; the row sum is the only reordering); ignore_index rows
+    contribute nothing and are not counted; an upstream gradient scales the result."""
+    import torch.nn as nn
+    from qtorch_b200 import glue
+    gen = torch.Generator().manual_seed(B + C)
+    logits = (torch.randn(B, C, generator=gen) * 3).to(DEV)
+    target = torch.randint(0, C, (B,), generator=gen).to(DEV)
+    for ignore in (False, True):
+        t = target.clone()
+        if ignore:
+            t[::3] = -100
+        la, lb = logits.clone().requires_grad_(), logits.clone().requires_grad_()
+        lib.profile_begin()
+        a = glue.CrossEntropyLoss()(la, t)
+        names = [r[0] for r in lib.profile_end()]
+        assert "qb_cross_entropy_fwd" in names
+        b = nn.CrossEntropyLoss()(lb, t)
+        assert a.shape == b.shape == ()
+        assert abs(float(a) - float(b)) <= 2e-7 * abs(float(b)) + 1e-7
+        (a * 1.7).backward()
+        (b * 1.7).backward()
+        assert float((la.grad - lb.grad).abs().max()) <= 1e-6 * float(lb.grad.abs().max())
+        if ignore:
+            assert float(la.grad[::3].abs().max()) == 0.0
+    # configurations outside the reference's use take torch's path and give torch's answer
+    w = torch.rand(C, generator=gen).to(DEV)
+    assert torch.equal(glue.CrossEntropyLoss(weight=w)(logits, target), nn.CrossEntropyLoss(weight=w)(logits, target))
+    assert torch.equal(glue.CrossEntropyLoss(reduction="sum")(logits, target), nn.CrossEntropyLoss(reduction="sum")(logits, target))

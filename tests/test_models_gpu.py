@@ -67,7 +67,8 @@ def test_benchmarked_model_train_step_vs_oracle(name):
     mod.load_state_dict(ref.state_dict())
     mod = mod.to(DEV).train()
     x, y = seeding.synthetic_batch((16, 3, 224, 224), 1000, seed=5)
-    crit = torch.nn.CrossEntropyLoss()
+    from qtorch_b200 import glue
+    crit = glue.CrossEntropyLoss()            # CUDA logits: libqb200; the oracle's CPU logits: torch's own path
     first = {}
     if name == "resnet18":
         ref.bn1.register_forward_hook(lambda m, i, o: first.__setitem__("ref", o.detach().clone()))

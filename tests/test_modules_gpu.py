@@ -411,3 +411,73 @@ def test_rangebn_code_handoff_bit_exact(lib, shape):
     want = torch.empty(x.numel(), dtype=torch.uint8, device=DEV)
     lib.fakequant_affine(x, 8, range_dev=qr, codes=want, want_y=False)
     assert torch.equal(b[8], want)
+
+
+@pytest.mark.parametrize("shape,quant,codes", [((16, 64, 8, 8), True, True), ((32, 16, 7, 7), True, True), ((8, 128, 12, 12), True, False),
+                                               ((8, 6, 6, 8), False, False), ((4, 2048, 4, 4), True, True),
+                                               ((256, 64, 28, 28), True, True)])
+def test_rangebn_stats_finalize_one_call(lib, shape, quant, codes):
+    """qb_rangebn_stats_finalize_nhwc == qb_rangebn_stats_nhwc + qb_rangebn_finalize, bit for bit (vectors, running buffers,
+    arg tables, codes), on the integer-atomic path (finalize at the tail of the finish kernel), the segment-merge path and the
+    generic path; called twice in a row so the self-resetting accumulators are exercised."""
+    B, C, H, W = shape
+    HW, K = H * W, 16
+    gen = torch.Generator().manual_seed(3)
+    x = (torch.randn(shape, generator=gen) * 2 + 0.3).to(DEV).contiguous(memory_format=torch.channels_last)
+    gamma, beta = (torch.rand(C, generator=gen) + 0.5).to(DEV), torch.randn(C, generator=gen).to(DEV)
+    qr = torch.tensor([float(x.min()) * 0.9, float(x.max()) * 0.8], device=DEV) if quant else None
+    res = []
+    for fused in (False, True, True):
+        xc = torch.empty(x.numel(), dtype=torch.uint8, device=DEV) if codes else None
+        rm, rv = torch.full((C,), 0.25, device=DEV), torch.full((C,), 1.5, device=DEV)
+        if fused:
+            vec, amax, amin = lib.rangebn_stats_finalize_nhwc(x, B, C, HW, K, 1e-5, 0.1, 8, gamma, beta, rm, rv, q_range=qr,
+                                                              q_bits=8, x_codes_out=xc)
+        else:
+            red, amax, amin = lib.rangebn_stats(x, B, C, HW, K, nhwc=True, q_range=qr, q_bits=8, x_codes_out=xc)
+            vec = lib.rangebn_finalize(red, C, K, B * HW, B * HW / K, 1e-5, 0.1, True, 8, gamma, beta, rm, rv)
+        res.append((vec, amax, amin, rm, rv) + ((xc,) if codes else ()))
+    for other in res[1:]:
+        for a, b in zip(res[0], other):
+            assert torch.equal(a, b)
+    # no gamma / beta, no arg tables (inference-style call)
+    rm, rv = torch.zeros(C, device=DEV), torch.zeros(C, device=DEV)
+    vec, amax, amin = lib.rangebn_stats_finalize_nhwc(x, B, C, HW, K, 1e-5, 0.1, 8, None, None, rm, rv, want_arg=False,
+                                                      q_range=qr, q_bits=8)
+    red, _, _ = lib.rangebn_stats(x, B, C, HW, K, nhwc=True, q_range=qr, q_bits=8, want_arg=False)
+    rm2, rv2 = torch.zeros(C, device=DEV), torch.zeros(C, device=DEV)
+    vec2 = lib.rangebn_finalize(red, C, K, B * HW, B * HW / K, 1e-5, 0.1, True, 8, None, None, rm2, rv2)
+    assert amax is None and torch.equal(vec[:3], vec2[:3]) and torch.equal(rm, rm2) and torch.equal(rv, rv2)
+
+
+@pytest.mark.parametrize("shape,fusedq", [((16, 64, 8, 8), True), ((8, 6, 6, 8), False), ((64, 128, 14, 14), True)])
+def test_rangebn_backward_reduce_coeffs_one_call(lib, shape, fusedq):
+    """qb_rangebn_bwd_reduce_coeffs_nhwc == qb_rangebn_bwd_reduce_nhwc + qb_rangebn_bwd_coeffs, bit for bit (dx, dgamma, dbeta),
+    with and without the fused gradient quantizer / code hand-off."""
+    B, C, H, W = shape
+    HW, K = H * W, 16
+    gen = torch.Generator().manual_seed(9)
+    x = (torch.randn(shape, generator=gen) * 2 + 0.3).to(DEV).contiguous(memory_format=torch.channels_last)
+    g = (torch.randn(shape, generator=gen) * 1e-3).to(DEV).contiguous(memory_format=torch.channels_last)
+    noise = (torch.rand(shape, generator=gen) - 0.5).to(DEV).contiguous(memory_format=torch.channels_last)
+    gamma, beta = (torch.rand(C, generator=gen) + 0.5).to(DEV), torch.randn(C, generator=gen).to(DEV)
+    qr = torch.tensor([float(x.min()) * 0.9, float(x.max()) * 0.8], device=DEV) if fusedq else None
+    xc = torch.empty(x.numel(), dtype=torch.uint8, device=DEV) if fusedq else None
+    rm, rv = torch.zeros(C, device=DEV), torch.zeros(C, device=DEV)
+    red, amax, amin = lib.rangebn_stats(x, B, C, HW, K, nhwc=True, q_range=qr, q_bits=8, x_codes_out=xc)
+    vec = lib.rangebn_finalize(red, C, K, B * HW, B * HW / K, 1e-5, 0.1, True, 8, gamma, beta, rm, rv)
+    gq = dict(range=lib.minmax(g), bits=8, noise=noise, stochastic=True, seed=0, step_dev=None) if fusedq else None
+    res = []
+    for one_call in (False, True):
+        lib.FUSE_RANGEBN_COEFFS = one_call
+        try:
+            lib.profile_begin()
+            out = lib.rangebn_backward(g, None if fusedq else x, B, C, HW, K, B * HW, B * HW / K, True, vec, True, amax, amin,
+                                       nhwc=True, q_range=qr, q_bits=8, grad_quant=gq, want_dx_range=fusedq, x_codes=xc)
+            names = [r[0] for r in lib.profile_end()]
+        finally:
+            lib.FUSE_RANGEBN_COEFFS = True
+        assert ("qb_rangebn_bwd_reduce_coeffs_nhwc" in names) == one_call and ("qb_rangebn_bwd_coeffs" in names) != one_call
+        res.append([t.clone() for t in out])
+    for a, b in zip(*res):
+        assert torch.equal(a, b)

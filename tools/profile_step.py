@@ -18,7 +18,8 @@ def main():
     model = (models.mobilenet_quantized(Q) if name == "mobilenet" else models.resnet_quantized(Q, depth=18, dataset="imagenet"))
     model = model.to(dev).train()
     opt = torch.optim.SGD(model.parameters(), lr=0.1, momentum=0.9)
-    crit = torch.nn.CrossEntropyLoss()
+    from qtorch_b200 import glue
+    crit = glue.CrossEntropyLoss()
     x = torch.randn(batch, 3, 224, 224, device=dev)
     y = torch.randint(0, 1000, (batch,), device=dev)
 
