@@ -41,6 +41,20 @@ def _maxpool(q):
     return nn.MaxPool2d
 
 
+def _prepare_weights(model, x):
+    """Native module set on CUDA: every layer's weight kernels are issued on a side stream now (quantize.prepare_weights)."""
+    if model._native_glue and x.is_cuda:
+        from . import quantize as Q
+        Q.prepare_weights(model)
+
+
+def _join_prepared(model, out):
+    if model._native_glue and out.is_cuda:
+        from . import quantize as Q
+        Q.join_prepared(out.device)
+    return out
+
+
 def _avgpool(q):
     """nn.AvgPool2d (resnet_quantized.py:153, mobilenet_quantized.py:114); native module set: glue.AvgPool2d, same values."""
     if getattr(q, "NATIVE_GLUE", False):
@@ -188,6 +202,7 @@ class QResNet(nn.Module):
         self.fc.bias.data.zero_()
 
     def forward(self, x):
+        _prepare_weights(self, x)
         x = self.bn1(self.conv1(x))
         if hasattr(self.maxpool, "relu_pool"):         # native glue: pool first, ReLU on the 4x smaller result (same values)
             x = self.maxpool.relu_pool(x, self.relu)
@@ -195,7 +210,7 @@ class QResNet(nn.Module):
             x = self.maxpool(self.relu(x))
         x = self.layer4(self.layer3(self.layer2(self.layer1(x))))
         x = self.avgpool(x)
-        return self.fc(x.view(x.size(0), -1))
+        return _join_prepared(self, self.fc(x.view(x.size(0), -1)))
 
     def regularization(self):
         """resnet_quantized.py:157-165: 0.5*wd*sum(w^2) over conv/linear weights and biases (native module set: one
@@ -290,11 +305,12 @@ class QMobileNet(nn.Module):
 
     def forward(self, x):
         f = self.features
+        _prepare_weights(self, x)
         x = _bn_relu(f[1], f[2], f[0](x))
         for i in range(3, len(f)):
             x = f[i](x)
         x = self.avg_pool(x)
-        return self.fc(x.view(x.size(0), -1))
+        return _join_prepared(self, self.fc(x.view(x.size(0), -1)))
 
     def regularization(self, weight_decay=4e-5):
         if self._native_glue and next(self.parameters()).is_cuda:

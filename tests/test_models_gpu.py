@@ -156,3 +156,41 @@ def test_benchmarked_model_train_step_vs_oracle(name):
     assert cos > min_cos
     for p in mod.parameters():
         assert p.grad is not None and torch.isfinite(p.grad).all()
+
+
+def test_weight_preparation_aside_changes_nothing():
+    """quantize.prepare_weights (every layer's weight kernels issued on a side stream at the top of the model's forward) against the
+    in-line preparation: same Philox seed, same data -> bit-identical losses and parameters after 4 steps, in training and in
+    evaluation, and the prepared entries are actually consumed."""
+    import qtorch_b200  # noqa: F401
+    from qtorch_b200 import glue, models, quantize as Q
+    gen = torch.Generator().manual_seed(5)
+    x = torch.randn(32, 3, 32, 32, generator=gen).to(DEV)
+    y = torch.randint(0, 10, (32,), generator=gen).to(DEV)
+    runs = []
+    for aside in (True, False):
+        Q.PREP_WEIGHTS_ASIDE = aside
+        try:
+            torch.manual_seed(3)
+            m = models.resnet_quantized(Q, depth=20, dataset="cifar10").to(DEV).train()
+            opt = glue.SGD(m.parameters(), lr=0.05, momentum=0.9)
+            crit = glue.CrossEntropyLoss()
+            Q.manual_seed(17)
+            losses = []
+            for step in range(4):
+                loss = crit(m(x), y) + m.regularization()
+                if aside and step > 0:
+                    assert all("_prepped" not in mod.__dict__ for mod in m.modules()), "a prepared weight was not consumed"
+                opt.zero_grad()
+                loss.backward()
+                opt.step()
+                losses.append(float(loss))
+            m.eval()
+            with torch.no_grad():
+                out = m(x) + m(x)
+            runs.append((losses, [p.detach().clone() for p in m.parameters()], [b.detach().clone() for b in m.buffers()], out))
+        finally:
+            Q.PREP_WEIGHTS_ASIDE = False
+    assert runs[0][0] == runs[1][0], (runs[0][0], runs[1][0])
+    for a, b in zip(runs[0][1] + runs[0][2] + [runs[0][3]], runs[1][1] + runs[1][2] + [runs[1][3]]):
+        assert torch.equal(a, b)
