@@ -52,7 +52,7 @@ __device__ __forceinline__ float4 apply_quad(uint32_t word, const AffineQ& aq, c
     float4 o;
     float t;
 #define QB_APPLY_ONE(dst, sh, f)                                                              \
-    t = __fmul_rn(__fsub_rn(q_affine_deq((float)((word >> sh) & 0xffu), aq.p), mu.f), sc.f);    \
+    t = __fmul_rn(__fsub_rn(q_affine_deq(code_byte_to_float<sh / 8>(word), aq.p), mu.f), sc.f);  \
     if (has_g) t = __fmul_rn(t, gm.f);                                                          \
     if (has_b) t = __fadd_rn(t, be.f);                                                          \
     dst = t;
@@ -118,7 +118,35 @@ k_measure_stats(const float* x, const float* r, float* y, int64_t B, int64_t inn
         const int64_t len = (inner - off < MS_TILE) ? inner - off : MS_TILE;
         const float* src = x + b * inner + off;
         float fs = 0.f, fq = 0.f;
-        if (vec) {
+        if (CODES && vec && ap.fixed && len == MS_TILE) {
+            // whole tile, per-thread channel parameters fixed: no bounds checks, no parameter reloads, full-warp shuffles - the
+            // generic body below spends ~28 instructions per element on those (ncu: issue-bound after the XU pipe was freed)
+            const int64_t base = b * inner + off;
+            const uint32_t* cp = reinterpret_cast<const uint32_t*>(reinterpret_cast<const uint8_t*>(x) + base) + threadIdx.x;
+            const float4* rp = ADD ? reinterpret_cast<const float4*>(r + base) + threadIdx.x : nullptr;
+            float4* yp = reinterpret_cast<float4*>(y + base) + threadIdx.x;
+            uint8_t* mp = ap.mask_out ? ap.mask_out + (base >> 3) + (threadIdx.x >> 1) : nullptr;
+            uint32_t cw[MS_VEC_PER_THREAD];
+            float4 rv[ADD ? MS_VEC_PER_THREAD : 1];
+#pragma unroll
+            for (int u = 0; u < MS_VEC_PER_THREAD; ++u) {
+                cw[u] = __ldcs(cp + u * MS_THREADS);
+                if (ADD) rv[u] = __ldcs(rp + u * MS_THREADS);
+            }
+#pragma unroll
+            for (int u = 0; u < MS_VEC_PER_THREAD; ++u) {
+                float4 w = apply_quad(cw[u], aq, mu, sc, gm, be, has_g, has_b);
+                if (ADD) w = make_float4(__fadd_rn(w.x, rv[u].x), __fadd_rn(w.y, rv[u].y), __fadd_rn(w.z, rv[u].z), __fadd_rn(w.w, rv[u].w));
+                w = make_float4(relu1(w.x), relu1(w.y), relu1(w.z), relu1(w.w));
+                yp[u * MS_THREADS] = w;
+                if (mp) {                                                     // warp-uniform
+                    const uint32_t nib = (w.x <= 0.0f ? 0u : 1u) | (w.y <= 0.0f ? 0u : 2u) | (w.z <= 0.0f ? 0u : 4u) | (w.w <= 0.0f ? 0u : 8u);
+                    const uint32_t hi = __shfl_down_sync(0xffffffffu, nib, 1);
+                    if ((threadIdx.x & 1) == 0) mp[u * (MS_THREADS / 2)] = (uint8_t)(nib | (hi << 4));
+                }
+                acc4(w, mn, mx, fs, fq);
+            }
+        } else if (vec) {
             const int64_t nq = len >> 2;
             float4 v[MS_VEC_PER_THREAD];
             float4 rv[ADD ? MS_VEC_PER_THREAD : 1];

@@ -701,10 +701,11 @@ k_rbn_apply_codes_nhwc(const uint8_t* __restrict__ codes, float* __restrict__ ou
     }
     auto one_row = [&](const uint2& pk, int64_t r) {
         F8 o;
+        float xh[8];
+        affine_deq8(pk, aq.p, xh);                       // PRMT + FADD per code: no I2F (the XU pipe was this pass' bound too)
 #pragma unroll
         for (int j = 0; j < 8; ++j) {
-            const float xh = q_affine_deq((float)(((j < 4 ? pk.x : pk.y) >> (8 * (j & 3))) & 0xffu), aq.p);
-            float t = __fmul_rn(__fsub_rn(xh, mu[j]), sc[j]);
+            float t = __fmul_rn(__fsub_rn(xh[j], mu[j]), sc[j]);
             if (p.p2) t = __fmul_rn(t, gm[j]);
             if (p.p3) t = __fadd_rn(t, be[j]);
             o.v[j] = t;

@@ -32,15 +32,26 @@ def bwd(vec, amax, amin):
                                  q_bits=8, grad_quant=gq, want_dx_range=True, x_codes=xc)
 
 
+def fused(vec, res=None):
+    """normalise + (add) + ReLU + next layer's statistics + 1-bit mask from the codes (RangeBN.forward_relu)"""
+    return _abi.rangebn_apply_relu_measure(xc, x, B, C, HW, vec, True, True, qr, 8, residual=res, want_bits=True)
+
+
 vec, amax, amin, out = fwd()
 for _ in range(3):
     fwd()
     bwd(vec, amax, amin)
+    if CODES:
+        fused(vec)
+        fused(vec, g)
 torch.cuda.synchronize()
 _abi.profile_begin()
 for _ in range(5):
     fwd()
     bwd(vec, amax, amin)
+    if CODES:
+        fused(vec)
+        fused(vec, g)
 torch.cuda.synchronize()
 recs = _abi.profile_end()
 agg = {}
