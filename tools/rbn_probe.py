@@ -37,13 +37,27 @@ def fused(vec, res=None):
     return _abi.rangebn_apply_relu_measure(xc, x, B, C, HW, vec, True, True, qr, 8, residual=res, want_bits=True)
 
 
+codes8 = torch.empty_like(x, dtype=torch.uint8)
+codes16 = torch.empty_like(x, dtype=torch.bfloat16)
+
+
+def others(bits):
+    """the quantizer / pack / ReLU-backward passes that sit between the RangeBN passes in a training step"""
+    r = _abi.minmax(g)
+    _abi.bwd_pack(g, range_dev=r, bits=8, seed=3)
+    _abi.fakequant_affine_rowsum(x, B * HW, C, 8, qr, codes8, codes16)
+    _abi.relu_bwd_minmax_bits(g, bits, want_dx=False)
+    _abi.relu_bwd_minmax_bits(g, bits, want_dx=True)
+    _abi.measure_stats(x)
+
+
 vec, amax, amin, out = fwd()
 for _ in range(3):
     fwd()
     bwd(vec, amax, amin)
     if CODES:
         fused(vec)
-        fused(vec, g)
+        others(fused(vec, g)[2])
 torch.cuda.synchronize()
 _abi.profile_begin()
 for _ in range(5):
@@ -51,7 +65,7 @@ for _ in range(5):
     bwd(vec, amax, amin)
     if CODES:
         fused(vec)
-        fused(vec, g)
+        others(fused(vec, g)[2])
 torch.cuda.synchronize()
 recs = _abi.profile_end()
 agg = {}
