@@ -376,24 +376,41 @@ k_conv_i8(const __grid_constant__ CUtensorMap tmap_x, const __grid_constant__ CU
                     const uint64_t rs2 = pack2(rs_a, rs_a);
                     const bool st_fast = want_stats && !need_la && c + 32 <= ncols;
                     uint64_t sum2 = 0ull, sq2 = 0ull;                    // (0.f, 0.f)
-#pragma unroll
-                    for (int q = 0; q < 32; q += 2) {
+                    // the statistics mode is loop invariant: three straight-line copies of the 16-pair loop instead of two
+                    // branches per pair (ncu on the 64-channel layers: 13 % of the stall samples were branch resolution)
+                    auto dequant_pair = [&](int q, float& va, float& vb) -> uint64_t {
                         uint64_t c0p, c1p;
                         lds_2x64(pa + q * 8, c0p, c1p);
                         const uint64_t c2p = lds_64(ca + q * 4);
                         const uint64_t v2 = fma2(c0p, pack2((float)(int32_t)r[q], (float)(int32_t)r[q + 1]), fma2(c1p, rs2, c2p));
-                        float va, vb;
                         unpack2(v2, va, vb);
                         r[q] = __float_as_uint(va);
                         r[q + 1] = __float_as_uint(vb);
-                        if (st_fast) {
+                        return v2;
+                    };
+                    if (st_fast) {
+#pragma unroll
+                        for (int q = 0; q < 32; q += 2) {
+                            float va, vb;
+                            const uint64_t v2 = dequant_pair(q, va, vb);
                             sum2 = add2(sum2, v2);
                             sq2 = fma2(v2, v2, sq2);
                             t_mn = min3(t_mn, va, vb);
                             t_mx = max3(t_mx, va, vb);
-                        } else if (want_stats && !need_la) {
+                        }
+                    } else if (want_stats && !need_la) {
+#pragma unroll
+                        for (int q = 0; q < 32; q += 2) {
+                            float va, vb;
+                            dequant_pair(q, va, vb);
                             if (c + q < ncols) { t_mn = fminf(t_mn, va); t_mx = fmaxf(t_mx, va); t_sum += va; t_sq = fmaf(va, va, t_sq); }
                             if (c + q + 1 < ncols) { t_mn = fminf(t_mn, vb); t_mx = fmaxf(t_mx, vb); t_sum += vb; t_sq = fmaf(vb, vb, t_sq); }
+                        }
+                    } else {
+#pragma unroll
+                        for (int q = 0; q < 32; q += 2) {
+                            float va, vb;
+                            dequant_pair(q, va, vb);
                         }
                     }
                     if (st_fast) {
