@@ -209,6 +209,10 @@ k_conv_i8(const __grid_constant__ CUtensorMap tmap_x, const __grid_constant__ CU
         constexpr uint32_t idesc = umma_idesc(/*S32*/ 2, /*A u8*/ 0, /*B s8*/ 1, 128, BN);
         const int mmas = g.BK / 32;
         const uint64_t ring_desc0 = umma_smem_desc(smem_u32(smem), g.BK);      // stage s: + s * stage_bytes (one add per stage)
+        const uint64_t halo_w_desc = umma_smem_desc(smem_u32(wres), g.BK);     // halo mode: resident weight slabs
+        uint32_t halo_a[9];                                                     // halo mode: operand offset of tap (r, s) in a stage
+#pragma unroll
+        for (int tap = 0; tap < 9; ++tap) halo_a[tap] = (uint32_t)(tap % 3) * hbox_bytes + (uint32_t)((tap / 3) * g.TW * g.BK);
         RingPos rp;
         int j = 0;
         for (int t = blockIdx.x; t < total_tiles; t += gridDim.x, ++j) {
@@ -223,15 +227,18 @@ k_conv_i8(const __grid_constant__ CUtensorMap tmap_x, const __grid_constant__ CU
                 mbar_wait(&full_bar[s], ph);
                 tc_fence_after_sync();
                 if (elect_one()) {
-                    const uint64_t st_desc = umma_smem_desc(smem_u32(smem + (size_t)s * stage_bytes), g.BK);
-                    const uint64_t w_desc = umma_smem_desc(smem_u32(wres), g.BK);
-                    for (int r = 0; r < g.kh; ++r)
-                        for (int s_ = 0; s_ < g.kw; ++s_) {
-                            const uint64_t a_desc = desc_add(st_desc, (uint32_t)s_ * hbox_bytes + (uint32_t)(r * g.TW * g.BK));
-                            const uint64_t b_desc = desc_add(w_desc, (uint32_t)(r * g.kw + s_) * b_bytes);
-                            for (int k = 0; k < mmas; ++k)
-                                umma_i8(d_tmem, desc_add(a_desc, k * 32), desc_add(b_desc, k * 32), idesc, (r | s_ | k) != 0);
-                        }
+                    // halo mode is 3x3 by construction: the nine taps are unrolled and their operand offsets are the
+                    // loop-invariant halo_a[] / tap * b_bytes - the rolled form spent ~75 instructions of uniform-datapath
+                    // arithmetic and constant-bank reloads per tap (ncu source view), as long as the MMAs themselves
+                    const uint64_t st_desc = desc_add(ring_desc0, (uint32_t)s * stage_bytes);
+#pragma unroll
+                    for (int tap = 0; tap < 9; ++tap) {
+                        const uint64_t a_desc = desc_add(st_desc, halo_a[tap]);
+                        const uint64_t b_desc = desc_add(halo_w_desc, (uint32_t)tap * b_bytes);
+#pragma unroll
+                        for (int k = 0; k < 4; ++k)
+                            if (k < mmas) umma_i8(d_tmem, desc_add(a_desc, k * 32), desc_add(b_desc, k * 32), idesc, (tap | k) != 0);
+                    }
                     umma_commit(&empty_bar[s]);
                     umma_commit(&tfull_bar[buf]);
                 }
