@@ -13,6 +13,8 @@
 // Slots are double buffered by call parity: a rank can run at most one call ahead of its slowest peer, because call
 // s+1 cannot complete without that peer's flag for s+1, which the peer only raises after finishing call s.
 // A bounded spin (about two seconds) records an error instead of hanging the GPU if a peer never arrives.
+#include <stdlib.h>
+
 #include "common.cuh"
 
 constexpr int AR_MAX_WORLD = 16;
@@ -26,9 +28,11 @@ struct ArCtrl {
     unsigned long long flags[2][AR_MAX_WORLD];
 };
 
+// A slot holds a message in the flagged ("LL") form below: every 4 payload bytes travel with a 4-byte tag, so it is twice
+// the message size.
 extern "C" size_t qb_allreduce_small_buffer_bytes(int world, size_t slot_bytes) {
     if (world < 1 || world > AR_MAX_WORLD) return 0;
-    return (size_t)AR_CTRL_BYTES + 2 * (size_t)world * slot_bytes;
+    return (size_t)AR_CTRL_BYTES + 2 * (size_t)world * (2 * slot_bytes);
 }
 
 __device__ __forceinline__ void st_release_sys(unsigned long long* p, unsigned long long v) {
@@ -64,6 +68,7 @@ __global__ void __launch_bounds__(AR_THREADS) k_allreduce_oneshot(T* __restrict_
     __syncthreads();
     const unsigned long long seq = s_seq;
     const int par = (int)(seq & 1ull);
+    slot_bytes *= 2;                                               // slot stride of the buffer layout (flagged form: 2x)
     const size_t slot_off = (size_t)AR_CTRL_BYTES + ((size_t)par * world + rank) * slot_bytes;
     // (a) my block into my slot on every rank (own rank included: plain local stores)
     for (int i = threadIdx.x; i < n; i += AR_THREADS) {
@@ -114,6 +119,92 @@ __global__ void __launch_bounds__(AR_THREADS) k_allreduce_oneshot(T* __restrict_
     }
 }
 
+// ---------------------------------------------------------------------------------------------------
+// Flagged one-shot exchange (default).  The separate flag + system fence of the kernel above costs a full NVLink round trip
+// per call on top of the data: here every 8-byte word that crosses the link carries 4 payload bytes and the 4-byte call tag
+// (aligned 8-byte stores are indivisible), so a reader that sees the tag has the data - no fence, no flag, no barrier between
+// the write and the read phase (a thread polls exactly the elements it wrote).  Same slots, double buffering and rank-ordered
+// reduction as above; a timeout is fatal in the same way.
+// ---------------------------------------------------------------------------------------------------
+__device__ __forceinline__ void st_volatile_u64(unsigned long long* p, unsigned long long v) {
+    asm volatile("st.volatile.global.u64 [%0], %1;" ::"l"(p), "l"(v) : "memory");
+}
+__device__ __forceinline__ unsigned long long ld_volatile_u64(const unsigned long long* p) {
+    unsigned long long v;
+    asm volatile("ld.volatile.global.u64 %0, [%1];" : "=l"(v) : "l"(p) : "memory");
+    return v;
+}
+
+template <typename T>
+__global__ void __launch_bounds__(AR_THREADS) k_allreduce_ll(T* __restrict__ data, int n, int mode, ArPeers peers, int rank, int world,
+                                                             size_t slot_bytes) {
+    constexpr int WORDS = sizeof(T) / 4;                           // 8-byte flagged words per element
+    __shared__ unsigned long long s_seq;
+    __shared__ int s_fail;
+    ArCtrl* ctrl = reinterpret_cast<ArCtrl*>(peers.buf[rank]);
+    if (threadIdx.x == 0) { s_seq = ctrl->seq + 1ull; s_fail = 0; }
+    __syncthreads();
+    const unsigned long long seq = s_seq;
+    const unsigned long long tag = (seq & 0xffffffffull) << 32;
+    const int par = (int)(seq & 1ull);
+    const size_t stride = 2 * slot_bytes;
+    const size_t my_off = (size_t)AR_CTRL_BYTES + ((size_t)par * world + rank) * stride;
+    for (int i = threadIdx.x; i < n; i += AR_THREADS) {
+        const T v = data[i];
+        unsigned long long w[WORDS];
+        if (WORDS == 2) {
+            const unsigned long long b = (unsigned long long)__double_as_longlong((double)v);
+            w[0] = (b & 0xffffffffull) | tag;
+            w[WORDS - 1] = (b >> 32) | tag;
+        } else {
+            w[0] = (unsigned long long)__float_as_uint((float)v) | tag;
+        }
+        for (int p = 0; p < world; ++p) {
+            unsigned long long* dst = reinterpret_cast<unsigned long long*>(peers.buf[p] + my_off) + (size_t)i * WORDS;
+#pragma unroll
+            for (int k = 0; k < WORDS; ++k) st_volatile_u64(dst + k, w[k]);
+        }
+    }
+    const unsigned char* mine = peers.buf[rank] + (size_t)AR_CTRL_BYTES + (size_t)par * world * stride;
+    for (int i = threadIdx.x; i < n; i += AR_THREADS) {
+        T acc = T(0);
+        for (int q = 0; q < world; ++q) {
+            const unsigned long long* src = reinterpret_cast<const unsigned long long*>(mine + (size_t)q * stride) + (size_t)i * WORDS;
+            unsigned long long w[WORDS];
+            unsigned int spins = 0;
+            unsigned long long t0 = 0ull;
+            bool ok = false;
+            while (!ok) {
+                ok = true;
+#pragma unroll
+                for (int k = 0; k < WORDS; ++k) {
+                    w[k] = ld_volatile_u64(src + k);
+                    ok = ok && ((w[k] & 0xffffffff00000000ull) == tag);
+                }
+                if (!ok && ++spins > 256) {
+                    __nanosleep(100);
+                    unsigned long long now;
+                    asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(now));
+                    if (t0 == 0ull) t0 = now;
+                    else if (now - t0 > AR_TIMEOUT_NS) { s_fail = 1; break; }
+                }
+            }
+            T v;
+            if (WORDS == 2) v = (T)__longlong_as_double((long long)((w[0] & 0xffffffffull) | (w[WORDS - 1] << 32)));
+            else v = (T)__uint_as_float((unsigned int)(w[0] & 0xffffffffull));
+            acc = q == 0 ? v : ar_combine<T>(acc, v, i, mode);
+        }
+        data[i] = acc;
+    }
+    __syncthreads();
+    if (s_fail) {
+        if (threadIdx.x == 0) { ctrl->error = 1u; __threadfence_system(); }
+        __syncthreads();
+        __trap();
+    }
+    if (threadIdx.x == 0) ctrl->seq = seq;
+}
+
 /* data: n elements of double (dtype 0) or float (dtype 1), reduced IN PLACE across the `world` ranks.
  * peer_bufs[world]: the peer-mapped address of every rank's buffer (qb_allreduce_small_buffer_bytes bytes, zero-filled
  * once before the first call, same slot_bytes everywhere).  Every rank must issue the same sequence of calls. */
@@ -131,7 +222,11 @@ extern "C" int qb_allreduce_small(void* data, int64_t n, int dtype, int mode, co
     ArPeers peers;
     for (int p = 0; p < AR_MAX_WORLD; ++p) peers.buf[p] = p < world ? reinterpret_cast<unsigned char*>(peer_bufs[p]) : nullptr;
     cudaStream_t st = qb_stream(stream);
-    if (dtype == 0) k_allreduce_oneshot<double><<<1, AR_THREADS, 0, st>>>(static_cast<double*>(data), (int)n, mode, peers, rank, world, slot_bytes);
+    static const bool flagged = []() { const char* e = getenv("QB_AR_FLAGGED"); return !(e && e[0] == '0'); }();
+    if (flagged) {
+        if (dtype == 0) k_allreduce_ll<double><<<1, AR_THREADS, 0, st>>>(static_cast<double*>(data), (int)n, mode, peers, rank, world, slot_bytes);
+        else k_allreduce_ll<float><<<1, AR_THREADS, 0, st>>>(static_cast<float*>(data), (int)n, mode, peers, rank, world, slot_bytes);
+    } else if (dtype == 0) k_allreduce_oneshot<double><<<1, AR_THREADS, 0, st>>>(static_cast<double*>(data), (int)n, mode, peers, rank, world, slot_bytes);
     else k_allreduce_oneshot<float><<<1, AR_THREADS, 0, st>>>(static_cast<float*>(data), (int)n, mode, peers, rank, world, slot_bytes);
     QB_LAUNCH_CHECK();
     return QB_OK;
