@@ -17,7 +17,9 @@ ENTRY = {"k_conv_wgrad": "qb_conv_wgrad", "k_conv_dgrad_flat": "qb_conv_dgrad", 
          "k_rbn_bwd_apply_fused": "qb_rangebn_bwd_apply_fused_nhwc", "k_rbn_apply_codes_nhwc": "qb_rangebn_apply_nhwc", "k_bwd_pack": "qb_bwd_pack",
          "k_fq_affine_v8": "qb_fakequant_affine16", "k_relu_bwd_minmax": "qb_relu_bwd_minmax_bits", "k_maxpool_bwd_3s2": "qb_maxpool2d_relu_nhwc_bwd",
          "k_maxpool_fwd_nhwc": "qb_maxpool2d_nhwc_fwd", "k_conv_dw3x3": "qb_conv_dw_fwd", "k_conv_dw_dgrad": "qb_conv_dw_dgrad",
-         "k_conv_dw_wgrad": "qb_conv_dw_wgrad", "k_gemm_i8": "qb_gemm_i8", "k_measure_stats": "qb_rangebn_apply_relu_measure"}
+         "k_conv_dw_wgrad": "qb_conv_dw_wgrad", "k_gemm_i8": "qb_gemm_i8", "k_measure_stats": "qb_rangebn_apply_relu_measure", "k_fq_affine_rowsum": "qb_fakequant_affine_rowsum",
+         "k_fq_affine_nchw3": "qb_fakequant_affine_nchw3", "k_avgpool_bwd_nhwc": "qb_avgpool2d_nhwc_bwd"}
+ALIAS = {"qb_rangebn_bwd_reduce_nhwc": "qb_rangebn_bwd_reduce_coeffs_nhwc"}      # same kernel behind the one-call entry point
 SCALE = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9, "ns": 1e-3, "us": 1.0, "ms": 1e3, "s": 1e6}
 
 
@@ -47,6 +49,8 @@ def main():
             acc[e][1] += len(v)
     for e, (b, n) in acc.items():
         out[e] = round(b / n)
+        if e in ALIAS:
+            out[ALIAS[e]] = out[e]
     json.dump(out, open(sys.argv[2], "w"), indent=1, sort_keys=True)
 
 
