@@ -406,6 +406,13 @@ int qb_rangebn_apply_relu_measure(const uint8_t* x_codes, const float* residual,
                                   size_t ws_bytes, void* stream);
 int qb_maxpool2d_nhwc_fwd(const float* x, float* out, uint8_t* idx, int64_t B, int64_t H, int64_t W, int64_t C, int k,
                           int stride, int pad, void* stream);
+/* maxpool(RangeBN-normalise(x)) from the uint8 codes of RangeBN's fake-quantized input (x_codes_out of
+ * qb_rangebn_stats_nhwc) and the vectors of qb_rangebn_finalize: the stem tail conv1 -> bn1 -> relu -> maxpool
+ * (models/resnet_quantized.py:147-150, quantize.py:488-499) without ever writing the normalised tensor.  out / idx equal
+ * qb_maxpool2d_nhwc_fwd on the output of qb_rangebn_apply_nhwc, bit for bit. */
+int qb_rangebn_apply_maxpool_nhwc(const uint8_t* x_codes, float* out, uint8_t* idx, int64_t B, int64_t H, int64_t W, int64_t C, int k,
+                                  int stride, int pad, const float* mean, const float* qscale, const float* qgamma,
+                                  const float* qbeta, const float* q_range, int q_bits, void* stream);
 int qb_maxpool2d_nhwc_bwd(const float* grad_out, const uint8_t* idx, float* dx, int64_t B, int64_t H, int64_t W, int64_t C,
                           int k, int stride, int pad, void* stream);
 /* Backward of ReLU -> MaxPool2d as one pass (models/resnet_quantized.py:147-150, bn1 -> relu -> maxpool): dx is the gradient

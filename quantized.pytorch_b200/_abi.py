@@ -74,6 +74,7 @@ PROTOTYPES = {
     "qb_allreduce_small": (_i32, [_p, _i64, _i32, _i32, _p, _i32, _i32, _sz, _p]),
     "qb_maxpool2d_nhwc_fwd": (_i32, [_p, _p, _p, _i64, _i64, _i64, _i64, _i32, _i32, _i32, _p]),
     "qb_maxpool2d_nhwc_bwd": (_i32, [_p, _p, _p, _i64, _i64, _i64, _i64, _i32, _i32, _i32, _p]),
+    "qb_rangebn_apply_maxpool_nhwc": (_i32, [_p, _p, _p, _i64, _i64, _i64, _i64, _i32, _i32, _i32, _p, _p, _p, _p, _p, _i32, _p]),
     "qb_avgpool2d_nhwc_fwd": (_i32, [_p, _p, _i64, _i64, _i64, _i64, _i32, _p]),
     "qb_avgpool2d_nhwc_bwd": (_i32, [_p, _p, _i64, _i64, _i64, _i64, _i32, _p]),
     "qb_cross_entropy_ws_bytes": (_sz, [_i64]),
@@ -964,6 +965,19 @@ def maxpool2d_nhwc_fwd(x, k, stride, pad):
     idx = torch.empty(out.numel(), dtype=torch.uint8, device=x.device)
     _run("qb_maxpool2d_nhwc_fwd", 4 * x.numel() + 5 * out.numel(), _ptr(x), _ptr(out), _ptr(idx), B, H, W, Cn, int(k), int(stride),
          int(pad), _stream())
+    return out, idx
+
+
+def rangebn_apply_maxpool(x_codes, in_shape, vec, has_gamma, has_beta, q_range, q_bits, k, stride, pad):
+    """maxpool(RangeBN-normalise(codes)) -> (out channels-last, idx uint8 flat) without the normalised tensor
+    (qb_rangebn_apply_maxpool_nhwc); ``in_shape`` = logical [B, C, H, W] of the RangeBN input."""
+    B, Cn, H, W = in_shape
+    Ho, Wo = (H + 2 * pad - k) // stride + 1, (W + 2 * pad - k) // stride + 1
+    out = torch.empty((B, Cn, Ho, Wo), dtype=torch.float32, device=x_codes.device, memory_format=torch.channels_last)
+    idx = torch.empty(out.numel(), dtype=torch.uint8, device=x_codes.device)
+    _run("qb_rangebn_apply_maxpool_nhwc", B * Cn * H * W + 5 * out.numel(), _ptr(x_codes), _ptr(out), _ptr(idx), B, H, W, Cn, int(k),
+         int(stride), int(pad), _ptr(vec[0]), _ptr(vec[2]), _ptr(vec[3]) if has_gamma else None, _ptr(vec[4]) if has_beta else None,
+         _ptr(q_range), int(q_bits), _stream())
     return out, idx
 
 

@@ -18,8 +18,21 @@ struct PoolGeom {
     FastDiv d_c8, d_wo, d_ho, d_w, d_h;
 };
 
-__global__ void __launch_bounds__(256) k_maxpool_fwd_nhwc(const float* __restrict__ x, float* __restrict__ out, uint8_t* __restrict__ idx,
-                                                          PoolGeom g, uint32_t total) {
+// CODES: the pooled tensor is the output of a RangeBN that has not been materialised - x holds the uint8 codes of RangeBN's
+// fake-quantized input (written by its statistics pass) and every window element is dequantised and normalised on the fly,
+// with the arithmetic of k_rbn_apply_codes_nhwc (quantize.py:488-499, four separately rounded fp32 operations), so the result
+// equals pooling the normalised tensor bit for bit while the 822 MB bn1 output of ResNet-18's stem is never written or read.
+struct PoolApply {
+    const float *mean, *qscale, *qgamma, *qbeta;   // per channel; qgamma / qbeta may be null
+    const float* q_range;
+    int q_bits;
+};
+
+template <bool CODES>
+__global__ void __launch_bounds__(256) k_maxpool_fwd_nhwc(const void* __restrict__ xin, float* __restrict__ out, uint8_t* __restrict__ idx,
+                                                          PoolGeom g, uint32_t total, PoolApply ap) {
+    const float* x = static_cast<const float*>(xin);
+    const uint8_t* xc = static_cast<const uint8_t*>(xin);
     const uint32_t t = blockIdx.x * 256u + threadIdx.x;
     if (t >= total) return;
     const uint32_t c8n = (uint32_t)g.C >> 3;
@@ -35,13 +48,101 @@ __global__ void __launch_bounds__(256) k_maxpool_fwd_nhwc(const float* __restric
     bool first = true;
 #pragma unroll
     for (int j = 0; j < 8; ++j) { mx[j] = -QB_INF; am[j] = 0; }
+    AffineQ aq;
+    float mu[8], sc[8], gm[8], be[8];
+    if (CODES) {
+        aq = load_affineq(ap.q_range, ap.q_bits);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+            mu[j] = __ldg(ap.mean + c0 + j);
+            sc[j] = __ldg(ap.qscale + c0 + j);
+            gm[j] = ap.qgamma ? __ldg(ap.qgamma + c0 + j) : 1.0f;
+            be[j] = ap.qbeta ? __ldg(ap.qbeta + c0 + j) : 0.0f;
+        }
+    }
+    // CODES, fast form.  The normalisation is a monotone map of the code (every rounded fp32 operation is monotone in its
+    // operand), so the window maximum of the normalised values sits at the window maximum of the codes - or the minimum, for a
+    // channel whose scale * gamma is negative - and ONE element per channel is normalised instead of nine: the window search
+    // runs on packed bytes (__vmaxu4 / __vcmpgtu4, 8 channels in two words).  "First maximal element wins" carries over as long
+    // as distinct codes give distinct normalised values; that is checked per channel from the images of codes 0 and 255 (their
+    // spacing per code step must exceed 2^-18 of the magnitudes involved, 8x the worst accumulated rounding error of the four
+    // operations), a channel with gamma == 0 maps every code to one value (first valid element wins, as in ATen), and a thread
+    // with any other channel takes the element-wise form below.  Without this the fused pass was instruction-bound (125
+    // instructions per output) and no faster than normalise-then-pool.
+    bool fast = false;
+    uint2 xorm = make_uint2(0u, 0u), andm = make_uint2(0xffffffffu, 0xffffffffu);
+    if (CODES) {
+        fast = true;
+        const float xmag = fmaxf(fabsf(aq.p.lo), fabsf(q_affine_deq(aq.p.qmax, aq.p)));
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+            float t0 = __fmul_rn(__fsub_rn(q_affine_deq(0.0f, aq.p), mu[j]), sc[j]);
+            float t1 = __fmul_rn(__fsub_rn(q_affine_deq(aq.p.qmax, aq.p), mu[j]), sc[j]);
+            if (ap.qgamma) { t0 = __fmul_rn(t0, gm[j]); t1 = __fmul_rn(t1, gm[j]); }
+            if (ap.qbeta) { t0 = __fadd_rn(t0, be[j]); t1 = __fadd_rn(t1, be[j]); }
+            const uint32_t byte = 0xffu << (8 * (j & 3));
+            const bool flat = ap.qgamma && gm[j] == 0.0f && t0 == t1;
+            const float step = fabsf(t1 - t0) / aq.p.qmax;
+            const bool sep = step > 3.8146973e-6f * fmaxf(fabsf(t0), fabsf(t1)) &&
+                             aq.p.scale > 3.8146973e-6f * (xmag + fabsf(mu[j]));                   // 2^-18
+            if (flat) { if (j < 4) andm.x &= ~byte; else andm.y &= ~byte; }
+            else if (!sep) fast = false;                                                           // also catches NaN parameters
+            else if (t1 < t0) { if (j < 4) xorm.x |= byte; else xorm.y |= byte; }
+        }
+    }
+    if (CODES && fast) {
+        uint2 best = make_uint2(0u, 0u), bidx = make_uint2(0u, 0u), firstpk = make_uint2(0u, 0u);
+        for (int kh = 0; kh < g.k; ++kh) {
+            const int h = h0 + kh;
+            if (h < 0 || h >= g.H) continue;
+            for (int kw = 0; kw < g.k; ++kw) {
+                const int w = w0 + kw;
+                if (w < 0 || w >= g.W) continue;
+                const uint2 pk = __ldg(reinterpret_cast<const uint2*>(xc + (((size_t)b * g.H + h) * g.W + w) * g.C + c0));
+                const uint2 key = make_uint2((pk.x ^ xorm.x) & andm.x, (pk.y ^ xorm.y) & andm.y);
+                const uint32_t code4 = (uint32_t)(kh * g.k + kw) * 0x01010101u;
+                if (first) {
+                    best = key; bidx = make_uint2(code4, code4); firstpk = pk; first = false;
+                } else {
+                    const uint32_t gx = __vcmpgtu4(key.x, best.x), gy = __vcmpgtu4(key.y, best.y);
+                    best.x = __vmaxu4(best.x, key.x); best.y = __vmaxu4(best.y, key.y);
+                    bidx.x = (bidx.x & ~gx) | (code4 & gx); bidx.y = (bidx.y & ~gy) | (code4 & gy);
+                }
+            }
+        }
+        const uint2 win = make_uint2(((best.x ^ xorm.x) & andm.x) | (firstpk.x & ~andm.x), ((best.y ^ xorm.y) & andm.y) | (firstpk.y & ~andm.y));
+        float xh[8];
+        affine_deq8(win, aq.p, xh);
+#pragma unroll
+        for (int j = 0; j < 8; ++j) {
+            float tt = __fmul_rn(__fsub_rn(xh[j], mu[j]), sc[j]);
+            if (ap.qgamma) tt = __fmul_rn(tt, gm[j]);
+            if (ap.qbeta) tt = __fadd_rn(tt, be[j]);
+            mx[j] = tt;
+            am[j] = ((j < 4 ? bidx.x : bidx.y) >> (8 * (j & 3))) & 0xffu;
+        }
+    } else
     for (int kh = 0; kh < g.k; ++kh) {
         const int h = h0 + kh;
         if (h < 0 || h >= g.H) continue;
         for (int kw = 0; kw < g.k; ++kw) {
             const int w = w0 + kw;
             if (w < 0 || w >= g.W) continue;
-            const F8 v = ld256_keep(x + (((size_t)b * g.H + h) * g.W + w) * g.C + c0);
+            const size_t e0 = (((size_t)b * g.H + h) * g.W + w) * g.C + c0;
+            F8 v;
+            if (CODES) {
+                float xh[8];
+                affine_deq8(__ldg(reinterpret_cast<const uint2*>(xc + e0)), aq.p, xh);
+#pragma unroll
+                for (int j = 0; j < 8; ++j) {
+                    float tt = __fmul_rn(__fsub_rn(xh[j], mu[j]), sc[j]);
+                    if (ap.qgamma) tt = __fmul_rn(tt, gm[j]);
+                    if (ap.qbeta) tt = __fadd_rn(tt, be[j]);
+                    v.v[j] = tt;
+                }
+            } else {
+                v = ld256_keep(x + e0);
+            }
             const uint32_t code = (uint32_t)(kh * g.k + kw);
 #pragma unroll
             for (int j = 0; j < 8; ++j) {
@@ -273,7 +374,27 @@ extern "C" int qb_maxpool2d_nhwc_fwd(const float* x, float* out, uint8_t* idx, i
     int rc = pool_geom(g, "qb_maxpool2d_nhwc_fwd", B, H, W, C, k, stride, pad, x, out, idx);
     if (rc) return rc;
     const uint32_t total = (uint32_t)((int64_t)B * g.Ho * g.Wo * (C / 8));
-    k_maxpool_fwd_nhwc<<<(total + 255u) / 256u, 256, 0, qb_stream(stream)>>>(x, out, idx, g, total);
+    k_maxpool_fwd_nhwc<false><<<(total + 255u) / 256u, 256, 0, qb_stream(stream)>>>(x, out, idx, g, total, PoolApply{});
+    QB_LAUNCH_CHECK();
+    return QB_OK;
+}
+
+/* maxpool(RangeBN-normalise(codes)) without the normalised tensor: x_codes are the uint8 codes [B, H, W, C] the channels-last
+ * RangeBN statistics pass wrote (qb_rangebn_stats_nhwc, x_codes_out), mean / qscale / qgamma / qbeta the vectors of
+ * qb_rangebn_finalize, q_range / q_bits the quantizer of those codes.  out / idx as qb_maxpool2d_nhwc_fwd on the normalised
+ * tensor, bit for bit (models/resnet_quantized.py:147-150: conv1 -> bn1 -> relu -> maxpool). */
+extern "C" int qb_rangebn_apply_maxpool_nhwc(const uint8_t* x_codes, float* out, uint8_t* idx, int64_t B, int64_t H, int64_t W, int64_t C,
+                                             int k, int stride, int pad, const float* mean, const float* qscale, const float* qgamma,
+                                             const float* qbeta, const float* q_range, int q_bits, void* stream) {
+    PoolGeom g;
+    int rc = pool_geom(g, "qb_rangebn_apply_maxpool_nhwc", B, H, W, C, k, stride, pad, out, out, idx);
+    if (rc) return rc;
+    QB_CHECK_ARG(x_codes && mean && qscale && q_range, "qb_rangebn_apply_maxpool_nhwc: null pointer");
+    QB_CHECK_ARG(q_bits >= 1 && q_bits <= 8, "qb_rangebn_apply_maxpool_nhwc: q_bits=%d", q_bits);
+    QB_CHECK_ARG((reinterpret_cast<uintptr_t>(x_codes) & 7) == 0, "qb_rangebn_apply_maxpool_nhwc: codes must be 8-byte aligned");
+    const uint32_t total = (uint32_t)((int64_t)B * g.Ho * g.Wo * (C / 8));
+    const PoolApply ap{mean, qscale, qgamma, qbeta, q_range, q_bits};
+    k_maxpool_fwd_nhwc<true><<<(total + 255u) / 256u, 256, 0, qb_stream(stream)>>>(x_codes, out, idx, g, total, ap);
     QB_LAUNCH_CHECK();
     return QB_OK;
 }

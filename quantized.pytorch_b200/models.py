@@ -203,11 +203,14 @@ class QResNet(nn.Module):
 
     def forward(self, x):
         _prepare_weights(self, x)
-        x = self.bn1(self.conv1(x))
-        if hasattr(self.maxpool, "relu_pool"):         # native glue: pool first, ReLU on the 4x smaller result (same values)
-            x = self.maxpool.relu_pool(x, self.relu)
+        x = self.conv1(x)
+        if hasattr(self.maxpool, "relu_pool") and hasattr(self.bn1, "forward_relu_pool"):
+            # native modules: the pooling reads bn1's codes (the normalised full-size tensor never exists), ReLU on the pooled result
+            x = self.bn1.forward_relu_pool(x, self.relu, self.maxpool)
+        elif hasattr(self.maxpool, "relu_pool"):       # native glue: pool first, ReLU on the 4x smaller result (same values)
+            x = self.maxpool.relu_pool(self.bn1(x), self.relu)
         else:
-            x = self.maxpool(self.relu(x))
+            x = self.maxpool(self.relu(self.bn1(x)))
         x = self.layer4(self.layer3(self.layer2(self.layer1(x))))
         x = self.avgpool(x)
         return _join_prepared(self, self.fc(x.view(x.size(0), -1)))

@@ -597,6 +597,7 @@ USE_NATIVE_BACKWARD = True    # dX / dW / db of the dense contractions on conv_b
 # the library.
 ALLOW_LIBRARY_FALLBACK = False
 USE_STEM_KERNEL = True
+FUSE_BN_POOL = os.environ.get("QB_FUSE_BN_POOL", "1") != "0"     # stem: max-pool straight from RangeBN's codes (RangeBN.forward_relu_pool)
 FUSE_QUANT_ROWSUM = os.environ.get("QB_FUSE_ROWSUM", "1") != "0"      # conv input quantizer also emits the per-pixel code sums (qb_fakequant_affine_rowsum)
 # one process: RangeBN statistics + per-channel finalize in one call (qb_rangebn_stats_finalize_nhwc).  Off by default: measured
 # 0.3 % SLOWER per training step than the two launches (profiles/ab_fusions_r02r.txt) - the single CTA serialises the fold of
@@ -1130,6 +1131,35 @@ class _ApplyReLUFn(Function):
         return dg, (dg if ctx.needs_input_grad[1] else None), None
 
 
+class _ApplyPoolFn(Function):
+    """Second half of RangeBN.forward_relu_pool: max-pooling straight from the codes of the statistics pass (the normalised
+    tensor is never written), then the ReLU and the next QuantMeasure's statistics on the 4x smaller pooled tensor - the
+    relu(maxpool(.)) evaluation of glue.MaxPool2d.relu_pool.  Backward: the one-pass gather of qb_maxpool2d_relu_nhwc_bwd
+    (gradient w.r.t. the RangeBN output with its range), handed to the _RangeBNFn node through the placeholder ``h``."""
+
+    @staticmethod
+    def forward(ctx, h, d, k, stride, pad):
+        from . import glue
+        B, Cn, HW = d["dims"]
+        shape = tuple(d["like"].shape)
+        out, idx = _abi.rangebn_apply_maxpool(d["xc"], shape, d["vec"], d["has_gamma"], d["has_beta"], d["q_range"], d["q_bits"],
+                                              k, stride, pad)
+        out, stats = _abi.relu_measure(out)
+        glue._last["stats"] = stats
+        ctx.save_for_backward(idx, out)
+        ctx.geom = (shape, k, stride, pad)
+        return out
+
+    @staticmethod
+    def backward(ctx, g):
+        idx, out = ctx.saved_tensors
+        shape, k, stride, pad = ctx.geom
+        g = _abi._f32c(g, "grad").contiguous(memory_format=torch.channels_last)
+        dx, rng = _abi.maxpool2d_relu_nhwc_bwd(g, idx, out, shape, k, stride, pad)
+        _stash_grad_range(dx, rng)
+        return dx, None, None, None, None
+
+
 class RangeBN(nn.Module):
     """quantize.py:435-505 ("normalized RangeBN")."""
 
@@ -1214,6 +1244,31 @@ class RangeBN(nn.Module):
             _stash_fwd_stats(out, stats)
         if out.requires_grad:
             glue._relu_out["t"] = (out, out._version)
+        return out
+
+
+    def forward_relu_pool(self, x, relu, pool):
+        """``pool(relu(self(x)))`` - the stem tail conv1 -> bn1 -> relu -> maxpool of models/resnet_quantized.py:147-150 - with
+        the pooling reading the uint8 codes of this module's statistics pass and normalising the nine window elements on the
+        fly (qb_rangebn_apply_maxpool_nhwc): the full-size normalised tensor (822 MB for ResNet-18 at batch 256) is neither
+        written nor read.  Same values and gradients as ``pool.relu_pool(self(x), relu)``, which runs whenever this does not apply."""
+        from . import glue
+        qi = self.quantize_input
+        k, s, p = pool.kernel_size, pool.stride, pool.padding
+        ok = (FUSE_BN_POOL and isinstance(relu, glue.ReLU) and isinstance(pool, glue.MaxPool2d) and relu.training and self.training
+              and x.dim() == 4 and x.is_cuda and x.dtype == torch.float32 and _abi.is_nhwc(x) and qi.enable_quant
+              and qi.num_bits <= 8 and x.shape[1] % 8 == 0 and x.numel() < 2 ** 32 and x.data_ptr() % 32 == 0
+              and torch.is_grad_enabled() and x.requires_grad and pool.dilation == 1 and not pool.ceil_mode
+              and not pool.return_indices and glue._native_ok(x, k, s, p))
+        if not ok:
+            return pool.relu_pool(self(x), relu)
+        d = {}
+        h = _RangeBNFn.apply(x, self.weight, self.bias, self.running_mean, self.running_var, self.training, self.momentum,
+                             self.num_chunks, self.eps, self.num_bits, self.num_bits_grad, qi.measure(x), qi.num_bits, d)
+        out = _ApplyPoolFn.apply(h, d, k, s, p)
+        stats, glue._last["stats"] = glue._last["stats"], None
+        if stats is not None:
+            _stash_fwd_stats(out, stats)
         return out
 
 

@@ -389,3 +389,73 @@ def test_cross_entropy_matches_torch(lib, B, C):
     w = torch.rand(C, generator=gen).to(DEV)
     assert torch.equal(glue.CrossEntropyLoss(weight=w)(logits, target), nn.CrossEntropyLoss(weight=w)(logits, target))
     assert torch.equal(glue.CrossEntropyLoss(reduction="sum")(logits, target), nn.CrossEntropyLoss(reduction="sum")(logits, target))
+
+
+@pytest.mark.parametrize("shape", [(8, 64, 28, 28), (4, 16, 9, 11), (2, 64, 112, 112), (3, 8, 5, 4)])
+def test_rangebn_forward_relu_pool_equals_the_composition(lib, shape):
+    """RangeBN.forward_relu_pool (qb_rangebn_apply_maxpool_nhwc: 3x3/2 max-pooling straight from the codes of the statistics pass,
+    the normalised tensor never written) == maxpool.relu_pool(bn(x), relu) bit for bit: output, stashed statistics of the next
+    layer, running buffers and - under the same injected noise - every gradient; and the kernel alone against pooling the
+    materialised normalisation (values and window indices)."""
+    from qtorch_b200 import glue, quantize as Q
+    torch.manual_seed(7)
+    B, C, H, W = shape
+    x = (torch.randn(shape, device=DEV) * 2 + 0.3).contiguous(memory_format=torch.channels_last)
+    # --- kernel level
+    HW = H * W
+    gamma, beta = torch.rand(C, device=DEV) + 0.5, torch.randn(C, device=DEV)
+    rm, rv = torch.zeros(C, device=DEV), torch.zeros(C, device=DEV)
+    qr = torch.tensor([float(x.min()) * 0.9, float(x.max()) * 0.8], device=DEV)
+    xc = torch.empty(x.numel(), dtype=torch.uint8, device=DEV)
+    K = 16 if (B * HW) % 16 == 0 else 1
+    red, amax, amin = lib.rangebn_stats(x, B, C, HW, K, nhwc=True, q_range=qr, q_bits=8, x_codes_out=xc)
+    vec = lib.rangebn_finalize(red, C, K, B * HW, B * HW / K, 1e-5, 0.1, True, 8, gamma, beta, rm, rv)
+    # the packed-byte window search (maximum of the codes, one normalisation per channel) against pooling the materialised
+    # normalisation: positive and negative slopes, a channel with gamma == 0 (every element equal: the first one wins) and one
+    # whose normalised values collapse onto beta (that thread must take the element-wise form) - set in the quantized vectors
+    vec = vec.clone()
+    vec[3, 1] = -vec[3, 1]
+    vec[3, 2] = 0.0
+    vec[3, 3], vec[4, 3] = 1e-9, 1.0
+    vec[3, 5] = -0.0
+    for has_gamma, has_beta in ((True, True), (True, False), (False, True), (False, False)):
+        full = lib.rangebn_apply(x, B, C, HW, vec, has_gamma, has_beta, nhwc=True, q_range=qr, q_bits=8, x_codes=xc)
+        want, widx = lib.maxpool2d_nhwc_fwd(full, 3, 2, 1)
+        got, gidx = lib.rangebn_apply_maxpool(xc, shape, vec, has_gamma, has_beta, qr, 8, 3, 2, 1)
+        assert torch.equal(got.view(torch.int32), want.view(torch.int32)) and torch.equal(gidx, widx), (has_gamma, has_beta)
+    # --- module level
+    if (B * HW) % 16 != 0:
+        return
+    go_shape = want.shape
+    go = torch.randn(go_shape, device=DEV).contiguous(memory_format=torch.channels_last)
+    noise = torch.rand(shape, device=DEV) - 0.5
+    state = Q.RangeBN(C).state_dict()
+    res = []
+    for fused in (True, False):
+        bn = Q.RangeBN(C)
+        bn.load_state_dict(state)
+        bn = bn.to(DEV).train()
+        relu, pool = glue.ReLU(inplace=True).train(), glue.MaxPool2d(3, 2, 1)
+        xi = x.clone().requires_grad_()
+        prev = Q.set_noise_provider(lambda shp: noise.clone())
+        Q.FUSE_BN_POOL = fused
+        try:
+            lib.profile_begin()
+            y = bn.forward_relu_pool(xi, relu, pool)
+            names = [n[0] for n in lib.profile_end()]
+            stats = Q._take_fwd_stats(y.detach())
+            out = y.detach().clone()
+            y.backward(go)
+        finally:
+            Q.FUSE_BN_POOL = True
+            Q.set_noise_provider(prev)
+        res.append(dict(out=out, stats=stats.clone(), names=names, dx=xi.grad.clone(), dgamma=bn.weight.grad.clone(),
+                        dbeta=bn.bias.grad.clone(), buffers={k: v.clone() for k, v in bn.state_dict().items()}))
+    f, c = res
+    assert "qb_rangebn_apply_maxpool_nhwc" in f["names"] and "qb_rangebn_apply_nhwc" not in f["names"], f["names"]
+    assert "qb_rangebn_apply_nhwc" in c["names"] and "qb_maxpool2d_nhwc_fwd" in c["names"], c["names"]
+    assert torch.equal(f["out"], c["out"]) and torch.equal(f["stats"], c["stats"])
+    for k in ("dx", "dgamma", "dbeta"):
+        assert torch.equal(f[k], c[k]), k
+    for k, v in c["buffers"].items():
+        assert torch.equal(f["buffers"][k], v), k

@@ -70,9 +70,9 @@ def test_benchmarked_model_train_step_vs_oracle(name):
     from qtorch_b200 import glue
     crit = glue.CrossEntropyLoss()            # CUDA logits: libqb200; the oracle's CPU logits: torch's own path
     first = {}
-    if name == "resnet18":
-        ref.bn1.register_forward_hook(lambda m, i, o: first.__setitem__("ref", o.detach().clone()))
-        mod.bn1.register_forward_hook(lambda m, i, o: first.__setitem__("cuda", o.detach().cpu().clone()))
+    if name == "resnet18":   # the first RangeBN runs fused with ReLU + max-pooling (RangeBN.forward_relu_pool): compare what layer1 receives
+        ref.layer1.register_forward_pre_hook(lambda m, i: first.__setitem__("ref", i[0].detach().clone()))
+        mod.layer1.register_forward_pre_hook(lambda m, i: first.__setitem__("cuda", i[0].detach().cpu().clone()))
     else:      # MobileNet's first RangeBN runs fused with its ReLU (RangeBN.forward_relu): compare what the next block receives
         ref.features[3].register_forward_pre_hook(lambda m, i: first.__setitem__("ref", i[0].detach().clone()))
         mod.features[3].register_forward_pre_hook(lambda m, i: first.__setitem__("cuda", i[0].detach().cpu().clone()))
