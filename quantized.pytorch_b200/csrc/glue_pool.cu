@@ -63,7 +63,7 @@ __global__ void __launch_bounds__(256) k_maxpool_fwd_nhwc(const void* __restrict
     // CODES, fast form.  The normalisation is a monotone map of the code (every rounded fp32 operation is monotone in its
     // operand), so the window maximum of the normalised values sits at the window maximum of the codes - or the minimum, for a
     // channel whose scale * gamma is negative - and ONE element per channel is normalised instead of nine: the window search
-    // runs on packed bytes (__vmaxu4 / __vcmpgtu4, 8 channels in two words).  "First maximal element wins" carries over as long
+    // runs on packed 16-bit composites of key and tap (two channels per word).  "First maximal element wins" carries over as long
     // as distinct codes give distinct normalised values; that is checked per channel from the images of codes 0 and 255 (their
     // spacing per code step must exceed 2^-18 of the magnitudes involved, 8x the worst accumulated rounding error of the four
     // operations), a channel with gamma == 0 maps every code to one value (first valid element wins, as in ATen), and a thread
@@ -91,25 +91,50 @@ __global__ void __launch_bounds__(256) k_maxpool_fwd_nhwc(const void* __restrict
         }
     }
     if (CODES && fast) {
-        uint2 best = make_uint2(0u, 0u), bidx = make_uint2(0u, 0u), firstpk = make_uint2(0u, 0u);
-        for (int kh = 0; kh < g.k; ++kh) {
-            const int h = h0 + kh;
-            if (h < 0 || h >= g.H) continue;
-            for (int kw = 0; kw < g.k; ++kw) {
-                const int w = w0 + kw;
-                if (w < 0 || w >= g.W) continue;
-                const uint2 pk = __ldg(reinterpret_cast<const uint2*>(xc + (((size_t)b * g.H + h) * g.W + w) * g.C + c0));
-                const uint2 key = make_uint2((pk.x ^ xorm.x) & andm.x, (pk.y ^ xorm.y) & andm.y);
-                const uint32_t code4 = (uint32_t)(kh * g.k + kw) * 0x01010101u;
-                if (first) {
-                    best = key; bidx = make_uint2(code4, code4); firstpk = pk; first = false;
-                } else {
-                    const uint32_t gx = __vcmpgtu4(key.x, best.x), gy = __vcmpgtu4(key.y, best.y);
-                    best.x = __vmaxu4(best.x, key.x); best.y = __vmaxu4(best.y, key.y);
-                    bidx.x = (bidx.x & ~gx) | (code4 & gx); bidx.y = (bidx.y & ~gy) | (code4 & gy);
+        // per channel the 16-bit composite (key << 8) | (255 - tap): its maximum over the window is the largest key and, among
+        // equal keys, the EARLIEST tap ("first maximal element wins"); two channels per word, one PRMT to build a pair from the
+        // key bytes and one packed 16-bit maximum per pair and tap (the byte-wise __vmaxu4 / __vcmpgtu4 pair is emulated on this
+        // architecture: ~25 instructions per tap).  Every valid tap's composite is >= 31, so 0 is the identity.
+        uint32_t bp[4] = {0u, 0u, 0u, 0u};
+        uint2 firstpk = make_uint2(0u, 0u);
+        auto tap_in = [&](const uint2& pk, uint32_t tap) {
+            const uint32_t kx = (pk.x ^ xorm.x) & andm.x, ky = (pk.y ^ xorm.y) & andm.y, tinv = 255u - tap;
+            bp[0] = __vmaxu2(bp[0], __byte_perm(kx, tinv, 0x1404));
+            bp[1] = __vmaxu2(bp[1], __byte_perm(kx, tinv, 0x3424));
+            bp[2] = __vmaxu2(bp[2], __byte_perm(ky, tinv, 0x1404));
+            bp[3] = __vmaxu2(bp[3], __byte_perm(ky, tinv, 0x3424));
+            if (first) { firstpk = pk; first = false; }
+        };
+        if (g.k == 3) {
+#pragma unroll
+            for (int kh = 0; kh < 3; ++kh) {
+                const int h = h0 + kh;
+                if (h < 0 || h >= g.H) continue;
+                const uint8_t* rowp = xc + (((size_t)b * g.H + h) * g.W) * g.C + c0;
+#pragma unroll
+                for (int kw = 0; kw < 3; ++kw) {
+                    const int w = w0 + kw;
+                    if (w < 0 || w >= g.W) continue;
+                    tap_in(__ldg(reinterpret_cast<const uint2*>(rowp + (size_t)w * g.C)), (uint32_t)(kh * 3 + kw));
+                }
+            }
+        } else {
+            for (int kh = 0; kh < g.k; ++kh) {
+                const int h = h0 + kh;
+                if (h < 0 || h >= g.H) continue;
+                for (int kw = 0; kw < g.k; ++kw) {
+                    const int w = w0 + kw;
+                    if (w < 0 || w >= g.W) continue;
+                    tap_in(__ldg(reinterpret_cast<const uint2*>(xc + (((size_t)b * g.H + h) * g.W + w) * g.C + c0)), (uint32_t)(kh * g.k + kw));
                 }
             }
         }
+        // bytes 1 and 3 of a pair word are the winning keys, bytes 0 and 2 the inverted taps
+        uint2 best, bidx;
+        best.x = __byte_perm(bp[0], bp[1], 0x7531);
+        best.y = __byte_perm(bp[2], bp[3], 0x7531);
+        bidx.x = ~__byte_perm(bp[0], bp[1], 0x6420);
+        bidx.y = ~__byte_perm(bp[2], bp[3], 0x6420);
         const uint2 win = make_uint2(((best.x ^ xorm.x) & andm.x) | (firstpk.x & ~andm.x), ((best.y ^ xorm.y) & andm.y) | (firstpk.y & ~andm.y));
         float xh[8];
         affine_deq8(win, aq.p, xh);
