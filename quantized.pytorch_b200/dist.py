@@ -188,6 +188,80 @@ def allreduce_gradients(model, group=None, average=True):
                 p.grad.div_(world)
 
 
+class OverlappedGradReducer:
+    """Gradient all-reduce overlapped with backward (what DistributedDataParallel's buckets do, for this package's explicit
+    reduction): the parameters are grouped, in reverse registration order (the order backward produces their gradients), into
+    buckets of ~``bucket_bytes``; a post-accumulate hook on every parameter counts its bucket down and the last one to arrive
+    launches the bucket's asynchronous all-reduce (NCCL: on the process group's own stream, concurrent with the rest of
+    backward); ``finish()`` after ``loss.backward()`` waits for the handles, applies the 1/world scaling and writes the reduced
+    values back into ``.grad``.  Same result as ``allreduce_gradients`` (a SUM all-reduce is element-wise: the grouping does not
+    change any sum), including the treatment of RangeBN's gamma / beta.  Opt-in; not capturable in a CUDA graph together with
+    the hooks' Python bookkeeping, so the benchmark's captured step keeps the flat-bucket form."""
+
+    def __init__(self, model, group=None, average=True, bucket_bytes=8 << 20):
+        self.group, self.average = group, average
+        self.world = dist.get_world_size(group)
+        replicated = set()
+        for m in model.modules():
+            if isinstance(m, Q.RangeBN):
+                replicated.update(id(p) for p in (m.weight, m.bias) if p is not None)
+        self.replicated = [p for p in model.parameters() if id(p) in replicated and p.requires_grad]
+        params = [p for p in model.parameters() if id(p) not in replicated and p.requires_grad]
+        self.buckets, cur, size = [], [], 0
+        for p in reversed(params):
+            cur.append(p)
+            size += p.numel() * p.element_size()
+            if size >= bucket_bytes:
+                self.buckets.append(cur)
+                cur, size = [], 0
+        if cur:
+            self.buckets.append(cur)
+        self._where = {id(p): i for i, b in enumerate(self.buckets) for p in b}
+        self._left = [len(b) for b in self.buckets]
+        self._pending = []
+        self._hooks = [p.register_post_accumulate_grad_hook(self._arrived) for p in params]
+
+    def _arrived(self, p):
+        i = self._where[id(p)]
+        self._left[i] -= 1
+        if self._left[i] == 0:
+            grads = [q.grad for q in self.buckets[i]]
+            flat = torch._utils._flatten_dense_tensors(grads)
+            self._pending.append((i, flat, grads, dist.all_reduce(flat, op=dist.ReduceOp.SUM, group=self.group, async_op=True)))
+
+    def finish(self):
+        """Call once after backward: every bucket is reduced, scaled and back in ``.grad``; counters are re-armed."""
+        done = set()
+        for i, flat, grads, work in self._pending:
+            work.wait()
+            if self.average:
+                flat.div_(self.world)
+            for g, f in zip(grads, torch._utils._unflatten_dense_tensors(flat, grads)):
+                g.copy_(f)
+            done.add(i)
+        self._pending = []
+        for i, b in enumerate(self.buckets):               # parameters that received no gradient this step leave a bucket open
+            if i not in done:
+                grads = [q.grad for q in b if q.grad is not None]
+                if grads:
+                    flat = torch._utils._flatten_dense_tensors(grads)
+                    dist.all_reduce(flat, op=dist.ReduceOp.SUM, group=self.group)
+                    if self.average:
+                        flat.div_(self.world)
+                    for g, f in zip(grads, torch._utils._unflatten_dense_tensors(flat, grads)):
+                        g.copy_(f)
+        self._left = [len(b) for b in self.buckets]
+        if self.average:
+            for p in self.replicated:
+                if p.grad is not None:
+                    p.grad.div_(self.world)
+
+    def remove(self):
+        for h in self._hooks:
+            h.remove()
+        self._hooks = []
+
+
 def shard_batch(x, rank=None, world=None):
     """Contiguous slice of the global batch for this rank (so RangeBN chunks map to whole ranks)."""
     rank = _state["rank"] if rank is None else rank

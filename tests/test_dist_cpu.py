@@ -91,6 +91,30 @@ def _worker(rank, world, port, ret):
         qdist.allreduce_gradients(m)
         for i, p in enumerate(m.parameters()):
             assert torch.allclose(p.grad, torch.full_like(p, 1.5 * (i + 1)))
+        # the same reduction overlapped with backward: buckets launched from post-accumulate hooks as their gradients arrive
+        torch.manual_seed(5)
+        net = torch.nn.Sequential(torch.nn.Linear(6, 16), torch.nn.ReLU(), torch.nn.Linear(16, 16), torch.nn.ReLU(),
+                                  torch.nn.Linear(16, 4), Q.RangeBN(4))
+        qdist.broadcast_parameters(net)
+        twin = torch.nn.Sequential(torch.nn.Linear(6, 16), torch.nn.ReLU(), torch.nn.Linear(16, 16), torch.nn.ReLU(),
+                                   torch.nn.Linear(16, 4), Q.RangeBN(4))
+        twin.load_state_dict(net.state_dict())
+        ovl = qdist.OverlappedGradReducer(net, bucket_bytes=200)       # small buckets: several of them, in backward order
+        assert len(ovl.buckets) >= 3 and ovl.buckets[0][0] is net[4].bias
+        xin = torch.randn(8, 6, generator=torch.Generator().manual_seed(40 + rank))
+        for step in range(2):                                          # counters re-arm between steps
+            for mdl in (net, twin):
+                for p_ in mdl.parameters():
+                    p_.grad = None
+            for mdl in (net, twin):
+                out = mdl[:5](xin * (step + 1))
+                gam = (out * mdl[5].weight + mdl[5].bias).square().mean()   # gamma / beta get (replicated-style) gradients too
+                gam.backward()
+            ovl.finish()
+            qdist.allreduce_gradients(twin)
+            for a, b in zip(net.parameters(), twin.parameters()):
+                assert torch.equal(a.grad, b.grad), (step, a.shape)
+        ovl.remove()
         qdist.shutdown()
         assert Q._reducer is None
         ret[rank] = "ok"
