@@ -61,3 +61,11 @@ def test_argument_errors_reported():
     assert rc == -1 and "bits" in _abi.last_error()
     rc = lib.qb_rangebn_stats(1, 3, 2, 5, 16, None, None, 1, 1, 1 << 20, None)
     assert rc == -1 and "divisible" in _abi.last_error()
+
+
+def test_every_entry_point_is_documented():
+    """INTEGRATION.md names every function include/qb200.h declares (the reference-side binding table stays complete)."""
+    text = open(os.path.join(ROOT, "INTEGRATION.md")).read()
+    missing = [n for n in declared_functions() if n not in text
+               and not (n.endswith("_supported") and "`*_supported` functions" in text)]
+    assert not missing, missing
